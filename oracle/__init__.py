@@ -1,0 +1,172 @@
+"""CPU oracles for the extend/shadow traversal path -- TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this package.  ``Oracle("ref")`` drives oracle/_ref/liboracle_ref.so (the reference's own unmodified
+lib/RenderCore_Bart/bvh.cpp + common.h compiled in place); ``Oracle("port")`` drives
+oracle/liboracle_port.so (the plain-C restatement, bart_port.c).  Both expose the same calls.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "liboracle_port.so")
+REF_SO = os.path.join(HERE, "_ref", "liboracle_ref.so")
+
+_f = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_i = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+
+
+def build() -> None:
+    """Compile the checkers (port always; _ref only where /root/reference exists)."""
+    subprocess.run(["make", "-s", "-C", HERE], check=True)
+
+
+def have_ref() -> bool:
+    return os.path.exists(REF_SO)
+
+
+def _load(kind: str):
+    path = REF_SO if kind == "ref" else PORT_SO
+    if not os.path.exists(path):
+        build()
+    lib = C.CDLL(path)
+    p = kind + "_"
+    g = lambda n: getattr(lib, p + n)
+    g("scene_create").restype = C.c_void_p
+    g("scene_destroy").argtypes = [C.c_void_p]
+    g("set_geometry").argtypes = [C.c_void_p, C.c_int, _f, C.c_int]
+    g("set_instance").argtypes = [C.c_void_p, C.c_int, C.c_int, _f]
+    g("build_toplevel").argtypes = [C.c_void_p]
+    g("blas_build_seconds").argtypes = [C.c_void_p]
+    g("blas_build_seconds").restype = C.c_double
+    g("tlas_build_seconds").argtypes = [C.c_void_p]
+    g("tlas_build_seconds").restype = C.c_double
+    g("get_inv_transform").argtypes = [C.c_void_p, C.c_int, _f]
+    if kind == "ref":
+        g("trace").argtypes = [C.c_void_p, C.c_int, _f, _f, _f, _i, C.c_int]
+    else:
+        g("trace").argtypes = [C.c_void_p, C.c_int, _f, _f, _f, _i, _i, C.c_int]
+        g("trace_brute").argtypes = [C.c_void_p, C.c_int, _f, _f, _f, _i, _i, C.c_int]
+        g("trace_visits").argtypes = [C.c_void_p, C.c_int, _f, _f, _f, _i, _i, _i, C.c_int]
+        g("trace_single").argtypes = [C.c_void_p, C.c_int, _f, _f, _i, _i, _f]
+        g("normalize_n").argtypes = [C.c_int, _f]
+        g("blas_node_count").argtypes = [C.c_void_p, C.c_int]
+    g("intersect_triangle").argtypes = [_f, _f, _f, _f]
+    g("intersect_aabb").argtypes = [_f, _f, _f, _f, _f]
+    g("normalize").argtypes = [_f, _f]
+    return lib
+
+
+class Oracle:
+    """One scene in one of the two CPU oracles.  Method names follow the CoreAPI calls they restate."""
+
+    def __init__(self, kind: str = "port"):
+        assert kind in ("ref", "port")
+        self.kind = kind
+        self.lib = _load(kind)
+        self._p = kind + "_"
+        self.h = C.c_void_p(self._fn("scene_create")())
+        self.n_inst = 0
+
+    def _fn(self, n):
+        return getattr(self.lib, self._p + n)
+
+    def close(self):
+        if self.h:
+            self._fn("scene_destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # RenderCore::SetGeometry (lib/RenderCore_Bart/rendercore.cpp:47)
+    def SetGeometry(self, mesh_idx: int, verts: np.ndarray):
+        verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+        rc = self._fn("set_geometry")(self.h, mesh_idx, verts, verts.shape[0])
+        assert rc == 0
+
+    # RenderCore::SetInstance (rendercore.cpp:82)
+    def SetInstance(self, inst_idx: int, mesh_idx: int, mat16=None):
+        m = np.eye(4, dtype=np.float32).reshape(16) if mat16 is None else np.ascontiguousarray(mat16, np.float32).reshape(16)
+        rc = self._fn("set_instance")(self.h, inst_idx, mesh_idx, m)
+        assert rc == 0
+        self.n_inst = max(self.n_inst, inst_idx + 1)
+
+    # TopLevelBVH::Rebuild, called per frame from RenderCore::Render (rendercore.cpp:199)
+    def UpdateToplevel(self):
+        self._fn("build_toplevel")(self.h)
+
+    def inv_transform(self, inst_idx: int) -> np.ndarray:
+        out = np.empty(16, np.float32)
+        self._fn("get_inv_transform")(self.h, inst_idx, out)
+        return out
+
+    @property
+    def blas_build_seconds(self):
+        return self._fn("blas_build_seconds")(self.h)
+
+    @property
+    def tlas_build_seconds(self):
+        return self._fn("tlas_build_seconds")(self.h)
+
+    def trace(self, O, D, nthreads: int = 1, mode: str = "bvh"):
+        """Closest hit per ray.  Returns (t float32[n], prim int32[n], inst int32[n]); miss = (1e34, -1, -1).
+        ``inst`` is -1-filled for kind='ref' (the reference API cannot return it)."""
+        O = np.ascontiguousarray(O, np.float32).reshape(-1, 3)
+        D = np.ascontiguousarray(D, np.float32).reshape(-1, 3)
+        n = O.shape[0]
+        t = np.empty(n, np.float32)
+        prim = np.empty(n, np.int32)
+        inst = np.full(n, -1, np.int32)
+        if self.kind == "ref":
+            assert mode == "bvh"
+            self._fn("trace")(self.h, n, O, D, t, prim, nthreads)
+        else:
+            self._fn("trace" if mode == "bvh" else "trace_brute")(self.h, n, O, D, t, prim, inst, nthreads)
+        return t, prim, inst
+
+    def trace_visits(self, O, D, nthreads: int = 1):
+        assert self.kind == "port"
+        O = np.ascontiguousarray(O, np.float32).reshape(-1, 3)
+        D = np.ascontiguousarray(D, np.float32).reshape(-1, 3)
+        n = O.shape[0]
+        t = np.empty(n, np.float32); prim = np.empty(n, np.int32); inst = np.empty(n, np.int32); vis = np.empty(n, np.int32)
+        self._fn("trace_visits")(self.h, n, O, D, t, prim, inst, vis, nthreads)
+        return t, prim, inst, vis
+
+    def t_of(self, O, D, inst, prim):
+        """Reference-arithmetic t of given (inst, prim) pairs (1e34 where the triangle test rejects)."""
+        assert self.kind == "port"
+        O = np.ascontiguousarray(O, np.float32).reshape(-1, 3)
+        D = np.ascontiguousarray(D, np.float32).reshape(-1, 3)
+        out = np.empty(O.shape[0], np.float32)
+        self._fn("trace_single")(self.h, O.shape[0], O, D, np.ascontiguousarray(inst, np.int32), np.ascontiguousarray(prim, np.int32), out)
+        return out
+
+    def occluded(self, O, D, tmax, nthreads: int = 1):
+        """Any-hit as the reference defines it: closest t < tmax (raytracer.cpp:135-139,155-159)."""
+        t, _, _ = self.trace(O, D, nthreads)
+        return t < np.asarray(tmax, np.float32)
+
+    def intersect_triangle(self, O, D, v9, t0=3.0e38):
+        t = np.array([t0], np.float32)
+        r = self._fn("intersect_triangle")(np.asarray(O, np.float32), np.asarray(D, np.float32), np.asarray(v9, np.float32).reshape(9), t)
+        return bool(r), float(t[0])
+
+    def intersect_aabb(self, O, D, bmin, bmax, t0=3.0e38):
+        t = np.array([t0], np.float32)
+        r = self._fn("intersect_aabb")(np.asarray(O, np.float32), np.asarray(D, np.float32), np.asarray(bmin, np.float32), np.asarray(bmax, np.float32), t)
+        return bool(r), float(t[0])
+
+    def normalize(self, v):
+        out = np.empty(3, np.float32)
+        self._fn("normalize")(np.asarray(v, np.float32), out)
+        return out
