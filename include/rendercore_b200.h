@@ -1,0 +1,121 @@
+/* include/rendercore_b200.h -- C ABI of libRenderCore_B200.so.
+ *
+ * Two groups of entry points:
+ *  (1) the Lighthouse 2 plugin symbols the RenderSystem binds with dlsym
+ *      (lib/RenderSystem/core_api_base.cpp:119-132; declared lib/RenderCore_Bart/core_api.h:63-64):
+ *          CoreAPI_Base* CreateCore();   void DestroyCore();
+ *      CreateCore returns the C++ object whose vtable is restated in include/lh2_abi.h.
+ *  (2) a flat, headless `b200_*` layer (plain pointers and sizes, no C++ and no torch types) that
+ *      exposes the same operations one-to-one plus the raw extend/shadow queries, so tests, the bench
+ *      and foreign hosts can drive the core without a C++ vtable.  Each function cites the reference
+ *      interface it stands for.
+ *
+ * All functions return 0 on success, non-zero on failure (message via b200_last_error); the C++
+ * CoreAPI shim turns non-zero into the reference's fatal-error convention (platform/system.cpp:221).
+ * There is NO CPU fallback: b200_create fails if no sm_100 device is usable.
+ *
+ * Ray / hit wire formats:
+ *   ray   : float4 O4 = (Ox,Oy,Oz,tmin), float4 D4 = (Dx,Dy,Dz,tmax)   -- 32 B/ray, two SoA planes
+ *           (OptiX Prime RAY_ORIGIN_TMIN_DIRECTION_TMAX, RenderCore_OptixPrime_B/rendercore.cpp:199;
+ *            the optix7 core stores the same two float4 planes, rendercore_optix7/optix/.optix.cu:125-135)
+ *   hit   : float4 {as_float(u16 | v16<<16), as_float(instIdx), as_float(primIdx), t} -- 16 B/ray,
+ *           miss = prim -1, inst -1(0xffffffff), t = 1e34  (rendercore_optix7/optix/.optix.cu:119-122,183-186)
+ *   shadow: 1 bit per ray, bit set = occluded (Prime HIT_BITMASK, RenderCore_OptixPrime_B/rendercore.cpp:203)
+ */
+#ifndef RENDERCORE_B200_H
+#define RENDERCORE_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_API __attribute__((visibility("default")))
+
+typedef struct b200_core b200_core; /* opaque */
+
+/* isect modes, Setting("isectMode", v) */
+#define B200_ISECT_REFERENCE 0  /* bit-exact restatement of Ray::IntersectTriangle + TLAS-leaf ray transform (parity runs) */
+#define B200_ISECT_WATERTIGHT 1 /* fused, scale-invariant Moeller-Trumbore with shared-edge consistent rounding */
+
+/* ---- lifetime: CreateCore/Init/Shutdown (lib/RenderCore_Bart/core_api.cpp:20-47,64-69) ---- */
+B200_API int b200_create( b200_core** out, int device );
+B200_API void b200_destroy( b200_core* c );
+B200_API const char* b200_last_error( void );
+/* all work of this core is enqueued on `stream` (a cudaStream_t; 0 = the legacy default stream) */
+B200_API int b200_set_stream( b200_core* c, void* stream );
+
+/* ---- scene: CoreAPI_Base::SetGeometry / SetInstance / UpdateToplevel (core_api_base.h:108-112) ---- */
+/* vertexData: float4[3*triangleCount], triangle-expanded (host_mesh.cpp:525-527).  triangles: optional
+ * CoreTri[triangleCount] (176 B each; only `material` is kept).  First call for a meshIdx builds the
+ * wide BVH; later calls with the same triangle count refit it on the GPU (Setting "refit" = 0 forces a rebuild). */
+B200_API int b200_set_geometry( b200_core* c, int meshIdx, const float* vertexData, int vertexCount, int triangleCount,
+	const void* triangles, const uint32_t* alphaFlags );
+/* transform: row-major float[16] (mat4::cell).  modelIdx == -1 ends the stream and truncates
+ * (lib/RenderSystem/rendersystem.cpp:167-169). */
+B200_API int b200_set_instance( b200_core* c, int instanceIdx, int modelIdx, const float* transform );
+B200_API int b200_update_toplevel( b200_core* c );
+/* GPU refit of an already-built mesh from new positions (host float4[3T]); what SetGeometry does on update */
+B200_API int b200_refit( b200_core* c, int meshIdx, const float* vertexData, int vertexCount );
+/* same, positions already resident in device memory (device float4[3T]) */
+B200_API int b200_refit_device( b200_core* c, int meshIdx, const void* dVertexData, int vertexCount );
+
+/* ---- CoreAPI_Base::Setting (core_api_base.h:92; keys rendersystem.cpp:231-236 + isectMode, refit, maxPathLength, spp, tileShard*) ---- */
+B200_API int b200_setting( b200_core* c, const char* name, float value );
+
+/* ---- raw wavefront queries: the extend / shadow waves ---- */
+/* host buffers; H2D + kernel + D2H + synchronise inside the call */
+B200_API int b200_trace_closest( b200_core* c, const float* O4, const float* D4, int n, float* hits );
+B200_API int b200_trace_any( b200_core* c, const float* O4, const float* D4, int n, uint32_t* occludedBits );
+/* device buffers (cudaMalloc'ed by anyone in this process); asynchronous on the core's stream.
+ * occludedBits must hold (n+31)/32 words; it is cleared by the call. */
+B200_API int b200_trace_closest_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dHits );
+B200_API int b200_trace_any_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dOccludedBits );
+/* per-ray traversal counters of the LAST b200_trace_closest call with Setting("countSteps",1):
+ * nodes visited and triangles tested (the analogue of the reference's `int* c`, bvh.cpp:259) */
+B200_API int b200_read_step_counters( b200_core* c, int n, uint32_t* nodesVisited, uint32_t* trisTested );
+
+/* ---- frame: SetTarget / SetLights / Render / GetCoreStats (core_api_base.h:84-96,102-105) ---- */
+B200_API int b200_set_target( b200_core* c, int width, int height, int spp );
+B200_API int b200_set_point_light( b200_core* c, const float* position3, const float* radiance3 );
+B200_API int b200_set_sky( b200_core* c, const float* radiance3 );
+/* view: ViewPyramid (68 bytes, common_classes.h:362-385).  converge: 0 = Converge, 1 = Restart */
+B200_API int b200_render( b200_core* c, const void* viewPyramid, int converge );
+/* accumulator float4[w*h] (sum over samples; w = sample count) and the normalised RGBA32F frame */
+B200_API int b200_read_accumulator( b200_core* c, float* dst );
+B200_API int b200_read_frame( b200_core* c, float* dst );
+B200_API void* b200_device_accumulator( b200_core* c ); /* device pointer, for NCCL gathers by the host layer */
+/* stats: the CoreStats fields (core_api_base.h:30-61) flattened; see struct below */
+typedef struct b200_stats {
+	uint32_t smCount, ccMajor, ccMinor, vramMB;
+	float bvhBuildTime;                 /* ms, host SAH build + conversion + upload (last SetGeometry batch) */
+	float refitTime, tlasTime;          /* ms */
+	uint32_t totalRays, totalExtensionRays, totalShadowRays;
+	float renderTime;                   /* ms, whole Render() */
+	uint32_t primaryRayCount; float traceTime0;
+	uint32_t bounce1RayCount; float traceTime1;
+	uint32_t deepRayCount; float traceTimeX;
+	float shadowTraceTime, shadeTime;
+	int32_t probedInstid, probedTriid; float probedDist;
+	uint32_t wideNodeCount, triangleCount, instanceCount, tlasNodeCount;
+	uint32_t kernelLaunches;            /* kernels this core has launched since creation */
+	float lastTraceMs;                  /* device time of the last b200_trace_* kernel (CUDA events on the core's stream) */
+} b200_stats;
+B200_API int b200_get_stats( b200_core* c, b200_stats* out );
+B200_API int b200_set_probe( b200_core* c, int x, int y );
+
+/* the core behind CreateCore() (NULL before CreateCore): lets a headless host read frames / stats of the plugin instance */
+B200_API b200_core* b200_plugin_core( void );
+
+/* pinned host memory helpers for callers that want the H2D/D2H legs at full PCIe speed */
+B200_API void* b200_host_alloc( uint64_t bytes );
+B200_API void b200_host_free( void* p );
+
+/* ---- the plugin symbols themselves (declared for completeness; C++ linkage of the return type) ---- */
+#ifdef __cplusplus
+} /* extern "C" */
+namespace lh2abi { class CoreAPI_Base; }
+extern "C" B200_API lh2abi::CoreAPI_Base* CreateCore();
+extern "C" B200_API void DestroyCore();
+#endif
+
+#endif /* RENDERCORE_B200_H */

@@ -1,0 +1,253 @@
+"""ctypes driver over the C ABI of libRenderCore_B200.so (include/rendercore_b200.h).
+
+This is the test/bench-side host layer: method names follow CoreAPI_Base
+(lib/RenderSystem/core_api_base.h:84-113) so the parity tests read like calls into a reference core.
+There is no CPU fallback anywhere: if the shared library is missing or no sm_100 GPU is visible the
+constructor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libRenderCore_B200.so")
+CSRC = os.path.join(HERE, "csrc")
+
+# every symbol include/rendercore_b200.h declares (checked by tests/test_abi.py without a GPU)
+C_ABI_SYMBOLS = [
+    "b200_create", "b200_destroy", "b200_last_error", "b200_set_stream", "b200_set_geometry", "b200_set_instance",
+    "b200_update_toplevel", "b200_refit", "b200_refit_device", "b200_setting", "b200_trace_closest", "b200_trace_any",
+    "b200_trace_closest_device", "b200_trace_any_device", "b200_read_step_counters", "b200_set_target",
+    "b200_set_point_light", "b200_set_sky", "b200_render", "b200_read_accumulator", "b200_read_frame",
+    "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
+    "b200_host_free", "CreateCore", "DestroyCore",
+]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("smCount", C.c_uint32), ("ccMajor", C.c_uint32), ("ccMinor", C.c_uint32), ("vramMB", C.c_uint32),
+        ("bvhBuildTime", C.c_float), ("refitTime", C.c_float), ("tlasTime", C.c_float),
+        ("totalRays", C.c_uint32), ("totalExtensionRays", C.c_uint32), ("totalShadowRays", C.c_uint32),
+        ("renderTime", C.c_float),
+        ("primaryRayCount", C.c_uint32), ("traceTime0", C.c_float),
+        ("bounce1RayCount", C.c_uint32), ("traceTime1", C.c_float),
+        ("deepRayCount", C.c_uint32), ("traceTimeX", C.c_float),
+        ("shadowTraceTime", C.c_float), ("shadeTime", C.c_float),
+        ("probedInstid", C.c_int32), ("probedTriid", C.c_int32), ("probedDist", C.c_float),
+        ("wideNodeCount", C.c_uint32), ("triangleCount", C.c_uint32), ("instanceCount", C.c_uint32), ("tlasNodeCount", C.c_uint32),
+        ("kernelLaunches", C.c_uint32), ("lastTraceMs", C.c_float),
+    ]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class ViewPyramid(C.Structure):
+    """lib/RenderSystem/common_classes.h:362-385 (68 bytes)."""
+    _fields_ = [("pos", C.c_float * 3), ("p1", C.c_float * 3), ("p2", C.c_float * 3), ("p3", C.c_float * 3),
+                ("aperture", C.c_float), ("spreadAngle", C.c_float), ("imagePlane", C.c_float),
+                ("focalDistance", C.c_float), ("distortion", C.c_float)]
+
+
+def build_library() -> str:
+    """nvcc build of the shared library for sm_100a (works without a GPU)."""
+    subprocess.run(["make", "-s", "-j8", "-C", CSRC], check=True)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(RenderCore_B200 has no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, ip, fp, up = C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+    sig = {
+        "b200_create": ([C.POINTER(vp), ip], ip), "b200_destroy": ([vp], None), "b200_last_error": ([], C.c_char_p),
+        "b200_set_stream": ([vp, vp], ip),
+        "b200_set_geometry": ([vp, ip, vp, ip, ip, vp, vp], ip), "b200_set_instance": ([vp, ip, ip, vp], ip),
+        "b200_update_toplevel": ([vp], ip), "b200_refit": ([vp, ip, vp, ip], ip), "b200_refit_device": ([vp, ip, vp, ip], ip),
+        "b200_setting": ([vp, C.c_char_p, C.c_float], ip),
+        "b200_trace_closest": ([vp, vp, vp, ip, vp], ip), "b200_trace_any": ([vp, vp, vp, ip, vp], ip),
+        "b200_trace_closest_device": ([vp, vp, vp, ip, vp], ip), "b200_trace_any_device": ([vp, vp, vp, ip, vp], ip),
+        "b200_read_step_counters": ([vp, ip, vp, vp], ip),
+        "b200_set_target": ([vp, ip, ip, ip], ip), "b200_set_point_light": ([vp, vp, vp], ip), "b200_set_sky": ([vp, vp], ip),
+        "b200_render": ([vp, vp, ip], ip), "b200_read_accumulator": ([vp, vp], ip), "b200_read_frame": ([vp, vp], ip),
+        "b200_device_accumulator": ([vp], vp), "b200_get_stats": ([vp, C.POINTER(Stats)], ip), "b200_set_probe": ([vp, ip, ip], ip),
+        "b200_plugin_core": ([], vp), "b200_host_alloc": ([C.c_uint64], vp), "b200_host_free": ([vp], None),
+    }
+    for name, (args, res) in sig.items():
+        fn = getattr(lib, name)
+        fn.argtypes, fn.restype = args, res
+    _lib = lib
+    return lib
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def pack_rays(O, D, tmin=0.0, tmax=1e34):
+    """(O[n,3], D[n,3]) -> the two float4 planes of the wire format: O4=(O,tmin), D4=(D,tmax)."""
+    O = np.asarray(O, np.float32).reshape(-1, 3)
+    D = np.asarray(D, np.float32).reshape(-1, 3)
+    n = O.shape[0]
+    O4 = np.empty((n, 4), np.float32)
+    D4 = np.empty((n, 4), np.float32)
+    O4[:, :3], D4[:, :3] = O, D
+    O4[:, 3], D4[:, 3] = tmin, tmax
+    return O4, D4
+
+
+def unpack_hits(hits: np.ndarray):
+    """float4 hit records -> dict(t, prim, inst, u, v) following the optix7 decode macros
+    (lib/rendercore_optix7/kernels/pathtracer.h:36-40)."""
+    h = np.ascontiguousarray(hits, np.float32).reshape(-1, 4)
+    bits = h.view(np.uint32)
+    return {
+        "t": h[:, 3].copy(), "prim": bits[:, 2].view(np.int32).copy(), "inst": bits[:, 1].view(np.int32).copy(),
+        "u": (bits[:, 0] & 0xFFFF).astype(np.float32) * np.float32(1.0 / 65535.0),
+        "v": (bits[:, 0] >> 16).astype(np.float32) * np.float32(1.0 / 65535.0),
+    }
+
+
+class RenderCoreB200:
+    """One core instance on one GPU."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        if self.lib.b200_create(C.byref(h), device):
+            raise B200Error(self.lib.b200_last_error().decode())
+        self.h = h
+        self._keep = []
+
+    def _chk(self, rc):
+        if rc:
+            raise B200Error(self.lib.b200_last_error().decode())
+
+    def Shutdown(self):
+        if getattr(self, "h", None):
+            self.lib.b200_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.Shutdown()
+        except Exception:
+            pass
+
+    # -- scene ------------------------------------------------------------------------------------
+    def SetGeometry(self, mesh_idx: int, verts: np.ndarray, core_tris: np.ndarray | None = None):
+        """verts[T,3,3] (or float4[3T]) -> float4[3T] vertexData as RenderSystem sends it (w = 1)."""
+        v = np.asarray(verts, np.float32)
+        if v.ndim == 3 and v.shape[1:] == (3, 3):
+            v4 = np.ones((v.shape[0] * 3, 4), np.float32)
+            v4[:, :3] = v.reshape(-1, 3)
+        else:
+            v4 = np.ascontiguousarray(v.reshape(-1, 4))
+        t = v4.shape[0] // 3
+        tri_ptr = core_tris.ctypes.data if core_tris is not None else None
+        self._chk(self.lib.b200_set_geometry(self.h, mesh_idx, v4.ctypes.data, v4.shape[0], t, tri_ptr, None))
+
+    def SetInstance(self, inst_idx: int, mesh_idx: int, transform=None):
+        m = None
+        if transform is not None:
+            m = np.ascontiguousarray(transform, np.float32).reshape(16)
+        self._chk(self.lib.b200_set_instance(self.h, inst_idx, mesh_idx, m.ctypes.data if m is not None else None))
+
+    def UpdateToplevel(self):
+        self._chk(self.lib.b200_update_toplevel(self.h))
+
+    def Refit(self, mesh_idx: int, verts: np.ndarray):
+        v = np.asarray(verts, np.float32)
+        v4 = np.ones((v.shape[0] * 3, 4), np.float32)
+        v4[:, :3] = v.reshape(-1, 3)
+        self._chk(self.lib.b200_refit(self.h, mesh_idx, v4.ctypes.data, v4.shape[0]))
+
+    def RefitDevice(self, mesh_idx: int, dptr: int, vertex_count: int):
+        self._chk(self.lib.b200_refit_device(self.h, mesh_idx, dptr, vertex_count))
+
+    def Setting(self, name: str, value: float):
+        self._chk(self.lib.b200_setting(self.h, name.encode(), float(value)))
+
+    def SetStream(self, stream_handle: int):
+        self._chk(self.lib.b200_set_stream(self.h, stream_handle))
+
+    # -- raw waves ----------------------------------------------------------------------------------
+    def TraceClosest(self, O4: np.ndarray, D4: np.ndarray) -> np.ndarray:
+        O4 = np.ascontiguousarray(O4, np.float32).reshape(-1, 4)
+        D4 = np.ascontiguousarray(D4, np.float32).reshape(-1, 4)
+        hits = np.empty((O4.shape[0], 4), np.float32)
+        self._chk(self.lib.b200_trace_closest(self.h, O4.ctypes.data, D4.ctypes.data, O4.shape[0], hits.ctypes.data))
+        return hits
+
+    def TraceAny(self, O4: np.ndarray, D4: np.ndarray) -> np.ndarray:
+        """Returns bool[n]: True = occluded."""
+        O4 = np.ascontiguousarray(O4, np.float32).reshape(-1, 4)
+        D4 = np.ascontiguousarray(D4, np.float32).reshape(-1, 4)
+        n = O4.shape[0]
+        bits = np.zeros((n + 31) // 32, np.uint32)
+        self._chk(self.lib.b200_trace_any(self.h, O4.ctypes.data, D4.ctypes.data, n, bits.ctypes.data))
+        return np.unpackbits(bits.view(np.uint8), bitorder="little")[:n].astype(bool)
+
+    def TraceClosestDevice(self, dO4: int, dD4: int, n: int, dHits: int):
+        self._chk(self.lib.b200_trace_closest_device(self.h, dO4, dD4, n, dHits))
+
+    def TraceAnyDevice(self, dO4: int, dD4: int, n: int, dBits: int):
+        self._chk(self.lib.b200_trace_any_device(self.h, dO4, dD4, n, dBits))
+
+    def StepCounters(self, n: int):
+        a = np.empty(n, np.uint32)
+        b = np.empty(n, np.uint32)
+        self._chk(self.lib.b200_read_step_counters(self.h, n, a.ctypes.data, b.ctypes.data))
+        return a, b
+
+    # -- frame --------------------------------------------------------------------------------------
+    def SetTarget(self, width: int, height: int, spp: int = 1):
+        self.width, self.height = width, height
+        self._chk(self.lib.b200_set_target(self.h, width, height, spp))
+
+    def SetPointLight(self, pos, radiance):
+        p = np.asarray(pos, np.float32)
+        r = np.asarray(radiance, np.float32)
+        self._chk(self.lib.b200_set_point_light(self.h, p.ctypes.data, r.ctypes.data))
+
+    def SetSky(self, radiance):
+        r = np.asarray(radiance, np.float32)
+        self._chk(self.lib.b200_set_sky(self.h, r.ctypes.data))
+
+    def Render(self, view: dict, converge: int = 1):
+        vp = ViewPyramid()
+        for k in ("pos", "p1", "p2", "p3"):
+            getattr(vp, k)[:] = [float(x) for x in view[k]]
+        vp.aperture, vp.spreadAngle, vp.imagePlane, vp.focalDistance, vp.distortion = 0.0, 0.01, 0.01, 1.0, 0.0
+        self._chk(self.lib.b200_render(self.h, C.byref(vp), converge))
+
+    def ReadAccumulator(self) -> np.ndarray:
+        out = np.empty((self.height, self.width, 4), np.float32)
+        self._chk(self.lib.b200_read_accumulator(self.h, out.ctypes.data))
+        return out
+
+    def ReadFrame(self) -> np.ndarray:
+        out = np.empty((self.height, self.width, 4), np.float32)
+        self._chk(self.lib.b200_read_frame(self.h, out.ctypes.data))
+        return out
+
+    def DeviceAccumulator(self) -> int:
+        return self.lib.b200_device_accumulator(self.h) or 0
+
+    def GetCoreStats(self) -> dict:
+        s = Stats()
+        self._chk(self.lib.b200_get_stats(self.h, C.byref(s)))
+        return s.as_dict()

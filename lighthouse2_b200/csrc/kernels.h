@@ -1,0 +1,43 @@
+// kernels.h -- host-callable launchers of the sm_100a kernels (implemented in *.cu).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace b200 {
+
+// Arguments of one extend (closest-hit) or shadow (any-hit) wave.
+struct TraceArgs {
+	const uint4* nodes;        // wide node pool, 5 x uint4 per node (BLAS nodes of all meshes, then the TLAS)
+	const float4* tris;        // 3 x float4 per triangle, leaf order
+	const float4* instances;   // 6 x float4 per instance record, TLAS leaf order
+	const float4* rayO;        // (Ox,Oy,Oz,tmin)
+	const float4* rayD;        // (Dx,Dy,Dz,tmax)
+	float4* hits;              // closest-hit output, 16 B/ray           (extend)
+	uint32_t* occluded;        // 1 bit/ray, pre-cleared, bit set = hit  (shadow)
+	uint32_t* fetchCounter;    // persistent-thread ray fetch counter (zeroed by the launcher)
+	const uint32_t* countPtr;  // optional device-resident ray count (wavefront counters); overrides `count`
+	uint32_t count;
+	uint32_t tlasRoot;         // absolute node index of the top-level root
+	uint32_t* stepNodes;       // optional per-ray counters (COUNT variants)
+	uint32_t* stepTris;
+};
+
+enum IsectMode { ISECT_REFERENCE = 0, ISECT_WATERTIGHT = 1 };
+
+// grid = persistent CTAs (multiple of the SM count); returns cudaGetLastError()
+cudaError_t LaunchExtend( const TraceArgs& a, IsectMode mode, bool countSteps, int smCount, cudaStream_t s );
+cudaError_t LaunchShadow( const TraceArgs& a, IsectMode mode, int smCount, cudaStream_t s );
+
+// ---- refit (refit.cu) -------------------------------------------------------------------------------
+struct RefitArgs {
+	uint4* nodes;              // this mesh's nodes (absolute pool pointer)
+	float4* tris;              // pool
+	const float4* verts;       // new positions, float4[3T], ORIGINAL primitive order
+	float4* nodeLo; float4* nodeHi; // scratch: float AABB per node of this mesh
+	uint32_t nodeBase;         // absolute index of the mesh root in the pool
+	uint32_t triBase, triCount;
+};
+cudaError_t LaunchRefitTriangles( const RefitArgs& a, cudaStream_t s );
+cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t levelEnd, cudaStream_t s );
+
+} // namespace b200

@@ -1,0 +1,130 @@
+// refit.cu -- GPU refit of a mesh's 8-wide BVH after its vertices moved (animated meshes, config C4).
+//
+// The reference has no refit: RenderCore::SetGeometry does a full SAH rebuild on every update
+// (lib/RenderCore_Bart/rendercore.cpp:78 -> bvh.cpp:57); the OptiX cores call optixAccelBuild with
+// OPTIX_BUILD_OPERATION_UPDATE (lib/rendercore_optix7/core_mesh.cpp:71-103).  Here the topology built by
+// bvh_builder.cpp is kept and only boxes are recomputed:
+//   1. refitTriangles: one thread per leaf-order triangle slot gathers its three new vertices
+//      (original primitive order, float4[3T]) and rewrites {v0|prim, e1, e2}          -- 48 B in, 48 B out / tri
+//   2. refitLevel, deepest level first (nodes are stored breadth-first, so a level is an index range):
+//      eight lanes per node, lane s owns child slot s; leaf slots bound their triangles from the new
+//      vertices, inner slots read the child's float box from scratch; an 8-lane shuffle reduction gives
+//      the node box; each lane re-quantises its own child against the new frame (double arithmetic,
+//      same formulas as QuantiseFrame/QuantiseChild in bvh_builder.cpp)              -- 80 B r/w + 32 B scratch / node
+#include "kernels.h"
+
+namespace b200 {
+
+namespace {
+
+__global__ void refitTrianglesKernel( const RefitArgs a )
+{
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= a.triCount) return;
+	float4* tp = a.tris + (size_t)(a.triBase + j) * 3;
+	const uint32_t prim = __float_as_uint( tp[0].w );
+	const float4 p0 = __ldg( a.verts + (size_t)prim * 3 ), p1 = __ldg( a.verts + (size_t)prim * 3 + 1 ), p2 = __ldg( a.verts + (size_t)prim * 3 + 2 );
+	tp[0] = make_float4( p0.x, p0.y, p0.z, __uint_as_float( prim ) );
+	tp[1] = make_float4( p1.x - p0.x, p1.y - p0.y, p1.z - p0.z, 0.f );
+	tp[2] = make_float4( p2.x - p0.x, p2.y - p0.y, p2.z - p0.z, 0.f );
+}
+
+__device__ __forceinline__ uint32_t frameExponent( float lo, float hi )
+{
+	const double ext = (double)hi - (double)lo;
+	int ex = -100;
+	if (ext > 0)
+	{
+		int fe;
+		frexp( ext / 255.0, &fe );
+		ex = fe;
+		if (ldexp( 255.0, ex - 1 ) >= ext) ex--;
+		if (ex < -100) ex = -100;
+	}
+	return (uint32_t)(ex + 127);
+}
+
+__device__ __forceinline__ void quantise( float p, uint32_t e, float lo, float hi, uint32_t& qlo, uint32_t& qhi )
+{
+	const double guard = 1.0 / 64.0;
+	const double inv = ldexp( 1.0, 127 - (int)e );
+	double l = floor( ((double)lo - (double)p) * inv - guard ), h = ceil( ((double)hi - (double)p) * inv + guard );
+	qlo = (uint32_t)(l < 0 ? 0 : (l > 255 ? 255 : l));
+	qhi = (uint32_t)(h < 0 ? 0 : (h > 255 ? 255 : h));
+}
+
+__global__ void refitLevelKernel( const RefitArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
+{
+	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t node = levelBegin + (gid >> 3), s = gid & 7;
+	const bool valid = node < levelEnd; // whole 8-lane groups are valid or not, so the shuffles below stay converged per group
+	const uint32_t n = valid ? node : levelBegin;
+	uint4* np = a.nodes + (size_t)(a.nodeBase + n) * 5;
+	const uint4 n0 = np[0], n1 = np[1];
+	const uint32_t imask = n0.w >> 24;
+	const uint32_t meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
+	float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+	if (meta)
+	{
+		if (imask & (1u << s))
+		{
+			// absolute child index -> index relative to this mesh's scratch
+			const uint32_t child = n1.x + __popc( imask & ((1u << s) - 1u) ) - a.nodeBase;
+			const float4 cl = a.nodeLo[child], ch = a.nodeHi[child];
+			lo[0] = cl.x, lo[1] = cl.y, lo[2] = cl.z, hi[0] = ch.x, hi[1] = ch.y, hi[2] = ch.z;
+		}
+		else
+		{
+			const uint32_t cnt = __popc( meta >> 5 ), first = n1.y + (meta & 31u);
+			for (uint32_t k = 0; k < cnt; k++)
+			{
+				const uint32_t prim = __float_as_uint( a.tris[(size_t)(first + k) * 3].w );
+				for (int c = 0; c < 3; c++)
+				{
+					const float4 p = __ldg( a.verts + (size_t)prim * 3 + c );
+					lo[0] = fminf( lo[0], p.x ), lo[1] = fminf( lo[1], p.y ), lo[2] = fminf( lo[2], p.z );
+					hi[0] = fmaxf( hi[0], p.x ), hi[1] = fmaxf( hi[1], p.y ), hi[2] = fmaxf( hi[2], p.z );
+				}
+			}
+		}
+	}
+	float nlo[3], nhi[3];
+	for (int c = 0; c < 3; c++)
+	{
+		float l = lo[c], h = hi[c];
+		for (int d = 1; d < 8; d <<= 1) l = fminf( l, __shfl_xor_sync( 0xffffffffu, l, d ) ), h = fmaxf( h, __shfl_xor_sync( 0xffffffffu, h, d ) );
+		nlo[c] = l, nhi[c] = h;
+	}
+	if (!valid) return;
+	uint32_t e[3], qlo[3] = { 0, 0, 0 }, qhi[3] = { 0, 0, 0 };
+	for (int c = 0; c < 3; c++) e[c] = frameExponent( nlo[c], nhi[c] );
+	if (meta) for (int c = 0; c < 3; c++) quantise( nlo[c], e[c], lo[c], hi[c], qlo[c], qhi[c] );
+	uint8_t* q = reinterpret_cast<uint8_t*>( np + 2 ); // qlox[8] qloy[8] qloz[8] qhix[8] qhiy[8] qhiz[8]
+	q[s] = (uint8_t)qlo[0], q[8 + s] = (uint8_t)qlo[1], q[16 + s] = (uint8_t)qlo[2];
+	q[24 + s] = (uint8_t)qhi[0], q[32 + s] = (uint8_t)qhi[1], q[40 + s] = (uint8_t)qhi[2];
+	if (s == 0)
+	{
+		np[0] = make_uint4( __float_as_uint( nlo[0] ), __float_as_uint( nlo[1] ), __float_as_uint( nlo[2] ),
+			e[0] | (e[1] << 8) | (e[2] << 16) | (imask << 24) );
+		a.nodeLo[n] = make_float4( nlo[0], nlo[1], nlo[2], 0 ), a.nodeHi[n] = make_float4( nhi[0], nhi[1], nhi[2], 0 );
+	}
+}
+
+} // namespace
+
+cudaError_t LaunchRefitTriangles( const RefitArgs& a, cudaStream_t s )
+{
+	if (!a.triCount) return cudaSuccess;
+	refitTrianglesKernel<<<(a.triCount + 255) / 256, 256, 0, s>>>( a );
+	return cudaGetLastError();
+}
+
+cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t levelEnd, cudaStream_t s )
+{
+	const uint32_t threads = (levelEnd - levelBegin) * 8;
+	if (!threads) return cudaSuccess;
+	refitLevelKernel<<<(threads + 255) / 256, 256, 0, s>>>( a, levelBegin, levelEnd );
+	return cudaGetLastError();
+}
+
+} // namespace b200

@@ -1,0 +1,453 @@
+// rendercore.cpp -- host side of RenderCore_B200 (scene upload, pools, wave launches, stats).
+// Counterpart of lib/RenderCore_Bart/rendercore.cpp:47-101 (SetGeometry/SetInstance) and of
+// lib/rendercore_optix7/rendercore.cpp:338-428 (SetGeometry/SetInstance/UpdateToplevel) for the B200 core.
+#include "rendercore.h"
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+namespace b200 {
+
+static double nowMs() { return std::chrono::duration<double, std::milli>( std::chrono::steady_clock::now().time_since_epoch() ).count(); }
+
+// ---- mat4::Inverted (lib/RenderSystem/common_types.h:568-611) -----------------------------------------
+// Cofactor expansion; each cofactor is six signed triple products accumulated left to right, which is the
+// evaluation order of the reference expression, so the result is bit-identical for any matrix.
+void Mat4Inverted( const float* c, float* out )
+{
+	static const int8_t T[16][6][4] = {
+		{ { 1, 5, 10, 15 }, { -1, 5, 11, 14 }, { -1, 9, 6, 15 }, { 1, 9, 7, 14 }, { 1, 13, 6, 11 }, { -1, 13, 7, 10 } },
+		{ { -1, 1, 10, 15 }, { 1, 1, 11, 14 }, { 1, 9, 2, 15 }, { -1, 9, 3, 14 }, { -1, 13, 2, 11 }, { 1, 13, 3, 10 } },
+		{ { 1, 1, 6, 15 }, { -1, 1, 7, 14 }, { -1, 5, 2, 15 }, { 1, 5, 3, 14 }, { 1, 13, 2, 7 }, { -1, 13, 3, 6 } },
+		{ { -1, 1, 6, 11 }, { 1, 1, 7, 10 }, { 1, 5, 2, 11 }, { -1, 5, 3, 10 }, { -1, 9, 2, 7 }, { 1, 9, 3, 6 } },
+		{ { -1, 4, 10, 15 }, { 1, 4, 11, 14 }, { 1, 8, 6, 15 }, { -1, 8, 7, 14 }, { -1, 12, 6, 11 }, { 1, 12, 7, 10 } },
+		{ { 1, 0, 10, 15 }, { -1, 0, 11, 14 }, { -1, 8, 2, 15 }, { 1, 8, 3, 14 }, { 1, 12, 2, 11 }, { -1, 12, 3, 10 } },
+		{ { -1, 0, 6, 15 }, { 1, 0, 7, 14 }, { 1, 4, 2, 15 }, { -1, 4, 3, 14 }, { -1, 12, 2, 7 }, { 1, 12, 3, 6 } },
+		{ { 1, 0, 6, 11 }, { -1, 0, 7, 10 }, { -1, 4, 2, 11 }, { 1, 4, 3, 10 }, { 1, 8, 2, 7 }, { -1, 8, 3, 6 } },
+		{ { 1, 4, 9, 15 }, { -1, 4, 11, 13 }, { -1, 8, 5, 15 }, { 1, 8, 7, 13 }, { 1, 12, 5, 11 }, { -1, 12, 7, 9 } },
+		{ { -1, 0, 9, 15 }, { 1, 0, 11, 13 }, { 1, 8, 1, 15 }, { -1, 8, 3, 13 }, { -1, 12, 1, 11 }, { 1, 12, 3, 9 } },
+		{ { 1, 0, 5, 15 }, { -1, 0, 7, 13 }, { -1, 4, 1, 15 }, { 1, 4, 3, 13 }, { 1, 12, 1, 7 }, { -1, 12, 3, 5 } },
+		{ { -1, 0, 5, 11 }, { 1, 0, 7, 9 }, { 1, 4, 1, 11 }, { -1, 4, 3, 9 }, { -1, 8, 1, 7 }, { 1, 8, 3, 5 } },
+		{ { -1, 4, 9, 14 }, { 1, 4, 10, 13 }, { 1, 8, 5, 14 }, { -1, 8, 6, 13 }, { -1, 12, 5, 10 }, { 1, 12, 6, 9 } },
+		{ { 1, 0, 9, 14 }, { -1, 0, 10, 13 }, { -1, 8, 1, 14 }, { 1, 8, 2, 13 }, { 1, 12, 1, 10 }, { -1, 12, 2, 9 } },
+		{ { -1, 0, 5, 14 }, { 1, 0, 6, 13 }, { 1, 4, 1, 14 }, { -1, 4, 2, 13 }, { -1, 12, 1, 6 }, { 1, 12, 2, 5 } },
+		{ { 1, 0, 5, 10 }, { -1, 0, 6, 9 }, { -1, 4, 1, 10 }, { 1, 4, 2, 9 }, { 1, 8, 1, 6 }, { -1, 8, 2, 5 } } };
+	float inv[16];
+	for (int i = 0; i < 16; i++)
+	{
+		float acc = 0;
+		for (int k = 0; k < 6; k++)
+		{
+			const int8_t* t = T[i][k];
+			volatile float first = t[0] < 0 ? -c[t[1]] : c[t[1]];
+			volatile float p = first * c[t[2]];
+			volatile float q = p * c[t[3]];
+			acc = k == 0 ? (float)q : acc + q;
+		}
+		inv[i] = acc;
+	}
+	const float det = c[0] * inv[0] + c[1] * inv[4] + c[2] * inv[8] + c[3] * inv[12];
+	for (int i = 0; i < 16; i++) out[i] = (i % 5 == 0) ? 1.f : 0.f;
+	if (det != 0)
+	{
+		const float invdet = 1.0f / det;
+		for (int i = 0; i < 16; i++) out[i] = inv[i] * invdet;
+	}
+}
+
+// ---- DeviceBuffer -------------------------------------------------------------------------------------
+cudaError_t DeviceBuffer::reserve( size_t need, bool keep, cudaStream_t s )
+{
+	if (need <= bytes) return cudaSuccess;
+	size_t cap = bytes ? bytes : 256;
+	while (cap < need) cap += cap / 2 + 256;
+	cap = (cap + 255) & ~(size_t)255;
+	void* np = nullptr;
+	cudaError_t e = cudaMalloc( &np, cap );
+	if (e != cudaSuccess) return e;
+	if (ptr)
+	{
+		if (keep)
+		{
+			e = cudaMemcpyAsync( np, ptr, bytes, cudaMemcpyDeviceToDevice, s );
+			if (e == cudaSuccess) e = cudaStreamSynchronize( s );
+			if (e != cudaSuccess) { cudaFree( np ); return e; }
+		}
+		else cudaStreamSynchronize( s );
+		cudaFree( ptr );
+	}
+	ptr = np, bytes = cap;
+	return cudaSuccess;
+}
+
+void DeviceBuffer::release()
+{
+	if (ptr) cudaFree( ptr );
+	ptr = nullptr, bytes = 0;
+}
+
+// ---- lifetime -----------------------------------------------------------------------------------------
+RenderCore::RenderCore( int dev ) : device( dev )
+{
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount( &count );
+	if (e != cudaSuccess || count == 0) { fail( "no CUDA device: RenderCore_B200 has no CPU fallback", e ); return; }
+	if (dev < 0 || dev >= count) { fail( "device index out of range" ); return; }
+	if ((e = cudaSetDevice( dev )) != cudaSuccess) { fail( "cudaSetDevice", e ); return; }
+	cudaDeviceProp prop;
+	if ((e = cudaGetDeviceProperties( &prop, dev )) != cudaSuccess) { fail( "cudaGetDeviceProperties", e ); return; }
+	if (prop.major < 10) { fail( std::string( "RenderCore_B200 kernels are built for sm_100a only; found " ) + prop.name ); return; }
+	smCount = prop.multiProcessorCount;
+	stats.smCount = smCount, stats.ccMajor = prop.major, stats.ccMinor = prop.minor;
+	stats.vramMB = (uint32_t)(prop.totalGlobalMem >> 20);
+	stats.probedInstid = stats.probedTriid = -1;
+	if ((e = cudaEventCreate( &evA )) != cudaSuccess || (e = cudaEventCreate( &evB )) != cudaSuccess) { fail( "cudaEventCreate", e ); return; }
+	if ((e = fetchCounter.reserve( 256, false, 0 )) != cudaSuccess) { fail( "cudaMalloc", e ); return; }
+	buildThreads = (int)std::thread::hardware_concurrency();
+	if (buildThreads < 1) buildThreads = 1;
+	initOk = true;
+}
+
+RenderCore::~RenderCore()
+{
+	if (!initOk) return;
+	cudaSetDevice( device );
+	cudaDeviceSynchronize();
+	DestroyWavefront( wf );
+	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &materialPool, &rayO, &rayD, &hitBuf, &bitBuf, &vertStage, &nodeLo, &nodeHi,
+		&stepNodes, &stepTris };
+	for (DeviceBuffer* b : all) b->release();
+	if (evA) cudaEventDestroy( evA );
+	if (evB) cudaEventDestroy( evB );
+}
+
+int RenderCore::fail( const char* what, cudaError_t e )
+{
+	error = std::string( what ) + ": " + cudaGetErrorString( e );
+	return 1;
+}
+int RenderCore::fail( const std::string& what )
+{
+	error = what;
+	return 1;
+}
+
+int RenderCore::Setting( const char* name, float value )
+{
+	// keys sent every frame by RenderSystem::Render (lib/RenderSystem/rendersystem.cpp:231-236)
+	if (!strcmp( name, "epsilon" )) { epsilon = value; return 0; }
+	if (!strcmp( name, "clampValue" ) || !strcmp( name, "clampDirect" ) || !strcmp( name, "clampIndirect" ) || !strcmp( name, "filter" ) ||
+		!strcmp( name, "TAA" )) return 0; // accepted, not used by the traversal path
+	// B200-specific keys
+	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
+	if (!strcmp( name, "countSteps" )) { countSteps = value >= 0.5f; return 0; }
+	if (!strcmp( name, "refit" )) { allowRefit = value >= 0.5f; return 0; }
+	if (!strcmp( name, "buildThreads" )) { buildThreads = value < 1 ? 1 : (int)value; return 0; }
+	return SettingWavefront( name, value );
+}
+
+
+// ---- geometry -----------------------------------------------------------------------------------------
+// CoreAPI_Base::SetGeometry (core_api_base.h:108).  vertexData is float4[3T], triangle-expanded.  The first
+// call for a mesh builds its wide BVH on the host and appends it to the pools; later calls with the same
+// triangle count refit on the GPU (the reference instead rebuilds: rendercore.cpp:78).
+int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCount, int triangleCount, const void* coreTris, const uint32_t* )
+{
+	if (meshIdx < 0 || triangleCount < 0 || vertexCount != 3 * triangleCount) return fail( "SetGeometry: bad arguments (vertexCount must be 3*triangleCount)" );
+	if (triangleCount > 0 && !vertexData) return fail( "SetGeometry: null vertexData" );
+	if (meshIdx > (int)meshes.size()) return fail( "SetGeometry: mesh indices must arrive densely" );
+	if (meshIdx < (int)meshes.size() && meshes[meshIdx].built)
+	{
+		if ((uint32_t)triangleCount == meshes[meshIdx].triCount && allowRefit) return Refit( meshIdx, vertexData, vertexCount );
+		if ((uint32_t)triangleCount != meshes[meshIdx].triCount && meshIdx != (int)meshes.size() - 1)
+			return fail( "SetGeometry: changing the triangle count is only supported for the most recently added mesh" );
+		if (meshIdx != (int)meshes.size() - 1 && !allowRefit)
+			return fail( "SetGeometry: rebuild (refit=0) is only supported for the most recently added mesh" );
+		// rebuild of the last mesh: drop it and fall through to a fresh build
+		blasNodeEnd = meshes[meshIdx].nodeBase, triEnd = meshes[meshIdx].triBase;
+		meshes.pop_back();
+	}
+	const double t0 = nowMs();
+	const uint32_t T = (uint32_t)triangleCount;
+	std::vector<Aabb> boxes( T );
+	for (uint32_t i = 0; i < T; i++)
+	{
+		boxes[i].reset();
+		for (int k = 0; k < 3; k++) boxes[i].grow( vertexData + (size_t)(3 * i + k) * 4 );
+	}
+	WideBvh bvh;
+	BuildWideBvh( boxes.data(), T, 3, buildThreads, bvh );
+	MeshRec m;
+	m.nodeBase = blasNodeEnd, m.nodeCount = (uint32_t)bvh.nodes.size(), m.triBase = triEnd, m.triCount = T;
+	m.levelStart = bvh.levelStart, m.bounds = bvh.bounds, m.built = true;
+	for (WideNode& n : bvh.nodes) n.childBase += m.nodeBase, n.primBase += m.triBase; // absolute pool indices
+	std::vector<WideTri> tris( T );
+	std::vector<uint32_t> material( T, 0 );
+	for (uint32_t j = 0; j < T; j++)
+	{
+		const uint32_t prim = bvh.primOrder[j];
+		const float *p0 = vertexData + (size_t)prim * 12, *p1 = p0 + 4, *p2 = p0 + 8;
+		WideTri& t = tris[j];
+		t.prim = prim, t.pad1 = t.pad2 = 0;
+		for (int a = 0; a < 3; a++) t.v0[a] = p0[a], t.e1[a] = p1[a] - p0[a], t.e2[a] = p2[a] - p0[a];
+		if (coreTris) memcpy( &material[j], (const char*)coreTris + (size_t)prim * 176 + 28, 4 ); // CoreTri::material, common_classes.h:67
+	}
+	cudaError_t e;
+	if ((e = nodePool.reserve( (size_t)(m.nodeBase + m.nodeCount + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
+	if ((e = triPool.reserve( (size_t)(m.triBase + T + 1) * 48, true, stream )) != cudaSuccess) return fail( "triangle pool", e );
+	if ((e = materialPool.reserve( (size_t)(m.triBase + T + 1) * 4, true, stream )) != cudaSuccess) return fail( "material pool", e );
+	if ((e = cudaMemcpyAsync( (char*)nodePool.ptr + (size_t)m.nodeBase * 80, bvh.nodes.data(), (size_t)m.nodeCount * 80, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "node upload", e );
+	if (T && (e = cudaMemcpyAsync( (char*)triPool.ptr + (size_t)m.triBase * 48, tris.data(), (size_t)T * 48, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "triangle upload", e );
+	if (T && (e = cudaMemcpyAsync( (char*)materialPool.ptr + (size_t)m.triBase * 4, material.data(), (size_t)T * 4, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "material upload", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "SetGeometry sync", e ); // the staging vectors die here
+	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
+	meshes.push_back( m );
+	tlasDirty = true;
+	stats.bvhBuildTime += (float)(nowMs() - t0);
+	stats.wideNodeCount = blasNodeEnd, stats.triangleCount = triEnd;
+	return 0;
+}
+
+// b200_refit: new positions for an existing mesh (host float4[3T])
+int RenderCore::Refit( int meshIdx, const float* vertexData, int vertexCount )
+{
+	if (meshIdx < 0 || meshIdx >= (int)meshes.size() || !meshes[meshIdx].built) return fail( "Refit: unknown mesh" );
+	MeshRec& m = meshes[meshIdx];
+	if ((uint32_t)vertexCount != 3 * m.triCount) return fail( "Refit: vertex count does not match the built mesh" );
+	cudaError_t e;
+	if ((e = vertStage.reserve( (size_t)vertexCount * 16 + 16, false, stream )) != cudaSuccess) return fail( "vertex staging", e );
+	if ((e = cudaMemcpyAsync( vertStage.ptr, vertexData, (size_t)vertexCount * 16, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "vertex upload", e );
+	// object-space bounds for the top level come from the host copy of the vertices (no read-back needed)
+	Aabb b;
+	b.reset();
+	for (int i = 0; i < vertexCount; i++) b.grow( vertexData + (size_t)i * 4 );
+	m.bounds = b;
+	return RefitDevice( meshIdx, vertStage.ptr, vertexCount, true );
+}
+
+int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, bool boundsKnown )
+{
+	if (meshIdx < 0 || meshIdx >= (int)meshes.size() || !meshes[meshIdx].built) return fail( "Refit: unknown mesh" );
+	MeshRec& m = meshes[meshIdx];
+	if ((uint32_t)vertexCount != 3 * m.triCount) return fail( "Refit: vertex count does not match the built mesh" );
+	cudaError_t e;
+	if ((e = nodeLo.reserve( (size_t)m.nodeCount * 16, false, stream )) != cudaSuccess) return fail( "refit scratch", e );
+	if ((e = nodeHi.reserve( (size_t)m.nodeCount * 16, false, stream )) != cudaSuccess) return fail( "refit scratch", e );
+	RefitArgs a;
+	a.nodes = (uint4*)nodePool.ptr, a.tris = (float4*)triPool.ptr, a.verts = (const float4*)dVerts;
+	a.nodeLo = (float4*)nodeLo.ptr, a.nodeHi = (float4*)nodeHi.ptr;
+	a.nodeBase = m.nodeBase, a.triBase = m.triBase, a.triCount = m.triCount;
+	cudaEventRecord( evA, stream );
+	if ((e = LaunchRefitTriangles( a, stream )) != cudaSuccess) return fail( "refit triangles", e );
+	stats.kernelLaunches++;
+	for (int level = (int)m.levelStart.size() - 2; level >= 0; level--)
+	{
+		if ((e = LaunchRefitLevel( a, m.levelStart[level], m.levelStart[level + 1], stream )) != cudaSuccess) return fail( "refit level", e );
+		stats.kernelLaunches++;
+	}
+	cudaEventRecord( evB, stream );
+	if (!boundsKnown)
+	{
+		// caller supplied device positions only: fetch the refitted root box (32 bytes)
+		float lo[4], hi[4];
+		if ((e = cudaMemcpyAsync( lo, nodeLo.ptr, 16, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "root box", e );
+		if ((e = cudaMemcpyAsync( hi, nodeHi.ptr, 16, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "root box", e );
+		if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "refit sync", e );
+		for (int c = 0; c < 3; c++) m.bounds.lo[c] = lo[c], m.bounds.hi[c] = hi[c];
+	}
+	else if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "refit sync", e );
+	float ms = 0;
+	cudaEventElapsedTime( &ms, evA, evB );
+	stats.refitTime = ms;
+	tlasDirty = true;
+	return 0;
+}
+
+// ---- instances ----------------------------------------------------------------------------------------
+// CoreAPI_Base::SetInstance (core_api_base.h:110); modelIdx == -1 ends the stream and truncates
+// (lib/RenderSystem/rendersystem.cpp:167-169, lib/RenderCore_Bart/rendercore.cpp:84-89).
+int RenderCore::SetInstance( int instanceIdx, int modelIdx, const float* transform )
+{
+	if (instanceIdx < 0) return fail( "SetInstance: negative index" );
+	if (modelIdx == -1)
+	{
+		if ((int)instances.size() > instanceIdx) instances.resize( instanceIdx ), tlasDirty = true;
+		return 0;
+	}
+	if (modelIdx < 0 || modelIdx >= (int)meshes.size()) return fail( "SetInstance: unknown mesh" );
+	if (instanceIdx > (int)instances.size()) return fail( "SetInstance: instance indices must arrive densely" );
+	if (instanceIdx == (int)instances.size()) instances.emplace_back();
+	InstanceHost& in = instances[instanceIdx];
+	in.mesh = modelIdx;
+	static const float ident[16] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+	memcpy( in.transform, transform ? transform : ident, 64 );
+	Mat4Inverted( in.transform, in.inv );
+	tlasDirty = true;
+	return 0;
+}
+
+// CoreAPI_Base::UpdateToplevel (core_api_base.h:112): full top-level rebuild, every frame if anything moved
+// (the CPU core rebuilds per Render, rendercore.cpp:199; optix7 rebuilds the IAS, rendercore.cpp:387-428).
+int RenderCore::UpdateToplevel()
+{
+	const double t0 = nowMs();
+	const uint32_t N = (uint32_t)instances.size();
+	std::vector<Aabb> boxes( N );
+	for (uint32_t i = 0; i < N; i++)
+	{
+		// world box = all 8 transformed corners of the mesh box (the CPU reference transforms only two,
+		// bvh.cpp:579-587, which is exact for translations and too small under rotation)
+		const Aabb& mb = meshes[instances[i].mesh].bounds;
+		const float* c = instances[i].transform;
+		boxes[i].reset();
+		if (meshes[instances[i].mesh].triCount == 0) { float z[3] = { c[3], c[7], c[11] }; boxes[i].grow( z ); continue; }
+		for (int k = 0; k < 8; k++)
+		{
+			const float x = (k & 1) ? mb.hi[0] : mb.lo[0], y = (k & 2) ? mb.hi[1] : mb.lo[1], z = (k & 4) ? mb.hi[2] : mb.lo[2];
+			float p[3] = { c[0] * x + c[1] * y + c[2] * z + c[3], c[4] * x + c[5] * y + c[6] * z + c[7], c[8] * x + c[9] * y + c[10] * z + c[11] };
+			boxes[i].grow( p );
+		}
+		// one ulp-scale pad: the device transforms the RAY instead of the box, so roundings differ
+		for (int a = 0; a < 3; a++)
+		{
+			const float pad = 4e-7f * fmaxf( fabsf( boxes[i].lo[a] ), fabsf( boxes[i].hi[a] ) ) + 1e-30f;
+			boxes[i].lo[a] -= pad, boxes[i].hi[a] += pad;
+		}
+	}
+	WideBvh tlas;
+	BuildWideBvh( boxes.data(), N, 1, 1, tlas );
+	std::vector<InstanceRec> recs( N );
+	for (uint32_t j = 0; j < N; j++)
+	{
+		const uint32_t id = tlas.primOrder[j];
+		InstanceRec& r = recs[j];
+		memset( &r, 0, sizeof( r ) );
+		memcpy( r.inv, instances[id].inv, 64 );
+		r.blasRoot = meshes[instances[id].mesh].nodeBase, r.instId = id, r.meshId = (uint32_t)instances[id].mesh;
+		const float* v = r.inv;
+		r.flags = (v[12] == 0 && v[13] == 0 && v[14] == 0 && v[15] == 1) ? 1u : 0u;
+	}
+	tlasRoot = blasNodeEnd, tlasNodeCount = (uint32_t)tlas.nodes.size();
+	for (WideNode& n : tlas.nodes) n.childBase += tlasRoot; // primBase indexes the instance records directly
+	cudaError_t e;
+	if ((e = nodePool.reserve( (size_t)(tlasRoot + tlasNodeCount) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
+	if ((e = instPool.reserve( (size_t)(N + 1) * 96, false, stream )) != cudaSuccess) return fail( "instance pool", e );
+	if ((e = cudaMemcpyAsync( (char*)nodePool.ptr + (size_t)tlasRoot * 80, tlas.nodes.data(), (size_t)tlasNodeCount * 80, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "tlas upload", e );
+	if (N && (e = cudaMemcpyAsync( instPool.ptr, recs.data(), (size_t)N * 96, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "instance upload", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "UpdateToplevel sync", e );
+	tlasDirty = false;
+	stats.tlasTime = (float)(nowMs() - t0);
+	stats.instanceCount = N, stats.tlasNodeCount = tlasNodeCount;
+	return 0;
+}
+
+int RenderCore::ensureToplevel() { return tlasDirty ? UpdateToplevel() : 0; }
+
+
+// ---- the raw waves -------------------------------------------------------------------------------------
+TraceArgs RenderCore::baseArgs() const
+{
+	TraceArgs a;
+	memset( &a, 0, sizeof( a ) );
+	a.nodes = (const uint4*)nodePool.ptr, a.tris = (const float4*)triPool.ptr, a.instances = (const float4*)instPool.ptr;
+	a.fetchCounter = (uint32_t*)fetchCounter.ptr;
+	a.tlasRoot = tlasRoot;
+	return a;
+}
+
+int RenderCore::TraceClosestDevice( const void* dO4, const void* dD4, int n, void* dHits, const uint32_t* dCount )
+{
+	if (n < 0) return fail( "trace: negative ray count" );
+	if (ensureToplevel()) return 1;
+	if (n == 0) return 0;
+	TraceArgs a = baseArgs();
+	a.rayO = (const float4*)dO4, a.rayD = (const float4*)dD4, a.hits = (float4*)dHits, a.count = (uint32_t)n, a.countPtr = dCount;
+	cudaError_t e;
+	if (countSteps)
+	{
+		if ((e = stepNodes.reserve( (size_t)n * 4, false, stream )) != cudaSuccess) return fail( "step counters", e );
+		if ((e = stepTris.reserve( (size_t)n * 4, false, stream )) != cudaSuccess) return fail( "step counters", e );
+		a.stepNodes = (uint32_t*)stepNodes.ptr, a.stepTris = (uint32_t*)stepTris.ptr;
+	}
+	cudaEventRecord( evA, stream );
+	if ((e = LaunchExtend( a, isect, countSteps, smCount, stream )) != cudaSuccess) return fail( "extend kernel launch", e );
+	cudaEventRecord( evB, stream );
+	stats.kernelLaunches++;
+	return 0;
+}
+
+int RenderCore::TraceAnyDevice( const void* dO4, const void* dD4, int n, void* dBits, const uint32_t* dCount )
+{
+	if (n < 0) return fail( "trace: negative ray count" );
+	if (ensureToplevel()) return 1;
+	if (n == 0) return 0;
+	TraceArgs a = baseArgs();
+	a.rayO = (const float4*)dO4, a.rayD = (const float4*)dD4, a.occluded = (uint32_t*)dBits, a.count = (uint32_t)n, a.countPtr = dCount;
+	cudaError_t e;
+	if ((e = cudaMemsetAsync( dBits, 0, (size_t)((n + 31) / 32) * 4, stream )) != cudaSuccess) return fail( "clear bitmask", e );
+	cudaEventRecord( evA, stream );
+	if ((e = LaunchShadow( a, isect, smCount, stream )) != cudaSuccess) return fail( "shadow kernel launch", e );
+	cudaEventRecord( evB, stream );
+	stats.kernelLaunches++;
+	return 0;
+}
+
+// host-buffer variants: H2D, wave, D2H, synchronise (the e2e path of bench.py)
+int RenderCore::TraceClosest( const float* O4, const float* D4, int n, float* hits )
+{
+	if (n < 0) return fail( "trace: negative ray count" );
+	if (n == 0) return ensureToplevel();
+	cudaError_t e;
+	const size_t rb = (size_t)n * 16;
+	if ((e = rayO.reserve( rb, false, stream )) != cudaSuccess || (e = rayD.reserve( rb, false, stream )) != cudaSuccess ||
+		(e = hitBuf.reserve( rb, false, stream )) != cudaSuccess) return fail( "ray buffers", e );
+	if ((e = cudaMemcpyAsync( rayO.ptr, O4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
+	if ((e = cudaMemcpyAsync( rayD.ptr, D4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
+	if (TraceClosestDevice( rayO.ptr, rayD.ptr, n, hitBuf.ptr )) return 1;
+	if ((e = cudaMemcpyAsync( hits, hitBuf.ptr, rb, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "hit download", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "extend wave", e );
+	cudaEventElapsedTime( &stats.lastTraceMs, evA, evB );
+	return 0;
+}
+
+int RenderCore::TraceAny( const float* O4, const float* D4, int n, uint32_t* bits )
+{
+	if (n < 0) return fail( "trace: negative ray count" );
+	if (n == 0) return ensureToplevel();
+	cudaError_t e;
+	const size_t rb = (size_t)n * 16, bb = (size_t)((n + 31) / 32) * 4;
+	if ((e = rayO.reserve( rb, false, stream )) != cudaSuccess || (e = rayD.reserve( rb, false, stream )) != cudaSuccess ||
+		(e = bitBuf.reserve( bb, false, stream )) != cudaSuccess) return fail( "ray buffers", e );
+	if ((e = cudaMemcpyAsync( rayO.ptr, O4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
+	if ((e = cudaMemcpyAsync( rayD.ptr, D4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
+	if (TraceAnyDevice( rayO.ptr, rayD.ptr, n, bitBuf.ptr )) return 1;
+	if ((e = cudaMemcpyAsync( bits, bitBuf.ptr, bb, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "bitmask download", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "shadow wave", e );
+	cudaEventElapsedTime( &stats.lastTraceMs, evA, evB );
+	return 0;
+}
+
+int RenderCore::ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris )
+{
+	if (!stepNodes.ptr || stepNodes.bytes < (size_t)n * 4) return fail( "ReadStepCounters: no counters (Setting countSteps=1, then trace)" );
+	cudaError_t e;
+	if ((e = cudaMemcpy( nodes, stepNodes.ptr, (size_t)n * 4, cudaMemcpyDeviceToHost )) != cudaSuccess) return fail( "counters", e );
+	if ((e = cudaMemcpy( tris, stepTris.ptr, (size_t)n * 4, cudaMemcpyDeviceToHost )) != cudaSuccess) return fail( "counters", e );
+	return 0;
+}
+
+void RenderCore::GetStats( b200_stats* out )
+{
+	// lastTraceMs of the device-pointer waves is resolved lazily here (the events may still be in flight)
+	if (evA && evB && cudaEventQuery( evB ) == cudaSuccess)
+	{
+		float ms = 0;
+		if (cudaEventElapsedTime( &ms, evA, evB ) == cudaSuccess) stats.lastTraceMs = ms;
+	}
+	cudaGetLastError();
+	*out = stats;
+}
+
+} // namespace b200

@@ -1,0 +1,102 @@
+// rendercore.h -- RenderCore_B200: device state + host logic behind the CoreAPI.
+// Mirrors the role of lib/RenderCore_Bart/rendercore.h:21-49 and lib/rendercore_optix7/rendercore.h.
+#pragma once
+#include "kernels.h"
+#include "wide_bvh.h"
+#include "../../include/rendercore_b200.h"
+#include <string>
+#include <vector>
+
+namespace b200 {
+
+// Growable device array (cudaMalloc); grow() preserves contents with a device-to-device copy.
+struct DeviceBuffer {
+	void* ptr = nullptr;
+	size_t bytes = 0;
+	cudaError_t reserve( size_t need, bool keep, cudaStream_t s );
+	void release();
+};
+
+struct MeshRec {
+	uint32_t nodeBase = 0, nodeCount = 0, triBase = 0, triCount = 0;
+	std::vector<uint32_t> levelStart; // relative to nodeBase
+	Aabb bounds;                      // object-space bounds of the current vertex positions
+	bool built = false;
+};
+
+struct InstanceHost { int mesh = -1; float transform[16]; float inv[16]; };
+
+struct WavefrontState; // wavefront.cu
+
+class RenderCore {
+public:
+	explicit RenderCore( int device );
+	~RenderCore();
+	bool ok() const { return initOk; }
+
+	// CoreAPI surface (lib/RenderSystem/core_api_base.h:84-113)
+	int SetGeometry( int meshIdx, const float* vertexData, int vertexCount, int triangleCount, const void* coreTris, const uint32_t* alphaFlags );
+	int SetInstance( int instanceIdx, int modelIdx, const float* transform );
+	int UpdateToplevel();
+	int Setting( const char* name, float value );
+	int SettingWavefront( const char* name, float value ); // wavefront.cu: maxPathLength, spp, tile sharding ...
+	int SetTarget( int width, int height, int spp );
+	int SetPointLight( const float* pos, const float* radiance );
+	int SetSky( const float* radiance );
+	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value
+	int Render( const void* viewPyramid, int converge );
+	int ReadAccumulator( float* dst );
+	int ReadFrame( float* dst );
+	void* DeviceAccumulator();
+	int SetProbe( int x, int y );
+
+	// raw waves
+	int TraceClosest( const float* O4, const float* D4, int n, float* hits );
+	int TraceAny( const float* O4, const float* D4, int n, uint32_t* bits );
+	int TraceClosestDevice( const void* dO4, const void* dD4, int n, void* dHits, const uint32_t* dCount = nullptr );
+	int TraceAnyDevice( const void* dO4, const void* dD4, int n, void* dBits, const uint32_t* dCount = nullptr );
+	int ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris );
+	int Refit( int meshIdx, const float* vertexData, int vertexCount );
+	int RefitDevice( int meshIdx, const void* dVerts, int vertexCount, bool boundsKnown );
+
+	int SetStream( void* s ) { stream = (cudaStream_t)s; return 0; }
+	void GetStats( b200_stats* out );
+	const std::string& Error() const { return error; }
+
+	// shared with wavefront.cu
+	int fail( const char* what, cudaError_t e );
+	int fail( const std::string& what );
+	TraceArgs baseArgs() const;
+	cudaStream_t stream = 0;
+	int smCount = 148;
+	IsectMode isect = ISECT_REFERENCE;
+	b200_stats stats{};
+	DeviceBuffer fetchCounter; // one uint32 per wave launch slot
+	float epsilon = 1e-4f;
+
+private:
+	int ensureToplevel();
+	bool initOk = false;
+	std::string error;
+	int device = 0;
+	// acceleration structure pools
+	DeviceBuffer nodePool, triPool, instPool, materialPool;
+	uint32_t blasNodeEnd = 0, triEnd = 0, tlasRoot = 0, tlasNodeCount = 0;
+	std::vector<MeshRec> meshes;
+	std::vector<InstanceHost> instances;
+	bool tlasDirty = true;
+	// scratch
+	DeviceBuffer rayO, rayD, hitBuf, bitBuf, vertStage, nodeLo, nodeHi, stepNodes, stepTris;
+	bool countSteps = false, allowRefit = true;
+	int buildThreads = 0;
+	cudaEvent_t evA = nullptr, evB = nullptr;
+	WavefrontState* wf = nullptr;
+	friend struct WavefrontState;
+};
+
+void DestroyWavefront( WavefrontState* wf ); // wavefront.cu
+
+// mat4::Inverted (lib/RenderSystem/common_types.h:568-611): cofactor inverse times 1/det, identity if det == 0.
+void Mat4Inverted( const float* cell, float* out );
+
+} // namespace b200

@@ -1,0 +1,396 @@
+// traverse.cu -- the extend (closest-hit) and shadow (any-hit) waves of RenderCore_B200.
+//
+// These two kernels replace, on sm_100a, what the reference cores delegate to closed libraries:
+//   extend : optixTrace closest-hit (lib/rendercore_optix7/optix/.optix.cu:125-135,177-187),
+//            rtpQueryExecute CLOSEST (lib/RenderCore_OptixPrime_B/rendercore.cpp:524-528)
+//   shadow : optixTrace TERMINATE_ON_FIRST_HIT (.optix.cu:137-149), rtpQueryExecute ANY (:556-565)
+// and, for results, what the CPU core computes in TopLevelBVH::Traverse / BVH2::Traverse /
+// Ray::IntersectTriangle (lib/RenderCore_Bart/bvh.cpp:594,258; common.h:19).
+//
+// Design (B200-first; no tensor cores: traversal is not a contraction):
+//  * persistent warps; lanes fetch rays with one warp-aggregated atomicAdd, refilling idle lanes when
+//    too few are active (ray-stream compaction by vote + prefix popcount)
+//  * rays are two coalesced float4 planes; hits are one float4
+//  * 8-wide BVH with 8-bit quantised child boxes (wide_bvh.h); five LDG.128 per node; the eight slab
+//    tests decode planes with one PRMT + one FFMA each; octant-ordered child visiting from a hit mask
+//  * traversal stack: (base,mask) groups, first STACK_SMEM entries per lane in shared memory, rest local
+//  * TLAS -> BLAS: an instance leaf transforms the ray (reference arithmetic in ISECT_REFERENCE mode)
+//    and traversal continues in the same loop; leaving the instance reloads the world ray
+//
+// Compiled with -fmad=false: every float op below rounds separately unless written as __fmaf_rn, so the
+// ISECT_REFERENCE triangle test and instance entry are bit-identical to the reference's scalar C++.
+#include "kernels.h"
+
+namespace b200 {
+
+namespace {
+
+constexpr int BLOCK_THREADS = 128;
+constexpr int STACK_SMEM = 8;        // per-lane stack entries kept in shared memory
+constexpr int STACK_LOCAL = 40;      // overflow entries in local memory
+constexpr float REF_EPSILON = 0.0001f; // lib/RenderSystem/common_settings.h:45
+constexpr uint32_t NO_INSTANCE = 0xffffffffu;
+
+__device__ __forceinline__ float max3f( float a, float b, float c )
+{
+	float r;
+	asm( "max.f32 %0, %1, %2, %3;" : "=f"( r ) : "f"( a ), "f"( b ), "f"( c ) ); // FMNMX3 (sm_100+)
+	return r;
+}
+__device__ __forceinline__ float min3f( float a, float b, float c )
+{
+	float r;
+	asm( "min.f32 %0, %1, %2, %3;" : "=f"( r ) : "f"( a ), "f"( b ), "f"( c ) );
+	return r;
+}
+__device__ __forceinline__ uint32_t lanemask_lt()
+{
+	uint32_t m;
+	asm( "mov.u32 %0, %%lanemask_lt;" : "=r"( m ) );
+	return m;
+}
+__device__ __forceinline__ uint32_t sign_extend_s8x4( uint32_t x )
+{
+	// each byte: 0x80 set -> 0xff, else 0x00
+	uint32_t r;
+	asm( "prmt.b32 %0, %1, 0, 0xba98;" : "=r"( r ) : "r"( x ) ); // replicate-sign mode selectors 8..b
+	return r;
+}
+// byte `sel` of q placed in byte 1 of 0x4B000000: the float 2^23 + 256*b (exact), decoded by one FFMA
+__device__ __forceinline__ float qbyte( uint32_t q, uint32_t sel ) { return __uint_as_float( __byte_perm( q, 0x4B000000u, sel ) ); }
+
+struct RayState {
+	float ox, oy, oz, dx, dy, dz;   // current-space ray (world in the TLAS, object inside an instance)
+	float ix, iy, iz;               // 1/d with zero components replaced by +-1e-18 (slab test only)
+	float tmin, t;                  // t = current closest hit / tmax
+	uint32_t octinv4;               // (7 - octant) replicated to 4 bytes
+};
+
+__device__ __forceinline__ void setupSlab( RayState& r )
+{
+	const float tiny = 1e-18f;
+	float dx = fabsf( r.dx ) > tiny ? r.dx : copysignf( tiny, r.dx );
+	float dy = fabsf( r.dy ) > tiny ? r.dy : copysignf( tiny, r.dy );
+	float dz = fabsf( r.dz ) > tiny ? r.dz : copysignf( tiny, r.dz );
+	r.ix = __frcp_rn( dx ), r.iy = __frcp_rn( dy ), r.iz = __frcp_rn( dz );
+	uint32_t oct = (r.dx < 0 ? 4u : 0u) | (r.dy < 0 ? 2u : 0u) | (r.dz < 0 ? 1u : 0u);
+	r.octinv4 = (7u - oct) * 0x01010101u;
+}
+
+// Instance entry.  ISECT_REFERENCE: exactly TopLevelBVH::Traverse's leaf code (bvh.cpp:607-610):
+//   O' = inv.TransformPoint(O)  (common_types.h:623-635, incl. the w != 1 divide)
+//   D' = normalize(inv.TransformVector(D))  (common_types.h:616-621; normalize = v * (1.0f/sqrtf(dot)), :87,363)
+// so t inside the instance is measured along the re-normalised object-space direction, as in the reference.
+// ISECT_WATERTIGHT: affine transform, direction NOT renormalised (t stays the world-space parameter).
+template <int ISECT>
+__device__ __forceinline__ void enterInstance( RayState& r, const float4* __restrict__ rec )
+{
+	const float4 r0 = __ldg( rec + 0 ), r1 = __ldg( rec + 1 ), r2 = __ldg( rec + 2 );
+	const float ox = r.ox, oy = r.oy, oz = r.oz, dx = r.dx, dy = r.dy, dz = r.dz;
+	if (ISECT == ISECT_REFERENCE)
+	{
+		const float4 r3 = __ldg( rec + 3 );
+		float px = r0.x * ox + r0.y * oy + r0.z * oz + r0.w;
+		float py = r1.x * ox + r1.y * oy + r1.z * oz + r1.w;
+		float pz = r2.x * ox + r2.y * oy + r2.z * oz + r2.w;
+		float w = r3.x * ox + r3.y * oy + r3.z * oz + r3.w;
+		if (w != 1) { float iw = 1.f / w; px = px * iw, py = py * iw, pz = pz * iw; }
+		float vx = r0.x * dx + r0.y * dy + r0.z * dz;
+		float vy = r1.x * dx + r1.y * dy + r1.z * dz;
+		float vz = r2.x * dx + r2.y * dy + r2.z * dz;
+		float invLen = 1.0f / sqrtf( vx * vx + vy * vy + vz * vz );
+		r.ox = px, r.oy = py, r.oz = pz;
+		r.dx = vx * invLen, r.dy = vy * invLen, r.dz = vz * invLen;
+	}
+	else
+	{
+		r.ox = __fmaf_rn( r0.x, ox, __fmaf_rn( r0.y, oy, __fmaf_rn( r0.z, oz, r0.w ) ) );
+		r.oy = __fmaf_rn( r1.x, ox, __fmaf_rn( r1.y, oy, __fmaf_rn( r1.z, oz, r1.w ) ) );
+		r.oz = __fmaf_rn( r2.x, ox, __fmaf_rn( r2.y, oy, __fmaf_rn( r2.z, oz, r2.w ) ) );
+		r.dx = __fmaf_rn( r0.x, dx, __fmaf_rn( r0.y, dy, r0.z * dz ) );
+		r.dy = __fmaf_rn( r1.x, dx, __fmaf_rn( r1.y, dy, r1.z * dz ) );
+		r.dz = __fmaf_rn( r2.x, dx, __fmaf_rn( r2.y, dy, r2.z * dz ) );
+	}
+	setupSlab( r );
+}
+
+// Triangle test.  ISECT_REFERENCE restates Ray::IntersectTriangle (lib/RenderCore_Bart/common.h:19-50)
+// operation by operation (e1/e2 are the same floats the reference computes at :25-26; f = 1.0/a in double
+// rounded to float equals the IEEE float quotient; bounds (EPSILON, 1/EPSILON) at :43), plus the wave's
+// own (tmin, t) interval.  Returns true and updates t,u,v on acceptance (strict found_t < t, bvh.cpp:268).
+template <int ISECT>
+__device__ __forceinline__ bool intersectTriangle( const RayState& r, const float4 v0, const float4 e1, const float4 e2, float& t,
+	float& uOut, float& vOut )
+{
+	if (ISECT == ISECT_REFERENCE)
+	{
+		const float hx = r.dy * e2.z - r.dz * e2.y, hy = r.dz * e2.x - r.dx * e2.z, hz = r.dx * e2.y - r.dy * e2.x;
+		const float a = e1.x * hx + e1.y * hy + e1.z * hz;
+		if (a > -REF_EPSILON && a < REF_EPSILON) return false;
+		const float f = 1.0f / a;
+		const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
+		const float u = f * (sx * hx + sy * hy + sz * hz);
+		if (u < 0.0f || u > 1.0f) return false;
+		const float qx = sy * e1.z - sz * e1.y, qy = sz * e1.x - sx * e1.z, qz = sx * e1.y - sy * e1.x;
+		const float v = f * (r.dx * qx + r.dy * qy + r.dz * qz);
+		if (v < 0.0f || u + v > 1.0f) return false;
+		const float tt = f * (e2.x * qx + e2.y * qy + e2.z * qz);
+		if (tt > REF_EPSILON && tt < 1 / REF_EPSILON && tt > r.tmin && tt < t) { t = tt, uOut = u, vOut = v; return true; }
+		return false;
+	}
+	else
+	{
+		// fused Moeller-Trumbore without absolute epsilons (scale invariant); edges shared by two
+		// triangles see the same rounded products, inclusive on both sides
+		const float hx = __fmaf_rn( r.dy, e2.z, -(r.dz * e2.y) ), hy = __fmaf_rn( r.dz, e2.x, -(r.dx * e2.z) ),
+					hz = __fmaf_rn( r.dx, e2.y, -(r.dy * e2.x) );
+		const float a = __fmaf_rn( e1.x, hx, __fmaf_rn( e1.y, hy, e1.z * hz ) );
+		if (a == 0.0f) return false;
+		const float f = __frcp_rn( a );
+		const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
+		const float u = f * __fmaf_rn( sx, hx, __fmaf_rn( sy, hy, sz * hz ) );
+		if (u < 0.0f || u > 1.0f) return false;
+		const float qx = __fmaf_rn( sy, e1.z, -(sz * e1.y) ), qy = __fmaf_rn( sz, e1.x, -(sx * e1.z) ),
+					qz = __fmaf_rn( sx, e1.y, -(sy * e1.x) );
+		const float v = f * __fmaf_rn( r.dx, qx, __fmaf_rn( r.dy, qy, r.dz * qz ) );
+		if (v < 0.0f || u + v > 1.0f) return false;
+		const float tt = f * __fmaf_rn( e2.x, qx, __fmaf_rn( e2.y, qy, e2.z * qz ) );
+		if (tt > r.tmin && tt < t) { t = tt, uOut = u, vOut = v; return true; }
+		return false;
+	}
+}
+
+
+// One wide-node visit: decode the 8 quantised child boxes and return the octant-ordered hit mask
+// (bits 31..24: inner children in visiting order, bits 23..0: leaf primitives relative to primBase).
+__device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
+	const uint4 n4 )
+{
+	const uint32_t ew = n0.w;
+	const float sx = __uint_as_float( (ew & 0xffu) << 23 ), sy = __uint_as_float( ((ew >> 8) & 0xffu) << 23 ),
+				sz = __uint_as_float( ((ew >> 16) & 0xffu) << 23 );
+	// plane t = (p + b*s - O) * idir = F*A + B with F = 2^23 + 256 b (see qbyte): A = s*idir/256,
+	// B = ((p - O) - 32768 s) * idir.  Far planes are scaled by 1+2^-21 so float rounding can only widen a box.
+	const float K = 1.0f + 4.76837158e-7f;
+	const float ax = (sx * 0.00390625f) * r.ix, ay = (sy * 0.00390625f) * r.iy, az = (sz * 0.00390625f) * r.iz;
+	const float bx = __fmaf_rn( -32768.f, sx, __uint_as_float( n0.x ) - r.ox ) * r.ix;
+	const float by = __fmaf_rn( -32768.f, sy, __uint_as_float( n0.y ) - r.oy ) * r.iy;
+	const float bz = __fmaf_rn( -32768.f, sz, __uint_as_float( n0.z ) - r.oz ) * r.iz;
+	const float axf = ax * K, ayf = ay * K, azf = az * K, bxf = bx * K, byf = by * K, bzf = bz * K;
+	const bool nx = r.dx < 0, ny = r.dy < 0, nz = r.dz < 0;
+	uint32_t hitmask = 0;
+#pragma unroll
+	for (int i = 0; i < 2; i++)
+	{
+		const uint32_t meta4 = i ? n1.w : n1.z;
+		const uint32_t qlox = i ? n2.y : n2.x, qloy = i ? n2.w : n2.z, qloz = i ? n3.y : n3.x;
+		const uint32_t qhix = i ? n3.w : n3.z, qhiy = i ? n4.y : n4.x, qhiz = i ? n4.w : n4.z;
+		const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
+		const uint32_t neary = ny ? qhiy : qloy, fary = ny ? qloy : qhiy;
+		const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
+		const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+		const uint32_t innerMask4 = sign_extend_s8x4( isInner4 << 3 );
+		const uint32_t bitIndex4 = (meta4 ^ (r.octinv4 & innerMask4)) & 0x1f1f1f1fu;
+		const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+#pragma unroll
+		for (int j = 0; j < 4; j++)
+		{
+			const uint32_t sel = 0x7604u | (j << 4);
+			const float tnx = __fmaf_rn( qbyte( nearx, sel ), ax, bx ), tny = __fmaf_rn( qbyte( neary, sel ), ay, by ),
+						tnz = __fmaf_rn( qbyte( nearz, sel ), az, bz );
+			const float tfx = __fmaf_rn( qbyte( farx, sel ), axf, bxf ), tfy = __fmaf_rn( qbyte( fary, sel ), ayf, byf ),
+						tfz = __fmaf_rn( qbyte( farz, sel ), azf, bzf );
+			const float tn = fmaxf( max3f( tnx, tny, tnz ), r.tmin );
+			const float tf = fminf( min3f( tfx, tfy, tfz ), r.t );
+			if (tn <= tf)
+			{
+				const uint32_t bits = (childBits4 >> (8 * j)) & 0xffu, idx = (bitIndex4 >> (8 * j)) & 0xffu;
+				hitmask |= bits << idx;
+			}
+		}
+	}
+	return hitmask;
+}
+
+template <int ISECT, bool ANYHIT, bool COUNT>
+__global__ void __launch_bounds__( BLOCK_THREADS, 4 ) traceKernel( const TraceArgs a )
+{
+	__shared__ uint2 sstack[STACK_SMEM * BLOCK_THREADS];
+	uint2 lstack[STACK_LOCAL];
+	const uint32_t lane = threadIdx.x & 31;
+	const uint32_t total = a.countPtr ? __ldg( a.countPtr ) : a.count;
+	const uint4* __restrict__ nodes = a.nodes;
+	const float4* __restrict__ tris = a.tris;
+
+	RayState r;
+	uint32_t rayIdx = 0, hitPrim = 0, hitInst = 0, curInst = 0, nNodes = 0, nTris = 0;
+	float hitU = 0, hitV = 0;
+	uint2 ngroup = make_uint2( 0, 0 ), tgroup = make_uint2( 0, 0 );
+	int sp = 0, instBase = -1;
+	bool active = false, exhausted = false;
+
+	auto push = [&]( const uint2 g ) {
+		if (sp < STACK_SMEM) sstack[sp * BLOCK_THREADS + threadIdx.x] = g; else lstack[sp - STACK_SMEM] = g;
+		sp++;
+	};
+	auto pop = [&]() -> uint2 {
+		sp--;
+		return sp < STACK_SMEM ? sstack[sp * BLOCK_THREADS + threadIdx.x] : lstack[sp - STACK_SMEM];
+	};
+
+	while (true)
+	{
+		// ---- ray fetch: idle lanes claim consecutive rays with one aggregated atomic ------------------
+		const uint32_t idleMask = __ballot_sync( 0xffffffffu, !active );
+		if (idleMask && !exhausted)
+		{
+			const uint32_t n = __popc( idleMask ), leader = __ffs( idleMask ) - 1;
+			uint32_t base = 0;
+			if (lane == leader) base = atomicAdd( a.fetchCounter, n );
+			base = __shfl_sync( 0xffffffffu, base, leader );
+			if (!active)
+			{
+				rayIdx = base + __popc( idleMask & lanemask_lt() );
+				if (rayIdx < total)
+				{
+					const float4 O4 = __ldg( a.rayO + rayIdx ), D4 = __ldg( a.rayD + rayIdx );
+					r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.tmin = O4.w;
+					r.dx = D4.x, r.dy = D4.y, r.dz = D4.z, r.t = D4.w;
+					setupSlab( r );
+					ngroup = make_uint2( a.tlasRoot, 0x80000000u ), tgroup = make_uint2( 0, 0 );
+					sp = 0, instBase = -1, curInst = NO_INSTANCE;
+					hitPrim = 0xffffffffu, hitInst = 0, hitU = hitV = 0, nNodes = nTris = 0;
+					active = true;
+				}
+			}
+			if (base + n >= total) exhausted = true;
+		}
+		if (!__any_sync( 0xffffffffu, active )) break;
+
+		// ---- traversal --------------------------------------------------------------------------------
+		if (active)
+		{
+			while (true)
+			{
+				if (ngroup.y > 0x00ffffffu)
+				{
+					const uint32_t hits = ngroup.y, imask = hits & 0xffu;
+					const uint32_t bit = 31 - __clz( hits );
+					ngroup.y = hits & ~(1u << bit);
+					const uint32_t nodeBase = ngroup.x;
+					if (ngroup.y > 0x00ffffffu) push( ngroup );
+					const uint32_t slot = (bit - 24) ^ (r.octinv4 & 0xffu);
+					const uint32_t rel = __popc( imask & ~(0xffffffffu << slot) );
+					const uint4* np = nodes + (size_t)(nodeBase + rel) * 5;
+					const uint4 n0 = __ldg( np ), n1 = __ldg( np + 1 ), n2 = __ldg( np + 2 ), n3 = __ldg( np + 3 ), n4 = __ldg( np + 4 );
+					if (COUNT) nNodes++;
+					const uint32_t hm = intersectNode( r, n0, n1, n2, n3, n4 );
+					ngroup = make_uint2( n1.x, (hm & 0xff000000u) | (n0.w >> 24) );
+					tgroup = make_uint2( n1.y, hm & 0x00ffffffu );
+				}
+				bool finished = false;
+				while (tgroup.y)
+				{
+					const uint32_t bit = 31 - __clz( tgroup.y );
+					tgroup.y &= ~(1u << bit);
+					const uint32_t idx = tgroup.x + bit;
+					if (instBase < 0)
+					{
+						// top level: the primitive is an instance -- remember what is left here, then descend
+						if (ngroup.y > 0x00ffffffu) push( ngroup );
+						if (tgroup.y) push( tgroup );
+						const float4* rec = a.instances + (size_t)idx * 6;
+						const float4 info = __ldg( rec + 4 );
+						enterInstance<ISECT>( r, rec );
+						curInst = __float_as_uint( info.y );
+						instBase = sp;
+						ngroup = make_uint2( __float_as_uint( info.x ), 0x80000000u );
+						tgroup = make_uint2( 0, 0 );
+						break;
+					}
+					const float4* tp = tris + (size_t)idx * 3;
+					const float4 v0 = __ldg( tp ), e1 = __ldg( tp + 1 ), e2 = __ldg( tp + 2 );
+					if (COUNT) nTris++;
+					if (intersectTriangle<ISECT>( r, v0, e1, e2, r.t, hitU, hitV ))
+					{
+						hitPrim = __float_as_uint( v0.w ), hitInst = curInst;
+						if (ANYHIT) { finished = true; break; }
+					}
+				}
+				if (!finished && ngroup.y <= 0x00ffffffu)
+				{
+					if (sp == instBase)
+					{
+						// bottom level exhausted: back to the world-space ray (t is kept, as in bvh.cpp:612-619)
+						const float4 O4 = __ldg( a.rayO + rayIdx ), D4 = __ldg( a.rayD + rayIdx );
+						r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.dx = D4.x, r.dy = D4.y, r.dz = D4.z;
+						setupSlab( r );
+						instBase = -1, curInst = NO_INSTANCE;
+					}
+					if (sp == 0) finished = true;
+					else
+					{
+						const uint2 g = pop();
+						if (g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
+					}
+				}
+				if (finished)
+				{
+					if (ANYHIT)
+					{
+						if (hitPrim != 0xffffffffu) atomicOr( a.occluded + (rayIdx >> 5), 1u << (rayIdx & 31) );
+					}
+					else
+					{
+						const bool hit = hitPrim != 0xffffffffu;
+						const uint32_t bary = (uint32_t)(65535.0f * hitU) + ((uint32_t)(65535.0f * hitV) << 16);
+						a.hits[rayIdx] = make_float4( __uint_as_float( hit ? bary : 0u ), __uint_as_float( hit ? hitInst : 0u ),
+							__uint_as_float( hitPrim ), hit ? r.t : 1e34f );
+					}
+					if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
+					active = false;
+					break;
+				}
+				// too few lanes left in this warp and rays remain: go back and refill the idle lanes
+				if (!exhausted && __popc( __activemask() ) < 20) break;
+			}
+		}
+		__syncwarp();
+	}
+}
+
+} // namespace
+
+namespace {
+int gExtendBlocksPerSM = 0, gShadowBlocksPerSM = 0;
+template <typename K> int blocksPerSM( K kernel )
+{
+	int n = 0;
+	cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, kernel, BLOCK_THREADS, 0 );
+	return n > 0 ? n : 1;
+}
+} // namespace
+
+cudaError_t LaunchExtend( const TraceArgs& a, IsectMode mode, bool countSteps, int smCount, cudaStream_t s )
+{
+	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
+	if (e != cudaSuccess) return e;
+	void ( *k )( const TraceArgs ) = mode == ISECT_REFERENCE
+		? (countSteps ? traceKernel<ISECT_REFERENCE, false, true> : traceKernel<ISECT_REFERENCE, false, false>)
+		: (countSteps ? traceKernel<ISECT_WATERTIGHT, false, true> : traceKernel<ISECT_WATERTIGHT, false, false>);
+	if (!gExtendBlocksPerSM) gExtendBlocksPerSM = blocksPerSM( traceKernel<ISECT_REFERENCE, false, false> );
+	k<<<smCount * gExtendBlocksPerSM, BLOCK_THREADS, 0, s>>>( a );
+	return cudaGetLastError();
+}
+
+cudaError_t LaunchShadow( const TraceArgs& a, IsectMode mode, int smCount, cudaStream_t s )
+{
+	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
+	if (e != cudaSuccess) return e;
+	void ( *k )( const TraceArgs ) = mode == ISECT_REFERENCE ? traceKernel<ISECT_REFERENCE, true, false> : traceKernel<ISECT_WATERTIGHT, true, false>;
+	if (!gShadowBlocksPerSM) gShadowBlocksPerSM = blocksPerSM( traceKernel<ISECT_REFERENCE, true, false> );
+	k<<<smCount * gShadowBlocksPerSM, BLOCK_THREADS, 0, s>>>( a );
+	return cudaGetLastError();
+}
+
+} // namespace b200

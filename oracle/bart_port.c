@@ -466,6 +466,7 @@ int port_set_geometry( void* h, int meshIdx, const float* verts, int triCount )
 {
 	Scene* s = (Scene*)h;
 	Mesh* m;
+	if (triCount <= 0) return 2; /* the reference has undefined behaviour for empty meshes (new BVHNode[0], bvh.cpp:64-69) */
 	if (meshIdx >= s->meshCount)
 	{
 		if (s->meshCount == s->meshCap)

@@ -50,6 +50,7 @@ int ref_set_geometry( void* h, int meshIdx, const float* verts, int triCount )
 {
 	RefScene* s = (RefScene*)h;
 	Mesh* mesh;
+	if (triCount <= 0) return 2; // BVH2::Rebuild writes pool[0] of a zero-length array (bvh.cpp:64-69): undefined behaviour
 	if (meshIdx >= (int)s->meshes.size())
 	{
 		s->meshes.push_back( mesh = new Mesh( triCount * 3, triCount ) );

@@ -1,0 +1,56 @@
+"""Parity checker: CUDA hit buffers vs the CPU oracle, with the documented exception classes.
+
+Bar (BASELINE.json north_star): prim / instance ids bit-exact for all rays except documented near-tie /
+grazing rays (< 1e-5 of rays); t within 1e-5 relative (we require BIT-EXACT t in ISECT_REFERENCE mode
+for every ray outside the exception classes).
+
+Exception classes, decided with the oracle's own arithmetic (never with the GPU's):
+  tie      -- GPU and oracle report different triangles whose reference-arithmetic t is bit-identical
+              (a ray through a shared edge/vertex): the reference keeps the first one ITS tree visits
+              (strict found_t < t, bvh.cpp:268), which no other tree can reproduce.
+  grazing  -- the GPU's answer equals the exhaustive search over all triangles (same triangle arithmetic)
+              but the reference BVH missed it: its float slab test is not conservative (bvh.cpp:7-42) and
+              culls a box the ray touches at a corner/edge.
+Anything else is a failure.
+"""
+import numpy as np
+
+from lighthouse2_b200.core import unpack_hits
+
+MISS_T = np.float32(1e34)
+
+
+def compare(case_name, hits, oracle_port, O, D, ref_t, ref_prim, ref_inst=None, check_inst=True):
+    h = unpack_hits(hits)
+    n = len(ref_t)
+    gt, gp, gi = h["t"], h["prim"], h["inst"]
+    same = (gp == ref_prim) & (gt.view(np.uint32) == ref_t.view(np.uint32))
+    if check_inst and ref_inst is not None:
+        same &= (gi == ref_inst) | (ref_prim < 0)
+    bad = np.flatnonzero(~same)
+    report = dict(case=case_name, rays=n, exact=int(same.sum()), tie=0, grazing=0, wrong=0)
+    if len(bad):
+        Ob, Db = O[bad], D[bad]
+        # reference-arithmetic t of the triangle the GPU chose
+        t_gpu_choice = oracle_port.t_of(Ob, Db, np.where(gp[bad] >= 0, gi[bad], -1), gp[bad])
+        tb, pb, ib = oracle_port.trace(Ob, Db, nthreads=8, mode="brute")
+        for k, i in enumerate(bad):
+            gpu_consistent = gt[i].view(np.uint32) == t_gpu_choice[k].view(np.uint32)  # GPU t is what the reference computes for that triangle
+            if gp[i] >= 0 and ref_prim[i] >= 0 and gpu_consistent and gt[i].view(np.uint32) == ref_t[i].view(np.uint32):
+                report["tie"] += 1
+            elif gpu_consistent and gt[i].view(np.uint32) == tb[k].view(np.uint32) and (gp[i] == pb[k] or gt[i] == tb[k]) and gt[i] < ref_t[i]:
+                report["grazing"] += 1
+            else:
+                report["wrong"] += 1
+                if report["wrong"] <= 5:
+                    print(f"[{case_name}] WRONG ray {i}: gpu (t={gt[i]!r}, prim={gp[i]}, inst={gi[i]}) oracle (t={ref_t[i]!r}, prim={ref_prim[i]}) "
+                          f"brute (t={tb[k]!r}, prim={pb[k]}, inst={ib[k]}) t_of_gpu_choice={t_gpu_choice[k]!r}")
+    report["exception_rate"] = (report["tie"] + report["grazing"]) / max(n, 1)
+    return report
+
+
+def assert_parity(report, max_rate=1e-5):
+    print("parity:", report)
+    assert report["wrong"] == 0, report
+    # < 1e-5 of rays; for small ray sets allow a single exceptional ray
+    assert report["tie"] + report["grazing"] <= max(1, int(max_rate * report["rays"])), report

@@ -1,0 +1,158 @@
+"""GPU parity tests: every call goes through the C ABI of libRenderCore_B200.so (host buffers in, host
+buffers out) and is compared with the golden hit buffers / the CPU oracle on the same seeded inputs."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import parity
+from lighthouse2_b200 import core, scenes
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def oracles():
+    import oracle
+    oracle.build()
+    return oracle
+
+
+def _run_case(case, oracles, golden=True, isect=0):
+    O, D = case["rays"]
+    rc = core.RenderCoreB200(0)
+    rc.Setting("isectMode", isect)
+    cases.load_core(rc, case)
+    O4, D4 = core.pack_rays(O, D)
+    hits = rc.TraceClosest(O4, D4)
+    port = cases.load_oracle(case, "port")
+    if golden:
+        g = np.load(os.path.join(GOLDEN, case["name"] + ".npz"))
+        ref_t, ref_prim, ref_inst = g["t"], g["prim"], g["inst"]
+    else:
+        ref_t, ref_prim, ref_inst = port.trace(O, D, nthreads=8)
+    rep = parity.compare(case["name"], hits, port, O, D, ref_t, ref_prim, ref_inst)
+    rc.Shutdown()
+    return rep, hits
+
+
+def test_c1_golden_hit_buffer(oracles):
+    """BASELINE configs[0]: 1K-triangle mesh, 640x360 primary rays vs the golden buffer made by the reference."""
+    rep, hits = _run_case(cases.case_c1(), oracles)
+    parity.assert_parity(rep)
+    assert rep["rays"] == 230400
+
+
+@pytest.mark.parametrize("make", [cases.case_soup, cases.case_instanced, cases.case_axis_aligned, cases.case_single_triangle])
+def test_small_cases_golden(oracles, make):
+    rep, _ = _run_case(make(), oracles)
+    parity.assert_parity(rep)
+
+
+def test_bigger_soup_vs_oracle(oracles):
+    case = cases.case_soup(n_tris=200_000, n_rays=300_000, seed=21)
+    rep, _ = _run_case(case, oracles, golden=False)
+    parity.assert_parity(rep)
+
+
+def test_any_hit_matches_closest(oracles):
+    """occluded(tmax) <=> oracle closest t < tmax (Appendix A.2), and == the GPU's own closest-hit wave."""
+    case = cases.case_soup(n_tris=50_000, n_rays=200_000, seed=31)
+    O, D = case["rays"]
+    rc = cases.load_core(core.RenderCoreB200(0), case)
+    rng = np.random.default_rng(1)
+    tmax = rng.uniform(0.5, 12.0, len(O)).astype(np.float32)
+    O4, D4 = core.pack_rays(O, D, tmin=0.0, tmax=tmax)
+    occ = rc.TraceAny(O4, D4)
+    port = cases.load_oracle(case, "port")
+    t, prim, _ = port.trace(O, D, nthreads=8)
+    expect = t < tmax
+    bad = np.flatnonzero(occ != expect)
+    # a ray whose closest t equals tmax to the last bit cannot disagree (strict <); anything else is an error
+    assert len(bad) <= max(1, int(1e-5 * len(O))), (len(bad), bad[:10])
+    O4c, D4c = core.pack_rays(O, D)
+    h = core.unpack_hits(rc.TraceClosest(O4c, D4c))
+    assert np.array_equal(occ, h["t"] < tmax)
+    rc.Shutdown()
+
+
+def test_empty_mesh_zero_rays_and_misses():
+    rc = core.RenderCoreB200(0)
+    case = cases.case_empty()
+    cases.load_core(rc, case)
+    O4, D4 = core.pack_rays(*case["rays"])
+    h = core.unpack_hits(rc.TraceClosest(O4, D4))
+    assert (h["prim"] == -1).all() and (h["t"] == np.float32(1e34)).all()
+    assert rc.TraceClosest(O4[:0], D4[:0]).shape == (0, 4)
+    assert not rc.TraceAny(O4, D4).any()
+    rc.Shutdown()
+
+
+def test_ragged_ray_counts(oracles):
+    """Ray counts that are not multiples of the warp / block size, through the 1-bit output too."""
+    case = cases.case_soup(n_tris=3000, n_rays=5000, seed=41)
+    O, D = case["rays"]
+    rc = cases.load_core(core.RenderCoreB200(0), case)
+    port = cases.load_oracle(case, "port")
+    t, prim, _ = port.trace(O, D, nthreads=4)
+    for n in (1, 31, 33, 127, 129, 4097):
+        O4, D4 = core.pack_rays(O[:n], D[:n])
+        h = core.unpack_hits(rc.TraceClosest(O4, D4))
+        assert np.array_equal(h["prim"], prim[:n]) and np.array_equal(h["t"].view(np.uint32), t[:n].view(np.uint32))
+        O4, D4 = core.pack_rays(O[:n], D[:n], tmax=3.0)
+        assert np.array_equal(rc.TraceAny(O4, D4), t[:n] < 3.0)
+    rc.Shutdown()
+
+
+def test_tmin_tmax_window(oracles):
+    """The wave's own (tmin, tmax) interval on top of the reference's fixed (1e-4, 1e4) window."""
+    case = cases.case_soup(n_tris=3000, n_rays=20000, seed=43)
+    O, D = case["rays"]
+    rc = cases.load_core(core.RenderCoreB200(0), case)
+    port = cases.load_oracle(case, "port")
+    t, prim, _ = port.trace(O, D, nthreads=4)
+    O4, D4 = core.pack_rays(O, D, tmin=0.0, tmax=2.0)
+    h = core.unpack_hits(rc.TraceClosest(O4, D4))
+    inside = t < 2.0
+    assert np.array_equal(h["prim"][inside], prim[inside])
+    assert (h["prim"][~inside] == -1).all()
+    rc.Shutdown()
+
+
+def test_refit_equals_rebuild(oracles):
+    """GPU refit (animated mesh) gives the same hits as a fresh build of the deformed mesh, and as the oracle
+    (which rebuilds: the reference has no refit, rendercore.cpp:78)."""
+    n_tris = 20000
+    v0 = scenes.deforming_sphere(n_tris, time=0.0, radius=3.0)
+    v1 = scenes.deforming_sphere(n_tris, time=1.3, radius=3.0)
+    O, D = scenes.random_rays(100_000, 5.0, seed=77)
+    O4, D4 = core.pack_rays(O, D)
+    rc = core.RenderCoreB200(0)
+    rc.SetGeometry(0, v0); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
+    rc.SetGeometry(0, v1)  # same triangle count -> GPU refit
+    rc.UpdateToplevel()
+    st = rc.GetCoreStats()
+    assert st["refitTime"] > 0
+    hits = rc.TraceClosest(O4, D4)
+    case = dict(name="refit", meshes=[v1], instances=[(0, None)], rays=(O, D))
+    port = cases.load_oracle(case, "port")
+    t, prim, inst = port.trace(O, D, nthreads=8)
+    rep = parity.compare("refit", hits, port, O, D, t, prim, inst)
+    parity.assert_parity(rep)
+    rc2 = cases.load_core(core.RenderCoreB200(0), case)
+    h2 = rc2.TraceClosest(O4, D4)
+    assert np.array_equal(hits.view(np.uint32)[:, 1:], h2.view(np.uint32)[:, 1:])
+    rc.Shutdown(); rc2.Shutdown()
+
+
+def test_step_counters(oracles):
+    case = cases.case_soup(n_tris=20000, n_rays=20000, seed=51)
+    rc = cases.load_core(core.RenderCoreB200(0), case)
+    rc.Setting("countSteps", 1)
+    O4, D4 = core.pack_rays(*case["rays"])
+    rc.TraceClosest(O4, D4)
+    nodes, tris = rc.StepCounters(len(O4))
+    assert nodes.min() >= 1 and nodes.mean() < 200 and tris.mean() < 200
+    rc.Shutdown()
