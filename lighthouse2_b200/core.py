@@ -14,7 +14,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libRenderCore_B200.so")
+LIB_PATH = os.environ.get("B200_LIB") or os.path.join(HERE, "lib", "libRenderCore_B200.so")  # B200_LIB: tuning variants (tools/build_variant.sh)
 CSRC = os.path.join(HERE, "csrc")
 
 # every symbol include/rendercore_b200.h declares (checked by tests/test_abi.py without a GPU)

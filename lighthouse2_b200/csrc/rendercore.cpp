@@ -354,6 +354,7 @@ TraceArgs RenderCore::baseArgs() const
 	a.nodes = (const uint4*)nodePool.ptr, a.tris = (const float4*)triPool.ptr, a.instances = (const float4*)instPool.ptr;
 	a.fetchCounter = (uint32_t*)fetchCounter.ptr;
 	a.tlasRoot = tlasRoot;
+	a.magic = 0x4B000000u;
 	return a;
 }
 

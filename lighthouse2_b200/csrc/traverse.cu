@@ -56,8 +56,18 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4( uint32_t x )
 	asm( "prmt.b32 %0, %1, 0, 0xba98;" : "=r"( r ) : "r"( x ) ); // replicate-sign mode selectors 8..b
 	return r;
 }
-// byte `sel` of q placed in byte 1 of 0x4B000000: the float 2^23 + 256*b (exact), decoded by one FFMA
-__device__ __forceinline__ float qbyte( uint32_t q, uint32_t sel ) { return __uint_as_float( __byte_perm( q, 0x4B000000u, sel ) ); }
+// byte J of q placed in byte 1 of K = 0x4B000000: the float 2^23 + 256*b (exact), decoded by one FFMA.  K arrives as
+// a kernel argument so that ptxas keeps it in a register and encodes the SELECTOR as the immediate (PRMT has one
+// immediate slot; with a literal K the four selectors were re-materialised with a MOV in front of every PRMT).
+template <int J> __device__ __forceinline__ float qbyte( uint32_t q, uint32_t K )
+{
+	uint32_t r;
+	if (J == 0) asm( "prmt.b32 %0, %1, %2, 0x7604;" : "=r"( r ) : "r"( q ), "r"( K ) );
+	else if (J == 1) asm( "prmt.b32 %0, %1, %2, 0x7614;" : "=r"( r ) : "r"( q ), "r"( K ) );
+	else if (J == 2) asm( "prmt.b32 %0, %1, %2, 0x7624;" : "=r"( r ) : "r"( q ), "r"( K ) );
+	else asm( "prmt.b32 %0, %1, %2, 0x7634;" : "=r"( r ) : "r"( q ), "r"( K ) );
+	return __uint_as_float( r );
+}
 
 struct RayState {
 	float ox, oy, oz, dx, dy, dz;   // current-space ray (world in the TLAS, object inside an instance)
@@ -117,45 +127,46 @@ __device__ __forceinline__ void enterInstance( RayState& r, const float4* __rest
 // Triangle test.  ISECT_REFERENCE restates Ray::IntersectTriangle (lib/RenderCore_Bart/common.h:19-50)
 // operation by operation (e1/e2 are the same floats the reference computes at :25-26; f = 1.0/a in double
 // rounded to float equals the IEEE float quotient; bounds (EPSILON, 1/EPSILON) at :43), plus the wave's
-// own (tmin, t) interval.  Returns true and updates t,u,v on acceptance (strict found_t < t, bvh.cpp:268).
+// own (tmin, t) interval.  O = (ox,oy,oz,tmin), D = (dx,dy,dz,t).  Returns true and writes tt,u,v on acceptance
+// (strict found_t < t, bvh.cpp:268).
 template <int ISECT>
-__device__ __forceinline__ bool intersectTriangle( const RayState& r, const float4 v0, const float4 e1, const float4 e2, float& t,
+__device__ __forceinline__ bool intersectTriangle( const float4 O, const float4 D, const float4 v0, const float4 e1, const float4 e2, float& tOut,
 	float& uOut, float& vOut )
 {
 	if (ISECT == ISECT_REFERENCE)
 	{
-		const float hx = r.dy * e2.z - r.dz * e2.y, hy = r.dz * e2.x - r.dx * e2.z, hz = r.dx * e2.y - r.dy * e2.x;
+		const float hx = D.y * e2.z - D.z * e2.y, hy = D.z * e2.x - D.x * e2.z, hz = D.x * e2.y - D.y * e2.x;
 		const float a = e1.x * hx + e1.y * hy + e1.z * hz;
 		if (a > -REF_EPSILON && a < REF_EPSILON) return false;
 		const float f = 1.0f / a;
-		const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
+		const float sx = O.x - v0.x, sy = O.y - v0.y, sz = O.z - v0.z;
 		const float u = f * (sx * hx + sy * hy + sz * hz);
 		if (u < 0.0f || u > 1.0f) return false;
 		const float qx = sy * e1.z - sz * e1.y, qy = sz * e1.x - sx * e1.z, qz = sx * e1.y - sy * e1.x;
-		const float v = f * (r.dx * qx + r.dy * qy + r.dz * qz);
+		const float v = f * (D.x * qx + D.y * qy + D.z * qz);
 		if (v < 0.0f || u + v > 1.0f) return false;
 		const float tt = f * (e2.x * qx + e2.y * qy + e2.z * qz);
-		if (tt > REF_EPSILON && tt < 1 / REF_EPSILON && tt > r.tmin && tt < t) { t = tt, uOut = u, vOut = v; return true; }
+		if (tt > REF_EPSILON && tt < 1 / REF_EPSILON && tt > O.w && tt < D.w) { tOut = tt, uOut = u, vOut = v; return true; }
 		return false;
 	}
 	else
 	{
 		// fused Moeller-Trumbore without absolute epsilons (scale invariant); edges shared by two
 		// triangles see the same rounded products, inclusive on both sides
-		const float hx = __fmaf_rn( r.dy, e2.z, -(r.dz * e2.y) ), hy = __fmaf_rn( r.dz, e2.x, -(r.dx * e2.z) ),
-					hz = __fmaf_rn( r.dx, e2.y, -(r.dy * e2.x) );
+		const float hx = __fmaf_rn( D.y, e2.z, -(D.z * e2.y) ), hy = __fmaf_rn( D.z, e2.x, -(D.x * e2.z) ),
+					hz = __fmaf_rn( D.x, e2.y, -(D.y * e2.x) );
 		const float a = __fmaf_rn( e1.x, hx, __fmaf_rn( e1.y, hy, e1.z * hz ) );
 		if (a == 0.0f) return false;
 		const float f = __frcp_rn( a );
-		const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
+		const float sx = O.x - v0.x, sy = O.y - v0.y, sz = O.z - v0.z;
 		const float u = f * __fmaf_rn( sx, hx, __fmaf_rn( sy, hy, sz * hz ) );
 		if (u < 0.0f || u > 1.0f) return false;
 		const float qx = __fmaf_rn( sy, e1.z, -(sz * e1.y) ), qy = __fmaf_rn( sz, e1.x, -(sx * e1.z) ),
 					qz = __fmaf_rn( sx, e1.y, -(sy * e1.x) );
-		const float v = f * __fmaf_rn( r.dx, qx, __fmaf_rn( r.dy, qy, r.dz * qz ) );
+		const float v = f * __fmaf_rn( D.x, qx, __fmaf_rn( D.y, qy, D.z * qz ) );
 		if (v < 0.0f || u + v > 1.0f) return false;
 		const float tt = f * __fmaf_rn( e2.x, qx, __fmaf_rn( e2.y, qy, e2.z * qz ) );
-		if (tt > r.tmin && tt < t) { t = tt, uOut = u, vOut = v; return true; }
+		if (tt > O.w && tt < D.w && tt > 0.0f) { tOut = tt, uOut = u, vOut = v; return true; }
 		return false;
 	}
 }
@@ -163,20 +174,38 @@ __device__ __forceinline__ bool intersectTriangle( const RayState& r, const floa
 
 // One wide-node visit: decode the 8 quantised child boxes and return the octant-ordered hit mask
 // (bits 31..24: inner children in visiting order, bits 23..0: leaf primitives relative to primBase).
-__device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
-	const uint4 n4 )
+template <int J> __device__ __forceinline__ void testChild( const RayState& r, const uint32_t K, const uint32_t nearx, const uint32_t neary,
+	const uint32_t nearz, const uint32_t farx, const uint32_t fary, const uint32_t farz, const float ax, const float ay, const float az,
+	const float bx, const float by, const float bz, const float axf, const float ayf, const float azf, const float bxf, const float byf,
+	const float bzf, const uint32_t childBits4, const uint32_t bitIndex4, uint32_t& hitmask )
+{
+	const float tnx = __fmaf_rn( qbyte<J>( nearx, K ), ax, bx ), tny = __fmaf_rn( qbyte<J>( neary, K ), ay, by ),
+				tnz = __fmaf_rn( qbyte<J>( nearz, K ), az, bz );
+	const float tfx = __fmaf_rn( qbyte<J>( farx, K ), axf, bxf ), tfy = __fmaf_rn( qbyte<J>( fary, K ), ayf, byf ),
+				tfz = __fmaf_rn( qbyte<J>( farz, K ), azf, bzf );
+	const float tn = fmaxf( max3f( tnx, tny, tnz ), r.tmin );
+	const float tf = fminf( min3f( tfx, tfy, tfz ), r.t );
+	if (tn <= tf)
+	{
+		const uint32_t bits = (childBits4 >> (8 * J)) & 0xffu, idx = (bitIndex4 >> (8 * J)) & 0xffu;
+		hitmask |= bits << idx;
+	}
+}
+
+__device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint32_t K, const uint4 n0, const uint4 n1, const uint4 n2,
+	const uint4 n3, const uint4 n4 )
 {
 	const uint32_t ew = n0.w;
 	const float sx = __uint_as_float( (ew & 0xffu) << 23 ), sy = __uint_as_float( ((ew >> 8) & 0xffu) << 23 ),
 				sz = __uint_as_float( ((ew >> 16) & 0xffu) << 23 );
 	// plane t = (p + b*s - O) * idir = F*A + B with F = 2^23 + 256 b (see qbyte): A = s*idir/256,
 	// B = ((p - O) - 32768 s) * idir.  Far planes are scaled by 1+2^-21 so float rounding can only widen a box.
-	const float K = 1.0f + 4.76837158e-7f;
+	const float WIDEN = 1.0f + 4.76837158e-7f;
 	const float ax = (sx * 0.00390625f) * r.ix, ay = (sy * 0.00390625f) * r.iy, az = (sz * 0.00390625f) * r.iz;
 	const float bx = __fmaf_rn( -32768.f, sx, __uint_as_float( n0.x ) - r.ox ) * r.ix;
 	const float by = __fmaf_rn( -32768.f, sy, __uint_as_float( n0.y ) - r.oy ) * r.iy;
 	const float bz = __fmaf_rn( -32768.f, sz, __uint_as_float( n0.z ) - r.oz ) * r.iz;
-	const float axf = ax * K, ayf = ay * K, azf = az * K, bxf = bx * K, byf = by * K, bzf = bz * K;
+	const float axf = ax * WIDEN, ayf = ay * WIDEN, azf = az * WIDEN, bxf = bx * WIDEN, byf = by * WIDEN, bzf = bz * WIDEN;
 	const bool nx = r.dx < 0, ny = r.dy < 0, nz = r.dz < 0;
 	uint32_t hitmask = 0;
 #pragma unroll
@@ -192,42 +221,60 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 		const uint32_t innerMask4 = sign_extend_s8x4( isInner4 << 3 );
 		const uint32_t bitIndex4 = (meta4 ^ (r.octinv4 & innerMask4)) & 0x1f1f1f1fu;
 		const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
-#pragma unroll
-		for (int j = 0; j < 4; j++)
-		{
-			const uint32_t sel = 0x7604u | (j << 4);
-			const float tnx = __fmaf_rn( qbyte( nearx, sel ), ax, bx ), tny = __fmaf_rn( qbyte( neary, sel ), ay, by ),
-						tnz = __fmaf_rn( qbyte( nearz, sel ), az, bz );
-			const float tfx = __fmaf_rn( qbyte( farx, sel ), axf, bxf ), tfy = __fmaf_rn( qbyte( fary, sel ), ayf, byf ),
-						tfz = __fmaf_rn( qbyte( farz, sel ), azf, bzf );
-			const float tn = fmaxf( max3f( tnx, tny, tnz ), r.tmin );
-			const float tf = fminf( min3f( tfx, tfy, tfz ), r.t );
-			if (tn <= tf)
-			{
-				const uint32_t bits = (childBits4 >> (8 * j)) & 0xffu, idx = (bitIndex4 >> (8 * j)) & 0xffu;
-				hitmask |= bits << idx;
-			}
-		}
+		testChild<0>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<1>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<2>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<3>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
 	}
 	return hitmask;
 }
 
+// ---- the wave kernel ------------------------------------------------------------------------------------
+// Lanes own rays and walk the wide BVH; leaf triangles are NOT tested by the lane that found them.  Each lane
+// appends (owner lane, triangle) pairs to a per-warp ring in shared memory and the warp tests 32 of them at a
+// time, one per lane, against the owners' rays mirrored in shared memory (a lane-divergent `while (triangles)`
+// loop ran with ~3 of 32 lanes active on incoherent rays).  Results go back through two ATOMS.MIN per hit:
+// smallest t, then (ties) the earliest-queued pair, so the first-visited triangle wins exact ties like the
+// reference's strict `found_t < t` (bvh.cpp:268).
+constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
+#ifndef B200_REFILL_BELOW
+#define B200_REFILL_BELOW 22
+#endif
+#ifndef B200_PARTIAL_BELOW
+#define B200_PARTIAL_BELOW 12
+#endif
+#ifndef B200_MIN_BLOCKS
+#define B200_MIN_BLOCKS 6
+#endif
+constexpr int QUEUE_CAP = 128;                       // ring entries per warp (a flush starts as soon as 32 are pending)
+constexpr int REFILL_BELOW = B200_REFILL_BELOW;      // leave the traversal loop to fetch rays when fewer lanes are active
+constexpr int PARTIAL_BELOW = B200_PARTIAL_BELOW;    // flush a partially filled ring for waiting lanes when fewer lanes have node work
+
 template <int ISECT, bool ANYHIT, bool COUNT>
-__global__ void __launch_bounds__( BLOCK_THREADS, 4 ) traceKernel( const TraceArgs a )
+__global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel( const TraceArgs a )
 {
 	__shared__ uint2 sstack[STACK_SMEM * BLOCK_THREADS];
+	__shared__ float4 sRayO[BLOCK_THREADS];          // current-space ray of each lane: (ox,oy,oz,tmin)
+	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
+	__shared__ uint32_t sSlot[BLOCK_THREADS];        // flush slot of the winning pair, 0xffffffff = none
+	__shared__ float4 sWorld[BLOCK_THREADS];         // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
+	__shared__ uint32_t sQueue[WARPS_PER_BLOCK][QUEUE_CAP];
 	uint2 lstack[STACK_LOCAL];
-	const uint32_t lane = threadIdx.x & 31;
+	const uint32_t lane = threadIdx.x & 31, warpBase = threadIdx.x & ~31u;
+	uint32_t* const queue = sQueue[threadIdx.x >> 5];
 	const uint32_t total = a.countPtr ? __ldg( a.countPtr ) : a.count;
 	const uint4* __restrict__ nodes = a.nodes;
 	const float4* __restrict__ tris = a.tris;
+	const uint32_t K = a.magic; // 0x4B000000, see qbyte
 
-	RayState r;
-	uint32_t rayIdx = 0, hitPrim = 0, hitInst = 0, curInst = 0, nNodes = 0, nTris = 0;
-	float hitU = 0, hitV = 0;
+	RayState r = {};
+	uint32_t rayIdx = 0, hitPrim = 0, hitInst = 0, hitBary = 0, curInst = 0, nNodes = 0, nTris = 0;
 	uint2 ngroup = make_uint2( 0, 0 ), tgroup = make_uint2( 0, 0 );
 	int sp = 0, instBase = -1;
-	bool active = false, exhausted = false;
+	uint32_t qhead = 0, qtail = 0;     // ring sequence numbers (warp-uniform)
+	uint32_t lastQueued = 0xffffffffu; // sequence number of this lane's newest queued pair
+	bool active = false, exhausted = false, terminated = false;
+	sSlot[threadIdx.x] = 0xffffffffu;
 
 	auto push = [&]( const uint2 g ) {
 		if (sp < STACK_SMEM) sstack[sp * BLOCK_THREADS + threadIdx.x] = g; else lstack[sp - STACK_SMEM] = g;
@@ -236,6 +283,49 @@ __global__ void __launch_bounds__( BLOCK_THREADS, 4 ) traceKernel( const TraceAr
 	auto pop = [&]() -> uint2 {
 		sp--;
 		return sp < STACK_SMEM ? sstack[sp * BLOCK_THREADS + threadIdx.x] : lstack[sp - STACK_SMEM];
+	};
+	auto mirrorRay = [&]() {
+		sRayO[threadIdx.x] = make_float4( r.ox, r.oy, r.oz, r.tmin );
+		sRayD[threadIdx.x] = make_float4( r.dx, r.dy, r.dz, r.t );
+	};
+	// test `n` (<= 32) queued pairs, one per lane; every lane of the warp calls this (converged)
+	auto flush = [&]( const uint32_t n ) {
+		const bool mine = lane < n;
+		bool hit = false;
+		float tt = 0, u = 0, v = 0;
+		uint32_t owner = 0, prim = 0;
+		if (mine)
+		{
+			const uint32_t e = queue[(qhead + lane) & (QUEUE_CAP - 1)];
+			owner = warpBase + (e >> 27);
+			const float4* tp = tris + (size_t)(e & 0x07ffffffu) * 3;
+			const float4 v0 = __ldg( tp ), e1 = __ldg( tp + 1 ), e2 = __ldg( tp + 2 );
+			const float4 O = sRayO[owner], D = sRayD[owner];
+			prim = __float_as_uint( v0.w );
+			hit = intersectTriangle<ISECT>( O, D, v0, e1, e2, tt, u, v );
+		}
+		qhead += n;
+		const uint32_t hitMask = __ballot_sync( 0xffffffffu, hit ); // also orders the mirror reads before the atomics
+		if (hitMask)
+		{
+			uint32_t* const tbest = reinterpret_cast<uint32_t*>( &sRayD[owner].w );
+			if (hit) atomicMin( tbest, __float_as_uint( tt ) );
+			__syncwarp();
+			if (hit && *tbest == __float_as_uint( tt )) atomicMin( &sSlot[owner], lane );
+			__syncwarp();
+			const uint32_t slot = sSlot[threadIdx.x];
+			const bool changed = slot != 0xffffffffu;
+			const uint32_t src = changed ? slot : lane;
+			const uint32_t bary = (uint32_t)(65535.0f * u) + ((uint32_t)(65535.0f * v) << 16);
+			const uint32_t wPrim = __shfl_sync( 0xffffffffu, prim, src ), wBary = __shfl_sync( 0xffffffffu, bary, src );
+			const float wT = __shfl_sync( 0xffffffffu, tt, src );
+			if (changed)
+			{
+				sSlot[threadIdx.x] = 0xffffffffu;
+				r.t = wT, hitPrim = wPrim, hitBary = wBary, hitInst = curInst;
+				if (ANYHIT) terminated = true, ngroup.y = 0, tgroup.y = 0;
+			}
+		}
 	};
 
 	while (true)
@@ -257,9 +347,11 @@ __global__ void __launch_bounds__( BLOCK_THREADS, 4 ) traceKernel( const TraceAr
 					r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.tmin = O4.w;
 					r.dx = D4.x, r.dy = D4.y, r.dz = D4.z, r.t = D4.w;
 					setupSlab( r );
+					sWorld[threadIdx.x] = make_float4( r.ix, r.iy, r.iz, __uint_as_float( r.octinv4 ) );
 					ngroup = make_uint2( a.tlasRoot, 0x80000000u ), tgroup = make_uint2( 0, 0 );
 					sp = 0, instBase = -1, curInst = NO_INSTANCE;
-					hitPrim = 0xffffffffu, hitInst = 0, hitU = hitV = 0, nNodes = nTris = 0;
+					hitPrim = 0xffffffffu, hitInst = 0, hitBary = 0, nNodes = nTris = 0;
+					lastQueued = qhead - 1, terminated = false;
 					active = true;
 				}
 			}
@@ -267,95 +359,136 @@ __global__ void __launch_bounds__( BLOCK_THREADS, 4 ) traceKernel( const TraceAr
 		}
 		if (!__any_sync( 0xffffffffu, active )) break;
 
-		// ---- traversal --------------------------------------------------------------------------------
-		if (active)
+		// ---- traversal: every pass = one node step per lane, then queue / flush triangle pairs ------------
+		while (true)
 		{
-			while (true)
+			// A. node step
+			if (active && ngroup.y > 0x00ffffffu)
 			{
-				if (ngroup.y > 0x00ffffffu)
+				const uint32_t hits = ngroup.y, imask = hits & 0xffu;
+				const uint32_t bit = 31 - __clz( hits );
+				ngroup.y = hits & ~(1u << bit);
+				const uint32_t nodeBase = ngroup.x;
+				if (ngroup.y > 0x00ffffffu) push( ngroup );
+				const uint32_t slot = (bit - 24) ^ (r.octinv4 & 0xffu);
+				const uint32_t rel = __popc( imask & ~(0xffffffffu << slot) );
+				const uint4* np = nodes + (size_t)(nodeBase + rel) * 5;
+				const uint4 n0 = __ldg( np ), n1 = __ldg( np + 1 ), n2 = __ldg( np + 2 ), n3 = __ldg( np + 3 ), n4 = __ldg( np + 4 );
+				if (COUNT) nNodes++;
+				const uint32_t hm = intersectNode( r, K, n0, n1, n2, n3, n4 );
+				ngroup = make_uint2( n1.x, (hm & 0xff000000u) | (n0.w >> 24) );
+				tgroup = make_uint2( n1.y, hm & 0x00ffffffu );
+			}
+			// B. top level: a hit leaf is an instance -- remember what is left here, then descend into its BLAS
+			if (active && instBase < 0 && tgroup.y)
+			{
+				const uint32_t bit = 31 - __clz( tgroup.y );
+				tgroup.y &= ~(1u << bit);
+				const uint32_t idx = tgroup.x + bit;
+				if (ngroup.y > 0x00ffffffu) push( ngroup );
+				if (tgroup.y) push( tgroup );
+				const float4* rec = a.instances + (size_t)idx * 6;
+				const float4 info = __ldg( rec + 4 );
+				enterInstance<ISECT>( r, rec );
+				mirrorRay();
+				curInst = __float_as_uint( info.y );
+				instBase = sp;
+				ngroup = make_uint2( __float_as_uint( info.x ), 0x80000000u );
+				tgroup = make_uint2( 0, 0 );
+			}
+			// C. bottom level: queue (owner, triangle) pairs.  Up to three per lane go in with one ballot-prefix step
+			//    (leaves hold <= 3 triangles); lanes that hit more leaves finish in one-pair-per-lane rounds.
+			{
+				uint32_t tb = (active && instBase >= 0) ? tgroup.y : 0u;
+				const uint32_t cnt = __popc( tb );
+				const uint32_t b1 = __ballot_sync( 0xffffffffu, cnt >= 1 );
+				if (b1)
 				{
-					const uint32_t hits = ngroup.y, imask = hits & 0xffu;
-					const uint32_t bit = 31 - __clz( hits );
-					ngroup.y = hits & ~(1u << bit);
-					const uint32_t nodeBase = ngroup.x;
-					if (ngroup.y > 0x00ffffffu) push( ngroup );
-					const uint32_t slot = (bit - 24) ^ (r.octinv4 & 0xffu);
-					const uint32_t rel = __popc( imask & ~(0xffffffffu << slot) );
-					const uint4* np = nodes + (size_t)(nodeBase + rel) * 5;
-					const uint4 n0 = __ldg( np ), n1 = __ldg( np + 1 ), n2 = __ldg( np + 2 ), n3 = __ldg( np + 3 ), n4 = __ldg( np + 4 );
-					if (COUNT) nNodes++;
-					const uint32_t hm = intersectNode( r, n0, n1, n2, n3, n4 );
-					ngroup = make_uint2( n1.x, (hm & 0xff000000u) | (n0.w >> 24) );
-					tgroup = make_uint2( n1.y, hm & 0x00ffffffu );
-				}
-				bool finished = false;
-				while (tgroup.y)
-				{
-					const uint32_t bit = 31 - __clz( tgroup.y );
-					tgroup.y &= ~(1u << bit);
-					const uint32_t idx = tgroup.x + bit;
-					if (instBase < 0)
+					const uint32_t b2 = __ballot_sync( 0xffffffffu, cnt >= 2 ), b3 = __ballot_sync( 0xffffffffu, cnt >= 3 );
+					uint32_t more = __ballot_sync( 0xffffffffu, cnt >= 4 );
+					const uint32_t lt = lanemask_lt();
+					const uint32_t base = qtail + __popc( b1 & lt ) + __popc( b2 & lt ) + __popc( b3 & lt );
+#pragma unroll
+					for (uint32_t k = 0; k < 3; k++)
+						if (cnt > k)
+						{
+							const uint32_t bit = 31 - __clz( tb );
+							tb &= ~(1u << bit);
+							queue[(base + k) & (QUEUE_CAP - 1)] = (tgroup.x + bit) | (lane << 27);
+							lastQueued = base + k;
+						}
+					if (COUNT) nTris += cnt;
+					qtail += __popc( b1 ) + __popc( b2 ) + __popc( b3 );
+					__syncwarp();
+					while (qtail - qhead >= 32) flush( 32 );
+					while (more)
 					{
-						// top level: the primitive is an instance -- remember what is left here, then descend
-						if (ngroup.y > 0x00ffffffu) push( ngroup );
-						if (tgroup.y) push( tgroup );
-						const float4* rec = a.instances + (size_t)idx * 6;
-						const float4 info = __ldg( rec + 4 );
-						enterInstance<ISECT>( r, rec );
-						curInst = __float_as_uint( info.y );
-						instBase = sp;
-						ngroup = make_uint2( __float_as_uint( info.x ), 0x80000000u );
-						tgroup = make_uint2( 0, 0 );
-						break;
+						const bool has = tb != 0;
+						if (has)
+						{
+							const uint32_t bit = 31 - __clz( tb );
+							tb &= ~(1u << bit);
+							lastQueued = qtail + __popc( more & lt );
+							queue[lastQueued & (QUEUE_CAP - 1)] = (tgroup.x + bit) | (lane << 27);
+						}
+						qtail += __popc( more );
+						__syncwarp();
+						if (qtail - qhead >= 32) flush( 32 );
+						more = __ballot_sync( 0xffffffffu, tb != 0 );
 					}
-					const float4* tp = tris + (size_t)idx * 3;
-					const float4 v0 = __ldg( tp ), e1 = __ldg( tp + 1 ), e2 = __ldg( tp + 2 );
-					if (COUNT) nTris++;
-					if (intersectTriangle<ISECT>( r, v0, e1, e2, r.t, hitU, hitV ))
-					{
-						hitPrim = __float_as_uint( v0.w ), hitInst = curInst;
-						if (ANYHIT) { finished = true; break; }
-					}
+					if (active && instBase >= 0) tgroup.y = 0;
 				}
-				if (!finished && ngroup.y <= 0x00ffffffu)
+			}
+			// D. lanes without node work: leave the instance / pop / retire (only once their queued pairs are tested)
+			bool waiting = false;
+			if (active && ngroup.y <= 0x00ffffffu)
+			{
+				const bool pending = (int32_t)(lastQueued - qhead) >= 0;
+				if (terminated || sp == instBase)
 				{
-					if (sp == instBase)
+					if (pending) waiting = true;
+					else if (!terminated)
 					{
 						// bottom level exhausted: back to the world-space ray (t is kept, as in bvh.cpp:612-619)
 						const float4 O4 = __ldg( a.rayO + rayIdx ), D4 = __ldg( a.rayD + rayIdx );
+						const float4 W = sWorld[threadIdx.x];
 						r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.dx = D4.x, r.dy = D4.y, r.dz = D4.z;
-						setupSlab( r );
+						r.ix = W.x, r.iy = W.y, r.iz = W.z, r.octinv4 = __float_as_uint( W.w );
 						instBase = -1, curInst = NO_INSTANCE;
 					}
-					if (sp == 0) finished = true;
+				}
+				if (!waiting)
+				{
+					if (terminated || sp == 0)
+					{
+						if (ANYHIT)
+						{
+							if (hitPrim != 0xffffffffu) atomicOr( a.occluded + (rayIdx >> 5), 1u << (rayIdx & 31) );
+						}
+						else
+						{
+							const bool hit = hitPrim != 0xffffffffu;
+							a.hits[rayIdx] = make_float4( __uint_as_float( hit ? hitBary : 0u ), __uint_as_float( hit ? hitInst : 0u ),
+								__uint_as_float( hitPrim ), hit ? r.t : 1e34f );
+						}
+						if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
+						active = false;
+					}
 					else
 					{
 						const uint2 g = pop();
 						if (g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
 					}
 				}
-				if (finished)
-				{
-					if (ANYHIT)
-					{
-						if (hitPrim != 0xffffffffu) atomicOr( a.occluded + (rayIdx >> 5), 1u << (rayIdx & 31) );
-					}
-					else
-					{
-						const bool hit = hitPrim != 0xffffffffu;
-						const uint32_t bary = (uint32_t)(65535.0f * hitU) + ((uint32_t)(65535.0f * hitV) << 16);
-						a.hits[rayIdx] = make_float4( __uint_as_float( hit ? bary : 0u ), __uint_as_float( hit ? hitInst : 0u ),
-							__uint_as_float( hitPrim ), hit ? r.t : 1e34f );
-					}
-					if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
-					active = false;
-					break;
-				}
-				// too few lanes left in this warp and rays remain: go back and refill the idle lanes
-				if (!exhausted && __popc( __activemask() ) < 20) break;
 			}
+			// E. flush a partially filled ring when lanes wait on it and little node work is left in the warp
+			const uint32_t waitMask = __ballot_sync( 0xffffffffu, waiting );
+			const uint32_t workMask = __ballot_sync( 0xffffffffu, active && (ngroup.y > 0x00ffffffu || (instBase < 0 && tgroup.y)) );
+			if (waitMask && qtail != qhead && __popc( workMask ) < PARTIAL_BELOW) flush( qtail - qhead );
+			// F. too few lanes left in this warp and rays remain: go back and refill the idle lanes
+			const uint32_t activeMask = __ballot_sync( 0xffffffffu, active );
+			if (!activeMask || (!exhausted && __popc( activeMask ) < REFILL_BELOW)) break;
 		}
-		__syncwarp();
 	}
 }
 
