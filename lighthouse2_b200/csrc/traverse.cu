@@ -246,7 +246,8 @@ constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
 #ifndef B200_MIN_BLOCKS
 #define B200_MIN_BLOCKS 6
 #endif
-constexpr int QUEUE_CAP = 128;                       // ring entries per warp (a flush starts as soon as 32 are pending)
+constexpr int ENQUEUE_MAX = 6;                         // pairs a lane may queue per pass
+constexpr int QUEUE_CAP = 256;                        // ring entries per warp (a flush starts as soon as 32 are pending)
 constexpr int REFILL_BELOW = B200_REFILL_BELOW;      // leave the traversal loop to fetch rays when fewer lanes are active
 constexpr int PARTIAL_BELOW = B200_PARTIAL_BELOW;    // flush a partially filled ring for waiting lanes when fewer lanes have node work
 
@@ -362,8 +363,8 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		// ---- traversal: every pass = one node step per lane, then queue / flush triangle pairs ------------
 		while (true)
 		{
-			// A. node step
-			if (active && ngroup.y > 0x00ffffffu)
+			// A. node step (not while leaf triangles of the previous step are still waiting to be queued)
+			if (active && ngroup.y > 0x00ffffffu && tgroup.y == 0)
 			{
 				const uint32_t hits = ngroup.y, imask = hits & 0xffu;
 				const uint32_t bit = 31 - __clz( hits );
@@ -396,52 +397,42 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				ngroup = make_uint2( __float_as_uint( info.x ), 0x80000000u );
 				tgroup = make_uint2( 0, 0 );
 			}
-			// C. bottom level: queue (owner, triangle) pairs.  Up to three per lane go in with one ballot-prefix step
-			//    (leaves hold <= 3 triangles); lanes that hit more leaves finish in one-pair-per-lane rounds.
+			// C. bottom level: queue (owner, triangle) pairs -- at most ENQUEUE_MAX per lane per pass (a lane that hit
+			//    more leaf triangles keeps the rest in tgroup and skips its next node step); positions come from a
+			//    warp scan of the per-lane counts.
 			{
-				uint32_t tb = (active && instBase >= 0) ? tgroup.y : 0u;
-				const uint32_t cnt = __popc( tb );
-				const uint32_t b1 = __ballot_sync( 0xffffffffu, cnt >= 1 );
-				if (b1)
+				const bool inBlas = active && instBase >= 0;
+				const uint32_t tb = inBlas ? tgroup.y : 0u;
+				const uint32_t cnt = min( (uint32_t)__popc( tb ), (uint32_t)ENQUEUE_MAX );
+				if (__ballot_sync( 0xffffffffu, cnt != 0 ))
 				{
-					const uint32_t b2 = __ballot_sync( 0xffffffffu, cnt >= 2 ), b3 = __ballot_sync( 0xffffffffu, cnt >= 3 );
-					uint32_t more = __ballot_sync( 0xffffffffu, cnt >= 4 );
-					const uint32_t lt = lanemask_lt();
-					const uint32_t base = qtail + __popc( b1 & lt ) + __popc( b2 & lt ) + __popc( b3 & lt );
+					uint32_t incl = cnt;
 #pragma unroll
-					for (uint32_t k = 0; k < 3; k++)
-						if (cnt > k)
-						{
-							const uint32_t bit = 31 - __clz( tb );
-							tb &= ~(1u << bit);
-							queue[(base + k) & (QUEUE_CAP - 1)] = (tgroup.x + bit) | (lane << 27);
-							lastQueued = base + k;
-						}
+					for (int d = 1; d < 32; d <<= 1)
+					{
+						const uint32_t up = __shfl_up_sync( 0xffffffffu, incl, d );
+						if (lane >= d) incl += up;
+					}
+					const uint32_t totalNew = __shfl_sync( 0xffffffffu, incl, 31 );
+					uint32_t pos = qtail + incl - cnt, rest = tb;
+					const uint32_t entry0 = tgroup.x | (lane << 27);
+					for (uint32_t k = 0; k < cnt; k++)
+					{
+						const uint32_t bit = 31 - __clz( rest );
+						rest &= ~(1u << bit);
+						queue[pos & (QUEUE_CAP - 1)] = entry0 + bit;
+						pos++;
+					}
+					if (cnt) lastQueued = pos - 1, tgroup.y = rest;
 					if (COUNT) nTris += cnt;
-					qtail += __popc( b1 ) + __popc( b2 ) + __popc( b3 );
+					qtail += totalNew;
 					__syncwarp();
 					while (qtail - qhead >= 32) flush( 32 );
-					while (more)
-					{
-						const bool has = tb != 0;
-						if (has)
-						{
-							const uint32_t bit = 31 - __clz( tb );
-							tb &= ~(1u << bit);
-							lastQueued = qtail + __popc( more & lt );
-							queue[lastQueued & (QUEUE_CAP - 1)] = (tgroup.x + bit) | (lane << 27);
-						}
-						qtail += __popc( more );
-						__syncwarp();
-						if (qtail - qhead >= 32) flush( 32 );
-						more = __ballot_sync( 0xffffffffu, tb != 0 );
-					}
-					if (active && instBase >= 0) tgroup.y = 0;
 				}
 			}
 			// D. lanes without node work: leave the instance / pop / retire (only once their queued pairs are tested)
 			bool waiting = false;
-			if (active && ngroup.y <= 0x00ffffffu)
+			if (active && ngroup.y <= 0x00ffffffu && tgroup.y == 0)
 			{
 				const bool pending = (int32_t)(lastQueued - qhead) >= 0;
 				if (terminated || sp == instBase)
@@ -482,9 +473,11 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				}
 			}
 			// E. flush a partially filled ring when lanes wait on it and little node work is left in the warp
-			const uint32_t waitMask = __ballot_sync( 0xffffffffu, waiting );
-			const uint32_t workMask = __ballot_sync( 0xffffffffu, active && (ngroup.y > 0x00ffffffu || (instBase < 0 && tgroup.y)) );
-			if (waitMask && qtail != qhead && __popc( workMask ) < PARTIAL_BELOW) flush( qtail - qhead );
+			if (__ballot_sync( 0xffffffffu, waiting ) && qtail != qhead)
+			{
+				const uint32_t workMask = __ballot_sync( 0xffffffffu, active && (ngroup.y > 0x00ffffffu || tgroup.y) );
+				if (__popc( workMask ) < PARTIAL_BELOW) flush( qtail - qhead );
+			}
 			// F. too few lanes left in this warp and rays remain: go back and refill the idle lanes
 			const uint32_t activeMask = __ballot_sync( 0xffffffffu, active );
 			if (!activeMask || (!exhausted && __popc( activeMask ) < REFILL_BELOW)) break;
