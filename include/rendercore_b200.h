@@ -59,7 +59,8 @@ B200_API int b200_refit( b200_core* c, int meshIdx, const float* vertexData, int
 /* same, positions already resident in device memory (device float4[3T]) */
 B200_API int b200_refit_device( b200_core* c, int meshIdx, const void* dVertexData, int vertexCount );
 
-/* ---- CoreAPI_Base::Setting (core_api_base.h:92; keys rendersystem.cpp:231-236 + isectMode, refit, maxPathLength, spp, tileShard*) ---- */
+/* ---- CoreAPI_Base::Setting (core_api_base.h:92; keys rendersystem.cpp:231-236 + isectMode, refit, countSteps, buildThreads,
+ * maxPathLength, shardIndex, shardCount, sampleOffset, jitter, pathsPerPass) ---- */
 B200_API int b200_setting( b200_core* c, const char* name, float value );
 
 /* ---- raw wavefront queries: the extend / shadow waves ---- */
@@ -70,6 +71,9 @@ B200_API int b200_trace_any( b200_core* c, const float* O4, const float* D4, int
  * occludedBits must hold (n+31)/32 words; it is cleared by the call. */
 B200_API int b200_trace_closest_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dHits );
 B200_API int b200_trace_any_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dOccludedBits );
+/* shadow wave fused with the connect step (.optix.cu:137-149, connections.h:23-34): every ray that is NOT occluded adds
+ * E4[i].xyz to dAccumulator[pixel], pixel = integer bits of E4[i].w (atomicAdd; device buffers, asynchronous) */
+B200_API int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator );
 /* per-ray traversal counters of the LAST b200_trace_closest call with Setting("countSteps",1):
  * nodes visited and triangles tested (the analogue of the reference's `int* c`, bvh.cpp:259) */
 B200_API int b200_read_step_counters( b200_core* c, int n, uint32_t* nodesVisited, uint32_t* trisTested );
@@ -78,6 +82,14 @@ B200_API int b200_read_step_counters( b200_core* c, int n, uint32_t* nodesVisite
 B200_API int b200_set_target( b200_core* c, int width, int height, int spp );
 B200_API int b200_set_point_light( b200_core* c, const float* position3, const float* radiance3 );
 B200_API int b200_set_sky( b200_core* c, const float* radiance3 );
+/* CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each; the diffuse stage keeps color.value */
+B200_API int b200_set_materials( b200_core* c, const void* coreMaterials, int count );
+/* headless shortcut for hosts without CoreMaterial structs: one float4 albedo per material index (CoreTri::material) */
+B200_API int b200_set_material_colors( b200_core* c, const float* rgba, int count );
+/* multi-GPU: render into a caller-owned device accumulator float4[w*h] (e.g. a torch tensor that NCCL reduces);
+ * NULL = the core's own.  After the gather, b200_finalize( total samples ) rebuilds the frame from it. */
+B200_API int b200_set_accumulator_buffer( b200_core* c, void* dAccumulator );
+B200_API int b200_finalize( b200_core* c, uint32_t totalSamples );
 /* view: ViewPyramid (68 bytes, common_classes.h:362-385).  converge: 0 = Converge, 1 = Restart */
 B200_API int b200_render( b200_core* c, const void* viewPyramid, int converge );
 /* accumulator float4[w*h] (sum over samples; w = sample count) and the normalised RGBA32F frame */

@@ -24,7 +24,8 @@ C_ABI_SYMBOLS = [
     "b200_trace_closest_device", "b200_trace_any_device", "b200_read_step_counters", "b200_set_target",
     "b200_set_point_light", "b200_set_sky", "b200_render", "b200_read_accumulator", "b200_read_frame",
     "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
-    "b200_host_free", "CreateCore", "DestroyCore",
+    "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors",
+    "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
 ]
 
 
@@ -85,6 +86,9 @@ def load_library() -> C.CDLL:
         "b200_render": ([vp, vp, ip], ip), "b200_read_accumulator": ([vp, vp], ip), "b200_read_frame": ([vp, vp], ip),
         "b200_device_accumulator": ([vp], vp), "b200_get_stats": ([vp, C.POINTER(Stats)], ip), "b200_set_probe": ([vp, ip, ip], ip),
         "b200_plugin_core": ([], vp), "b200_host_alloc": ([C.c_uint64], vp), "b200_host_free": ([vp], None),
+        "b200_set_materials": ([vp, vp, ip], ip), "b200_set_material_colors": ([vp, vp, ip], ip),
+        "b200_set_accumulator_buffer": ([vp, vp], ip), "b200_finalize": ([vp, C.c_uint32], ip),
+        "b200_trace_connect_device": ([vp, vp, vp, ip, vp, vp], ip),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, name)
@@ -226,6 +230,19 @@ class RenderCoreB200:
     def SetSky(self, radiance):
         r = np.asarray(radiance, np.float32)
         self._chk(self.lib.b200_set_sky(self.h, r.ctypes.data))
+
+    def SetMaterialColors(self, rgba):
+        c = np.ascontiguousarray(rgba, np.float32).reshape(-1, 4)
+        self._chk(self.lib.b200_set_material_colors(self.h, c.ctypes.data, c.shape[0]))
+
+    def SetAccumulatorBuffer(self, dptr: int):
+        self._chk(self.lib.b200_set_accumulator_buffer(self.h, dptr))
+
+    def Finalize(self, total_samples: int):
+        self._chk(self.lib.b200_finalize(self.h, total_samples))
+
+    def TraceConnectDevice(self, dO4: int, dD4: int, n: int, dE4: int, dAcc: int):
+        self._chk(self.lib.b200_trace_connect_device(self.h, dO4, dD4, n, dE4, dAcc))
 
     def Render(self, view: dict, converge: int = 1):
         vp = ViewPyramid()

@@ -51,6 +51,11 @@ int b200_read_step_counters( b200_core* c, int n, uint32_t* nodes, uint32_t* tri
 int b200_set_target( b200_core* c, int w, int h, int spp ) { FORWARD( c, SetTarget( w, h, spp ) ) }
 int b200_set_point_light( b200_core* c, const float* p, const float* r ) { FORWARD( c, SetPointLight( p, r ) ) }
 int b200_set_sky( b200_core* c, const float* r ) { FORWARD( c, SetSky( r ) ) }
+int b200_set_materials( b200_core* c, const void* coreMaterials, int count ) { FORWARD( c, SetMaterials( coreMaterials, count ) ) }
+int b200_set_material_colors( b200_core* c, const float* rgba, int count ) { FORWARD( c, SetMaterialColors( rgba, count ) ) }
+int b200_set_accumulator_buffer( b200_core* c, void* dAcc ) { FORWARD( c, SetAccumulatorBuffer( dAcc ) ) }
+int b200_finalize( b200_core* c, uint32_t totalSamples ) { FORWARD( c, Finalize( totalSamples ) ) }
+int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, int n, const void* dE4, void* dAcc ) { FORWARD( c, TraceConnectDevice( dO4, dD4, n, dE4, dAcc ) ) }
 int b200_render( b200_core* c, const void* view, int converge ) { FORWARD( c, Render( view, converge ) ) }
 int b200_read_accumulator( b200_core* c, float* dst ) { FORWARD( c, ReadAccumulator( dst ) ) }
 int b200_read_frame( b200_core* c, float* dst ) { FORWARD( c, ReadFrame( dst ) ) }

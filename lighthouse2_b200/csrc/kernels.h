@@ -13,7 +13,9 @@ struct TraceArgs {
 	const float4* rayO;        // (Ox,Oy,Oz,tmin)
 	const float4* rayD;        // (Dx,Dy,Dz,tmax)
 	float4* hits;              // closest-hit output, 16 B/ray           (extend)
-	uint32_t* occluded;        // 1 bit/ray, pre-cleared, bit set = hit  (shadow)
+	uint32_t* occluded;        // 1 bit/ray, pre-cleared, bit set = hit  (shadow); may be null when `accumulator` is set
+	const float4* potentials;  // optional fused connect (shadow): E4 = (rgb, pixelIdx bits) per shadow ray ...
+	float4* accumulator;       // ... added to accumulator[pixelIdx] when the ray is NOT occluded (.optix.cu:137-149, connections.h:23-34)
 	uint32_t* fetchCounter;    // persistent-thread ray fetch counter (zeroed by the launcher)
 	const uint32_t* countPtr;  // optional device-resident ray count (wavefront counters); overrides `count`
 	uint32_t count;
@@ -35,6 +37,7 @@ struct RefitArgs {
 	float4* tris;              // pool
 	const float4* verts;       // new positions, float4[3T], ORIGINAL primitive order
 	float4* nodeLo; float4* nodeHi; // scratch: float AABB per node of this mesh
+	float4* shade;             // pool: (geometric normal, material bits) per ORIGINAL primitive of every mesh; normals are refreshed
 	uint32_t nodeBase;         // absolute index of the mesh root in the pool
 	uint32_t triBase, triCount;
 };

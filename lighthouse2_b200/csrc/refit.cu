@@ -27,6 +27,15 @@ __global__ void refitTrianglesKernel( const RefitArgs a )
 	tp[0] = make_float4( p0.x, p0.y, p0.z, __uint_as_float( prim ) );
 	tp[1] = make_float4( p1.x - p0.x, p1.y - p0.y, p1.z - p0.z, 0.f );
 	tp[2] = make_float4( p2.x - p0.x, p2.y - p0.y, p2.z - p0.z, 0.f );
+	if (a.shade)
+	{
+		// geometric normal of the moved triangle (object space), material bits kept
+		const float e1x = p1.x - p0.x, e1y = p1.y - p0.y, e1z = p1.z - p0.z, e2x = p2.x - p0.x, e2y = p2.y - p0.y, e2z = p2.z - p0.z;
+		float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
+		const float l2 = nx * nx + ny * ny + nz * nz, il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
+		float4* sp = a.shade + a.triBase + prim;
+		*sp = make_float4( nx * il, ny * il, nz * il, sp->w );
+	}
 }
 
 __device__ __forceinline__ uint32_t frameExponent( float lo, float hi )

@@ -116,7 +116,7 @@ RenderCore::~RenderCore()
 	cudaSetDevice( device );
 	cudaDeviceSynchronize();
 	DestroyWavefront( wf );
-	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &materialPool, &rayO, &rayD, &hitBuf, &bitBuf, &vertStage, &nodeLo, &nodeHi,
+	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &instShadePool, &rayO, &rayD, &hitBuf, &bitBuf, &vertStage, &nodeLo, &nodeHi,
 		&stepNodes, &stepTris };
 	for (DeviceBuffer* b : all) b->release();
 	if (evA) cudaEventDestroy( evA );
@@ -183,8 +183,8 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	m.nodeBase = blasNodeEnd, m.nodeCount = (uint32_t)bvh.nodes.size(), m.triBase = triEnd, m.triCount = T;
 	m.levelStart = bvh.levelStart, m.bounds = bvh.bounds, m.built = true;
 	for (WideNode& n : bvh.nodes) n.childBase += m.nodeBase, n.primBase += m.triBase; // absolute pool indices
+	if ((uint64_t)m.triBase + T + 32 >= (1ull << 27)) return fail( "SetGeometry: more than 2^27 triangles in one core (queue entries carry 27-bit triangle indices)" );
 	std::vector<WideTri> tris( T );
-	std::vector<uint32_t> material( T, 0 );
 	for (uint32_t j = 0; j < T; j++)
 	{
 		const uint32_t prim = bvh.primOrder[j];
@@ -192,15 +192,35 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 		WideTri& t = tris[j];
 		t.prim = prim, t.pad1 = t.pad2 = 0;
 		for (int a = 0; a < 3; a++) t.v0[a] = p0[a], t.e1[a] = p1[a] - p0[a], t.e2[a] = p2[a] - p0[a];
-		if (coreTris) memcpy( &material[j], (const char*)coreTris + (size_t)prim * 176 + 28, 4 ); // CoreTri::material, common_classes.h:67
+	}
+	// shading record per ORIGINAL primitive: geometric normal (CoreTri::Nx,Ny,Nz when supplied, common_classes.h:69-71,
+	// else from the vertices) + CoreTri::material (:67); what the shade stage reads via instanceTriangles[PRIMIDX]
+	// in the reference (lib/rendercore_optix7/kernels/pathtracer.h:70-100)
+	struct ShadeRec { float n[3]; uint32_t material; };
+	std::vector<ShadeRec> shade( T );
+	for (uint32_t i = 0; i < T; i++)
+	{
+		const float *p0 = vertexData + (size_t)i * 12, *p1 = p0 + 4, *p2 = p0 + 8;
+		const float e1[3] = { p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2] }, e2[3] = { p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2] };
+		float n[3] = { e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0] };
+		const float l2 = n[0] * n[0] + n[1] * n[1] + n[2] * n[2], il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
+		shade[i].n[0] = n[0] * il, shade[i].n[1] = n[1] * il, shade[i].n[2] = n[2] * il, shade[i].material = 0;
+		if (coreTris)
+		{
+			const char* ct = (const char*)coreTris + (size_t)i * 176;
+			float N[3];
+			memcpy( &N[0], ct + 44, 4 ), memcpy( &N[1], ct + 60, 4 ), memcpy( &N[2], ct + 76, 4 );
+			if (N[0] * N[0] + N[1] * N[1] + N[2] * N[2] > 0.5f) shade[i].n[0] = N[0], shade[i].n[1] = N[1], shade[i].n[2] = N[2];
+			memcpy( &shade[i].material, ct + 28, 4 );
+		}
 	}
 	cudaError_t e;
 	if ((e = nodePool.reserve( (size_t)(m.nodeBase + m.nodeCount + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
 	if ((e = triPool.reserve( (size_t)(m.triBase + T + 1) * 48, true, stream )) != cudaSuccess) return fail( "triangle pool", e );
-	if ((e = materialPool.reserve( (size_t)(m.triBase + T + 1) * 4, true, stream )) != cudaSuccess) return fail( "material pool", e );
+	if ((e = shadePool.reserve( (size_t)(m.triBase + T + 1) * 16, true, stream )) != cudaSuccess) return fail( "shading pool", e );
 	if ((e = cudaMemcpyAsync( (char*)nodePool.ptr + (size_t)m.nodeBase * 80, bvh.nodes.data(), (size_t)m.nodeCount * 80, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "node upload", e );
 	if (T && (e = cudaMemcpyAsync( (char*)triPool.ptr + (size_t)m.triBase * 48, tris.data(), (size_t)T * 48, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "triangle upload", e );
-	if (T && (e = cudaMemcpyAsync( (char*)materialPool.ptr + (size_t)m.triBase * 4, material.data(), (size_t)T * 4, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "material upload", e );
+	if (T && (e = cudaMemcpyAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, shade.data(), (size_t)T * 16, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "shading upload", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "SetGeometry sync", e ); // the staging vectors die here
 	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
 	meshes.push_back( m );
@@ -237,7 +257,7 @@ int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, b
 	if ((e = nodeHi.reserve( (size_t)m.nodeCount * 16, false, stream )) != cudaSuccess) return fail( "refit scratch", e );
 	RefitArgs a;
 	a.nodes = (uint4*)nodePool.ptr, a.tris = (float4*)triPool.ptr, a.verts = (const float4*)dVerts;
-	a.nodeLo = (float4*)nodeLo.ptr, a.nodeHi = (float4*)nodeHi.ptr;
+	a.nodeLo = (float4*)nodeLo.ptr, a.nodeHi = (float4*)nodeHi.ptr, a.shade = (float4*)shadePool.ptr;
 	a.nodeBase = m.nodeBase, a.triBase = m.triBase, a.triCount = m.triCount;
 	cudaEventRecord( evA, stream );
 	if ((e = LaunchRefitTriangles( a, stream )) != cudaSuccess) return fail( "refit triangles", e );
@@ -329,6 +349,15 @@ int RenderCore::UpdateToplevel()
 		const float* v = r.inv;
 		r.flags = (v[12] == 0 && v[13] == 0 && v[14] == 0 && v[15] == 1) ? 1u : 0u;
 	}
+	// shading-time instance table by INSTANCE ID (the reference's CoreInstanceDesc array, rendercore_optix7/rendercore.cpp:639-674):
+	// forward transform rows (normals to world space, pathtracer.h via GetShadingData) + the mesh's first triangle in the pools
+	struct InstShade { float row[3][4]; uint32_t triBase, meshId, pad0, pad1; };
+	std::vector<InstShade> ish( N );
+	for (uint32_t i = 0; i < N; i++)
+	{
+		memcpy( ish[i].row, instances[i].transform, 48 );
+		ish[i].triBase = meshes[instances[i].mesh].triBase, ish[i].meshId = (uint32_t)instances[i].mesh, ish[i].pad0 = ish[i].pad1 = 0;
+	}
 	tlasRoot = blasNodeEnd, tlasNodeCount = (uint32_t)tlas.nodes.size();
 	for (WideNode& n : tlas.nodes) n.childBase += tlasRoot; // primBase indexes the instance records directly
 	cudaError_t e;
@@ -336,6 +365,8 @@ int RenderCore::UpdateToplevel()
 	if ((e = instPool.reserve( (size_t)(N + 1) * 96, false, stream )) != cudaSuccess) return fail( "instance pool", e );
 	if ((e = cudaMemcpyAsync( (char*)nodePool.ptr + (size_t)tlasRoot * 80, tlas.nodes.data(), (size_t)tlasNodeCount * 80, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "tlas upload", e );
 	if (N && (e = cudaMemcpyAsync( instPool.ptr, recs.data(), (size_t)N * 96, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "instance upload", e );
+	if ((e = instShadePool.reserve( (size_t)(N + 1) * 64, false, stream )) != cudaSuccess) return fail( "instance shading pool", e );
+	if (N && (e = cudaMemcpyAsync( instShadePool.ptr, ish.data(), (size_t)N * 64, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "instance shading upload", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "UpdateToplevel sync", e );
 	tlasDirty = false;
 	stats.tlasTime = (float)(nowMs() - t0);
@@ -390,6 +421,25 @@ int RenderCore::TraceAnyDevice( const void* dO4, const void* dD4, int n, void* d
 	if ((e = cudaMemsetAsync( dBits, 0, (size_t)((n + 31) / 32) * 4, stream )) != cudaSuccess) return fail( "clear bitmask", e );
 	cudaEventRecord( evA, stream );
 	if ((e = LaunchShadow( a, isect, smCount, stream )) != cudaSuccess) return fail( "shadow kernel launch", e );
+	cudaEventRecord( evB, stream );
+	stats.kernelLaunches++;
+	return 0;
+}
+
+// shadow wave fused with the connect step: unoccluded rays add E4.xyz to accumulator[pixelIdx = bits of E4.w]
+// (rendercore_optix7/optix/.optix.cu:137-149; RenderCore_OptixPrime_B/kernels/connections.h:23-34)
+int RenderCore::TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount )
+{
+	if (n < 0) return fail( "trace: negative ray count" );
+	if (!dE4 || !dAccumulator) return fail( "connect: null potentials / accumulator" );
+	if (ensureToplevel()) return 1;
+	if (n == 0) return 0;
+	TraceArgs a = baseArgs();
+	a.rayO = (const float4*)dO4, a.rayD = (const float4*)dD4, a.potentials = (const float4*)dE4, a.accumulator = (float4*)dAccumulator;
+	a.count = (uint32_t)n, a.countPtr = dCount;
+	cudaError_t e;
+	cudaEventRecord( evA, stream );
+	if ((e = LaunchShadow( a, isect, smCount, stream )) != cudaSuccess) return fail( "connect kernel launch", e );
 	cudaEventRecord( evB, stream );
 	stats.kernelLaunches++;
 	return 0;

@@ -44,6 +44,9 @@ public:
 	int SetPointLight( const float* pos, const float* radiance );
 	int SetSky( const float* radiance );
 	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value
+	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: float4 albedo per material
+	int SetAccumulatorBuffer( void* devicePtr );              // caller-owned float4[w*h] accumulator (multi-GPU gathers), null = own
+	int Finalize( uint32_t totalSamples );                    // frame = accumulator / totalSamples (after a gather)
 	int Render( const void* viewPyramid, int converge );
 	int ReadAccumulator( float* dst );
 	int ReadFrame( float* dst );
@@ -55,6 +58,7 @@ public:
 	int TraceAny( const float* O4, const float* D4, int n, uint32_t* bits );
 	int TraceClosestDevice( const void* dO4, const void* dD4, int n, void* dHits, const uint32_t* dCount = nullptr );
 	int TraceAnyDevice( const void* dO4, const void* dD4, int n, void* dBits, const uint32_t* dCount = nullptr );
+	int TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount = nullptr );
 	int ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris );
 	int Refit( int meshIdx, const float* vertexData, int vertexCount );
 	int RefitDevice( int meshIdx, const void* dVerts, int vertexCount, bool boundsKnown );
@@ -80,7 +84,7 @@ private:
 	std::string error;
 	int device = 0;
 	// acceleration structure pools
-	DeviceBuffer nodePool, triPool, instPool, materialPool;
+	DeviceBuffer nodePool, triPool, instPool, shadePool, instShadePool;
 	uint32_t blasNodeEnd = 0, triEnd = 0, tlasRoot = 0, tlasNodeCount = 0;
 	std::vector<MeshRec> meshes;
 	std::vector<InstanceHost> instances;

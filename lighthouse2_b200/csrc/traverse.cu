@@ -454,7 +454,17 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					{
 						if (ANYHIT)
 						{
-							if (hitPrim != 0xffffffffu) atomicOr( a.occluded + (rayIdx >> 5), 1u << (rayIdx & 31) );
+							if (a.accumulator)
+							{
+								// fused connect: an unoccluded shadow ray delivers its potential contribution
+								if (hitPrim == 0xffffffffu)
+								{
+									const float4 E = __ldg( a.potentials + rayIdx );
+									float* px = reinterpret_cast<float*>( a.accumulator + __float_as_uint( E.w ) );
+									atomicAdd( px, E.x ), atomicAdd( px + 1, E.y ), atomicAdd( px + 2, E.z );
+								}
+							}
+							else if (hitPrim != 0xffffffffu) atomicOr( a.occluded + (rayIdx >> 5), 1u << (rayIdx & 31) );
 						}
 						else
 						{
