@@ -390,8 +390,13 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	for (uint32_t s0 = 0; s0 < (uint32_t)w->spp; s0 += samplesPerPass)
 	{
 		f.samplesThisPass = (uint32_t)w->spp - s0 < samplesPerPass ? (uint32_t)w->spp - s0 : samplesPerPass;
-		f.sampleBase = (uint32_t)w->sampleOffset + w->samplesTaken + s0;
-		f.R0 = (f.sampleBase + 1) * 7907u; // "samplesTaken * 7907 + pathLength * 91771" (RenderCore_PrimeRef/rendercore.cpp shade call)
+		// pathIdx = pixel + sample * pixelCount must stay below 2^32: the sample index wraps after `period` samples and the wrap
+		// count goes into the salt instead ("samplesTaken * 7907 + pathLength * 91771" in the reference's shade call)
+		const uint32_t globalSample = (uint32_t)w->sampleOffset + w->samplesTaken + s0;
+		uint32_t period = 0xffffffffu / f.pixelCount - (uint32_t)w->spp;
+		if (period < 1 || period > 0x7fffffffu) period = 1;
+		f.sampleBase = globalSample % period;
+		f.R0 = (globalSample / period + 1) * 7907u;
 		if ((e = cudaMemsetAsync( dCounters, 0, sizeof( WaveCounters ) * (MAX_PATH_LENGTH + 2), stream )) != cudaSuccess) return fail( "counter clear", e );
 		const uint32_t paths = perSample * f.samplesThisPass;
 		if (!paths) continue;

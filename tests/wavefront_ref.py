@@ -62,7 +62,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, sky=(0, 0
     sky = np.asarray(sky, f32)
     for s in range(spp):
         sample = sample_offset + s
-        R0 = np.uint32(((sample + 1) * 7907) & 0xFFFFFFFF)
+        R0 = np.uint32(7907)
         pix = np.arange(npx, dtype=np.uint32)
         path_idx = (pix + np.uint32(sample) * np.uint32(npx)).astype(np.uint32)
         x, y = (pix % width).astype(f32), (pix // width).astype(f32)
