@@ -40,7 +40,7 @@ SHADOW_BYTES_PER_RAY = 32.125    # 32 B ray in + 1 bit out
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tris", type=int, default=1_000_000)
@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=65536, help="pixels in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-frame", action="store_true")
     ap.add_argument("--check", action="store_true", help="compare a sample of the GPU hits with the CPU checker")
     return ap.parse_args()
 
@@ -81,7 +82,7 @@ class ClockSampler:
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
                                       stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
@@ -311,6 +312,43 @@ def run_b200(args):
         barrier()
         e2e_ms = ea.elapsed_time(eb) / e2e_steps
 
+    # ---- the same scene through Render(): full wavefront frame (ray generation, shade, fused connect), tile-sharded over the
+    #      ranks, accumulator gathered with one NCCL all-reduce.  Reported beside the wave numbers, not as `value`.
+    frame = None
+    if not args.no_frame:
+        from lighthouse2_b200 import multigpu
+        sr = multigpu.ShardedRenderer(rank, world, local, mode="tiles", existing_core=rc)
+        sr.SetTarget(args.width, args.height, 1)
+        rc.SetPointLight(scenes.C2_LIGHT, (4000.0, 4000.0, 3600.0))
+        rc.SetSky((0.4, 0.5, 0.7))
+        rc.Setting("maxPathLength", args.bounces + 1)
+        view = scenes.view_pyramid(width=args.width, height=args.height, **scenes.C2_CAMERA)
+        for _ in range(2):
+            sr.Render(view, 1)
+        fsteps = max(3, min(args.steps, 10))
+        barrier()
+        t0 = time.perf_counter()
+        r_ms = g_ms = 0.0
+        rays_f = 0
+        for _ in range(fsteps):
+            a_, b_ = sr.Render(view, 1)
+            r_ms += a_; g_ms += b_
+            rays_f += rc.GetCoreStats()["totalRays"]
+        barrier()
+        wall_ms = (time.perf_counter() - t0) * 1e3 / fsteps
+        st = rc.GetCoreStats()
+        fv = torch.tensor([wall_ms, r_ms / fsteps, g_ms / fsteps], device=dev, dtype=torch.float64)
+        fr = torch.tensor([rays_f / fsteps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(fv, op=dist.ReduceOp.MAX)
+            dist.all_reduce(fr, op=dist.ReduceOp.SUM)
+        fv = fv.tolist()
+        frame = {"ms_per_frame_wall": fv[0], "render_ms": fv[1], "gather_ms": fv[2], "rays_per_frame": fr.item(),
+                 "mrays_s": fr.item() / (fv[0] * 1e-3) / 1e6, "gather_bytes": args.width * args.height * 16,
+                 "rank0_stats": {k: st[k] for k in ("primaryRayCount", "traceTime0", "bounce1RayCount", "traceTime1", "deepRayCount", "traceTimeX",
+                                                    "totalShadowRays", "shadowTraceTime", "shadeTime", "renderTime")},
+                 "note": "Render() + NCCL all-reduce of the float4 accumulator, 1 spp, tile-sharded; wall clock incl. host sync per frame"}
+
     # ---- reduce over ranks: slowest rank's time, all ranks' rays ------------------------------------------------
     vec = torch.tensor([total_ms, e2e_ms or 0.0, ext_ms] + [cls_ms.get(c, 0.0) for c in ("primary", "shadow", "diffuse")], device=dev, dtype=torch.float64)
     cnt = torch.tensor([total_rays, ext_rays] + [cls_rays.get(c, 0) for c in ("primary", "shadow", "diffuse")], device=dev, dtype=torch.float64)
@@ -361,6 +399,8 @@ def run_b200(args):
             r = cpu_pass(args, verts, args.cpu_sample, steps=2, warmup=1)
             line["cpu_baseline"] = {"value": r["value"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
                                     "per_class": r["per_class"], "bvh_build_s": r["bvh_build_s"]}
+        if frame:
+            line["frame"] = frame
         if args.check:
             line["check"] = check_against_cpu(rc, core, verts, waves)
         print(json.dumps(line), flush=True)

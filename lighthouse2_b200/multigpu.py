@@ -1,0 +1,96 @@
+"""One process per GPU: tile- or sample-sharded frames with the accumulator gathered over NCCL.
+
+The reference has no multi-GPU path (single device picked by CUDATools::FastestDevice, lib/CUDA/shared_host_code/
+cudatools.h:62-87).  Here the scene is replicated, every rank renders its interleaved 32x8 tiles (or its own samples)
+into a torch-owned float4[w*h] accumulator that the core writes directly (b200_set_accumulator_buffer), and ONE
+collective per frame -- ``all_reduce(SUM)`` over NCCL/NVLink; disjoint pixels, so the sum is the union, bit-identical to
+a single-GPU frame -- makes the full accumulator resident on every rank.  torch / torch.distributed are plumbing only
+(device memory, streams, the collective); all kernels are the core's own.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+TILE_W, TILE_H = 32, 8  # must match wavefront.cu
+
+
+def tile_grid(width: int, height: int):
+    return (width + TILE_W - 1) // TILE_W, (height + TILE_H - 1) // TILE_H
+
+
+def tile_owner_map(width: int, height: int, shard_count: int) -> np.ndarray:
+    """int32[h, w]: which shard renders each pixel (tile t -> shard t % shard_count), as wavefront.cu assigns them."""
+    tx, ty = tile_grid(width, height)
+    tiles = np.arange(tx * ty, dtype=np.int64).reshape(ty, tx) % shard_count
+    return np.repeat(np.repeat(tiles, TILE_H, axis=0), TILE_W, axis=1)[:height, :width].astype(np.int32)
+
+
+def shard_pixel_counts(width: int, height: int, shard_count: int) -> np.ndarray:
+    return np.bincount(tile_owner_map(width, height, shard_count).ravel(), minlength=shard_count)
+
+
+class ShardedRenderer:
+    """CoreAPI-shaped wrapper for rank ``rank`` of ``world``: same calls as RenderCoreB200, Render() returns after the gather."""
+
+    def __init__(self, rank: int, world: int, local_device: int, mode: str = "tiles", existing_core=None):
+        import torch
+        from . import core
+        assert mode in ("tiles", "samples")
+        self.torch, self.rank, self.world, self.mode = torch, rank, world, mode
+        self.device = torch.device("cuda", local_device)
+        self.core = existing_core if existing_core is not None else core.RenderCoreB200(local_device)
+        self.core.SetStream(torch.cuda.current_stream(self.device).cuda_stream)
+        self.acc = None
+        self.spp = 1
+        self.samples_taken = 0
+
+    def __getattr__(self, name):  # SetGeometry, SetInstance, UpdateToplevel, SetPointLight, ... go straight to the core
+        return getattr(self.core, name)
+
+    def SetTarget(self, width: int, height: int, spp: int = 1):
+        torch = self.torch
+        self.width, self.height, self.spp = width, height, spp
+        self.acc = torch.zeros((height, width, 4), dtype=torch.float32, device=self.device)
+        self.core.SetAccumulatorBuffer(self.acc.data_ptr())
+        self.core.SetTarget(width, height, spp)
+        if self.mode == "tiles":
+            self.core.Setting("shardCount", self.world)
+            self.core.Setting("shardIndex", self.rank)
+        self.samples_taken = 0
+
+    def Render(self, view: dict, converge: int = 1):
+        """Render this rank's share, then all-reduce the accumulator.  Returns (render_ms, gather_ms) device times."""
+        import torch.distributed as dist
+        torch = self.torch
+        if converge == 1:
+            self.samples_taken = 0
+        if self.mode == "samples":
+            # this frame's samples are [taken, taken + world*spp); rank r renders [taken + r*spp, taken + (r+1)*spp)
+            self.core.Setting("sampleOffset", self.samples_taken + self.rank * self.spp)
+        elif self.samples_taken:
+            self.core.Setting("sampleOffset", self.samples_taken)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        stream = torch.cuda.current_stream(self.device)
+        e0.record(stream)
+        # each rank's accumulator holds only its own contribution of THIS frame; earlier frames are already global sums
+        prev = self.acc.clone() if (converge == 0 and self.samples_taken) else None
+        self.core.Render(view, 1)
+        e1.record(stream)
+        if self.world > 1:
+            dist.all_reduce(self.acc, op=dist.ReduceOp.SUM)
+        if prev is not None:
+            self.acc += prev
+        e2.record(stream)
+        self.samples_taken += self.spp * (self.world if self.mode == "samples" else 1)
+        self.core.Finalize(self.samples_taken)
+        torch.cuda.synchronize(self.device)
+        return e0.elapsed_time(e1), e1.elapsed_time(e2)
+
+    def ReadAccumulator(self) -> np.ndarray:
+        return self.acc.cpu().numpy()
+
+    def ReadFrame(self) -> np.ndarray:
+        return self.core.ReadFrame()
+
+    def Shutdown(self):
+        self.core.Shutdown()
