@@ -292,6 +292,7 @@ def run_b200(args):
 
     # ---- e2e: host buffers through the C ABI (H2D + wave + D2H + sync inside each call) ------------------------
     e2e_ms = None
+    pcie_h2d = 0.0
     if not args.no_e2e:
         lib, h = rc.lib, rc.h
 
@@ -311,6 +312,15 @@ def run_b200(args):
         eb.record(stream)
         barrier()
         e2e_ms = ea.elapsed_time(eb) / e2e_steps
+        # context for the e2e number: what a plain pinned-memory copy achieves on this box (the e2e floor is h2d_bytes / this)
+        big = max(waves, key=lambda w_: w_["n"])
+        torch.cuda.synchronize()
+        ea.record(stream)
+        for _ in range(5):
+            big["dO"].copy_(big["hO"], non_blocking=True)
+        eb.record(stream)
+        torch.cuda.synchronize()
+        pcie_h2d = 5 * big["n"] * 16 / (ea.elapsed_time(eb) * 1e-3) / 1e9
 
     # ---- the same scene through Render(): full wavefront frame (ray generation, shade, fused connect), tile-sharded over the
     #      ranks, accumulator gathered with one NCCL all-reduce.  Reported beside the wave numbers, not as `value`.
@@ -393,7 +403,8 @@ def run_b200(args):
             h2d = sum(w["n"] * 32 for w in waves)
             d2h = sum(w["n"] * 16 if w["kind"] == "closest" else ((w["n"] + 31) // 32) * 4 for w in waves)
             line["e2e"] = {"value": all_rays_step / (e2e_ms_max * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d,
-                           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms_max,
+                           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms_max, "pcie_h2d_gbs_measured": pcie_h2d,
+                           "pcie_floor_ms": h2d / (pcie_h2d * 1e9) * 1e3,
                            "api": "b200_trace_closest / b200_trace_any with pinned host buffers"}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_pass(args, verts, args.cpu_sample, steps=2, warmup=1)

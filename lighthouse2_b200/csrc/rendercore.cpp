@@ -121,6 +121,7 @@ RenderCore::~RenderCore()
 	for (DeviceBuffer* b : all) b->release();
 	if (evA) cudaEventDestroy( evA );
 	if (evB) cudaEventDestroy( evB );
+	if (copyIn) { cudaStreamDestroy( copyIn ), cudaStreamDestroy( copyOut ); for (cudaEvent_t ev : chunkEv) if (ev) cudaEventDestroy( ev ); }
 }
 
 int RenderCore::fail( const char* what, cudaError_t e )
@@ -445,40 +446,71 @@ int RenderCore::TraceConnectDevice( const void* dO4, const void* dD4, int n, con
 	return 0;
 }
 
-// host-buffer variants: H2D, wave, D2H, synchronise (the e2e path of bench.py)
-int RenderCore::TraceClosest( const float* O4, const float* D4, int n, float* hits )
+// The host-buffer waves are pipelined: the rays go up in chunks on a copy-in stream, each chunk's kernel waits only for its
+// own upload, and its results go down on a copy-out stream while the next chunk is traced (PCIe is full duplex, so upload,
+// kernel and download overlap; with pinned host memory the call costs about the upload alone).
+static int chunkRays( int n )
+{
+	int c = n / 6;
+	if (c < (1 << 18)) c = 1 << 18; // smaller chunks starve the persistent grid (148 SMs x 6 CTAs x 128 lanes)
+	return (c + 1023) & ~1023;
+}
+
+int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit )
 {
 	if (n < 0) return fail( "trace: negative ray count" );
 	if (n == 0) return ensureToplevel();
+	if (ensureToplevel()) return 1;
 	cudaError_t e;
-	const size_t rb = (size_t)n * 16;
+	const size_t rb = (size_t)n * 16, bb = (size_t)((n + 31) / 32) * 4;
+	DeviceBuffer& outBuf = anyHit ? bitBuf : hitBuf;
 	if ((e = rayO.reserve( rb, false, stream )) != cudaSuccess || (e = rayD.reserve( rb, false, stream )) != cudaSuccess ||
-		(e = hitBuf.reserve( rb, false, stream )) != cudaSuccess) return fail( "ray buffers", e );
-	if ((e = cudaMemcpyAsync( rayO.ptr, O4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
-	if ((e = cudaMemcpyAsync( rayD.ptr, D4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
-	if (TraceClosestDevice( rayO.ptr, rayD.ptr, n, hitBuf.ptr )) return 1;
-	if ((e = cudaMemcpyAsync( hits, hitBuf.ptr, rb, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "hit download", e );
-	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "extend wave", e );
-	cudaEventElapsedTime( &stats.lastTraceMs, evA, evB );
+		(e = outBuf.reserve( anyHit ? bb : rb, false, stream )) != cudaSuccess) return fail( "ray buffers", e );
+	const int chunk = countSteps ? n : chunkRays( n );
+	const int nChunks = (n + chunk - 1) / chunk;
+	if (nChunks > MAX_CHUNKS) return fail( "trace: too many chunks" );
+	if (!copyIn)
+	{
+		if ((e = cudaStreamCreateWithFlags( &copyIn, cudaStreamNonBlocking )) != cudaSuccess || (e = cudaStreamCreateWithFlags( &copyOut, cudaStreamNonBlocking )) != cudaSuccess)
+			return fail( "copy streams", e );
+		for (int i = 0; i < 2 * MAX_CHUNKS + 1; i++) if ((e = cudaEventCreateWithFlags( &chunkEv[i], cudaEventDisableTiming )) != cudaSuccess) return fail( "chunk events", e );
+	}
+	// the uploads may start once everything queued on the core's stream so far is done (the staging buffers may still be read)
+	cudaEventRecord( chunkEv[2 * MAX_CHUNKS], stream );
+	cudaStreamWaitEvent( copyIn, chunkEv[2 * MAX_CHUNKS], 0 );
+	for (int k = 0; k < nChunks; k++)
+	{
+		const int off = k * chunk, m = n - off < chunk ? n - off : chunk;
+		const size_t ob = (size_t)off * 16, mb = (size_t)m * 16;
+		if ((e = cudaMemcpyAsync( (char*)rayO.ptr + ob, (const char*)O4 + ob, mb, cudaMemcpyHostToDevice, copyIn )) != cudaSuccess) return fail( "ray upload", e );
+		if ((e = cudaMemcpyAsync( (char*)rayD.ptr + ob, (const char*)D4 + ob, mb, cudaMemcpyHostToDevice, copyIn )) != cudaSuccess) return fail( "ray upload", e );
+		cudaEventRecord( chunkEv[2 * k], copyIn );
+		cudaStreamWaitEvent( stream, chunkEv[2 * k], 0 );
+		if (anyHit)
+		{
+			char* dBits = (char*)bitBuf.ptr + (size_t)(off / 32) * 4; // chunk is a multiple of 1024 rays
+			if (TraceAnyDevice( (char*)rayO.ptr + ob, (char*)rayD.ptr + ob, m, dBits )) return 1;
+			cudaEventRecord( chunkEv[2 * k + 1], stream );
+			cudaStreamWaitEvent( copyOut, chunkEv[2 * k + 1], 0 );
+			if ((e = cudaMemcpyAsync( (char*)out + (size_t)(off / 32) * 4, dBits, (size_t)((m + 31) / 32) * 4, cudaMemcpyDeviceToHost, copyOut )) != cudaSuccess) return fail( "bitmask download", e );
+		}
+		else
+		{
+			if (TraceClosestDevice( (char*)rayO.ptr + ob, (char*)rayD.ptr + ob, m, (char*)hitBuf.ptr + ob )) return 1;
+			cudaEventRecord( chunkEv[2 * k + 1], stream );
+			cudaStreamWaitEvent( copyOut, chunkEv[2 * k + 1], 0 );
+			if ((e = cudaMemcpyAsync( (char*)out + ob, (char*)hitBuf.ptr + ob, mb, cudaMemcpyDeviceToHost, copyOut )) != cudaSuccess) return fail( "hit download", e );
+		}
+	}
+	if ((e = cudaStreamSynchronize( copyOut )) != cudaSuccess) return fail( anyHit ? "shadow wave" : "extend wave", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( anyHit ? "shadow wave" : "extend wave", e );
+	cudaEventElapsedTime( &stats.lastTraceMs, evA, evB ); // device time of the LAST chunk's kernel
 	return 0;
 }
 
-int RenderCore::TraceAny( const float* O4, const float* D4, int n, uint32_t* bits )
-{
-	if (n < 0) return fail( "trace: negative ray count" );
-	if (n == 0) return ensureToplevel();
-	cudaError_t e;
-	const size_t rb = (size_t)n * 16, bb = (size_t)((n + 31) / 32) * 4;
-	if ((e = rayO.reserve( rb, false, stream )) != cudaSuccess || (e = rayD.reserve( rb, false, stream )) != cudaSuccess ||
-		(e = bitBuf.reserve( bb, false, stream )) != cudaSuccess) return fail( "ray buffers", e );
-	if ((e = cudaMemcpyAsync( rayO.ptr, O4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
-	if ((e = cudaMemcpyAsync( rayD.ptr, D4, rb, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "ray upload", e );
-	if (TraceAnyDevice( rayO.ptr, rayD.ptr, n, bitBuf.ptr )) return 1;
-	if ((e = cudaMemcpyAsync( bits, bitBuf.ptr, bb, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "bitmask download", e );
-	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "shadow wave", e );
-	cudaEventElapsedTime( &stats.lastTraceMs, evA, evB );
-	return 0;
-}
+// host-buffer variants: H2D, wave, D2H, synchronise (the e2e path of bench.py)
+int RenderCore::TraceClosest( const float* O4, const float* D4, int n, float* hits ) { return hostWave( O4, D4, n, hits, false ); }
+int RenderCore::TraceAny( const float* O4, const float* D4, int n, uint32_t* bits ) { return hostWave( O4, D4, n, bits, true ); }
 
 int RenderCore::ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris )
 {

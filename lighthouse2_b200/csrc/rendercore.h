@@ -80,6 +80,10 @@ public:
 
 private:
 	int ensureToplevel();
+	int hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit );
+	static constexpr int MAX_CHUNKS = 8;
+	cudaStream_t copyIn = nullptr, copyOut = nullptr;
+	cudaEvent_t chunkEv[2 * MAX_CHUNKS + 1] = {};
 	bool initOk = false;
 	std::string error;
 	int device = 0;
