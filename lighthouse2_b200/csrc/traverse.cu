@@ -246,8 +246,7 @@ constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
 #ifndef B200_MIN_BLOCKS
 #define B200_MIN_BLOCKS 6
 #endif
-constexpr int ENQUEUE_MAX = 6;                         // pairs a lane may queue per pass
-constexpr int QUEUE_CAP = 256;                        // ring entries per warp (a flush starts as soon as 32 are pending)
+constexpr int RING_CAP = 64;                          // leaf records per warp ring (a pass adds at most 32)
 constexpr int REFILL_BELOW = B200_REFILL_BELOW;      // leave the traversal loop to fetch rays when fewer lanes are active
 constexpr int PARTIAL_BELOW = B200_PARTIAL_BELOW;    // flush a partially filled ring for waiting lanes when fewer lanes have node work
 
@@ -259,10 +258,10 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
 	__shared__ uint32_t sSlot[BLOCK_THREADS];        // flush slot of the winning pair, 0xffffffff = none
 	__shared__ float4 sWorld[BLOCK_THREADS];         // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
-	__shared__ uint32_t sQueue[WARPS_PER_BLOCK][QUEUE_CAP];
+	__shared__ uint2 sRing[WARPS_PER_BLOCK][RING_CAP]; // leaf records: (first triangle | owner lane << 27, 24-bit triangle mask)
 	uint2 lstack[STACK_LOCAL];
 	const uint32_t lane = threadIdx.x & 31, warpBase = threadIdx.x & ~31u;
-	uint32_t* const queue = sQueue[threadIdx.x >> 5];
+	uint2* const ring = sRing[threadIdx.x >> 5];
 	const uint32_t total = a.countPtr ? __ldg( a.countPtr ) : a.count;
 	const uint4* __restrict__ nodes = a.nodes;
 	const float4* __restrict__ tris = a.tris;
@@ -272,8 +271,9 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	uint32_t rayIdx = 0, hitPrim = 0, hitInst = 0, hitBary = 0, curInst = 0, nNodes = 0, nTris = 0;
 	uint2 ngroup = make_uint2( 0, 0 ), tgroup = make_uint2( 0, 0 );
 	int sp = 0, instBase = -1;
-	uint32_t qhead = 0, qtail = 0;     // ring sequence numbers (warp-uniform)
-	uint32_t lastQueued = 0xffffffffu; // sequence number of this lane's newest queued pair
+	uint32_t qhead = 0, qtail = 0;     // ring sequence numbers of the leaf records (warp-uniform)
+	uint32_t pendingTris = 0;          // triangles in the ring (warp-uniform)
+	uint32_t lastQueued = 0xffffffffu; // sequence number of this lane's newest record
 	bool active = false, exhausted = false, terminated = false;
 	sSlot[threadIdx.x] = 0xffffffffu;
 
@@ -289,23 +289,57 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		sRayO[threadIdx.x] = make_float4( r.ox, r.oy, r.oz, r.tmin );
 		sRayD[threadIdx.x] = make_float4( r.dx, r.dy, r.dz, r.t );
 	};
-	// test `n` (<= 32) queued pairs, one per lane; every lane of the warp calls this (converged)
-	auto flush = [&]( const uint32_t n ) {
-		const bool mine = lane < n;
+	// One round: the first min(32, pending) triangles of the ring, one per lane; every lane of the warp calls this (converged).
+	// Lane r loads record r, a warp scan of the triangle counts gives each record its range, tester lane L finds its record
+	// with a 5-step search over the scanned counts and takes that record's (L - start)-th triangle.
+	auto flush = [&]() {
+		const uint32_t nrec = min( qtail - qhead, 32u );
+		const uint2 rec = lane < nrec ? ring[(qhead + lane) & (RING_CAP - 1)] : make_uint2( 0u, 0u );
+		const uint32_t cnt = __popc( rec.y );
+		uint32_t incl = cnt;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1)
+		{
+			const uint32_t up = __shfl_up_sync( 0xffffffffu, incl, d );
+			if (lane >= d) incl += up;
+		}
+		const uint32_t take = min( __shfl_sync( 0xffffffffu, incl, 31 ), 32u );
+		uint32_t ri = 0; // number of records that end at or before triangle `lane` = index of the record holding it
+#pragma unroll
+		for (int step = 16; step; step >>= 1)
+		{
+			const uint32_t v = __shfl_sync( 0xffffffffu, incl, ri + step - 1 );
+			if (v <= lane) ri += step;
+		}
+		ri = min( ri, 31u );
+		const uint32_t rx = __shfl_sync( 0xffffffffu, rec.x, ri ), ry = __shfl_sync( 0xffffffffu, rec.y, ri );
+		const uint32_t rstart = __shfl_sync( 0xffffffffu, incl - cnt, ri );
+		const bool mine = lane < take;
 		bool hit = false;
 		float tt = 0, u = 0, v = 0;
 		uint32_t owner = 0, prim = 0;
 		if (mine)
 		{
-			const uint32_t e = queue[(qhead + lane) & (QUEUE_CAP - 1)];
-			owner = warpBase + (e >> 27);
-			const float4* tp = tris + (size_t)(e & 0x07ffffffu) * 3;
+			uint32_t m = ry;
+			for (uint32_t k = lane - rstart; k; k--) m &= ~(0x80000000u >> __clz( m )); // drop the k triangles before mine
+			const uint32_t bit = 31 - __clz( m );
+			owner = warpBase + (rx >> 27);
+			const float4* tp = tris + (size_t)((rx & 0x07ffffffu) + bit) * 3;
 			const float4 v0 = __ldg( tp ), e1 = __ldg( tp + 1 ), e2 = __ldg( tp + 2 );
 			const float4 O = sRayO[owner], D = sRayD[owner];
 			prim = __float_as_uint( v0.w );
 			hit = intersectTriangle<ISECT>( O, D, v0, e1, e2, tt, u, v );
 		}
-		qhead += n;
+		// retire consumed records; the record that straddles the 32-triangle boundary keeps its untested triangles
+		const bool full = lane < nrec && incl <= take;
+		if (lane < nrec && incl > take && incl - cnt < take)
+		{
+			uint32_t m = rec.y;
+			for (uint32_t k = take - (incl - cnt); k; k--) m &= ~(0x80000000u >> __clz( m ));
+			ring[(qhead + lane) & (RING_CAP - 1)].y = m;
+		}
+		qhead += __popc( __ballot_sync( 0xffffffffu, full ) );
+		pendingTris -= take;
 		const uint32_t hitMask = __ballot_sync( 0xffffffffu, hit ); // also orders the mirror reads before the atomics
 		if (hitMask)
 		{
@@ -327,6 +361,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				if (ANYHIT) terminated = true, ngroup.y = 0, tgroup.y = 0;
 			}
 		}
+		__syncwarp();
 	};
 
 	while (true)
@@ -397,37 +432,24 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				ngroup = make_uint2( __float_as_uint( info.x ), 0x80000000u );
 				tgroup = make_uint2( 0, 0 );
 			}
-			// C. bottom level: queue (owner, triangle) pairs -- at most ENQUEUE_MAX per lane per pass (a lane that hit
-			//    more leaf triangles keeps the rest in tgroup and skips its next node step); positions come from a
-			//    warp scan of the per-lane counts.
+			// C. bottom level: a lane that hit leaf triangles appends ONE record (first triangle, mask, owner) to the warp's
+			//    ring; as soon as 32 triangles are pending the warp tests them, one per lane
 			{
-				const bool inBlas = active && instBase >= 0;
-				const uint32_t tb = inBlas ? tgroup.y : 0u;
-				const uint32_t cnt = min( (uint32_t)__popc( tb ), (uint32_t)ENQUEUE_MAX );
-				if (__ballot_sync( 0xffffffffu, cnt != 0 ))
+				const bool has = active && instBase >= 0 && tgroup.y != 0;
+				const uint32_t m = __ballot_sync( 0xffffffffu, has );
+				if (m)
 				{
-					uint32_t incl = cnt;
-#pragma unroll
-					for (int d = 1; d < 32; d <<= 1)
+					if (has)
 					{
-						const uint32_t up = __shfl_up_sync( 0xffffffffu, incl, d );
-						if (lane >= d) incl += up;
+						lastQueued = qtail + __popc( m & lanemask_lt() );
+						ring[lastQueued & (RING_CAP - 1)] = make_uint2( tgroup.x | (lane << 27), tgroup.y );
+						if (COUNT) nTris += __popc( tgroup.y );
 					}
-					const uint32_t totalNew = __shfl_sync( 0xffffffffu, incl, 31 );
-					uint32_t pos = qtail + incl - cnt, rest = tb;
-					const uint32_t entry0 = tgroup.x | (lane << 27);
-					for (uint32_t k = 0; k < cnt; k++)
-					{
-						const uint32_t bit = 31 - __clz( rest );
-						rest &= ~(1u << bit);
-						queue[pos & (QUEUE_CAP - 1)] = entry0 + bit;
-						pos++;
-					}
-					if (cnt) lastQueued = pos - 1, tgroup.y = rest;
-					if (COUNT) nTris += cnt;
-					qtail += totalNew;
+					pendingTris += __reduce_add_sync( 0xffffffffu, has ? (uint32_t)__popc( tgroup.y ) : 0u );
+					if (has) tgroup.y = 0;
+					qtail += __popc( m );
 					__syncwarp();
-					while (qtail - qhead >= 32) flush( 32 );
+					while (pendingTris >= 32) flush();
 				}
 			}
 			// D. lanes without node work: leave the instance / pop / retire (only once their queued pairs are tested)
@@ -483,10 +505,10 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				}
 			}
 			// E. flush a partially filled ring when lanes wait on it and little node work is left in the warp
-			if (__ballot_sync( 0xffffffffu, waiting ) && qtail != qhead)
+			if (__ballot_sync( 0xffffffffu, waiting ) && pendingTris)
 			{
 				const uint32_t workMask = __ballot_sync( 0xffffffffu, active && (ngroup.y > 0x00ffffffu || tgroup.y) );
-				if (__popc( workMask ) < PARTIAL_BELOW) flush( qtail - qhead );
+				if (__popc( workMask ) < PARTIAL_BELOW) while (pendingTris) flush();
 			}
 			// F. too few lanes left in this warp and rays remain: go back and refill the idle lanes
 			const uint32_t activeMask = __ballot_sync( 0xffffffffu, active );
