@@ -303,17 +303,14 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			const uint32_t up = __shfl_up_sync( 0xffffffffu, incl, d );
 			if (lane >= d) incl += up;
 		}
-		const uint32_t take = min( __shfl_sync( 0xffffffffu, incl, 31 ), 32u );
-		uint32_t ri = 0; // number of records that end at or before triangle `lane` = index of the record holding it
-#pragma unroll
-		for (int step = 16; step; step >>= 1)
-		{
-			const uint32_t v = __shfl_sync( 0xffffffffu, incl, ri + step - 1 );
-			if (v <= lane) ri += step;
-		}
-		ri = min( ri, 31u );
+		const uint32_t start = incl - cnt, total = __shfl_sync( 0xffffffffu, incl, 31 );
+		const uint32_t take = min( total, 32u );
+		// every record holds >= 1 triangle, so record starts are distinct: bit s of `starts` = a record starts at triangle s;
+		// the record of tester lane L is the number of starts at or below L, minus one
+		const uint32_t starts = __reduce_or_sync( 0xffffffffu, (lane < nrec && start < 32u) ? 1u << start : 0u );
+		const uint32_t ri = min( (uint32_t)__popc( starts & (0xffffffffu >> (31 - lane)) ) - 1u, 31u );
 		const uint32_t rx = __shfl_sync( 0xffffffffu, rec.x, ri ), ry = __shfl_sync( 0xffffffffu, rec.y, ri );
-		const uint32_t rstart = __shfl_sync( 0xffffffffu, incl - cnt, ri );
+		const uint32_t rstart = __shfl_sync( 0xffffffffu, start, ri );
 		const bool mine = lane < take;
 		bool hit = false;
 		float tt = 0, u = 0, v = 0;
