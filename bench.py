@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-frame", action="store_true")
+    ap.add_argument("--setting", action="append", default=[], help="name=value, applied to the core before the scene is built")
+    ap.add_argument("--stats", action="store_true", help="also report nodes visited / triangles tested per ray (untimed counting run)")
     ap.add_argument("--check", action="store_true", help="compare a sample of the GPU hits with the CPU checker")
     return ap.parse_args()
 
@@ -215,6 +217,8 @@ def run_b200(args):
 
     rc = core.RenderCoreB200(local)
     rc.Setting("isectMode", args.isect)
+    for kv in args.setting:
+        rc.Setting(kv.split("=")[0], float(kv.split("=")[1]))
     verts = scenes.sphere_field(args.tris)
     t0 = time.perf_counter()
     rc.SetGeometry(0, verts)
@@ -413,6 +417,16 @@ def run_b200(args):
                                     "per_class": r["per_class"], "bvh_build_s": r["bvh_build_s"]}
         if frame:
             line["frame"] = frame
+        if args.stats:
+            rc.Setting("countSteps", 1)
+            line["steps_per_ray"] = {}
+            for w in waves:
+                if w["kind"] == "closest":
+                    rc.TraceClosest(w["O4"], w["D4"])
+                    nn, nt = rc.StepCounters(w["n"])
+                    line["steps_per_ray"][f"{w['cls']}{w['bounce']}"] = {"nodes": float(nn.mean()), "tris": float(nt.mean()), "nodes_max": int(nn.max()),
+                                                                             "nodes_pct": [float(x) for x in np.percentile(nn, [50, 90, 99, 99.9, 99.99])]}
+            rc.Setting("countSteps", 0)
         if args.check:
             line["check"] = check_against_cpu(rc, core, verts, waves)
         print(json.dumps(line), flush=True)

@@ -13,6 +13,8 @@
 
 namespace b200 {
 
+float g_sahPrimCost = 0.4f;
+
 namespace {
 
 struct Ref { Aabb b; float c[3]; uint32_t id; }; // primitive reference, partitioned in place
@@ -24,7 +26,8 @@ struct Node2 {
 };
 
 constexpr int BINS = 16;
-constexpr float COST_TRAVERSE = 1.0f, COST_PRIM = 0.4f; // a leaf triangle costs ~0.4 of a wide-node visit in the kernels
+constexpr float COST_TRAVERSE = 1.0f;
+#define COST_PRIM g_sahPrimCost // cost of a leaf triangle relative to a wide-node visit in the kernels (Setting "sahPrimCost")
 
 struct Builder2 {
 	std::vector<Ref> refs;

@@ -145,6 +145,7 @@ int RenderCore::Setting( const char* name, float value )
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
 	if (!strcmp( name, "countSteps" )) { countSteps = value >= 0.5f; return 0; }
 	if (!strcmp( name, "refit" )) { allowRefit = value >= 0.5f; return 0; }
+	if (!strcmp( name, "sahPrimCost" )) { if (!(value > 0)) return fail( "Setting sahPrimCost: > 0" ); g_sahPrimCost = value; return 0; }
 	if (!strcmp( name, "buildThreads" )) { buildThreads = value < 1 ? 1 : (int)value; return 0; }
 	return SettingWavefront( name, value );
 }

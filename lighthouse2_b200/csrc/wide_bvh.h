@@ -69,6 +69,8 @@ struct WideBvh {
 	Aabb bounds;
 };
 
+extern float g_sahPrimCost; // builder tunable: SAH cost of one leaf triangle relative to one wide-node visit
+
 // Binned-SAH BVH2 over `n` primitive boxes, collapsed to the 8-wide layout above.
 // maxLeafPrims: 3 for triangles (unary 3-bit count), 1 for instances.  Indices in the result are
 // relative (root = 0, primBase relative to 0); the core rebases them when it places the tree in its pools.
