@@ -41,7 +41,7 @@ struct RefitArgs {
 	uint32_t nodeBase;         // absolute index of the mesh root in the pool
 	uint32_t triBase, triCount;
 };
-cudaError_t LaunchRefitTriangles( const RefitArgs& a, cudaStream_t s );
+cudaError_t LaunchRefitTop( const RefitArgs& a, const uint32_t* levelStart, int nTop, cudaStream_t s ); // levels [0,nTop) in one launch
 cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t levelEnd, cudaStream_t s );
 
 } // namespace b200

@@ -4,39 +4,17 @@
 // (lib/RenderCore_Bart/rendercore.cpp:78 -> bvh.cpp:57); the OptiX cores call optixAccelBuild with
 // OPTIX_BUILD_OPERATION_UPDATE (lib/rendercore_optix7/core_mesh.cpp:71-103).  Here the topology built by
 // bvh_builder.cpp is kept and only boxes are recomputed:
-//   1. refitTriangles: one thread per leaf-order triangle slot gathers its three new vertices
-//      (original primitive order, float4[3T]) and rewrites {v0|prim, e1, e2}          -- 48 B in, 48 B out / tri
-//   2. refitLevel, deepest level first (nodes are stored breadth-first, so a level is an index range):
-//      eight lanes per node, lane s owns child slot s; leaf slots bound their triangles from the new
-//      vertices, inner slots read the child's float box from scratch; an 8-lane shuffle reduction gives
-//      the node box; each lane re-quantises its own child against the new frame (double arithmetic,
-//      same formulas as QuantiseFrame/QuantiseChild in bvh_builder.cpp)              -- 80 B r/w + 32 B scratch / node
+//   refitLevel, deepest level first (nodes are stored breadth-first, so a level is an index range): eight lanes per node, lane s
+//   owns child slot s.  A leaf slot gathers the new vertices of its <= 3 triangles once (original primitive order, float4[3T]),
+//   rewrites their leaf-order records {v0|prim, e1, e2} and shading normals, and bounds them; an inner slot reads the child's
+//   float box from scratch; an 8-lane shuffle reduction gives the node box; each lane re-quantises its own child against the
+//   new frame (double arithmetic, same formulas as QuantiseFrame/QuantiseChild in bvh_builder.cpp).
+//   Bytes: per triangle 16 (record .w) + 48 (vertices) read, 48 + 16 written; per node 80 read + 80 written + 32 scratch.
 #include "kernels.h"
 
 namespace b200 {
 
 namespace {
-
-__global__ void refitTrianglesKernel( const RefitArgs a )
-{
-	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-	if (j >= a.triCount) return;
-	float4* tp = a.tris + (size_t)(a.triBase + j) * 3;
-	const uint32_t prim = __float_as_uint( tp[0].w );
-	const float4 p0 = __ldg( a.verts + (size_t)prim * 3 ), p1 = __ldg( a.verts + (size_t)prim * 3 + 1 ), p2 = __ldg( a.verts + (size_t)prim * 3 + 2 );
-	tp[0] = make_float4( p0.x, p0.y, p0.z, __uint_as_float( prim ) );
-	tp[1] = make_float4( p1.x - p0.x, p1.y - p0.y, p1.z - p0.z, 0.f );
-	tp[2] = make_float4( p2.x - p0.x, p2.y - p0.y, p2.z - p0.z, 0.f );
-	if (a.shade)
-	{
-		// geometric normal of the moved triangle (object space), material bits kept
-		const float e1x = p1.x - p0.x, e1y = p1.y - p0.y, e1z = p1.z - p0.z, e2x = p2.x - p0.x, e2y = p2.y - p0.y, e2z = p2.z - p0.z;
-		float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
-		const float l2 = nx * nx + ny * ny + nz * nz, il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
-		float4* sp = a.shade + a.triBase + prim;
-		*sp = make_float4( nx * il, ny * il, nz * il, sp->w );
-	}
-}
 
 __device__ __forceinline__ uint32_t frameExponent( float lo, float hi )
 {
@@ -62,11 +40,9 @@ __device__ __forceinline__ void quantise( float p, uint32_t e, float lo, float h
 	qhi = (uint32_t)(h < 0 ? 0 : (h > 255 ? 255 : h));
 }
 
-__global__ void refitLevelKernel( const RefitArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
+// one child slot of one node; all 8 lanes of a node's group call this together (valid or not), groups are 8-aligned in the warp
+__device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t node, const uint32_t s, const bool valid, const uint32_t levelBegin )
 {
-	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-	const uint32_t node = levelBegin + (gid >> 3), s = gid & 7;
-	const bool valid = node < levelEnd; // whole 8-lane groups are valid or not, so the shuffles below stay converged per group
 	const uint32_t n = valid ? node : levelBegin;
 	uint4* np = a.nodes + (size_t)(a.nodeBase + n) * 5;
 	const uint4 n0 = np[0], n1 = np[1];
@@ -84,16 +60,30 @@ __global__ void refitLevelKernel( const RefitArgs a, const uint32_t levelBegin, 
 		}
 		else
 		{
+			// leaf slot: this lane owns the slot's <= 3 triangles.  Gather their new vertices ONCE (original primitive order),
+			// rewrite the leaf-order records {v0|prim, e1, e2} and the shading normal, and bound them.
 			const uint32_t cnt = __popc( meta >> 5 ), first = n1.y + (meta & 31u);
 			for (uint32_t k = 0; k < cnt; k++)
 			{
-				const uint32_t prim = __float_as_uint( a.tris[(size_t)(first + k) * 3].w );
-				for (int c = 0; c < 3; c++)
+				float4* tp = a.tris + (size_t)(first + k) * 3;
+				const uint32_t prim = __float_as_uint( tp[0].w );
+				const float4* vp = a.verts + (size_t)prim * 3;
+				const float4 p0 = __ldg( vp ), p1 = __ldg( vp + 1 ), p2 = __ldg( vp + 2 );
+				const float e1x = p1.x - p0.x, e1y = p1.y - p0.y, e1z = p1.z - p0.z, e2x = p2.x - p0.x, e2y = p2.y - p0.y, e2z = p2.z - p0.z;
+				tp[0] = make_float4( p0.x, p0.y, p0.z, __uint_as_float( prim ) );
+				tp[1] = make_float4( e1x, e1y, e1z, 0.f );
+				tp[2] = make_float4( e2x, e2y, e2z, 0.f );
+				if (a.shade)
 				{
-					const float4 p = __ldg( a.verts + (size_t)prim * 3 + c );
-					lo[0] = fminf( lo[0], p.x ), lo[1] = fminf( lo[1], p.y ), lo[2] = fminf( lo[2], p.z );
-					hi[0] = fmaxf( hi[0], p.x ), hi[1] = fmaxf( hi[1], p.y ), hi[2] = fmaxf( hi[2], p.z );
+					float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
+					const float l2 = nx * nx + ny * ny + nz * nz, il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
+					float4* sp = a.shade + a.triBase + prim;
+					*sp = make_float4( nx * il, ny * il, nz * il, sp->w );
 				}
+				lo[0] = fminf( lo[0], fminf( p0.x, fminf( p1.x, p2.x ) ) ), lo[1] = fminf( lo[1], fminf( p0.y, fminf( p1.y, p2.y ) ) );
+				lo[2] = fminf( lo[2], fminf( p0.z, fminf( p1.z, p2.z ) ) );
+				hi[0] = fmaxf( hi[0], fmaxf( p0.x, fmaxf( p1.x, p2.x ) ) ), hi[1] = fmaxf( hi[1], fmaxf( p0.y, fmaxf( p1.y, p2.y ) ) );
+				hi[2] = fmaxf( hi[2], fmaxf( p0.z, fmaxf( p1.z, p2.z ) ) );
 			}
 		}
 	}
@@ -119,12 +109,40 @@ __global__ void refitLevelKernel( const RefitArgs a, const uint32_t levelBegin, 
 	}
 }
 
+__global__ void refitLevelKernel( const RefitArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
+{
+	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t node = levelBegin + (gid >> 3);
+	refitSlot( a, node, gid & 7, node < levelEnd, levelBegin ); // whole 8-lane groups are valid or not, so the shuffles stay converged per group
+}
+
+// the small top levels in ONE launch: a single CTA walks them bottom-up with a block barrier between levels
+struct TopLevels { uint32_t start[17]; int count; }; // start[i]..start[i+1] = level i (root level first)
+__global__ void __launch_bounds__( 1024 ) refitTopKernel( const RefitArgs a, const TopLevels t )
+{
+	for (int level = t.count - 1; level >= 0; level--)
+	{
+		const uint32_t begin = t.start[level], end = t.start[level + 1], slots = (end - begin) * 8;
+		for (uint32_t i = threadIdx.x; i < ((slots + 1023u) & ~1023u); i += 1024)
+		{
+			const uint32_t node = begin + (i >> 3);
+			refitSlot( a, node, i & 7, node < end, begin );
+		}
+		__threadfence_block();
+		__syncthreads();
+	}
+}
+
 } // namespace
 
-cudaError_t LaunchRefitTriangles( const RefitArgs& a, cudaStream_t s )
+// levels [0, nTop) of `levelStart` (root first) in one launch; nTop <= 16
+cudaError_t LaunchRefitTop( const RefitArgs& a, const uint32_t* levelStart, int nTop, cudaStream_t s )
 {
-	if (!a.triCount) return cudaSuccess;
-	refitTrianglesKernel<<<(a.triCount + 255) / 256, 256, 0, s>>>( a );
+	if (nTop <= 0) return cudaSuccess;
+	TopLevels t;
+	t.count = nTop;
+	for (int i = 0; i <= nTop; i++) t.start[i] = levelStart[i];
+	refitTopKernel<<<1, 1024, 0, s>>>( a, t );
 	return cudaGetLastError();
 }
 

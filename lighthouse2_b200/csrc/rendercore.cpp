@@ -262,11 +262,18 @@ int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, b
 	a.nodeLo = (float4*)nodeLo.ptr, a.nodeHi = (float4*)nodeHi.ptr, a.shade = (float4*)shadePool.ptr;
 	a.nodeBase = m.nodeBase, a.triBase = m.triBase, a.triCount = m.triCount;
 	cudaEventRecord( evA, stream );
-	if ((e = LaunchRefitTriangles( a, stream )) != cudaSuccess) return fail( "refit triangles", e );
-	stats.kernelLaunches++;
-	for (int level = (int)m.levelStart.size() - 2; level >= 0; level--)
+	// deepest level first; the tiny top levels (at most 16 nodes each) share one single-CTA launch
+	const int levels = (int)m.levelStart.size() - 1;
+	int nTop = 0;
+	while (nTop < levels && nTop < 16 && m.levelStart[nTop + 1] - m.levelStart[nTop] <= 16) nTop++; // measured: a single CTA is slower than one launch per level beyond a few nodes
+	for (int level = levels - 1; level >= nTop; level--)
 	{
 		if ((e = LaunchRefitLevel( a, m.levelStart[level], m.levelStart[level + 1], stream )) != cudaSuccess) return fail( "refit level", e );
+		stats.kernelLaunches++;
+	}
+	if (nTop)
+	{
+		if ((e = LaunchRefitTop( a, m.levelStart.data(), nTop, stream )) != cudaSuccess) return fail( "refit top levels", e );
 		stats.kernelLaunches++;
 	}
 	cudaEventRecord( evB, stream );

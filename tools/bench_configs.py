@@ -40,6 +40,33 @@ def stats_line(name, rc, frames, extra):
     print(json.dumps(line), flush=True)
 
 
+def refit_traffic(n_tris, nodes):
+    """Algorithmic bytes of one refit (refit.cu): per triangle 16 B record tag + 48 B vertices + 16 B shading record read, 48 B record +
+    16 B shading record written; per node 80 B read + 80 B written + 32 B float box written (and read once by the parent)."""
+    return 144 * n_tris + 224 * nodes
+
+
+def refit_c2(frames):
+    """GPU refit of the 1M-triangle C2 mesh (vertices already on the device): the HBM-bound size of the refit kernel."""
+    import torch
+    rc = core.RenderCoreB200(0)
+    verts = scenes.sphere_field(1_000_000)
+    rc.SetGeometry(0, verts); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
+    v4 = np.ones((verts.shape[0] * 3, 4), np.float32); v4[:, :3] = verts.reshape(-1, 3) * 1.001
+    dv = torch.from_numpy(v4).cuda()
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(frames + 2):
+        rc.RefitDevice(0, dv.data_ptr(), v4.shape[0])
+        ms.append(rc.GetCoreStats()["refitTime"])
+    ms = float(np.mean(ms[2:]))
+    nodes = rc.GetCoreStats()["wideNodeCount"]
+    b = refit_traffic(verts.shape[0], nodes)
+    print(json.dumps({"config": "refit of the C2 mesh (1M triangles), device-resident vertices", "refit_ms_device": ms, "refit_bytes": b,
+                      "refit_gbs": b / (ms * 1e-3) / 1e9, "hbm_frac_of_6543": b / (ms * 1e-3) / 1e9 / 6543.1, "nodes": nodes}), flush=True)
+    rc.Shutdown()
+
+
 def c1(frames):
     rc = core.RenderCoreB200(0)
     rc.SetGeometry(0, scenes.grid_mesh()); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
@@ -95,7 +122,7 @@ def c4(frames, n_inst=1000, n_tris=100_000):
                 if isinstance(v_, (int, float)):
                     acc[k] = acc.get(k, 0) + v_
     m = lambda n, t: (acc[n] / (acc[t] * 1e-3) / 1e6) if acc.get(t, 0) > 0 else None
-    refit_bytes = 48 * n_tris + 64 * n_tris + 2 * 80 * nodes
+    refit_bytes = refit_traffic(n_tris, nodes)
     print(json.dumps({"config": f"C4 {n_inst} inst x {n_tris} tri BLAS 1080p 2spp, refit + TLAS rebuild per frame", "frames": frames,
                       "refit_ms_device": refit_ms / frames, "refit_gbs": refit_bytes / (refit_ms / frames * 1e-3) / 1e9, "refit_bytes": refit_bytes,
                       "tlas_rebuild_ms_host": tlas_ms / frames, "scene_update_ms_wall": host_ms / frames, "render_ms": acc["renderTime"] / frames,
@@ -110,4 +137,4 @@ if __name__ == "__main__":
     args = [a for a in sys.argv[1:] if not a.startswith("--")] or ["c1", "c3", "c4"]
     frames = int(sys.argv[sys.argv.index("--frames") + 1]) if "--frames" in sys.argv else 5
     for a in args:
-        {"c1": c1, "c3": c3, "c4": c4}[a](frames)
+        {"c1": c1, "c3": c3, "c4": c4, "refit": refit_c2}[a](frames)
