@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=65536, help="pixels in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-detail", action="store_true", help="per-wave wall time of the host-buffer calls for several chunk schedules (stderr)")
     ap.add_argument("--no-frame", action="store_true")
     ap.add_argument("--setting", action="append", default=[], help="name=value, applied to the core before the scene is built")
     ap.add_argument("--stats", action="store_true", help="also report nodes visited / triangles tested per ray (untimed counting run)")
@@ -326,6 +327,39 @@ def run_b200(args):
         eb.record(stream)
         torch.cuda.synchronize()
         pcie_h2d = 5 * big["n"] * 16 / (ea.elapsed_time(eb) * 1e-3) / 1e9
+
+        if args.e2e_detail and rank == 0:
+            def copy_ms(w):  # the wave's own upload alone, and its kernel alone
+                torch.cuda.synchronize(); t0 = time.perf_counter()
+                for _ in range(5):
+                    w["dO"].copy_(w["hO"], non_blocking=True); w["dD"].copy_(w["hD"], non_blocking=True)
+                torch.cuda.synchronize(); up = (time.perf_counter() - t0) / 5 * 1e3
+                t0 = time.perf_counter()
+                for _ in range(5):
+                    launch(w)
+                torch.cuda.synchronize(); k = (time.perf_counter() - t0) / 5 * 1e3
+                t0 = time.perf_counter()
+                for _ in range(5):
+                    w["hOut"].copy_(w["dOut"], non_blocking=True)
+                torch.cuda.synchronize(); dn = (time.perf_counter() - t0) / 5 * 1e3
+                return up, k, dn
+            print("wave            n      up_ms  kern_ms  down_ms", file=sys.stderr)
+            for w in waves:
+                print("%-9s %9d  %7.3f  %7.3f  %7.3f" % ((w["cls"] + str(w["bounce"]), w["n"]) + copy_ms(w)), file=sys.stderr)
+            for zc, two, parts in ((0, 0, 6), (0, 0, 8), (0, 1, 4), (0, 1, 6), (0, 1, 8), (0, 1, 12), (1, 0, 4), (1, 1, 2), (1, 1, 4), (1, 1, 8)):
+                rc.Setting("zeroCopy", zc); rc.Setting("twoStreams", two); rc.Setting("zeroCopyBelow", 1 << 30)
+                rc.Setting("pinnedChunks" if zc else "hostChunks", parts)
+                row = []
+                for w in waves:
+                    fn = lib.b200_trace_closest if w["kind"] == "closest" else lib.b200_trace_any
+                    best = 1e9
+                    for _ in range(6):
+                        t0 = time.perf_counter()
+                        fn(h, w["hO"].data_ptr(), w["hD"].data_ptr(), w["n"], w["hOut"].data_ptr())
+                        best = min(best, (time.perf_counter() - t0) * 1e3)
+                    row.append(best)
+                print("zc %d two %d parts %2d: " % (zc, two, parts) + " ".join("%6.3f" % x for x in row) + "  sum %.3f" % sum(row), file=sys.stderr)
+            rc.Setting("zeroCopyBelow", 400000); rc.Setting("zeroCopy", 1); rc.Setting("twoStreams", 1); rc.Setting("pinnedChunks", 1); rc.Setting("hostChunks", 4)
 
     # ---- the same scene through Render(): full wavefront frame (ray generation, shade, fused connect), tile-sharded over the
     #      ranks, accumulator gathered with one NCCL all-reduce.  Reported beside the wave numbers, not as `value`.

@@ -12,6 +12,10 @@ struct TraceArgs {
 	const float4* instances;   // 6 x float4 per instance record, TLAS leaf order
 	const float4* rayO;        // (Ox,Oy,Oz,tmin)
 	const float4* rayD;        // (Dx,Dy,Dz,tmax)
+	const float4* hostO;       // optional zero-copy source: ray planes in pinned host memory, read over PCIe at ray fetch and written
+	const float4* hostD;       //   through to stageO/stageD (== rayO/rayD, device), from where a lane re-reads its world-space ray
+	float4* stageO;
+	float4* stageD;
 	float4* hits;              // closest-hit output, 16 B/ray           (extend)
 	uint32_t* occluded;        // 1 bit/ray, pre-cleared, bit set = hit  (shadow); may be null when `accumulator` is set
 	const float4* potentials;  // optional fused connect (shadow): E4 = (rgb, pixelIdx bits) per shadow ray ...

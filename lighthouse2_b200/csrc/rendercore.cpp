@@ -121,7 +121,7 @@ RenderCore::~RenderCore()
 	for (DeviceBuffer* b : all) b->release();
 	if (evA) cudaEventDestroy( evA );
 	if (evB) cudaEventDestroy( evB );
-	if (copyIn) { cudaStreamDestroy( copyIn ), cudaStreamDestroy( copyOut ); for (cudaEvent_t ev : chunkEv) if (ev) cudaEventDestroy( ev ); }
+	if (copyIn) { cudaStreamDestroy( copyIn ), cudaStreamDestroy( copyOut ), cudaStreamDestroy( stream2 ); for (cudaEvent_t ev : chunkEv) if (ev) cudaEventDestroy( ev ); }
 }
 
 int RenderCore::fail( const char* what, cudaError_t e )
@@ -143,6 +143,12 @@ int RenderCore::Setting( const char* name, float value )
 		!strcmp( name, "TAA" )) return 0; // accepted, not used by the traversal path
 	// B200-specific keys
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
+	if (!strcmp( name, "twoStreams" )) { twoStreams = value >= 0.5f; return 0; }
+	if (!strcmp( name, "zeroCopy" )) { zeroCopy = value >= 0.5f; return 0; }
+	if (!strcmp( name, "pinnedChunks" )) { pinnedChunks = (int)value; return 0; }
+	if (!strcmp( name, "zeroCopyBelow" )) { zeroCopyBelow = (int)value; return 0; }
+	if (!strcmp( name, "hostChunks" )) { hostChunks = (int)value; return 0; }
+	if (!strcmp( name, "hostChunkMode" )) { hostChunkMode = (int)value; return 0; }
 	if (!strcmp( name, "countSteps" )) { countSteps = value >= 0.5f; return 0; }
 	if (!strcmp( name, "refit" )) { allowRefit = value >= 0.5f; return 0; }
 	if (!strcmp( name, "sahPrimCost" )) { if (!(value > 0)) return fail( "Setting sahPrimCost: > 0" ); g_sahPrimCost = value; return 0; }
@@ -457,11 +463,24 @@ int RenderCore::TraceConnectDevice( const void* dO4, const void* dD4, int n, con
 // The host-buffer waves are pipelined: the rays go up in chunks on a copy-in stream, each chunk's kernel waits only for its
 // own upload, and its results go down on a copy-out stream while the next chunk is traced (PCIe is full duplex, so upload,
 // kernel and download overlap; with pinned host memory the call costs about the upload alone).
-static int chunkRays( int n )
+// Chunk schedule of a host-buffer wave.  mode 0: `parts` equal chunks (at least 256K rays each); mode 1: halving chunks
+// (n/2, n/4, ... down to 32K rays) so that little work is left after the last byte has arrived.
+static int chunkSchedule( int n, int* offsets, int maxChunks, int mode, int parts )
 {
-	int c = n / 6;
-	if (c < (1 << 18)) c = 1 << 18; // smaller chunks starve the persistent grid (148 SMs x 6 CTAs x 128 lanes)
-	return (c + 1023) & ~1023;
+	int count = 0, off = 0;
+	if (parts > maxChunks) parts = maxChunks;
+	if (parts < 1) parts = 1;
+	const int equal = (((n / parts > (1 << 18) ? n / parts : (1 << 18))) + 1023) & ~1023;
+	while (off < n)
+	{
+		int m = mode ? ((n - off) / 2 + 1023) & ~1023 : equal;
+		if (mode && m < (1 << 15)) m = n - off;
+		if (count == maxChunks - 1 || (n - off) - m < (1 << 14)) m = n - off; // no tiny tail chunk
+		offsets[count++] = off;
+		off += m;
+	}
+	offsets[count] = n;
+	return count;
 }
 
 int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit )
@@ -474,45 +493,98 @@ int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bo
 	DeviceBuffer& outBuf = anyHit ? bitBuf : hitBuf;
 	if ((e = rayO.reserve( rb, false, stream )) != cudaSuccess || (e = rayD.reserve( rb, false, stream )) != cudaSuccess ||
 		(e = outBuf.reserve( anyHit ? bb : rb, false, stream )) != cudaSuccess) return fail( "ray buffers", e );
-	const int chunk = countSteps ? n : chunkRays( n );
-	const int nChunks = (n + chunk - 1) / chunk;
-	if (nChunks > MAX_CHUNKS) return fail( "trace: too many chunks" );
+	if (countSteps && ((e = stepNodes.reserve( (size_t)n * 4, false, stream )) != cudaSuccess || (e = stepTris.reserve( (size_t)n * 4, false, stream )) != cudaSuccess))
+		return fail( "step counters", e );
 	if (!copyIn)
 	{
-		if ((e = cudaStreamCreateWithFlags( &copyIn, cudaStreamNonBlocking )) != cudaSuccess || (e = cudaStreamCreateWithFlags( &copyOut, cudaStreamNonBlocking )) != cudaSuccess)
-			return fail( "copy streams", e );
+		if ((e = cudaStreamCreateWithFlags( &copyIn, cudaStreamNonBlocking )) != cudaSuccess || (e = cudaStreamCreateWithFlags( &copyOut, cudaStreamNonBlocking )) != cudaSuccess ||
+			(e = cudaStreamCreateWithFlags( &stream2, cudaStreamNonBlocking )) != cudaSuccess) return fail( "copy streams", e );
 		for (int i = 0; i < 2 * MAX_CHUNKS + 1; i++) if ((e = cudaEventCreateWithFlags( &chunkEv[i], cudaEventDisableTiming )) != cudaSuccess) return fail( "chunk events", e );
 	}
+	// Small waves over pinned (page-locked) ray planes: the kernel itself fetches the rays over PCIe, no staging copy and no
+	// upload -> trace dependency.  (Measured: wins below ~0.5M rays; above, chunked DMA uploads overlap better.)
+	const float4 *zcO = nullptr, *zcD = nullptr;
+	if (zeroCopy && !countSteps && n <= zeroCopyBelow)
+	{
+		cudaPointerAttributes pa, pb;
+		if (cudaPointerGetAttributes( &pa, O4 ) == cudaSuccess && cudaPointerGetAttributes( &pb, D4 ) == cudaSuccess &&
+			pa.type == cudaMemoryTypeHost && pb.type == cudaMemoryTypeHost && pa.devicePointer && pb.devicePointer)
+			zcO = (const float4*)pa.devicePointer, zcD = (const float4*)pb.devicePointer;
+		cudaGetLastError();
+	}
+	// The wave is cut into chunks: upload k+1 (copy engine), trace k, download k-1 (second copy engine) run concurrently.  Chunk
+	// kernels alternate between two streams, so that the tail of one (few long rays left) overlaps the start of the next.
+	int offsets[MAX_CHUNKS + 1];
+	int nChunks = 1;
+	offsets[0] = 0, offsets[1] = n;
+	if (!countSteps) nChunks = chunkSchedule( n, offsets, MAX_CHUNKS, hostChunkMode, zcO ? pinnedChunks : hostChunks );
+	const int join = 2 * MAX_CHUNKS;
+	static const bool traceChunks = getenv( "B200_TRACE_CHUNKS" ) != nullptr; // debugging aid: per-chunk timeline on stderr
+	static cudaEvent_t tev[4 * MAX_CHUNKS + 1];
+	if (traceChunks && !tev[0]) for (cudaEvent_t& t : tev) cudaEventCreate( &t );
 	// the uploads may start once everything queued on the core's stream so far is done (the staging buffers may still be read)
-	cudaEventRecord( chunkEv[2 * MAX_CHUNKS], stream );
-	cudaStreamWaitEvent( copyIn, chunkEv[2 * MAX_CHUNKS], 0 );
+	cudaEventRecord( chunkEv[join], stream );
+	cudaStreamWaitEvent( copyIn, chunkEv[join], 0 );
+	cudaStreamWaitEvent( stream2, chunkEv[join], 0 );
+	if (traceChunks) cudaEventRecord( tev[4 * MAX_CHUNKS], stream );
 	for (int k = 0; k < nChunks; k++)
 	{
-		const int off = k * chunk, m = n - off < chunk ? n - off : chunk;
+		const int off = offsets[k], m = offsets[k + 1] - off;
 		const size_t ob = (size_t)off * 16, mb = (size_t)m * 16;
-		if ((e = cudaMemcpyAsync( (char*)rayO.ptr + ob, (const char*)O4 + ob, mb, cudaMemcpyHostToDevice, copyIn )) != cudaSuccess) return fail( "ray upload", e );
-		if ((e = cudaMemcpyAsync( (char*)rayD.ptr + ob, (const char*)D4 + ob, mb, cudaMemcpyHostToDevice, copyIn )) != cudaSuccess) return fail( "ray upload", e );
-		cudaEventRecord( chunkEv[2 * k], copyIn );
-		cudaStreamWaitEvent( stream, chunkEv[2 * k], 0 );
+		cudaStream_t s = (k & 1) && twoStreams ? stream2 : stream;
+		TraceArgs a = baseArgs();
+		a.fetchCounter += k; // concurrent launches: one fetch counter each
+		a.rayO = (const float4*)rayO.ptr + off, a.rayD = (const float4*)rayD.ptr + off, a.count = (uint32_t)m;
+		if (zcO) a.hostO = zcO + off, a.hostD = zcD + off, a.stageO = (float4*)rayO.ptr + off, a.stageD = (float4*)rayD.ptr + off;
+		else
+		{
+			if ((e = cudaMemcpyAsync( (char*)rayO.ptr + ob, (const char*)O4 + ob, mb, cudaMemcpyHostToDevice, copyIn )) != cudaSuccess) return fail( "ray upload", e );
+			if ((e = cudaMemcpyAsync( (char*)rayD.ptr + ob, (const char*)D4 + ob, mb, cudaMemcpyHostToDevice, copyIn )) != cudaSuccess) return fail( "ray upload", e );
+			cudaEventRecord( chunkEv[MAX_CHUNKS + k], copyIn );
+			cudaStreamWaitEvent( s, chunkEv[MAX_CHUNKS + k], 0 );
+			if (traceChunks) cudaEventRecord( tev[4 * k], copyIn );
+		}
+		if (traceChunks) cudaEventRecord( tev[4 * k + 1], s );
+		if (k == nChunks - 1) cudaEventRecord( evA, s );
+		const void* dOut;
+		size_t outOff, outBytes;
 		if (anyHit)
 		{
-			char* dBits = (char*)bitBuf.ptr + (size_t)(off / 32) * 4; // chunk is a multiple of 1024 rays
-			if (TraceAnyDevice( (char*)rayO.ptr + ob, (char*)rayD.ptr + ob, m, dBits )) return 1;
-			cudaEventRecord( chunkEv[2 * k + 1], stream );
-			cudaStreamWaitEvent( copyOut, chunkEv[2 * k + 1], 0 );
-			if ((e = cudaMemcpyAsync( (char*)out + (size_t)(off / 32) * 4, dBits, (size_t)((m + 31) / 32) * 4, cudaMemcpyDeviceToHost, copyOut )) != cudaSuccess) return fail( "bitmask download", e );
+			outOff = (size_t)(off / 32) * 4, outBytes = (size_t)((m + 31) / 32) * 4; // chunks start at multiples of 1024 rays
+			a.occluded = (uint32_t*)((char*)bitBuf.ptr + outOff), dOut = a.occluded;
+			if ((e = cudaMemsetAsync( a.occluded, 0, outBytes, s )) != cudaSuccess) return fail( "clear bitmask", e );
+			if ((e = LaunchShadow( a, isect, smCount, s )) != cudaSuccess) return fail( "shadow kernel launch", e );
 		}
 		else
 		{
-			if (TraceClosestDevice( (char*)rayO.ptr + ob, (char*)rayD.ptr + ob, m, (char*)hitBuf.ptr + ob )) return 1;
-			cudaEventRecord( chunkEv[2 * k + 1], stream );
-			cudaStreamWaitEvent( copyOut, chunkEv[2 * k + 1], 0 );
-			if ((e = cudaMemcpyAsync( (char*)out + ob, (char*)hitBuf.ptr + ob, mb, cudaMemcpyDeviceToHost, copyOut )) != cudaSuccess) return fail( "hit download", e );
+			outOff = ob, outBytes = mb;
+			a.hits = (float4*)hitBuf.ptr + off, dOut = a.hits;
+			if (countSteps) a.stepNodes = (uint32_t*)stepNodes.ptr, a.stepTris = (uint32_t*)stepTris.ptr;
+			if ((e = LaunchExtend( a, isect, countSteps, smCount, s )) != cudaSuccess) return fail( "extend kernel launch", e );
 		}
+		if (k == nChunks - 1) cudaEventRecord( evB, s );
+		stats.kernelLaunches++;
+		cudaEventRecord( chunkEv[k], s );
+		cudaStreamWaitEvent( copyOut, chunkEv[k], 0 );
+		if (traceChunks) cudaEventRecord( tev[4 * k + 2], s );
+		if ((e = cudaMemcpyAsync( (char*)out + outOff, dOut, outBytes, cudaMemcpyDeviceToHost, copyOut )) != cudaSuccess) return fail( "result download", e );
+		if (traceChunks) cudaEventRecord( tev[4 * k + 3], copyOut );
 	}
+	if (nChunks > 1 && twoStreams) { cudaEventRecord( chunkEv[join], stream2 ); cudaStreamWaitEvent( stream, chunkEv[join], 0 ); }
 	if ((e = cudaStreamSynchronize( copyOut )) != cudaSuccess) return fail( anyHit ? "shadow wave" : "extend wave", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( anyHit ? "shadow wave" : "extend wave", e );
 	cudaEventElapsedTime( &stats.lastTraceMs, evA, evB ); // device time of the LAST chunk's kernel
+	if (traceChunks)
+	{
+		fprintf( stderr, "[chunks%s] n=%d %s:", zcO ? " zc" : "", n, anyHit ? "any" : "closest" );
+		for (int k = 0; k < nChunks; k++)
+		{
+			float t[4] = {};
+			for (int j = zcO ? 1 : 0; j < 4; j++) cudaEventElapsedTime( &t[j], tev[4 * MAX_CHUNKS], tev[4 * k + j] );
+			fprintf( stderr, " [%dK up %.0f k %.0f-%.0f dn %.0f]", (offsets[k + 1] - offsets[k]) >> 10, t[0] * 1e3f, t[1] * 1e3f, t[2] * 1e3f, t[3] * 1e3f );
+		}
+		fprintf( stderr, "\n" );
+	}
 	return 0;
 }
 

@@ -81,8 +81,8 @@ public:
 private:
 	int ensureToplevel();
 	int hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit );
-	static constexpr int MAX_CHUNKS = 8;
-	cudaStream_t copyIn = nullptr, copyOut = nullptr;
+	static constexpr int MAX_CHUNKS = 12;
+	cudaStream_t copyIn = nullptr, copyOut = nullptr, stream2 = nullptr;
 	cudaEvent_t chunkEv[2 * MAX_CHUNKS + 1] = {};
 	bool initOk = false;
 	std::string error;
@@ -96,6 +96,8 @@ private:
 	// scratch
 	DeviceBuffer rayO, rayD, hitBuf, bitBuf, vertStage, nodeLo, nodeHi, stepNodes, stepTris;
 	bool countSteps = false, allowRefit = true;
+	bool zeroCopy = true, twoStreams = true; int pinnedChunks = 1, zeroCopyBelow = 400000; // pinned host ray planes are fetched by the kernel itself (Setting zeroCopy / pinnedChunks)
+	int hostChunks = 4, hostChunkMode = 0; // chunk schedule of the host-buffer waves (Setting hostChunks / hostChunkMode)
 	int buildThreads = 0;
 	cudaEvent_t evA = nullptr, evB = nullptr;
 	WavefrontState* wf = nullptr;

@@ -376,7 +376,8 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				rayIdx = base + __popc( idleMask & lanemask_lt() );
 				if (rayIdx < total)
 				{
-					const float4 O4 = __ldg( a.rayO + rayIdx ), D4 = __ldg( a.rayD + rayIdx );
+					const float4 O4 = __ldg( (a.hostO ? a.hostO : a.rayO) + rayIdx ), D4 = __ldg( (a.hostO ? a.hostD : a.rayD) + rayIdx );
+					if (a.hostO) a.stageO[rayIdx] = O4, a.stageD[rayIdx] = D4; // host-buffer wave: the upload happens here
 					r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.tmin = O4.w;
 					r.dx = D4.x, r.dy = D4.y, r.dz = D4.z, r.t = D4.w;
 					setupSlab( r );

@@ -89,6 +89,45 @@ def test_c2_host_chunks_equal_device_wave(c2):
     assert np.array_equal(bits, core.unpack_hits(host)["t"] < np.float32(70.0))
 
 
+def test_c2_pinned_host_wave_equals_device_wave(c2):
+    """Pinned host planes take the zero-copy path (the kernel fetches rays over PCIe, several chunk launches on two
+    streams); results must equal the pageable-buffer path, the device-pointer wave, and the path with zeroCopy off."""
+    import torch
+    rc = c2["rc"]
+    lib, h = rc.lib, rc.h
+    rc.Setting("zeroCopyBelow", 1 << 30); rc.Setting("pinnedChunks", 4)  # force the zero-copy path for the big waves too
+    for w in c2["waves"][:3]:  # primary (4 chunks), shadow (any-hit), diffuse
+        n = w["O4"].shape[0]
+        hO, hD = torch.from_numpy(w["O4"]).pin_memory(), torch.from_numpy(w["D4"]).pin_memory()
+        if w["kind"] == "closest":
+            ref = rc.TraceClosest(w["O4"], w["D4"])  # pageable numpy buffers: staged chunks
+            outs = []
+            for zc in (1, 0, 1):
+                rc.Setting("zeroCopy", zc)
+                out = torch.full((n, 4), -1.0).pin_memory()
+                assert lib.b200_trace_closest(h, hO.data_ptr(), hD.data_ptr(), n, out.data_ptr()) == 0
+                outs.append(out.numpy().view(np.uint32).copy())
+            for o in outs:
+                assert np.array_equal(o, ref.view(np.uint32))
+        else:
+            ref = rc.TraceAny(w["O4"], w["D4"])
+            for zc in (1, 0):
+                rc.Setting("zeroCopy", zc)
+                bits = torch.full(((n + 31) // 32,), -1, dtype=torch.int32).pin_memory()
+                assert lib.b200_trace_any(h, hO.data_ptr(), hD.data_ptr(), n, bits.data_ptr()) == 0
+                got = np.unpackbits(bits.numpy().view(np.uint8), bitorder="little")[:n].astype(bool)
+                assert np.array_equal(got, ref)
+    rc.Setting("zeroCopy", 1)
+    # ragged sizes around the chunk / bitmask-word boundaries
+    w = c2["waves"][0]
+    for n in (1, 31, 33, 1025, 262143, 262145, 524289 + 17):
+        hO, hD = torch.from_numpy(w["O4"][:n].copy()).pin_memory(), torch.from_numpy(w["D4"][:n].copy()).pin_memory()
+        out = torch.full((n, 4), -1.0).pin_memory()
+        assert lib.b200_trace_closest(h, hO.data_ptr(), hD.data_ptr(), n, out.data_ptr()) == 0
+        assert np.array_equal(out.numpy().view(np.uint32), rc.TraceClosest(w["O4"][:n], w["D4"][:n]).view(np.uint32))
+    rc.Setting("zeroCopyBelow", 400000); rc.Setting("pinnedChunks", 1)
+
+
 def test_c2_refit_with_same_vertices_is_identity(c2):
     rc = c2["rc"]
     w = c2["waves"][2]
