@@ -371,6 +371,7 @@ def run_b200(args):
         rc.SetPointLight(scenes.C2_LIGHT, (4000.0, 4000.0, 3600.0))
         rc.SetSky((0.4, 0.5, 0.7))
         rc.Setting("maxPathLength", args.bounces + 1)
+        rc.Setting("russianRoulette", 0)  # fixed-depth pass: the frame traces the same waves as the wave benchmark above
         view = scenes.view_pyramid(width=args.width, height=args.height, **scenes.C2_CAMERA)
         for _ in range(2):
             sr.Render(view, 1)

@@ -82,9 +82,16 @@ B200_API int b200_read_step_counters( b200_core* c, int n, uint32_t* nodesVisite
 B200_API int b200_set_target( b200_core* c, int width, int height, int spp );
 B200_API int b200_set_point_light( b200_core* c, const float* position3, const float* radiance3 );
 B200_API int b200_set_sky( b200_core* c, const float* radiance3 );
-/* CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each; the diffuse stage keeps color.value */
+/* CoreAPI_Base::SetLights (core_api_base.h:102-105): the four arrays in the reference's layouts (common_classes.h:275-345:
+ * CoreLightTri 96 B, CorePointLight 32 B, CoreSpotLight 48 B, CoreDirectionalLight 32 B); copied before returning */
+B200_API int b200_set_lights( b200_core* c, const void* areaLights, int areaLightCount, const void* pointLights, int pointLightCount,
+	const void* spotLights, int spotLightCount, const void* directionalLights, int directionalLightCount );
+/* CoreAPI_Base::SetSkyData (core_api_base.h:106): equirectangular float3 pixels[width * height] (tools_shared.h:185-192) */
+B200_API int b200_set_sky_data( b200_core* c, const float* rgb, int width, int height );
+/* CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each; the Lambert stage keeps color.value and
+ * roughness.value (a colour component above 1 makes the material a light, common_classes.h ShadingData::IsEmissive) */
 B200_API int b200_set_materials( b200_core* c, const void* coreMaterials, int count );
-/* headless shortcut for hosts without CoreMaterial structs: one float4 albedo per material index (CoreTri::material) */
+/* headless shortcut for hosts without CoreMaterial structs: (albedo rgb, roughness) per material index (CoreTri::material) */
 B200_API int b200_set_material_colors( b200_core* c, const float* rgba, int count );
 /* multi-GPU: render into a caller-owned device accumulator float4[w*h] (e.g. a torch tensor that NCCL reduces);
  * NULL = the core's own.  After the gather, b200_finalize( total samples ) rebuilds the frame from it. */

@@ -22,7 +22,7 @@ C_ABI_SYMBOLS = [
     "b200_create", "b200_destroy", "b200_last_error", "b200_set_stream", "b200_set_geometry", "b200_set_instance",
     "b200_update_toplevel", "b200_refit", "b200_refit_device", "b200_setting", "b200_trace_closest", "b200_trace_any",
     "b200_trace_closest_device", "b200_trace_any_device", "b200_read_step_counters", "b200_set_target",
-    "b200_set_point_light", "b200_set_sky", "b200_render", "b200_read_accumulator", "b200_read_frame",
+    "b200_set_point_light", "b200_set_sky", "b200_set_lights", "b200_set_sky_data", "b200_render", "b200_read_accumulator", "b200_read_frame",
     "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
     "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors",
     "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
@@ -83,6 +83,7 @@ def load_library() -> C.CDLL:
         "b200_trace_closest_device": ([vp, vp, vp, ip, vp], ip), "b200_trace_any_device": ([vp, vp, vp, ip, vp], ip),
         "b200_read_step_counters": ([vp, ip, vp, vp], ip),
         "b200_set_target": ([vp, ip, ip, ip], ip), "b200_set_point_light": ([vp, vp, vp], ip), "b200_set_sky": ([vp, vp], ip),
+        "b200_set_lights": ([vp, vp, ip, vp, ip, vp, ip, vp, ip], ip), "b200_set_sky_data": ([vp, vp, ip, ip], ip),
         "b200_render": ([vp, vp, ip], ip), "b200_read_accumulator": ([vp, vp], ip), "b200_read_frame": ([vp, vp], ip),
         "b200_device_accumulator": ([vp], vp), "b200_get_stats": ([vp, C.POINTER(Stats)], ip), "b200_set_probe": ([vp, ip, ip], ip),
         "b200_plugin_core": ([], vp), "b200_host_alloc": ([C.c_uint64], vp), "b200_host_free": ([vp], None),
@@ -123,6 +124,24 @@ def unpack_hits(hits: np.ndarray):
         "u": (bits[:, 0] & 0xFFFF).astype(np.float32) * np.float32(1.0 / 65535.0),
         "v": (bits[:, 0] >> 16).astype(np.float32) * np.float32(1.0 / 65535.0),
     }
+
+
+def core_tris(verts: np.ndarray, materials=None) -> np.ndarray:
+    """CoreTri[T] (176 bytes each, lib/RenderSystem/common_classes.h:60-82) for verts[T,3,3]: material (offset 28),
+    geometric normal Nx/Ny/Nz (44/60/76), area (92) and vertex0/1/2 (128/144/160) filled, the rest zero; ltriIdx = -1."""
+    v = np.asarray(verts, np.float32)
+    t = v.shape[0]
+    out = np.zeros((t, 44), np.float32)
+    n = np.cross(v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]).astype(np.float32)
+    ln = np.sqrt(np.einsum("ij,ij->i", n, n)).astype(np.float32)
+    nn = n / np.maximum(ln, np.float32(1e-30))[:, None]
+    out[:, 11], out[:, 15], out[:, 19] = nn[:, 0], nn[:, 1], nn[:, 2]
+    out[:, 23] = ln * np.float32(0.5)
+    out[:, 32:35], out[:, 36:39], out[:, 40:43] = v[:, 0], v[:, 1], v[:, 2]
+    iv = out.view(np.int32)
+    iv[:, 3] = -1
+    iv[:, 7] = 0 if materials is None else np.asarray(materials, np.int32)
+    return out
 
 
 class RenderCoreB200:
@@ -230,6 +249,23 @@ class RenderCoreB200:
     def SetSky(self, radiance):
         r = np.asarray(radiance, np.float32)
         self._chk(self.lib.b200_set_sky(self.h, r.ctypes.data))
+
+    def SetLights(self, area=None, point=None, spot=None, directional=None):
+        """CoreAPI_Base::SetLights.  Each argument is a float32 array in the reference's record layout
+        (common_classes.h:275-345): area [n, 24], point [n, 8], spot [n, 12], directional [n, 8] (see lights.py)."""
+        arrs = []
+        for a, width in ((area, 24), (point, 8), (spot, 12), (directional, 8)):
+            a = np.zeros((0, width), np.float32) if a is None else np.ascontiguousarray(a, np.float32).reshape(-1, width)
+            arrs.append(a)
+        args = []
+        for a in arrs:
+            args += [a.ctypes.data if len(a) else None, len(a)]
+        self._chk(self.lib.b200_set_lights(self.h, *args))
+
+    def SetSkyData(self, rgb):
+        """CoreAPI_Base::SetSkyData: equirectangular float32 image [height, width, 3]."""
+        px = np.ascontiguousarray(rgb, np.float32)
+        self._chk(self.lib.b200_set_sky_data(self.h, px.ctypes.data, px.shape[1], px.shape[0]))
 
     def SetMaterialColors(self, rgba):
         c = np.ascontiguousarray(rgba, np.float32).reshape(-1, 4)

@@ -51,6 +51,11 @@ int b200_read_step_counters( b200_core* c, int n, uint32_t* nodes, uint32_t* tri
 int b200_set_target( b200_core* c, int w, int h, int spp ) { FORWARD( c, SetTarget( w, h, spp ) ) }
 int b200_set_point_light( b200_core* c, const float* p, const float* r ) { FORWARD( c, SetPointLight( p, r ) ) }
 int b200_set_sky( b200_core* c, const float* r ) { FORWARD( c, SetSky( r ) ) }
+int b200_set_lights( b200_core* c, const void* area, int nArea, const void* point, int nPoint, const void* spot, int nSpot, const void* dir, int nDir )
+{
+	FORWARD( c, SetLights( area, nArea, point, nPoint, spot, nSpot, dir, nDir ) )
+}
+int b200_set_sky_data( b200_core* c, const float* rgb, int width, int height ) { FORWARD( c, SetSkyData( rgb, width, height ) ) }
 int b200_set_materials( b200_core* c, const void* coreMaterials, int count ) { FORWARD( c, SetMaterials( coreMaterials, count ) ) }
 int b200_set_material_colors( b200_core* c, const float* rgba, int count ) { FORWARD( c, SetMaterialColors( rgba, count ) ) }
 int b200_set_accumulator_buffer( b200_core* c, void* dAcc ) { FORWARD( c, SetAccumulatorBuffer( dAcc ) ) }
@@ -133,20 +138,15 @@ public:
 	void Shutdown() override { delete gCore; gCore = nullptr; }
 	void SetTextures( const CoreTexDesc*, const int ) override {}
 	void SetMaterials( CoreMaterial* mat, const int materialCount ) override { CHK( SetMaterials( mat, materialCount ) ); }
-	void SetLights( const CoreLightTri*, const int, const CorePointLight* pointLights, const int pointLightCount, const CoreSpotLight*,
-		const int, const CoreDirectionalLight*, const int ) override
+	void SetLights( const CoreLightTri* areaLights, const int areaLightCount, const CorePointLight* pointLights, const int pointLightCount,
+		const CoreSpotLight* spotLights, const int spotLightCount, const CoreDirectionalLight* directionalLights, const int directionalLightCount ) override
 	{
-		if (pointLightCount > 0) CHK( SetPointLight( &pointLights[0].position.x, &pointLights[0].radiance.x ) );
+		CHK( SetLights( areaLights, areaLightCount, pointLights, pointLightCount, spotLights, spotLightCount, directionalLights, directionalLightCount ) );
 	}
 	void SetSkyData( const float3_t* pixels, const uint width, const uint height, const mat4_t& ) override
 	{
-		// the traversal core keeps a constant sky: the mean of the supplied dome
 		if (!pixels || !width || !height) return;
-		double s[3] = { 0, 0, 0 };
-		const size_t n = (size_t)width * height;
-		for (size_t i = 0; i < n; i++) s[0] += pixels[i].x, s[1] += pixels[i].y, s[2] += pixels[i].z;
-		float m[3] = { (float)(s[0] / n), (float)(s[1] / n), (float)(s[2] / n) };
-		CHK( SetSky( m ) );
+		CHK( SetSkyData( &pixels[0].x, (int)width, (int)height ) );
 	}
 	void SetGeometry( const int meshIdx, const float4_t* vertexData, const int vertexCount, const int triangleCount, const CoreTri* triangles,
 		const uint* alphaFlags ) override

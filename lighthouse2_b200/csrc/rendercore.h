@@ -43,8 +43,10 @@ public:
 	int SetTarget( int width, int height, int spp );
 	int SetPointLight( const float* pos, const float* radiance );
 	int SetSky( const float* radiance );
-	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value
-	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: float4 albedo per material
+	int SetLights( const void* area, int nArea, const void* point, int nPoint, const void* spot, int nSpot, const void* dir, int nDir ); // reference layouts
+	int SetSkyData( const float* rgb, int width, int height ); // equirectangular float3 image
+	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value and roughness.value
+	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: (albedo rgb, roughness) per material; rgb > 1 = emissive
 	int SetAccumulatorBuffer( void* devicePtr );              // caller-owned float4[w*h] accumulator (multi-GPU gathers), null = own
 	int Finalize( uint32_t totalSamples );                    // frame = accumulator / totalSamples (after a gather)
 	int Render( const void* viewPyramid, int converge );

@@ -11,8 +11,11 @@
 //     with atomicAdd; the reference's `accumulator[pixelIdx] += E` is a non-atomic RMW that races for spp > 1,
 //     .optix.cu:148, connections.h:33)
 //   * output goes to a device RGBA32F buffer (no GL texture exists on this box)
-//   * the shade stage is the minimal diffuse model SURVEY.md 7 step 6 asks for (Lambert, one point light with NEE,
-//     constant sky, fixed path length); the full LH2 material system is a "next" row
+//   * the shade stage follows the reference's shadeKernel (lib/rendercore_optix7/kernels/pathtracer.h:54-240) with its
+//     Lambert BSDF (lib/sharedBSDFs/lambert.h: diffuse + pure specular reflection by roughness): area / point / spot /
+//     directional lights picked by potential contribution, MIS between NEE and emissive hits, postponed BSDF pdf,
+//     Russian roulette, HDR skydome lookup, intensity clamp.  Left out: textures, interpolated normals, transmission,
+//     blue-noise tables (a data file of the reference) -- every random number is the WangHash/xor32 stream
 // Pixels can be sharded over several cores/GPUs by interleaved 32x8 tiles (Setting shardIndex/shardCount) or by sample
 // (Setting sampleOffset); per-path random streams depend only on (pixel, sample, bounce), so any sharding gives the same
 // image and the accumulators of all shards simply add up.
@@ -30,15 +33,27 @@ struct WaveCounters { uint32_t extensionRays, shadowRays, pad0, pad1; }; // one 
 
 struct FrameParams {
 	float pos[3], p1[3], right[3], up[3]; // right = p2 - p1, up = p3 - p1
-	float lightPos[3], lightRadiance[3], sky[3];
-	float epsilon;
+	float sky[3];                         // constant sky (used when no skydome image is set)
+	float epsilon, clampValue;
 	uint32_t width, height, pixelCount;
 	uint32_t shardIndex, shardCount, ownTiles, tilesX, tilesY;
 	uint32_t sampleBase, samplesThisPass; // global index of the first sample of this pass
 	uint32_t R0;                          // per-frame RNG salt
-	uint32_t hasLight, jitter, materialCount;
+	uint32_t roulette;                    // Russian roulette on (the reference's behaviour) / off (fixed-depth benchmark passes)
+	uint32_t jitter, materialCount, bounceCap; // bounceCap: 0 = none, 1 = stop after one diffuse bounce (the reference's ENOUGH_BOUNCES), 2 = two
 	int32_t probePixel;
+	// lights (lib/RenderSystem/common_classes.h:275-345 as float4 views, lib/CUDA/shared_kernel_code/lights_shared.h)
+	const float4* areaLights;  // 6 float4 each
+	const float4* pointLights; // 2
+	const float4* spotLights;  // 3
+	const float4* dirLights;   // 2
+	int32_t areaCount, pointCount, spotCount, dirCount;
+	const float4* skyPixels;   // skydome image (rgb, 1), skyWidth x skyHeight; null = constant sky
+	uint32_t skyWidth, skyHeight;
 };
+
+constexpr uint32_t S_SPECULAR = 1, S_BOUNCED = 2, S_VIASPECULAR = 4, S_BOUNCEDTWICE = 8; // pathtracer.h:29-32
+constexpr uint32_t PATHIDX_BITS = 28, PATHIDX_MASK = (1u << PATHIDX_BITS) - 1;          // path word = pathIdx | flags << 28
 
 // lib/CUDA/shared_kernel_code/tools_shared.h:60-62
 __device__ __forceinline__ uint32_t WangHash( uint32_t s ) { s = (s ^ 61) ^ (s >> 16), s *= 9, s = s ^ (s >> 4), s *= 0x27d4eb2d, s = s ^ (s >> 15); return s; }
@@ -67,7 +82,7 @@ __device__ __forceinline__ uint32_t warpAppend( uint32_t* counter, bool want )
 // ---- primary rays (GPU cores: rendercore_optix7/optix/.optix.cu:66-123, RenderCore_OptixPrime_B/kernels/camera.h:40-94) ----------
 // u = (x + r0) / w, v = (y + r1) / h, P = p1 + u right + v up, D = normalize(P - pos); pinhole (aperture is not sampled).
 __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParams f, float4* __restrict__ rayO, float4* __restrict__ rayD,
-	float4* __restrict__ pathState, WaveCounters* counters )
+	float4* __restrict__ pathState, float4* __restrict__ pathInfo, WaveCounters* counters )
 {
 	const uint32_t total = f.ownTiles * TILE_PIXELS * f.samplesThisPass;
 	const uint32_t stride = gridDim.x * blockDim.x;
@@ -101,7 +116,8 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 		const float il = 1.0f / sqrtf( dx * dx + dy * dy + dz * dz );
 		rayO[slot] = make_float4( f.pos[0], f.pos[1], f.pos[2], f.epsilon );
 		rayD[slot] = make_float4( dx * il, dy * il, dz * il, 1e34f );
-		pathState[slot] = make_float4( 1.f, 1.f, 1.f, __uint_as_float( pathIdx ) );
+		pathState[slot] = make_float4( 1.f, 1.f, 1.f, 1.f );                      // throughput, postponed bsdf pdf
+		pathInfo[slot] = make_float4( __uint_as_float( pathIdx ), 0.f, 0.f, 0.f ); // pathIdx | flags << 28, normal at the previous vertex
 	}
 }
 
@@ -122,10 +138,189 @@ __device__ __forceinline__ void SafeOrigin( const float ix, const float iy, cons
 	ox = ix + rx * eps * (1 - v) + nx * eps * v, oy = iy + ry * eps * (1 - v) + ny * eps * v, oz = iz + rz * eps * (1 - v) + nz * eps * v;
 }
 
-// ---- shade (model: lib/RenderCore_PrimeRef/kernels/pathtracer.h:46-165 reduced to Lambert + one point light) ----------------------
+// ---- small vector helpers for the shade stage --------------------------------------------------------------------------------------
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 v3( const float x, const float y, const float z ) { V3 r; r.x = x, r.y = y, r.z = z; return r; }
+__device__ __forceinline__ V3 v3( const float4 a ) { return v3( a.x, a.y, a.z ); }
+__device__ __forceinline__ V3 operator+( const V3 a, const V3 b ) { return v3( a.x + b.x, a.y + b.y, a.z + b.z ); }
+__device__ __forceinline__ V3 operator-( const V3 a, const V3 b ) { return v3( a.x - b.x, a.y - b.y, a.z - b.z ); }
+__device__ __forceinline__ V3 operator*( const V3 a, const V3 b ) { return v3( a.x * b.x, a.y * b.y, a.z * b.z ); }
+__device__ __forceinline__ V3 operator*( const V3 a, const float s ) { return v3( a.x * s, a.y * s, a.z * s ); }
+__device__ __forceinline__ float dot( const V3 a, const V3 b ) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 normalize( const V3 a ) { return a * (1.0f / sqrtf( dot( a, a ) )); }
+
+// ---- lights (lib/CUDA/shared_kernel_code/lights_shared.h) ---------------------------------------------------------------------------
+// potential contribution of light i to a surface point I with normal N: the importance used to pick a light (:33-94).
+// `bary.x < 0` = implicit-connection variant: the light is taken at the given point P (an emissive hit) instead of a sampled point.
+__device__ __forceinline__ float PotentialAreaLight( const FrameParams& f, const int i, const V3 I, const V3 N, const V3 P, const V3 bary )
+{
+	const float4 c4 = __ldg( f.areaLights + i * 6 ), LN = __ldg( f.areaLights + i * 6 + 1 );
+	V3 L = P;
+	if (bary.x >= 0)
+	{
+		const float4 V0 = __ldg( f.areaLights + i * 6 + 3 ), V1 = __ldg( f.areaLights + i * 6 + 4 ), V2 = __ldg( f.areaLights + i * 6 + 5 );
+		L = v3( V0 ) * bary.x + v3( V1 ) * bary.y + v3( V2 ) * bary.z;
+	}
+	L = L - I;
+	const float att = 1.0f / dot( L, L );
+	L = normalize( L );
+	return c4.w * fmaxf( 0.0f, -dot( v3( LN ), L ) ) * fmaxf( 0.0f, dot( N, L ) ) * att;
+}
+__device__ __forceinline__ float PotentialPointLight( const FrameParams& f, const int i, const V3 I, const V3 N )
+{
+	const float4 p4 = __ldg( f.pointLights + i * 2 );
+	const V3 L = v3( p4 ) - I;
+	return p4.w * fmaxf( 0.0f, dot( N, L ) ) * (1.0f / dot( L, L )); // L is not normalised here in the reference either (:60-62)
+}
+__device__ __forceinline__ float PotentialSpotLight( const FrameParams& f, const int i, const V3 I, const V3 N )
+{
+	const float4 p4 = __ldg( f.spotLights + i * 3 ), r4 = __ldg( f.spotLights + i * 3 + 1 ), d4 = __ldg( f.spotLights + i * 3 + 2 );
+	V3 L = v3( p4 ) - I;
+	const float att = 1.0f / dot( L, L );
+	L = normalize( L );
+	const float d = (fmaxf( 0.0f, -dot( L, v3( d4 ) ) ) - r4.w) / (p4.w - r4.w); // p4.w = cos inner, r4.w = cos outer
+	return (r4.x + r4.y + r4.z) * fmaxf( 0.0f, fminf( 1.0f, d ) ) * fmaxf( 0.0f, dot( N, L ) ) * att;
+}
+__device__ __forceinline__ float PotentialDirLight( const FrameParams& f, const int i, const V3 N )
+{
+	const float4 d4 = __ldg( f.dirLights + i * 2 );
+	return d4.w * fmaxf( 0.0f, -dot( v3( d4 ), N ) );
+}
+// light k of the concatenated list area | point | spot | directional
+__device__ __forceinline__ float PotentialLight( const FrameParams& f, int k, const V3 I, const V3 N, const V3 P, const V3 bary )
+{
+	if (k < f.areaCount) return PotentialAreaLight( f, k, I, N, P, bary );
+	k -= f.areaCount;
+	if (k < f.pointCount) return PotentialPointLight( f, k, I, N );
+	k -= f.pointCount;
+	if (k < f.spotCount) return PotentialSpotLight( f, k, I, N );
+	return PotentialDirLight( f, k - f.spotCount, N );
+}
+
+// :103-120 -- probability that NEE at the previous vertex (O, normal N) would have picked area light `idx`, seen at point I.
+// The reference keeps the potentials in a fixed array of 8 (MAXISLIGHTS) and overruns it with more lights; here nothing is stored.
+__device__ float LightPickProb( const FrameParams& f, const int idx, const V3 O, const V3 N, const V3 I )
+{
+	const int lights = f.areaCount + f.pointCount + f.spotCount + f.dirCount;
+	const V3 none = v3( -1.f, -1.f, -1.f );
+	float sum = 0, mine = 0;
+	for (int k = 0; k < lights; k++)
+	{
+		const float c = PotentialLight( f, k, O, N, I, none );
+		sum += c;
+		if (k == idx) mine = c;
+	}
+	return sum <= 0 ? 0.f : mine / sum;
+}
+
+// :122-142 -- uniform point on a triangle from ONE random number (base-4 digits walk a 4-way subdivision)
+__device__ V3 RandomBarycentrics( const float r0 )
+{
+	const uint32_t uf = (uint32_t)(r0 * 4294967296.0f);
+	float ax = 1, ay = 0, bx = 0, by = 1, cx = 0, cy = 0;
+	for (int i = 0; i < 16; i++)
+	{
+		const int d = (uf >> (2 * (15 - i))) & 3;
+		float nax, nay, nbx, nby, ncx, ncy;
+		if (d == 0) nax = (bx + cx) * 0.5f, nay = (by + cy) * 0.5f, nbx = (ax + cx) * 0.5f, nby = (ay + cy) * 0.5f, ncx = (ax + bx) * 0.5f, ncy = (ay + by) * 0.5f;
+		else if (d == 1) nax = ax, nay = ay, nbx = (ax + bx) * 0.5f, nby = (ay + by) * 0.5f, ncx = (ax + cx) * 0.5f, ncy = (ay + cy) * 0.5f;
+		else if (d == 2) nax = (bx + ax) * 0.5f, nay = (by + ay) * 0.5f, nbx = bx, nby = by, ncx = (bx + cx) * 0.5f, ncy = (by + cy) * 0.5f;
+		else nax = (cx + ax) * 0.5f, nay = (cy + ay) * 0.5f, nbx = (cx + bx) * 0.5f, nby = (cy + by) * 0.5f, ncx = cx, ncy = cy;
+		ax = nax, ay = nay, bx = nbx, by = nby, cx = ncx, cy = ncy;
+	}
+	const float rx = (ax + bx + cx) * 0.3333333f, ry = (ay + by + cy) * 0.3333333f;
+	return v3( rx, ry, 1 - rx - ry );
+}
+
+// :144-234 -- pick a light by potential contribution, return the sampled point on it
+__device__ V3 RandomPointOnLight( const FrameParams& f, const float r0, float r1, const V3 I, const V3 N, float& pickProb, float& lightPdf, V3& lightColor )
+{
+	const int lights = f.areaCount + f.pointCount + f.spotCount + f.dirCount;
+	const V3 bary = RandomBarycentrics( r0 ), zero = v3( 0.f, 0.f, 0.f );
+	lightPdf = 0, pickProb = 0, lightColor = zero;
+	float sum = 0;
+	for (int k = 0; k < lights; k++) sum += PotentialLight( f, k, I, N, zero, bary );
+	if (!(sum > 0)) return v3( 1.f, 1.f, 1.f );
+	r1 *= sum;
+	int k = 0;
+	float total = 0, chosen = 0;
+	bool found = false;
+	for (int i = 0; i < lights; i++)
+	{
+		const float c = PotentialLight( f, i, I, N, zero, bary );
+		total += c;
+		if (i == 0) chosen = c;
+		if (!found && total >= r1) k = i, chosen = c, found = true;
+	}
+	pickProb = chosen / sum;
+	if (k < f.areaCount)
+	{
+		const float4 LN = __ldg( f.areaLights + k * 6 + 1 ), rad = __ldg( f.areaLights + k * 6 + 2 );
+		const float4 V0 = __ldg( f.areaLights + k * 6 + 3 ), V1 = __ldg( f.areaLights + k * 6 + 4 ), V2 = __ldg( f.areaLights + k * 6 + 5 );
+		lightColor = v3( rad );
+		const V3 P = v3( V0 ) * bary.x + v3( V1 ) * bary.y + v3( V2 ) * bary.z;
+		V3 L = I - P; // from the light to the surface point
+		const float sqDist = dot( L, L );
+		L = normalize( L );
+		const float LNdotL = dot( L, v3( LN ) );
+		lightPdf = (LNdotL > 0 && dot( L, N ) < 0) ? sqDist / (LN.w * LNdotL) : 0; // LN.w = area
+		return P;
+	}
+	k -= f.areaCount;
+	if (k < f.pointCount)
+	{
+		const float4 p4 = __ldg( f.pointLights + k * 2 ), rad = __ldg( f.pointLights + k * 2 + 1 );
+		lightColor = v3( rad ); // the reference assigns a shadowing local here (:196) and leaves the output unset; the radiance is what is meant
+		const V3 L = I - v3( p4 );
+		lightPdf = dot( L, N ) < 0 ? dot( L, L ) : 0;
+		return v3( p4 );
+	}
+	k -= f.pointCount;
+	if (k < f.spotCount)
+	{
+		const float4 p4 = __ldg( f.spotLights + k * 3 ), r4 = __ldg( f.spotLights + k * 3 + 1 ), d4 = __ldg( f.spotLights + k * 3 + 2 );
+		V3 L = I - v3( p4 );
+		const float sqDist = dot( L, L );
+		L = normalize( L );
+		const float d = (fmaxf( 0.0f, dot( L, v3( d4 ) ) ) - r4.w) / (p4.w - r4.w);
+		const float LNdotL = fminf( 1.0f, d );
+		lightPdf = (LNdotL > 0 && dot( L, N ) < 0) ? sqDist / LNdotL : 0;
+		lightColor = v3( r4 );
+		return v3( p4 );
+	}
+	k -= f.spotCount;
+	const float4 d4 = __ldg( f.dirLights + k * 2 ), rad = __ldg( f.dirLights + k * 2 + 1 );
+	lightColor = v3( rad );
+	lightPdf = dot( v3( d4 ), N ) < 0 ? 1.f : 0.f;
+	return I - v3( d4 ) * 1000.0f;
+}
+
+// tools_shared.h:185-192 (formulas by Paul Debevec): nearest texel of the equirectangular skydome
+__device__ __forceinline__ V3 SampleSkydome( const FrameParams& f, const V3 D )
+{
+	if (!f.skyPixels) return v3( f.sky[0], f.sky[1], f.sky[2] );
+	const uint32_t u = (uint32_t)((float)f.skyWidth * 0.5f * (1.0f + atan2f( D.x, -D.z ) * INVPI));
+	const uint32_t v = (uint32_t)((float)f.skyHeight * acosf( D.y ) * INVPI);
+	const uint32_t idx = u + v * f.skyWidth;
+	return idx < f.skyWidth * f.skyHeight ? v3( __ldg( f.skyPixels + idx ) ) : v3( 0.f, 0.f, 0.f );
+}
+
+// core_settings.h:190-192 (CLAMPINTENSITY) and FIXNAN_FLOAT3
+__device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
+{
+	const float m = fmaxf( c.x, fmaxf( c.y, c.z ) );
+	if (m > clampValue) c = c * (clampValue / m);
+	if (!isfinite( c.x + c.y + c.z )) c = v3( 0.f, 0.f, 0.f );
+	return c;
+}
+
+// ---- shade (lib/rendercore_optix7/kernels/pathtracer.h:54-240, BSDF = lib/sharedBSDFs/lambert.h without transmission) -------------
+// Path state: rayO/rayD (the extension ray), pathState = (throughput rgb, postponed bsdf pdf), pathInfo = (pathIdx | flags << 28,
+// normal at the previous vertex).  One thread per path; new extension / shadow rays are compacted with warp-aggregated appends.
 __global__ void __launch_bounds__( 128 ) shadeKernel( const FrameParams f, const int pathLength, const int maxPathLength,
-	const float4* __restrict__ rayO, const float4* __restrict__ rayD, const float4* __restrict__ pathState, const float4* __restrict__ hits,
-	float4* __restrict__ rayOout, float4* __restrict__ rayDout, float4* __restrict__ pathStateOut,
+	const float4* __restrict__ rayO, const float4* __restrict__ rayD, const float4* __restrict__ pathState, const float4* __restrict__ pathInfo,
+	const float4* __restrict__ hits,
+	float4* __restrict__ rayOout, float4* __restrict__ rayDout, float4* __restrict__ pathStateOut, float4* __restrict__ pathInfoOut,
 	float4* __restrict__ conO, float4* __restrict__ conD, float4* __restrict__ conE,
 	const float4* __restrict__ shade, const float4* __restrict__ instShade, const float4* __restrict__ materials,
 	float4* accumulator, WaveCounters* counters )
@@ -136,19 +331,24 @@ __global__ void __launch_bounds__( 128 ) shadeKernel( const FrameParams f, const
 	{
 		const uint32_t job = base + (threadIdx.x & 31);
 		bool wantShadow = false, wantExt = false;
-		float sox = 0, soy = 0, soz = 0, lx = 0, ly = 0, lz = 0, ldist = 0, ex = 0, ey = 0, ez = 0;
-		float eox = 0, eoy = 0, eoz = 0, rx = 0, ry = 0, rz = 0, tx = 0, ty = 0, tz = 0;
-		uint32_t pathIdx = 0, pixelIdx = 0;
+		V3 so = v3( 0.f, 0.f, 0.f ), sl = so, se = so, eo = so, er = so, et = so, en = so;
+		float sdist = 0, epdf = 0;
+		uint32_t pathIdx = 0, pixelIdx = 0, flags = 0;
 		if (job < count)
 		{
-			const float4 O4 = __ldg( rayO + job ), D4 = __ldg( rayD + job ), T4 = __ldg( pathState + job ), hit = __ldg( hits + job );
-			pathIdx = __float_as_uint( T4.w ), pixelIdx = pathIdx % f.pixelCount;
+			const float4 O4 = __ldg( rayO + job ), D4 = __ldg( rayD + job ), T4 = __ldg( pathState + job ), P4 = __ldg( pathInfo + job ), hit = __ldg( hits + job );
+			pathIdx = __float_as_uint( P4.x ) & PATHIDX_MASK, flags = __float_as_uint( P4.x ) >> PATHIDX_BITS, pixelIdx = pathIdx % f.pixelCount;
 			const int prim = (int)__float_as_uint( hit.z );
+			const V3 D = v3( D4 ), O = v3( O4 ), lastN = v3( P4.y, P4.z, P4.w );
+			V3 throughput = v3( T4 );
+			const float bsdfPdf = T4.w;
 			float* px = reinterpret_cast<float*>( accumulator + pixelIdx );
+			if (pathLength == 1) atomicAdd( px + 3, prim < 0 ? 10000.f : hit.w ); // depth for the DOF / filter passes (pathtracer.h:74)
 			if (prim < 0)
 			{
-				// sky (the reference samples the skydome, pathtracer.h:77-82; this core keeps a constant sky colour)
-				atomicAdd( px, T4.x * f.sky[0] ), atomicAdd( px + 1, T4.y * f.sky[1] ), atomicAdd( px + 2, T4.z * f.sky[2] );
+				// the path left the scene: skydome (pathtracer.h:77-84)
+				const V3 c = ClampAndFix( throughput * SampleSkydome( f, D ) * (1.0f / bsdfPdf), f.clampValue );
+				atomicAdd( px, c.x ), atomicAdd( px + 1, c.y ), atomicAdd( px + 2, c.z );
 			}
 			else
 			{
@@ -158,61 +358,129 @@ __global__ void __launch_bounds__( 128 ) shadeKernel( const FrameParams f, const
 				const float4 m0 = __ldg( instShade + inst * 4 ), m1 = __ldg( instShade + inst * 4 + 1 ), m2 = __ldg( instShade + inst * 4 + 2 ),
 							 info = __ldg( instShade + inst * 4 + 3 );
 				const float4 sh = __ldg( shade + __float_as_uint( info.x ) + prim );
-				// world-space geometric normal: normalize( transform.TransformVector( N ) ) (bvh.cpp:616-619)
-				float nx = m0.x * sh.x + m0.y * sh.y + m0.z * sh.z, ny = m1.x * sh.x + m1.y * sh.y + m1.z * sh.z, nz = m2.x * sh.x + m2.y * sh.y + m2.z * sh.z;
-				const float nl = 1.0f / sqrtf( nx * nx + ny * ny + nz * nz );
-				nx *= nl, ny *= nl, nz *= nl;
-				if (D4.x * nx + D4.y * ny + D4.z * nz > 0) nx = -nx, ny = -ny, nz = -nz; // faceDir (pathtracer.h:117-118)
+				// world-space geometric normal: normalize( transform.TransformVector( N ) ) (bvh.cpp:616-619); also stands in for the
+				// interpolated and the normal-mapped normal (iN, fN) of GetShadingData
+				const V3 N = normalize( v3( m0.x * sh.x + m0.y * sh.y + m0.z * sh.z, m1.x * sh.x + m1.y * sh.y + m1.z * sh.z, m2.x * sh.x + m2.y * sh.y + m2.z * sh.z ) );
 				const uint32_t mat = __float_as_uint( sh.w );
-				float cr = 0.8f, cg = 0.8f, cb = 0.8f;
-				if (mat < f.materialCount) { const float4 c = __ldg( materials + mat ); cr = c.x, cg = c.y, cb = c.z; }
-				const float ix = O4.x + hit.w * D4.x, iy = O4.y + hit.w * D4.y, iz = O4.z + hit.w * D4.z;
-				// next event estimation towards the point light (pathtracer.h:121-145)
-				if (f.hasLight)
+				V3 color = v3( 0.8f, 0.8f, 0.8f );
+				float roughness = 1.0f;
+				if (mat < f.materialCount) { const float4 c = __ldg( materials + mat ); color = v3( c ), roughness = c.w; }
+				const V3 I = O + D * hit.w;
+				if (color.x > 1.0f || color.y > 1.0f || color.z > 1.0f)
 				{
-					float Lx = f.lightPos[0] - ix, Ly = f.lightPos[1] - iy, Lz = f.lightPos[2] - iz;
-					const float d2 = Lx * Lx + Ly * Ly + Lz * Lz, dist = sqrtf( d2 ), id = 1.0f / dist;
-					Lx *= id, Ly *= id, Lz *= id;
-					const float NdotL = Lx * nx + Ly * ny + Lz * nz;
-					if (NdotL > 0 && dist > 4 * f.epsilon)
+					// the path ends on a light (pathtracer.h:120-148); lights are single sided
+					const float DdotNL = -dot( D, N );
+					if (DdotNL > 0)
 					{
-						const float s = NdotL * INVPI / d2;
-						ex = T4.x * cr * f.lightRadiance[0] * s, ey = T4.y * cg * f.lightRadiance[1] * s, ez = T4.z * cb * f.lightRadiance[2] * s;
-						SafeOrigin( ix, iy, iz, Lx, Ly, Lz, nx, ny, nz, f.epsilon, sox, soy, soz );
-						lx = Lx, ly = Ly, lz = Lz, ldist = dist - 2 * f.epsilon;
-						wantShadow = true;
+						V3 c = throughput * color; // (the reference drops the throughput on the specular branch, :129)
+						if (pathLength > 1 && !(flags & S_SPECULAR))
+						{
+							// the previous vertex did NEE: weigh this implicit connection against it (MIS)
+							int ltri = -1;
+							float area = 0;
+							for (int i = 0; i < f.areaCount; i++)
+								if (__float_as_int( __ldg( f.areaLights + i * 6 + 3 ).w ) == prim && __float_as_int( __ldg( f.areaLights + i * 6 + 4 ).w ) == (int)inst)
+									ltri = i, area = __ldg( f.areaLights + i * 6 + 1 ).w;
+							const float lightPdf = ltri >= 0 ? (hit.w * hit.w) / (DdotNL * area) : 0.f;    // CalculateLightPDF, lights_shared.h:96-99
+							const float pickProb = ltri >= 0 ? LightPickProb( f, ltri, O, lastN, I ) : 0.f;
+							const float w = bsdfPdf + lightPdf * pickProb;
+							c = w > 0 ? c * (1.0f / w) : v3( 0.f, 0.f, 0.f );
+						}
+						c = ClampAndFix( c, f.clampValue );
+						atomicAdd( px, c.x ), atomicAdd( px + 1, c.y ), atomicAdd( px + 2, c.z );
 					}
 				}
-				// diffuse bounce: cosine-weighted direction, Lambert throughput = albedo (bsdf * cos / pdf)
-				if (pathLength < maxPathLength)
+				else
 				{
-					uint32_t seed = WangHash( pathIdx * 17 + f.R0 + (uint32_t)pathLength * 91771u ); // pathtracer.h:155; rendercore.cpp (R0 per bounce)
-					const float r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
-					const float term1 = TWOPI * r0, term2 = sqrtf( 1 - r1 );
-					float sn, cs;
-					__sincosf( term1, &sn, &cs );
-					Tangent2World( cs * term2, sn * term2, sqrtf( r1 ), nx, ny, nz, rx, ry, rz );
-					const float rl = 1.0f / sqrtf( rx * rx + ry * ry + rz * rz );
-					rx *= rl, ry *= rl, rz *= rl;
-					SafeOrigin( ix, iy, iz, rx, ry, rz, nx, ny, nz, f.epsilon, eox, eoy, eoz );
-					tx = T4.x * cr, ty = T4.y * cg, tz = T4.z * cb;
-					wantExt = true;
+					if (roughness <= 0.001f) flags |= S_SPECULAR; else flags &= ~S_SPECULAR; // pathtracer.h:151
+					uint32_t seed = WangHash( pathIdx * 17 + f.R0 + (uint32_t)pathLength * 91771u ); // :154; R0 changes per bounce (rendercore.cpp:716)
+					const float faceDir = dot( D, N ) > 0 ? -1.f : 1.f;
+					const V3 fN = N * faceDir;
+					throughput = throughput * (1.0f / bsdfPdf); // postponed pdf (:161)
+					// next event estimation (:163-199)
+					if (!(flags & S_SPECULAR) && f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0)
+					{
+						const float r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
+						float pickProb, lightPdf;
+						V3 lightColor;
+						V3 L = RandomPointOnLight( f, r0, r1, I, fN, pickProb, lightPdf, lightColor ) - I;
+						const float dist = sqrtf( dot( L, L ) );
+						L = L * (1.0f / dist);
+						const float NdotL = dot( L, fN );
+						if (NdotL > 0 && lightPdf > 0)
+						{
+							// EvaluateBSDF (lambert.h:58-69): color / pi, pdf = |cos| / pi; scaled by the chance of a diffuse bounce (:186)
+							const float lbsdfPdf = fabsf( NdotL ) * INVPI;
+							if (lbsdfPdf > 0)
+							{
+								se = ClampAndFix( throughput * color * lightColor * (INVPI * roughness * (NdotL / (pickProb * lightPdf + lbsdfPdf))), f.clampValue );
+								SafeOrigin( I.x, I.y, I.z, L.x, L.y, L.z, fN.x, fN.y, fN.z, f.epsilon, so.x, so.y, so.z );
+								sl = L, sdist = dist - 2 * f.epsilon;
+								wantShadow = true;
+							}
+						}
+					}
+					// extension (:201-239)
+					const bool enough = (f.bounceCap == 1 && (flags & S_BOUNCED)) || (f.bounceCap == 2 && (flags & S_BOUNCEDTWICE));
+					if (!enough && pathLength < maxPathLength)
+					{
+						const float r3 = RandomFloat( seed ), r4 = RandomFloat( seed );
+						// SampleBSDF (lambert.h:71-123) with TRANSMISSION = 0: a specular reflection with probability 1 - roughness
+						const float pReflect = 1 - roughness;
+						V3 R, bsdf;
+						float newPdf = 1;
+						bool specular = true;
+						if (r3 < pReflect)
+						{
+							R = D - fN * (2 * dot( D, fN ));
+							bsdf = color * (1.0f / fabsf( dot( fN, R ) ));
+						}
+						else
+						{
+							const float r5 = (r3 - pReflect) / (1 - pReflect);
+							const float term1 = TWOPI * r5, term2 = sqrtf( 1 - r4 ); // DiffuseReflectionCosWeighted, tools_shared.h:250-256
+							float sn, cs;
+							__sincosf( term1, &sn, &cs );
+							Tangent2World( cs * term2, sn * term2, sqrtf( r4 ), fN.x, fN.y, fN.z, R.x, R.y, R.z );
+							R = normalize( R );
+							newPdf = fmaxf( 0.0f, dot( R, fN ) ) * INVPI;
+							specular = false;
+							bsdf = color * INVPI;
+						}
+						if (dot( fN, R ) <= 0) newPdf = 0;
+						if (newPdf >= 1e-4f) // also false for NaN (:222)
+						{
+							if (specular) flags |= S_SPECULAR;
+							// Russian roulette from the second diffuse vertex on (:225-227)
+							const float p = (!f.roulette || (flags & S_SPECULAR) || !(flags & S_BOUNCED)) ? 1.f : fminf( 1.0f, fmaxf( fmaxf( bsdf.x, bsdf.y ), bsdf.z ) );
+							if (!(p < RandomFloat( seed )))
+							{
+								throughput = throughput * (1.0f / p);
+								if (!(flags & S_SPECULAR)) flags |= (flags & S_BOUNCED) ? S_BOUNCEDTWICE : S_BOUNCED; else flags |= S_VIASPECULAR;
+								SafeOrigin( I.x, I.y, I.z, R.x, R.y, R.z, fN.x, fN.y, fN.z, f.epsilon, eo.x, eo.y, eo.z );
+								if (!isfinite( throughput.x + throughput.y + throughput.z )) throughput = v3( 0.f, 0.f, 0.f );
+								er = R, en = fN, et = throughput * bsdf * fabsf( dot( fN, R ) ), epdf = newPdf;
+								wantExt = true;
+							}
+						}
+					}
 				}
 			}
 		}
 		const uint32_t sslot = warpAppend( &counters[pathLength].shadowRays, wantShadow );
 		if (wantShadow)
 		{
-			conO[sslot] = make_float4( sox, soy, soz, f.epsilon );
-			conD[sslot] = make_float4( lx, ly, lz, ldist );
-			conE[sslot] = make_float4( ex, ey, ez, __uint_as_float( pixelIdx ) );
+			conO[sslot] = make_float4( so.x, so.y, so.z, f.epsilon );
+			conD[sslot] = make_float4( sl.x, sl.y, sl.z, sdist );
+			conE[sslot] = make_float4( se.x, se.y, se.z, __uint_as_float( pixelIdx ) );
 		}
 		const uint32_t eslot = warpAppend( &counters[pathLength + 1].extensionRays, wantExt );
 		if (wantExt)
 		{
-			rayOout[eslot] = make_float4( eox, eoy, eoz, f.epsilon );
-			rayDout[eslot] = make_float4( rx, ry, rz, 1e34f );
-			pathStateOut[eslot] = make_float4( tx, ty, tz, __uint_as_float( pathIdx ) );
+			rayOout[eslot] = make_float4( eo.x, eo.y, eo.z, f.epsilon );
+			rayDout[eslot] = make_float4( er.x, er.y, er.z, 1e34f );
+			pathStateOut[eslot] = make_float4( et.x, et.y, et.z, epdf );
+			pathInfoOut[eslot] = make_float4( __uint_as_float( pathIdx | (flags << PATHIDX_BITS) ), en.x, en.y, en.z );
 		}
 	}
 }
@@ -235,18 +503,21 @@ struct WavefrontState {
 	int shardIndex = 0, shardCount = 1, sampleOffset = 0, jitter = 1;
 	uint32_t pathsPerPass = 32u << 20;
 	uint32_t capacity = 0; // rays per buffer
-	DeviceBuffer rayO[2], rayD[2], state[2], hits, conO, conD, conE, counters, accumOwn, frame, materials;
+	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO, conD, conE, counters, accumOwn, frame, materials, lights, skyImage;
 	float4* accumExternal = nullptr;
 	uint32_t materialCount = 0;
-	float lightPos[3] = { 0, 0, 0 }, lightRadiance[3] = { 0, 0, 0 }, sky[3] = { 0, 0, 0 };
-	bool hasLight = false;
+	float sky[3] = { 0, 0, 0 }, clampValue = 10.0f; // clampValue: the RenderSystem's default (rendersystem.cpp:228-233 sends it every frame)
+	int lightCounts[4] = { 0, 0, 0, 0 };             // area, point, spot, directional; packed in this order in `lights`
+	uint32_t skyWidth = 0, skyHeight = 0;
+	int bounceCap = 0, roulette = 1;
 	uint32_t samplesTaken = 0, frameCounter = 0;
 	int probeX = -1, probeY = -1;
 	cudaEvent_t ev[2 * (3 * MAX_PATH_LENGTH + 2)] = {};
 	float4* accumulator() { return accumExternal ? accumExternal : (float4*)accumOwn.ptr; }
 	~WavefrontState()
 	{
-		DeviceBuffer* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &state[0], &state[1], &hits, &conO, &conD, &conE, &counters, &accumOwn, &frame, &materials };
+		DeviceBuffer* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &state[0], &state[1], &info[0], &info[1], &hits, &conO, &conD, &conE, &counters,
+			&accumOwn, &frame, &materials, &lights, &skyImage };
 		for (DeviceBuffer* b : all) b->release();
 		for (cudaEvent_t e : ev) if (e) cudaEventDestroy( e );
 	}
@@ -269,6 +540,9 @@ int RenderCore::SettingWavefront( const char* name, float value )
 	if (!strcmp( name, "shardIndex" )) { if (v < 0 || v >= w->shardCount) return fail( "Setting shardIndex: 0..shardCount-1 (set shardCount first)" ); w->shardIndex = v; return 0; }
 	if (!strcmp( name, "sampleOffset" )) { if (v < 0) return fail( "Setting sampleOffset: >= 0" ); w->sampleOffset = v; return 0; }
 	if (!strcmp( name, "jitter" )) { w->jitter = value >= 0.5f; return 0; }
+	if (!strcmp( name, "clampValue" )) { if (!(value > 0)) return fail( "Setting clampValue: > 0" ); w->clampValue = value; return 0; }
+	if (!strcmp( name, "russianRoulette" )) { w->roulette = value >= 0.5f; return 0; }
+	if (!strcmp( name, "diffuseBounceCap" )) { if (v < 0 || v > 2) return fail( "Setting diffuseBounceCap: 0 (off), 1 or 2" ); w->bounceCap = v; return 0; }
 	if (!strcmp( name, "pathsPerPass" )) { if (value < 1024) return fail( "Setting pathsPerPass: >= 1024" ); w->pathsPerPass = (uint32_t)value; return 0; }
 	return fail( std::string( "Setting: unknown key " ) + name );
 }
@@ -295,24 +569,62 @@ int RenderCore::SetAccumulatorBuffer( void* devicePtr )
 	return 0;
 }
 
-int RenderCore::SetPointLight( const float* pos, const float* radiance )
+// CoreAPI_Base::SetLights (core_api_base.h:102-105): the four arrays in the reference's host layouts (common_classes.h:275-345:
+// CoreLightTri 96 B, CorePointLight 32 B, CoreSpotLight 48 B, CoreDirectionalLight 32 B), copied as float4 records
+int RenderCore::SetLights( const void* area, int nArea, const void* point, int nPoint, const void* spot, int nSpot, const void* dir, int nDir )
 {
 	WavefrontState* w = state( wf );
-	if (!pos || !radiance) { w->hasLight = false; return 0; }
-	memcpy( w->lightPos, pos, 12 ), memcpy( w->lightRadiance, radiance, 12 );
-	w->hasLight = true;
+	if (nArea < 0 || nPoint < 0 || nSpot < 0 || nDir < 0 || (nArea && !area) || (nPoint && !point) || (nSpot && !spot) || (nDir && !dir))
+		return fail( "SetLights: bad arguments" );
+	const size_t bytes[4] = { (size_t)nArea * 96, (size_t)nPoint * 32, (size_t)nSpot * 48, (size_t)nDir * 32 };
+	const void* src[4] = { area, point, spot, dir };
+	std::vector<char> packed( bytes[0] + bytes[1] + bytes[2] + bytes[3] + 16 );
+	size_t off = 0;
+	for (int k = 0; k < 4; k++) { if (bytes[k]) memcpy( packed.data() + off, src[k], bytes[k] ); off += bytes[k]; }
+	cudaError_t e;
+	if ((e = w->lights.reserve( packed.size(), false, stream )) != cudaSuccess) return fail( "lights", e );
+	if ((e = cudaMemcpyAsync( w->lights.ptr, packed.data(), packed.size(), cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "lights upload", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "lights sync", e );
+	w->lightCounts[0] = nArea, w->lightCounts[1] = nPoint, w->lightCounts[2] = nSpot, w->lightCounts[3] = nDir;
 	return 0;
 }
 
+// headless shortcut: exactly one point light (energy = r + g + b as the RenderSystem computes it, host_light.cpp), or none
+int RenderCore::SetPointLight( const float* pos, const float* radiance )
+{
+	if (!pos || !radiance) return SetLights( nullptr, 0, nullptr, 0, nullptr, 0, nullptr, 0 );
+	const float rec[8] = { pos[0], pos[1], pos[2], radiance[0] + radiance[1] + radiance[2], radiance[0], radiance[1], radiance[2], 0 };
+	return SetLights( nullptr, 0, rec, 1, nullptr, 0, nullptr, 0 );
+}
+
+// constant sky
 int RenderCore::SetSky( const float* radiance )
 {
 	if (!radiance) return fail( "SetSky: null" );
-	memcpy( state( wf )->sky, radiance, 12 );
+	WavefrontState* w = state( wf );
+	memcpy( w->sky, radiance, 12 );
+	w->skyWidth = w->skyHeight = 0;
 	return 0;
 }
 
-// CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each; the diffuse stage keeps color.value
-// (offset 0, common_classes.h:177-238)
+// CoreAPI_Base::SetSkyData (core_api_base.h:106): float3 pixels[width * height], equirectangular (tools_shared.h:185-192)
+int RenderCore::SetSkyData( const float* rgb, int width, int height )
+{
+	WavefrontState* w = state( wf );
+	if (!rgb || width <= 0 || height <= 0) return fail( "SetSkyData: bad arguments" );
+	const size_t n = (size_t)width * height;
+	std::vector<float> px( n * 4 );
+	for (size_t i = 0; i < n; i++) px[i * 4] = rgb[i * 3], px[i * 4 + 1] = rgb[i * 3 + 1], px[i * 4 + 2] = rgb[i * 3 + 2], px[i * 4 + 3] = 1.0f;
+	cudaError_t e;
+	if ((e = w->skyImage.reserve( n * 16, false, stream )) != cudaSuccess) return fail( "sky image", e );
+	if ((e = cudaMemcpyAsync( w->skyImage.ptr, px.data(), n * 16, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "sky upload", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "sky sync", e );
+	w->skyWidth = (uint32_t)width, w->skyHeight = (uint32_t)height;
+	return 0;
+}
+
+// CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each; the Lambert stage keeps color.value
+// (offset 0) and roughness.value (offset 304 = 4 Vec3Values + flags/pad + absorption + 3 ScalarValues; common_classes.h:177-238)
 int RenderCore::SetMaterials( const void* coreMaterials, int count )
 {
 	WavefrontState* w = state( wf );
@@ -321,7 +633,7 @@ int RenderCore::SetMaterials( const void* coreMaterials, int count )
 	for (int i = 0; i < count; i++)
 	{
 		memcpy( &colors[(size_t)i * 4], (const char*)coreMaterials + (size_t)i * 688, 12 );
-		colors[(size_t)i * 4 + 3] = 0;
+		memcpy( &colors[(size_t)i * 4 + 3], (const char*)coreMaterials + (size_t)i * 688 + 304, 4 );
 	}
 	return SetMaterialColors( colors.data(), count );
 }
@@ -356,13 +668,19 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	FrameParams f;
 	memset( &f, 0, sizeof( f ) );
 	for (int a = 0; a < 3; a++) f.pos[a] = vp[a], f.p1[a] = vp[3 + a], f.right[a] = vp[6 + a] - vp[3 + a], f.up[a] = vp[9 + a] - vp[3 + a];
-	memcpy( f.lightPos, w->lightPos, 12 ), memcpy( f.lightRadiance, w->lightRadiance, 12 ), memcpy( f.sky, w->sky, 12 );
+	memcpy( f.sky, w->sky, 12 );
+	f.clampValue = w->clampValue, f.bounceCap = (uint32_t)w->bounceCap, f.roulette = (uint32_t)w->roulette;
+	f.areaCount = w->lightCounts[0], f.pointCount = w->lightCounts[1], f.spotCount = w->lightCounts[2], f.dirCount = w->lightCounts[3];
+	f.areaLights = (const float4*)w->lights.ptr, f.pointLights = f.areaLights + f.areaCount * 6, f.spotLights = f.pointLights + f.pointCount * 2;
+	f.dirLights = f.spotLights + f.spotCount * 3;
+	const bool anyLight = f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0;
+	if (w->skyWidth) f.skyPixels = (const float4*)w->skyImage.ptr, f.skyWidth = w->skyWidth, f.skyHeight = w->skyHeight;
 	f.epsilon = epsilon, f.width = (uint32_t)w->width, f.height = (uint32_t)w->height, f.pixelCount = f.width * f.height;
 	f.tilesX = (f.width + TILE_W - 1) / TILE_W, f.tilesY = (f.height + TILE_H - 1) / TILE_H;
 	const uint32_t nTiles = f.tilesX * f.tilesY;
 	f.shardIndex = (uint32_t)w->shardIndex, f.shardCount = (uint32_t)w->shardCount;
 	f.ownTiles = nTiles > f.shardIndex ? (nTiles - f.shardIndex + f.shardCount - 1) / f.shardCount : 0;
-	f.hasLight = w->hasLight, f.jitter = (uint32_t)w->jitter, f.materialCount = w->materialCount;
+	f.jitter = (uint32_t)w->jitter, f.materialCount = w->materialCount;
 	f.probePixel = (w->probeX >= 0 && w->probeY >= 0 && w->probeX < w->width && w->probeY < w->height) ? w->probeX + w->probeY * w->width : -1;
 	const size_t px = (size_t)f.pixelCount;
 	if (converge == 1 || w->samplesTaken == 0)
@@ -378,7 +696,8 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	const uint32_t cap = perSample * samplesPerPass + 32;
 	if (cap > w->capacity)
 	{
-		DeviceBuffer* bufs[] = { &w->rayO[0], &w->rayO[1], &w->rayD[0], &w->rayD[1], &w->state[0], &w->state[1], &w->hits, &w->conO, &w->conD, &w->conE };
+		DeviceBuffer* bufs[] = { &w->rayO[0], &w->rayO[1], &w->rayD[0], &w->rayD[1], &w->state[0], &w->state[1], &w->info[0], &w->info[1], &w->hits,
+			&w->conO, &w->conD, &w->conE };
 		for (DeviceBuffer* b : bufs) if ((e = b->reserve( (size_t)cap * 16, false, stream )) != cudaSuccess) return fail( "path buffers", e );
 		w->capacity = cap;
 	}
@@ -390,17 +709,18 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	for (uint32_t s0 = 0; s0 < (uint32_t)w->spp; s0 += samplesPerPass)
 	{
 		f.samplesThisPass = (uint32_t)w->spp - s0 < samplesPerPass ? (uint32_t)w->spp - s0 : samplesPerPass;
-		// pathIdx = pixel + sample * pixelCount must stay below 2^32: the sample index wraps after `period` samples and the wrap
+		// pathIdx = pixel + sample * pixelCount must stay below 2^28 (the path word keeps 4 flag bits): the sample index wraps after `period` samples and the wrap
 		// count goes into the salt instead ("samplesTaken * 7907 + pathLength * 91771" in the reference's shade call)
 		const uint32_t globalSample = (uint32_t)w->sampleOffset + w->samplesTaken + s0;
-		uint32_t period = 0xffffffffu / f.pixelCount - (uint32_t)w->spp;
-		if (period < 1 || period > 0x7fffffffu) period = 1;
+		if ((uint64_t)f.pixelCount * (uint64_t)w->spp > PATHIDX_MASK) return fail( "Render: width * height * spp exceeds 2^28 path indices" );
+		const uint32_t period = PATHIDX_MASK / f.pixelCount - (uint32_t)w->spp + 1;
 		f.sampleBase = globalSample % period;
 		f.R0 = (globalSample / period + 1) * 7907u;
 		if ((e = cudaMemsetAsync( dCounters, 0, sizeof( WaveCounters ) * (MAX_PATH_LENGTH + 2), stream )) != cudaSuccess) return fail( "counter clear", e );
 		const uint32_t paths = perSample * f.samplesThisPass;
 		if (!paths) continue;
-		generateEyeRaysKernel<<<smCount * 4, 256, 0, stream>>>( f, (float4*)w->rayO[0].ptr, (float4*)w->rayD[0].ptr, (float4*)w->state[0].ptr, dCounters );
+		generateEyeRaysKernel<<<smCount * 4, 256, 0, stream>>>( f, (float4*)w->rayO[0].ptr, (float4*)w->rayD[0].ptr, (float4*)w->state[0].ptr, (float4*)w->info[0].ptr,
+			dCounters );
 		stats.kernelLaunches++;
 		int in = 0;
 		cudaEvent_t* ev = w->ev + 2;
@@ -411,12 +731,12 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 			if (TraceClosestDevice( w->rayO[in].ptr, w->rayD[in].ptr, (int)paths, w->hits.ptr, &dCounters[len].extensionRays )) return 1;
 			cudaEventRecord( ev[1], stream );
 			shadeKernel<<<smCount * 8, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
-				(const float4*)w->state[in].ptr, (const float4*)w->hits.ptr, (float4*)w->rayO[out].ptr, (float4*)w->rayD[out].ptr, (float4*)w->state[out].ptr,
-				(float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)instShadePool.ptr,
+				(const float4*)w->state[in].ptr, (const float4*)w->info[in].ptr, (const float4*)w->hits.ptr, (float4*)w->rayO[out].ptr, (float4*)w->rayD[out].ptr,
+				(float4*)w->state[out].ptr, (float4*)w->info[out].ptr, (float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)instShadePool.ptr,
 				(const float4*)w->materials.ptr, w->accumulator(), dCounters );
 			stats.kernelLaunches++;
 			cudaEventRecord( ev[2], stream );
-			if (w->hasLight)
+			if (anyLight)
 			{
 				if (TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), &dCounters[len].shadowRays )) return 1;
 			}

@@ -5,7 +5,7 @@ import pytest
 
 import cases
 import wavefront_ref
-from lighthouse2_b200 import core, scenes
+from lighthouse2_b200 import core, lights, scenes
 
 pytestmark = pytest.mark.gpu
 
@@ -48,7 +48,10 @@ def test_frame_matches_cpu_restatement():
     rc.Render(view, converge=1)
     acc = rc.ReadAccumulator()[..., :3]
     port = cases.load_oracle(dict(case, rays=None), "port")
-    ref = wavefront_ref.render(port, case["meshes"], case["instances"], view, w, h, light=LIGHT, sky=SKY, max_path_length=4)
+    ref4 = wavefront_ref.render(port, case["meshes"], case["instances"], view, w, h, light=LIGHT, sky=SKY, max_path_length=4)
+    ref = ref4[..., :3]
+    depth = rc.ReadAccumulator()[..., 3]
+    assert np.allclose(depth, ref4[..., 3], rtol=1e-5)  # primary hit distance (10000 on a miss), pathtracer.h:74
     mean = float(ref.mean())
     rmse = float(np.sqrt(np.mean((acc - ref) ** 2)))
     big = np.abs(acc - ref).max(axis=2) > 0.01 * mean
@@ -157,3 +160,99 @@ def test_probe_reports_primary_hit():
     assert st["probedTriid"] == prim[0] and st["probedInstid"] == inst[0]
     assert abs(st["probedDist"] - t[0]) <= 1e-5 * t[0]
     rc.Shutdown()
+
+
+def _lit_scene():
+    """_scene() plus an emissive quad above it; materials: 0 grey diffuse, 1 red glossy, 2 mirror, 3 emitter."""
+    case = _scene()
+    quad = np.array([[[-0.4, 0, -0.3], [0.4, 0, -0.3], [0.4, 0, 0.3]], [[-0.4, 0, -0.3], [0.4, 0, 0.3], [-0.4, 0, 0.3]]], np.float32)
+    Mq = np.eye(4, dtype=np.float32).reshape(16)
+    Mq[[3, 7, 11]] = (0.1, 1.6, 0.0)
+    case["meshes"] = case["meshes"] + [quad]
+    case["instances"] = case["instances"] + [(2, Mq)]
+    grid, sph = case["meshes"][0], case["meshes"][1]
+    pm = [((np.arange(len(grid)) // 2) % 5 == 0).astype(np.uint32),          # every fifth quad of the floor is glossy red
+          np.where((np.arange(len(sph)) // 7) % 3 == 0, 2, 0).astype(np.uint32),  # mirror bands on the spheres
+          np.full(len(quad), 3, np.uint32)]
+    mats = np.array([[0.8, 0.8, 0.8, 1.0], [0.9, 0.2, 0.15, 0.3], [0.95, 0.95, 0.95, 0.0], [12.0, 11.0, 10.0, 1.0]], np.float32)
+    world = quad + np.array([0.1, 1.6, 0.0], np.float32)
+    n = np.cross(world[0, 1] - world[0, 0], world[0, 2] - world[0, 0])
+    assert n[1] < 0, "the emitter must face down"
+    area = lights.stack([lights.area_light(world[i, 0], world[i, 1], world[i, 2], mats[3, :3], i, 4) for i in range(2)], 24)
+    point = lights.stack([lights.point_light((0.5, 3.0, -1.0), (20.0, 18.0, 15.0))], 8)
+    spot = lights.stack([lights.spot_light((-1.5, 2.0, -1.0), (0.6, -0.8, 0.4), 0.95, 0.8, (30.0, 30.0, 40.0))], 12)
+    direc = lights.stack([lights.directional_light((0.3, -1.0, 0.2), (0.5, 0.45, 0.4))], 8)
+    rng = np.random.default_rng(11)
+    sky = (rng.random((8, 16, 3)) * np.array([0.3, 0.4, 0.6])).astype(np.float32)
+    return dict(case=case, prim_materials=pm, materials=mats, area=area, point=point, spot=spot, dir=direc, sky=sky)
+
+
+def _lit_core(sc, w, h, spp=1, max_len=5, **settings):
+    case = sc["case"]
+    rc = core.RenderCoreB200(0)
+    for i, m in enumerate(case["meshes"]):
+        rc.SetGeometry(i, m, core.core_tris(m, sc["prim_materials"][i]))
+    for i, (mesh, mat) in enumerate(case["instances"]):
+        rc.SetInstance(i, mesh, mat)
+    rc.SetInstance(len(case["instances"]), -1)
+    rc.UpdateToplevel()
+    rc.SetTarget(w, h, spp)
+    rc.SetMaterialColors(sc["materials"])
+    rc.SetLights(sc["area"], sc["point"], sc["spot"], sc["dir"])
+    rc.SetSkyData(sc["sky"])
+    rc.Setting("maxPathLength", max_len)
+    rc.Setting("jitter", 0)
+    for k, v in settings.items():
+        rc.Setting(k, v)
+    return rc
+
+
+@pytest.mark.parametrize("cap,roulette", [(0, 1), (1, 1), (0, 0)])
+def test_lit_frame_matches_cpu_restatement(cap, roulette):
+    """The full shade stage: area + point + spot + directional lights picked by potential contribution,
+    MIS on emissive hits, glossy / mirror / diffuse Lambert materials, Russian roulette, skydome image, intensity clamp.
+    Image vs the numpy restatement that traces through the CPU oracle.  cap = 1 is the reference's ENOUGH_BOUNCES.
+    Bar: RMSE <= 1% of the mean radiance and < 2% of pixels off by more than 2% (discrete choices -- light pick,
+    roulette, specular/diffuse lobe -- fork on last-bit differences of the GPU's fast intrinsics)."""
+    sc = _lit_scene()
+    w, h = 160, 90
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    rc = _lit_core(sc, w, h, spp=2, diffuseBounceCap=cap, russianRoulette=roulette)
+    rc.Render(view, converge=1)
+    acc = rc.ReadAccumulator()
+    st = rc.GetCoreStats()
+    port = cases.load_oracle(dict(sc["case"], rays=None), "port")
+    stats = {}
+    ref = wavefront_ref.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
+                               lights=wavefront_ref.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
+                               materials=sc["materials"], prim_materials=sc["prim_materials"], max_path_length=5, spp=2,
+                               bounce_cap=cap, roulette=bool(roulette), stats=stats)
+    mean = float(ref[..., :3].mean())
+    rmse = float(np.sqrt(np.mean((acc[..., :3] - ref[..., :3]) ** 2)))
+    big = np.abs(acc[..., :3] - ref[..., :3]).max(axis=2) > 0.02 * mean
+    print("lit image: mean", mean, "rmse", rmse, "pixels off by >2%:", int(big.sum()), "of", w * h,
+          "rays gpu", st["totalExtensionRays"], st["totalShadowRays"], "ref", sum(stats["ext"]), sum(stats["shadow"]))
+    assert np.isfinite(acc).all() and mean > 0.05
+    assert rmse <= 1e-2 * mean, (rmse, mean)
+    assert big.mean() < 2e-2
+    assert np.allclose(acc[..., 3], ref[..., 3], rtol=1e-5)
+    # the same number of rays, up to the forked paths
+    assert abs(st["totalExtensionRays"] - sum(stats["ext"])) <= 0.005 * sum(stats["ext"])
+    assert abs(st["totalShadowRays"] - sum(stats["shadow"])) <= 0.005 * sum(stats["shadow"])
+    rc.Shutdown()
+
+
+def test_emitter_seen_directly_and_one_sided():
+    """A camera ray that hits the emitter's front adds its radiance (clamped by clampValue); its back is black."""
+    sc = _lit_scene()
+    w, h = 64, 64
+    for eye_y, expect_lit in ((1.0, True), (2.5, False)):  # from below (front side) / from above (back side)
+        view = scenes.view_pyramid(width=w, height=h, pos=(0.1, eye_y, -0.1), target=(0.1, 1.6, 0.0), fov_deg=30.0)
+        rc = _lit_core(sc, w, h, clampValue=1e6)
+        rc.Render(view, converge=1)
+        centre = rc.ReadAccumulator()[h // 2, w // 2, :3]
+        if expect_lit:
+            assert np.allclose(centre, sc["materials"][3, :3], rtol=1e-6)
+        else:
+            assert np.all(centre == 0)
+        rc.Shutdown()

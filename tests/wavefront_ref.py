@@ -4,6 +4,10 @@ Same loop, same per-path random streams (WangHash + xor32, lib/CUDA/shared_kerne
 every extend / shadow query goes through the CPU oracle (the reference's TopLevelBVH::Traverse), as SURVEY.md
 Appendix A.9 prescribes for image-level parity.  numpy float32 throughout; transcendental functions differ from the
 GPU's fast-math versions in the last bits, so images agree to an RMSE, not bit for bit.
+
+The shade stage restates lib/rendercore_optix7/kernels/pathtracer.h:54-240 with the Lambert BSDF of
+lib/sharedBSDFs/lambert.h (no transmission) and the light sampling of lib/CUDA/shared_kernel_code/lights_shared.h, with
+the same simplifications as the CUDA core (geometric normals, no textures, WangHash/xor32 instead of blue noise).
 """
 import numpy as np
 
@@ -43,23 +47,193 @@ def tangent2world(V, N):
     return (V[:, 0:1] * T + V[:, 1:2] * B + V[:, 2:3] * N).astype(f32)
 
 
-def render(oracle, meshes, instances, view, width, height, light=None, sky=(0, 0, 0), materials=None, max_path_length=5,
-           spp=1, sample_offset=0, nthreads=8):
-    """Returns the accumulator float32[h, w, 3] (sum over samples).  meshes: list of verts[T,3,3]; instances: list of
-    (mesh, mat16 or None); light = (pos3, radiance3) or None.  Pixel-centre rays (jitter off)."""
+INVPI = f32(0.31830988618379067154)
+TWOPI = f32(6.28318530717958647692)
+S_SPECULAR, S_BOUNCED, S_VIASPECULAR, S_BOUNCEDTWICE = 1, 2, 4, 8
+
+
+def dot(a, b):
+    return (a[:, 0] * b[:, 0] + a[:, 1] * b[:, 1] + a[:, 2] * b[:, 2]).astype(f32)
+
+
+def normalize(a):
+    return (a * (f32(1) / np.sqrt(dot(a, a)))[:, None]).astype(f32)
+
+
+class Lights:
+    """The four light arrays of SetLights as float32 records (lighthouse2_b200/lights.py)."""
+
+    def __init__(self, area=None, point=None, spot=None, directional=None):
+        self.area = np.zeros((0, 24), f32) if area is None else np.asarray(area, f32).reshape(-1, 24)
+        self.point = np.zeros((0, 8), f32) if point is None else np.asarray(point, f32).reshape(-1, 8)
+        self.spot = np.zeros((0, 12), f32) if spot is None else np.asarray(spot, f32).reshape(-1, 12)
+        self.dir = np.zeros((0, 8), f32) if directional is None else np.asarray(directional, f32).reshape(-1, 8)
+
+    @property
+    def count(self):
+        return len(self.area) + len(self.point) + len(self.spot) + len(self.dir)
+
+    def potentials(self, I, N, P=None, bary=None):
+        """[n, lights] potential contributions (lights_shared.h:33-94).  bary given: area lights sampled at the
+        barycentric point; else (implicit connection) seen at point P."""
+        cols = []
+        with np.errstate(all="ignore"):
+            for a in self.area:
+                if bary is not None:
+                    L = (bary[:, 0:1] * a[12:15][None] + bary[:, 1:2] * a[16:19][None] + bary[:, 2:3] * a[20:23][None]).astype(f32)
+                else:
+                    L = P
+                L = (L - I).astype(f32)
+                att = f32(1) / dot(L, L)
+                L = normalize(L)
+                ln = np.broadcast_to(a[4:7], L.shape)
+                cols.append(a[3] * np.maximum(f32(0), -dot(ln, L)) * np.maximum(f32(0), dot(N, L)) * att)
+            for p in self.point:
+                L = (p[0:3][None] - I).astype(f32)
+                cols.append(p[3] * np.maximum(f32(0), dot(N, L)) * (f32(1) / dot(L, L)))
+            for s in self.spot:
+                L = (s[0:3][None] - I).astype(f32)
+                att = f32(1) / dot(L, L)
+                L = normalize(L)
+                d = (np.maximum(f32(0), -dot(L, np.broadcast_to(s[8:11], L.shape))) - s[7]) / (s[3] - s[7])
+                cols.append((s[4] + s[5] + s[6]) * np.maximum(f32(0), np.minimum(f32(1), d)) * np.maximum(f32(0), dot(N, L)) * att)
+            for d in self.dir:
+                cols.append(d[3] * np.maximum(f32(0), -dot(np.broadcast_to(d[0:3], N.shape), N)))
+        return np.stack(cols, axis=1).astype(f32) if cols else np.zeros((len(I), 0), f32)
+
+
+def random_barycentrics(r0):
+    """lights_shared.h:122-142."""
+    uf = np.minimum(r0.astype(np.float64) * 4294967296.0, 4294967295.0).astype(np.uint32)  # float -> uint saturates on the GPU
+    n = len(r0)
+    A = np.tile(np.array([1, 0], f32), (n, 1)); B = np.tile(np.array([0, 1], f32), (n, 1)); C = np.zeros((n, 2), f32)
+    h = f32(0.5)
+    for i in range(16):
+        d = ((uf >> np.uint32(2 * (15 - i))) & np.uint32(3))[:, None]
+        An = np.where(d == 0, (B + C) * h, np.where(d == 1, A, np.where(d == 2, (B + A) * h, (C + A) * h)))
+        Bn = np.where(d == 0, (A + C) * h, np.where(d == 1, (A + B) * h, np.where(d == 2, B, (C + B) * h)))
+        Cn = np.where(d == 0, (A + B) * h, np.where(d == 1, (A + C) * h, np.where(d == 2, (B + C) * h, C)))
+        A, B, C = An.astype(f32), Bn.astype(f32), Cn.astype(f32)
+    r = ((A + B + C) * f32(0.3333333)).astype(f32)
+    return np.stack([r[:, 0], r[:, 1], f32(1) - r[:, 0] - r[:, 1]], axis=1).astype(f32)
+
+
+def random_point_on_light(lights, r0, r1, I, N):
+    """lights_shared.h:144-234.  Returns P, pickProb, lightPdf, lightColor."""
+    n = len(I)
+    bary = random_barycentrics(r0)
+    pot = lights.potentials(I, N, bary=bary)
+    total = np.zeros(n, f32)
+    run = []
+    for k in range(pot.shape[1]):
+        total = (total + pot[:, k]).astype(f32)
+        run.append(total)
+    run = np.stack(run, axis=1)
+    s = run[:, -1]
+    ok = s > 0
+    r1s = (r1 * s).astype(f32)
+    ge = run >= r1s[:, None]
+    k = np.where(ge.any(axis=1), ge.argmax(axis=1), 0)
+    with np.errstate(all="ignore"):
+        pick = (pot[np.arange(n), k] / s).astype(f32)
+    P = np.ones((n, 3), f32)
+    pdf = np.zeros(n, f32)
+    col = np.zeros((n, 3), f32)
+    na, npt, nsp = len(lights.area), len(lights.point), len(lights.spot)
+    with np.errstate(all="ignore"):
+        for i in range(lights.count):
+            sel = ok & (k == i)
+            if not sel.any():
+                continue
+            Is, Ns = I[sel], N[sel]
+            if i < na:
+                a = lights.area[i]
+                b = bary[sel]
+                Pp = (b[:, 0:1] * a[12:15][None] + b[:, 1:2] * a[16:19][None] + b[:, 2:3] * a[20:23][None]).astype(f32)
+                L = (Is - Pp).astype(f32)
+                sq = dot(L, L)
+                L = normalize(L)
+                lndl = dot(L, np.broadcast_to(a[4:7], L.shape))
+                P[sel], col[sel] = Pp, a[8:11]
+                pdf[sel] = np.where((lndl > 0) & (dot(L, Ns) < 0), sq / (a[7] * lndl), f32(0))
+            elif i < na + npt:
+                p = lights.point[i - na]
+                L = (Is - p[0:3][None]).astype(f32)
+                P[sel], col[sel] = p[0:3], p[4:7]
+                pdf[sel] = np.where(dot(L, Ns) < 0, dot(L, L), f32(0))
+            elif i < na + npt + nsp:
+                sp = lights.spot[i - na - npt]
+                L = (Is - sp[0:3][None]).astype(f32)
+                sq = dot(L, L)
+                L = normalize(L)
+                d = (np.maximum(f32(0), dot(L, np.broadcast_to(sp[8:11], L.shape))) - sp[7]) / (sp[3] - sp[7])
+                lndl = np.minimum(f32(1), d)
+                P[sel], col[sel] = sp[0:3], sp[4:7]
+                pdf[sel] = np.where((lndl > 0) & (dot(L, Ns) < 0), sq / lndl, f32(0))
+            else:
+                dl = lights.dir[i - na - npt - nsp]
+                P[sel], col[sel] = (Is - dl[0:3][None] * f32(1000)).astype(f32), dl[4:7]
+                pdf[sel] = np.where(dot(np.broadcast_to(dl[0:3], Ns.shape), Ns) < 0, f32(1), f32(0))
+    pick = np.where(ok, pick, f32(0)).astype(f32)
+    return P, pick, pdf.astype(f32), col
+
+
+def sample_skydome(D, sky, sky_image):
+    """tools_shared.h:185-192."""
+    if sky_image is None:
+        return np.broadcast_to(np.asarray(sky, f32), D.shape).astype(f32)
+    h, w = sky_image.shape[:2]
+    u = (f32(w) * f32(0.5) * (f32(1) + np.arctan2(D[:, 0], -D[:, 2]).astype(f32) * INVPI)).astype(f32).astype(np.int64)
+    v = (f32(h) * np.arccos(np.clip(D[:, 1], -1, 1)).astype(f32) * INVPI).astype(f32).astype(np.int64)
+    idx = u + v * w
+    flat = sky_image.reshape(-1, 3).astype(f32)
+    ok = (idx >= 0) & (idx < w * h)
+    out = np.zeros(D.shape, f32)
+    out[ok] = flat[idx[ok]]
+    return out
+
+
+def clamp_and_fix(c, clamp):
+    m = np.max(c, axis=1)
+    with np.errstate(all="ignore"):
+        scale = np.where(m > clamp, clamp / m, f32(1)).astype(f32)
+    c = (c * scale[:, None]).astype(f32)
+    bad = ~np.isfinite(c.sum(axis=1))
+    c[bad] = 0
+    return c
+
+
+def render(oracle, meshes, instances, view, width, height, light=None, lights=None, sky=(0, 0, 0), sky_image=None,
+           materials=None, prim_materials=None, max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True,
+           nthreads=8, stats=None):
+    """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
+    meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
+    point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness), prim_materials = per mesh
+    uint32[T] material index (default 0); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off)."""
     npx = width * height
-    acc = np.zeros((npx, 3), np.float64)
+    acc = np.zeros((npx, 4), np.float64)
     pos, p1 = view["pos"].astype(f32), view["p1"].astype(f32)
     right, up = (view["p2"] - view["p1"]).astype(f32), (view["p3"] - view["p1"]).astype(f32)
+    clamp = f32(clamp)
+    if lights is None:
+        lights = Lights()
+        if light is not None:
+            lp, lr = np.asarray(light[0], f32), np.asarray(light[1], f32)
+            lights = Lights(point=np.array([[lp[0], lp[1], lp[2], lr[0] + lr[1] + lr[2], lr[0], lr[1], lr[2], 0]], f32))
     normals = []
     for v in meshes:
         n = np.cross(v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]).astype(f32)
-        l2 = np.einsum("ij,ij->i", n, n)
+        l2 = dot(n, n)
         il = np.where(l2 > 0, f32(1) / np.sqrt(np.maximum(l2, 1e-38)), 0).astype(f32)
         normals.append(n * il[:, None])
     mats = [np.eye(4, dtype=f32) if m is None else np.asarray(m, f32).reshape(4, 4) for _, m in instances]
     inst_mesh = [mesh for mesh, _ in instances]
-    sky = np.asarray(sky, f32)
+    if materials is not None:
+        materials = np.asarray(materials, f32).reshape(-1, 4)
+
+    def add(px, c):
+        np.add.at(acc, (px, slice(0, 3)), c.astype(np.float64))
+
     for s in range(spp):
         sample = sample_offset + s
         R0 = np.uint32(7907)
@@ -68,58 +242,143 @@ def render(oracle, meshes, instances, view, width, height, light=None, sky=(0, 0
         x, y = (pix % width).astype(f32), (pix // width).astype(f32)
         u, v = (x + f32(0.5)) / f32(width), (y + f32(0.5)) / f32(height)
         D = (p1[None] + u[:, None] * right[None] + v[:, None] * up[None] - pos[None]).astype(f32)
-        D = (D * (f32(1) / np.sqrt(np.einsum("ij,ij->i", D, D)))[:, None]).astype(f32)
+        D = (D * (f32(1) / np.sqrt(dot(D, D)))[:, None]).astype(f32)
         O = np.broadcast_to(pos, D.shape).astype(f32).copy()
         T = np.ones((npx, 3), f32)
+        pdf_prev = np.ones(npx, f32)
+        flags = np.zeros(npx, np.uint32)
+        lastN = np.zeros((npx, 3), f32)
         for length in range(1, max_path_length + 1):
             if len(O) == 0:
                 break
+            if stats is not None:
+                stats.setdefault("ext", []).append(len(O))
             t, prim, inst = oracle.trace(O, D, nthreads=nthreads)
             px = (path_idx % np.uint32(npx)).astype(np.int64)
             miss = prim < 0
-            np.add.at(acc, px[miss], (T[miss] * sky[None]).astype(np.float64))
+            if length == 1:
+                np.add.at(acc, (px, 3), np.where(miss, 10000.0, t.astype(np.float64)))
+            with np.errstate(all="ignore"):
+                add(px[miss], clamp_and_fix((T[miss] * sample_skydome(D[miss], sky, sky_image) * (f32(1) / pdf_prev[miss])[:, None]).astype(f32), clamp))
             h = ~miss
             if not h.any():
                 break
             O, D, T, t, prim, inst, path_idx, px = O[h], D[h], T[h], t[h], prim[h], inst[h], path_idx[h], px[h]
+            pdf_prev, flags, lastN = pdf_prev[h], flags[h], lastN[h]
+            n = len(O)
             N = np.empty_like(O)
-            color = np.full_like(O, f32(0.8))
+            mat = np.zeros(n, np.int64)
             for i in np.unique(inst):
                 sel = inst == i
                 n_obj = normals[inst_mesh[i]][prim[sel]]
-                n_w = (n_obj @ mats[i][:3, :3].T).astype(f32)
-                N[sel] = n_w * (f32(1) / np.sqrt(np.einsum("ij,ij->i", n_w, n_w)))[:, None]
+                m = mats[i]
+                n_w = np.stack([m[0, 0] * n_obj[:, 0] + m[0, 1] * n_obj[:, 1] + m[0, 2] * n_obj[:, 2],
+                                m[1, 0] * n_obj[:, 0] + m[1, 1] * n_obj[:, 1] + m[1, 2] * n_obj[:, 2],
+                                m[2, 0] * n_obj[:, 0] + m[2, 1] * n_obj[:, 1] + m[2, 2] * n_obj[:, 2]], axis=1).astype(f32)
+                N[sel] = normalize(n_w)
+                if prim_materials is not None:
+                    mat[sel] = prim_materials[inst_mesh[i]][prim[sel]]
+            color = np.full((n, 3), f32(0.8))
+            rough = np.ones(n, f32)
             if materials is not None:
-                raise NotImplementedError
-            flip = np.einsum("ij,ij->i", D, N) > 0
-            N[flip] = -N[flip]
-            I = (O + t[:, None] * D).astype(f32)
-            if light is not None:
-                lp, lr = np.asarray(light[0], f32), np.asarray(light[1], f32)
-                L = (lp[None] - I).astype(f32)
-                d2 = np.einsum("ij,ij->i", L, L).astype(f32)
-                dist = np.sqrt(d2)
-                L = (L * (f32(1) / dist)[:, None]).astype(f32)
-                ndl = np.einsum("ij,ij->i", L, N).astype(f32)
-                ok = (ndl > 0) & (dist > 4 * EPS)
+                known = mat < len(materials)
+                color[known], rough[known] = materials[mat[known], :3], materials[mat[known], 3]
+            I = (O + D * t[:, None]).astype(f32)
+            # ---- paths that end on a light (pathtracer.h:120-148)
+            emissive = (color > 1).any(axis=1)
+            if emissive.any():
+                e = np.nonzero(emissive)[0]
+                ddn = -dot(D[e], N[e])
+                c = (T[e] * color[e]).astype(f32)
+                mis = (length > 1) & ((flags[e] & S_SPECULAR) == 0)
+                if mis.any():
+                    ltri = np.full(len(e), -1)
+                    area = np.zeros(len(e), f32)
+                    for li, a in enumerate(lights.area):
+                        match = (prim[e] == a[15:16].view(np.int32)[0]) & (inst[e] == a[19:20].view(np.int32)[0])
+                        ltri[match], area[match] = li, a[7]
+                    with np.errstate(all="ignore"):
+                        light_pdf = np.where(ltri >= 0, (t[e] * t[e]) / (ddn * area), f32(0)).astype(f32)
+                        pot = lights.potentials(O[e], lastN[e], P=I[e])
+                        ssum = np.zeros(len(e), f32)
+                        for k in range(pot.shape[1]):
+                            ssum = (ssum + pot[:, k]).astype(f32)
+                        mine = pot[np.arange(len(e)), np.maximum(ltri, 0)] if pot.shape[1] else np.zeros(len(e), f32)
+                        pick = np.where((ltri >= 0) & (ssum > 0), mine / ssum, f32(0)).astype(f32)
+                        w = (pdf_prev[e] + light_pdf * pick).astype(f32)
+                        cm = np.where((w > 0)[:, None], c * (f32(1) / w)[:, None], f32(0)).astype(f32)
+                    c = np.where(mis[:, None], cm, c)
+                c = clamp_and_fix(c, clamp)
+                front = ddn > 0
+                add(px[e][front], c[front])
+            keep = ~emissive
+            if not keep.any():
+                break
+            O, D, T, t, N, I, color, rough, path_idx, px = (a[keep] for a in (O, D, T, t, N, I, color, rough, path_idx, px))
+            pdf_prev, flags, lastN = pdf_prev[keep], flags[keep], lastN[keep]
+            n = len(O)
+            flags = np.where(rough <= f32(0.001), flags | S_SPECULAR, flags & ~np.uint32(S_SPECULAR)).astype(np.uint32)
+            seed = wang_hash(path_idx * np.uint32(17) + R0 + np.uint32(length) * np.uint32(91771))
+            face = np.where(dot(D, N) > 0, f32(-1), f32(1))
+            fN = (N * face[:, None]).astype(f32)
+            with np.errstate(all="ignore"):
+                T = (T * (f32(1) / pdf_prev)[:, None]).astype(f32)
+            # ---- next event estimation (pathtracer.h:163-199)
+            nee = (flags & S_SPECULAR) == 0
+            if lights.count > 0 and nee.any():
+                seed_n, r0 = random_float(seed.copy())
+                seed_n, r1 = random_float(seed_n)
+                seed = np.where(nee, seed_n, seed)
+                q = np.nonzero(nee)[0]
+                P, pick, lpdf, lcol = random_point_on_light(lights, r0[q], r1[q], I[q], fN[q])
+                L = (P - I[q]).astype(f32)
+                dist = np.sqrt(dot(L, L))
+                with np.errstate(all="ignore"):
+                    L = (L * (f32(1) / dist)[:, None]).astype(f32)
+                    ndl = dot(L, fN[q])
+                    bpdf = (np.abs(ndl) * INVPI).astype(f32)
+                    ok = (ndl > 0) & (lpdf > 0) & (bpdf > 0)
+                    sc = (INVPI * rough[q] * (ndl / (pick * lpdf + bpdf))).astype(f32)
+                    E = clamp_and_fix((T[q] * color[q] * lcol * sc[:, None]).astype(f32), clamp)
                 if ok.any():
-                    sc = (ndl[ok] * f32(0.31830988618379067154) / d2[ok]).astype(f32)
-                    E = (T[ok] * color[ok] * lr[None] * sc[:, None]).astype(f32)
-                    So = safe_origin(I[ok], L[ok], N[ok], EPS)
+                    So = safe_origin(I[q][ok], L[ok], fN[q][ok], EPS)
                     tmax = dist[ok] - 2 * EPS
+                    if stats is not None:
+                        stats.setdefault("shadow", []).append(int(ok.sum()))
                     ts, _, _ = oracle.trace(So, L[ok], nthreads=nthreads)
                     vis = ~(ts < tmax)
-                    np.add.at(acc, px[ok][vis], E[vis].astype(np.float64))
+                    add(px[q][ok][vis], E[ok][vis])
+            # ---- extension (pathtracer.h:201-239, SampleBSDF of lambert.h with TRANSMISSION = 0)
+            enough = ((bounce_cap == 1) & ((flags & S_BOUNCED) != 0)) | ((bounce_cap == 2) & ((flags & S_BOUNCEDTWICE) != 0))
             if length == max_path_length:
                 break
-            seed = wang_hash(path_idx * np.uint32(17) + R0 + np.uint32(length) * np.uint32(91771))
-            seed, r0 = random_float(seed)
-            seed, r1 = random_float(seed)
-            term1, term2 = f32(6.28318530717958647692) * r0, np.sqrt(f32(1) - r1)
-            V = np.stack([np.cos(term1) * term2, np.sin(term1) * term2, np.sqrt(r1)], axis=1).astype(f32)
-            R = tangent2world(V, N)
-            R = (R * (f32(1) / np.sqrt(np.einsum("ij,ij->i", R, R)))[:, None]).astype(f32)
-            O = safe_origin(I, R, N, EPS)
-            D = R
-            T = (T * color).astype(f32)
-    return acc.reshape(height, width, 3).astype(f32)
+            seed, r3 = random_float(seed)
+            seed, r4 = random_float(seed)
+            p_reflect = (f32(1) - rough).astype(f32)
+            spec = r3 < p_reflect
+            ddotn = dot(D, fN)
+            R_spec = (D - fN * (f32(2) * ddotn)[:, None]).astype(f32)
+            with np.errstate(all="ignore"):
+                r5 = ((r3 - p_reflect) / (f32(1) - p_reflect)).astype(f32)
+                term1, term2 = TWOPI * r5, np.sqrt(f32(1) - r4)
+                V = np.stack([np.cos(term1) * term2, np.sin(term1) * term2, np.sqrt(r4)], axis=1).astype(f32)
+                R_diff = normalize(tangent2world(V, fN))
+                R = np.where(spec[:, None], R_spec, R_diff).astype(f32)
+                cosr = dot(fN, R)
+                bsdf = np.where(spec[:, None], color * (f32(1) / np.abs(cosr))[:, None], color * INVPI).astype(f32)
+                new_pdf = np.where(spec, f32(1), np.maximum(f32(0), cosr) * INVPI).astype(f32)
+            new_pdf = np.where(cosr <= 0, f32(0), new_pdf)
+            alive = ~enough & (new_pdf >= f32(1e-4))
+            flags = np.where(alive & spec, flags | S_SPECULAR, flags).astype(np.uint32)
+            p = np.where(((flags & S_SPECULAR) != 0) | ((flags & S_BOUNCED) == 0) | (not roulette), f32(1), np.minimum(f32(1), bsdf.max(axis=1))).astype(f32)
+            seed, rr = random_float(seed)
+            alive &= ~(p < rr)
+            with np.errstate(all="ignore"):
+                T = (T * (f32(1) / p)[:, None]).astype(f32)
+            is_spec = (flags & S_SPECULAR) != 0
+            flags = np.where(is_spec, flags | S_VIASPECULAR, flags | np.where((flags & S_BOUNCED) != 0, S_BOUNCEDTWICE, S_BOUNCED)).astype(np.uint32)
+            T[~np.isfinite(T.sum(axis=1))] = 0
+            newO = safe_origin(I, R, fN, EPS)
+            newT = (T * bsdf * np.abs(cosr)[:, None]).astype(f32)
+            O, D, T, pdf_prev, flags, lastN, path_idx = newO[alive], R[alive], newT[alive], new_pdf[alive], flags[alive], fN[alive], path_idx[alive]
+    return acc.reshape(height, width, 4).astype(f32)

@@ -30,7 +30,7 @@ def main():
     sr = multigpu.ShardedRenderer(rank, world, local, mode="tiles")
     sr.SetGeometry(0, scenes.sphere_field(1_000_000)); sr.SetInstance(0, 0); sr.SetInstance(1, -1); sr.UpdateToplevel()
     sr.SetTarget(w, h, spp)
-    sr.SetPointLight(scenes.C2_LIGHT, (4000.0, 4000.0, 3600.0)); sr.SetSky((0.4, 0.5, 0.7)); sr.Setting("maxPathLength", 5)
+    sr.SetPointLight(scenes.C2_LIGHT, (4000.0, 4000.0, 3600.0)); sr.SetSky((0.4, 0.5, 0.7)); sr.Setting("maxPathLength", 5); sr.Setting("russianRoulette", 0)
     view = scenes.view_pyramid(width=w, height=h, **scenes.C2_CAMERA)
     sr.Render(view, 1)
     sync = lambda: (torch.cuda.synchronize(), dist.barrier() if world > 1 else None, torch.cuda.synchronize())

@@ -84,7 +84,7 @@ def c3(frames, n_tris=10_000_000):
     rc.SetGeometry(0, verts); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
     t2 = time.perf_counter()
     st = rc.GetCoreStats()
-    rc.SetTarget(1920, 1080, 1); rc.SetPointLight((0.0, 120.0, -60.0), (2e4, 2e4, 1.8e4)); rc.SetSky((0.4, 0.5, 0.7)); rc.Setting("maxPathLength", 5)
+    rc.SetTarget(1920, 1080, 1); rc.SetPointLight((0.0, 120.0, -60.0), (2e4, 2e4, 1.8e4)); rc.SetSky((0.4, 0.5, 0.7)); rc.Setting("maxPathLength", 5); rc.Setting("russianRoulette", 0)
     view = scenes.view_pyramid(width=1920, height=1080, **scenes.C3_CAMERA)
     stats_line(f"C3 {n_tris} tri soup 1080p 4 bounces", rc, frames,
                {"view": view, "scene_gen_s": t1 - t0, "bvh_build_upload_s": t2 - t1, "wide_nodes": st["wideNodeCount"],
