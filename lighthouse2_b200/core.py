@@ -284,7 +284,8 @@ class RenderCoreB200:
         vp = ViewPyramid()
         for k in ("pos", "p1", "p2", "p3"):
             getattr(vp, k)[:] = [float(x) for x in view[k]]
-        vp.aperture, vp.spreadAngle, vp.imagePlane, vp.focalDistance, vp.distortion = 0.0, 0.01, 0.01, 1.0, 0.0
+        vp.aperture, vp.spreadAngle, vp.imagePlane, vp.focalDistance, vp.distortion = (
+            float(view.get("aperture", 0.0)), 0.01, 0.01, 1.0, float(view.get("distortion", 0.0)))
         self._chk(self.lib.b200_render(self.h, C.byref(vp), converge))
 
     def ReadAccumulator(self) -> np.ndarray:

@@ -34,6 +34,7 @@ struct WaveCounters { uint32_t extensionRays, shadowRays, pad0, pad1; }; // one 
 struct FrameParams {
 	float pos[3], p1[3], right[3], up[3]; // right = p2 - p1, up = p3 - p1
 	float sky[3];                         // constant sky (used when no skydome image is set)
+	float aperture, distortion;           // ViewPyramid::aperture (lens radius), ::distortion (barrel distortion; 0 = none)
 	float epsilon, clampValue;
 	uint32_t width, height, pixelCount;
 	uint32_t shardIndex, shardCount, ownTiles, tilesX, tilesY;
@@ -80,7 +81,7 @@ __device__ __forceinline__ uint32_t warpAppend( uint32_t* counter, bool want )
 }
 
 // ---- primary rays (GPU cores: rendercore_optix7/optix/.optix.cu:66-123, RenderCore_OptixPrime_B/kernels/camera.h:40-94) ----------
-// u = (x + r0) / w, v = (y + r1) / h, P = p1 + u right + v up, D = normalize(P - pos); pinhole (aperture is not sampled).
+// u = (x + r0) / w, v = (y + r1) / h, P = p1 + u right + v up, O = point on the lens, D = normalize(P - O); optional barrel distortion.
 __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParams f, float4* __restrict__ rayO, float4* __restrict__ rayD,
 	float4* __restrict__ pathState, float4* __restrict__ pathInfo, WaveCounters* counters )
 {
@@ -104,17 +105,40 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 		if (!valid) continue;
 		const uint32_t pixelIdx = x + y * f.width, pathIdx = pixelIdx + (f.sampleBase + sample) * f.pixelCount;
 		float r0 = 0.5f, r1 = 0.5f;
-		if (f.jitter)
+		uint32_t seed = WangHash( pathIdx + f.R0 );
+		if (f.jitter) r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
+		// thin lens: a point on a 9-blade aperture of radius `aperture` in the screen-parallel plane through pos (RandomPointOnLens, .optix.cu:51-64)
+		float ox = f.pos[0], oy = f.pos[1], oz = f.pos[2];
+		if (f.aperture > 0)
 		{
-			uint32_t seed = WangHash( pathIdx + f.R0 );
-			r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
+			const float l0 = RandomFloat( seed );
+			float l1 = RandomFloat( seed );
+			const float blade = (float)(int)(l0 * 9);
+			float l2 = (l0 - blade * (1.0f / 9.0f)) * 9.0f;
+			float x1, y1, x2, y2;
+			__sincosf( blade * 3.14159265358979323846f / 4.5f, &x1, &y1 );
+			__sincosf( (blade + 1.0f) * 3.14159265358979323846f / 4.5f, &x2, &y2 );
+			if (l1 + l2 > 1) l1 = 1.0f - l1, l2 = 1.0f - l2;
+			const float xr = x1 * l1 + x2 * l2, yr = y1 * l1 + y2 * l2;
+			ox += f.aperture * (f.right[0] * xr + f.up[0] * yr), oy += f.aperture * (f.right[1] * xr + f.up[1] * yr), oz += f.aperture * (f.right[2] * xr + f.up[2] * yr);
 		}
-		const float u = ((float)x + r0) / (float)f.width, v = ((float)y + r1) / (float)f.height;
-		const float dx = f.p1[0] + u * f.right[0] + v * f.up[0] - f.pos[0];
-		const float dy = f.p1[1] + u * f.right[1] + v * f.up[1] - f.pos[1];
-		const float dz = f.p1[2] + u * f.right[2] + v * f.up[2] - f.pos[2];
+		float u, v;
+		if (f.distortion == 0) u = ((float)x + r0) / (float)f.width, v = ((float)y + r1) / (float)f.height;
+		else
+		{
+			// barrel distortion of the pixel position about the screen centre (.optix.cu:88-97)
+			const float tx = (float)x / (float)f.width - 0.5f, ty = (float)y / (float)f.height - 0.5f;
+			const float rr = tx * tx + ty * ty;
+			const float rq = sqrtf( rr ) * (1.0f + f.distortion * rr + f.distortion * rr * rr);
+			const float theta = atan2f( tx, ty );
+			const float bx = (sinf( theta ) * rq + 0.5f) * (float)f.width, by = (cosf( theta ) * rq + 0.5f) * (float)f.height;
+			u = (bx + r0) / (float)f.width, v = (by + r1) / (float)f.height;
+		}
+		const float dx = f.p1[0] + u * f.right[0] + v * f.up[0] - ox;
+		const float dy = f.p1[1] + u * f.right[1] + v * f.up[1] - oy;
+		const float dz = f.p1[2] + u * f.right[2] + v * f.up[2] - oz;
 		const float il = 1.0f / sqrtf( dx * dx + dy * dy + dz * dz );
-		rayO[slot] = make_float4( f.pos[0], f.pos[1], f.pos[2], f.epsilon );
+		rayO[slot] = make_float4( ox, oy, oz, f.epsilon );
 		rayD[slot] = make_float4( dx * il, dy * il, dz * il, 1e34f );
 		pathState[slot] = make_float4( 1.f, 1.f, 1.f, 1.f );                      // throughput, postponed bsdf pdf
 		pathInfo[slot] = make_float4( __uint_as_float( pathIdx ), 0.f, 0.f, 0.f ); // pathIdx | flags << 28, normal at the previous vertex
@@ -669,6 +693,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	memset( &f, 0, sizeof( f ) );
 	for (int a = 0; a < 3; a++) f.pos[a] = vp[a], f.p1[a] = vp[3 + a], f.right[a] = vp[6 + a] - vp[3 + a], f.up[a] = vp[9 + a] - vp[3 + a];
 	memcpy( f.sky, w->sky, 12 );
+	f.aperture = vp[12], f.distortion = vp[16];
 	f.clampValue = w->clampValue, f.bounceCap = (uint32_t)w->bounceCap, f.roulette = (uint32_t)w->roulette;
 	f.areaCount = w->lightCounts[0], f.pointCount = w->lightCounts[1], f.spotCount = w->lightCounts[2], f.dirCount = w->lightCounts[3];
 	f.areaLights = (const float4*)w->lights.ptr, f.pointLights = f.areaLights + f.areaCount * 6, f.spotLights = f.pointLights + f.pointCount * 2;

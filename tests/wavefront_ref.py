@@ -241,9 +241,29 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
         path_idx = (pix + np.uint32(sample) * np.uint32(npx)).astype(np.uint32)
         x, y = (pix % width).astype(f32), (pix // width).astype(f32)
         u, v = (x + f32(0.5)) / f32(width), (y + f32(0.5)) / f32(height)
-        D = (p1[None] + u[:, None] * right[None] + v[:, None] * up[None] - pos[None]).astype(f32)
+        O = np.broadcast_to(pos, (npx, 3)).astype(f32).copy()
+        aperture, distortion = f32(view.get("aperture", 0.0)), f32(view.get("distortion", 0.0))
+        if aperture > 0:  # RandomPointOnLens (rendercore_optix7/optix/.optix.cu:51-64); jitter is off, so the lens takes the first two numbers
+            seed = wang_hash(path_idx + R0)
+            seed, l0 = random_float(seed)
+            seed, l1 = random_float(seed)
+            blade = (l0 * f32(9)).astype(np.int32).astype(f32)
+            l2 = ((l0 - blade * f32(1.0 / 9.0)) * f32(9)).astype(f32)
+            a1, a2 = blade * f32(np.pi) / f32(4.5), (blade + f32(1)) * f32(np.pi) / f32(4.5)
+            x1, y1, x2, y2 = np.sin(a1), np.cos(a1), np.sin(a2), np.cos(a2)
+            swap = (l1 + l2) > 1
+            l1, l2 = np.where(swap, f32(1) - l1, l1).astype(f32), np.where(swap, f32(1) - l2, l2).astype(f32)
+            xr, yr = (x1 * l1 + x2 * l2).astype(f32), (y1 * l1 + y2 * l2).astype(f32)
+            O = (O + aperture * (right[None] * xr[:, None] + up[None] * yr[:, None])).astype(f32)
+        if distortion != 0:  # barrel distortion (.optix.cu:88-97)
+            tx, ty = x / f32(width) - f32(0.5), y / f32(height) - f32(0.5)
+            rr = tx * tx + ty * ty
+            rq = np.sqrt(rr) * (f32(1) + distortion * rr + distortion * rr * rr)
+            theta = np.arctan2(tx, ty)
+            bx, by = (np.sin(theta) * rq + f32(0.5)) * f32(width), (np.cos(theta) * rq + f32(0.5)) * f32(height)
+            u, v = ((bx + f32(0.5)) / f32(width)).astype(f32), ((by + f32(0.5)) / f32(height)).astype(f32)
+        D = (p1[None] + u[:, None] * right[None] + v[:, None] * up[None] - O).astype(f32)
         D = (D * (f32(1) / np.sqrt(dot(D, D)))[:, None]).astype(f32)
-        O = np.broadcast_to(pos, D.shape).astype(f32).copy()
         T = np.ones((npx, 3), f32)
         pdf_prev = np.ones(npx, f32)
         flags = np.zeros(npx, np.uint32)
