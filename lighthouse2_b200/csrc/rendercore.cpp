@@ -443,8 +443,10 @@ int RenderCore::TraceAnyDevice( const void* dO4, const void* dD4, int n, void* d
 
 // shadow wave fused with the connect step: unoccluded rays add E4.xyz to accumulator[pixelIdx = bits of E4.w]
 // (rendercore_optix7/optix/.optix.cu:137-149; RenderCore_OptixPrime_B/kernels/connections.h:23-34)
-int RenderCore::TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount )
+int RenderCore::TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount,
+	cudaStream_t onStream, int counterSlot )
 {
+	cudaStream_t s = onStream ? onStream : stream;
 	if (n < 0) return fail( "trace: negative ray count" );
 	if (!dE4 || !dAccumulator) return fail( "connect: null potentials / accumulator" );
 	if (ensureToplevel()) return 1;
@@ -452,10 +454,11 @@ int RenderCore::TraceConnectDevice( const void* dO4, const void* dD4, int n, con
 	TraceArgs a = baseArgs();
 	a.rayO = (const float4*)dO4, a.rayD = (const float4*)dD4, a.potentials = (const float4*)dE4, a.accumulator = (float4*)dAccumulator;
 	a.count = (uint32_t)n, a.countPtr = dCount;
+	a.fetchCounter += counterSlot; // a wave that runs beside another one needs its own fetch counter
 	cudaError_t e;
-	cudaEventRecord( evA, stream );
-	if ((e = LaunchShadow( a, isect, smCount, stream )) != cudaSuccess) return fail( "connect kernel launch", e );
-	cudaEventRecord( evB, stream );
+	if (!onStream) cudaEventRecord( evA, s );
+	if ((e = LaunchShadow( a, isect, smCount, s )) != cudaSuccess) return fail( "connect kernel launch", e );
+	if (!onStream) cudaEventRecord( evB, s );
 	stats.kernelLaunches++;
 	return 0;
 }

@@ -60,7 +60,8 @@ public:
 	int TraceAny( const float* O4, const float* D4, int n, uint32_t* bits );
 	int TraceClosestDevice( const void* dO4, const void* dD4, int n, void* dHits, const uint32_t* dCount = nullptr );
 	int TraceAnyDevice( const void* dO4, const void* dD4, int n, void* dBits, const uint32_t* dCount = nullptr );
-	int TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount = nullptr );
+	int TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount = nullptr,
+		cudaStream_t onStream = nullptr, int counterSlot = 0 );
 	int ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris );
 	int Refit( int meshIdx, const float* vertexData, int vertexCount );
 	int RefitDevice( int meshIdx, const void* dVerts, int vertexCount, bool boundsKnown );

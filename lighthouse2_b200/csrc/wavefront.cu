@@ -536,7 +536,11 @@ struct WavefrontState {
 	int bounceCap = 0, roulette = 1;
 	uint32_t samplesTaken = 0, frameCounter = 0;
 	int probeX = -1, probeY = -1;
-	cudaEvent_t ev[2 * (3 * MAX_PATH_LENGTH + 2)] = {};
+	cudaEvent_t ev[2 + 6 * MAX_PATH_LENGTH] = {}; // frame begin/end, then per path length: extend begin/end, shade begin/end, connect begin/end
+	// the connect (shadow) wave of bounce k runs on its own stream beside the extend wave of bounce k+1 (Setting overlapConnect)
+	cudaStream_t connectStream = nullptr;
+	cudaEvent_t shadeDone[MAX_PATH_LENGTH + 1] = {}, connectDone[MAX_PATH_LENGTH + 1] = {};
+	int overlapConnect = 1;
 	float4* accumulator() { return accumExternal ? accumExternal : (float4*)accumOwn.ptr; }
 	~WavefrontState()
 	{
@@ -544,6 +548,9 @@ struct WavefrontState {
 			&accumOwn, &frame, &materials, &lights, &skyImage };
 		for (DeviceBuffer* b : all) b->release();
 		for (cudaEvent_t e : ev) if (e) cudaEventDestroy( e );
+		for (cudaEvent_t e : shadeDone) if (e) cudaEventDestroy( e );
+		for (cudaEvent_t e : connectDone) if (e) cudaEventDestroy( e );
+		if (connectStream) cudaStreamDestroy( connectStream );
 	}
 };
 
@@ -565,6 +572,7 @@ int RenderCore::SettingWavefront( const char* name, float value )
 	if (!strcmp( name, "sampleOffset" )) { if (v < 0) return fail( "Setting sampleOffset: >= 0" ); w->sampleOffset = v; return 0; }
 	if (!strcmp( name, "jitter" )) { w->jitter = value >= 0.5f; return 0; }
 	if (!strcmp( name, "clampValue" )) { if (!(value > 0)) return fail( "Setting clampValue: > 0" ); w->clampValue = value; return 0; }
+	if (!strcmp( name, "overlapConnect" )) { w->overlapConnect = value >= 0.5f; return 0; }
 	if (!strcmp( name, "russianRoulette" )) { w->roulette = value >= 0.5f; return 0; }
 	if (!strcmp( name, "diffuseBounceCap" )) { if (v < 0 || v > 2) return fail( "Setting diffuseBounceCap: 0 (off), 1 or 2" ); w->bounceCap = v; return 0; }
 	if (!strcmp( name, "pathsPerPass" )) { if (value < 1024) return fail( "Setting pathsPerPass: >= 1024" ); w->pathsPerPass = (uint32_t)value; return 0; }
@@ -584,6 +592,9 @@ int RenderCore::SetTarget( int width, int height, int spp )
 	if ((e = cudaMemsetAsync( w->accumulator(), 0, px * 16, stream )) != cudaSuccess) return fail( "SetTarget clear", e );
 	w->samplesTaken = 0;
 	for (cudaEvent_t& ev : w->ev) if (!ev && (e = cudaEventCreate( &ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
+	for (cudaEvent_t& ev : w->shadeDone) if (!ev && (e = cudaEventCreateWithFlags( &ev, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
+	for (cudaEvent_t& ev : w->connectDone) if (!ev && (e = cudaEventCreateWithFlags( &ev, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
+	if (!w->connectStream && (e = cudaStreamCreateWithFlags( &w->connectStream, cudaStreamNonBlocking )) != cudaSuccess) return fail( "connect stream", e );
 	return 0;
 }
 
@@ -699,6 +710,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	f.areaLights = (const float4*)w->lights.ptr, f.pointLights = f.areaLights + f.areaCount * 6, f.spotLights = f.pointLights + f.pointCount * 2;
 	f.dirLights = f.spotLights + f.spotCount * 3;
 	const bool anyLight = f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0;
+	const bool overlap = anyLight && w->overlapConnect;
 	if (w->skyWidth) f.skyPixels = (const float4*)w->skyImage.ptr, f.skyWidth = w->skyWidth, f.skyHeight = w->skyHeight;
 	f.epsilon = epsilon, f.width = (uint32_t)w->width, f.height = (uint32_t)w->height, f.pixelCount = f.width * f.height;
 	f.tilesX = (f.width + TILE_W - 1) / TILE_W, f.tilesY = (f.height + TILE_H - 1) / TILE_H;
@@ -755,29 +767,44 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 			cudaEventRecord( ev[0], stream );
 			if (TraceClosestDevice( w->rayO[in].ptr, w->rayD[in].ptr, (int)paths, w->hits.ptr, &dCounters[len].extensionRays )) return 1;
 			cudaEventRecord( ev[1], stream );
+			// shade k adds to the accumulator: it runs after connect k-1 so that every pixel sees its adds in one fixed order
+			if (overlap && len > 1) cudaStreamWaitEvent( stream, w->connectDone[len - 1], 0 );
+			cudaEventRecord( ev[2], stream );
 			shadeKernel<<<smCount * 8, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
 				(const float4*)w->state[in].ptr, (const float4*)w->info[in].ptr, (const float4*)w->hits.ptr, (float4*)w->rayO[out].ptr, (float4*)w->rayD[out].ptr,
 				(float4*)w->state[out].ptr, (float4*)w->info[out].ptr, (float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)instShadePool.ptr,
 				(const float4*)w->materials.ptr, w->accumulator(), dCounters );
 			stats.kernelLaunches++;
-			cudaEventRecord( ev[2], stream );
-			if (anyLight)
-			{
-				if (TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), &dCounters[len].shadowRays )) return 1;
-			}
 			cudaEventRecord( ev[3], stream );
-			ev += 4;
+			if (anyLight && overlap)
+			{
+				// connect k on its own stream, beside extend k+1: the tails of the two persistent launches fill each other
+				cudaEventRecord( w->shadeDone[len], stream );
+				cudaStreamWaitEvent( w->connectStream, w->shadeDone[len], 0 );
+				cudaEventRecord( ev[4], w->connectStream );
+				if (TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), &dCounters[len].shadowRays, w->connectStream, 1 )) return 1;
+				cudaEventRecord( ev[5], w->connectStream );
+				cudaEventRecord( w->connectDone[len], w->connectStream );
+			}
+			else
+			{
+				cudaEventRecord( ev[4], stream );
+				if (anyLight && TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), &dCounters[len].shadowRays )) return 1;
+				cudaEventRecord( ev[5], stream );
+			}
+			ev += 6;
 			in = out;
 		}
+		if (overlap) cudaStreamWaitEvent( stream, w->connectDone[maxLen], 0 );
 		// per-pass statistics (one synchronisation per pass, not per bounce)
 		WaveCounters hc[MAX_PATH_LENGTH + 2];
 		if ((e = cudaMemcpyAsync( hc, dCounters, sizeof( hc ), cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "counter read-back", e );
 		if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "Render", e );
 		ev = w->ev + 2;
-		for (int len = 1; len <= maxLen; len++, ev += 4)
+		for (int len = 1; len <= maxLen; len++, ev += 6)
 		{
 			float tExt = 0, tShade = 0, tShadow = 0;
-			cudaEventElapsedTime( &tExt, ev[0], ev[1] ), cudaEventElapsedTime( &tShade, ev[1], ev[2] ), cudaEventElapsedTime( &tShadow, ev[2], ev[3] );
+			cudaEventElapsedTime( &tExt, ev[0], ev[1] ), cudaEventElapsedTime( &tShade, ev[2], ev[3] ), cudaEventElapsedTime( &tShadow, ev[4], ev[5] );
 			const uint32_t n = hc[len].extensionRays;
 			if (len == 1) stats.primaryRayCount += n, stats.traceTime0 += tExt;
 			else if (len == 2) stats.bounce1RayCount += n, stats.traceTime1 += tExt;

@@ -18,17 +18,30 @@ from lighthouse2_b200 import core, scenes  # noqa: E402
 
 
 def stats_line(name, rc, frames, extra):
+    # per-class rates: waves one after the other (overlapConnect = 0), so that each event pair times one wave alone;
+    # frame time: the default schedule (connect wave of bounce k beside the extend wave of bounce k+1)
     acc = {}
+    rc.Setting("overlapConnect", 0)
     for _ in range(2):
         rc.Render(extra["view"], 1)
-    t0 = time.perf_counter()
     for _ in range(frames):
         rc.Render(extra["view"], 1)
         st = rc.GetCoreStats()
         for k, v in st.items():
             if isinstance(v, (int, float)):
                 acc[k] = acc.get(k, 0) + v
+    serial_render_ms = acc["renderTime"] / frames
+    rc.Setting("overlapConnect", 1)
+    for _ in range(2):
+        rc.Render(extra["view"], 1)
+    t0 = time.perf_counter()
+    overlapped = 0.0
+    for _ in range(frames):
+        rc.Render(extra["view"], 1)
+        overlapped += rc.GetCoreStats()["renderTime"]
     wall = (time.perf_counter() - t0) / frames * 1e3
+    acc["renderTime"] = overlapped
+    extra = dict(extra, render_ms_waves_serial=serial_render_ms)
     m = lambda n, t: (acc[n] / (acc[t] * 1e-3) / 1e6) if acc.get(t, 0) > 0 else None
     line = {"config": name, "frames": frames, "ms_per_frame_wall": wall, "render_ms": acc["renderTime"] / frames,
             "rays_per_frame": acc["totalRays"] / frames,
