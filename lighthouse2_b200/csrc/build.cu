@@ -1,0 +1,323 @@
+// build.cu -- GPU build of a mesh's 8-wide BVH topology.
+//
+// Replaces, for new or re-topologised meshes, the host SAH builder (bvh_builder.cpp) and with it what the reference does in
+// BVH2::Rebuild (lib/RenderCore_Bart/bvh.cpp:57-256) / optixAccelBuild (lib/rendercore_optix7/core_mesh.cpp:94-130):
+//   1. per-triangle boxes + centroid bounds                         (primBoundsKernel)
+//   2. 63-bit Morton codes of the centroids, radix sort             (mortonKernel, cub::DeviceRadixSort -- a library sort, not a hot op)
+//   3. binary radix tree over the sorted codes (Karras, "Maximizing Parallelism in the Construction of BVHs, Octrees, and
+//      k-d Trees", HPG 2012)                                        (radixTreeKernel)
+//   4. bottom-up boxes with one atomic counter per inner node      (binaryBoxesKernel)
+//   5. top-down collapse to 8-wide nodes, one launch per level: a wide node starts from the two children of its binary node and
+//      keeps opening the child with the largest area until it has eight; subtrees of at most three triangles become leaf
+//      slots; children go to the octant slot they are farthest against (same rule as AssignSlots in bvh_builder.cpp); node and
+//      triangle ranges are claimed with atomics, so a level is a contiguous index range as the refit expects (collapseKernel)
+// Only the TOPOLOGY is written (imask, meta, childBase, primBase, the primitive tag of every leaf-order triangle slot): the boxes,
+// frames, quantised planes and triangle records are then produced by the level-by-level refit (refit.cu), which a built mesh
+// needs anyway.  Any conservative hierarchy gives the reference's closest hits (the BLAS traversal never culls by distance,
+// bvh.cpp:281-298), so results equal the SAH tree's; the LBVH tree is faster to build and slower to trace.
+#include "kernels.h"
+#include <cub/device/device_radix_sort.cuh>
+#include <vector>
+
+namespace b200 {
+
+namespace {
+
+constexpr uint32_t LEAF = 0x80000000u; // child reference: bit 31 = sorted-leaf index, else inner binary node
+
+__device__ __forceinline__ int orderedInt( const float f ) { const int i = __float_as_int( f ); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float orderedFloat( const int i ) { return __int_as_float( i >= 0 ? i : i ^ 0x7fffffff ); }
+
+// 1. boxes of the triangles and the bounds of their centroids (ordered-int atomics; centroidBounds = {minx,miny,minz,maxx,maxy,maxz})
+__global__ void primBoundsKernel( const float4* __restrict__ verts, const uint32_t T, float4* __restrict__ primLo, float4* __restrict__ primHi, int* centroidBounds )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	float c[3] = { 0, 0, 0 };
+	const bool valid = i < T;
+	if (valid)
+	{
+		const float4 p0 = __ldg( verts + (size_t)i * 3 ), p1 = __ldg( verts + (size_t)i * 3 + 1 ), p2 = __ldg( verts + (size_t)i * 3 + 2 );
+		const float lx = fminf( p0.x, fminf( p1.x, p2.x ) ), ly = fminf( p0.y, fminf( p1.y, p2.y ) ), lz = fminf( p0.z, fminf( p1.z, p2.z ) );
+		const float hx = fmaxf( p0.x, fmaxf( p1.x, p2.x ) ), hy = fmaxf( p0.y, fmaxf( p1.y, p2.y ) ), hz = fmaxf( p0.z, fmaxf( p1.z, p2.z ) );
+		primLo[i] = make_float4( lx, ly, lz, 0 ), primHi[i] = make_float4( hx, hy, hz, 0 );
+		c[0] = 0.5f * (lx + hx), c[1] = 0.5f * (ly + hy), c[2] = 0.5f * (lz + hz);
+	}
+	for (int a = 0; a < 3; a++)
+	{
+		int lo = valid ? orderedInt( c[a] ) : 0x7fffffff, hi = valid ? orderedInt( c[a] ) : (int)0x80000000;
+		lo = __reduce_min_sync( 0xffffffffu, lo ), hi = __reduce_max_sync( 0xffffffffu, hi );
+		if ((threadIdx.x & 31) == 0) atomicMin( centroidBounds + a, lo ), atomicMax( centroidBounds + 3 + a, hi );
+	}
+}
+
+__device__ __forceinline__ uint64_t spread21( uint64_t x )
+{
+	x &= 0x1fffffull;
+	x = (x | x << 32) & 0x1f00000000ffffull;
+	x = (x | x << 16) & 0x1f0000ff0000ffull;
+	x = (x | x << 8) & 0x100f00f00f00f00full;
+	x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+	x = (x | x << 2) & 0x1249249249249249ull;
+	return x;
+}
+
+// 2. Morton code of every centroid on a 2^21 grid over the centroid bounds
+__global__ void mortonKernel( const float4* __restrict__ primLo, const float4* __restrict__ primHi, const uint32_t T, const int* __restrict__ centroidBounds,
+	uint64_t* __restrict__ keys, uint32_t* __restrict__ vals )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= T) return;
+	const float4 lo = primLo[i], hi = primHi[i];
+	const float c[3] = { 0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z) };
+	uint64_t q[3];
+	for (int a = 0; a < 3; a++)
+	{
+		const float mn = orderedFloat( centroidBounds[a] ), mx = orderedFloat( centroidBounds[3 + a] );
+		const float ext = mx - mn;
+		float t = ext > 0 ? (c[a] - mn) / ext : 0.f;
+		t = fminf( fmaxf( t, 0.f ), 1.f );
+		uint32_t g = (uint32_t)(t * 2097151.0f);
+		q[a] = g > 2097151u ? 2097151u : g;
+	}
+	keys[i] = spread21( q[0] ) << 2 | spread21( q[1] ) << 1 | spread21( q[2] );
+	vals[i] = i;
+}
+
+// common-prefix length of sorted keys i and j (-1 outside the array); equal keys fall back to the index, which keeps the tree well formed
+__device__ __forceinline__ int prefixLen( const uint64_t* __restrict__ keys, const int n, const int i, const int j )
+{
+	if (j < 0 || j >= n) return -1;
+	const uint64_t a = keys[i], b = keys[j];
+	return a != b ? __clzll( (long long)(a ^ b) ) : 64 + __clz( i ^ j );
+}
+
+// 3. Karras 2012, algorithm of section 4: inner node i of the binary radix tree over n sorted keys (n >= 2)
+__global__ void radixTreeKernel( const uint64_t* __restrict__ keys, const int n, uint32_t* __restrict__ childL, uint32_t* __restrict__ childR,
+	uint32_t* __restrict__ rangeFirst, uint32_t* __restrict__ rangeCount, uint32_t* __restrict__ parentInner, uint32_t* __restrict__ parentLeaf )
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n - 1) return;
+	const int d = prefixLen( keys, n, i, i + 1 ) - prefixLen( keys, n, i, i - 1 ) >= 0 ? 1 : -1;
+	const int dmin = prefixLen( keys, n, i, i - d );
+	int lmax = 2;
+	while (prefixLen( keys, n, i, i + lmax * d ) > dmin) lmax *= 2;
+	int l = 0;
+	for (int t = lmax / 2; t >= 1; t /= 2) if (prefixLen( keys, n, i, i + (l + t) * d ) > dmin) l += t;
+	const int j = i + l * d;
+	const int dnode = prefixLen( keys, n, i, j );
+	int s = 0;
+	for (int div = 2, t = (l + div - 1) / div; ; div *= 2, t = (l + div - 1) / div)
+	{
+		if (prefixLen( keys, n, i, i + (s + t) * d ) > dnode) s += t;
+		if (t <= 1) break;
+	}
+	const int gamma = i + s * d + min( d, 0 );
+	const int first = min( i, j ), last = max( i, j );
+	const uint32_t L = first == gamma ? (LEAF | (uint32_t)gamma) : (uint32_t)gamma;
+	const uint32_t R = last == gamma + 1 ? (LEAF | (uint32_t)(gamma + 1)) : (uint32_t)(gamma + 1);
+	childL[i] = L, childR[i] = R, rangeFirst[i] = (uint32_t)first, rangeCount[i] = (uint32_t)(last - first + 1);
+	if (L & LEAF) parentLeaf[gamma] = (uint32_t)i; else parentInner[gamma] = (uint32_t)i;
+	if (R & LEAF) parentLeaf[gamma + 1] = (uint32_t)i; else parentInner[gamma + 1] = (uint32_t)i;
+	if (i == 0) parentInner[0] = 0xffffffffu;
+}
+
+// 4. boxes of the binary inner nodes: every sorted leaf walks up; the second thread to reach a node merges its children
+__global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, const float4* __restrict__ primLo, const float4* __restrict__ primHi, const int n,
+	const uint32_t* __restrict__ childL, const uint32_t* __restrict__ childR, const uint32_t* __restrict__ parentInner, const uint32_t* __restrict__ parentLeaf,
+	float4* nodeLo, float4* nodeHi, uint32_t* visits )
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	uint32_t node = parentLeaf[i];
+	while (node != 0xffffffffu)
+	{
+		__threadfence();
+		if (atomicAdd( visits + node, 1u ) == 0) return; // the sibling subtree is not done yet
+		__threadfence();
+		float4 lo[2], hi[2];
+		const uint32_t c[2] = { childL[node], childR[node] };
+		for (int k = 0; k < 2; k++)
+		{
+			if (c[k] & LEAF) { const uint32_t p = sortedPrim[c[k] & ~LEAF]; lo[k] = primLo[p], hi[k] = primHi[p]; }
+			else lo[k] = __ldcg( nodeLo + c[k] ), hi[k] = __ldcg( nodeHi + c[k] );
+		}
+		__stcg( nodeLo + node, make_float4( fminf( lo[0].x, lo[1].x ), fminf( lo[0].y, lo[1].y ), fminf( lo[0].z, lo[1].z ), 0 ) );
+		__stcg( nodeHi + node, make_float4( fmaxf( hi[0].x, hi[1].x ), fmaxf( hi[0].y, hi[1].y ), fmaxf( hi[0].z, hi[1].z ), 0 ) );
+		node = parentInner[node];
+	}
+}
+
+struct CollapseArgs {
+	const uint32_t *sortedPrim, *childL, *childR, *rangeFirst, *rangeCount;
+	const float4 *primLo, *primHi, *nodeLo, *nodeHi;
+	uint32_t* wideToBinary;   // [maxNodes] binary inner node that wide node w represents
+	uint4* nodes;             // output, relative index 0 = this mesh's root (pool pointer already offset)
+	float4* tris;             // output triangle records (pool pointer already offset): only .w of the first float4 (the primitive tag) is written
+	uint32_t* counters;       // [0] wide nodes allocated, [1] leaf-order triangle slots allocated, [2] overflow flag
+	uint32_t nodeBase, triBase, maxNodes;
+};
+
+__device__ __forceinline__ void refBox( const CollapseArgs& a, const uint32_t ref, float lo[3], float hi[3], uint32_t& count )
+{
+	float4 l, h;
+	if (ref & LEAF) { const uint32_t p = a.sortedPrim[ref & ~LEAF]; l = a.primLo[p], h = a.primHi[p], count = 1; }
+	else l = a.nodeLo[ref], h = a.nodeHi[ref], count = a.rangeCount[ref];
+	lo[0] = l.x, lo[1] = l.y, lo[2] = l.z, hi[0] = h.x, hi[1] = h.y, hi[2] = h.z;
+}
+
+// 5. one level of the top-down collapse: thread w builds wide node `levelBegin + w` from its binary node
+__global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
+{
+	const uint32_t w = levelBegin + blockIdx.x * blockDim.x + threadIdx.x;
+	if (w >= levelEnd) return;
+	const uint32_t root = a.wideToBinary[w];
+	uint32_t ref[8], cnt[8];
+	float lo[8][3], hi[8][3];
+	int n = 2;
+	ref[0] = a.childL[root], ref[1] = a.childR[root];
+	refBox( a, ref[0], lo[0], hi[0], cnt[0] ), refBox( a, ref[1], lo[1], hi[1], cnt[1] );
+	// open the largest child that is still too big for a leaf slot until all eight slots are used
+	while (n < 8)
+	{
+		int best = -1;
+		float bestArea = -1.f;
+		for (int i = 0; i < n; i++) if (cnt[i] > 3)
+		{
+			const float x = hi[i][0] - lo[i][0], y = hi[i][1] - lo[i][1], z = hi[i][2] - lo[i][2], area = x * y + y * z + z * x;
+			if (area > bestArea) bestArea = area, best = i;
+		}
+		if (best < 0) break;
+		const uint32_t opened = ref[best];
+		ref[best] = a.childL[opened], ref[n] = a.childR[opened];
+		refBox( a, ref[best], lo[best], hi[best], cnt[best] ), refBox( a, ref[n], lo[n], hi[n], cnt[n] );
+		n++;
+	}
+	// octant slots: slot s is visited first by rays whose direction signs are the complement of s (traverse.cu), so a child
+	// goes to the slot whose sign vector it lies farthest against -- greedy over the 8 x n table, as AssignSlots does on the host
+	float nlo[3], nhi[3];
+	for (int c = 0; c < 3; c++)
+	{
+		nlo[c] = lo[0][c], nhi[c] = hi[0][c];
+		for (int i = 1; i < n; i++) nlo[c] = fminf( nlo[c], lo[i][c] ), nhi[c] = fmaxf( nhi[c], hi[i][c] );
+	}
+	int childInSlot[8] = { -1, -1, -1, -1, -1, -1, -1, -1 };
+	uint32_t done = 0;
+	for (int k = 0; k < n; k++)
+	{
+		float best = 3.0e38f;
+		int bs = 0, bi = 0;
+		for (int s = 0; s < 8; s++) if (childInSlot[s] < 0)
+			for (int i = 0; i < n; i++) if (!(done & (1u << i)))
+			{
+				float d = 0;
+				for (int c = 0; c < 3; c++)
+				{
+					const float rel = 0.5f * (lo[i][c] + hi[i][c]) - 0.5f * (nlo[c] + nhi[c]);
+					d += ((s >> (2 - c)) & 1) ? -rel : rel;
+				}
+				if (d < best) best = d, bs = s, bi = i;
+			}
+		childInSlot[bs] = bi, done |= 1u << bi;
+	}
+	uint32_t innerCount = 0, leafPrims = 0;
+	for (int i = 0; i < n; i++) if (cnt[i] > 3) innerCount++; else leafPrims += cnt[i];
+	const uint32_t childBase = innerCount ? atomicAdd( a.counters, innerCount ) : 0;
+	const uint32_t primBase = leafPrims ? atomicAdd( a.counters + 1, leafPrims ) : 0;
+	if (childBase + innerCount > a.maxNodes) { atomicExch( a.counters + 2, 1u ); return; }
+	uint32_t imask = 0, metaLo = 0, metaHi = 0, inner = 0, off = 0;
+	for (int s = 0; s < 8; s++)
+	{
+		const int i = childInSlot[s];
+		if (i < 0) continue;
+		uint32_t meta;
+		if (cnt[i] > 3)
+		{
+			imask |= 1u << s, meta = 0x20u | (24u + (uint32_t)s);
+			a.wideToBinary[childBase + inner] = ref[i];
+			inner++;
+		}
+		else
+		{
+			meta = (((1u << cnt[i]) - 1u) << 5) | off;
+			// the subtree's triangles are a contiguous run of the sorted order
+			const uint32_t first = (ref[i] & LEAF) ? (ref[i] & ~LEAF) : a.rangeFirst[ref[i]];
+			for (uint32_t k = 0; k < cnt[i]; k++)
+				a.tris[(size_t)(primBase + off + k) * 3].w = __uint_as_float( a.sortedPrim[first + k] );
+			off += cnt[i];
+		}
+		if (s < 4) metaLo |= meta << (8 * s); else metaHi |= meta << (8 * (s - 4));
+	}
+	uint4* np = a.nodes + (size_t)w * 5;
+	np[0] = make_uint4( 0, 0, 0, imask << 24 );
+	np[1] = make_uint4( a.nodeBase + childBase, a.triBase + primBase, metaLo, metaHi );
+	np[2] = np[3] = np[4] = make_uint4( 0, 0, 0, 0 );
+}
+
+} // namespace
+
+// Builds the wide-BVH topology of `T` triangles (dVerts = float4[3T], device) into nodes[0 .. nodeCount) / tris[0 .. T) (pool pointers
+// already offset to this mesh's base; indices stored in the nodes are absolute: + nodeBase / + triBase).  levelStart (relative,
+// size levels + 1) and nodeCount are returned for the refit, which the caller runs next.  T >= 4.
+cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, float4* tris, uint32_t nodeBase, uint32_t triBase, uint32_t maxNodes,
+	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount )
+{
+	cudaError_t e;
+	char* scratch = nullptr;
+	auto align = []( size_t x ) { return (x + 255) & ~(size_t)255; };
+	size_t sortBytes = 0;
+	cub::DeviceRadixSort::SortPairs( nullptr, sortBytes, (const uint64_t*)nullptr, (uint64_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)T, 0, 63, s );
+	// scratch layout
+	size_t off = 0;
+	auto take = [&]( size_t bytes ) { const size_t o = off; off += align( bytes ); return o; };
+	const size_t oPrimLo = take( (size_t)T * 16 ), oPrimHi = take( (size_t)T * 16 ), oKeys = take( (size_t)T * 8 ), oKeys2 = take( (size_t)T * 8 );
+	const size_t oVals = take( (size_t)T * 4 ), oVals2 = take( (size_t)T * 4 ), oSort = take( sortBytes );
+	const size_t oChildL = take( (size_t)T * 4 ), oChildR = take( (size_t)T * 4 ), oFirst = take( (size_t)T * 4 ), oCount = take( (size_t)T * 4 );
+	const size_t oParI = take( (size_t)T * 4 ), oParL = take( (size_t)T * 4 ), oVisits = take( (size_t)T * 4 );
+	const size_t oNodeLo = take( (size_t)T * 16 ), oNodeHi = take( (size_t)T * 16 ), oW2B = take( (size_t)maxNodes * 4 + 64 ), oSmall = take( 256 );
+	if ((e = cudaMallocAsync( (void**)&scratch, off, s )) != cudaSuccess) return e;
+	float4 *primLo = (float4*)(scratch + oPrimLo), *primHi = (float4*)(scratch + oPrimHi), *nodeLo = (float4*)(scratch + oNodeLo), *nodeHi = (float4*)(scratch + oNodeHi);
+	uint64_t *keys = (uint64_t*)(scratch + oKeys), *keys2 = (uint64_t*)(scratch + oKeys2);
+	uint32_t *vals = (uint32_t*)(scratch + oVals), *vals2 = (uint32_t*)(scratch + oVals2);
+	uint32_t *childL = (uint32_t*)(scratch + oChildL), *childR = (uint32_t*)(scratch + oChildR), *first = (uint32_t*)(scratch + oFirst), *count = (uint32_t*)(scratch + oCount);
+	uint32_t *parI = (uint32_t*)(scratch + oParI), *parL = (uint32_t*)(scratch + oParL), *visits = (uint32_t*)(scratch + oVisits), *w2b = (uint32_t*)(scratch + oW2B);
+	int* cbounds = (int*)(scratch + oSmall);
+	uint32_t* counters = (uint32_t*)(scratch + oSmall + 64);
+	auto done = [&]( cudaError_t err ) { cudaFreeAsync( scratch, s ); return err; };
+
+	const int initBounds[6] = { 0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000 };
+	const uint32_t initCounters[4] = { 1, 0, 0, 0 }; // wide node 0 = the root is taken
+	const uint32_t rootBinary = 0;
+	if ((e = cudaMemcpyAsync( cbounds, initBounds, sizeof( initBounds ), cudaMemcpyHostToDevice, s )) != cudaSuccess) return done( e );
+	if ((e = cudaMemcpyAsync( counters, initCounters, sizeof( initCounters ), cudaMemcpyHostToDevice, s )) != cudaSuccess) return done( e );
+	if ((e = cudaMemcpyAsync( w2b, &rootBinary, 4, cudaMemcpyHostToDevice, s )) != cudaSuccess) return done( e );
+	if ((e = cudaMemsetAsync( visits, 0, (size_t)T * 4, s )) != cudaSuccess) return done( e );
+	const uint32_t blocks = (T + 255) / 256;
+	primBoundsKernel<<<blocks, 256, 0, s>>>( dVerts, T, primLo, primHi, cbounds );
+	mortonKernel<<<blocks, 256, 0, s>>>( primLo, primHi, T, cbounds, keys, vals );
+	if ((e = cub::DeviceRadixSort::SortPairs( scratch + oSort, sortBytes, keys, keys2, vals, vals2, (int)T, 0, 63, s )) != cudaSuccess) return done( e );
+	radixTreeKernel<<<blocks, 256, 0, s>>>( keys2, (int)T, childL, childR, first, count, parI, parL );
+	binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, parI, parL, nodeLo, nodeHi, visits );
+	if ((e = cudaGetLastError()) != cudaSuccess) return done( e );
+	CollapseArgs a;
+	a.sortedPrim = vals2, a.childL = childL, a.childR = childR, a.rangeFirst = first, a.rangeCount = count;
+	a.primLo = primLo, a.primHi = primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi;
+	a.wideToBinary = w2b, a.nodes = nodes, a.tris = tris, a.counters = counters;
+	a.nodeBase = nodeBase, a.triBase = triBase, a.maxNodes = maxNodes;
+	levelStart.clear();
+	levelStart.push_back( 0 );
+	uint32_t begin = 0, end = 1;
+	while (begin < end)
+	{
+		collapseKernel<<<(end - begin + 127) / 128, 128, 0, s>>>( a, begin, end );
+		uint32_t h[3];
+		if ((e = cudaMemcpyAsync( h, counters, 12, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
+		if ((e = cudaStreamSynchronize( s )) != cudaSuccess) return done( e );
+		if (h[2] || h[0] > maxNodes) return done( cudaErrorMemoryAllocation ); // more wide nodes than reserved
+		levelStart.push_back( end );
+		begin = end, end = h[0];
+	}
+	nodeCount = end;
+	return done( cudaSuccess );
+}
+
+} // namespace b200

@@ -2,6 +2,7 @@
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
+#include <vector>
 
 namespace b200 {
 
@@ -47,5 +48,9 @@ struct RefitArgs {
 };
 cudaError_t LaunchRefitTop( const RefitArgs& a, const uint32_t* levelStart, int nTop, cudaStream_t s ); // levels [0,nTop) in one launch
 cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t levelEnd, cudaStream_t s );
+
+// ---- GPU build of the wide-BVH topology (build.cu); the caller runs the refit afterwards -----------------------
+cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, float4* tris, uint32_t nodeBase, uint32_t triBase, uint32_t maxNodes,
+	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount );
 
 } // namespace b200

@@ -143,6 +143,7 @@ int RenderCore::Setting( const char* name, float value )
 		return 0; // accepted; used by the filtering cores only (clampValue goes to the shade stage, wavefront.cu)
 	// B200-specific keys
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
+	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 0.5f; return 0; }
 	if (!strcmp( name, "twoStreams" )) { twoStreams = value >= 0.5f; return 0; }
 	if (!strcmp( name, "zeroCopy" )) { zeroCopy = value >= 0.5f; return 0; }
 	if (!strcmp( name, "pinnedChunks" )) { pinnedChunks = (int)value; return 0; }
@@ -158,6 +159,71 @@ int RenderCore::Setting( const char* name, float value )
 
 
 // ---- geometry -----------------------------------------------------------------------------------------
+// shading record per ORIGINAL primitive: geometric normal (CoreTri::Nx,Ny,Nz when supplied, common_classes.h:69-71,
+// else from the vertices) + CoreTri::material (:67); what the shade stage reads via instanceTriangles[PRIMIDX]
+// in the reference (lib/rendercore_optix7/kernels/pathtracer.h:70-100)
+struct ShadeRec { float n[3]; uint32_t material; };
+static void makeShadeRecords( const float* vertexData, const uint32_t T, const void* coreTris, std::vector<ShadeRec>& shade )
+{
+	shade.resize( T );
+	for (uint32_t i = 0; i < T; i++)
+	{
+		const float *p0 = vertexData + (size_t)i * 12, *p1 = p0 + 4, *p2 = p0 + 8;
+		const float e1[3] = { p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2] }, e2[3] = { p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2] };
+		float n[3] = { e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0] };
+		const float l2 = n[0] * n[0] + n[1] * n[1] + n[2] * n[2], il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
+		shade[i].n[0] = n[0] * il, shade[i].n[1] = n[1] * il, shade[i].n[2] = n[2] * il, shade[i].material = 0;
+		if (coreTris)
+		{
+			const char* ct = (const char*)coreTris + (size_t)i * 176;
+			float N[3];
+			memcpy( &N[0], ct + 44, 4 ), memcpy( &N[1], ct + 60, 4 ), memcpy( &N[2], ct + 76, 4 );
+			if (N[0] * N[0] + N[1] * N[1] + N[2] * N[2] > 0.5f) shade[i].n[0] = N[0], shade[i].n[1] = N[1], shade[i].n[2] = N[2];
+			memcpy( &shade[i].material, ct + 28, 4 );
+		}
+	}
+}
+
+// SetGeometry with Setting gpuBuild = 1: the vertices go up once, the topology is built on the device (build.cu) and the refit
+// that follows fills boxes, quantised planes and triangle records.  Nothing but 12 bytes per level comes back to the host.
+int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T, const void* coreTris, double t0 )
+{
+	MeshRec m;
+	m.nodeBase = blasNodeEnd, m.triBase = triEnd, m.triCount = T;
+	if ((uint64_t)m.triBase + T + 32 >= (1ull << 27)) return fail( "SetGeometry: more than 2^27 triangles in one core (queue entries carry 27-bit triangle indices)" );
+	const uint32_t maxNodes = T / 2 + 64;
+	// shading records: the refit below writes the geometric normals; only CoreTri::material has to come from the host
+	std::vector<ShadeRec> shade;
+	if (coreTris)
+	{
+		shade.resize( T );
+		for (uint32_t i = 0; i < T; i++)
+		{
+			shade[i].n[0] = shade[i].n[1] = shade[i].n[2] = 0;
+			memcpy( &shade[i].material, (const char*)coreTris + (size_t)i * 176 + 28, 4 );
+		}
+	}
+	cudaError_t e;
+	if ((e = nodePool.reserve( (size_t)(m.nodeBase + maxNodes + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
+	if ((e = triPool.reserve( (size_t)(m.triBase + T + 1) * 48, true, stream )) != cudaSuccess) return fail( "triangle pool", e );
+	if ((e = shadePool.reserve( (size_t)(m.triBase + T + 1) * 16, true, stream )) != cudaSuccess) return fail( "shading pool", e );
+	if ((e = vertStage.reserve( (size_t)T * 48 + 16, false, stream )) != cudaSuccess) return fail( "vertex staging", e );
+	if ((e = cudaMemcpyAsync( vertStage.ptr, vertexData, (size_t)T * 48, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "vertex upload", e );
+	if (coreTris) e = cudaMemcpyAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, shade.data(), (size_t)T * 16, cudaMemcpyHostToDevice, stream );
+	else e = cudaMemsetAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, 0, (size_t)T * 16, stream );
+	if (e != cudaSuccess) return fail( "shading upload", e );
+	if ((e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
+		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount )) != cudaSuccess) return fail( "GPU BVH build", e );
+	m.built = true;
+	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
+	meshes.push_back( m );
+	if (RefitDevice( meshIdx, vertStage.ptr, (int)(3 * T), false )) return 1; // boxes, planes, triangle records; fetches the root box
+	stats.bvhBuildTime += (float)(nowMs() - t0);
+	stats.wideNodeCount = blasNodeEnd, stats.triangleCount = triEnd;
+	return 0;
+}
+
+
 // CoreAPI_Base::SetGeometry (core_api_base.h:108).  vertexData is float4[3T], triangle-expanded.  The first
 // call for a mesh builds its wide BVH on the host and appends it to the pools; later calls with the same
 // triangle count refit on the GPU (the reference instead rebuilds: rendercore.cpp:78).
@@ -179,6 +245,7 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	}
 	const double t0 = nowMs();
 	const uint32_t T = (uint32_t)triangleCount;
+	if (gpuBuild && T >= 64) return buildOnDevice( meshIdx, vertexData, T, coreTris, t0 );
 	std::vector<Aabb> boxes( T );
 	for (uint32_t i = 0; i < T; i++)
 	{
@@ -201,27 +268,8 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 		t.prim = prim, t.pad1 = t.pad2 = 0;
 		for (int a = 0; a < 3; a++) t.v0[a] = p0[a], t.e1[a] = p1[a] - p0[a], t.e2[a] = p2[a] - p0[a];
 	}
-	// shading record per ORIGINAL primitive: geometric normal (CoreTri::Nx,Ny,Nz when supplied, common_classes.h:69-71,
-	// else from the vertices) + CoreTri::material (:67); what the shade stage reads via instanceTriangles[PRIMIDX]
-	// in the reference (lib/rendercore_optix7/kernels/pathtracer.h:70-100)
-	struct ShadeRec { float n[3]; uint32_t material; };
-	std::vector<ShadeRec> shade( T );
-	for (uint32_t i = 0; i < T; i++)
-	{
-		const float *p0 = vertexData + (size_t)i * 12, *p1 = p0 + 4, *p2 = p0 + 8;
-		const float e1[3] = { p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2] }, e2[3] = { p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2] };
-		float n[3] = { e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0] };
-		const float l2 = n[0] * n[0] + n[1] * n[1] + n[2] * n[2], il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
-		shade[i].n[0] = n[0] * il, shade[i].n[1] = n[1] * il, shade[i].n[2] = n[2] * il, shade[i].material = 0;
-		if (coreTris)
-		{
-			const char* ct = (const char*)coreTris + (size_t)i * 176;
-			float N[3];
-			memcpy( &N[0], ct + 44, 4 ), memcpy( &N[1], ct + 60, 4 ), memcpy( &N[2], ct + 76, 4 );
-			if (N[0] * N[0] + N[1] * N[1] + N[2] * N[2] > 0.5f) shade[i].n[0] = N[0], shade[i].n[1] = N[1], shade[i].n[2] = N[2];
-			memcpy( &shade[i].material, ct + 28, 4 );
-		}
-	}
+	std::vector<ShadeRec> shade;
+	makeShadeRecords( vertexData, T, coreTris, shade );
 	cudaError_t e;
 	if ((e = nodePool.reserve( (size_t)(m.nodeBase + m.nodeCount + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
 	if ((e = triPool.reserve( (size_t)(m.triBase + T + 1) * 48, true, stream )) != cudaSuccess) return fail( "triangle pool", e );

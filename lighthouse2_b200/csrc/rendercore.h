@@ -84,6 +84,7 @@ public:
 private:
 	int ensureToplevel();
 	int hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit );
+	int buildOnDevice( int meshIdx, const float* vertexData, uint32_t T, const void* coreTris, double t0 );
 	static constexpr int MAX_CHUNKS = 12;
 	cudaStream_t copyIn = nullptr, copyOut = nullptr, stream2 = nullptr;
 	cudaEvent_t chunkEv[2 * MAX_CHUNKS + 1] = {};
@@ -98,7 +99,7 @@ private:
 	bool tlasDirty = true;
 	// scratch
 	DeviceBuffer rayO, rayD, hitBuf, bitBuf, vertStage, nodeLo, nodeHi, stepNodes, stepTris;
-	bool countSteps = false, allowRefit = true;
+	bool countSteps = false, allowRefit = true, gpuBuild = false; // gpuBuild: new meshes get an LBVH built on the device (build.cu)
 	bool zeroCopy = true, twoStreams = true; int pinnedChunks = 1, zeroCopyBelow = 400000; // pinned host ray planes are fetched by the kernel itself (Setting zeroCopy / pinnedChunks)
 	int hostChunks = 4, hostChunkMode = 0; // chunk schedule of the host-buffer waves (Setting hostChunks / hostChunkMode)
 	int buildThreads = 0;

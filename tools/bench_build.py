@@ -1,0 +1,32 @@
+#!/usr/bin/env python
+"""BVH build time, host SAH builder vs the GPU builder (Setting gpuBuild), as SetGeometry wall time (upload included) on the C2
+sphere field and a C3-class soup.  Usage: python tools/bench_build.py [tris ...]"""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np  # noqa: E402
+from lighthouse2_b200 import core, scenes  # noqa: E402
+
+sizes = [int(a) for a in sys.argv[1:]] or [1_000_000, 10_000_000]
+for n in sizes:
+    for name, gen in (("sphere field", scenes.sphere_field), ("soup", scenes.triangle_soup)):
+        verts = gen(n)
+        v4 = np.ones((verts.shape[0] * 3, 4), np.float32); v4[:, :3] = verts.reshape(-1, 3)
+        row = {"scene": name, "triangles": int(verts.shape[0])}
+        for gpu in (0, 1):
+            best = 1e9
+            for rep in range(2 if gpu == 0 and n > 2_000_000 else 3):
+                rc = core.RenderCoreB200(0)
+                rc.Setting("gpuBuild", gpu)
+                t0 = time.perf_counter()
+                rc.SetGeometry(0, v4)
+                best = min(best, time.perf_counter() - t0)
+                nodes = rc.GetCoreStats()["wideNodeCount"]
+                rc.Shutdown()
+            row["gpu_build_s" if gpu else "host_build_s"] = round(best, 4)
+            row["gpu_nodes" if gpu else "host_nodes"] = nodes
+        print(json.dumps(row), flush=True)

@@ -4,7 +4,7 @@ rays / trace time per wave class from CoreStats (apps/imguiapp/main.cpp:230-233)
   C1  1K-triangle mesh, 640x360
   C3  10M-triangle soup, 1080p, primary + 4 diffuse bounces (+ NEE shadow rays)
   C4  1000 instances x 100K-triangle BLAS, 1080p x 2 spp, per frame: GPU refit of the BLAS + TLAS rebuild + primary/shadow
-Usage: python tools/bench_configs.py [c1] [c3] [c4] [--frames N]"""
+Usage: python tools/bench_configs.py [c1] [c3] [c3gpu] [c4] [refit] [--frames N]   (c3gpu: the same with Setting gpuBuild = 1)"""
 import json
 import os
 import sys
@@ -89,8 +89,9 @@ def c1(frames):
     rc.Shutdown()
 
 
-def c3(frames, n_tris=10_000_000):
+def c3(frames, n_tris=10_000_000, gpu_build=0):
     rc = core.RenderCoreB200(0)
+    rc.Setting("gpuBuild", gpu_build)
     t0 = time.perf_counter()
     verts = scenes.triangle_soup(n_tris)
     t1 = time.perf_counter()
@@ -99,7 +100,7 @@ def c3(frames, n_tris=10_000_000):
     st = rc.GetCoreStats()
     rc.SetTarget(1920, 1080, 1); rc.SetPointLight((0.0, 120.0, -60.0), (2e4, 2e4, 1.8e4)); rc.SetSky((0.4, 0.5, 0.7)); rc.Setting("maxPathLength", 5); rc.Setting("russianRoulette", 0)
     view = scenes.view_pyramid(width=1920, height=1080, **scenes.C3_CAMERA)
-    stats_line(f"C3 {n_tris} tri soup 1080p 4 bounces", rc, frames,
+    stats_line(f"C3 {n_tris} tri soup 1080p 4 bounces" + (" (BVH built on the GPU)" if gpu_build else ""), rc, frames,
                {"view": view, "scene_gen_s": t1 - t0, "bvh_build_upload_s": t2 - t1, "wide_nodes": st["wideNodeCount"],
                 "scene_mb": (st["wideNodeCount"] * 80 + st["triangleCount"] * 48) / 1e6})
     rc.Shutdown()
@@ -147,7 +148,7 @@ def c4(frames, n_inst=1000, n_tris=100_000):
 
 
 if __name__ == "__main__":
-    args = [a for a in sys.argv[1:] if not a.startswith("--")] or ["c1", "c3", "c4"]
+    args = [a for a in sys.argv[1:] if not a.startswith("--") and not a.isdigit()] or ["c1", "c3", "c4"]
     frames = int(sys.argv[sys.argv.index("--frames") + 1]) if "--frames" in sys.argv else 5
     for a in args:
-        {"c1": c1, "c3": c3, "c4": c4, "refit": refit_c2}[a](frames)
+        {"c1": c1, "c3": c3, "c3gpu": lambda f: c3(f, gpu_build=1), "c4": c4, "refit": refit_c2}[a](frames)
