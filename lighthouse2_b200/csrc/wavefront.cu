@@ -29,7 +29,14 @@ namespace {
 constexpr int TILE_W = 32, TILE_H = 8, TILE_PIXELS = TILE_W * TILE_H;
 constexpr float INVPI = 0.31830988618379067154f, TWOPI = 6.28318530717958647692f;
 
-struct WaveCounters { uint32_t extensionRays, shadowRays, pad0, pad1; }; // one per path length (index 0: probe result)
+constexpr int MAX_PATH_LENGTH = 16; // MAXPATHLENGTH of the optix7 core (core_settings.h:24)
+// Device-resident wave counters (the reference's Counters, core_settings.h:103-117), uint32 words:
+//   [2 len - 1] = extension rays of path length len (written by generate for len = 1, by shade( len - 1 ) otherwise)
+//   [2 len]     = shadow rays emitted by shade( len )
+// so the two counts one shade launch appends to, [2 len] and [2 len + 1], form ONE aligned 64-bit word and are claimed together.
+constexpr int PROBE_BASE = 2 * (MAX_PATH_LENGTH + 1), COUNTER_WORDS = PROBE_BASE + 4; // probe: inst, prim, dist bits, valid
+__host__ __device__ __forceinline__ int extCounter( const int len ) { return 2 * len - 1; }
+__host__ __device__ __forceinline__ int shadowCounter( const int len ) { return 2 * len; }
 
 struct FrameParams {
 	float pos[3], p1[3], right[3], up[3]; // right = p2 - p1, up = p3 - p1
@@ -68,28 +75,61 @@ __device__ __forceinline__ uint32_t laneMaskLt()
 	return m;
 }
 
-// warp-aggregated append (stream compaction): all 32 lanes call; returns the slot of lanes with want == true
-__device__ __forceinline__ uint32_t warpAppend( uint32_t* counter, bool want )
+// Block-aggregated appends (stream compaction).  One atomic per CTA and iteration: every append of a wave goes to the same
+// address, and same-address atomics serialise in L2 -- with one atomic per WARP the shade kernel spent half its time waiting for
+// them (ncu: 47 % of the stall samples on the atomicAdd).  All threads of the block call, every iteration, in uniform control flow.
+template <int WARPS> __device__ __forceinline__ uint32_t blockAppend( uint32_t* counter, const bool want, uint32_t* sWarp /* [WARPS + 1] */ )
 {
-	const uint32_t m = __ballot_sync( 0xffffffffu, want );
-	if (!m) return 0;
-	const uint32_t leader = __ffs( m ) - 1;
-	uint32_t base = 0;
-	if ((threadIdx.x & 31) == leader) base = atomicAdd( counter, __popc( m ) );
-	base = __shfl_sync( 0xffffffffu, base, leader );
-	return base + __popc( m & laneMaskLt() );
+	const uint32_t m = __ballot_sync( 0xffffffffu, want ), warp = threadIdx.x >> 5;
+	if ((threadIdx.x & 31) == 0) sWarp[warp] = __popc( m );
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		uint32_t total = 0;
+		for (int i = 0; i < WARPS; i++) { const uint32_t c = sWarp[i]; sWarp[i] = total, total += c; }
+		sWarp[WARPS] = total ? atomicAdd( counter, total ) : 0;
+	}
+	__syncthreads();
+	const uint32_t slot = sWarp[WARPS] + sWarp[warp] + __popc( m & laneMaskLt() );
+	__syncthreads(); // sWarp is reused by the next call
+	return slot;
+}
+// two streams at once: counts[0] += #wantA, counts[1] += #wantB with one 64-bit atomic (counts is 8-byte aligned)
+template <int WARPS> __device__ __forceinline__ void blockAppend2( uint32_t* counts, const bool wantA, const bool wantB, uint32_t* sWarp /* [2 WARPS + 2] */,
+	uint32_t& slotA, uint32_t& slotB )
+{
+	const uint32_t mA = __ballot_sync( 0xffffffffu, wantA ), mB = __ballot_sync( 0xffffffffu, wantB ), warp = threadIdx.x >> 5;
+	if ((threadIdx.x & 31) == 0) sWarp[warp] = __popc( mA ), sWarp[WARPS + warp] = __popc( mB );
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		uint32_t tA = 0, tB = 0;
+		for (int i = 0; i < WARPS; i++)
+		{
+			const uint32_t a = sWarp[i], b = sWarp[WARPS + i];
+			sWarp[i] = tA, sWarp[WARPS + i] = tB, tA += a, tB += b;
+		}
+		unsigned long long base = 0;
+		if (tA | tB) base = atomicAdd( reinterpret_cast<unsigned long long*>( counts ), (unsigned long long)tA | ((unsigned long long)tB << 32) );
+		sWarp[2 * WARPS] = (uint32_t)base, sWarp[2 * WARPS + 1] = (uint32_t)(base >> 32);
+	}
+	__syncthreads();
+	slotA = sWarp[2 * WARPS] + sWarp[warp] + __popc( mA & laneMaskLt() );
+	slotB = sWarp[2 * WARPS + 1] + sWarp[WARPS + warp] + __popc( mB & laneMaskLt() );
+	__syncthreads();
 }
 
 // ---- primary rays (GPU cores: rendercore_optix7/optix/.optix.cu:66-123, RenderCore_OptixPrime_B/kernels/camera.h:40-94) ----------
 // u = (x + r0) / w, v = (y + r1) / h, P = p1 + u right + v up, O = point on the lens, D = normalize(P - O); optional barrel distortion.
 __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParams f, float4* __restrict__ rayO, float4* __restrict__ rayD,
-	float4* __restrict__ pathState, float4* __restrict__ pathInfo, WaveCounters* counters )
+	float4* __restrict__ pathState, float4* __restrict__ pathInfo, uint32_t* counters )
 {
+	__shared__ uint32_t sWarp[9];
 	const uint32_t total = f.ownTiles * TILE_PIXELS * f.samplesThisPass;
 	const uint32_t stride = gridDim.x * blockDim.x;
-	for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < total; base += stride)
+	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) // block-uniform trip count (blockAppend synchronises)
 	{
-		const uint32_t job = base + (threadIdx.x & 31);
+		const uint32_t job = base + threadIdx.x;
 		bool valid = job < total;
 		uint32_t x = 0, y = 0, sample = 0;
 		if (valid)
@@ -101,7 +141,7 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 			x = (tile % f.tilesX) * TILE_W + (inTile % TILE_W), y = (tile / f.tilesX) * TILE_H + inTile / TILE_W;
 			valid = x < f.width && y < f.height;
 		}
-		const uint32_t slot = warpAppend( &counters[1].extensionRays, valid );
+		const uint32_t slot = blockAppend<8>( counters + extCounter( 1 ), valid, sWarp );
 		if (!valid) continue;
 		const uint32_t pixelIdx = x + y * f.width, pathIdx = pixelIdx + (f.sampleBase + sample) * f.pixelCount;
 		float r0 = 0.5f, r1 = 0.5f;
@@ -341,19 +381,26 @@ __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 // ---- shade (lib/rendercore_optix7/kernels/pathtracer.h:54-240, BSDF = lib/sharedBSDFs/lambert.h without transmission) -------------
 // Path state: rayO/rayD (the extension ray), pathState = (throughput rgb, postponed bsdf pdf), pathInfo = (pathIdx | flags << 28,
 // normal at the previous vertex).  One thread per path; new extension / shadow rays are compacted with warp-aggregated appends.
-__global__ void __launch_bounds__( 128 ) shadeKernel( const FrameParams f, const int pathLength, const int maxPathLength,
+#ifndef B200_SHADE_MIN_BLOCKS
+#define B200_SHADE_MIN_BLOCKS 1
+#endif
+#ifndef B200_SHADE_GRID
+#define B200_SHADE_GRID 8
+#endif
+__global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( const FrameParams f, const int pathLength, const int maxPathLength,
 	const float4* __restrict__ rayO, const float4* __restrict__ rayD, const float4* __restrict__ pathState, const float4* __restrict__ pathInfo,
 	const float4* __restrict__ hits,
 	float4* __restrict__ rayOout, float4* __restrict__ rayDout, float4* __restrict__ pathStateOut, float4* __restrict__ pathInfoOut,
 	float4* __restrict__ conO, float4* __restrict__ conD, float4* __restrict__ conE,
 	const float4* __restrict__ shade, const float4* __restrict__ instShade, const float4* __restrict__ materials,
-	float4* accumulator, WaveCounters* counters )
+	float4* accumulator, uint32_t* counters )
 {
-	const uint32_t count = counters[pathLength].extensionRays;
+	__shared__ uint32_t sWarp[2 * 4 + 2];
+	const uint32_t count = counters[extCounter( pathLength )];
 	const uint32_t stride = gridDim.x * blockDim.x;
-	for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < count; base += stride)
+	for (uint32_t base = blockIdx.x * blockDim.x; base < count; base += stride) // block-uniform trip count (blockAppend2 synchronises)
 	{
-		const uint32_t job = base + (threadIdx.x & 31);
+		const uint32_t job = base + threadIdx.x;
 		bool wantShadow = false, wantExt = false;
 		V3 so = v3( 0.f, 0.f, 0.f ), sl = so, se = so, eo = so, er = so, et = so, en = so;
 		float sdist = 0, epdf = 0;
@@ -378,7 +425,7 @@ __global__ void __launch_bounds__( 128 ) shadeKernel( const FrameParams f, const
 			{
 				const uint32_t inst = __float_as_uint( hit.y );
 				if (pathLength == 1 && (int)pixelIdx == f.probePixel && pathIdx < f.pixelCount)
-					counters[0].extensionRays = inst, counters[0].shadowRays = (uint32_t)prim, counters[0].pad0 = __float_as_uint( hit.w ); // pathtracer.h:94-97
+					counters[PROBE_BASE] = inst, counters[PROBE_BASE + 1] = (uint32_t)prim, counters[PROBE_BASE + 2] = __float_as_uint( hit.w ), counters[PROBE_BASE + 3] = 1; // pathtracer.h:94-97
 				const float4 m0 = __ldg( instShade + inst * 4 ), m1 = __ldg( instShade + inst * 4 + 1 ), m2 = __ldg( instShade + inst * 4 + 2 ),
 							 info = __ldg( instShade + inst * 4 + 3 );
 				const float4 sh = __ldg( shade + __float_as_uint( info.x ) + prim );
@@ -491,14 +538,14 @@ __global__ void __launch_bounds__( 128 ) shadeKernel( const FrameParams f, const
 				}
 			}
 		}
-		const uint32_t sslot = warpAppend( &counters[pathLength].shadowRays, wantShadow );
+		uint32_t sslot, eslot;
+		blockAppend2<4>( counters + shadowCounter( pathLength ), wantShadow, wantExt, sWarp, sslot, eslot ); // [2 len] shadow, [2 len + 1] = extension of len + 1
 		if (wantShadow)
 		{
 			conO[sslot] = make_float4( so.x, so.y, so.z, f.epsilon );
 			conD[sslot] = make_float4( sl.x, sl.y, sl.z, sdist );
 			conE[sslot] = make_float4( se.x, se.y, se.z, __uint_as_float( pixelIdx ) );
 		}
-		const uint32_t eslot = warpAppend( &counters[pathLength + 1].extensionRays, wantExt );
 		if (wantExt)
 		{
 			rayOout[eslot] = make_float4( eo.x, eo.y, eo.z, f.epsilon );
@@ -517,8 +564,6 @@ __global__ void finalizeKernel( const float4* __restrict__ accumulator, float4* 
 	const float4 a = accumulator[i];
 	frame[i] = make_float4( a.x * scale, a.y * scale, a.z * scale, 1.0f );
 }
-
-constexpr int MAX_PATH_LENGTH = 16; // MAXPATHLENGTH of the optix7 core (core_settings.h:24)
 
 } // namespace
 
@@ -588,7 +633,7 @@ int RenderCore::SetTarget( int width, int height, int spp )
 	const size_t px = (size_t)width * height;
 	cudaError_t e;
 	if ((e = w->accumOwn.reserve( px * 16, false, stream )) != cudaSuccess || (e = w->frame.reserve( px * 16, false, stream )) != cudaSuccess) return fail( "SetTarget buffers", e );
-	if ((e = w->counters.reserve( sizeof( WaveCounters ) * (MAX_PATH_LENGTH + 2), false, stream )) != cudaSuccess) return fail( "SetTarget counters", e );
+	if ((e = w->counters.reserve( sizeof( uint32_t ) * COUNTER_WORDS, false, stream )) != cudaSuccess) return fail( "SetTarget counters", e );
 	if ((e = cudaMemsetAsync( w->accumulator(), 0, px * 16, stream )) != cudaSuccess) return fail( "SetTarget clear", e );
 	w->samplesTaken = 0;
 	for (cudaEvent_t& ev : w->ev) if (!ev && (e = cudaEventCreate( &ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
@@ -738,7 +783,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		for (DeviceBuffer* b : bufs) if ((e = b->reserve( (size_t)cap * 16, false, stream )) != cudaSuccess) return fail( "path buffers", e );
 		w->capacity = cap;
 	}
-	WaveCounters* dCounters = (WaveCounters*)w->counters.ptr;
+	uint32_t* dCounters = (uint32_t*)w->counters.ptr;
 	const int maxLen = w->maxPathLength;
 	memset( &stats.totalRays, 0, (char*)&stats.probedInstid - (char*)&stats.totalRays );
 	cudaEvent_t frameA = w->ev[0], frameB = w->ev[1];
@@ -753,7 +798,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		const uint32_t period = PATHIDX_MASK / f.pixelCount - (uint32_t)w->spp + 1;
 		f.sampleBase = globalSample % period;
 		f.R0 = (globalSample / period + 1) * 7907u;
-		if ((e = cudaMemsetAsync( dCounters, 0, sizeof( WaveCounters ) * (MAX_PATH_LENGTH + 2), stream )) != cudaSuccess) return fail( "counter clear", e );
+		if ((e = cudaMemsetAsync( dCounters, 0, sizeof( uint32_t ) * COUNTER_WORDS, stream )) != cudaSuccess) return fail( "counter clear", e );
 		const uint32_t paths = perSample * f.samplesThisPass;
 		if (!paths) continue;
 		generateEyeRaysKernel<<<smCount * 4, 256, 0, stream>>>( f, (float4*)w->rayO[0].ptr, (float4*)w->rayD[0].ptr, (float4*)w->state[0].ptr, (float4*)w->info[0].ptr,
@@ -765,12 +810,12 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		{
 			const int out = in ^ 1;
 			cudaEventRecord( ev[0], stream );
-			if (TraceClosestDevice( w->rayO[in].ptr, w->rayD[in].ptr, (int)paths, w->hits.ptr, &dCounters[len].extensionRays )) return 1;
+			if (TraceClosestDevice( w->rayO[in].ptr, w->rayD[in].ptr, (int)paths, w->hits.ptr, dCounters + extCounter( len ) )) return 1;
 			cudaEventRecord( ev[1], stream );
 			// shade k adds to the accumulator: it runs after connect k-1 so that every pixel sees its adds in one fixed order
 			if (overlap && len > 1) cudaStreamWaitEvent( stream, w->connectDone[len - 1], 0 );
 			cudaEventRecord( ev[2], stream );
-			shadeKernel<<<smCount * 8, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
+			shadeKernel<<<smCount * B200_SHADE_GRID, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
 				(const float4*)w->state[in].ptr, (const float4*)w->info[in].ptr, (const float4*)w->hits.ptr, (float4*)w->rayO[out].ptr, (float4*)w->rayD[out].ptr,
 				(float4*)w->state[out].ptr, (float4*)w->info[out].ptr, (float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)instShadePool.ptr,
 				(const float4*)w->materials.ptr, w->accumulator(), dCounters );
@@ -782,14 +827,14 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 				cudaEventRecord( w->shadeDone[len], stream );
 				cudaStreamWaitEvent( w->connectStream, w->shadeDone[len], 0 );
 				cudaEventRecord( ev[4], w->connectStream );
-				if (TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), &dCounters[len].shadowRays, w->connectStream, 1 )) return 1;
+				if (TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), dCounters + shadowCounter( len ), w->connectStream, 1 )) return 1;
 				cudaEventRecord( ev[5], w->connectStream );
 				cudaEventRecord( w->connectDone[len], w->connectStream );
 			}
 			else
 			{
 				cudaEventRecord( ev[4], stream );
-				if (anyLight && TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), &dCounters[len].shadowRays )) return 1;
+				if (anyLight && TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), dCounters + shadowCounter( len ) )) return 1;
 				cudaEventRecord( ev[5], stream );
 			}
 			ev += 6;
@@ -797,7 +842,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		}
 		if (overlap) cudaStreamWaitEvent( stream, w->connectDone[maxLen], 0 );
 		// per-pass statistics (one synchronisation per pass, not per bounce)
-		WaveCounters hc[MAX_PATH_LENGTH + 2];
+		uint32_t hc[COUNTER_WORDS];
 		if ((e = cudaMemcpyAsync( hc, dCounters, sizeof( hc ), cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "counter read-back", e );
 		if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "Render", e );
 		ev = w->ev + 2;
@@ -805,17 +850,17 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		{
 			float tExt = 0, tShade = 0, tShadow = 0;
 			cudaEventElapsedTime( &tExt, ev[0], ev[1] ), cudaEventElapsedTime( &tShade, ev[2], ev[3] ), cudaEventElapsedTime( &tShadow, ev[4], ev[5] );
-			const uint32_t n = hc[len].extensionRays;
+			const uint32_t n = hc[extCounter( len )];
 			if (len == 1) stats.primaryRayCount += n, stats.traceTime0 += tExt;
 			else if (len == 2) stats.bounce1RayCount += n, stats.traceTime1 += tExt;
 			else stats.deepRayCount += n, stats.traceTimeX += tExt;
-			stats.totalExtensionRays += n, stats.totalShadowRays += hc[len].shadowRays;
+			stats.totalExtensionRays += n, stats.totalShadowRays += hc[shadowCounter( len )];
 			stats.shadowTraceTime += tShadow, stats.shadeTime += tShade;
 		}
-		if (f.probePixel >= 0 && s0 == 0 && hc[0].pad0)
+		if (f.probePixel >= 0 && s0 == 0 && hc[PROBE_BASE + 3])
 		{
-			stats.probedInstid = (int32_t)hc[0].extensionRays, stats.probedTriid = (int32_t)hc[0].shadowRays;
-			memcpy( &stats.probedDist, &hc[0].pad0, 4 );
+			stats.probedInstid = (int32_t)hc[PROBE_BASE], stats.probedTriid = (int32_t)hc[PROBE_BASE + 1];
+			memcpy( &stats.probedDist, &hc[PROBE_BASE + 2], 4 );
 		}
 	}
 	w->samplesTaken += (uint32_t)w->spp;
