@@ -67,12 +67,12 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def measured_traffic():
-    """dram bytes per launch of the extend kernel from the committed ncu --set full capture (profiles/), or None."""
+def measured_traffic(key="extend_dram_bytes_per_launch"):
+    """dram bytes per launch of the extend kernel (or another entry) from the committed ncu --set full capture (profiles/), or None."""
     p = os.path.join(ROOT, "profiles", "roofline.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("extend_dram_bytes_per_launch")
+            return json.load(open(p)).get(key)
         except Exception:
             return None
     return None
@@ -435,7 +435,7 @@ def run_b200(args):
             "rays": rays,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(),
                          "kernel": "traceKernel<closest> (extend wave)", "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY, "peak_source": peak_src,
-                         "note": "stream roofline of a latency/L2-bound traversal kernel; see DESIGN.md"},
+                         "note": "stream roofline of an instruction-issue-bound traversal kernel; see DESIGN.md", "ncu": measured_traffic("extend_ncu")},
             "gpu_launches": int(launches),
             "clocks": clock_info,
         }
