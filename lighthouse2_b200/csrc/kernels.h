@@ -25,7 +25,7 @@ struct TraceArgs {
 	const uint32_t* countPtr;  // optional device-resident ray count (wavefront counters); overrides `count`
 	uint32_t count;
 	uint32_t tlasRoot;         // absolute node index of the top-level root
-	uint32_t magic;            // 0x4B000000 (2^23 as float bits); passed as an argument on purpose, see qbyte() in traverse.cu
+	uint32_t magic;            // byte-decode constant, set by the launchers; passed as an argument on purpose, see qbyte() / qpair() in traverse.cu
 	uint32_t* stepNodes;       // optional per-ray counters (COUNT variants)
 	uint32_t* stepTris;
 };

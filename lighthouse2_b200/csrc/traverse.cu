@@ -20,6 +20,11 @@
 // Compiled with -fmad=false: every float op below rounds separately unless written as __fmaf_rn, so the
 // ISECT_REFERENCE triangle test and instance entry are bit-identical to the reference's scalar C++.
 #include "kernels.h"
+#include <cuda_fp16.h>
+
+#ifndef B200_HALF_DECODE
+#define B200_HALF_DECODE 1 // node planes: two bytes per PRMT + HADD2.F32 (1) or one PRMT per byte (0); see qpair / qbyte
+#endif
 
 namespace b200 {
 
@@ -67,6 +72,19 @@ template <int J> __device__ __forceinline__ float qbyte( uint32_t q, uint32_t K 
 	else if (J == 2) asm( "prmt.b32 %0, %1, %2, 0x7624;" : "=r"( r ) : "r"( q ), "r"( K ) );
 	else asm( "prmt.b32 %0, %1, %2, 0x7634;" : "=r"( r ) : "r"( q ), "r"( K ) );
 	return __uint_as_float( r );
+}
+
+// Two bytes per PRMT: bytes 2P and 2P+1 of q become the half2 (1024 + b0, 1024 + b1) -- 0x64 from K = 0x64646464 is the high
+// byte of each half -- and two HADD2.F32 turn them into floats.  The conversions run on the FMA pipe, the PRMT on the ALU pipe,
+// which is the one the node test saturates (145 ALU-pipe vs 80 FMA-pipe instructions per node with one PRMT per byte; both
+// pipes take one warp instruction every two cycles).
+template <int P> __device__ __forceinline__ void qpair( const uint32_t q, const uint32_t K, float& f0, float& f1 )
+{
+	uint32_t r;
+	if (P == 0) asm( "prmt.b32 %0, %1, %2, 0x4140;" : "=r"( r ) : "r"( q ), "r"( K ) );
+	else asm( "prmt.b32 %0, %1, %2, 0x4342;" : "=r"( r ) : "r"( q ), "r"( K ) );
+	const __half2 h = *reinterpret_cast<const __half2*>( &r );
+	f0 = __low2float( h ), f1 = __high2float( h );
 }
 
 struct RayState {
@@ -201,10 +219,18 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 	// plane t = (p + b*s - O) * idir = F*A + B with F = 2^23 + 256 b (see qbyte): A = s*idir/256,
 	// B = ((p - O) - 32768 s) * idir.  Far planes are scaled by 1+2^-21 so float rounding can only widen a box.
 	const float WIDEN = 1.0f + 4.76837158e-7f;
+#if B200_HALF_DECODE
+	// F = 1024 + b: A = s*idir, B = ((p - O) - 1024 s) * idir
+	const float ax = sx * r.ix, ay = sy * r.iy, az = sz * r.iz;
+	const float bx = __fmaf_rn( -1024.f, sx, __uint_as_float( n0.x ) - r.ox ) * r.ix;
+	const float by = __fmaf_rn( -1024.f, sy, __uint_as_float( n0.y ) - r.oy ) * r.iy;
+	const float bz = __fmaf_rn( -1024.f, sz, __uint_as_float( n0.z ) - r.oz ) * r.iz;
+#else
 	const float ax = (sx * 0.00390625f) * r.ix, ay = (sy * 0.00390625f) * r.iy, az = (sz * 0.00390625f) * r.iz;
 	const float bx = __fmaf_rn( -32768.f, sx, __uint_as_float( n0.x ) - r.ox ) * r.ix;
 	const float by = __fmaf_rn( -32768.f, sy, __uint_as_float( n0.y ) - r.oy ) * r.iy;
 	const float bz = __fmaf_rn( -32768.f, sz, __uint_as_float( n0.z ) - r.oz ) * r.iz;
+#endif
 	const float axf = ax * WIDEN, ayf = ay * WIDEN, azf = az * WIDEN, bxf = bx * WIDEN, byf = by * WIDEN, bzf = bz * WIDEN;
 	const bool nx = r.dx < 0, ny = r.dy < 0, nz = r.dz < 0;
 	uint32_t hitmask = 0;
@@ -221,10 +247,28 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 		const uint32_t innerMask4 = sign_extend_s8x4( isInner4 << 3 );
 		const uint32_t bitIndex4 = (meta4 ^ (r.octinv4 & innerMask4)) & 0x1f1f1f1fu;
 		const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+#if B200_HALF_DECODE
+		float fnx[4], fny[4], fnz[4], ffx[4], ffy[4], ffz[4];
+		qpair<0>( nearx, K, fnx[0], fnx[1] ), qpair<1>( nearx, K, fnx[2], fnx[3] ), qpair<0>( neary, K, fny[0], fny[1] ), qpair<1>( neary, K, fny[2], fny[3] );
+		qpair<0>( nearz, K, fnz[0], fnz[1] ), qpair<1>( nearz, K, fnz[2], fnz[3] ), qpair<0>( farx, K, ffx[0], ffx[1] ), qpair<1>( farx, K, ffx[2], ffx[3] );
+		qpair<0>( fary, K, ffy[0], ffy[1] ), qpair<1>( fary, K, ffy[2], ffy[3] ), qpair<0>( farz, K, ffz[0], ffz[1] ), qpair<1>( farz, K, ffz[2], ffz[3] );
+#pragma unroll
+		for (int j = 0; j < 4; j++)
+		{
+			const float tn = fmaxf( max3f( __fmaf_rn( fnx[j], ax, bx ), __fmaf_rn( fny[j], ay, by ), __fmaf_rn( fnz[j], az, bz ) ), r.tmin );
+			const float tf = fminf( min3f( __fmaf_rn( ffx[j], axf, bxf ), __fmaf_rn( ffy[j], ayf, byf ), __fmaf_rn( ffz[j], azf, bzf ) ), r.t );
+			if (tn <= tf)
+			{
+				const uint32_t bits = (childBits4 >> (8 * j)) & 0xffu, idx = (bitIndex4 >> (8 * j)) & 0xffu;
+				hitmask |= bits << idx;
+			}
+		}
+#else
 		testChild<0>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
 		testChild<1>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
 		testChild<2>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
 		testChild<3>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+#endif
 	}
 	return hitmask;
 }
@@ -265,7 +309,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	const uint32_t total = a.countPtr ? __ldg( a.countPtr ) : a.count;
 	const uint4* __restrict__ nodes = a.nodes;
 	const float4* __restrict__ tris = a.tris;
-	const uint32_t K = a.magic; // 0x4B000000, see qbyte
+	const uint32_t K = a.magic; // see qbyte / qpair; set by the launchers
 
 	RayState r = {};
 	uint32_t rayIdx = 0, hitPrim = 0, hitInst = 0, hitBary = 0, curInst = 0, nNodes = 0, nTris = 0;
@@ -527,8 +571,10 @@ template <typename K> int blocksPerSM( K kernel )
 }
 } // namespace
 
-cudaError_t LaunchExtend( const TraceArgs& a, IsectMode mode, bool countSteps, int smCount, cudaStream_t s )
+cudaError_t LaunchExtend( const TraceArgs& args, IsectMode mode, bool countSteps, int smCount, cudaStream_t s )
 {
+	TraceArgs a = args;
+	a.magic = B200_HALF_DECODE ? 0x64646464u : 0x4B000000u;
 	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
 	if (e != cudaSuccess) return e;
 	void ( *k )( const TraceArgs ) = mode == ISECT_REFERENCE
@@ -539,8 +585,10 @@ cudaError_t LaunchExtend( const TraceArgs& a, IsectMode mode, bool countSteps, i
 	return cudaGetLastError();
 }
 
-cudaError_t LaunchShadow( const TraceArgs& a, IsectMode mode, int smCount, cudaStream_t s )
+cudaError_t LaunchShadow( const TraceArgs& args, IsectMode mode, int smCount, cudaStream_t s )
 {
+	TraceArgs a = args;
+	a.magic = B200_HALF_DECODE ? 0x64646464u : 0x4B000000u;
 	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
 	if (e != cudaSuccess) return e;
 	void ( *k )( const TraceArgs ) = mode == ISECT_REFERENCE ? traceKernel<ISECT_REFERENCE, true, false> : traceKernel<ISECT_WATERTIGHT, true, false>;
