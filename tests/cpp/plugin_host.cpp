@@ -1,0 +1,135 @@
+// plugin_host.cpp -- TEST INFRASTRUCTURE: a stand-in for the reference's RenderSystem that loads RenderCore_B200 the way
+// CoreAPI_Base::CreateCoreAPI does (lib/RenderSystem/core_api_base.cpp:97-132: dlopen RTLD_NOW|RTLD_GLOBAL, dlsym CreateCore /
+// DestroyCore, CreateCore(), Init()) and then issues the per-frame call order of RenderSystem::SynchronizeSceneData / Render
+// (lib/RenderSystem/rendersystem.cpp:214-238) through the C++ vtable only.  The scene comes from a binary file written by the
+// pytest side (tests/test_plugin_gpu.py); the frame and the CoreStats go back the same way.
+//
+//   plugin_host <libRenderCore_B200.so> <scene.bin> <out.bin>
+#include "../../include/lh2_abi.h"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <dlfcn.h>
+#include <vector>
+
+using namespace lh2abi;
+
+static std::vector<char> readAll( const char* path )
+{
+	FILE* f = fopen( path, "rb" );
+	if (!f) { fprintf( stderr, "cannot open %s\n", path ); exit( 2 ); }
+	fseek( f, 0, SEEK_END );
+	long n = ftell( f );
+	fseek( f, 0, SEEK_SET );
+	std::vector<char> b( n );
+	if (fread( b.data(), 1, n, f ) != (size_t)n) exit( 2 );
+	fclose( f );
+	return b;
+}
+
+struct Reader {
+	const char* p;
+	template <class T> T get() { T v; memcpy( &v, p, sizeof( T ) ); p += sizeof( T ); return v; }
+	const void* bytes( size_t n ) { const void* q = p; p += n; return q; }
+};
+
+int main( int argc, char** argv )
+{
+	if (argc < 4) return 2;
+	void* lib = dlopen( argv[1], RTLD_NOW | RTLD_GLOBAL );
+	if (!lib) { fprintf( stderr, "dlopen: %s\n", dlerror() ); return 3; }
+	typedef CoreAPI_Base* (*createCoreFunction)();
+	typedef void (*destroyCoreFunction)();
+	createCoreFunction createCore = (createCoreFunction)dlsym( lib, "CreateCore" );
+	destroyCoreFunction destroyCore = (destroyCoreFunction)dlsym( lib, "DestroyCore" );
+	if (!createCore || !destroyCore) { fprintf( stderr, "CreateCore / DestroyCore not exported\n" ); return 3; }
+	CoreAPI_Base* api = createCore();
+	api->Init(); // the loader calls Init a second time (core_api_base.cpp:128-129)
+
+	std::vector<char> file = readAll( argv[2] );
+	Reader r{ file.data() };
+	const int width = r.get<int>(), height = r.get<int>(), spp = r.get<int>(), frames = r.get<int>();
+	const int probeX = r.get<int>(), probeY = r.get<int>();
+	ViewPyramid view = r.get<ViewPyramid>();
+	// SynchronizeSceneData order: sky, textures, materials, geometry, instances, toplevel, lights (rendersystem.cpp:214-222)
+	const int skyW = r.get<int>(), skyH = r.get<int>();
+	const float3_t* sky = (const float3_t*)r.bytes( (size_t)skyW * skyH * 12 );
+	mat4_t identity;
+	memset( &identity, 0, sizeof( identity ) );
+	float* cells = (float*)&identity;
+	cells[0] = cells[5] = cells[10] = cells[15] = 1;
+	if (skyW) api->SetSkyData( sky, (uint)skyW, (uint)skyH, identity );
+	api->SetTextures( nullptr, 0 );
+	const int materialCount = r.get<int>();
+	std::vector<CoreMaterial> materials( materialCount );
+	for (int i = 0; i < materialCount; i++)
+	{
+		memset( &materials[i], 0, sizeof( CoreMaterial ) );
+		const float* c = (const float*)r.bytes( 16 ); // rgb, roughness
+		materials[i].color.value.x = c[0], materials[i].color.value.y = c[1], materials[i].color.value.z = c[2];
+		materials[i].color.textureID = -1;
+		materials[i].roughness.value = c[3];
+	}
+	api->SetMaterials( materials.data(), materialCount );
+	const int meshCount = r.get<int>();
+	for (int m = 0; m < meshCount; m++)
+	{
+		const int triCount = r.get<int>();
+		const float4_t* verts = (const float4_t*)r.bytes( (size_t)triCount * 48 );
+		const CoreTri* tris = (const CoreTri*)r.bytes( (size_t)triCount * sizeof( CoreTri ) );
+		api->SetGeometry( m, verts, triCount * 3, triCount, tris, nullptr );
+	}
+	const int instanceCount = r.get<int>();
+	for (int i = 0; i < instanceCount; i++)
+	{
+		const int mesh = r.get<int>();
+		mat4_t T = r.get<mat4_t>();
+		api->SetInstance( i, mesh, T );
+	}
+	api->SetInstance( instanceCount, -1, identity ); // end of the instance stream (rendersystem.cpp:167-169)
+	api->UpdateToplevel();
+	const int nArea = r.get<int>(), nPoint = r.get<int>(), nSpot = r.get<int>(), nDir = r.get<int>();
+	const CoreLightTri* area = (const CoreLightTri*)r.bytes( (size_t)nArea * sizeof( CoreLightTri ) );
+	const CorePointLight* point = (const CorePointLight*)r.bytes( (size_t)nPoint * sizeof( CorePointLight ) );
+	const CoreSpotLight* spot = (const CoreSpotLight*)r.bytes( (size_t)nSpot * sizeof( CoreSpotLight ) );
+	const CoreDirectionalLight* dir = (const CoreDirectionalLight*)r.bytes( (size_t)nDir * sizeof( CoreDirectionalLight ) );
+	api->SetLights( area, nArea, point, nPoint, spot, nSpot, dir, nDir );
+
+	GLTexture target;
+	target.ID = 0, target.width = (uint)width, target.height = (uint)height;
+	api->SetTarget( &target, (uint)spp );
+	int2_t probe;
+	probe.x = probeX, probe.y = probeY;
+	api->SetProbePos( probe );
+	// the six settings RenderSystem::Render sends every frame (rendersystem.cpp:228-236), then B200's own keys
+	api->Setting( "epsilon", 1e-4f ), api->Setting( "clampValue", 10.0f ), api->Setting( "clampDirect", 10.0f ), api->Setting( "clampIndirect", 10.0f );
+	api->Setting( "filter", 0 ), api->Setting( "TAA", 0 );
+	api->Setting( "jitter", 0 ), api->Setting( "maxPathLength", 4 );
+	CoreStats stats;
+	for (int f = 0; f < frames; f++)
+	{
+		api->Render( view, f == 0 ? Restart : Converge );
+		stats = api->GetCoreStats();
+	}
+	// pixels: the reference cores write a GL texture; this core keeps the frame in a device buffer with an extern "C" read-back
+	typedef void* (*pluginCoreFunction)();
+	typedef int (*readFunction)( void*, float* );
+	pluginCoreFunction pluginCore = (pluginCoreFunction)dlsym( lib, "b200_plugin_core" );
+	readFunction readFrame = (readFunction)dlsym( lib, "b200_read_frame" ), readAccumulator = (readFunction)dlsym( lib, "b200_read_accumulator" );
+	if (!pluginCore || !readFrame || !readAccumulator) return 4;
+	std::vector<float> frame( (size_t)width * height * 4 ), accumulator( (size_t)width * height * 4 );
+	if (readFrame( pluginCore(), frame.data() ) || readAccumulator( pluginCore(), accumulator.data() )) return 5;
+	FILE* out = fopen( argv[3], "wb" );
+	if (!out) return 6;
+	fwrite( frame.data(), 4, frame.size(), out );
+	fwrite( accumulator.data(), 4, accumulator.size(), out );
+	fwrite( &stats, sizeof( stats ), 1, out );
+	const char* name = stats.deviceName ? stats.deviceName : "";
+	char nameBuf[64] = {};
+	strncpy( nameBuf, name, 63 );
+	fwrite( nameBuf, 1, 64, out );
+	fclose( out );
+	api->Shutdown();
+	destroyCore();
+	return 0;
+}

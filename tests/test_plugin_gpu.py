@@ -1,0 +1,87 @@
+"""The drop-in boundary end to end: a C++ host (tests/cpp/plugin_host.cpp) loads libRenderCore_B200.so exactly as the
+reference's loader does (dlopen + CreateCore, lib/RenderSystem/core_api_base.cpp:97-132), drives it through the CoreAPI_Base
+vtable in RenderSystem's call order with the reference's own structs (CoreTri, CoreMaterial, CoreLightTri, ...), and must
+produce the same frame, bit for bit, as the flat C ABI driven from Python."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from lighthouse2_b200 import core, scenes
+from test_wavefront_gpu import _lit_scene
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _write_scene(path, sc, view, w, h, spp, frames, probe):
+    case = sc["case"]
+    with open(path, "wb") as f:
+        f.write(struct.pack("<6i", w, h, spp, frames, probe[0], probe[1]))
+        vp = np.zeros(17, np.float32)
+        vp[0:3], vp[3:6], vp[6:9], vp[9:12] = view["pos"], view["p1"], view["p2"], view["p3"]
+        vp[12:17] = (0.0, 0.01, 0.01, 1.0, 0.0)
+        f.write(vp.tobytes())
+        sky = sc["sky"]
+        f.write(struct.pack("<2i", sky.shape[1], sky.shape[0]))
+        f.write(np.ascontiguousarray(sky, np.float32).tobytes())
+        mats = np.ascontiguousarray(sc["materials"], np.float32)
+        f.write(struct.pack("<i", len(mats)))
+        f.write(mats.tobytes())
+        f.write(struct.pack("<i", len(case["meshes"])))
+        for i, m in enumerate(case["meshes"]):
+            v4 = np.ones((len(m) * 3, 4), np.float32)
+            v4[:, :3] = m.reshape(-1, 3)
+            f.write(struct.pack("<i", len(m)))
+            f.write(v4.tobytes())
+            f.write(core.core_tris(m, sc["prim_materials"][i]).tobytes())
+        f.write(struct.pack("<i", len(case["instances"])))
+        for mesh, mat in case["instances"]:
+            f.write(struct.pack("<i", mesh))
+            f.write(np.ascontiguousarray(np.eye(4, dtype=np.float32).reshape(16) if mat is None else mat, np.float32).tobytes())
+        f.write(struct.pack("<4i", len(sc["area"]), len(sc["point"]), len(sc["spot"]), len(sc["dir"])))
+        for k in ("area", "point", "spot", "dir"):
+            f.write(np.ascontiguousarray(sc[k], np.float32).tobytes())
+
+
+def test_cpp_host_through_the_vtable_equals_the_c_abi(tmp_path):
+    sc = _lit_scene()
+    w, h, spp, frames = 160, 90, 1, 2
+    probe = (w // 2, h // 2)
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    exe = str(tmp_path / "plugin_host")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-o", exe, os.path.join(HERE, "cpp", "plugin_host.cpp"), "-ldl"], check=True)
+    scene_bin, out_bin = str(tmp_path / "scene.bin"), str(tmp_path / "out.bin")
+    _write_scene(scene_bin, sc, view, w, h, spp, frames, probe)
+    r = subprocess.run([exe, core.LIB_PATH, scene_bin, out_bin], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    raw = open(out_bin, "rb").read()
+    n = w * h * 4
+    frame = np.frombuffer(raw, np.float32, n).reshape(h, w, 4)
+    acc = np.frombuffer(raw, np.float32, n, offset=n * 4).reshape(h, w, 4)
+    stats = raw[2 * n * 4:2 * n * 4 + 104]
+    name = raw[2 * n * 4 + 104:].split(b"\0")[0].decode()
+    # CoreStats (core_api_base.h:30-61): char* @0, SMcount..VRAM @8, texel counts @24, bvhBuildTime @36, totalRays @40, ... probed @92
+    sm, cc_major = struct.unpack_from("<2I", stats, 8)
+    total, ext, shadow = struct.unpack_from("<3I", stats, 40)
+    render_time, primary = struct.unpack_from("<fI", stats, 52)
+    probed_inst, probed_tri, probed_dist = struct.unpack_from("<iif", stats, 92)
+    assert sm == 148 and cc_major == 10 and "B200" in name
+    assert primary == w * h and total == ext + shadow and 0 < render_time < 1.0  # seconds
+
+    # the same frames through the flat C ABI
+    from test_wavefront_gpu import _lit_core
+    rc = _lit_core(sc, w, h, spp=spp, max_len=4)
+    rc._chk(rc.lib.b200_set_probe(rc.h, *probe))
+    rc.Render(view, converge=1)
+    rc.Render(view, converge=0)
+    ref_acc, ref_frame, st = rc.ReadAccumulator(), rc.ReadFrame(), rc.GetCoreStats()
+    rc.Shutdown()
+    assert np.array_equal(acc.view(np.uint32), ref_acc.view(np.uint32))
+    assert np.array_equal(frame.view(np.uint32), ref_frame.view(np.uint32))
+    assert np.allclose(frame[..., :3] * frames * spp, acc[..., :3], rtol=1e-6)
+    assert (total, ext, shadow) == (st["totalRays"], st["totalExtensionRays"], st["totalShadowRays"])
+    assert (probed_inst, probed_tri) == (st["probedInstid"], st["probedTriid"]) and probed_tri >= 0
+    assert probed_dist == pytest.approx(st["probedDist"], rel=1e-6)
