@@ -156,3 +156,37 @@ def test_step_counters(oracles):
     nodes, tris = rc.StepCounters(len(O4))
     assert nodes.min() >= 1 and nodes.mean() < 200 and tris.mean() < 200
     rc.Shutdown()
+
+
+def test_errors_are_reported_not_swallowed():
+    """The C ABI returns non-zero with a message (the plugin shim turns that into the reference's FatalError + exit,
+    lib/platform/system.cpp:221-236); nothing falls back silently."""
+    rc = core.RenderCoreB200(0)
+    tri = scenes.grid_mesh(2, 2)
+    v4 = np.ones((len(tri) * 3, 4), np.float32)
+    lib, h = rc.lib, rc.h
+    assert lib.b200_set_geometry(h, 0, v4.ctypes.data, len(tri) * 3 - 1, len(tri), None, None) != 0  # vertexCount != 3 T
+    assert b"vertexCount" in lib.b200_last_error()
+    assert lib.b200_set_geometry(h, 3, v4.ctypes.data, len(tri) * 3, len(tri), None, None) != 0      # mesh indices must be dense
+    assert lib.b200_set_geometry(h, 0, None, len(tri) * 3, len(tri), None, None) != 0                # null vertices
+    rc.SetGeometry(0, tri)
+    with pytest.raises(core.B200Error):
+        rc.SetInstance(0, 5)                                                                          # unknown mesh
+    with pytest.raises(core.B200Error):
+        rc.Refit(0, tri[:-1])                                                                         # triangle count changed
+    with pytest.raises(core.B200Error):
+        rc.Setting("noSuchKey", 1)
+    with pytest.raises(core.B200Error):
+        rc.Setting("maxPathLength", 99)
+    view = scenes.view_pyramid(width=16, height=16, **scenes.C1_CAMERA)
+    with pytest.raises(core.B200Error):
+        rc.Render(view, 1)                                                                            # before SetTarget
+    with pytest.raises(core.B200Error):
+        rc.SetTarget(0, 16, 1)
+    rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
+    O, D = scenes.random_rays(8, 2.0, seed=1)
+    O4, D4 = core.pack_rays(O, D)
+    assert lib.b200_trace_closest(h, O4.ctypes.data, D4.ctypes.data, -1, None) != 0                   # negative count
+    hits = rc.TraceClosest(O4, D4)                                                                    # and the core still works afterwards
+    assert hits.shape == (8, 4)
+    rc.Shutdown()
