@@ -93,6 +93,9 @@ B200_API int b200_set_sky_data( b200_core* c, const float* rgb, int width, int h
 B200_API int b200_set_materials( b200_core* c, const void* coreMaterials, int count );
 /* headless shortcut for hosts without CoreMaterial structs: (albedo rgb, roughness) per material index (CoreTri::material) */
 B200_API int b200_set_material_colors( b200_core* c, const float* rgba, int count );
+/* the full record the shade stage keeps, 12 floats per material: albedo rgb, roughness | transmission, eta, smooth-normals flag, 0 |
+ * absorption rgb, 0 (CoreMaterial color / roughness / transmission / eta / flags & SMOOTH / absorption) */
+B200_API int b200_set_material_table( b200_core* c, const float* props12, int count );
 /* multi-GPU: render into a caller-owned device accumulator float4[w*h] (e.g. a torch tensor that NCCL reduces);
  * NULL = the core's own.  After the gather, b200_finalize( total samples ) rebuilds the frame from it. */
 B200_API int b200_set_accumulator_buffer( b200_core* c, void* dAccumulator );

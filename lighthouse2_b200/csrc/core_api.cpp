@@ -58,6 +58,7 @@ int b200_set_lights( b200_core* c, const void* area, int nArea, const void* poin
 int b200_set_sky_data( b200_core* c, const float* rgb, int width, int height ) { FORWARD( c, SetSkyData( rgb, width, height ) ) }
 int b200_set_materials( b200_core* c, const void* coreMaterials, int count ) { FORWARD( c, SetMaterials( coreMaterials, count ) ) }
 int b200_set_material_colors( b200_core* c, const float* rgba, int count ) { FORWARD( c, SetMaterialColors( rgba, count ) ) }
+int b200_set_material_table( b200_core* c, const float* props12, int count ) { FORWARD( c, SetMaterialTable( props12, count ) ) }
 int b200_set_accumulator_buffer( b200_core* c, void* dAcc ) { FORWARD( c, SetAccumulatorBuffer( dAcc ) ) }
 int b200_finalize( b200_core* c, uint32_t totalSamples ) { FORWARD( c, Finalize( totalSamples ) ) }
 int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, int n, const void* dE4, void* dAcc ) { FORWARD( c, TraceConnectDevice( dO4, dD4, n, dE4, dAcc ) ) }

@@ -116,7 +116,7 @@ RenderCore::~RenderCore()
 	cudaSetDevice( device );
 	cudaDeviceSynchronize();
 	DestroyWavefront( wf );
-	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &instShadePool, &rayO, &rayD, &hitBuf, &bitBuf, &vertStage, &nodeLo, &nodeHi,
+	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &vnormPool, &instShadePool, &rayO, &rayD, &hitBuf, &bitBuf, &vertStage, &nodeLo, &nodeHi,
 		&stepNodes, &stepTris };
 	for (DeviceBuffer* b : all) b->release();
 	if (evA) cudaEventDestroy( evA );
@@ -184,6 +184,33 @@ static void makeShadeRecords( const float* vertexData, const uint32_t T, const v
 	}
 }
 
+// per-vertex normals of a mesh (CoreTri::vN0/vN1/vN2, common_classes.h:66-71) for SMOOTH materials: 3 float4 per ORIGINAL primitive,
+// indexed like the shading records.  The pool exists only once a mesh has supplied CoreTris; other meshes read zeros (= flat).
+int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
+{
+	if (!coreTris && !vnormPool.ptr) return 0;
+	cudaError_t e;
+	const size_t oldBytes = vnormPool.bytes, need = (size_t)(m.triBase + m.triCount + 1) * 48;
+	if ((e = vnormPool.reserve( need, true, stream )) != cudaSuccess) return fail( "vertex normal pool", e );
+	if (vnormPool.bytes > oldBytes && (e = cudaMemsetAsync( (char*)vnormPool.ptr + oldBytes, 0, vnormPool.bytes - oldBytes, stream )) != cudaSuccess) return fail( "vertex normal pool", e );
+	char* dst = (char*)vnormPool.ptr + (size_t)m.triBase * 48;
+	if (!coreTris) e = cudaMemsetAsync( dst, 0, (size_t)m.triCount * 48, stream );
+	else
+	{
+		std::vector<float> vn( (size_t)m.triCount * 12 );
+		for (uint32_t i = 0; i < m.triCount; i++)
+		{
+			const char* ct = (const char*)coreTris + (size_t)i * 176;
+			float* o = &vn[(size_t)i * 12];
+			memcpy( o, ct + 32, 12 ), memcpy( o + 4, ct + 48, 12 ), memcpy( o + 8, ct + 64, 12 );
+			o[3] = o[7] = o[11] = 0;
+		}
+		e = cudaMemcpyAsync( dst, vn.data(), vn.size() * 4, cudaMemcpyHostToDevice, stream );
+		if (e == cudaSuccess) e = cudaStreamSynchronize( stream ); // the staging vector dies here
+	}
+	return e == cudaSuccess ? 0 : fail( "vertex normal upload", e );
+}
+
 // SetGeometry with Setting gpuBuild = 1: the vertices go up once, the topology is built on the device (build.cu) and the refit
 // that follows fills boxes, quantised planes and triangle records.  Nothing but 12 bytes per level comes back to the host.
 int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T, const void* coreTris, double t0 )
@@ -217,6 +244,7 @@ int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T,
 	m.built = true;
 	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
 	meshes.push_back( m );
+	if (uploadVertexNormals( m, coreTris )) return 1;
 	if (RefitDevice( meshIdx, vertStage.ptr, (int)(3 * T), false )) return 1; // boxes, planes, triangle records; fetches the root box
 	stats.bvhBuildTime += (float)(nowMs() - t0);
 	stats.wideNodeCount = blasNodeEnd, stats.triangleCount = triEnd;
@@ -234,7 +262,11 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	if (meshIdx > (int)meshes.size()) return fail( "SetGeometry: mesh indices must arrive densely" );
 	if (meshIdx < (int)meshes.size() && meshes[meshIdx].built)
 	{
-		if ((uint32_t)triangleCount == meshes[meshIdx].triCount && allowRefit) return Refit( meshIdx, vertexData, vertexCount );
+		if ((uint32_t)triangleCount == meshes[meshIdx].triCount && allowRefit)
+		{
+			if (coreTris && uploadVertexNormals( meshes[meshIdx], coreTris )) return 1; // animated meshes bring new vertex normals
+			return Refit( meshIdx, vertexData, vertexCount );
+		}
 		if ((uint32_t)triangleCount != meshes[meshIdx].triCount && meshIdx != (int)meshes.size() - 1)
 			return fail( "SetGeometry: changing the triangle count is only supported for the most recently added mesh" );
 		if (meshIdx != (int)meshes.size() - 1 && !allowRefit)
@@ -280,6 +312,7 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "SetGeometry sync", e ); // the staging vectors die here
 	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
 	meshes.push_back( m );
+	if (uploadVertexNormals( m, coreTris )) return 1;
 	tlasDirty = true;
 	stats.bvhBuildTime += (float)(nowMs() - t0);
 	stats.wideNodeCount = blasNodeEnd, stats.triangleCount = triEnd;

@@ -47,6 +47,7 @@ public:
 	int SetSkyData( const float* rgb, int width, int height ); // equirectangular float3 image
 	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value and roughness.value
 	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: (albedo rgb, roughness) per material; rgb > 1 = emissive
+	int SetMaterialTable( const float* props12, int count );  // 12 floats per material: albedo rgb, roughness | transmission, eta, smooth flag, - | absorption rgb, -
 	int SetAccumulatorBuffer( void* devicePtr );              // caller-owned float4[w*h] accumulator (multi-GPU gathers), null = own
 	int Finalize( uint32_t totalSamples );                    // frame = accumulator / totalSamples (after a gather)
 	int Render( const void* viewPyramid, int converge );
@@ -85,6 +86,7 @@ private:
 	int ensureToplevel();
 	int hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit );
 	int buildOnDevice( int meshIdx, const float* vertexData, uint32_t T, const void* coreTris, double t0 );
+	int uploadVertexNormals( const MeshRec& m, const void* coreTris );
 	static constexpr int MAX_CHUNKS = 12;
 	cudaStream_t copyIn = nullptr, copyOut = nullptr, stream2 = nullptr;
 	cudaEvent_t chunkEv[2 * MAX_CHUNKS + 1] = {};
@@ -92,7 +94,7 @@ private:
 	std::string error;
 	int device = 0;
 	// acceleration structure pools
-	DeviceBuffer nodePool, triPool, instPool, shadePool, instShadePool;
+	DeviceBuffer nodePool, triPool, instPool, shadePool, vnormPool, instShadePool; // vnormPool: per-vertex normals, only when CoreTris were supplied
 	uint32_t blasNodeEnd = 0, triEnd = 0, tlasRoot = 0, tlasNodeCount = 0;
 	std::vector<MeshRec> meshes;
 	std::vector<InstanceHost> instances;

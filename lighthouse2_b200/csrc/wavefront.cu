@@ -14,8 +14,9 @@
 //   * the shade stage follows the reference's shadeKernel (lib/rendercore_optix7/kernels/pathtracer.h:54-240) with its
 //     Lambert BSDF (lib/sharedBSDFs/lambert.h: diffuse + pure specular reflection by roughness): area / point / spot /
 //     directional lights picked by potential contribution, MIS between NEE and emissive hits, postponed BSDF pdf,
-//     Russian roulette, HDR skydome lookup, intensity clamp.  Left out: textures, interpolated normals, transmission,
-//     blue-noise tables (a data file of the reference) -- every random number is the WangHash/xor32 stream
+//     dielectric transmission (Fresnel, refraction, Beer absorption), interpolated vertex normals for SMOOTH materials,
+//     Russian roulette, HDR skydome lookup, intensity clamp.  Left out: textures and normal maps, consistent-normal
+//     correction, blue-noise tables (a data file of the reference) -- every random number is the WangHash/xor32 stream
 // Pixels can be sharded over several cores/GPUs by interleaved 32x8 tiles (Setting shardIndex/shardCount) or by sample
 // (Setting sampleOffset); per-path random streams depend only on (pixel, sample, bounce), so any sharding gives the same
 // image and the accumulators of all shards simply add up.
@@ -382,7 +383,7 @@ __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 // Path state: rayO/rayD (the extension ray), pathState = (throughput rgb, postponed bsdf pdf), pathInfo = (pathIdx | flags << 28,
 // normal at the previous vertex).  One thread per path; new extension / shadow rays are compacted with warp-aggregated appends.
 #ifndef B200_SHADE_MIN_BLOCKS
-#define B200_SHADE_MIN_BLOCKS 1
+#define B200_SHADE_MIN_BLOCKS 5
 #endif
 #ifndef B200_SHADE_GRID
 #define B200_SHADE_GRID 8
@@ -392,7 +393,7 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 	const float4* __restrict__ hits,
 	float4* __restrict__ rayOout, float4* __restrict__ rayDout, float4* __restrict__ pathStateOut, float4* __restrict__ pathInfoOut,
 	float4* __restrict__ conO, float4* __restrict__ conD, float4* __restrict__ conE,
-	const float4* __restrict__ shade, const float4* __restrict__ instShade, const float4* __restrict__ materials,
+	const float4* __restrict__ shade, const float4* __restrict__ vertexNormals, const float4* __restrict__ instShade, const float4* __restrict__ materials,
 	float4* accumulator, uint32_t* counters )
 {
 	__shared__ uint32_t sWarp[2 * 4 + 2];
@@ -433,9 +434,29 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 				// interpolated and the normal-mapped normal (iN, fN) of GetShadingData
 				const V3 N = normalize( v3( m0.x * sh.x + m0.y * sh.y + m0.z * sh.z, m1.x * sh.x + m1.y * sh.y + m1.z * sh.z, m2.x * sh.x + m2.y * sh.y + m2.z * sh.z ) );
 				const uint32_t mat = __float_as_uint( sh.w );
-				V3 color = v3( 0.8f, 0.8f, 0.8f );
-				float roughness = 1.0f;
-				if (mat < f.materialCount) { const float4 c = __ldg( materials + mat ); color = v3( c ), roughness = c.w; }
+				// material table: 3 float4 per material = (albedo rgb, roughness) (transmission, eta, smooth-normals flag, -) (absorption rgb, -)
+				V3 color = v3( 0.8f, 0.8f, 0.8f ), absorption = v3( 0.f, 0.f, 0.f );
+				float roughness = 1.0f, transmission = 0.0f, eta = 1.0f;
+				bool smooth = false;
+				if (mat < f.materialCount)
+				{
+					const float4 c0 = __ldg( materials + mat * 3 ), c1 = __ldg( materials + mat * 3 + 1 ), c2 = __ldg( materials + mat * 3 + 2 );
+					color = v3( c0 ), roughness = c0.w, transmission = c1.x, eta = c1.y, smooth = c1.z != 0.0f, absorption = v3( c2 );
+				}
+				// interpolated normal (GetShadingData, material_shared.h:75-81: w N0 + u N1 + v N2 for SMOOTH materials), transformed like N;
+				// it also stands in for the normal-mapped normal fN.  (Consistent normals, :90-97, need the per-vertex alpha of the
+				// host mesh and are not applied.)
+				V3 sN = N;
+				if (smooth && vertexNormals)
+				{
+					const float4* vn = vertexNormals + (size_t)(__float_as_uint( info.x ) + prim) * 3;
+					const float4 a0 = __ldg( vn ), a1 = __ldg( vn + 1 ), a2 = __ldg( vn + 2 );
+					const uint32_t bary = __float_as_uint( hit.x );
+					const float bu = (float)(bary & 0xffffu) * (1.0f / 65535.0f), bv = (float)(bary >> 16) * (1.0f / 65535.0f), bw = 1 - (bu + bv);
+					const V3 on = v3( a0 ) * bw + v3( a1 ) * bu + v3( a2 ) * bv;
+					if (dot( on, on ) > 0)
+						sN = normalize( v3( m0.x * on.x + m0.y * on.y + m0.z * on.z, m1.x * on.x + m1.y * on.y + m1.z * on.z, m2.x * on.x + m2.y * on.y + m2.z * on.z ) );
+				}
 				const V3 I = O + D * hit.w;
 				if (color.x > 1.0f || color.y > 1.0f || color.z > 1.0f)
 				{
@@ -463,10 +484,11 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 				}
 				else
 				{
-					if (roughness <= 0.001f) flags |= S_SPECULAR; else flags &= ~S_SPECULAR; // pathtracer.h:151
+					if (roughness <= 0.001f || transmission > 0.999f) flags |= S_SPECULAR; else flags &= ~S_SPECULAR; // pathtracer.h:151
 					uint32_t seed = WangHash( pathIdx * 17 + f.R0 + (uint32_t)pathLength * 91771u ); // :154; R0 changes per bounce (rendercore.cpp:716)
 					const float faceDir = dot( D, N ) > 0 ? -1.f : 1.f;
-					const V3 fN = N * faceDir;
+					const V3 gF = N * faceDir, sF = sN * faceDir; // geometric / shading normal on the side the ray came from
+					if (faceDir == 1) absorption = v3( 0.f, 0.f, 0.f ); // the ray travelled outside the medium (:158)
 					throughput = throughput * (1.0f / bsdfPdf); // postponed pdf (:161)
 					// next event estimation (:163-199)
 					if (!(flags & S_SPECULAR) && f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0)
@@ -474,10 +496,10 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 						const float r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
 						float pickProb, lightPdf;
 						V3 lightColor;
-						V3 L = RandomPointOnLight( f, r0, r1, I, fN, pickProb, lightPdf, lightColor ) - I;
+						V3 L = RandomPointOnLight( f, r0, r1, I, sF, pickProb, lightPdf, lightColor ) - I;
 						const float dist = sqrtf( dot( L, L ) );
 						L = L * (1.0f / dist);
-						const float NdotL = dot( L, fN );
+						const float NdotL = dot( L, sF );
 						if (NdotL > 0 && lightPdf > 0)
 						{
 							// EvaluateBSDF (lambert.h:58-69): color / pi, pdf = |cos| / pi; scaled by the chance of a diffuse bounce (:186)
@@ -485,7 +507,7 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 							if (lbsdfPdf > 0)
 							{
 								se = ClampAndFix( throughput * color * lightColor * (INVPI * roughness * (NdotL / (pickProb * lightPdf + lbsdfPdf))), f.clampValue );
-								SafeOrigin( I.x, I.y, I.z, L.x, L.y, L.z, fN.x, fN.y, fN.z, f.epsilon, so.x, so.y, so.z );
+								SafeOrigin( I.x, I.y, I.z, L.x, L.y, L.z, gF.x, gF.y, gF.z, f.epsilon, so.x, so.y, so.z );
 								sl = L, sdist = dist - 2 * f.epsilon;
 								wantShadow = true;
 							}
@@ -496,29 +518,60 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 					if (!enough && pathLength < maxPathLength)
 					{
 						const float r3 = RandomFloat( seed ), r4 = RandomFloat( seed );
-						// SampleBSDF (lambert.h:71-123) with TRANSMISSION = 0: a specular reflection with probability 1 - roughness
-						const float pReflect = 1 - roughness;
-						V3 R, bsdf;
+						// SampleBSDF (lambert.h:71-123)
+						V3 R = sF, bsdf = v3( 0.f, 0.f, 0.f );
 						float newPdf = 1;
-						bool specular = true;
-						if (r3 < pReflect)
+						bool specular = true, refracted = false;
+						if (r4 < transmission)
 						{
-							R = D - fN * (2 * dot( D, fN ));
-							bsdf = color * (1.0f / fabsf( dot( fN, R ) ));
+							// dielectric: Fresnel reflection or refraction, Beer absorption over the distance travelled inside (:84-103)
+							const float eio = faceDir < 0 ? 1.0f / eta : eta;
+							const float VdotN = -dot( sF, D ); // wo = -D; positive by construction of sF unless the shading normal leans away
+							float F = 1.0f;
+							{
+								float e2 = eio, c = VdotN;
+								if (c < 0.0f) e2 = 1.0f / e2, c = fabsf( c );
+								const float sinT2 = e2 * e2 * (1.0f - c * c);
+								if (sinT2 <= 1.0f)
+								{
+									const float ldn = sqrtf( 1.0f - sinT2 );
+									const float ra = (c - e2 * ldn) / (c + e2 * ldn), rb = (ldn - e2 * c) / (ldn + e2 * c);
+									F = 0.5f * (ra * ra + rb * rb);
+								}
+							}
+							const V3 beer = v3( __expf( -absorption.x * hit.w * 2.0f ), __expf( -absorption.y * hit.w * 2.0f ), __expf( -absorption.z * hit.w * 2.0f ) );
+							if (r3 < F) R = D - sF * (2 * dot( D, sF ));
+							else
+							{
+								// Refract_L (:45-56): eta = eio, wi = wo = -D
+								const float cosI = fabsf( dot( sF, D ) ), sin2I = fmaxf( 0.0f, 1.0f - cosI * cosI ), sin2T = eio * eio * sin2I;
+								if (sin2T >= 1) newPdf = 0; // total internal reflection: the reference carries on with a zero throughput, the path ends here
+								else R = D * eio + sF * (eio * cosI - sqrtf( 1.0f - sin2T )), refracted = true;
+							}
+							bsdf = color * beer * (1.0f / fabsf( dot( sF, R ) ));
 						}
 						else
 						{
-							const float r5 = (r3 - pReflect) / (1 - pReflect);
-							const float term1 = TWOPI * r5, term2 = sqrtf( 1 - r4 ); // DiffuseReflectionCosWeighted, tools_shared.h:250-256
-							float sn, cs;
-							__sincosf( term1, &sn, &cs );
-							Tangent2World( cs * term2, sn * term2, sqrtf( r4 ), fN.x, fN.y, fN.z, R.x, R.y, R.z );
-							R = normalize( R );
-							newPdf = fmaxf( 0.0f, dot( R, fN ) ) * INVPI;
-							specular = false;
-							bsdf = color * INVPI;
+							const float pReflect = 1 - roughness; // a specular reflection with probability 1 - roughness
+							if (r3 < pReflect)
+							{
+								R = D - sF * (2 * dot( D, sF ));
+								bsdf = color * (1.0f / fabsf( dot( sF, R ) ));
+							}
+							else
+							{
+								const float r5 = (r3 - pReflect) / (1 - pReflect), r6 = (r4 - transmission) / (1 - transmission);
+								const float term1 = TWOPI * r5, term2 = sqrtf( 1 - r6 ); // DiffuseReflectionCosWeighted, tools_shared.h:250-256
+								float sn, cs;
+								__sincosf( term1, &sn, &cs );
+								Tangent2World( cs * term2, sn * term2, sqrtf( r6 ), sF.x, sF.y, sF.z, R.x, R.y, R.z );
+								R = normalize( R );
+								newPdf = fmaxf( 0.0f, dot( R, sF ) ) * INVPI;
+								specular = false;
+								bsdf = color * INVPI;
+							}
 						}
-						if (dot( fN, R ) <= 0) newPdf = 0;
+						if (!refracted && dot( gF, R ) <= 0) newPdf = 0; // the sampled direction must leave on the geometric side (:121); refraction returns before this test
 						if (newPdf >= 1e-4f) // also false for NaN (:222)
 						{
 							if (specular) flags |= S_SPECULAR;
@@ -528,9 +581,9 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 							{
 								throughput = throughput * (1.0f / p);
 								if (!(flags & S_SPECULAR)) flags |= (flags & S_BOUNCED) ? S_BOUNCEDTWICE : S_BOUNCED; else flags |= S_VIASPECULAR;
-								SafeOrigin( I.x, I.y, I.z, R.x, R.y, R.z, fN.x, fN.y, fN.z, f.epsilon, eo.x, eo.y, eo.z );
+								SafeOrigin( I.x, I.y, I.z, R.x, R.y, R.z, gF.x, gF.y, gF.z, f.epsilon, eo.x, eo.y, eo.z );
 								if (!isfinite( throughput.x + throughput.y + throughput.z )) throughput = v3( 0.f, 0.f, 0.f );
-								er = R, en = fN, et = throughput * bsdf * fabsf( dot( fN, R ) ), epdf = newPdf;
+								er = R, en = sF, et = throughput * bsdf * fabsf( dot( sF, R ) ), epdf = newPdf;
 								wantExt = true;
 							}
 						}
@@ -703,27 +756,40 @@ int RenderCore::SetSkyData( const float* rgb, int width, int height )
 	return 0;
 }
 
-// CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each; the Lambert stage keeps color.value
-// (offset 0) and roughness.value (offset 304 = 4 Vec3Values + flags/pad + absorption + 3 ScalarValues; common_classes.h:177-238)
+// CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each (common_classes.h:177-238).  The Lambert
+// stage keeps color.value (offset 0), flags (160; bit 0 = SMOOTH, host_material.h:66-71), absorption.value (168), roughness.value
+// (304 = 4 Vec3Values + flags/pad + absorption + 3 ScalarValues), transmission.value (528) and eta.value (560).
 int RenderCore::SetMaterials( const void* coreMaterials, int count )
 {
-	WavefrontState* w = state( wf );
 	if (count < 0 || (count > 0 && !coreMaterials)) return fail( "SetMaterials: bad arguments" );
-	std::vector<float> colors( (size_t)count * 4 );
+	std::vector<float> table( (size_t)count * 12, 0.f );
 	for (int i = 0; i < count; i++)
 	{
-		memcpy( &colors[(size_t)i * 4], (const char*)coreMaterials + (size_t)i * 688, 12 );
-		memcpy( &colors[(size_t)i * 4 + 3], (const char*)coreMaterials + (size_t)i * 688 + 304, 4 );
+		const char* m = (const char*)coreMaterials + (size_t)i * 688;
+		float* t = &table[(size_t)i * 12];
+		uint32_t flags;
+		memcpy( t, m, 12 ), memcpy( t + 3, m + 304, 4 ), memcpy( t + 4, m + 528, 4 ), memcpy( t + 5, m + 560, 4 ), memcpy( &flags, m + 160, 4 ), memcpy( t + 8, m + 168, 12 );
+		t[6] = (flags & 1) ? 1.f : 0.f;
 	}
-	return SetMaterialColors( colors.data(), count );
+	return SetMaterialTable( table.data(), count );
 }
 
+// headless shortcut: (albedo rgb, roughness) per material, opaque, flat normals
 int RenderCore::SetMaterialColors( const float* rgba, int count )
 {
+	if (count < 0 || (count > 0 && !rgba)) return fail( "SetMaterialColors: bad arguments" );
+	std::vector<float> table( (size_t)count * 12, 0.f );
+	for (int i = 0; i < count; i++) memcpy( &table[(size_t)i * 12], rgba + (size_t)i * 4, 16 ), table[(size_t)i * 12 + 5] = 1.f;
+	return SetMaterialTable( table.data(), count );
+}
+
+int RenderCore::SetMaterialTable( const float* props12, int count )
+{
 	WavefrontState* w = state( wf );
+	if (count < 0 || (count > 0 && !props12)) return fail( "SetMaterialTable: bad arguments" );
 	cudaError_t e;
-	if ((e = w->materials.reserve( (size_t)(count + 1) * 16, false, stream )) != cudaSuccess) return fail( "materials", e );
-	if (count && (e = cudaMemcpyAsync( w->materials.ptr, rgba, (size_t)count * 16, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "materials upload", e );
+	if ((e = w->materials.reserve( (size_t)(count + 1) * 48, false, stream )) != cudaSuccess) return fail( "materials", e );
+	if (count && (e = cudaMemcpyAsync( w->materials.ptr, props12, (size_t)count * 48, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "materials upload", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "materials sync", e );
 	w->materialCount = (uint32_t)count;
 	return 0;
@@ -817,7 +883,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 			cudaEventRecord( ev[2], stream );
 			shadeKernel<<<smCount * B200_SHADE_GRID, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
 				(const float4*)w->state[in].ptr, (const float4*)w->info[in].ptr, (const float4*)w->hits.ptr, (float4*)w->rayO[out].ptr, (float4*)w->rayD[out].ptr,
-				(float4*)w->state[out].ptr, (float4*)w->info[out].ptr, (float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)instShadePool.ptr,
+				(float4*)w->state[out].ptr, (float4*)w->info[out].ptr, (float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)vnormPool.ptr, (const float4*)instShadePool.ptr,
 				(const float4*)w->materials.ptr, w->accumulator(), dCounters );
 			stats.kernelLaunches++;
 			cudaEventRecord( ev[3], stream );

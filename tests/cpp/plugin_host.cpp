@@ -65,10 +65,12 @@ int main( int argc, char** argv )
 	for (int i = 0; i < materialCount; i++)
 	{
 		memset( &materials[i], 0, sizeof( CoreMaterial ) );
-		const float* c = (const float*)r.bytes( 16 ); // rgb, roughness
+		const float* c = (const float*)r.bytes( 48 ); // rgb, roughness | transmission, eta, smooth, - | absorption rgb, -
 		materials[i].color.value.x = c[0], materials[i].color.value.y = c[1], materials[i].color.value.z = c[2];
 		materials[i].color.textureID = -1;
-		materials[i].roughness.value = c[3];
+		materials[i].roughness.value = c[3], materials[i].transmission.value = c[4], materials[i].eta.value = c[5];
+		materials[i].flags = c[6] != 0 ? 1u : 0u; // HostMaterial::SMOOTH
+		materials[i].absorption.value.x = c[8], materials[i].absorption.value.y = c[9], materials[i].absorption.value.z = c[10];
 	}
 	api->SetMaterials( materials.data(), materialCount );
 	const int meshCount = r.get<int>();

@@ -172,9 +172,18 @@ def _lit_scene():
     case["instances"] = case["instances"] + [(2, Mq)]
     grid, sph = case["meshes"][0], case["meshes"][1]
     pm = [((np.arange(len(grid)) // 2) % 5 == 0).astype(np.uint32),          # every fifth quad of the floor is glossy red
-          np.where((np.arange(len(sph)) // 7) % 3 == 0, 2, 0).astype(np.uint32),  # mirror bands on the spheres
+          np.choose((np.arange(len(sph)) // 7) % 4, [0, 2, 4, 5]).astype(np.uint32),  # bands on the spheres: diffuse, mirror, glass, smooth frosted
           np.full(len(quad), 3, np.uint32)]
-    mats = np.array([[0.8, 0.8, 0.8, 1.0], [0.9, 0.2, 0.15, 0.3], [0.95, 0.95, 0.95, 0.0], [12.0, 11.0, 10.0, 1.0]], np.float32)
+    # material table: albedo rgb, roughness | transmission, eta, smooth flag, - | absorption rgb, -
+    mats = np.array([[0.8, 0.8, 0.8, 1.0, 0, 1, 0, 0, 0, 0, 0, 0],           # 0 grey diffuse
+                     [0.9, 0.2, 0.15, 0.3, 0, 1, 0, 0, 0, 0, 0, 0],          # 1 red glossy
+                     [0.95, 0.95, 0.95, 0.0, 0, 1, 0, 0, 0, 0, 0, 0],        # 2 mirror
+                     [12.0, 11.0, 10.0, 1.0, 0, 1, 0, 0, 0, 0, 0, 0],        # 3 emitter
+                     [0.95, 0.97, 1.0, 1.0, 1.0, 1.0 / 1.5, 1, 0, 0.8, 0.3, 0.1, 0],   # 4 glass (smooth normals, absorbing)
+                     [0.7, 0.8, 0.6, 0.8, 0.4, 1.0 / 1.3, 1, 0, 0.2, 0.2, 0.2, 0]],    # 5 frosted: 40% transmission, smooth
+                    np.float32)
+    sphn = (sph / np.linalg.norm(sph, axis=2, keepdims=True)).astype(np.float32)  # the sphere is centred on its origin
+    vnormals = [None, sphn, None]
     world = quad + np.array([0.1, 1.6, 0.0], np.float32)
     n = np.cross(world[0, 1] - world[0, 0], world[0, 2] - world[0, 0])
     assert n[1] < 0, "the emitter must face down"
@@ -184,20 +193,20 @@ def _lit_scene():
     direc = lights.stack([lights.directional_light((0.3, -1.0, 0.2), (0.5, 0.45, 0.4))], 8)
     rng = np.random.default_rng(11)
     sky = (rng.random((8, 16, 3)) * np.array([0.3, 0.4, 0.6])).astype(np.float32)
-    return dict(case=case, prim_materials=pm, materials=mats, area=area, point=point, spot=spot, dir=direc, sky=sky)
+    return dict(case=case, prim_materials=pm, materials=mats, vertex_normals=vnormals, area=area, point=point, spot=spot, dir=direc, sky=sky)
 
 
 def _lit_core(sc, w, h, spp=1, max_len=5, **settings):
     case = sc["case"]
     rc = core.RenderCoreB200(0)
     for i, m in enumerate(case["meshes"]):
-        rc.SetGeometry(i, m, core.core_tris(m, sc["prim_materials"][i]))
+        rc.SetGeometry(i, m, core.core_tris(m, sc["prim_materials"][i], sc["vertex_normals"][i]))
     for i, (mesh, mat) in enumerate(case["instances"]):
         rc.SetInstance(i, mesh, mat)
     rc.SetInstance(len(case["instances"]), -1)
     rc.UpdateToplevel()
     rc.SetTarget(w, h, spp)
-    rc.SetMaterialColors(sc["materials"])
+    rc.SetMaterialTable(sc["materials"])
     rc.SetLights(sc["area"], sc["point"], sc["spot"], sc["dir"])
     rc.SetSkyData(sc["sky"])
     rc.Setting("maxPathLength", max_len)
@@ -225,7 +234,8 @@ def test_lit_frame_matches_cpu_restatement(cap, roulette):
     stats = {}
     ref = wavefront_ref.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
                                lights=wavefront_ref.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
-                               materials=sc["materials"], prim_materials=sc["prim_materials"], max_path_length=5, spp=2,
+                               materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
+                               max_path_length=5, spp=2,
                                bounce_cap=cap, roulette=bool(roulette), stats=stats)
     mean = float(ref[..., :3].mean())
     rmse = float(np.sqrt(np.mean((acc[..., :3] - ref[..., :3]) ** 2)))

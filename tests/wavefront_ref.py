@@ -204,12 +204,13 @@ def clamp_and_fix(c, clamp):
 
 
 def render(oracle, meshes, instances, view, width, height, light=None, lights=None, sky=(0, 0, 0), sky_image=None,
-           materials=None, prim_materials=None, max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True,
-           nthreads=8, stats=None):
+           materials=None, prim_materials=None, vertex_normals=None, max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0,
+           roulette=True, nthreads=8, stats=None):
     """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
     meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
-    point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness), prim_materials = per mesh
-    uint32[T] material index (default 0); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off)."""
+    point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or float32[n, 12] (+ transmission,
+    eta, smooth flag, - | absorption rgb, -), prim_materials = per mesh uint32[T] material index (default 0); vertex_normals =
+    per mesh float32[T, 3, 3] or None; sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off)."""
     npx = width * height
     acc = np.zeros((npx, 4), np.float64)
     pos, p1 = view["pos"].astype(f32), view["p1"].astype(f32)
@@ -229,7 +230,12 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
     mats = [np.eye(4, dtype=f32) if m is None else np.asarray(m, f32).reshape(4, 4) for _, m in instances]
     inst_mesh = [mesh for mesh, _ in instances]
     if materials is not None:
-        materials = np.asarray(materials, f32).reshape(-1, 4)
+        materials = np.asarray(materials, f32)
+        if materials.shape[-1] == 4:
+            full = np.zeros((len(materials), 12), f32)
+            full[:, :4], full[:, 5] = materials, 1
+            materials = full
+    invs = [np.linalg.inv(m.astype(np.float64)).astype(f32) for m in mats]
 
     def add(px, c):
         np.add.at(acc, (px, slice(0, 3)), c.astype(np.float64))
@@ -287,22 +293,53 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             pdf_prev, flags, lastN = pdf_prev[h], flags[h], lastN[h]
             n = len(O)
             N = np.empty_like(O)
+            sN = np.empty_like(O)
             mat = np.zeros(n, np.int64)
+
+            def to_world(m, v):
+                return np.stack([m[0, 0] * v[:, 0] + m[0, 1] * v[:, 1] + m[0, 2] * v[:, 2],
+                                 m[1, 0] * v[:, 0] + m[1, 1] * v[:, 1] + m[1, 2] * v[:, 2],
+                                 m[2, 0] * v[:, 0] + m[2, 1] * v[:, 1] + m[2, 2] * v[:, 2]], axis=1).astype(f32)
             for i in np.unique(inst):
                 sel = inst == i
-                n_obj = normals[inst_mesh[i]][prim[sel]]
-                m = mats[i]
-                n_w = np.stack([m[0, 0] * n_obj[:, 0] + m[0, 1] * n_obj[:, 1] + m[0, 2] * n_obj[:, 2],
-                                m[1, 0] * n_obj[:, 0] + m[1, 1] * n_obj[:, 1] + m[1, 2] * n_obj[:, 2],
-                                m[2, 0] * n_obj[:, 0] + m[2, 1] * n_obj[:, 1] + m[2, 2] * n_obj[:, 2]], axis=1).astype(f32)
-                N[sel] = normalize(n_w)
+                mesh = inst_mesh[i]
+                N[sel] = normalize(to_world(mats[i], normals[mesh][prim[sel]]))
                 if prim_materials is not None:
-                    mat[sel] = prim_materials[inst_mesh[i]][prim[sel]]
+                    mat[sel] = prim_materials[mesh][prim[sel]]
             color = np.full((n, 3), f32(0.8))
             rough = np.ones(n, f32)
+            transmission, eta, smooth = np.zeros(n, f32), np.ones(n, f32), np.zeros(n, bool)
+            absorption = np.zeros((n, 3), f32)
             if materials is not None:
                 known = mat < len(materials)
-                color[known], rough[known] = materials[mat[known], :3], materials[mat[known], 3]
+                mk = materials[mat[known]]
+                color[known], rough[known], transmission[known], eta[known] = mk[:, :3], mk[:, 3], mk[:, 4], mk[:, 5]
+                smooth[known], absorption[known] = mk[:, 6] != 0, mk[:, 8:11]
+            # interpolated normals for SMOOTH materials: w N0 + u N1 + v N2 with the 16-bit barycentrics of the hit record
+            sN[:] = N
+            if vertex_normals is not None:
+                for i in np.unique(inst):
+                    mesh = inst_mesh[i]
+                    sel = np.nonzero((inst == i) & smooth)[0]
+                    if vertex_normals[mesh] is None or len(sel) == 0:
+                        continue
+                    tri = meshes[mesh][prim[sel]]
+                    iv = invs[i]
+                    Oo = (to_world(iv, O[sel]) + iv[:3, 3][None]).astype(f32)
+                    Do = normalize(to_world(iv, D[sel]))
+                    e1, e2 = (tri[:, 1] - tri[:, 0]).astype(f32), (tri[:, 2] - tri[:, 0]).astype(f32)
+                    hh = np.cross(Do, e2).astype(f32)
+                    ff = (f32(1) / dot(e1, hh)).astype(f32)
+                    ss = (Oo - tri[:, 0]).astype(f32)
+                    bu = (ff * dot(ss, hh)).astype(f32)
+                    bv = (ff * dot(Do, np.cross(ss, e1).astype(f32))).astype(f32)
+                    bu = np.floor(f32(65535) * bu).astype(f32) * f32(1.0 / 65535.0)
+                    bv = np.floor(f32(65535) * bv).astype(f32) * f32(1.0 / 65535.0)
+                    bw = f32(1) - (bu + bv)
+                    vn = vertex_normals[mesh][prim[sel]].astype(f32)
+                    on = (vn[:, 0] * bw[:, None] + vn[:, 1] * bu[:, None] + vn[:, 2] * bv[:, None]).astype(f32)
+                    ok = dot(on, on) > 0
+                    sN[sel[ok]] = normalize(to_world(mats[i], on[ok]))
             I = (O + D * t[:, None]).astype(f32)
             # ---- paths that end on a light (pathtracer.h:120-148)
             emissive = (color > 1).any(axis=1)
@@ -335,12 +372,15 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             if not keep.any():
                 break
             O, D, T, t, N, I, color, rough, path_idx, px = (a[keep] for a in (O, D, T, t, N, I, color, rough, path_idx, px))
+            sN, transmission, eta, absorption = sN[keep], transmission[keep], eta[keep], absorption[keep]
             pdf_prev, flags, lastN = pdf_prev[keep], flags[keep], lastN[keep]
             n = len(O)
-            flags = np.where(rough <= f32(0.001), flags | S_SPECULAR, flags & ~np.uint32(S_SPECULAR)).astype(np.uint32)
+            flags = np.where((rough <= f32(0.001)) | (transmission > f32(0.999)), flags | S_SPECULAR, flags & ~np.uint32(S_SPECULAR)).astype(np.uint32)
             seed = wang_hash(path_idx * np.uint32(17) + R0 + np.uint32(length) * np.uint32(91771))
             face = np.where(dot(D, N) > 0, f32(-1), f32(1))
-            fN = (N * face[:, None]).astype(f32)
+            gF = (N * face[:, None]).astype(f32)   # geometric normal on the side the ray came from
+            fN = (sN * face[:, None]).astype(f32)  # shading normal, same side
+            absorption = np.where((face == 1)[:, None], f32(0), absorption).astype(f32)
             with np.errstate(all="ignore"):
                 T = (T * (f32(1) / pdf_prev)[:, None]).astype(f32)
             # ---- next event estimation (pathtracer.h:163-199)
@@ -361,7 +401,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                     sc = (INVPI * rough[q] * (ndl / (pick * lpdf + bpdf))).astype(f32)
                     E = clamp_and_fix((T[q] * color[q] * lcol * sc[:, None]).astype(f32), clamp)
                 if ok.any():
-                    So = safe_origin(I[q][ok], L[ok], fN[q][ok], EPS)
+                    So = safe_origin(I[q][ok], L[ok], gF[q][ok], EPS)
                     tmax = dist[ok] - 2 * EPS
                     if stats is not None:
                         stats.setdefault("shadow", []).append(int(ok.sum()))
@@ -375,19 +415,43 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             seed, r3 = random_float(seed)
             seed, r4 = random_float(seed)
             p_reflect = (f32(1) - rough).astype(f32)
-            spec = r3 < p_reflect
             ddotn = dot(D, fN)
-            R_spec = (D - fN * (f32(2) * ddotn)[:, None]).astype(f32)
+            R_refl = (D - fN * (f32(2) * ddotn)[:, None]).astype(f32)
+            trans = r4 < transmission
             with np.errstate(all="ignore"):
+                # dielectric branch (lambert.h:84-103)
+                eio = np.where(face < 0, f32(1) / eta, eta).astype(f32)
+                c = -ddotn
+                e2 = np.where(c < 0, f32(1) / eio, eio).astype(f32)
+                c = np.abs(c)
+                sinT2 = (e2 * e2 * (f32(1) - c * c)).astype(f32)
+                ldn = np.sqrt(np.maximum(f32(0), f32(1) - sinT2)).astype(f32)
+                ra, rb = (c - e2 * ldn) / (c + e2 * ldn), (ldn - e2 * c) / (ldn + e2 * c)
+                F = np.where(sinT2 <= 1, f32(0.5) * (ra * ra + rb * rb), f32(1)).astype(f32)
+                beer = np.exp(-absorption * (t * f32(2))[:, None]).astype(f32)
+                cosI = np.abs(ddotn)
+                sin2T = (eio * eio * np.maximum(f32(0), f32(1) - cosI * cosI)).astype(f32)
+                tir = sin2T >= 1
+                R_refr = (D * eio[:, None] + fN * (eio * cosI - np.sqrt(np.maximum(f32(0), f32(1) - sin2T)))[:, None]).astype(f32)
+                reflect_t = trans & (r3 < F)
+                refract_t = trans & ~(r3 < F) & ~tir
+                dead_tir = trans & ~(r3 < F) & tir
+                # opaque branch
+                spec_o = ~trans & (r3 < p_reflect)
                 r5 = ((r3 - p_reflect) / (f32(1) - p_reflect)).astype(f32)
-                term1, term2 = TWOPI * r5, np.sqrt(f32(1) - r4)
-                V = np.stack([np.cos(term1) * term2, np.sin(term1) * term2, np.sqrt(r4)], axis=1).astype(f32)
+                r6 = ((r4 - transmission) / (f32(1) - transmission)).astype(f32)
+                term1, term2 = TWOPI * r5, np.sqrt(f32(1) - r6)
+                V = np.stack([np.cos(term1) * term2, np.sin(term1) * term2, np.sqrt(r6)], axis=1).astype(f32)
                 R_diff = normalize(tangent2world(V, fN))
-                R = np.where(spec[:, None], R_spec, R_diff).astype(f32)
+                diffuse = ~trans & ~spec_o
+                R = np.where((reflect_t | spec_o)[:, None], R_refl, np.where(refract_t[:, None], R_refr, R_diff)).astype(f32)
                 cosr = dot(fN, R)
-                bsdf = np.where(spec[:, None], color * (f32(1) / np.abs(cosr))[:, None], color * INVPI).astype(f32)
-                new_pdf = np.where(spec, f32(1), np.maximum(f32(0), cosr) * INVPI).astype(f32)
-            new_pdf = np.where(cosr <= 0, f32(0), new_pdf)
+                inv_cos = (f32(1) / np.abs(cosr))[:, None]
+                bsdf = np.where(trans[:, None], color * beer * inv_cos, np.where(spec_o[:, None], color * inv_cos, color * INVPI)).astype(f32)
+                new_pdf = np.where(diffuse, np.maximum(f32(0), cosr) * INVPI, f32(1)).astype(f32)
+            new_pdf = np.where(dead_tir, f32(0), new_pdf)
+            new_pdf = np.where(~refract_t & (dot(gF, R) <= 0), f32(0), new_pdf)
+            spec = ~diffuse
             alive = ~enough & (new_pdf >= f32(1e-4))
             flags = np.where(alive & spec, flags | S_SPECULAR, flags).astype(np.uint32)
             p = np.where(((flags & S_SPECULAR) != 0) | ((flags & S_BOUNCED) == 0) | (not roulette), f32(1), np.minimum(f32(1), bsdf.max(axis=1))).astype(f32)
@@ -398,7 +462,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             is_spec = (flags & S_SPECULAR) != 0
             flags = np.where(is_spec, flags | S_VIASPECULAR, flags | np.where((flags & S_BOUNCED) != 0, S_BOUNCEDTWICE, S_BOUNCED)).astype(np.uint32)
             T[~np.isfinite(T.sum(axis=1))] = 0
-            newO = safe_origin(I, R, fN, EPS)
+            newO = safe_origin(I, R, gF, EPS)
             newT = (T * bsdf * np.abs(cosr)[:, None]).astype(f32)
             O, D, T, pdf_prev, flags, lastN, path_idx = newO[alive], R[alive], newT[alive], new_pdf[alive], flags[alive], fN[alive], path_idx[alive]
     return acc.reshape(height, width, 4).astype(f32)
