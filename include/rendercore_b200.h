@@ -93,9 +93,12 @@ B200_API int b200_set_sky_data( b200_core* c, const float* rgb, int width, int h
 B200_API int b200_set_materials( b200_core* c, const void* coreMaterials, int count );
 /* headless shortcut for hosts without CoreMaterial structs: (albedo rgb, roughness) per material index (CoreTri::material) */
 B200_API int b200_set_material_colors( b200_core* c, const float* rgba, int count );
-/* the full record the shade stage keeps, 12 floats per material: albedo rgb, roughness | transmission, eta, smooth-normals flag, 0 |
- * absorption rgb, 0 (CoreMaterial color / roughness / transmission / eta / flags & SMOOTH / absorption) */
-B200_API int b200_set_material_table( b200_core* c, const float* props12, int count );
+/* the full record the shade stage keeps, 16 floats per material: albedo rgb, roughness | transmission, eta, flags (1 SMOOTH +
+ * 2 HASALPHA), 0 | extinction rgb (1 - CoreMaterial::absorption), diffuse texture index or -1 | uv scale xy, uv offset xy */
+B200_API int b200_set_material_table( b200_core* c, const float* props16, int count );
+/* CoreAPI_Base::SetTextures (core_api_base.h:98): CoreTexDesc[count] in the host layout (40 bytes, common_classes.h:246-269); call before
+ * the materials.  ARGB32 maps are copied (MIP levels included) and sampled as the diffuse map of the materials that name them */
+B200_API int b200_set_textures( b200_core* c, const void* coreTexDescs, int count );
 /* multi-GPU: render into a caller-owned device accumulator float4[w*h] (e.g. a torch tensor that NCCL reduces);
  * NULL = the core's own.  After the gather, b200_finalize( total samples ) rebuilds the frame from it. */
 B200_API int b200_set_accumulator_buffer( b200_core* c, void* dAccumulator );

@@ -24,7 +24,7 @@ C_ABI_SYMBOLS = [
     "b200_trace_closest_device", "b200_trace_any_device", "b200_read_step_counters", "b200_set_target",
     "b200_set_point_light", "b200_set_sky", "b200_set_lights", "b200_set_sky_data", "b200_render", "b200_read_accumulator", "b200_read_frame",
     "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
-    "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors", "b200_set_material_table",
+    "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors", "b200_set_material_table", "b200_set_textures",
     "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
 ]
 
@@ -87,7 +87,7 @@ def load_library() -> C.CDLL:
         "b200_render": ([vp, vp, ip], ip), "b200_read_accumulator": ([vp, vp], ip), "b200_read_frame": ([vp, vp], ip),
         "b200_device_accumulator": ([vp], vp), "b200_get_stats": ([vp, C.POINTER(Stats)], ip), "b200_set_probe": ([vp, ip, ip], ip),
         "b200_plugin_core": ([], vp), "b200_host_alloc": ([C.c_uint64], vp), "b200_host_free": ([vp], None),
-        "b200_set_materials": ([vp, vp, ip], ip), "b200_set_material_colors": ([vp, vp, ip], ip), "b200_set_material_table": ([vp, vp, ip], ip),
+        "b200_set_materials": ([vp, vp, ip], ip), "b200_set_material_colors": ([vp, vp, ip], ip), "b200_set_material_table": ([vp, vp, ip], ip), "b200_set_textures": ([vp, vp, ip], ip),
         "b200_set_accumulator_buffer": ([vp, vp], ip), "b200_finalize": ([vp, C.c_uint32], ip),
         "b200_trace_connect_device": ([vp, vp, vp, ip, vp, vp], ip),
     }
@@ -126,10 +126,11 @@ def unpack_hits(hits: np.ndarray):
     }
 
 
-def core_tris(verts: np.ndarray, materials=None, vertex_normals=None) -> np.ndarray:
+def core_tris(verts: np.ndarray, materials=None, vertex_normals=None, uvs=None, lod=None) -> np.ndarray:
     """CoreTri[T] (176 bytes each, lib/RenderSystem/common_classes.h:60-82) for verts[T,3,3]: material (offset 28),
     geometric normal Nx/Ny/Nz (44/60/76), area (92) and vertex0/1/2 (128/144/160) filled, the rest zero; ltriIdx = -1.
-    vertex_normals[T,3,3] fills vN0/vN1/vN2 (offsets 32/48/64) for SMOOTH materials."""
+    vertex_normals[T,3,3] fills vN0/vN1/vN2 (offsets 32/48/64) for SMOOTH materials; uvs[T,3,2] the texture coordinates
+    u0..2 / v0..2 (offsets 0 / 16), lod[T] CoreTri::LOD (124)."""
     v = np.asarray(verts, np.float32)
     t = v.shape[0]
     out = np.zeros((t, 44), np.float32)
@@ -142,6 +143,11 @@ def core_tris(verts: np.ndarray, materials=None, vertex_normals=None) -> np.ndar
     if vertex_normals is not None:
         vn = np.asarray(vertex_normals, np.float32)
         out[:, 8:11], out[:, 12:15], out[:, 16:19] = vn[:, 0], vn[:, 1], vn[:, 2]
+    if uvs is not None:
+        uv = np.asarray(uvs, np.float32)
+        out[:, 0:3], out[:, 4:7] = uv[:, :, 0], uv[:, :, 1]
+    if lod is not None:
+        out[:, 31] = np.asarray(lod, np.float32)
     iv = out.view(np.int32)
     iv[:, 3] = -1
     iv[:, 7] = 0 if materials is None else np.asarray(materials, np.int32)
@@ -276,9 +282,22 @@ class RenderCoreB200:
         self._chk(self.lib.b200_set_material_colors(self.h, c.ctypes.data, c.shape[0]))
 
     def SetMaterialTable(self, props):
-        """float32[n, 12]: albedo rgb, roughness | transmission, eta, smooth flag, 0 | absorption rgb, 0."""
-        c = np.ascontiguousarray(props, np.float32).reshape(-1, 12)
+        """float32[n, 16]: albedo rgb, roughness | transmission, eta, flags (1 SMOOTH + 2 HASALPHA), 0 | extinction rgb,
+        diffuse texture index or -1 | uv scale xy, uv offset xy."""
+        c = np.ascontiguousarray(props, np.float32).reshape(-1, 16)
         self._chk(self.lib.b200_set_material_table(self.h, c.ctypes.data, c.shape[0]))
+
+    def SetTextures(self, textures):
+        """CoreAPI_Base::SetTextures.  textures: list of (width, height, texels uint32[pixelCount] ARGB32 with the MIP levels
+        behind each other, mip_levels); builds the CoreTexDesc array (40 bytes each, common_classes.h:246-269)."""
+        descs = np.zeros((len(textures), 10), np.uint32)
+        keep = []
+        for i, (w, h, texels, mips) in enumerate(textures):
+            t = np.ascontiguousarray(texels, np.uint32)
+            keep.append(t)
+            descs[i, 0:2] = np.array([t.ctypes.data], np.uint64).view(np.uint32)
+            descs[i, 2], descs[i, 3], descs[i, 5], descs[i, 7], descs[i, 8] = w, h, len(t), mips, 0
+        self._chk(self.lib.b200_set_textures(self.h, descs.ctypes.data if len(textures) else None, len(textures)))
 
     def SetAccumulatorBuffer(self, dptr: int):
         self._chk(self.lib.b200_set_accumulator_buffer(self.h, dptr))

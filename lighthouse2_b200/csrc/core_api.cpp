@@ -58,7 +58,8 @@ int b200_set_lights( b200_core* c, const void* area, int nArea, const void* poin
 int b200_set_sky_data( b200_core* c, const float* rgb, int width, int height ) { FORWARD( c, SetSkyData( rgb, width, height ) ) }
 int b200_set_materials( b200_core* c, const void* coreMaterials, int count ) { FORWARD( c, SetMaterials( coreMaterials, count ) ) }
 int b200_set_material_colors( b200_core* c, const float* rgba, int count ) { FORWARD( c, SetMaterialColors( rgba, count ) ) }
-int b200_set_material_table( b200_core* c, const float* props12, int count ) { FORWARD( c, SetMaterialTable( props12, count ) ) }
+int b200_set_material_table( b200_core* c, const float* props16, int count ) { FORWARD( c, SetMaterialTable( props16, count ) ) }
+int b200_set_textures( b200_core* c, const void* coreTexDescs, int count ) { FORWARD( c, SetTextures( coreTexDescs, count ) ) }
 int b200_set_accumulator_buffer( b200_core* c, void* dAcc ) { FORWARD( c, SetAccumulatorBuffer( dAcc ) ) }
 int b200_finalize( b200_core* c, uint32_t totalSamples ) { FORWARD( c, Finalize( totalSamples ) ) }
 int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, int n, const void* dE4, void* dAcc ) { FORWARD( c, TraceConnectDevice( dO4, dD4, n, dE4, dAcc ) ) }
@@ -137,7 +138,7 @@ public:
 	void Setting( const char* name, float value ) override { gCore->Setting( name, value ); /* unknown keys are ignored like the reference cores do */ }
 	void Render( const ViewPyramid& view, const Convergence converge ) override { CHK( Render( &view, (int)converge ) ); }
 	void Shutdown() override { delete gCore; gCore = nullptr; }
-	void SetTextures( const CoreTexDesc*, const int ) override {}
+	void SetTextures( const CoreTexDesc* tex, const int textureCount ) override { CHK( SetTextures( tex, textureCount ) ); }
 	void SetMaterials( CoreMaterial* mat, const int materialCount ) override { CHK( SetMaterials( mat, materialCount ) ); }
 	void SetLights( const CoreLightTri* areaLights, const int areaLightCount, const CorePointLight* pointLights, const int pointLightCount,
 		const CoreSpotLight* spotLights, const int spotLightCount, const CoreDirectionalLight* directionalLights, const int directionalLightCount ) override

@@ -184,31 +184,34 @@ static void makeShadeRecords( const float* vertexData, const uint32_t T, const v
 	}
 }
 
-// per-vertex normals of a mesh (CoreTri::vN0/vN1/vN2, common_classes.h:66-71) for SMOOTH materials: 3 float4 per ORIGINAL primitive,
-// indexed like the shading records.  The pool exists only once a mesh has supplied CoreTris; other meshes read zeros (= flat).
+// per-triangle shading attributes of a mesh from its CoreTris (common_classes.h:57-91): vertex normals vN0/vN1/vN2 (offsets 32/48/64) for
+// SMOOTH materials, texture coordinates u0..2 (0) / v0..2 (16) and LOD (124) for mapped ones.  4 float4 per ORIGINAL primitive, indexed
+// like the shading records: (vN0,u0) (vN1,u1) (vN2,u2) (v0,v1,v2,LOD).  The pool exists only once a mesh has supplied CoreTris; other
+// meshes read zeros (= flat, unmapped).
 int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 {
 	if (!coreTris && !vnormPool.ptr) return 0;
 	cudaError_t e;
-	const size_t oldBytes = vnormPool.bytes, need = (size_t)(m.triBase + m.triCount + 1) * 48;
-	if ((e = vnormPool.reserve( need, true, stream )) != cudaSuccess) return fail( "vertex normal pool", e );
-	if (vnormPool.bytes > oldBytes && (e = cudaMemsetAsync( (char*)vnormPool.ptr + oldBytes, 0, vnormPool.bytes - oldBytes, stream )) != cudaSuccess) return fail( "vertex normal pool", e );
-	char* dst = (char*)vnormPool.ptr + (size_t)m.triBase * 48;
-	if (!coreTris) e = cudaMemsetAsync( dst, 0, (size_t)m.triCount * 48, stream );
+	const size_t oldBytes = vnormPool.bytes, need = (size_t)(m.triBase + m.triCount + 1) * 64;
+	if ((e = vnormPool.reserve( need, true, stream )) != cudaSuccess) return fail( "triangle attribute pool", e );
+	if (vnormPool.bytes > oldBytes && (e = cudaMemsetAsync( (char*)vnormPool.ptr + oldBytes, 0, vnormPool.bytes - oldBytes, stream )) != cudaSuccess) return fail( "triangle attribute pool", e );
+	char* dst = (char*)vnormPool.ptr + (size_t)m.triBase * 64;
+	if (!coreTris) e = cudaMemsetAsync( dst, 0, (size_t)m.triCount * 64, stream );
 	else
 	{
-		std::vector<float> vn( (size_t)m.triCount * 12 );
+		std::vector<float> at( (size_t)m.triCount * 16 );
 		for (uint32_t i = 0; i < m.triCount; i++)
 		{
 			const char* ct = (const char*)coreTris + (size_t)i * 176;
-			float* o = &vn[(size_t)i * 12];
+			float* o = &at[(size_t)i * 16];
 			memcpy( o, ct + 32, 12 ), memcpy( o + 4, ct + 48, 12 ), memcpy( o + 8, ct + 64, 12 );
-			o[3] = o[7] = o[11] = 0;
+			memcpy( o + 3, ct, 4 ), memcpy( o + 7, ct + 4, 4 ), memcpy( o + 11, ct + 8, 4 );
+			memcpy( o + 12, ct + 16, 12 ), memcpy( o + 15, ct + 124, 4 );
 		}
-		e = cudaMemcpyAsync( dst, vn.data(), vn.size() * 4, cudaMemcpyHostToDevice, stream );
+		e = cudaMemcpyAsync( dst, at.data(), at.size() * 4, cudaMemcpyHostToDevice, stream );
 		if (e == cudaSuccess) e = cudaStreamSynchronize( stream ); // the staging vector dies here
 	}
-	return e == cudaSuccess ? 0 : fail( "vertex normal upload", e );
+	return e == cudaSuccess ? 0 : fail( "triangle attribute upload", e );
 }
 
 // SetGeometry with Setting gpuBuild = 1: the vertices go up once, the topology is built on the device (build.cu) and the refit

@@ -47,7 +47,8 @@ public:
 	int SetSkyData( const float* rgb, int width, int height ); // equirectangular float3 image
 	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value and roughness.value
 	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: (albedo rgb, roughness) per material; rgb > 1 = emissive
-	int SetMaterialTable( const float* props12, int count );  // 12 floats per material: albedo rgb, roughness | transmission, eta, smooth flag, - | absorption rgb, -
+	int SetMaterialTable( const float* props16, int count );  // 16 floats per material, see wavefront.cu
+	int SetTextures( const void* coreTexDescs, int count );   // CoreTexDesc[count], host layout, 40 B each; ARGB32 maps are sampled
 	int SetAccumulatorBuffer( void* devicePtr );              // caller-owned float4[w*h] accumulator (multi-GPU gathers), null = own
 	int Finalize( uint32_t totalSamples );                    // frame = accumulator / totalSamples (after a gather)
 	int Render( const void* viewPyramid, int converge );
@@ -94,7 +95,7 @@ private:
 	std::string error;
 	int device = 0;
 	// acceleration structure pools
-	DeviceBuffer nodePool, triPool, instPool, shadePool, vnormPool, instShadePool; // vnormPool: per-vertex normals, only when CoreTris were supplied
+	DeviceBuffer nodePool, triPool, instPool, shadePool, vnormPool, instShadePool; // vnormPool: per-triangle shading attributes (vertex normals, uv, LOD), only when CoreTris were supplied
 	uint32_t blasNodeEnd = 0, triEnd = 0, tlasRoot = 0, tlasNodeCount = 0;
 	std::vector<MeshRec> meshes;
 	std::vector<InstanceHost> instances;

@@ -15,13 +15,16 @@
 //     Lambert BSDF (lib/sharedBSDFs/lambert.h: diffuse + pure specular reflection by roughness): area / point / spot /
 //     directional lights picked by potential contribution, MIS between NEE and emissive hits, postponed BSDF pdf,
 //     dielectric transmission (Fresnel, refraction, Beer absorption), interpolated vertex normals for SMOOTH materials,
-//     Russian roulette, HDR skydome lookup, intensity clamp.  Left out: textures and normal maps, consistent-normal
-//     correction, blue-noise tables (a data file of the reference) -- every random number is the WangHash/xor32 stream
+//     ARGB32 diffuse maps (trilinear over the MIP chain at the ray-cone LOD) with alpha pass-through, Russian roulette, HDR
+//     skydome lookup, intensity clamp.  Left out: normal / roughness / specularity / detail maps, HDR (ARGB128) maps, the
+//     consistent-normal correction, the Disney BSDF, blue-noise tables (a data file of the reference) -- every random number
+//     is the WangHash/xor32 stream
 // Pixels can be sharded over several cores/GPUs by interleaved 32x8 tiles (Setting shardIndex/shardCount) or by sample
 // (Setting sampleOffset); per-path random streams depend only on (pixel, sample, bounce), so any sharding gives the same
 // image and the accumulators of all shards simply add up.
 #include "rendercore.h"
 #include <cstring>
+#include <vector>
 
 namespace b200 {
 
@@ -59,6 +62,8 @@ struct FrameParams {
 	int32_t areaCount, pointCount, spotCount, dirCount;
 	const float4* skyPixels;   // skydome image (rgb, 1), skyWidth x skyHeight; null = constant sky
 	uint32_t skyWidth, skyHeight;
+	const uint32_t* texels;    // ARGB32 texels of all textures, MIP levels behind each other (SetTextures)
+	float spreadAngle;         // ViewPyramid::spreadAngle: ray cone width per unit distance, for the texture LOD
 };
 
 constexpr uint32_t S_SPECULAR = 1, S_BOUNCED = 2, S_VIASPECULAR = 4, S_BOUNCEDTWICE = 8; // pathtracer.h:29-32
@@ -370,6 +375,38 @@ __device__ __forceinline__ V3 SampleSkydome( const FrameParams& f, const V3 D )
 	return idx < f.skyWidth * f.skyHeight ? v3( __ldg( f.skyPixels + idx ) ) : v3( 0.f, 0.f, 0.f );
 }
 
+// lib/CUDA/shared_kernel_code/sampling_shared.h:36-76 (FetchTexel, BILINEAR as the optix7 core builds it) for ARGB32 storage
+__device__ __forceinline__ float4 TexelToFloat4( const uint32_t t )
+{
+	const float r = 1.0f / 256.0f;
+	return make_float4( (float)(t & 255u) * r, (float)((t >> 8) & 255u) * r, (float)((t >> 16) & 255u) * r, (float)(t >> 24) * r );
+}
+__device__ float4 FetchTexel( const uint32_t* __restrict__ texels, const float tu, const float tv, const uint32_t o, const int w, const int h )
+{
+	const float tcx = fmaxf( tu + 1000, 0.0f ) * (float)w - 0.5f, tcy = fmaxf( tv + 1000, 0.0f ) * (float)h - 0.5f;
+	const int iu = ((int)tcx) % w, iv = ((int)tcy) % h;
+	const float fu = tcx - floorf( tcx ), fv = tcy - floorf( tcy );
+	const float w0 = (1 - fu) * (1 - fv), w1 = fu * (1 - fv), w2 = (1 - fu) * fv, w3 = 1 - (w0 + w1 + w2);
+	const int iu1 = (iu + 1) % w, iv1 = (iv + 1) % h;
+	const float4 p0 = TexelToFloat4( __ldg( texels + o + iu + iv * w ) ), p1 = TexelToFloat4( __ldg( texels + o + iu1 + iv * w ) );
+	const float4 p2 = TexelToFloat4( __ldg( texels + o + iu + iv1 * w ) ), p3 = TexelToFloat4( __ldg( texels + o + iu1 + iv1 * w ) );
+	return make_float4( p0.x * w0 + p1.x * w1 + p2.x * w2 + p3.x * w3, p0.y * w0 + p1.y * w1 + p2.y * w2 + p3.y * w3,
+		p0.z * w0 + p1.z * w1 + p2.z * w2 + p3.z * w3, p0.w * w0 + p1.w * w1 + p2.w * w2 + p3.w * w3 );
+}
+// :78-93 (FetchTexelTrilinear); `levels` is the texture's own MIP count where the reference assumes MIPLEVELCOUNT = 5
+__device__ float4 FetchTexelTrilinear( const uint32_t* __restrict__ texels, const float lambda, const float tu, const float tv, const uint32_t offset,
+	const int width, const int height, const int levels )
+{
+	const int level0 = min( levels - 1, (int)lambda ), level1 = min( levels - 1, level0 + 1 );
+	const float fl = lambda - floorf( lambda );
+	uint32_t o0 = offset, o1 = offset;
+	int w0 = width, h0 = height, w1 = width, h1 = height;
+	for (int i = 0; i < level0; i++) o0 += w0 * h0, w0 >>= 1, h0 >>= 1;
+	for (int i = 0; i < level1; i++) o1 += w1 * h1, w1 >>= 1, h1 >>= 1;
+	const float4 p0 = FetchTexel( texels, tu, tv, o0, w0, h0 ), p1 = FetchTexel( texels, tu, tv, o1, w1, h1 );
+	return make_float4( (1 - fl) * p0.x + fl * p1.x, (1 - fl) * p0.y + fl * p1.y, (1 - fl) * p0.z + fl * p1.z, (1 - fl) * p0.w + fl * p1.w );
+}
+
 // core_settings.h:190-192 (CLAMPINTENSITY) and FIXNAN_FLOAT3
 __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 {
@@ -434,30 +471,61 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 				// interpolated and the normal-mapped normal (iN, fN) of GetShadingData
 				const V3 N = normalize( v3( m0.x * sh.x + m0.y * sh.y + m0.z * sh.z, m1.x * sh.x + m1.y * sh.y + m1.z * sh.z, m2.x * sh.x + m2.y * sh.y + m2.z * sh.z ) );
 				const uint32_t mat = __float_as_uint( sh.w );
-				// material table: 3 float4 per material = (albedo rgb, roughness) (transmission, eta, smooth-normals flag, -) (absorption rgb, -)
+				// material table, 5 float4 per material: (albedo rgb, roughness) (transmission, eta, flag bits, MIP levels)
+				// (extinction rgb, first texel) (uv scale, uv offset) (texture width, height, -, -); flags: 1 SMOOTH, 2 HASALPHA, 4 diffuse map
 				V3 color = v3( 0.8f, 0.8f, 0.8f ), absorption = v3( 0.f, 0.f, 0.f );
 				float roughness = 1.0f, transmission = 0.0f, eta = 1.0f;
-				bool smooth = false;
+				uint32_t mflags = 0;
+				float4 c1 = make_float4( 0, 0, 0, 0 ), c2 = c1, c3 = c1, c4 = c1;
 				if (mat < f.materialCount)
 				{
-					const float4 c0 = __ldg( materials + mat * 3 ), c1 = __ldg( materials + mat * 3 + 1 ), c2 = __ldg( materials + mat * 3 + 2 );
-					color = v3( c0 ), roughness = c0.w, transmission = c1.x, eta = c1.y, smooth = c1.z != 0.0f, absorption = v3( c2 );
+					const float4 c0 = __ldg( materials + mat * 5 );
+					c1 = __ldg( materials + mat * 5 + 1 ), c2 = __ldg( materials + mat * 5 + 2 );
+					color = v3( c0 ), roughness = c0.w, transmission = c1.x, eta = c1.y, mflags = __float_as_uint( c1.z ), absorption = v3( c2 );
+				}
+				// per-triangle attributes (CoreTri): vertex normals, texture coordinates, LOD -- 4 float4: (vN0,u0) (vN1,u1) (vN2,u2) (v0,v1,v2,LOD)
+				const uint32_t bary = __float_as_uint( hit.x );
+				const float bu = (float)(bary & 0xffffu) * (1.0f / 65535.0f), bv = (float)(bary >> 16) * (1.0f / 65535.0f), bw = 1 - (bu + bv);
+				float4 a0 = make_float4( 0, 0, 0, 0 ), a1 = a0, a2 = a0, a3 = a0;
+				if ((mflags & 5u) && vertexNormals)
+				{
+					const float4* ta = vertexNormals + (size_t)(__float_as_uint( info.x ) + prim) * 4;
+					a0 = __ldg( ta ), a1 = __ldg( ta + 1 ), a2 = __ldg( ta + 2 ), a3 = __ldg( ta + 3 );
 				}
 				// interpolated normal (GetShadingData, material_shared.h:75-81: w N0 + u N1 + v N2 for SMOOTH materials), transformed like N;
 				// it also stands in for the normal-mapped normal fN.  (Consistent normals, :90-97, need the per-vertex alpha of the
 				// host mesh and are not applied.)
 				V3 sN = N;
-				if (smooth && vertexNormals)
+				if (mflags & 1u)
 				{
-					const float4* vn = vertexNormals + (size_t)(__float_as_uint( info.x ) + prim) * 3;
-					const float4 a0 = __ldg( vn ), a1 = __ldg( vn + 1 ), a2 = __ldg( vn + 2 );
-					const uint32_t bary = __float_as_uint( hit.x );
-					const float bu = (float)(bary & 0xffffu) * (1.0f / 65535.0f), bv = (float)(bary >> 16) * (1.0f / 65535.0f), bw = 1 - (bu + bv);
 					const V3 on = v3( a0 ) * bw + v3( a1 ) * bu + v3( a2 ) * bv;
 					if (dot( on, on ) > 0)
 						sN = normalize( v3( m0.x * on.x + m0.y * on.y + m0.z * on.z, m1.x * on.x + m1.y * on.y + m1.z * on.z, m2.x * on.x + m2.y * on.y + m2.z * on.z ) );
 				}
 				const V3 I = O + D * hit.w;
+				// diffuse map (material_shared.h:99-131): trilinear fetch at the ray-cone LOD; an alpha texel below 0.5 lets the path through
+				if ((mflags & 4u) && f.texels)
+				{
+					c3 = __ldg( materials + mat * 5 + 3 ), c4 = __ldg( materials + mat * 5 + 4 );
+					const float tu = bw * a0.w + bu * a1.w + bv * a2.w, tv = bw * a3.x + bu * a3.y + bv * a3.z;
+					const float lambda = a3.w + log2f( f.spreadAngle * hit.w * (1.0f / fabsf( dot( D, N ) )) );
+					const float4 texel = FetchTexelTrilinear( f.texels, lambda, c3.x * (c3.z + tu), c3.y * (c3.w + tv), __float_as_uint( c2.w ),
+						(int)__float_as_uint( c4.x ), (int)__float_as_uint( c4.y ), (int)__float_as_uint( c1.w ) );
+					if ((mflags & 2u) && texel.w < 0.5f)
+					{
+						// pathtracer.h:104-116: the path continues in the same direction from just behind the surface, state unchanged
+						if (pathLength < maxPathLength)
+						{
+							const V3 po = I + D * f.epsilon;
+							eo = po, er = D, en = lastN, et = isfinite( throughput.x + throughput.y + throughput.z ) ? throughput : v3( 0.f, 0.f, 0.f ), epdf = bsdfPdf;
+							wantExt = true;
+						}
+						color = v3( 0.f, 0.f, 0.f ), mflags |= 0x80000000u; // nothing else happens at this vertex
+					}
+					else color = color * v3( texel );
+				}
+				if (mflags & 0x80000000u) {}
+				else
 				if (color.x > 1.0f || color.y > 1.0f || color.z > 1.0f)
 				{
 					// the path ends on a light (pathtracer.h:120-148); lights are single sided
@@ -625,7 +693,9 @@ struct WavefrontState {
 	int shardIndex = 0, shardCount = 1, sampleOffset = 0, jitter = 1;
 	uint32_t pathsPerPass = 32u << 20;
 	uint32_t capacity = 0; // rays per buffer
-	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO, conD, conE, counters, accumOwn, frame, materials, lights, skyImage;
+	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO, conD, conE, counters, accumOwn, frame, materials, lights, skyImage, texels;
+	struct TextureRec { uint32_t offset, width, height, mipLevels; bool valid; };
+	std::vector<TextureRec> textures;
 	float4* accumExternal = nullptr;
 	uint32_t materialCount = 0;
 	float sky[3] = { 0, 0, 0 }, clampValue = 10.0f; // clampValue: the RenderSystem's default (rendersystem.cpp:228-233 sends it every frame)
@@ -643,7 +713,7 @@ struct WavefrontState {
 	~WavefrontState()
 	{
 		DeviceBuffer* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &state[0], &state[1], &info[0], &info[1], &hits, &conO, &conD, &conE, &counters,
-			&accumOwn, &frame, &materials, &lights, &skyImage };
+			&accumOwn, &frame, &materials, &lights, &skyImage, &texels };
 		for (DeviceBuffer* b : all) b->release();
 		for (cudaEvent_t e : ev) if (e) cudaEventDestroy( e );
 		for (cudaEvent_t e : shadeDone) if (e) cudaEventDestroy( e );
@@ -756,40 +826,95 @@ int RenderCore::SetSkyData( const float* rgb, int width, int height )
 	return 0;
 }
 
-// CoreAPI_Base::SetMaterials (core_api_base.h:100): CoreMaterial[count], 688 bytes each (common_classes.h:177-238).  The Lambert
-// stage keeps color.value (offset 0), flags (160; bit 0 = SMOOTH, host_material.h:66-71), absorption.value (168), roughness.value
-// (304 = 4 Vec3Values + flags/pad + absorption + 3 ScalarValues), transmission.value (528) and eta.value (560).
+// CoreAPI_Base::SetTextures (core_api_base.h:98): CoreTexDesc[count] in the host layout (common_classes.h:246-269, 40 bytes: data
+// pointer, width, height, flags, pixelCount, firstPixel, MIPlevels, storage).  ARGB32 textures are copied, MIP levels included, into
+// one texel pool (what SyncStorageType does, lib/rendercore_optix7/rendercore.cpp:447-505); other storages are not sampled here.
+int RenderCore::SetTextures( const void* coreTexDescs, int count )
+{
+	WavefrontState* w = state( wf );
+	if (count < 0 || (count > 0 && !coreTexDescs)) return fail( "SetTextures: bad arguments" );
+	w->textures.assign( (size_t)count, WavefrontState::TextureRec{ 0, 0, 0, 0, false } );
+	std::vector<uint32_t> pool;
+	for (int i = 0; i < count; i++)
+	{
+		const char* d = (const char*)coreTexDescs + (size_t)i * 40;
+		const uint32_t* data;
+		uint32_t width, height, pixelCount, mips, storage;
+		memcpy( &data, d, 8 ), memcpy( &width, d + 8, 4 ), memcpy( &height, d + 12, 4 ), memcpy( &pixelCount, d + 20, 4 ), memcpy( &mips, d + 28, 4 ), memcpy( &storage, d + 32, 4 );
+		if (storage != 0 /* ARGB32 */ || !data || !width || !height) continue;
+		// the levels actually present: level k has (w >> k)(h >> k) texels
+		uint32_t have = 0, need = 0, ww = width, hh = height;
+		while (have < (mips ? mips : 1) && ww && hh && need + ww * hh <= pixelCount) need += ww * hh, ww >>= 1, hh >>= 1, have++;
+		if (!have) return fail( "SetTextures: pixelCount smaller than width * height" );
+		w->textures[i] = { (uint32_t)pool.size(), width, height, have, true };
+		pool.insert( pool.end(), data, data + need );
+	}
+	cudaError_t e;
+	if ((e = w->texels.reserve( pool.size() * 4 + 64, false, stream )) != cudaSuccess) return fail( "texel pool", e );
+	if (!pool.empty() && (e = cudaMemcpyAsync( w->texels.ptr, pool.data(), pool.size() * 4, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "texel upload", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "texel sync", e );
+	return 0;
+}
+
+// CoreAPI_Base::SetMaterials (core_api_base.h:100; after SetTextures, :99): CoreMaterial[count], 688 bytes each
+// (common_classes.h:177-238).  The Lambert stage keeps color.value (offset 0) with its map (textureID 12, uvscale 24, uvoffset 32),
+// flags (160; 1 = SMOOTH, 2 = HASALPHA, host_material.h:66-71), absorption.value (168; stored as 1 - absorption like
+// rendercore_optix7/rendercore.cpp:529-531), roughness.value (304), transmission.value (528) and eta.value (560).
 int RenderCore::SetMaterials( const void* coreMaterials, int count )
 {
 	if (count < 0 || (count > 0 && !coreMaterials)) return fail( "SetMaterials: bad arguments" );
-	std::vector<float> table( (size_t)count * 12, 0.f );
+	std::vector<float> table( (size_t)count * 16, 0.f );
 	for (int i = 0; i < count; i++)
 	{
 		const char* m = (const char*)coreMaterials + (size_t)i * 688;
-		float* t = &table[(size_t)i * 12];
+		float* t = &table[(size_t)i * 16];
 		uint32_t flags;
-		memcpy( t, m, 12 ), memcpy( t + 3, m + 304, 4 ), memcpy( t + 4, m + 528, 4 ), memcpy( t + 5, m + 560, 4 ), memcpy( &flags, m + 160, 4 ), memcpy( t + 8, m + 168, 12 );
-		t[6] = (flags & 1) ? 1.f : 0.f;
+		int32_t textureID;
+		float absorption[3];
+		memcpy( t, m, 12 ), memcpy( t + 3, m + 304, 4 ), memcpy( t + 4, m + 528, 4 ), memcpy( t + 5, m + 560, 4 ), memcpy( &flags, m + 160, 4 );
+		memcpy( absorption, m + 168, 12 ), memcpy( &textureID, m + 12, 4 ), memcpy( t + 12, m + 24, 16 );
+		t[6] = (float)(flags & 3u);
+		t[8] = 1 - absorption[0], t[9] = 1 - absorption[1], t[10] = 1 - absorption[2];
+		t[11] = (float)textureID;
 	}
 	return SetMaterialTable( table.data(), count );
 }
 
-// headless shortcut: (albedo rgb, roughness) per material, opaque, flat normals
+// headless shortcut: (albedo rgb, roughness) per material, opaque, flat normals, no map
 int RenderCore::SetMaterialColors( const float* rgba, int count )
 {
 	if (count < 0 || (count > 0 && !rgba)) return fail( "SetMaterialColors: bad arguments" );
-	std::vector<float> table( (size_t)count * 12, 0.f );
-	for (int i = 0; i < count; i++) memcpy( &table[(size_t)i * 12], rgba + (size_t)i * 4, 16 ), table[(size_t)i * 12 + 5] = 1.f;
+	std::vector<float> table( (size_t)count * 16, 0.f );
+	for (int i = 0; i < count; i++)
+	{
+		float* t = &table[(size_t)i * 16];
+		memcpy( t, rgba + (size_t)i * 4, 16 );
+		t[5] = 1.f, t[11] = -1.f, t[12] = t[13] = 1.f;
+	}
 	return SetMaterialTable( table.data(), count );
 }
 
-int RenderCore::SetMaterialTable( const float* props12, int count )
+// 16 floats per material: albedo rgb, roughness | transmission, eta, flags (1 SMOOTH + 2 HASALPHA), 0 | extinction rgb, diffuse
+// texture index (-1 = none) | uv scale xy, uv offset xy.  Texture indices refer to the last SetTextures.
+int RenderCore::SetMaterialTable( const float* props16, int count )
 {
 	WavefrontState* w = state( wf );
-	if (count < 0 || (count > 0 && !props12)) return fail( "SetMaterialTable: bad arguments" );
+	if (count < 0 || (count > 0 && !props16)) return fail( "SetMaterialTable: bad arguments" );
+	std::vector<float> dev( (size_t)count * 20, 0.f );
+	for (int i = 0; i < count; i++)
+	{
+		const float* t = props16 + (size_t)i * 16;
+		float* d = &dev[(size_t)i * 20];
+		memcpy( d, t, 64 );
+		uint32_t flags = (uint32_t)t[6] & 3u, offset = 0, dims[4] = { 0, 0, 0, 0 }, mips = 0;
+		const int tex = (int)t[11];
+		if (tex >= 0 && tex < (int)w->textures.size() && w->textures[tex].valid)
+			flags |= 4u, offset = w->textures[tex].offset, dims[0] = w->textures[tex].width, dims[1] = w->textures[tex].height, mips = w->textures[tex].mipLevels;
+		memcpy( d + 6, &flags, 4 ), memcpy( d + 7, &mips, 4 ), memcpy( d + 11, &offset, 4 ), memcpy( d + 16, dims, 16 );
+	}
 	cudaError_t e;
-	if ((e = w->materials.reserve( (size_t)(count + 1) * 48, false, stream )) != cudaSuccess) return fail( "materials", e );
-	if (count && (e = cudaMemcpyAsync( w->materials.ptr, props12, (size_t)count * 48, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "materials upload", e );
+	if ((e = w->materials.reserve( (size_t)(count + 1) * 80, false, stream )) != cudaSuccess) return fail( "materials", e );
+	if (count && (e = cudaMemcpyAsync( w->materials.ptr, dev.data(), (size_t)count * 80, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "materials upload", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "materials sync", e );
 	w->materialCount = (uint32_t)count;
 	return 0;
@@ -815,7 +940,8 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	memset( &f, 0, sizeof( f ) );
 	for (int a = 0; a < 3; a++) f.pos[a] = vp[a], f.p1[a] = vp[3 + a], f.right[a] = vp[6 + a] - vp[3 + a], f.up[a] = vp[9 + a] - vp[3 + a];
 	memcpy( f.sky, w->sky, 12 );
-	f.aperture = vp[12], f.distortion = vp[16];
+	f.aperture = vp[12], f.spreadAngle = vp[13], f.distortion = vp[16];
+	f.texels = w->texels.bytes ? (const uint32_t*)w->texels.ptr : nullptr;
 	f.clampValue = w->clampValue, f.bounceCap = (uint32_t)w->bounceCap, f.roulette = (uint32_t)w->roulette;
 	f.areaCount = w->lightCounts[0], f.pointCount = w->lightCounts[1], f.spotCount = w->lightCounts[2], f.dirCount = w->lightCounts[3];
 	f.areaLights = (const float4*)w->lights.ptr, f.pointLights = f.areaLights + f.areaCount * 6, f.spotLights = f.pointLights + f.pointCount * 2;

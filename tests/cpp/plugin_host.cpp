@@ -59,18 +59,31 @@ int main( int argc, char** argv )
 	float* cells = (float*)&identity;
 	cells[0] = cells[5] = cells[10] = cells[15] = 1;
 	if (skyW) api->SetSkyData( sky, (uint)skyW, (uint)skyH, identity );
-	api->SetTextures( nullptr, 0 );
+	const int textureCount = r.get<int>();
+	std::vector<CoreTexDesc> textures( textureCount );
+	for (int i = 0; i < textureCount; i++)
+	{
+		memset( &textures[i], 0, sizeof( CoreTexDesc ) );
+		textures[i].width = (uint)r.get<int>(), textures[i].height = (uint)r.get<int>();
+		textures[i].pixelCount = (uint)r.get<int>(), textures[i].MIPlevels = (uint)r.get<int>();
+		textures[i].storage = ARGB32;
+		textures[i].idata = (uchar4_t*)r.bytes( (size_t)textures[i].pixelCount * 4 );
+	}
+	api->SetTextures( textures.data(), textureCount ); // before the materials (core_api_base.h:99)
 	const int materialCount = r.get<int>();
 	std::vector<CoreMaterial> materials( materialCount );
 	for (int i = 0; i < materialCount; i++)
 	{
 		memset( &materials[i], 0, sizeof( CoreMaterial ) );
-		const float* c = (const float*)r.bytes( 48 ); // rgb, roughness | transmission, eta, smooth, - | absorption rgb, -
+		// the table of b200_set_material_table: rgb, roughness | transmission, eta, flags, - | extinction rgb, texture | uv scale, uv offset
+		const float* c = (const float*)r.bytes( 64 );
 		materials[i].color.value.x = c[0], materials[i].color.value.y = c[1], materials[i].color.value.z = c[2];
-		materials[i].color.textureID = -1;
+		materials[i].color.textureID = (int)c[11];
+		materials[i].color.uvscale.x = c[12], materials[i].color.uvscale.y = c[13], materials[i].color.uvoffset.x = c[14], materials[i].color.uvoffset.y = c[15];
 		materials[i].roughness.value = c[3], materials[i].transmission.value = c[4], materials[i].eta.value = c[5];
-		materials[i].flags = c[6] != 0 ? 1u : 0u; // HostMaterial::SMOOTH
-		materials[i].absorption.value.x = c[8], materials[i].absorption.value.y = c[9], materials[i].absorption.value.z = c[10];
+		materials[i].flags = (uint)c[6]; // HostMaterial::SMOOTH = 1, HASALPHA = 2
+		// the cores keep 1 - absorption (rendercore_optix7/rendercore.cpp:529-531); the test values are dyadic, so this is exact
+		materials[i].absorption.value.x = 1 - c[8], materials[i].absorption.value.y = 1 - c[9], materials[i].absorption.value.z = 1 - c[10];
 	}
 	api->SetMaterials( materials.data(), materialCount );
 	const int meshCount = r.get<int>();

@@ -27,7 +27,11 @@ def _write_scene(path, sc, view, w, h, spp, frames, probe):
         sky = sc["sky"]
         f.write(struct.pack("<2i", sky.shape[1], sky.shape[0]))
         f.write(np.ascontiguousarray(sky, np.float32).tobytes())
-        mats = np.ascontiguousarray(sc["materials"], np.float32)  # [n, 12]: see _lit_scene
+        f.write(struct.pack("<i", len(sc["textures"])))
+        for (tw, th, texels, mips) in sc["textures"]:
+            f.write(struct.pack("<4i", tw, th, len(texels), mips))
+            f.write(np.ascontiguousarray(texels, np.uint32).tobytes())
+        mats = np.ascontiguousarray(sc["materials"], np.float32)  # [n, 16]: see _lit_scene
         f.write(struct.pack("<i", len(mats)))
         f.write(mats.tobytes())
         f.write(struct.pack("<i", len(case["meshes"])))
@@ -36,7 +40,7 @@ def _write_scene(path, sc, view, w, h, spp, frames, probe):
             v4[:, :3] = m.reshape(-1, 3)
             f.write(struct.pack("<i", len(m)))
             f.write(v4.tobytes())
-            f.write(core.core_tris(m, sc["prim_materials"][i], sc["vertex_normals"][i]).tobytes())
+            f.write(core.core_tris(m, sc["prim_materials"][i], sc["vertex_normals"][i], sc["uvs"][i], sc["lods"][i]).tobytes())
         f.write(struct.pack("<i", len(case["instances"])))
         for mesh, mat in case["instances"]:
             f.write(struct.pack("<i", mesh))

@@ -171,17 +171,31 @@ def _lit_scene():
     case["meshes"] = case["meshes"] + [quad]
     case["instances"] = case["instances"] + [(2, Mq)]
     grid, sph = case["meshes"][0], case["meshes"][1]
-    pm = [((np.arange(len(grid)) // 2) % 5 == 0).astype(np.uint32),          # every fifth quad of the floor is glossy red
+    pm = [np.where((np.arange(len(grid)) // 2) % 5 == 0, 1, 6).astype(np.uint32),  # floor: textured with alpha holes, every fifth quad glossy red
           np.choose((np.arange(len(sph)) // 7) % 4, [0, 2, 4, 5]).astype(np.uint32),  # bands on the spheres: diffuse, mirror, glass, smooth frosted
           np.full(len(quad), 3, np.uint32)]
-    # material table: albedo rgb, roughness | transmission, eta, smooth flag, - | absorption rgb, -
-    mats = np.array([[0.8, 0.8, 0.8, 1.0, 0, 1, 0, 0, 0, 0, 0, 0],           # 0 grey diffuse
-                     [0.9, 0.2, 0.15, 0.3, 0, 1, 0, 0, 0, 0, 0, 0],          # 1 red glossy
-                     [0.95, 0.95, 0.95, 0.0, 0, 1, 0, 0, 0, 0, 0, 0],        # 2 mirror
-                     [12.0, 11.0, 10.0, 1.0, 0, 1, 0, 0, 0, 0, 0, 0],        # 3 emitter
-                     [0.95, 0.97, 1.0, 1.0, 1.0, 1.0 / 1.5, 1, 0, 0.8, 0.3, 0.1, 0],   # 4 glass (smooth normals, absorbing)
-                     [0.7, 0.8, 0.6, 0.8, 0.4, 1.0 / 1.3, 1, 0, 0.2, 0.2, 0.2, 0]],    # 5 frosted: 40% transmission, smooth
+    # material table (b200_set_material_table): albedo rgb, roughness | transmission, eta, flags (1 SMOOTH + 2 HASALPHA), - |
+    # extinction rgb, diffuse texture or -1 | uv scale, uv offset
+    mats = np.array([[0.8, 0.8, 0.8, 1.0, 0, 1, 0, 0, 0, 0, 0, -1, 1, 1, 0, 0],             # 0 grey diffuse
+                     [0.9, 0.2, 0.15, 0.3, 0, 1, 0, 0, 0, 0, 0, -1, 1, 1, 0, 0],            # 1 red glossy
+                     [0.95, 0.95, 0.95, 0.0, 0, 1, 0, 0, 0, 0, 0, -1, 1, 1, 0, 0],          # 2 mirror
+                     [12.0, 11.0, 10.0, 1.0, 0, 1, 0, 0, 0, 0, 0, -1, 1, 1, 0, 0],          # 3 emitter
+                     [0.95, 0.97, 1.0, 1.0, 1.0, 1.0 / 1.5, 1, 0, 0.75, 0.25, 0.125, -1, 1, 1, 0, 0],   # 4 glass (smooth normals, absorbing)
+                     [0.7, 0.8, 0.6, 0.8, 0.4, 1.0 / 1.3, 1, 0, 0.25, 0.25, 0.25, -1, 1, 1, 0, 0],      # 5 frosted: 40% transmission, smooth
+                     [1.0, 0.9, 0.8, 1.0, 0, 1, 2, 0, 0, 0, 0, 0, 1.5, 2.0, 0.25, 0.125]],              # 6 mapped floor, HASALPHA
                     np.float32)
+    # texture 0: 16x16 ARGB32 with 5 MIP levels; a fifth of the base texels are transparent
+    rng_t = np.random.default_rng(5)
+    levels = []
+    for k in range(5):
+        side = 16 >> k
+        rgba = rng_t.integers(60, 256, (side * side, 4)).astype(np.uint32)
+        rgba[:, 3] = np.where(rng_t.random(side * side) < 0.2, 0, 255)
+        levels.append(rgba[:, 0] | (rgba[:, 1] << 8) | (rgba[:, 2] << 16) | (rgba[:, 3] << 24))
+    textures = [(16, 16, np.concatenate(levels).astype(np.uint32), 5)]
+    guv = np.stack([grid[:, :, 0] * 0.7 + 0.3, grid[:, :, 2] * 0.9 - 0.1], axis=2).astype(np.float32)  # uv from the floor's x, z
+    uvs = [guv, None, None]
+    lods = [(0.3 + 0.2 * np.sin(np.arange(len(grid)))).astype(np.float32) + 6.0, None, None]  # CoreTri::LOD (+6: the cone is narrow at this scale)
     sphn = (sph / np.linalg.norm(sph, axis=2, keepdims=True)).astype(np.float32)  # the sphere is centred on its origin
     vnormals = [None, sphn, None]
     world = quad + np.array([0.1, 1.6, 0.0], np.float32)
@@ -193,19 +207,20 @@ def _lit_scene():
     direc = lights.stack([lights.directional_light((0.3, -1.0, 0.2), (0.5, 0.45, 0.4))], 8)
     rng = np.random.default_rng(11)
     sky = (rng.random((8, 16, 3)) * np.array([0.3, 0.4, 0.6])).astype(np.float32)
-    return dict(case=case, prim_materials=pm, materials=mats, vertex_normals=vnormals, area=area, point=point, spot=spot, dir=direc, sky=sky)
+    return dict(case=case, prim_materials=pm, materials=mats, vertex_normals=vnormals, uvs=uvs, lods=lods, textures=textures, area=area, point=point, spot=spot, dir=direc, sky=sky)
 
 
 def _lit_core(sc, w, h, spp=1, max_len=5, **settings):
     case = sc["case"]
     rc = core.RenderCoreB200(0)
     for i, m in enumerate(case["meshes"]):
-        rc.SetGeometry(i, m, core.core_tris(m, sc["prim_materials"][i], sc["vertex_normals"][i]))
+        rc.SetGeometry(i, m, core.core_tris(m, sc["prim_materials"][i], sc["vertex_normals"][i], sc["uvs"][i], sc["lods"][i]))
     for i, (mesh, mat) in enumerate(case["instances"]):
         rc.SetInstance(i, mesh, mat)
     rc.SetInstance(len(case["instances"]), -1)
     rc.UpdateToplevel()
     rc.SetTarget(w, h, spp)
+    rc.SetTextures(sc["textures"])
     rc.SetMaterialTable(sc["materials"])
     rc.SetLights(sc["area"], sc["point"], sc["spot"], sc["dir"])
     rc.SetSkyData(sc["sky"])
@@ -235,7 +250,7 @@ def test_lit_frame_matches_cpu_restatement(cap, roulette):
     ref = wavefront_ref.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
                                lights=wavefront_ref.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
                                materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
-                               max_path_length=5, spp=2,
+                               uvs=sc["uvs"], lods=sc["lods"], textures=sc["textures"], max_path_length=5, spp=2,
                                bounce_cap=cap, roulette=bool(roulette), stats=stats)
     mean = float(ref[..., :3].mean())
     rmse = float(np.sqrt(np.mean((acc[..., :3] - ref[..., :3]) ** 2)))

@@ -193,6 +193,39 @@ def sample_skydome(D, sky, sky_image):
     return out
 
 
+def fetch_texel(texels, tu, tv, o, w, h):
+    """sampling_shared.h:36-76 (BILINEAR, ARGB32); o, w, h are arrays (per ray)."""
+    tcx = (np.maximum(tu + f32(1000), f32(0)) * w.astype(f32) - f32(0.5)).astype(f32)
+    tcy = (np.maximum(tv + f32(1000), f32(0)) * h.astype(f32) - f32(0.5)).astype(f32)
+    iu, iv = tcx.astype(np.int64) % w, tcy.astype(np.int64) % h
+    fu, fv = (tcx - np.floor(tcx)).astype(f32), (tcy - np.floor(tcy)).astype(f32)
+    w0, w1, w2 = (1 - fu) * (1 - fv), fu * (1 - fv), (1 - fu) * fv
+    w3 = (1 - (w0 + w1 + w2)).astype(f32)
+    iu1, iv1 = (iu + 1) % w, (iv + 1) % h
+
+    def px(x, y):
+        t = texels[o + x + y * w]
+        return np.stack([(t & 255), (t >> 8) & 255, (t >> 16) & 255, t >> 24], axis=1).astype(f32) * f32(1.0 / 256.0)
+    return (px(iu, iv) * w0[:, None] + px(iu1, iv) * w1[:, None] + px(iu, iv1) * w2[:, None] + px(iu1, iv1) * w3[:, None]).astype(f32)
+
+
+def fetch_texel_trilinear(texels, lam, tu, tv, offset, width, height, levels):
+    """sampling_shared.h:78-93 with the texture's own MIP count."""
+    level0 = np.minimum(levels - 1, np.trunc(lam).astype(np.int64))
+    level1 = np.minimum(levels - 1, level0 + 1)
+    fl = (lam - np.floor(lam)).astype(f32)
+
+    def level(lv):
+        o, w, h = offset.astype(np.int64).copy(), width.astype(np.int64).copy(), height.astype(np.int64).copy()
+        for i in range(int(max(lv.max(), 0))):
+            go = lv > i
+            o = np.where(go, o + w * h, o); w = np.where(go, w >> 1, w); h = np.where(go, h >> 1, h)
+        return o, w, h
+    p0 = fetch_texel(texels, tu, tv, *level(level0))
+    p1 = fetch_texel(texels, tu, tv, *level(level1))
+    return ((1 - fl)[:, None] * p0 + fl[:, None] * p1).astype(f32)
+
+
 def clamp_and_fix(c, clamp):
     m = np.max(c, axis=1)
     with np.errstate(all="ignore"):
@@ -204,13 +237,14 @@ def clamp_and_fix(c, clamp):
 
 
 def render(oracle, meshes, instances, view, width, height, light=None, lights=None, sky=(0, 0, 0), sky_image=None,
-           materials=None, prim_materials=None, vertex_normals=None, max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0,
-           roulette=True, nthreads=8, stats=None):
+           materials=None, prim_materials=None, vertex_normals=None, uvs=None, lods=None, textures=None, spread_angle=0.01,
+           max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True, nthreads=8, stats=None):
     """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
     meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
-    point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or float32[n, 12] (+ transmission,
-    eta, smooth flag, - | absorption rgb, -), prim_materials = per mesh uint32[T] material index (default 0); vertex_normals =
-    per mesh float32[T, 3, 3] or None; sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off)."""
+    point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or the float32[n, 16] table of
+    b200_set_material_table; prim_materials = per mesh uint32[T] material index (default 0); vertex_normals = per mesh
+    float32[T, 3, 3] or None; uvs = per mesh float32[T, 3, 2] or None, lods = per mesh float32[T] or None; textures = list of
+    (width, height, texels uint32[], mip_levels); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off)."""
     npx = width * height
     acc = np.zeros((npx, 4), np.float64)
     pos, p1 = view["pos"].astype(f32), view["p1"].astype(f32)
@@ -232,9 +266,18 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
     if materials is not None:
         materials = np.asarray(materials, f32)
         if materials.shape[-1] == 4:
-            full = np.zeros((len(materials), 12), f32)
-            full[:, :4], full[:, 5] = materials, 1
+            full = np.zeros((len(materials), 16), f32)
+            full[:, :4], full[:, 5], full[:, 11], full[:, 12:14] = materials, 1, -1, 1
             materials = full
+    tex_pool, tex_rec = np.zeros(1, np.uint32), []
+    if textures:
+        off = 0
+        chunks = []
+        for (tw, th, tx, mips) in textures:
+            tex_rec.append((off, tw, th, mips))
+            chunks.append(np.asarray(tx, np.uint32))
+            off += len(tx)
+        tex_pool = np.concatenate(chunks)
     invs = [np.linalg.inv(m.astype(np.float64)).astype(f32) for m in mats]
 
     def add(px, c):
@@ -314,14 +357,26 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                 known = mat < len(materials)
                 mk = materials[mat[known]]
                 color[known], rough[known], transmission[known], eta[known] = mk[:, :3], mk[:, 3], mk[:, 4], mk[:, 5]
-                smooth[known], absorption[known] = mk[:, 6] != 0, mk[:, 8:11]
+                mflags = np.zeros(n, np.int64)
+                mflags[known] = mk[:, 6].astype(np.int64)
+                smooth[known], absorption[known] = (mflags[known] & 1) != 0, mk[:, 8:11]
+                tex_id = np.full(n, -1, np.int64)
+                tex_id[known] = mk[:, 11].astype(np.int64)
+                uvso = np.zeros((n, 4), f32)
+                uvso[known] = mk[:, 12:16]
             # interpolated normals for SMOOTH materials: w N0 + u N1 + v N2 with the 16-bit barycentrics of the hit record
             sN[:] = N
-            if vertex_normals is not None:
+            I_all = (O + D * t[:, None]).astype(f32)
+            passthrough = np.zeros(n, bool)
+            mapped = np.zeros(n, bool)
+            if materials is not None and textures:
+                mapped = (tex_id >= 0) & (tex_id < len(tex_rec))
+            if vertex_normals is not None or mapped.any():
                 for i in np.unique(inst):
                     mesh = inst_mesh[i]
-                    sel = np.nonzero((inst == i) & smooth)[0]
-                    if vertex_normals[mesh] is None or len(sel) == 0:
+                    has_vn = vertex_normals is not None and vertex_normals[mesh] is not None
+                    sel = np.nonzero((inst == i) & ((smooth & has_vn) | mapped))[0]
+                    if len(sel) == 0:
                         continue
                     tri = meshes[mesh][prim[sel]]
                     iv = invs[i]
@@ -336,11 +391,41 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                     bu = np.floor(f32(65535) * bu).astype(f32) * f32(1.0 / 65535.0)
                     bv = np.floor(f32(65535) * bv).astype(f32) * f32(1.0 / 65535.0)
                     bw = f32(1) - (bu + bv)
-                    vn = vertex_normals[mesh][prim[sel]].astype(f32)
-                    on = (vn[:, 0] * bw[:, None] + vn[:, 1] * bu[:, None] + vn[:, 2] * bv[:, None]).astype(f32)
-                    ok = dot(on, on) > 0
-                    sN[sel[ok]] = normalize(to_world(mats[i], on[ok]))
-            I = (O + D * t[:, None]).astype(f32)
+                    if has_vn:
+                        sm = smooth[sel]
+                        vn = vertex_normals[mesh][prim[sel]].astype(f32)
+                        on = (vn[:, 0] * bw[:, None] + vn[:, 1] * bu[:, None] + vn[:, 2] * bv[:, None]).astype(f32)
+                        ok = sm & (dot(on, on) > 0)
+                        sN[sel[ok]] = normalize(to_world(mats[i], on[ok]))
+                    mp = mapped[sel]
+                    if mp.any():
+                        # diffuse map (material_shared.h:99-131): trilinear fetch at the ray-cone LOD, alpha below 0.5 = pass through
+                        q = sel[mp]
+                        uv = uvs[mesh][prim[q]].astype(f32) if (uvs is not None and uvs[mesh] is not None) else np.zeros((len(q), 3, 2), f32)
+                        ld = lods[mesh][prim[q]].astype(f32) if (lods is not None and lods[mesh] is not None) else np.zeros(len(q), f32)
+                        tu = (bw[mp] * uv[:, 0, 0] + bu[mp] * uv[:, 1, 0] + bv[mp] * uv[:, 2, 0]).astype(f32)
+                        tv = (bw[mp] * uv[:, 0, 1] + bu[mp] * uv[:, 1, 1] + bv[mp] * uv[:, 2, 1]).astype(f32)
+                        with np.errstate(all="ignore"):
+                            lam = (ld + np.log2(f32(spread_angle) * t[q] * (f32(1) / np.abs(dot(D[q], N[q]))))).astype(f32)
+                        rec = np.array([tex_rec[k] for k in tex_id[q]], np.int64)
+                        texel = fetch_texel_trilinear(tex_pool, lam, (uvso[q, 0] * (uvso[q, 2] + tu)).astype(f32), (uvso[q, 1] * (uvso[q, 3] + tv)).astype(f32),
+                                                      rec[:, 0], rec[:, 1], rec[:, 2], rec[:, 3])
+                        hole = ((mflags[q] & 2) != 0) & (texel[:, 3] < f32(0.5))
+                        passthrough[q[hole]] = True
+                        color[q[~hole]] = (color[q[~hole]] * texel[~hole, :3]).astype(f32)
+            I = I_all
+            # alpha holes (pathtracer.h:104-116): the path continues from just behind the surface with its state unchanged
+            carry = None
+            if passthrough.any() and length < max_path_length:
+                pt = passthrough
+                Tpt = T[pt].copy()
+                Tpt[~np.isfinite(Tpt.sum(axis=1))] = 0
+                carry = ((I[pt] + D[pt] * EPS).astype(f32), D[pt], Tpt, pdf_prev[pt], flags[pt], lastN[pt], path_idx[pt])
+            if passthrough.any():
+                kp = ~passthrough
+                O, D, T, t, prim, inst, path_idx, px, N, sN, I, color, rough = (a[kp] for a in (O, D, T, t, prim, inst, path_idx, px, N, sN, I, color, rough))
+                pdf_prev, flags, lastN, transmission, eta, absorption = (a[kp] for a in (pdf_prev, flags, lastN, transmission, eta, absorption))
+                n = len(O)
             # ---- paths that end on a light (pathtracer.h:120-148)
             emissive = (color > 1).any(axis=1)
             if emissive.any():
@@ -370,7 +455,10 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                 add(px[e][front], c[front])
             keep = ~emissive
             if not keep.any():
-                break
+                if carry is None:
+                    break
+                O, D, T, pdf_prev, flags, lastN, path_idx = carry
+                continue
             O, D, T, t, N, I, color, rough, path_idx, px = (a[keep] for a in (O, D, T, t, N, I, color, rough, path_idx, px))
             sN, transmission, eta, absorption = sN[keep], transmission[keep], eta[keep], absorption[keep]
             pdf_prev, flags, lastN = pdf_prev[keep], flags[keep], lastN[keep]
@@ -465,4 +553,6 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             newO = safe_origin(I, R, gF, EPS)
             newT = (T * bsdf * np.abs(cosr)[:, None]).astype(f32)
             O, D, T, pdf_prev, flags, lastN, path_idx = newO[alive], R[alive], newT[alive], new_pdf[alive], flags[alive], fN[alive], path_idx[alive]
+            if carry is not None:
+                O, D, T, pdf_prev, flags, lastN, path_idx = (np.concatenate([a, b]) for a, b in zip((O, D, T, pdf_prev, flags, lastN, path_idx), carry))
     return acc.reshape(height, width, 4).astype(f32)
