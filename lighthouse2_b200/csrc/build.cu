@@ -16,7 +16,12 @@
 // needs anyway.  Any conservative hierarchy gives the reference's closest hits (the BLAS traversal never culls by distance,
 // bvh.cpp:281-298), so results equal the SAH tree's; the LBVH tree is faster to build and slower to trace.
 #include "kernels.h"
+#include "wide_bvh.h"
 #include <cub/device/device_radix_sort.cuh>
+
+#ifndef B200_DP_COLLAPSE
+#define B200_DP_COLLAPSE 1 // children of a wide node from the SAH dynamic programme (1) or by opening the largest child (0)
+#endif
 #include <vector>
 
 namespace b200 {
@@ -121,10 +126,32 @@ __global__ void radixTreeKernel( const uint64_t* __restrict__ keys, const int n,
 	if (i == 0) parentInner[0] = 0xffffffffu;
 }
 
-// 4. boxes of the binary inner nodes: every sorted leaf walks up; the second thread to reach a node merges its children
+// 4. boxes of the binary inner nodes and the collapse plan: every sorted leaf walks up; the second thread to reach a node merges its
+// children.  The plan is the dynamic programme of bvh_builder.cpp (after Ylitie, Karras, Laine, HPG 2017, sec. 4.1) run bottom-up:
+// cost[i-1] = cheapest way to represent the subtree as a forest of at most i roots (i = 1: one wide node, or one leaf slot when it has
+// at most three triangles), node cost = area, leaf cost = area * triangles * primCost.  planLo = cost[0..3], planHi = cost[4..6] and a
+// word with the choices: bits 3(i-2)..3(i-2)+2 = left's share of i roots for i = 2..7 (0 = "use i-1 roots"), bits 18..20 = left's
+// share of the 8 slots when the node becomes a wide node, bit 21 = a single root is a leaf slot.
+__device__ __forceinline__ void loadPlan( const uint32_t ref, const uint32_t* __restrict__ sortedPrim, const float4* __restrict__ primLo, const float4* __restrict__ primHi,
+	const float4* planLo, const float4* planHi, const float primCost, float c[7] )
+{
+	if (ref & LEAF)
+	{
+		const uint32_t p = sortedPrim[ref & ~LEAF];
+		const float4 l = primLo[p], h = primHi[p];
+		const float x = h.x - l.x, y = h.y - l.y, z = h.z - l.z, v = (x * y + y * z + z * x) * primCost;
+		for (int i = 0; i < 7; i++) c[i] = v;
+	}
+	else
+	{
+		const float4 a = __ldcg( planLo + ref ), b = __ldcg( planHi + ref );
+		c[0] = a.x, c[1] = a.y, c[2] = a.z, c[3] = a.w, c[4] = b.x, c[5] = b.y, c[6] = b.z;
+	}
+}
+
 __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, const float4* __restrict__ primLo, const float4* __restrict__ primHi, const int n,
-	const uint32_t* __restrict__ childL, const uint32_t* __restrict__ childR, const uint32_t* __restrict__ parentInner, const uint32_t* __restrict__ parentLeaf,
-	float4* nodeLo, float4* nodeHi, uint32_t* visits )
+	const uint32_t* __restrict__ childL, const uint32_t* __restrict__ childR, const uint32_t* __restrict__ rangeCount, const uint32_t* __restrict__ parentInner,
+	const uint32_t* __restrict__ parentLeaf, float4* nodeLo, float4* nodeHi, float4* planLo, float4* planHi, const float primCost, uint32_t* visits )
 {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
@@ -141,15 +168,40 @@ __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, cons
 			if (c[k] & LEAF) { const uint32_t p = sortedPrim[c[k] & ~LEAF]; lo[k] = primLo[p], hi[k] = primHi[p]; }
 			else lo[k] = __ldcg( nodeLo + c[k] ), hi[k] = __ldcg( nodeHi + c[k] );
 		}
-		__stcg( nodeLo + node, make_float4( fminf( lo[0].x, lo[1].x ), fminf( lo[0].y, lo[1].y ), fminf( lo[0].z, lo[1].z ), 0 ) );
-		__stcg( nodeHi + node, make_float4( fmaxf( hi[0].x, hi[1].x ), fmaxf( hi[0].y, hi[1].y ), fmaxf( hi[0].z, hi[1].z ), 0 ) );
+		const float4 nl = make_float4( fminf( lo[0].x, lo[1].x ), fminf( lo[0].y, lo[1].y ), fminf( lo[0].z, lo[1].z ), 0 );
+		const float4 nh = make_float4( fmaxf( hi[0].x, hi[1].x ), fmaxf( hi[0].y, hi[1].y ), fmaxf( hi[0].z, hi[1].z ), 0 );
+		__stcg( nodeLo + node, nl ), __stcg( nodeHi + node, nh );
+		// collapse plan
+		float cl[7], cr[7], cost[7];
+		loadPlan( c[0], sortedPrim, primLo, primHi, planLo, planHi, primCost, cl );
+		loadPlan( c[1], sortedPrim, primLo, primHi, planLo, planHi, primCost, cr );
+		const float ex = nh.x - nl.x, ey = nh.y - nl.y, ez = nh.z - nl.z, area = ex * ey + ey * ez + ez * ex;
+		uint32_t bits = 0;
+		float best8 = 3.0e38f;
+		int k8 = 4;
+		for (int k = 1; k < 8; k++) { const float v = cl[k - 1] + cr[8 - k - 1]; if (v < best8) best8 = v, k8 = k; }
+		const uint32_t count = rangeCount[node];
+		const float wideCost = area + best8, leafCost = count <= 3 ? area * (float)count * primCost : 3.0e38f;
+		cost[0] = fminf( leafCost, wideCost );
+		bits |= (uint32_t)k8 << 18;
+		if (leafCost <= wideCost) bits |= 1u << 21;
+		for (int r = 2; r <= 7; r++)
+		{
+			float best = 3.0e38f;
+			int bk = 1;
+			for (int k = 1; k < r; k++) { const float v = cl[k - 1] + cr[r - k - 1]; if (v < best) best = v, bk = k; }
+			if (best < cost[r - 2]) cost[r - 1] = best, bits |= (uint32_t)bk << (3 * (r - 2));
+			else cost[r - 1] = cost[r - 2];
+		}
+		__stcg( planLo + node, make_float4( cost[0], cost[1], cost[2], cost[3] ) );
+		__stcg( planHi + node, make_float4( cost[4], cost[5], cost[6], __uint_as_float( bits ) ) );
 		node = parentInner[node];
 	}
 }
 
 struct CollapseArgs {
 	const uint32_t *sortedPrim, *childL, *childR, *rangeFirst, *rangeCount;
-	const float4 *primLo, *primHi, *nodeLo, *nodeHi;
+	const float4 *primLo, *primHi, *nodeLo, *nodeHi, *planHi;
 	uint32_t* wideToBinary;   // [maxNodes] binary inner node that wide node w represents
 	uint4* nodes;             // output, relative index 0 = this mesh's root (pool pointer already offset)
 	float4* tris;             // output triangle records (pool pointer already offset): only .w of the first float4 (the primitive tag) is written
@@ -173,7 +225,43 @@ __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin,
 	const uint32_t root = a.wideToBinary[w];
 	uint32_t ref[8], cnt[8];
 	float lo[8][3], hi[8][3];
-	int n = 2;
+	bool innerChild[8];
+	int n = 0;
+#if B200_DP_COLLAPSE
+	// the children are the forest the plan chose: left gets k8 of the eight slots, right the rest; a subtree with an allowance of i
+	// roots either settles for fewer (choice 0), becomes one root (a leaf slot or a wide node), or hands k roots to its left child
+	{
+		const uint32_t rootBits = __float_as_uint( a.planHi[root].w ), k8 = (rootBits >> 18) & 7u;
+		uint32_t stackRef[8], stackAllow[8];
+		int sp = 0;
+		stackRef[sp] = a.childR[root], stackAllow[sp++] = 8 - k8;
+		stackRef[sp] = a.childL[root], stackAllow[sp++] = k8;
+		while (sp)
+		{
+			const uint32_t m = stackRef[--sp];
+			uint32_t allow = stackAllow[sp];
+			uint32_t bits = 0;
+			if (!(m & LEAF))
+			{
+				bits = __float_as_uint( a.planHi[m].w );
+				while (allow > 1 && ((bits >> (3 * (allow - 2))) & 7u) == 0) allow--;
+			}
+			if ((m & LEAF) || allow == 1)
+			{
+				ref[n] = m, innerChild[n] = !(m & LEAF) && !((bits >> 21) & 1u);
+				refBox( a, m, lo[n], hi[n], cnt[n] );
+				n++;
+			}
+			else
+			{
+				const uint32_t k = (bits >> (3 * (allow - 2))) & 7u;
+				stackRef[sp] = a.childR[m], stackAllow[sp++] = allow - k;
+				stackRef[sp] = a.childL[m], stackAllow[sp++] = k;
+			}
+		}
+	}
+#else
+	n = 2;
 	ref[0] = a.childL[root], ref[1] = a.childR[root];
 	refBox( a, ref[0], lo[0], hi[0], cnt[0] ), refBox( a, ref[1], lo[1], hi[1], cnt[1] );
 	// open the largest child that is still too big for a leaf slot until all eight slots are used
@@ -192,6 +280,8 @@ __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin,
 		refBox( a, ref[best], lo[best], hi[best], cnt[best] ), refBox( a, ref[n], lo[n], hi[n], cnt[n] );
 		n++;
 	}
+	for (int i = 0; i < n; i++) innerChild[i] = cnt[i] > 3;
+#endif
 	// octant slots: slot s is visited first by rays whose direction signs are the complement of s (traverse.cu), so a child
 	// goes to the slot whose sign vector it lies farthest against -- greedy over the 8 x n table, as AssignSlots does on the host
 	float nlo[3], nhi[3];
@@ -220,7 +310,7 @@ __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin,
 		childInSlot[bs] = bi, done |= 1u << bi;
 	}
 	uint32_t innerCount = 0, leafPrims = 0;
-	for (int i = 0; i < n; i++) if (cnt[i] > 3) innerCount++; else leafPrims += cnt[i];
+	for (int i = 0; i < n; i++) if (innerChild[i]) innerCount++; else leafPrims += cnt[i];
 	const uint32_t childBase = innerCount ? atomicAdd( a.counters, innerCount ) : 0;
 	const uint32_t primBase = leafPrims ? atomicAdd( a.counters + 1, leafPrims ) : 0;
 	if (childBase + innerCount > a.maxNodes) { atomicExch( a.counters + 2, 1u ); return; }
@@ -230,7 +320,7 @@ __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin,
 		const int i = childInSlot[s];
 		if (i < 0) continue;
 		uint32_t meta;
-		if (cnt[i] > 3)
+		if (innerChild[i])
 		{
 			imask |= 1u << s, meta = 0x20u | (24u + (uint32_t)s);
 			a.wideToBinary[childBase + inner] = ref[i];
@@ -273,9 +363,11 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	const size_t oVals = take( (size_t)T * 4 ), oVals2 = take( (size_t)T * 4 ), oSort = take( sortBytes );
 	const size_t oChildL = take( (size_t)T * 4 ), oChildR = take( (size_t)T * 4 ), oFirst = take( (size_t)T * 4 ), oCount = take( (size_t)T * 4 );
 	const size_t oParI = take( (size_t)T * 4 ), oParL = take( (size_t)T * 4 ), oVisits = take( (size_t)T * 4 );
-	const size_t oNodeLo = take( (size_t)T * 16 ), oNodeHi = take( (size_t)T * 16 ), oW2B = take( (size_t)maxNodes * 4 + 64 ), oSmall = take( 256 );
+	const size_t oNodeLo = take( (size_t)T * 16 ), oNodeHi = take( (size_t)T * 16 ), oPlanLo = take( (size_t)T * 16 ), oPlanHi = take( (size_t)T * 16 );
+	const size_t oW2B = take( (size_t)maxNodes * 4 + 64 ), oSmall = take( 256 );
 	if ((e = cudaMallocAsync( (void**)&scratch, off, s )) != cudaSuccess) return e;
 	float4 *primLo = (float4*)(scratch + oPrimLo), *primHi = (float4*)(scratch + oPrimHi), *nodeLo = (float4*)(scratch + oNodeLo), *nodeHi = (float4*)(scratch + oNodeHi);
+	float4 *planLo = (float4*)(scratch + oPlanLo), *planHi = (float4*)(scratch + oPlanHi);
 	uint64_t *keys = (uint64_t*)(scratch + oKeys), *keys2 = (uint64_t*)(scratch + oKeys2);
 	uint32_t *vals = (uint32_t*)(scratch + oVals), *vals2 = (uint32_t*)(scratch + oVals2);
 	uint32_t *childL = (uint32_t*)(scratch + oChildL), *childR = (uint32_t*)(scratch + oChildR), *first = (uint32_t*)(scratch + oFirst), *count = (uint32_t*)(scratch + oCount);
@@ -296,11 +388,11 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	mortonKernel<<<blocks, 256, 0, s>>>( primLo, primHi, T, cbounds, keys, vals );
 	if ((e = cub::DeviceRadixSort::SortPairs( scratch + oSort, sortBytes, keys, keys2, vals, vals2, (int)T, 0, 63, s )) != cudaSuccess) return done( e );
 	radixTreeKernel<<<blocks, 256, 0, s>>>( keys2, (int)T, childL, childR, first, count, parI, parL );
-	binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, parI, parL, nodeLo, nodeHi, visits );
+	binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, count, parI, parL, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost, visits );
 	if ((e = cudaGetLastError()) != cudaSuccess) return done( e );
 	CollapseArgs a;
 	a.sortedPrim = vals2, a.childL = childL, a.childR = childR, a.rangeFirst = first, a.rangeCount = count;
-	a.primLo = primLo, a.primHi = primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi;
+	a.primLo = primLo, a.primHi = primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = planHi;
 	a.wideToBinary = w2b, a.nodes = nodes, a.tris = tris, a.counters = counters;
 	a.nodeBase = nodeBase, a.triBase = triBase, a.maxNodes = maxNodes;
 	levelStart.clear();

@@ -221,7 +221,7 @@ int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T,
 	MeshRec m;
 	m.nodeBase = blasNodeEnd, m.triBase = triEnd, m.triCount = T;
 	if ((uint64_t)m.triBase + T + 32 >= (1ull << 27)) return fail( "SetGeometry: more than 2^27 triangles in one core (queue entries carry 27-bit triangle indices)" );
-	const uint32_t maxNodes = T / 2 + 64;
+	const uint32_t maxNodes = T + 64; // one wide node per binary inner node at most
 	// shading records: the refit below writes the geometric normals; only CoreTri::material has to come from the host
 	std::vector<ShadeRec> shade;
 	if (coreTris)
