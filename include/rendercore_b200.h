@@ -98,6 +98,10 @@ B200_API int b200_set_material_colors( b200_core* c, const float* rgba, int coun
 B200_API int b200_set_material_table( b200_core* c, const float* props16, int count );
 /* CoreAPI_Base::SetTextures (core_api_base.h:98): CoreTexDesc[count] in the host layout (40 bytes, common_classes.h:246-269); call before
  * the materials.  ARGB32 maps are copied (MIP levels included) and sampled as the diffuse map of the materials that name them */
+/* Diagnostic: evaluate the Disney BSDF of the shade stage (Setting "bsdf" = 1) on its own, on the device.  in28: 28 floats per
+ * item (color, transmittance, three 0.8 fixed-point parameter words as bits, eta, iN, N, iT, wow, then distance r0 r1 for mode 0 =
+ * SampleBSDF or wiw for mode 1 = EvaluateBSDF; lib/sharedBSDFs/disney.h:227,314); out8: wiw, pdf, value, specular. */
+B200_API int b200_disney_probe( b200_core* c, int mode, int n, const float* in28, float* out8 );
 B200_API int b200_set_textures( b200_core* c, const void* coreTexDescs, int count );
 /* multi-GPU: render into a caller-owned device accumulator float4[w*h] (e.g. a torch tensor that NCCL reduces);
  * NULL = the core's own.  After the gather, b200_finalize( total samples ) rebuilds the frame from it. */

@@ -25,6 +25,7 @@ C_ABI_SYMBOLS = [
     "b200_set_point_light", "b200_set_sky", "b200_set_lights", "b200_set_sky_data", "b200_render", "b200_read_accumulator", "b200_read_frame",
     "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
     "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors", "b200_set_material_table", "b200_set_textures",
+    "b200_disney_probe",
     "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
 ]
 
@@ -88,6 +89,7 @@ def load_library() -> C.CDLL:
         "b200_device_accumulator": ([vp], vp), "b200_get_stats": ([vp, C.POINTER(Stats)], ip), "b200_set_probe": ([vp, ip, ip], ip),
         "b200_plugin_core": ([], vp), "b200_host_alloc": ([C.c_uint64], vp), "b200_host_free": ([vp], None),
         "b200_set_materials": ([vp, vp, ip], ip), "b200_set_material_colors": ([vp, vp, ip], ip), "b200_set_material_table": ([vp, vp, ip], ip), "b200_set_textures": ([vp, vp, ip], ip),
+        "b200_disney_probe": ([vp, ip, ip, vp, vp], ip),
         "b200_set_accumulator_buffer": ([vp, vp], ip), "b200_finalize": ([vp, C.c_uint32], ip),
         "b200_trace_connect_device": ([vp, vp, vp, ip, vp, vp], ip),
     }
@@ -126,11 +128,12 @@ def unpack_hits(hits: np.ndarray):
     }
 
 
-def core_tris(verts: np.ndarray, materials=None, vertex_normals=None, uvs=None, lod=None) -> np.ndarray:
+def core_tris(verts: np.ndarray, materials=None, vertex_normals=None, uvs=None, lod=None, tangents=None, alphas=None) -> np.ndarray:
     """CoreTri[T] (176 bytes each, lib/RenderSystem/common_classes.h:60-82) for verts[T,3,3]: material (offset 28),
     geometric normal Nx/Ny/Nz (44/60/76), area (92) and vertex0/1/2 (128/144/160) filled, the rest zero; ltriIdx = -1.
     vertex_normals[T,3,3] fills vN0/vN1/vN2 (offsets 32/48/64) for SMOOTH materials; uvs[T,3,2] the texture coordinates
-    u0..2 / v0..2 (offsets 0 / 16), lod[T] CoreTri::LOD (124)."""
+    u0..2 / v0..2 (offsets 0 / 16), lod[T] CoreTri::LOD (124), tangents[T,3] CoreTri::T (80; the Disney BSDF's anisotropy
+    axis), alphas[T,3] the per-vertex angles of the consistent-normal interpolation (CoreTri::alpha, 112)."""
     v = np.asarray(verts, np.float32)
     t = v.shape[0]
     out = np.zeros((t, 44), np.float32)
@@ -148,9 +151,61 @@ def core_tris(verts: np.ndarray, materials=None, vertex_normals=None, uvs=None, 
         out[:, 0:3], out[:, 4:7] = uv[:, :, 0], uv[:, :, 1]
     if lod is not None:
         out[:, 31] = np.asarray(lod, np.float32)
+    if tangents is not None:
+        out[:, 20:23] = np.asarray(tangents, np.float32)
+    if alphas is not None:
+        out[:, 28:31] = np.asarray(alphas, np.float32)
     iv = out.view(np.int32)
     iv[:, 3] = -1
     iv[:, 7] = 0 if materials is None else np.asarray(materials, np.int32)
+    return out
+
+
+# CoreMaterial (688 bytes, lib/RenderSystem/common_classes.h:177-238): byte offset of each value; Vec3Value = value float3,
+# textureID, scale, uvscale, uvoffset (40 B); ScalarValue = value, textureID, component, scale, uvscale, uvoffset (32 B)
+CORE_MATERIAL_SCALARS = dict(metallic=208, subsurface=240, specular=272, roughness=304, specularTint=336, anisotropic=368, sheen=400,
+                             sheenTint=432, clearcoat=464, clearcoatGloss=496, transmission=528, eta=560)
+CORE_MATERIAL_DEFAULTS = dict(metallic=0.0, subsurface=0.0, specular=0.5, roughness=0.5, specularTint=0.0, anisotropic=0.0, sheen=0.0,
+                              sheenTint=0.0, clearcoat=0.0, clearcoatGloss=1.0, transmission=0.0, eta=1.0)  # host_material.h
+
+
+def core_materials(materials) -> np.ndarray:
+    """CoreMaterial[n] as bytes [n, 688] from a list of dicts: color (rgb), absorption (rgb, default 0), flags (1 SMOOTH,
+    2 HASALPHA), texture (diffuse map index, default -1), uvscale / uvoffset, and the Disney scalars of
+    CORE_MATERIAL_SCALARS (HostMaterial defaults where missing).  Every textureID that is not given is -1."""
+    out = np.zeros((len(materials), 688), np.uint8)
+    f, i = out.view(np.float32), out.view(np.int32)
+    for k, m in enumerate(materials):
+        for off in (0, 40, 80, 120, 168):  # color, detailColor, normals, detailNormals, absorption
+            i[k, off // 4 + 3] = -1
+            f[k, off // 4 + 4] = 1.0
+            f[k, off // 4 + 5:off // 4 + 7] = 1.0
+        for off in list(CORE_MATERIAL_SCALARS.values()) + [592, 624, 656]:
+            i[k, off // 4 + 1] = -1
+            f[k, off // 4 + 3] = 1.0
+            f[k, off // 4 + 4:off // 4 + 6] = 1.0
+        f[k, 0:3] = m.get("color", (0.8, 0.8, 0.8))
+        i[k, 3] = m.get("texture", -1)
+        f[k, 6:8] = m.get("uvscale", (1.0, 1.0))
+        f[k, 8:10] = m.get("uvoffset", (0.0, 0.0))
+        i[k, 40] = m.get("flags", 0)
+        f[k, 42:45] = m.get("absorption", (0.0, 0.0, 0.0))
+        for name, off in CORE_MATERIAL_SCALARS.items():
+            f[k, off // 4] = m.get(name, CORE_MATERIAL_DEFAULTS[name])
+    return out
+
+
+def disney_words(materials) -> np.ndarray:
+    """The three 0.8 fixed-point parameter words per material as the cores pack them (TOUINT4,
+    lib/rendercore_optix7/rendercore.cpp:511-512, 532-534) plus eta as float bits: uint32[n, 4]."""
+    order = ["metallic", "subsurface", "specular", "roughness", "specularTint", "anisotropic", "sheen", "sheenTint", "clearcoat",
+             "clearcoatGloss", "transmission"]
+    out = np.zeros((len(materials), 4), np.uint32)
+    for k, m in enumerate(materials):
+        for j, name in enumerate(order):
+            v = np.float32(m.get(name, CORE_MATERIAL_DEFAULTS[name]))
+            out[k, j // 4] += np.uint32(int(np.float32(v * np.float32(255.0)))) << np.uint32(8 * (j & 3))
+        out[k, 3] = np.float32(m.get("eta", CORE_MATERIAL_DEFAULTS["eta"])).view(np.uint32)
     return out
 
 
@@ -280,6 +335,19 @@ class RenderCoreB200:
     def SetMaterialColors(self, rgba):
         c = np.ascontiguousarray(rgba, np.float32).reshape(-1, 4)
         self._chk(self.lib.b200_set_material_colors(self.h, c.ctypes.data, c.shape[0]))
+
+    def SetMaterials(self, materials):
+        """CoreAPI_Base::SetMaterials: CoreMaterial bytes [n, 688] (core_materials) or a list of dicts for core_materials."""
+        c = materials if isinstance(materials, np.ndarray) else core_materials(materials)
+        c = np.ascontiguousarray(c, np.uint8).reshape(-1, 688)
+        self._chk(self.lib.b200_set_materials(self.h, c.ctypes.data, c.shape[0]))
+
+    def DisneyProbe(self, mode: int, items: np.ndarray) -> np.ndarray:
+        """b200_disney_probe: float32[n, 28] -> float32[n, 8] (see include/rendercore_b200.h)."""
+        a = np.ascontiguousarray(items, np.float32).reshape(-1, 28)
+        out = np.zeros((a.shape[0], 8), np.float32)
+        self._chk(self.lib.b200_disney_probe(self.h, mode, a.shape[0], a.ctypes.data, out.ctypes.data))
+        return out
 
     def SetMaterialTable(self, props):
         """float32[n, 16]: albedo rgb, roughness | transmission, eta, flags (1 SMOOTH + 2 HASALPHA), 0 | extinction rgb,

@@ -60,6 +60,7 @@ int b200_set_materials( b200_core* c, const void* coreMaterials, int count ) { F
 int b200_set_material_colors( b200_core* c, const float* rgba, int count ) { FORWARD( c, SetMaterialColors( rgba, count ) ) }
 int b200_set_material_table( b200_core* c, const float* props16, int count ) { FORWARD( c, SetMaterialTable( props16, count ) ) }
 int b200_set_textures( b200_core* c, const void* coreTexDescs, int count ) { FORWARD( c, SetTextures( coreTexDescs, count ) ) }
+int b200_disney_probe( b200_core* c, int mode, int n, const float* in28, float* out8 ) { FORWARD( c, DisneyProbe( mode, n, in28, out8 ) ) }
 int b200_set_accumulator_buffer( b200_core* c, void* dAcc ) { FORWARD( c, SetAccumulatorBuffer( dAcc ) ) }
 int b200_finalize( b200_core* c, uint32_t totalSamples ) { FORWARD( c, Finalize( totalSamples ) ) }
 int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, int n, const void* dE4, void* dAcc ) { FORWARD( c, TraceConnectDevice( dO4, dD4, n, dE4, dAcc ) ) }

@@ -192,21 +192,24 @@ int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 {
 	if (!coreTris && !vnormPool.ptr) return 0;
 	cudaError_t e;
-	const size_t oldBytes = vnormPool.bytes, need = (size_t)(m.triBase + m.triCount + 1) * 64;
+	constexpr size_t REC = TRI_ATTR_STRIDE * 16; // bytes per triangle
+	const size_t oldBytes = vnormPool.bytes, need = (size_t)(m.triBase + m.triCount + 1) * REC;
 	if ((e = vnormPool.reserve( need, true, stream )) != cudaSuccess) return fail( "triangle attribute pool", e );
 	if (vnormPool.bytes > oldBytes && (e = cudaMemsetAsync( (char*)vnormPool.ptr + oldBytes, 0, vnormPool.bytes - oldBytes, stream )) != cudaSuccess) return fail( "triangle attribute pool", e );
-	char* dst = (char*)vnormPool.ptr + (size_t)m.triBase * 64;
-	if (!coreTris) e = cudaMemsetAsync( dst, 0, (size_t)m.triCount * 64, stream );
+	char* dst = (char*)vnormPool.ptr + (size_t)m.triBase * REC;
+	if (!coreTris) e = cudaMemsetAsync( dst, 0, (size_t)m.triCount * REC, stream );
 	else
 	{
-		std::vector<float> at( (size_t)m.triCount * 16 );
+		// CoreTri (common_classes.h:62-83): u0..2 @0, v0..2 @16, vN0 @32, vN1 @48, vN2 @64, T @80, alpha @112 (w = LOD)
+		std::vector<float> at( (size_t)m.triCount * TRI_ATTR_STRIDE * 4, 0.f );
 		for (uint32_t i = 0; i < m.triCount; i++)
 		{
 			const char* ct = (const char*)coreTris + (size_t)i * 176;
-			float* o = &at[(size_t)i * 16];
+			float* o = &at[(size_t)i * TRI_ATTR_STRIDE * 4];
 			memcpy( o, ct + 32, 12 ), memcpy( o + 4, ct + 48, 12 ), memcpy( o + 8, ct + 64, 12 );
 			memcpy( o + 3, ct, 4 ), memcpy( o + 7, ct + 4, 4 ), memcpy( o + 11, ct + 8, 4 );
 			memcpy( o + 12, ct + 16, 12 ), memcpy( o + 15, ct + 124, 4 );
+			memcpy( o + 16, ct + 80, 12 ), memcpy( o + 19, ct + 112, 4 ), memcpy( o + 20, ct + 116, 8 );
 		}
 		e = cudaMemcpyAsync( dst, at.data(), at.size() * 4, cudaMemcpyHostToDevice, stream );
 		if (e == cudaSuccess) e = cudaStreamSynchronize( stream ); // the staging vector dies here

@@ -47,6 +47,8 @@ public:
 	int SetSkyData( const float* rgb, int width, int height ); // equirectangular float3 image
 	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value and roughness.value
 	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: (albedo rgb, roughness) per material; rgb > 1 = emissive
+	int DisneyProbe( int mode, int n, const float* in28, float* out8 ); // diagnostic: the Disney BSDF alone (wavefront.cu::disneyProbeKernel)
+	int uploadMaterials( const float* props16, const uint32_t* disneyWords, int count );
 	int SetMaterialTable( const float* props16, int count );  // 16 floats per material, see wavefront.cu
 	int SetTextures( const void* coreTexDescs, int count );   // CoreTexDesc[count], host layout, 40 B each; ARGB32 maps are sampled
 	int SetAccumulatorBuffer( void* devicePtr );              // caller-owned float4[w*h] accumulator (multi-GPU gathers), null = own
@@ -95,7 +97,7 @@ private:
 	std::string error;
 	int device = 0;
 	// acceleration structure pools
-	DeviceBuffer nodePool, triPool, instPool, shadePool, vnormPool, instShadePool; // vnormPool: per-triangle shading attributes (vertex normals, uv, LOD), only when CoreTris were supplied
+	DeviceBuffer nodePool, triPool, instPool, shadePool, vnormPool, instShadePool; // vnormPool: per-triangle shading attributes (TRI_ATTR_STRIDE float4: vertex normals, uv, LOD, tangent, vertex alphas), only when CoreTris were supplied
 	uint32_t blasNodeEnd = 0, triEnd = 0, tlasRoot = 0, tlasNodeCount = 0;
 	std::vector<MeshRec> meshes;
 	std::vector<InstanceHost> instances;

@@ -31,7 +31,7 @@ namespace b200 {
 namespace {
 
 constexpr int TILE_W = 32, TILE_H = 8, TILE_PIXELS = TILE_W * TILE_H;
-constexpr float INVPI = 0.31830988618379067154f, TWOPI = 6.28318530717958647692f;
+constexpr float PI = 3.14159265358979323846f, INVPI = 0.31830988618379067154f, TWOPI = 6.28318530717958647692f;
 
 constexpr int MAX_PATH_LENGTH = 16; // MAXPATHLENGTH of the optix7 core (core_settings.h:24)
 // Device-resident wave counters (the reference's Counters, core_settings.h:103-117), uint32 words:
@@ -218,6 +218,7 @@ __device__ __forceinline__ V3 operator*( const V3 a, const V3 b ) { return v3( a
 __device__ __forceinline__ V3 operator*( const V3 a, const float s ) { return v3( a.x * s, a.y * s, a.z * s ); }
 __device__ __forceinline__ float dot( const V3 a, const V3 b ) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ V3 normalize( const V3 a ) { return a * (1.0f / sqrtf( dot( a, a ) )); }
+#include "disney.cuh"
 
 // ---- lights (lib/CUDA/shared_kernel_code/lights_shared.h) ---------------------------------------------------------------------------
 // potential contribution of light i to a surface point I with normal N: the importance used to pick a light (:33-94).
@@ -425,7 +426,7 @@ __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 #ifndef B200_SHADE_GRID
 #define B200_SHADE_GRID 8
 #endif
-__global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( const FrameParams f, const int pathLength, const int maxPathLength,
+template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200_SHADE_MIN_BLOCKS ) shadeKernel( const FrameParams f, const int pathLength, const int maxPathLength,
 	const float4* __restrict__ rayO, const float4* __restrict__ rayD, const float4* __restrict__ pathState, const float4* __restrict__ pathInfo,
 	const float4* __restrict__ hits,
 	float4* __restrict__ rayOout, float4* __restrict__ rayDout, float4* __restrict__ pathStateOut, float4* __restrict__ pathInfoOut,
@@ -471,26 +472,37 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 				// interpolated and the normal-mapped normal (iN, fN) of GetShadingData
 				const V3 N = normalize( v3( m0.x * sh.x + m0.y * sh.y + m0.z * sh.z, m1.x * sh.x + m1.y * sh.y + m1.z * sh.z, m2.x * sh.x + m2.y * sh.y + m2.z * sh.z ) );
 				const uint32_t mat = __float_as_uint( sh.w );
-				// material table, 5 float4 per material: (albedo rgb, roughness) (transmission, eta, flag bits, MIP levels)
-				// (extinction rgb, first texel) (uv scale, uv offset) (texture width, height, -, -); flags: 1 SMOOTH, 2 HASALPHA, 4 diffuse map
+				// material table, MAT_STRIDE float4 per material: (albedo rgb, roughness) (transmission, eta, flag bits, MIP levels)
+				// (extinction rgb, first texel) (uv scale, uv offset) (texture width, height, -, -) (Disney parameter words x y z, -);
+				// flags: 1 SMOOTH, 2 HASALPHA, 4 diffuse map
 				V3 color = v3( 0.8f, 0.8f, 0.8f ), absorption = v3( 0.f, 0.f, 0.f );
 				float roughness = 1.0f, transmission = 0.0f, eta = 1.0f;
 				uint32_t mflags = 0;
 				float4 c1 = make_float4( 0, 0, 0, 0 ), c2 = c1, c3 = c1, c4 = c1;
+				disney::Data dd;
+				if (DISNEY) disney::Unpack( dd, 0x80800000u /* specular 0.5, roughness 0.5 */, 0u, 0u ), dd.eta = 1.0f;
 				if (mat < f.materialCount)
 				{
-					const float4 c0 = __ldg( materials + mat * 5 );
-					c1 = __ldg( materials + mat * 5 + 1 ), c2 = __ldg( materials + mat * 5 + 2 );
+					const float4 c0 = __ldg( materials + mat * MAT_STRIDE );
+					c1 = __ldg( materials + mat * MAT_STRIDE + 1 ), c2 = __ldg( materials + mat * MAT_STRIDE + 2 );
 					color = v3( c0 ), roughness = c0.w, transmission = c1.x, eta = c1.y, mflags = __float_as_uint( c1.z ), absorption = v3( c2 );
+					if (DISNEY)
+					{
+						const float4 c5 = __ldg( materials + mat * MAT_STRIDE + 5 );
+						disney::Unpack( dd, __float_as_uint( c5.x ), __float_as_uint( c5.y ), __float_as_uint( c5.z ) );
+						dd.eta = eta, roughness = dd.roughness, transmission = dd.transmission; // the 0.8 fixed-point values drive the specular test too
+					}
 				}
+				if (DISNEY) disney::Tint( dd, color );
 				// per-triangle attributes (CoreTri): vertex normals, texture coordinates, LOD -- 4 float4: (vN0,u0) (vN1,u1) (vN2,u2) (v0,v1,v2,LOD)
 				const uint32_t bary = __float_as_uint( hit.x );
 				const float bu = (float)(bary & 0xffffu) * (1.0f / 65535.0f), bv = (float)(bary >> 16) * (1.0f / 65535.0f), bw = 1 - (bu + bv);
-				float4 a0 = make_float4( 0, 0, 0, 0 ), a1 = a0, a2 = a0, a3 = a0;
-				if ((mflags & 5u) && vertexNormals)
+				float4 a0 = make_float4( 0, 0, 0, 0 ), a1 = a0, a2 = a0, a3 = a0, a4 = a0, a5 = a0;
+				if (((mflags & 5u) || DISNEY) && vertexNormals)
 				{
-					const float4* ta = vertexNormals + (size_t)(__float_as_uint( info.x ) + prim) * 4;
+					const float4* ta = vertexNormals + (size_t)(__float_as_uint( info.x ) + prim) * TRI_ATTR_STRIDE;
 					a0 = __ldg( ta ), a1 = __ldg( ta + 1 ), a2 = __ldg( ta + 2 ), a3 = __ldg( ta + 3 );
+					if (DISNEY) a4 = __ldg( ta + 4 ), a5 = __ldg( ta + 5 ); // (tangent, alpha0) (alpha1, alpha2, -, -)
 				}
 				// interpolated normal (GetShadingData, material_shared.h:75-81: w N0 + u N1 + v N2 for SMOOTH materials), transformed like N;
 				// it also stands in for the normal-mapped normal fN.  (Consistent normals, :90-97, need the per-vertex alpha of the
@@ -502,11 +514,24 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 					if (dot( on, on ) > 0)
 						sN = normalize( v3( m0.x * on.x + m0.y * on.y + m0.z * on.z, m1.x * on.x + m1.y * on.y + m1.z * on.z, m2.x * on.x + m2.y * on.y + m2.z * on.z ) );
 				}
+				V3 tangent = v3( a4 );
+				if (DISNEY)
+				{
+					// consistent normal interpolation (material_shared.h:87-97) with the per-vertex alphas of the host mesh
+					if (vertexNormals)
+					{
+						const bool backSide = dot( D, N ) > 0;
+						const float alpha = bw * a4.w + bu * a5.x + bv * a5.y;
+						sN = disney::ConsistentNormal( D * -1.0f, backSide ? sN * -1.0f : sN, alpha ) * (backSide ? -1.0f : 1.0f);
+					}
+					// the reference takes CoreTri::T as it is (object space); a mesh without CoreTris gets an arbitrary tangent
+					if (!(dot( tangent, tangent ) > 0)) tangent = fabsf( sN.x ) > 0.9f ? v3( 0.f, 1.f, 0.f ) : v3( 1.f, 0.f, 0.f );
+				}
 				const V3 I = O + D * hit.w;
 				// diffuse map (material_shared.h:99-131): trilinear fetch at the ray-cone LOD; an alpha texel below 0.5 lets the path through
 				if ((mflags & 4u) && f.texels)
 				{
-					c3 = __ldg( materials + mat * 5 + 3 ), c4 = __ldg( materials + mat * 5 + 4 );
+					c3 = __ldg( materials + mat * MAT_STRIDE + 3 ), c4 = __ldg( materials + mat * MAT_STRIDE + 4 );
 					const float tu = bw * a0.w + bu * a1.w + bv * a2.w, tv = bw * a3.x + bu * a3.y + bv * a3.z;
 					const float lambda = a3.w + log2f( f.spreadAngle * hit.w * (1.0f / fabsf( dot( D, N ) )) );
 					const float4 texel = FetchTexelTrilinear( f.texels, lambda, c3.x * (c3.z + tu), c3.y * (c3.w + tv), __float_as_uint( c2.w ),
@@ -571,10 +596,13 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 						if (NdotL > 0 && lightPdf > 0)
 						{
 							// EvaluateBSDF (lambert.h:58-69): color / pi, pdf = |cos| / pi; scaled by the chance of a diffuse bounce (:186)
-							const float lbsdfPdf = fabsf( NdotL ) * INVPI;
+							float lbsdfPdf = fabsf( NdotL ) * INVPI;
+							V3 sampled = color * (INVPI * roughness);
+							if (DISNEY) dd.color = color, dd.transmittance = absorption, sampled = disney::EvaluateBSDF( dd, sN, tangent, D * -1.0f, L, lbsdfPdf ); // unflipped normal (:186)
 							if (lbsdfPdf > 0)
 							{
-								se = ClampAndFix( throughput * color * lightColor * (INVPI * roughness * (NdotL / (pickProb * lightPdf + lbsdfPdf))), f.clampValue );
+								if (DISNEY) se = ClampAndFix( throughput * sampled * lightColor * (NdotL / (pickProb * lightPdf + lbsdfPdf)), f.clampValue );
+								else se = ClampAndFix( throughput * color * lightColor * (INVPI * roughness * (NdotL / (pickProb * lightPdf + lbsdfPdf))), f.clampValue );
 								SafeOrigin( I.x, I.y, I.z, L.x, L.y, L.z, gF.x, gF.y, gF.z, f.epsilon, so.x, so.y, so.z );
 								sl = L, sdist = dist - 2 * f.epsilon;
 								wantShadow = true;
@@ -590,7 +618,13 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 						V3 R = sF, bsdf = v3( 0.f, 0.f, 0.f );
 						float newPdf = 1;
 						bool specular = true, refracted = false;
-						if (r4 < transmission)
+						if (DISNEY)
+						{
+							specular = false;
+							dd.color = color, dd.transmittance = absorption;
+							bsdf = disney::SampleBSDF( dd, sN, N, tangent, D * -1.0f, hit.w, r3, r4, R, newPdf, specular );
+						}
+						else if (r4 < transmission)
 						{
 							// dielectric: Fresnel reflection or refraction, Beer absorption over the distance travelled inside (:84-103)
 							const float eio = faceDir < 0 ? 1.0f / eta : eta;
@@ -639,7 +673,7 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 								bsdf = color * INVPI;
 							}
 						}
-						if (!refracted && dot( gF, R ) <= 0) newPdf = 0; // the sampled direction must leave on the geometric side (:121); refraction returns before this test
+						if (!DISNEY && !refracted && dot( gF, R ) <= 0) newPdf = 0; // the sampled direction must leave on the geometric side (:121); refraction returns before this test
 						if (newPdf >= 1e-4f) // also false for NaN (:222)
 						{
 							if (specular) flags |= S_SPECULAR;
@@ -677,6 +711,29 @@ __global__ void __launch_bounds__( 128, B200_SHADE_MIN_BLOCKS ) shadeKernel( con
 	}
 }
 
+// Diagnostic: the Disney BSDF on its own, for the parity test against the reference's disney.h (tests/test_disney_gpu.py).
+// in: 28 floats per item -- color, transmittance, three parameter words (bits), eta, iN, N, iT, wow, then (distance, r0, r1) for
+// mode 0 = SampleBSDF or wiw for mode 1 = EvaluateBSDF; out: 8 floats -- (wiw, pdf, value, specular) / (-, pdf, value, 0).
+__global__ void disneyProbeKernel( const int n, const int mode, const float* __restrict__ in, float* __restrict__ out )
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float* p = in + (size_t)i * 28;
+	disney::Data d;
+	d.color = v3( p[0], p[1], p[2] ), d.transmittance = v3( p[3], p[4], p[5] );
+	disney::Unpack( d, __float_as_uint( p[6] ), __float_as_uint( p[7] ), __float_as_uint( p[8] ) );
+	d.eta = p[9];
+	disney::Tint( d, d.color );
+	const V3 iN = v3( p[10], p[11], p[12] ), N = v3( p[13], p[14], p[15] ), iT = v3( p[16], p[17], p[18] ), wow = v3( p[19], p[20], p[21] );
+	V3 wiw = v3( p[22], p[23], p[24] ), value;
+	float pdf = 0;
+	bool specular = false;
+	if (mode == 0) value = disney::SampleBSDF( d, iN, N, iT, wow, p[22], p[23], p[24], wiw, pdf, specular );
+	else value = disney::EvaluateBSDF( d, iN, iT, wow, wiw, pdf );
+	float* o = out + (size_t)i * 8;
+	o[0] = wiw.x, o[1] = wiw.y, o[2] = wiw.z, o[3] = pdf, o[4] = value.x, o[5] = value.y, o[6] = value.z, o[7] = specular ? 1.f : 0.f;
+}
+
 // lib/CUDA/shared_kernel_code/finalize_shared.h:29-45: accumulator * 1/samples -> render target (here: a device buffer)
 __global__ void finalizeKernel( const float4* __restrict__ accumulator, float4* __restrict__ frame, const uint32_t pixels, const float scale )
 {
@@ -701,7 +758,7 @@ struct WavefrontState {
 	float sky[3] = { 0, 0, 0 }, clampValue = 10.0f; // clampValue: the RenderSystem's default (rendersystem.cpp:228-233 sends it every frame)
 	int lightCounts[4] = { 0, 0, 0, 0 };             // area, point, spot, directional; packed in this order in `lights`
 	uint32_t skyWidth = 0, skyHeight = 0;
-	int bounceCap = 0, roulette = 1;
+	int bounceCap = 0, roulette = 1, bsdf = 0; // bsdf: 0 = Lambert + speculars, 1 = Disney principled (rendercore_optix7/kernels/bsdf.h picks one at compile time)
 	uint32_t samplesTaken = 0, frameCounter = 0;
 	int probeX = -1, probeY = -1;
 	cudaEvent_t ev[2 + 6 * MAX_PATH_LENGTH] = {}; // frame begin/end, then per path length: extend begin/end, shade begin/end, connect begin/end
@@ -742,6 +799,7 @@ int RenderCore::SettingWavefront( const char* name, float value )
 	if (!strcmp( name, "clampValue" )) { if (!(value > 0)) return fail( "Setting clampValue: > 0" ); w->clampValue = value; return 0; }
 	if (!strcmp( name, "overlapConnect" )) { w->overlapConnect = value >= 0.5f; return 0; }
 	if (!strcmp( name, "russianRoulette" )) { w->roulette = value >= 0.5f; return 0; }
+	if (!strcmp( name, "bsdf" )) { if (v < 0 || v > 1) return fail( "Setting bsdf: 0 (Lambert, lib/sharedBSDFs/lambert.h) or 1 (Disney, disney.h)" ); w->bsdf = v; return 0; }
 	if (!strcmp( name, "diffuseBounceCap" )) { if (v < 0 || v > 2) return fail( "Setting diffuseBounceCap: 0 (off), 1 or 2" ); w->bounceCap = v; return 0; }
 	if (!strcmp( name, "pathsPerPass" )) { if (value < 1024) return fail( "Setting pathsPerPass: >= 1024" ); w->pathsPerPass = (uint32_t)value; return 0; }
 	return fail( std::string( "Setting: unknown key " ) + name );
@@ -864,6 +922,7 @@ int RenderCore::SetMaterials( const void* coreMaterials, int count )
 {
 	if (count < 0 || (count > 0 && !coreMaterials)) return fail( "SetMaterials: bad arguments" );
 	std::vector<float> table( (size_t)count * 16, 0.f );
+	std::vector<uint32_t> words( (size_t)count * 3, 0u );
 	for (int i = 0; i < count; i++)
 	{
 		const char* m = (const char*)coreMaterials + (size_t)i * 688;
@@ -876,8 +935,18 @@ int RenderCore::SetMaterials( const void* coreMaterials, int count )
 		t[6] = (float)(flags & 3u);
 		t[8] = 1 - absorption[0], t[9] = 1 - absorption[1], t[10] = 1 - absorption[2];
 		t[11] = (float)textureID;
+		// the Disney parameters as 0.8 fixed point, four to a word (TOUINT4, rendercore_optix7/rendercore.cpp:511-512, 532-534):
+		// ScalarValue::value of metallic @208, subsurface @240, specular @272, roughness @304 | specularTint @336, anisotropic @368,
+		// sheen @400, sheenTint @432 | clearcoat @464, clearcoatGloss @496, transmission @528
+		static const int offsets[11] = { 208, 240, 272, 304, 336, 368, 400, 432, 464, 496, 528 };
+		for (int k = 0; k < 11; k++)
+		{
+			float value;
+			memcpy( &value, m + offsets[k], 4 );
+			words[(size_t)i * 3 + k / 4] += (uint32_t)(value * 255.0f) << (8 * (k & 3));
+		}
 	}
-	return SetMaterialTable( table.data(), count );
+	return uploadMaterials( table.data(), words.data(), count );
 }
 
 // headless shortcut: (albedo rgb, roughness) per material, opaque, flat normals, no map
@@ -895,29 +964,59 @@ int RenderCore::SetMaterialColors( const float* rgba, int count )
 }
 
 // 16 floats per material: albedo rgb, roughness | transmission, eta, flags (1 SMOOTH + 2 HASALPHA), 0 | extinction rgb, diffuse
-// texture index (-1 = none) | uv scale xy, uv offset xy.  Texture indices refer to the last SetTextures.
+// texture index (-1 = none) | uv scale xy, uv offset xy.  Texture indices refer to the last SetTextures.  The Disney parameters
+// this table does not carry take the HostMaterial defaults (specular 0.5, the rest 0); roughness and transmission are quantised.
 int RenderCore::SetMaterialTable( const float* props16, int count )
 {
-	WavefrontState* w = state( wf );
 	if (count < 0 || (count > 0 && !props16)) return fail( "SetMaterialTable: bad arguments" );
-	std::vector<float> dev( (size_t)count * 20, 0.f );
+	std::vector<uint32_t> words( (size_t)count * 3, 0u );
 	for (int i = 0; i < count; i++)
 	{
 		const float* t = props16 + (size_t)i * 16;
-		float* d = &dev[(size_t)i * 20];
+		words[(size_t)i * 3] = ((uint32_t)(0.5f * 255.0f) << 16) + ((uint32_t)(fminf( fmaxf( t[3], 0.f ), 1.f ) * 255.0f) << 24);
+		words[(size_t)i * 3 + 2] = (uint32_t)(fminf( fmaxf( t[4], 0.f ), 1.f ) * 255.0f) << 16;
+	}
+	return uploadMaterials( props16, words.data(), count );
+}
+
+int RenderCore::uploadMaterials( const float* props16, const uint32_t* disneyWords, int count )
+{
+	WavefrontState* w = state( wf );
+	constexpr int REC = MAT_STRIDE * 4; // floats per device record
+	std::vector<float> dev( (size_t)count * REC, 0.f );
+	for (int i = 0; i < count; i++)
+	{
+		const float* t = props16 + (size_t)i * 16;
+		float* d = &dev[(size_t)i * REC];
 		memcpy( d, t, 64 );
 		uint32_t flags = (uint32_t)t[6] & 3u, offset = 0, dims[4] = { 0, 0, 0, 0 }, mips = 0;
 		const int tex = (int)t[11];
 		if (tex >= 0 && tex < (int)w->textures.size() && w->textures[tex].valid)
 			flags |= 4u, offset = w->textures[tex].offset, dims[0] = w->textures[tex].width, dims[1] = w->textures[tex].height, mips = w->textures[tex].mipLevels;
 		memcpy( d + 6, &flags, 4 ), memcpy( d + 7, &mips, 4 ), memcpy( d + 11, &offset, 4 ), memcpy( d + 16, dims, 16 );
+		memcpy( d + 20, disneyWords + (size_t)i * 3, 12 );
 	}
 	cudaError_t e;
-	if ((e = w->materials.reserve( (size_t)(count + 1) * 80, false, stream )) != cudaSuccess) return fail( "materials", e );
-	if (count && (e = cudaMemcpyAsync( w->materials.ptr, dev.data(), (size_t)count * 80, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "materials upload", e );
+	if ((e = w->materials.reserve( (size_t)(count + 1) * REC * 4, false, stream )) != cudaSuccess) return fail( "materials", e );
+	if (count && (e = cudaMemcpyAsync( w->materials.ptr, dev.data(), (size_t)count * REC * 4, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "materials upload", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "materials sync", e );
 	w->materialCount = (uint32_t)count;
 	return 0;
+}
+
+int RenderCore::DisneyProbe( int mode, int n, const float* in28, float* out8 )
+{
+	if (n < 0 || (mode != 0 && mode != 1) || (n > 0 && (!in28 || !out8))) return fail( "DisneyProbe: bad arguments" );
+	if (n == 0) return 0;
+	DeviceBuffer in, out;
+	cudaError_t e;
+	if ((e = in.reserve( (size_t)n * 112, false, stream )) != cudaSuccess || (e = out.reserve( (size_t)n * 32, false, stream )) != cudaSuccess) return fail( "DisneyProbe buffers", e );
+	e = cudaMemcpyAsync( in.ptr, in28, (size_t)n * 112, cudaMemcpyHostToDevice, stream );
+	if (e == cudaSuccess) disneyProbeKernel<<<(n + 127) / 128, 128, 0, stream>>>( n, mode, (const float*)in.ptr, (float*)out.ptr ), e = cudaGetLastError();
+	if (e == cudaSuccess) e = cudaMemcpyAsync( out8, out.ptr, (size_t)n * 32, cudaMemcpyDeviceToHost, stream );
+	if (e == cudaSuccess) e = cudaStreamSynchronize( stream );
+	in.release(), out.release();
+	return e == cudaSuccess ? 0 : fail( "DisneyProbe", e );
 }
 
 int RenderCore::SetProbe( int x, int y )
@@ -1007,7 +1106,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 			// shade k adds to the accumulator: it runs after connect k-1 so that every pixel sees its adds in one fixed order
 			if (overlap && len > 1) cudaStreamWaitEvent( stream, w->connectDone[len - 1], 0 );
 			cudaEventRecord( ev[2], stream );
-			shadeKernel<<<smCount * B200_SHADE_GRID, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
+			( w->bsdf ? shadeKernel<true> : shadeKernel<false> )<<<smCount * B200_SHADE_GRID, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
 				(const float4*)w->state[in].ptr, (const float4*)w->info[in].ptr, (const float4*)w->hits.ptr, (float4*)w->rayO[out].ptr, (float4*)w->rayD[out].ptr,
 				(float4*)w->state[out].ptr, (float4*)w->info[out].ptr, (float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)vnormPool.ptr, (const float4*)instShadePool.ptr,
 				(const float4*)w->materials.ptr, w->accumulator(), dCounters );

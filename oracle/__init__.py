@@ -170,3 +170,56 @@ class Oracle:
         out = np.empty(3, np.float32)
         self._fn("normalize")(np.asarray(v, np.float32), out)
         return out
+
+
+BSDF_REF_SO = os.path.join(HERE, "_ref", "liboracle_bsdf_ref.so")
+
+
+def have_bsdf_ref() -> bool:
+    return os.path.exists(BSDF_REF_SO)
+
+
+class DisneyRef:
+    """The reference's own Disney BSDF (lib/sharedBSDFs/disney.h + ggxmdf.h, unmodified, compiled for the host by
+    oracle/Makefile; see ref_bsdf_driver.cpp), over arrays.  Materials are given the way the reference's ShadingData holds
+    them: color[n,3], transmittance[n,3], tint4[n,4] (tint rgb, luminance), params uint32[n,4] (three words of 0.8
+    fixed-point parameters, eta as float bits)."""
+
+    def __init__(self):
+        if not os.path.exists(BSDF_REF_SO):
+            build()
+        if not os.path.exists(BSDF_REF_SO):
+            raise RuntimeError("oracle/_ref/liboracle_bsdf_ref.so is missing and /root/reference is not here to build it")
+        lib = C.CDLL(BSDF_REF_SO)
+        u = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+        lib.ref_disney_sample.argtypes = [C.c_int, _f, _f, _f, u, _f, _f, _f, _f, _f, _f, _f, _f, _f, _i, _f]
+        lib.ref_disney_evaluate.argtypes = [C.c_int, _f, _f, _f, u, _f, _f, _f, _f, _f, _f]
+        lib.ref_consistent_normal.argtypes = [C.c_int, _f, _f, _f, _f]
+        self.lib = lib
+
+    @staticmethod
+    def _c(a, dt=np.float32):
+        return np.ascontiguousarray(a, dt)
+
+    def sample(self, color, transmittance, tint4, params, iN, N, iT, wow, distance, r0, r1):
+        """SampleBSDF (disney.h:227-312) -> (wiw[n,3], pdf[n], specular[n] bool, value[n,3])"""
+        n = len(r0)
+        wiw, pdf, spec, value = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32), np.zeros((n, 3), np.float32)
+        c = self._c
+        self.lib.ref_disney_sample(n, c(color), c(transmittance), c(tint4), c(params, np.uint32), c(iN), c(N), c(iT), c(wow), c(distance), c(r0), c(r1),
+                                   wiw, pdf, spec, value)
+        return wiw, pdf, spec != 0, value
+
+    def evaluate(self, color, transmittance, tint4, params, iN, iT, wow, wiw):
+        """EvaluateBSDF (disney.h:314-348) -> (value[n,3], pdf[n])"""
+        n = len(wiw)
+        pdf, value = np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+        c = self._c
+        self.lib.ref_disney_evaluate(n, c(color), c(transmittance), c(tint4), c(params, np.uint32), c(iN), c(iT), c(wow), c(wiw), pdf, value)
+        return value, pdf
+
+    def consistent_normal(self, D, iN, alpha):
+        """ConsistentNormal (tools_shared.h:296-310)"""
+        out = np.zeros((len(alpha), 3), np.float32)
+        self.lib.ref_consistent_normal(len(alpha), self._c(D), self._c(iN), self._c(alpha), out)
+        return out

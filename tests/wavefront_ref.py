@@ -226,6 +226,20 @@ def fetch_texel_trilinear(texels, lam, tu, tv, offset, width, height, levels):
     return ((1 - fl)[:, None] * p0 + fl[:, None] * p1).astype(f32)
 
 
+def disney_tint(color):
+    """tint4 of GetShadingData (material_shared.h:19-35, 68-69): the base colour at unit luminance, and CIE Y."""
+    c = np.asarray(color, f32)
+    M = np.array([[0.412453, 0.357580, 0.180423], [0.212671, 0.715160, 0.072169], [0.019334, 0.119193, 0.950227]], f32)
+    Mi = np.array([[3.240479, -1.537150, -0.498535], [-0.969256, 1.875992, 0.041556], [0.055648, -0.204043, 1.057311]], f32)
+    xyz = np.stack([np.maximum(f32(0), ((M[k, 0] * c[:, 0] + M[k, 1] * c[:, 1]).astype(f32) + M[k, 2] * c[:, 2]).astype(f32)) for k in range(3)], axis=1)
+    Y = xyz[:, 1]
+    with np.errstate(all="ignore"):
+        s = (xyz * (f32(1) / Y)[:, None]).astype(f32)
+    rgb = np.stack([np.maximum(f32(0), ((Mi[k, 0] * s[:, 0] + Mi[k, 1] * s[:, 1]).astype(f32) + Mi[k, 2] * s[:, 2]).astype(f32)) for k in range(3)], axis=1)
+    rgb = np.where((Y > 0)[:, None], rgb, f32(1)).astype(f32)
+    return np.concatenate([rgb, Y[:, None]], axis=1).astype(f32)
+
+
 def clamp_and_fix(c, clamp):
     m = np.max(c, axis=1)
     with np.errstate(all="ignore"):
