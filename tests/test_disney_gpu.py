@@ -95,3 +95,90 @@ def test_sample_matches_reference(rc, ref):
     print("sample: live", int(live.sum()), "mismatching", int((~ok).sum()), "specular", int(spec.sum()), "tir", int(tir.sum()))
     assert live.mean() > 0.5 and spec.sum() > 1000
     assert (~ok).mean() < 2e-3, (out[live][~ok][:5], wiw[live][~ok][:5], pdf[live][~ok][:5], value[live][~ok][:5])
+
+
+# ---- whole frames: Setting bsdf = 1 against the numpy restatement of the wavefront loop that calls the reference's BSDF ------------
+def _disney_scene():
+    """The lit scene of test_wavefront_gpu (textured alpha floor, spheres, emitter, four light kinds, skydome) with Disney
+    materials: plastic, metal, anisotropic, cloth, car paint, glass, a bit of everything, and the emitter."""
+    from test_wavefront_gpu import _lit_scene
+    sc = _lit_scene()
+    grid, sph, quad = sc["case"]["meshes"]
+    sc["dicts"] = [
+        dict(color=(0.8, 0.8, 0.8), roughness=0.8),                                                        # 0 plastic
+        dict(color=(0.9, 0.2, 0.15), roughness=0.3, metallic=1.0),                                         # 1 red metal
+        dict(color=(0.95, 0.95, 0.95), roughness=0.0),                                                     # 2 roughness 0: pure specular vertex
+        dict(color=(12.0, 11.0, 10.0)),                                                                    # 3 emitter
+        dict(color=(0.95, 0.97, 1.0), roughness=0.1, transmission=1.0, eta=1.0 / 1.5, flags=1, absorption=(0.25, 0.75, 0.875)),  # 4 glass
+        dict(color=(0.3, 0.5, 0.8), roughness=0.5, sheen=1.0, sheenTint=0.5, subsurface=0.5, clearcoat=1.0, clearcoatGloss=0.7, flags=1,
+             anisotropic=0.6, specularTint=0.4),                                                           # 5 everything, smooth normals
+        dict(color=(1.0, 0.9, 0.8), roughness=0.6, flags=2, texture=0, uvscale=(1.5, 2.0), uvoffset=(0.25, 0.125), specular=1.0),  # 6 mapped floor, HASALPHA
+    ]
+    # the 16-float table the numpy restatement reads (colour, flags, texture, eta, extinction = 1 - absorption)
+    t = np.zeros((len(sc["dicts"]), 16), np.float32)
+    for k, m in enumerate(sc["dicts"]):
+        t[k, 0:3], t[k, 3], t[k, 4], t[k, 5], t[k, 6] = m["color"], m.get("roughness", 0.5), m.get("transmission", 0.0), m.get("eta", 1.0), m.get("flags", 0)
+        t[k, 8:11] = 1 - np.asarray(m.get("absorption", (0, 0, 0)), np.float32)
+        t[k, 11], t[k, 12:14], t[k, 14:16] = m.get("texture", -1), m.get("uvscale", (1, 1)), m.get("uvoffset", (0, 0))
+    sc["materials"] = t
+    sc["words"] = core.disney_words(sc["dicts"])
+    rng = np.random.default_rng(9)
+    unit = lambda v: (v / np.linalg.norm(v, axis=-1, keepdims=True)).astype(np.float32)
+    # tangents along the first edge; vertex alphas as the host mesh computes them: the largest angle between a vertex normal and
+    # the normals of the triangles around it -- here simply a small random angle on the spheres, 0 on the flat meshes
+    sc["tangents"] = [unit(m[:, 1] - m[:, 0]) for m in (grid, sph, quad)]
+    sc["alphas"] = [np.zeros((len(grid), 3), np.float32), (rng.random((len(sph), 3)) * 0.3).astype(np.float32), np.zeros((len(quad), 3), np.float32)]
+    return sc
+
+
+def _disney_core(sc, w, h, spp, **settings):
+    case = sc["case"]
+    c = core.RenderCoreB200(0)
+    for i, m in enumerate(case["meshes"]):
+        c.SetGeometry(i, m, core.core_tris(m, sc["prim_materials"][i], sc["vertex_normals"][i], sc["uvs"][i], sc["lods"][i], sc["tangents"][i], sc["alphas"][i]))
+    for i, (mesh, mat) in enumerate(case["instances"]):
+        c.SetInstance(i, mesh, mat)
+    c.SetInstance(len(case["instances"]), -1)
+    c.UpdateToplevel()
+    c.SetTarget(w, h, spp)
+    c.SetTextures(sc["textures"])
+    c.SetMaterials(sc["dicts"])
+    c.SetLights(sc["area"], sc["point"], sc["spot"], sc["dir"])
+    c.SetSkyData(sc["sky"])
+    c.Setting("maxPathLength", 5)
+    c.Setting("jitter", 0)
+    c.Setting("bsdf", 1)
+    for k, v in settings.items():
+        c.Setting(k, v)
+    return c
+
+
+@pytest.mark.parametrize("roulette", [1, 0])
+def test_disney_frame_matches_reference_bsdf_restatement(ref, roulette):
+    import cases
+    from lighthouse2_b200 import scenes
+    sc = _disney_scene()
+    w, h, spp = 160, 90, 2
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    c = _disney_core(sc, w, h, spp, russianRoulette=roulette)
+    c.Render(view, converge=1)
+    acc, st = c.ReadAccumulator(), c.GetCoreStats()
+    c.Shutdown()
+    port = cases.load_oracle(dict(sc["case"], rays=None), "port")
+    stats = {}
+    img = wr.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
+                    lights=wr.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
+                    materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
+                    uvs=sc["uvs"], lods=sc["lods"], textures=sc["textures"], max_path_length=5, spp=spp, roulette=bool(roulette), stats=stats,
+                    disney=ref, material_words=sc["words"], tangents=sc["tangents"], alphas=sc["alphas"])
+    mean = float(img[..., :3].mean())
+    rmse = float(np.sqrt(np.mean((acc[..., :3] - img[..., :3]) ** 2)))
+    big = np.abs(acc[..., :3] - img[..., :3]).max(axis=2) > 0.02 * mean
+    print("disney image: mean", mean, "rmse", rmse, "pixels off by >2%:", int(big.sum()), "of", w * h,
+          "rays gpu", st["totalExtensionRays"], st["totalShadowRays"], "ref", sum(stats["ext"]), sum(stats["shadow"]))
+    assert np.isfinite(acc).all() and mean > 0.05
+    assert rmse <= 1e-2 * mean, (rmse, mean)
+    assert big.mean() < 2e-2
+    assert np.allclose(acc[..., 3], img[..., 3], rtol=1e-5)
+    assert abs(st["totalExtensionRays"] - sum(stats["ext"])) <= 0.005 * sum(stats["ext"])
+    assert abs(st["totalShadowRays"] - sum(stats["shadow"])) <= 0.005 * sum(stats["shadow"])

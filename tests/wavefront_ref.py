@@ -252,13 +252,17 @@ def clamp_and_fix(c, clamp):
 
 def render(oracle, meshes, instances, view, width, height, light=None, lights=None, sky=(0, 0, 0), sky_image=None,
            materials=None, prim_materials=None, vertex_normals=None, uvs=None, lods=None, textures=None, spread_angle=0.01,
-           max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True, nthreads=8, stats=None):
+           max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True, nthreads=8, stats=None,
+           disney=None, material_words=None, tangents=None, alphas=None):
     """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
     meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
     point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or the float32[n, 16] table of
     b200_set_material_table; prim_materials = per mesh uint32[T] material index (default 0); vertex_normals = per mesh
     float32[T, 3, 3] or None; uvs = per mesh float32[T, 3, 2] or None, lods = per mesh float32[T] or None; textures = list of
-    (width, height, texels uint32[], mip_levels); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off)."""
+    (width, height, texels uint32[], mip_levels); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off).
+    disney = oracle.DisneyRef() switches the BSDF to the reference's Disney one (Setting bsdf = 1): material_words =
+    uint32[n, 4] (core.disney_words), tangents = per mesh float32[T, 3] (CoreTri::T), alphas = per mesh float32[T, 3]
+    (CoreTri::alpha; consistent normal interpolation, material_shared.h:87-97)."""
     npx = width * height
     acc = np.zeros((npx, 4), np.float64)
     pos, p1 = view["pos"].astype(f32), view["p1"].astype(f32)
@@ -378,6 +382,14 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                 tex_id[known] = mk[:, 11].astype(np.int64)
                 uvso = np.zeros((n, 4), f32)
                 uvso[known] = mk[:, 12:16]
+            words = np.tile(np.array([0x80800000, 0, 0, f32(1).view(np.uint32)], np.uint32), (n, 1))
+            base_color = color.copy()
+            if disney is not None and materials is not None:
+                words[known] = np.asarray(material_words, np.uint32)[mat[known]]
+                byte = lambda w, sh: (((w >> np.uint32(sh)) & np.uint32(255)).astype(f32) * f32(1.0 / 255.0)).astype(f32)
+                rough = np.maximum(f32(0.001), byte(words[:, 0], 24))
+                transmission = byte(words[:, 2], 16)
+            tang = np.zeros((n, 3), f32)
             # interpolated normals for SMOOTH materials: w N0 + u N1 + v N2 with the 16-bit barycentrics of the hit record
             sN[:] = N
             I_all = (O + D * t[:, None]).astype(f32)
@@ -385,11 +397,11 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             mapped = np.zeros(n, bool)
             if materials is not None and textures:
                 mapped = (tex_id >= 0) & (tex_id < len(tex_rec))
-            if vertex_normals is not None or mapped.any():
+            if vertex_normals is not None or mapped.any() or disney is not None:
                 for i in np.unique(inst):
                     mesh = inst_mesh[i]
                     has_vn = vertex_normals is not None and vertex_normals[mesh] is not None
-                    sel = np.nonzero((inst == i) & ((smooth & has_vn) | mapped))[0]
+                    sel = np.nonzero((inst == i) & ((smooth & has_vn) | mapped | (disney is not None)))[0]
                     if len(sel) == 0:
                         continue
                     tri = meshes[mesh][prim[sel]]
@@ -411,6 +423,15 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                         on = (vn[:, 0] * bw[:, None] + vn[:, 1] * bu[:, None] + vn[:, 2] * bv[:, None]).astype(f32)
                         ok = sm & (dot(on, on) > 0)
                         sN[sel[ok]] = normalize(to_world(mats[i], on[ok]))
+                    if disney is not None:
+                        if alphas is not None:  # consistent normal interpolation (material_shared.h:87-97)
+                            al = alphas[mesh][prim[sel]].astype(f32) if alphas[mesh] is not None else np.zeros((len(sel), 3), f32)
+                            alpha = ((bw * al[:, 0] + bu * al[:, 1]).astype(f32) + bv * al[:, 2]).astype(f32)
+                            back = dot(D[sel], N[sel]) > 0
+                            sg = np.where(back, f32(-1), f32(1))[:, None]
+                            sN[sel] = (disney.consistent_normal((D[sel] * f32(-1)).astype(f32), (sN[sel] * sg).astype(f32), alpha) * sg).astype(f32)
+                        if tangents is not None and tangents[mesh] is not None:
+                            tang[sel] = tangents[mesh][prim[sel]]
                     mp = mapped[sel]
                     if mp.any():
                         # diffuse map (material_shared.h:99-131): trilinear fetch at the ray-cone LOD, alpha below 0.5 = pass through
@@ -427,6 +448,9 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                         hole = ((mflags[q] & 2) != 0) & (texel[:, 3] < f32(0.5))
                         passthrough[q[hole]] = True
                         color[q[~hole]] = (color[q[~hole]] * texel[~hole, :3]).astype(f32)
+            if disney is not None:  # a triangle without a tangent gets an arbitrary one (the reference would divide by zero)
+                notan = ~(dot(tang, tang) > 0)
+                tang[notan] = np.where((np.abs(sN[notan, 0]) > f32(0.9))[:, None], np.array([0, 1, 0], f32), np.array([1, 0, 0], f32))
             I = I_all
             # alpha holes (pathtracer.h:104-116): the path continues from just behind the surface with its state unchanged
             carry = None
@@ -438,6 +462,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             if passthrough.any():
                 kp = ~passthrough
                 O, D, T, t, prim, inst, path_idx, px, N, sN, I, color, rough = (a[kp] for a in (O, D, T, t, prim, inst, path_idx, px, N, sN, I, color, rough))
+                words, base_color, tang = words[kp], base_color[kp], tang[kp]
                 pdf_prev, flags, lastN, transmission, eta, absorption = (a[kp] for a in (pdf_prev, flags, lastN, transmission, eta, absorption))
                 n = len(O)
             # ---- paths that end on a light (pathtracer.h:120-148)
@@ -475,6 +500,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                 continue
             O, D, T, t, N, I, color, rough, path_idx, px = (a[keep] for a in (O, D, T, t, N, I, color, rough, path_idx, px))
             sN, transmission, eta, absorption = sN[keep], transmission[keep], eta[keep], absorption[keep]
+            words, base_color, tang = words[keep], base_color[keep], tang[keep]
             pdf_prev, flags, lastN = pdf_prev[keep], flags[keep], lastN[keep]
             n = len(O)
             flags = np.where((rough <= f32(0.001)) | (transmission > f32(0.999)), flags | S_SPECULAR, flags & ~np.uint32(S_SPECULAR)).astype(np.uint32)
@@ -498,10 +524,16 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                 with np.errstate(all="ignore"):
                     L = (L * (f32(1) / dist)[:, None]).astype(f32)
                     ndl = dot(L, fN[q])
-                    bpdf = (np.abs(ndl) * INVPI).astype(f32)
-                    ok = (ndl > 0) & (lpdf > 0) & (bpdf > 0)
-                    sc = (INVPI * rough[q] * (ndl / (pick * lpdf + bpdf))).astype(f32)
-                    E = clamp_and_fix((T[q] * color[q] * lcol * sc[:, None]).astype(f32), clamp)
+                    if disney is None:
+                        bpdf = (np.abs(ndl) * INVPI).astype(f32)
+                        ok = (ndl > 0) & (lpdf > 0) & (bpdf > 0)
+                        sc = (INVPI * rough[q] * (ndl / (pick * lpdf + bpdf))).astype(f32)
+                        E = clamp_and_fix((T[q] * color[q] * lcol * sc[:, None]).astype(f32), clamp)
+                    else:
+                        # EvaluateBSDF with the unflipped shading normal (pathtracer.h:186)
+                        val, bpdf = disney.evaluate(color[q], absorption[q], disney_tint(base_color[q]), words[q], sN[q], tang[q], (D[q] * f32(-1)).astype(f32), L)
+                        ok = (ndl > 0) & (lpdf > 0) & (bpdf > 0)
+                        E = clamp_and_fix((T[q] * val * lcol * (ndl / (pick * lpdf + bpdf))[:, None]).astype(f32), clamp)
                 if ok.any():
                     So = safe_origin(I[q][ok], L[ok], gF[q][ok], EPS)
                     tmax = dist[ok] - 2 * EPS
@@ -554,6 +586,12 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             new_pdf = np.where(dead_tir, f32(0), new_pdf)
             new_pdf = np.where(~refract_t & (dot(gF, R) <= 0), f32(0), new_pdf)
             spec = ~diffuse
+            if disney is not None:
+                # SampleBSDF( shadingData, fN, N, T, -D, HIT_T, r3, r4, ... ) (pathtracer.h:219); total internal reflection ends the path
+                R, new_pdf, spec, bsdf = disney.sample(color, absorption, disney_tint(base_color), words, sN, N, tang, (D * f32(-1)).astype(f32), t, r3, r4)
+                new_pdf = np.where(spec & (np.abs(R).sum(axis=1) == 0), f32(0), new_pdf).astype(f32)
+                with np.errstate(all="ignore"):
+                    cosr = dot(fN, R)
             alive = ~enough & (new_pdf >= f32(1e-4))
             flags = np.where(alive & spec, flags | S_SPECULAR, flags).astype(np.uint32)
             p = np.where(((flags & S_SPECULAR) != 0) | ((flags & S_BOUNCED) == 0) | (not roulette), f32(1), np.minimum(f32(1), bsdf.max(axis=1))).astype(f32)
