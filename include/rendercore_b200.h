@@ -98,6 +98,11 @@ B200_API int b200_set_material_colors( b200_core* c, const float* rgba, int coun
 B200_API int b200_set_material_table( b200_core* c, const float* props16, int count );
 /* CoreAPI_Base::SetTextures (core_api_base.h:98): CoreTexDesc[count] in the host layout (40 bytes, common_classes.h:246-269); call before
  * the materials.  ARGB32 maps are copied (MIP levels included) and sampled as the diffuse map of the materials that name them */
+/* Blue-noise sampling (BLUENOISE, rendercore_optix7/core_settings.h:29): the table the reference's cores build in Init
+ * (rendercore_optix7/rendercore.cpp:258-267; 5 * 65536 words: Sobol sequence, scrambling tile at 65536, ranking tile at 3 * 65536).
+ * With a table set, the first 256 samples of a pixel draw the pixel / lens position and the BSDF sample from it and the first two
+ * the light sample (.optix.cu:66-79, pathtracer.h:168-222), as the reference does; words = NULL returns to xor32 numbers. */
+B200_API int b200_set_blue_noise( b200_core* c, const uint32_t* words, int count );
 /* Diagnostic: evaluate the Disney BSDF of the shade stage (Setting "bsdf" = 1) on its own, on the device.  in28: 28 floats per
  * item (color, transmittance, three 0.8 fixed-point parameter words as bits, eta, iN, N, iT, wow, then distance r0 r1 for mode 0 =
  * SampleBSDF or wiw for mode 1 = EvaluateBSDF; lib/sharedBSDFs/disney.h:227,314); out8: wiw, pdf, value, specular. */

@@ -25,7 +25,7 @@ C_ABI_SYMBOLS = [
     "b200_set_point_light", "b200_set_sky", "b200_set_lights", "b200_set_sky_data", "b200_render", "b200_read_accumulator", "b200_read_frame",
     "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
     "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors", "b200_set_material_table", "b200_set_textures",
-    "b200_disney_probe",
+    "b200_disney_probe", "b200_set_blue_noise",
     "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
 ]
 
@@ -89,7 +89,7 @@ def load_library() -> C.CDLL:
         "b200_device_accumulator": ([vp], vp), "b200_get_stats": ([vp, C.POINTER(Stats)], ip), "b200_set_probe": ([vp, ip, ip], ip),
         "b200_plugin_core": ([], vp), "b200_host_alloc": ([C.c_uint64], vp), "b200_host_free": ([vp], None),
         "b200_set_materials": ([vp, vp, ip], ip), "b200_set_material_colors": ([vp, vp, ip], ip), "b200_set_material_table": ([vp, vp, ip], ip), "b200_set_textures": ([vp, vp, ip], ip),
-        "b200_disney_probe": ([vp, ip, ip, vp, vp], ip),
+        "b200_disney_probe": ([vp, ip, ip, vp, vp], ip), "b200_set_blue_noise": ([vp, vp, ip], ip),
         "b200_set_accumulator_buffer": ([vp, vp], ip), "b200_finalize": ([vp, C.c_uint32], ip),
         "b200_trace_connect_device": ([vp, vp, vp, ip, vp, vp], ip),
     }
@@ -341,6 +341,14 @@ class RenderCoreB200:
         c = materials if isinstance(materials, np.ndarray) else core_materials(materials)
         c = np.ascontiguousarray(c, np.uint8).reshape(-1, 688)
         self._chk(self.lib.b200_set_materials(self.h, c.ctypes.data, c.shape[0]))
+
+    def SetBlueNoise(self, words):
+        """b200_set_blue_noise: uint32[5 * 65536] in the reference's layout, or None for xor32 numbers."""
+        if words is None:
+            self._chk(self.lib.b200_set_blue_noise(self.h, None, 0))
+            return
+        t = np.ascontiguousarray(words, np.uint32).reshape(-1)
+        self._chk(self.lib.b200_set_blue_noise(self.h, t.ctypes.data, t.shape[0]))
 
     def DisneyProbe(self, mode: int, items: np.ndarray) -> np.ndarray:
         """b200_disney_probe: float32[n, 28] -> float32[n, 8] (see include/rendercore_b200.h)."""

@@ -60,6 +60,7 @@ int b200_set_materials( b200_core* c, const void* coreMaterials, int count ) { F
 int b200_set_material_colors( b200_core* c, const float* rgba, int count ) { FORWARD( c, SetMaterialColors( rgba, count ) ) }
 int b200_set_material_table( b200_core* c, const float* props16, int count ) { FORWARD( c, SetMaterialTable( props16, count ) ) }
 int b200_set_textures( b200_core* c, const void* coreTexDescs, int count ) { FORWARD( c, SetTextures( coreTexDescs, count ) ) }
+int b200_set_blue_noise( b200_core* c, const uint32_t* words, int count ) { FORWARD( c, SetBlueNoise( words, count ) ) }
 int b200_disney_probe( b200_core* c, int mode, int n, const float* in28, float* out8 ) { FORWARD( c, DisneyProbe( mode, n, in28, out8 ) ) }
 int b200_set_accumulator_buffer( b200_core* c, void* dAcc ) { FORWARD( c, SetAccumulatorBuffer( dAcc ) ) }
 int b200_finalize( b200_core* c, uint32_t totalSamples ) { FORWARD( c, Finalize( totalSamples ) ) }

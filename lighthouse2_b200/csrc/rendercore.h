@@ -47,6 +47,7 @@ public:
 	int SetSkyData( const float* rgb, int width, int height ); // equirectangular float3 image
 	int SetMaterials( const void* coreMaterials, int count ); // CoreMaterial[count], 688 B each; keeps color.value and roughness.value
 	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: (albedo rgb, roughness) per material; rgb > 1 = emissive
+	int SetBlueNoise( const uint32_t* words, int count );     // the reference's 5 x 65536-word blue-noise table, or null
 	int DisneyProbe( int mode, int n, const float* in28, float* out8 ); // diagnostic: the Disney BSDF alone (wavefront.cu::disneyProbeKernel)
 	int uploadMaterials( const float* props16, const uint32_t* disneyWords, int count );
 	int SetMaterialTable( const float* props16, int count );  // 16 floats per material, see wavefront.cu

@@ -64,6 +64,7 @@ struct FrameParams {
 	uint32_t skyWidth, skyHeight;
 	const uint32_t* texels;    // ARGB32 texels of all textures, MIP levels behind each other (SetTextures)
 	float spreadAngle;         // ViewPyramid::spreadAngle: ray cone width per unit distance, for the texture LOD
+	const uint32_t* blueNoise; // 5 x 65536 words in the reference's layout (SetBlueNoise); null = xor32 numbers only
 };
 
 constexpr uint32_t S_SPECULAR = 1, S_BOUNCED = 2, S_VIASPECULAR = 4, S_BOUNCEDTWICE = 8; // pathtracer.h:29-32
@@ -73,6 +74,17 @@ constexpr uint32_t PATHIDX_BITS = 28, PATHIDX_MASK = (1u << PATHIDX_BITS) - 1;  
 __device__ __forceinline__ uint32_t WangHash( uint32_t s ) { s = (s ^ 61) ^ (s >> 16), s *= 9, s = s ^ (s >> 4), s *= 0x27d4eb2d, s = s ^ (s >> 15); return s; }
 __device__ __forceinline__ uint32_t RandomInt( uint32_t& s ) { s ^= s << 13, s ^= s >> 17, s ^= s << 5; return s; }
 __device__ __forceinline__ float RandomFloat( uint32_t& s ) { return RandomInt( s ) * 2.3283064365387e-10f; }
+
+// tools_shared.h:332-347 (after E. Heitz et al., "A Low-Discrepancy Sampler that Distributes Monte Carlo Errors as a Blue Noise in
+// Screen Space"): table = 256 x 256 Sobol bytes, then scrambling and ranking tiles of 128 x 128 x 8, one word per entry
+__device__ __forceinline__ float BlueNoiseSampler( const uint32_t* __restrict__ table, int x, int y, int sampleIndex, int sampleDimension )
+{
+	x &= 127, y &= 127, sampleIndex &= 255, sampleDimension &= 255;
+	const int ranked = (sampleIndex ^ (int)__ldg( table + sampleDimension + (x + y * 128) * 8 + 65536 * 3 )) & 255;
+	int value = (int)__ldg( table + sampleDimension + ranked * 256 );
+	value ^= (int)__ldg( table + (sampleDimension & 7) + (x + y * 128) * 8 + 65536 );
+	return (0.5f + (float)value) * (1.0f / 256.0f);
+}
 
 __device__ __forceinline__ uint32_t laneMaskLt()
 {
@@ -152,13 +164,20 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 		const uint32_t pixelIdx = x + y * f.width, pathIdx = pixelIdx + (f.sampleBase + sample) * f.pixelCount;
 		float r0 = 0.5f, r1 = 0.5f;
 		uint32_t seed = WangHash( pathIdx + f.R0 );
-		if (f.jitter) r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
+		// the first 256 samples of a pixel take their four numbers from the blue-noise table (.optix.cu:66-79)
+		const int sampleIdx = (int)(f.sampleBase + sample);
+		const bool blue = f.blueNoise && sampleIdx < 256;
+		if (f.jitter)
+		{
+			if (blue) r0 = BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 0 ), r1 = BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 1 );
+			else r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
+		}
 		// thin lens: a point on a 9-blade aperture of radius `aperture` in the screen-parallel plane through pos (RandomPointOnLens, .optix.cu:51-64)
 		float ox = f.pos[0], oy = f.pos[1], oz = f.pos[2];
 		if (f.aperture > 0)
 		{
-			const float l0 = RandomFloat( seed );
-			float l1 = RandomFloat( seed );
+			const float l0 = blue ? BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 2 ) : RandomFloat( seed );
+			float l1 = blue ? BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 3 ) : RandomFloat( seed );
 			const float blade = (float)(int)(l0 * 9);
 			float l2 = (l0 - blade * (1.0f / 9.0f)) * 9.0f;
 			float x1, y1, x2, y2;
@@ -586,7 +605,11 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					// next event estimation (:163-199)
 					if (!(flags & S_SPECULAR) && f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0)
 					{
-						const float r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
+						// (the reference draws these two from the blue-noise table for the first TWO samples only, pathtracer.h:168)
+						const int sampleIdx = (int)(pathIdx / f.pixelCount), bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
+						const bool blue = f.blueNoise && sampleIdx < 2;
+						const float r0 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 4 + 4 * pathLength ) : RandomFloat( seed );
+						const float r1 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 5 + 4 * pathLength ) : RandomFloat( seed );
 						float pickProb, lightPdf;
 						V3 lightColor;
 						V3 L = RandomPointOnLight( f, r0, r1, I, sF, pickProb, lightPdf, lightColor ) - I;
@@ -613,7 +636,10 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					const bool enough = (f.bounceCap == 1 && (flags & S_BOUNCED)) || (f.bounceCap == 2 && (flags & S_BOUNCEDTWICE));
 					if (!enough && pathLength < maxPathLength)
 					{
-						const float r3 = RandomFloat( seed ), r4 = RandomFloat( seed );
+						const int sampleIdx = (int)(pathIdx / f.pixelCount), bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
+						const bool blue = f.blueNoise && sampleIdx < 256; // pathtracer.h:212-222
+						const float r3 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 6 + 4 * pathLength ) : RandomFloat( seed );
+						const float r4 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 7 + 4 * pathLength ) : RandomFloat( seed );
 						// SampleBSDF (lambert.h:71-123)
 						V3 R = sF, bsdf = v3( 0.f, 0.f, 0.f );
 						float newPdf = 1;
@@ -750,7 +776,8 @@ struct WavefrontState {
 	int shardIndex = 0, shardCount = 1, sampleOffset = 0, jitter = 1;
 	uint32_t pathsPerPass = 32u << 20;
 	uint32_t capacity = 0; // rays per buffer
-	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO, conD, conE, counters, accumOwn, frame, materials, lights, skyImage, texels;
+	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO, conD, conE, counters, accumOwn, frame, materials, lights, skyImage, texels, blueNoise;
+	bool haveBlueNoise = false;
 	struct TextureRec { uint32_t offset, width, height, mipLevels; bool valid; };
 	std::vector<TextureRec> textures;
 	float4* accumExternal = nullptr;
@@ -770,7 +797,7 @@ struct WavefrontState {
 	~WavefrontState()
 	{
 		DeviceBuffer* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &state[0], &state[1], &info[0], &info[1], &hits, &conO, &conD, &conE, &counters,
-			&accumOwn, &frame, &materials, &lights, &skyImage, &texels };
+			&accumOwn, &frame, &materials, &lights, &skyImage, &texels, &blueNoise };
 		for (DeviceBuffer* b : all) b->release();
 		for (cudaEvent_t e : ev) if (e) cudaEventDestroy( e );
 		for (cudaEvent_t e : shadeDone) if (e) cudaEventDestroy( e );
@@ -1004,6 +1031,22 @@ int RenderCore::uploadMaterials( const float* props16, const uint32_t* disneyWor
 	return 0;
 }
 
+// The blue-noise table of the reference's cores (rendercore_optix7/rendercore.cpp:258-267: 65536 Sobol entries, then the scrambling
+// and ranking tiles at word offsets 65536 and 3 * 65536; 5 * 65536 words).  The reference compiles the data in (core_settings.h:207);
+// this core takes it from the host.  words = null switches back to xor32 numbers.
+int RenderCore::SetBlueNoise( const uint32_t* words, int count )
+{
+	WavefrontState* w = state( wf );
+	if (!words) { w->haveBlueNoise = false; return 0; }
+	if (count != 5 * 65536) return fail( "SetBlueNoise: the table has 5 * 65536 words" );
+	cudaError_t e;
+	if ((e = w->blueNoise.reserve( (size_t)count * 4, false, stream )) != cudaSuccess) return fail( "blue noise table", e );
+	if ((e = cudaMemcpyAsync( w->blueNoise.ptr, words, (size_t)count * 4, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "blue noise upload", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "blue noise sync", e );
+	w->haveBlueNoise = true;
+	return 0;
+}
+
 int RenderCore::DisneyProbe( int mode, int n, const float* in28, float* out8 )
 {
 	if (n < 0 || (mode != 0 && mode != 1) || (n > 0 && (!in28 || !out8))) return fail( "DisneyProbe: bad arguments" );
@@ -1088,6 +1131,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		if ((uint64_t)f.pixelCount * (uint64_t)w->spp > PATHIDX_MASK) return fail( "Render: width * height * spp exceeds 2^28 path indices" );
 		const uint32_t period = PATHIDX_MASK / f.pixelCount - (uint32_t)w->spp + 1;
 		f.sampleBase = globalSample % period;
+		f.blueNoise = (w->haveBlueNoise && globalSample < period) ? (const uint32_t*)w->blueNoise.ptr : nullptr; // not after the sample index wrapped
 		f.R0 = (globalSample / period + 1) * 7907u;
 		if ((e = cudaMemsetAsync( dCounters, 0, sizeof( uint32_t ) * COUNTER_WORDS, stream )) != cudaSuccess) return fail( "counter clear", e );
 		const uint32_t paths = perSample * f.samplesThisPass;

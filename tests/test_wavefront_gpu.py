@@ -267,6 +267,39 @@ def test_lit_frame_matches_cpu_restatement(cap, roulette):
     rc.Shutdown()
 
 
+def test_blue_noise_sampling_matches_cpu_restatement():
+    """BLUENOISE of the reference's cores (pathtracer.h:168-222, .optix.cu:66-79): with a table set, the first 256 samples
+    draw the lens point and the BSDF sample from it and the first two the light sample.  The table here is synthetic (the
+    reference compiles Heitz' tables in; this core takes them from the host): the check is the indexing, sample 0..2 so
+    that both the `< 2` and the `< 256` rule are crossed."""
+    sc = _lit_scene()
+    w, h, spp = 160, 90, 3
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    view["aperture"] = 0.02
+    table = np.random.default_rng(77).integers(0, 256, 5 * 65536).astype(np.uint32)
+    rc = _lit_core(sc, w, h, spp=spp)
+    rc.SetBlueNoise(table)
+    rc.Render(view, converge=1)
+    acc, st = rc.ReadAccumulator(), rc.GetCoreStats()
+    rc.SetBlueNoise(None)
+    rc.Render(view, converge=1)
+    plain = rc.ReadAccumulator()
+    rc.Shutdown()
+    port = cases.load_oracle(dict(sc["case"], rays=None), "port")
+    stats = {}
+    ref = wavefront_ref.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
+                               lights=wavefront_ref.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
+                               materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
+                               uvs=sc["uvs"], lods=sc["lods"], textures=sc["textures"], max_path_length=5, spp=spp, stats=stats, blue_noise=table)
+    mean = float(ref[..., :3].mean())
+    rmse = float(np.sqrt(np.mean((acc[..., :3] - ref[..., :3]) ** 2)))
+    big = np.abs(acc[..., :3] - ref[..., :3]).max(axis=2) > 0.02 * mean
+    print("blue noise image: mean", mean, "rmse", rmse, "pixels off by >2%:", int(big.sum()), "rays", st["totalExtensionRays"], sum(stats["ext"]))
+    assert rmse <= 1e-2 * mean and big.mean() < 2e-2
+    assert abs(st["totalExtensionRays"] - sum(stats["ext"])) <= 0.005 * sum(stats["ext"])
+    assert np.abs(plain[..., :3] - acc[..., :3]).mean() > 0.01 * mean  # the table is really used
+
+
 def test_emitter_seen_directly_and_one_sided():
     """A camera ray that hits the emitter's front adds its radiance (clamped by clampValue); its back is black."""
     sc = _lit_scene()

@@ -226,6 +226,16 @@ def fetch_texel_trilinear(texels, lam, tu, tv, offset, width, height, levels):
     return ((1 - fl)[:, None] * p0 + fl[:, None] * p1).astype(f32)
 
 
+def blue_noise_sampler(table, x, y, sample_index, dim):
+    """blueNoiseSampler (tools_shared.h:332-347) over arrays of pixel coordinates; table = uint32[5 * 65536]."""
+    x, y = np.asarray(x, np.int64) & 127, np.asarray(y, np.int64) & 127
+    si, dim = int(sample_index) & 255, int(dim) & 255
+    ranked = (si ^ table[dim + (x + y * 128) * 8 + 65536 * 3].astype(np.int64)) & 255
+    value = table[dim + ranked * 256].astype(np.int64)
+    value = value ^ table[(dim & 7) + (x + y * 128) * 8 + 65536].astype(np.int64)
+    return ((f32(0.5) + value.astype(f32)) * f32(1.0 / 256.0)).astype(f32)
+
+
 def disney_tint(color):
     """tint4 of GetShadingData (material_shared.h:19-35, 68-69): the base colour at unit luminance, and CIE Y."""
     c = np.asarray(color, f32)
@@ -253,7 +263,7 @@ def clamp_and_fix(c, clamp):
 def render(oracle, meshes, instances, view, width, height, light=None, lights=None, sky=(0, 0, 0), sky_image=None,
            materials=None, prim_materials=None, vertex_normals=None, uvs=None, lods=None, textures=None, spread_angle=0.01,
            max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True, nthreads=8, stats=None,
-           disney=None, material_words=None, tangents=None, alphas=None):
+           disney=None, material_words=None, tangents=None, alphas=None, blue_noise=None):
     """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
     meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
     point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or the float32[n, 16] table of
@@ -312,8 +322,12 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
         aperture, distortion = f32(view.get("aperture", 0.0)), f32(view.get("distortion", 0.0))
         if aperture > 0:  # RandomPointOnLens (rendercore_optix7/optix/.optix.cu:51-64); jitter is off, so the lens takes the first two numbers
             seed = wang_hash(path_idx + R0)
-            seed, l0 = random_float(seed)
-            seed, l1 = random_float(seed)
+            if blue_noise is not None and sample < 256:
+                l0 = blue_noise_sampler(blue_noise, pix % width, pix // width, sample, 2)
+                l1 = blue_noise_sampler(blue_noise, pix % width, pix // width, sample, 3)
+            else:
+                seed, l0 = random_float(seed)
+                seed, l1 = random_float(seed)
             blade = (l0 * f32(9)).astype(np.int32).astype(f32)
             l2 = ((l0 - blade * f32(1.0 / 9.0)) * f32(9)).astype(f32)
             a1, a2 = blade * f32(np.pi) / f32(4.5), (blade + f32(1)) * f32(np.pi) / f32(4.5)
@@ -514,9 +528,13 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             # ---- next event estimation (pathtracer.h:163-199)
             nee = (flags & S_SPECULAR) == 0
             if lights.count > 0 and nee.any():
-                seed_n, r0 = random_float(seed.copy())
-                seed_n, r1 = random_float(seed_n)
-                seed = np.where(nee, seed_n, seed)
+                if blue_noise is not None and sample < 2:  # pathtracer.h:168-173
+                    r0 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 4 + 4 * length)
+                    r1 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 5 + 4 * length)
+                else:
+                    seed_n, r0 = random_float(seed.copy())
+                    seed_n, r1 = random_float(seed_n)
+                    seed = np.where(nee, seed_n, seed)
                 q = np.nonzero(nee)[0]
                 P, pick, lpdf, lcol = random_point_on_light(lights, r0[q], r1[q], I[q], fN[q])
                 L = (P - I[q]).astype(f32)
@@ -546,8 +564,12 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             enough = ((bounce_cap == 1) & ((flags & S_BOUNCED) != 0)) | ((bounce_cap == 2) & ((flags & S_BOUNCEDTWICE) != 0))
             if length == max_path_length:
                 break
-            seed, r3 = random_float(seed)
-            seed, r4 = random_float(seed)
+            if blue_noise is not None and sample < 256:  # pathtracer.h:212-217
+                r3 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 6 + 4 * length)
+                r4 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 7 + 4 * length)
+            else:
+                seed, r3 = random_float(seed)
+                seed, r4 = random_float(seed)
             p_reflect = (f32(1) - rough).astype(f32)
             ddotn = dot(D, fN)
             R_refl = (D - fN * (f32(2) * ddotn)[:, None]).astype(f32)
