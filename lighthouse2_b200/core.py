@@ -169,6 +169,10 @@ CORE_MATERIAL_DEFAULTS = dict(metallic=0.0, subsurface=0.0, specular=0.5, roughn
                               sheenTint=0.0, clearcoat=0.0, clearcoatGloss=1.0, transmission=0.0, eta=1.0)  # host_material.h
 
 
+# byte offsets of (textureID, scale, uvscale, uvoffset) of detailColor @40, normals @80, detailNormals @120 and roughness @304
+CORE_MATERIAL_MAPS = dict(detail=(52, 56, 60, 68), normals=(92, 96, 100, 108), detail_normals=(132, 136, 140, 148), roughness_map=(308, 316, 320, 328))
+
+
 def core_materials(materials) -> np.ndarray:
     """CoreMaterial[n] as bytes [n, 688] from a list of dicts: color (rgb), absorption (rgb, default 0), flags (1 SMOOTH,
     2 HASALPHA), texture (diffuse map index, default -1), uvscale / uvoffset, and the Disney scalars of
@@ -192,6 +196,14 @@ def core_materials(materials) -> np.ndarray:
         f[k, 42:45] = m.get("absorption", (0.0, 0.0, 0.0))
         for name, off in CORE_MATERIAL_SCALARS.items():
             f[k, off // 4] = m.get(name, CORE_MATERIAL_DEFAULTS[name])
+        # the other maps: {"detail" | "normals" | "detail_normals" | "roughness_map": dict(texture=, scale=, uvscale=, uvoffset=)}
+        for name, (o_tex, o_scale, o_uvs, o_uvo) in CORE_MATERIAL_MAPS.items():
+            mm = m.get(name)
+            if mm is not None:
+                i[k, o_tex // 4] = mm.get("texture", -1)
+                f[k, o_scale // 4] = mm.get("scale", 1.0)
+                f[k, o_uvs // 4:o_uvs // 4 + 2] = mm.get("uvscale", (1.0, 1.0))
+                f[k, o_uvo // 4:o_uvo // 4 + 2] = mm.get("uvoffset", (0.0, 0.0))
     return out
 
 
@@ -365,14 +377,16 @@ class RenderCoreB200:
 
     def SetTextures(self, textures):
         """CoreAPI_Base::SetTextures.  textures: list of (width, height, texels uint32[pixelCount] ARGB32 with the MIP levels
-        behind each other, mip_levels); builds the CoreTexDesc array (40 bytes each, common_classes.h:246-269)."""
+        behind each other, mip_levels[, storage]); storage 0 = ARGB32 (default), 2 = NRM32 (normal maps).  Builds the
+        CoreTexDesc array (40 bytes each, common_classes.h:246-269)."""
         descs = np.zeros((len(textures), 10), np.uint32)
         keep = []
-        for i, (w, h, texels, mips) in enumerate(textures):
+        for i, tex in enumerate(textures):
+            w, h, texels, mips = tex[:4]
             t = np.ascontiguousarray(texels, np.uint32)
             keep.append(t)
             descs[i, 0:2] = np.array([t.ctypes.data], np.uint64).view(np.uint32)
-            descs[i, 2], descs[i, 3], descs[i, 5], descs[i, 7], descs[i, 8] = w, h, len(t), mips, 0
+            descs[i, 2], descs[i, 3], descs[i, 5], descs[i, 7], descs[i, 8] = w, h, len(t), mips, (tex[4] if len(tex) > 4 else 0)
         self._chk(self.lib.b200_set_textures(self.h, descs.ctypes.data if len(textures) else None, len(textures)))
 
     def SetAccumulatorBuffer(self, dptr: int):

@@ -6,9 +6,9 @@
 
 namespace b200 {
 
-// shade-stage records: float4s per triangle in the attribute pool ((vN0,u0) (vN1,u1) (vN2,u2) (v0,v1,v2,LOD) (T,alpha0) (alpha1,alpha2,-,-))
-// and per material in the material table (wavefront.cu::shadeKernel)
-constexpr int TRI_ATTR_STRIDE = 6, MAT_STRIDE = 6;
+// shade-stage records: float4s per triangle in the attribute pool ((vN0,u0) (vN1,u1) (vN2,u2) (v0,v1,v2,LOD) (T,alpha0) (B,alpha1)
+// (alpha2,-,-,-)) and per material in the material table (wavefront.cu::shadeKernel: 6 base float4, then two per extra map)
+constexpr int TRI_ATTR_STRIDE = 7, MAT_STRIDE = 14;
 
 // Arguments of one extend (closest-hit) or shadow (any-hit) wave.
 struct TraceArgs {

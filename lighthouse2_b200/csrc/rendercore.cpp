@@ -200,7 +200,7 @@ int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 	if (!coreTris) e = cudaMemsetAsync( dst, 0, (size_t)m.triCount * REC, stream );
 	else
 	{
-		// CoreTri (common_classes.h:62-83): u0..2 @0, v0..2 @16, vN0 @32, vN1 @48, vN2 @64, T @80, alpha @112 (w = LOD)
+		// CoreTri (common_classes.h:62-83): u0..2 @0, v0..2 @16, vN0 @32, vN1 @48, vN2 @64, T @80, B @96, alpha @112 (w = LOD)
 		std::vector<float> at( (size_t)m.triCount * TRI_ATTR_STRIDE * 4, 0.f );
 		for (uint32_t i = 0; i < m.triCount; i++)
 		{
@@ -209,7 +209,7 @@ int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 			memcpy( o, ct + 32, 12 ), memcpy( o + 4, ct + 48, 12 ), memcpy( o + 8, ct + 64, 12 );
 			memcpy( o + 3, ct, 4 ), memcpy( o + 7, ct + 4, 4 ), memcpy( o + 11, ct + 8, 4 );
 			memcpy( o + 12, ct + 16, 12 ), memcpy( o + 15, ct + 124, 4 );
-			memcpy( o + 16, ct + 80, 12 ), memcpy( o + 19, ct + 112, 4 ), memcpy( o + 20, ct + 116, 8 );
+			memcpy( o + 16, ct + 80, 12 ), memcpy( o + 19, ct + 112, 4 ), memcpy( o + 20, ct + 96, 12 ), memcpy( o + 23, ct + 116, 4 ), memcpy( o + 24, ct + 120, 4 );
 		}
 		e = cudaMemcpyAsync( dst, at.data(), at.size() * 4, cudaMemcpyHostToDevice, stream );
 		if (e == cudaSuccess) e = cudaStreamSynchronize( stream ); // the staging vector dies here

@@ -49,7 +49,8 @@ public:
 	int SetMaterialColors( const float* rgba, int count );    // headless shortcut: (albedo rgb, roughness) per material; rgb > 1 = emissive
 	int SetBlueNoise( const uint32_t* words, int count );     // the reference's 5 x 65536-word blue-noise table, or null
 	int DisneyProbe( int mode, int n, const float* in28, float* out8 ); // diagnostic: the Disney BSDF alone (wavefront.cu::disneyProbeKernel)
-	int uploadMaterials( const float* props16, const uint32_t* disneyWords, int count );
+	struct MaterialMap { int32_t texture; float scale, uvscale[2], uvoffset[2]; }; // per material: detail colour, normals, detail normals, roughness
+	int uploadMaterials( const float* props16, const uint32_t* disneyWords, const MaterialMap* maps, int count );
 	int SetMaterialTable( const float* props16, int count );  // 16 floats per material, see wavefront.cu
 	int SetTextures( const void* coreTexDescs, int count );   // CoreTexDesc[count], host layout, 40 B each; ARGB32 maps are sampled
 	int SetAccumulatorBuffer( void* devicePtr );              // caller-owned float4[w*h] accumulator (multi-GPU gathers), null = own

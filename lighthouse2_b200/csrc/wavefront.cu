@@ -427,6 +427,16 @@ __device__ float4 FetchTexelTrilinear( const uint32_t* __restrict__ texels, cons
 	return make_float4( (1 - fl) * p0.x + fl * p1.x, (1 - fl) * p0.y + fl * p1.y, (1 - fl) * p0.z + fl * p1.z, (1 - fl) * p0.w + fl * p1.w );
 }
 
+// material flag bits of the device record: SMOOTH, HASALPHA (host_material.h:66-71), then one bit per map that is present
+constexpr uint32_t M_DIFFUSEMAP = 4, M_DIFFUSEMAP2 = 8, M_NORMALMAP = 16, M_NORMALMAP2 = 32, M_ROUGHNESSMAP = 64;
+constexpr uint32_t M_ANYMAP = M_DIFFUSEMAP | M_DIFFUSEMAP2 | M_NORMALMAP | M_NORMALMAP2 | M_ROUGHNESSMAP;
+// one extra map of a material: rec[0] = (uv scale, uv offset), rec[1] = (first texel, width, height, xy scale of a normal map)
+__device__ __forceinline__ float4 FetchMap( const uint32_t* __restrict__ texels, const float4* __restrict__ rec, const float tu, const float tv )
+{
+	const float4 uv = __ldg( rec ), d = __ldg( rec + 1 );
+	return FetchTexel( texels, uv.x * (uv.z + tu), uv.y * (uv.w + tv), __float_as_uint( d.x ), (int)__float_as_uint( d.y ), (int)__float_as_uint( d.z ) );
+}
+
 // core_settings.h:190-192 (CLAMPINTENSITY) and FIXNAN_FLOAT3
 __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 {
@@ -517,11 +527,13 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 				const uint32_t bary = __float_as_uint( hit.x );
 				const float bu = (float)(bary & 0xffffu) * (1.0f / 65535.0f), bv = (float)(bary >> 16) * (1.0f / 65535.0f), bw = 1 - (bu + bv);
 				float4 a0 = make_float4( 0, 0, 0, 0 ), a1 = a0, a2 = a0, a3 = a0, a4 = a0, a5 = a0;
-				if (((mflags & 5u) || DISNEY) && vertexNormals)
+				float alpha2 = 0;
+				if (((mflags & (1u | M_ANYMAP)) || DISNEY) && vertexNormals)
 				{
 					const float4* ta = vertexNormals + (size_t)(__float_as_uint( info.x ) + prim) * TRI_ATTR_STRIDE;
 					a0 = __ldg( ta ), a1 = __ldg( ta + 1 ), a2 = __ldg( ta + 2 ), a3 = __ldg( ta + 3 );
-					if (DISNEY) a4 = __ldg( ta + 4 ), a5 = __ldg( ta + 5 ); // (tangent, alpha0) (alpha1, alpha2, -, -)
+					if (DISNEY || (mflags & M_NORMALMAP)) a4 = __ldg( ta + 4 ), a5 = __ldg( ta + 5 ); // (tangent, alpha0) (bitangent, alpha1)
+					if (DISNEY) alpha2 = __ldg( ta + 6 ).x;
 				}
 				// interpolated normal (GetShadingData, material_shared.h:75-81: w N0 + u N1 + v N2 for SMOOTH materials), transformed like N;
 				// it also stands in for the normal-mapped normal fN.  (Consistent normals, :90-97, need the per-vertex alpha of the
@@ -540,18 +552,20 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					if (vertexNormals)
 					{
 						const bool backSide = dot( D, N ) > 0;
-						const float alpha = bw * a4.w + bu * a5.x + bv * a5.y;
+						const float alpha = bw * a4.w + bu * a5.w + bv * alpha2;
 						sN = disney::ConsistentNormal( D * -1.0f, backSide ? sN * -1.0f : sN, alpha ) * (backSide ? -1.0f : 1.0f);
 					}
 					// the reference takes CoreTri::T as it is (object space); a mesh without CoreTris gets an arbitrary tangent
 					if (!(dot( tangent, tangent ) > 0)) tangent = fabsf( sN.x ) > 0.9f ? v3( 0.f, 1.f, 0.f ) : v3( 1.f, 0.f, 0.f );
 				}
 				const V3 I = O + D * hit.w;
-				// diffuse map (material_shared.h:99-131): trilinear fetch at the ray-cone LOD; an alpha texel below 0.5 lets the path through
-				if ((mflags & 4u) && f.texels)
+				// maps (material_shared.h:99-173).  Diffuse map: trilinear fetch at the ray-cone LOD; an alpha texel below 0.5 lets the path through
+				float tu = 0, tv = 0;
+				if ((mflags & M_ANYMAP) && f.texels) tu = bw * a0.w + bu * a1.w + bv * a2.w, tv = bw * a3.x + bu * a3.y + bv * a3.z;
+				else mflags &= ~M_ANYMAP;
+				if (mflags & M_DIFFUSEMAP)
 				{
 					c3 = __ldg( materials + mat * MAT_STRIDE + 3 ), c4 = __ldg( materials + mat * MAT_STRIDE + 4 );
-					const float tu = bw * a0.w + bu * a1.w + bv * a2.w, tv = bw * a3.x + bu * a3.y + bv * a3.z;
 					const float lambda = a3.w + log2f( f.spreadAngle * hit.w * (1.0f / fabsf( dot( D, N ) )) );
 					const float4 texel = FetchTexelTrilinear( f.texels, lambda, c3.x * (c3.z + tu), c3.y * (c3.w + tv), __float_as_uint( c2.w ),
 						(int)__float_as_uint( c4.x ), (int)__float_as_uint( c4.y ), (int)__float_as_uint( c1.w ) );
@@ -564,9 +578,38 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 							eo = po, er = D, en = lastN, et = isfinite( throughput.x + throughput.y + throughput.z ) ? throughput : v3( 0.f, 0.f, 0.f ), epdf = bsdfPdf;
 							wantExt = true;
 						}
-						color = v3( 0.f, 0.f, 0.f ), mflags |= 0x80000000u; // nothing else happens at this vertex
+						color = v3( 0.f, 0.f, 0.f ), mflags = 0x80000000u; // nothing else happens at this vertex
 					}
-					else color = color * v3( texel );
+					else
+					{
+						color = color * v3( texel );
+						if (mflags & M_DIFFUSEMAP2) // detail layer: additive around 0.5, needs the base map (:120-130)
+							color = color + v3( FetchMap( f.texels, materials + mat * MAT_STRIDE + 6, tu, tv ) ) - v3( 0.5f, 0.5f, 0.5f );
+					}
+				}
+				if (mflags & M_NORMALMAP)
+				{
+					// :132-159; the reference derives the xy scale from bits of the packed record that alias the medium colour (:141),
+					// this core takes Vec3Value::scale of CoreMaterial::normals / detailNormals
+					const float4* rec = materials + mat * MAT_STRIDE + 8;
+					V3 sn = (v3( FetchMap( f.texels, rec, tu, tv ) ) - v3( 0.5f, 0.5f, 0.5f )) * 2.0f;
+					const float s0 = __ldg( rec + 1 ).w;
+					sn.x *= s0, sn.y *= s0;
+					if (mflags & M_NORMALMAP2)
+					{
+						V3 layer = (v3( FetchMap( f.texels, rec + 2, tu, tv ) ) - v3( 0.5f, 0.5f, 0.5f )) * 2.0f;
+						const float s1 = __ldg( rec + 3 ).w;
+						layer.x *= s1, layer.y *= s1;
+						sn = sn + layer;
+					}
+					sn = normalize( sn );
+					sN = normalize( v3( a4 ) * sn.x + v3( a5 ) * sn.y + sN * sn.z ); // tangent, bitangent as the CoreTri holds them
+				}
+				if (mflags & M_ROUGHNESSMAP)
+				{
+					// :161-169: the map's red channel replaces the roughness byte
+					roughness = fmaxf( 0.001f, (float)(uint32_t)(FetchMap( f.texels, materials + mat * MAT_STRIDE + 12, tu, tv ).x * 255.0f) * (1.0f / 255.0f) );
+					if (DISNEY) dd.roughness = roughness;
 				}
 				if (mflags & 0x80000000u) {}
 				else
@@ -913,7 +956,8 @@ int RenderCore::SetSkyData( const float* rgb, int width, int height )
 
 // CoreAPI_Base::SetTextures (core_api_base.h:98): CoreTexDesc[count] in the host layout (common_classes.h:246-269, 40 bytes: data
 // pointer, width, height, flags, pixelCount, firstPixel, MIPlevels, storage).  ARGB32 textures are copied, MIP levels included, into
-// one texel pool (what SyncStorageType does, lib/rendercore_optix7/rendercore.cpp:447-505); other storages are not sampled here.
+// one texel pool (what SyncStorageType does, lib/rendercore_optix7/rendercore.cpp:447-505), NRM32 normal maps beside them (the
+// reference keeps a second pool with the same texel format); ARGB128 (HDR) textures are not sampled here.
 int RenderCore::SetTextures( const void* coreTexDescs, int count )
 {
 	WavefrontState* w = state( wf );
@@ -926,7 +970,7 @@ int RenderCore::SetTextures( const void* coreTexDescs, int count )
 		const uint32_t* data;
 		uint32_t width, height, pixelCount, mips, storage;
 		memcpy( &data, d, 8 ), memcpy( &width, d + 8, 4 ), memcpy( &height, d + 12, 4 ), memcpy( &pixelCount, d + 20, 4 ), memcpy( &mips, d + 28, 4 ), memcpy( &storage, d + 32, 4 );
-		if (storage != 0 /* ARGB32 */ || !data || !width || !height) continue;
+		if ((storage != 0 /* ARGB32 */ && storage != 2 /* NRM32: the same four bytes per texel */) || !data || !width || !height) continue;
 		// the levels actually present: level k has (w >> k)(h >> k) texels
 		uint32_t have = 0, need = 0, ww = width, hh = height;
 		while (have < (mips ? mips : 1) && ww && hh && need + ww * hh <= pixelCount) need += ww * hh, ww >>= 1, hh >>= 1, have++;
@@ -950,9 +994,18 @@ int RenderCore::SetMaterials( const void* coreMaterials, int count )
 	if (count < 0 || (count > 0 && !coreMaterials)) return fail( "SetMaterials: bad arguments" );
 	std::vector<float> table( (size_t)count * 16, 0.f );
 	std::vector<uint32_t> words( (size_t)count * 3, 0u );
+	std::vector<MaterialMap> maps( (size_t)count * 4 );
 	for (int i = 0; i < count; i++)
 	{
 		const char* m = (const char*)coreMaterials + (size_t)i * 688;
+		// the other maps: detailColor @40, normals @80, detailNormals @120 (Vec3Value: textureID +12, scale +16, uvscale +20, uvoffset +28),
+		// roughness @304 (ScalarValue: textureID +4, scale +12, uvscale +16, uvoffset +24)
+		static const int mapAt[4][4] = { { 52, 56, 60, 68 }, { 92, 96, 100, 108 }, { 132, 136, 140, 148 }, { 308, 316, 320, 328 } };
+		for (int k = 0; k < 4; k++)
+		{
+			MaterialMap& mm = maps[(size_t)i * 4 + k];
+			memcpy( &mm.texture, m + mapAt[k][0], 4 ), memcpy( &mm.scale, m + mapAt[k][1], 4 ), memcpy( mm.uvscale, m + mapAt[k][2], 8 ), memcpy( mm.uvoffset, m + mapAt[k][3], 8 );
+		}
 		float* t = &table[(size_t)i * 16];
 		uint32_t flags;
 		int32_t textureID;
@@ -973,7 +1026,7 @@ int RenderCore::SetMaterials( const void* coreMaterials, int count )
 			words[(size_t)i * 3 + k / 4] += (uint32_t)(value * 255.0f) << (8 * (k & 3));
 		}
 	}
-	return uploadMaterials( table.data(), words.data(), count );
+	return uploadMaterials( table.data(), words.data(), maps.data(), count );
 }
 
 // headless shortcut: (albedo rgb, roughness) per material, opaque, flat normals, no map
@@ -1003,10 +1056,10 @@ int RenderCore::SetMaterialTable( const float* props16, int count )
 		words[(size_t)i * 3] = ((uint32_t)(0.5f * 255.0f) << 16) + ((uint32_t)(fminf( fmaxf( t[3], 0.f ), 1.f ) * 255.0f) << 24);
 		words[(size_t)i * 3 + 2] = (uint32_t)(fminf( fmaxf( t[4], 0.f ), 1.f ) * 255.0f) << 16;
 	}
-	return uploadMaterials( props16, words.data(), count );
+	return uploadMaterials( props16, words.data(), nullptr, count );
 }
 
-int RenderCore::uploadMaterials( const float* props16, const uint32_t* disneyWords, int count )
+int RenderCore::uploadMaterials( const float* props16, const uint32_t* disneyWords, const MaterialMap* maps, int count )
 {
 	WavefrontState* w = state( wf );
 	constexpr int REC = MAT_STRIDE * 4; // floats per device record
@@ -1019,7 +1072,20 @@ int RenderCore::uploadMaterials( const float* props16, const uint32_t* disneyWor
 		uint32_t flags = (uint32_t)t[6] & 3u, offset = 0, dims[4] = { 0, 0, 0, 0 }, mips = 0;
 		const int tex = (int)t[11];
 		if (tex >= 0 && tex < (int)w->textures.size() && w->textures[tex].valid)
-			flags |= 4u, offset = w->textures[tex].offset, dims[0] = w->textures[tex].width, dims[1] = w->textures[tex].height, mips = w->textures[tex].mipLevels;
+			flags |= M_DIFFUSEMAP, offset = w->textures[tex].offset, dims[0] = w->textures[tex].width, dims[1] = w->textures[tex].height, mips = w->textures[tex].mipLevels;
+		// detail colour, normal map, detail normal map, roughness map: two float4 each from float 24 on; the detail layers need their base map
+		static const uint32_t mapBit[4] = { M_DIFFUSEMAP2, M_NORMALMAP, M_NORMALMAP2, M_ROUGHNESSMAP };
+		for (int k = 0; maps && k < 4; k++)
+		{
+			const MaterialMap& mm = maps[(size_t)i * 4 + k];
+			if (mm.texture < 0 || mm.texture >= (int)w->textures.size() || !w->textures[mm.texture].valid) continue;
+			if ((k == 0 && !(flags & M_DIFFUSEMAP)) || (k == 2 && !(flags & M_NORMALMAP))) continue;
+			flags |= mapBit[k];
+			float* r = d + 24 + 8 * k;
+			const WavefrontState::TextureRec& t = w->textures[mm.texture];
+			r[0] = mm.uvscale[0], r[1] = mm.uvscale[1], r[2] = mm.uvoffset[0], r[3] = mm.uvoffset[1];
+			memcpy( r + 4, &t.offset, 4 ), memcpy( r + 5, &t.width, 4 ), memcpy( r + 6, &t.height, 4 ), r[7] = mm.scale;
+		}
 		memcpy( d + 6, &flags, 4 ), memcpy( d + 7, &mips, 4 ), memcpy( d + 11, &offset, 4 ), memcpy( d + 16, dims, 16 );
 		memcpy( d + 20, disneyWords + (size_t)i * 3, 12 );
 	}

@@ -182,3 +182,78 @@ def test_disney_frame_matches_reference_bsdf_restatement(ref, roulette):
     assert np.allclose(acc[..., 3], img[..., 3], rtol=1e-5)
     assert abs(st["totalExtensionRays"] - sum(stats["ext"])) <= 0.005 * sum(stats["ext"])
     assert abs(st["totalShadowRays"] - sum(stats["shadow"])) <= 0.005 * sum(stats["shadow"])
+
+
+# ---- the other maps of GetShadingData: detail colour, normal map + detail normal map, roughness map (material_shared.h:120-169) ---
+def _mapped_scene():
+    sc = _disney_scene()
+    grid, sph, quad = sc["case"]["meshes"]
+    rng = np.random.default_rng(21)
+    argb = lambda n: (rng.integers(0, 256, (n, 4)).astype(np.uint32) * np.array([1, 1 << 8, 1 << 16, 1 << 24], np.uint32)).sum(axis=1).astype(np.uint32)
+
+    def normal_map(side):  # mostly +z with some tilt, alpha unused
+        v = rng.normal(size=(side * side, 3)) * 0.35 + np.array([0, 0, 1.0])
+        v /= np.linalg.norm(v, axis=1, keepdims=True)
+        b = np.clip((v * 0.5 + 0.5) * 256, 0, 255).astype(np.uint32)
+        return (b[:, 0] | (b[:, 1] << 8) | (b[:, 2] << 16) | (255 << 24)).astype(np.uint32)
+    sc["textures"] = sc["textures"] + [(8, 8, argb(64), 1), (16, 16, normal_map(16), 1, 2), (8, 8, normal_map(8), 1, 2), (8, 8, argb(64), 1)]
+    # floor material 6: base map + detail layer + normal map + detail normal map + roughness map; sphere material 5: normal map only
+    sc["dicts"][6].update(detail=dict(texture=1, uvscale=(3.0, 3.0)), normals=dict(texture=2, scale=0.7, uvscale=(2.0, 2.0), uvoffset=(0.1, 0.2)),
+                          detail_normals=dict(texture=3, scale=0.5, uvscale=(5.0, 5.0)), roughness_map=dict(texture=4, uvscale=(1.5, 1.5)))
+    sc["dicts"][5].update(normals=dict(texture=2, scale=1.0, uvscale=(4.0, 4.0)))
+    sc["maps"] = [({k: m[k] for k in ("detail", "normals", "detail_normals", "roughness_map") if k in m} or None) for m in sc["dicts"]]
+    unit = lambda v: (v / np.linalg.norm(v, axis=-1, keepdims=True)).astype(np.float32)
+    sc["bitangents"] = [unit(np.cross(np.cross(m[:, 1] - m[:, 0], m[:, 2] - m[:, 0]), m[:, 1] - m[:, 0])) for m in (grid, sph, quad)]
+    # the spheres get texture coordinates too
+    sph_uv = np.stack([np.arctan2(sph[:, :, 0], sph[:, :, 2]) / (2 * np.pi) + 0.5, np.arccos(np.clip(sph[:, :, 1] / 0.35, -1, 1)) / np.pi], axis=2).astype(np.float32)
+    sc["uvs"] = [sc["uvs"][0], sph_uv, None]
+    return sc
+
+
+@pytest.mark.parametrize("bsdf", [0, 1])
+def test_detail_normal_and_roughness_maps(ref, bsdf):
+    import cases
+    from lighthouse2_b200 import scenes
+    sc = _mapped_scene()
+    w, h, spp = 160, 90, 2
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    case = sc["case"]
+    c = core.RenderCoreB200(0)
+    for i, m in enumerate(case["meshes"]):
+        ct = core.core_tris(m, sc["prim_materials"][i], sc["vertex_normals"][i], sc["uvs"][i], sc["lods"][i], sc["tangents"][i], sc["alphas"][i])
+        ct[:, 24:27] = sc["bitangents"][i]  # CoreTri::B at byte 96
+        c.SetGeometry(i, m, ct)
+    for i, (mesh, mat) in enumerate(case["instances"]):
+        c.SetInstance(i, mesh, mat)
+    c.SetInstance(len(case["instances"]), -1)
+    c.UpdateToplevel()
+    c.SetTarget(w, h, spp)
+    c.SetTextures(sc["textures"])
+    c.SetMaterials(sc["dicts"])
+    c.SetLights(sc["area"], sc["point"], sc["spot"], sc["dir"])
+    c.SetSkyData(sc["sky"])
+    for k, v in dict(maxPathLength=5, jitter=0, bsdf=bsdf).items():
+        c.Setting(k, v)
+    c.Render(view, converge=1)
+    acc, st = c.ReadAccumulator(), c.GetCoreStats()
+    # the same frame without the extra maps must differ: the maps are really sampled
+    plain = [{k: v for k, v in m.items() if k not in ("detail", "normals", "detail_normals", "roughness_map")} for m in sc["dicts"]]
+    c.SetMaterials(plain)
+    c.Render(view, converge=1)
+    flat = c.ReadAccumulator()
+    c.Shutdown()
+    port = cases.load_oracle(dict(case, rays=None), "port")
+    stats = {}
+    kw = dict(disney=ref, material_words=sc["words"], alphas=sc["alphas"]) if bsdf else {}
+    img = wr.render(port, case["meshes"], case["instances"], view, w, h, lights=wr.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]),
+                    sky_image=sc["sky"], materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
+                    uvs=sc["uvs"], lods=sc["lods"], textures=sc["textures"], max_path_length=5, spp=spp, stats=stats,
+                    tangents=sc["tangents"], bitangents=sc["bitangents"], material_maps=sc["maps"], **kw)
+    mean = float(img[..., :3].mean())
+    rmse = float(np.sqrt(np.mean((acc[..., :3] - img[..., :3]) ** 2)))
+    big = np.abs(acc[..., :3] - img[..., :3]).max(axis=2) > 0.02 * mean
+    print("mapped image (bsdf %d): mean" % bsdf, mean, "rmse", rmse, "pixels off by >2%:", int(big.sum()), "rays", st["totalExtensionRays"], sum(stats["ext"]),
+          "vs unmapped", float(np.abs(flat[..., :3] - acc[..., :3]).mean()))
+    assert np.isfinite(acc).all() and rmse <= 1e-2 * mean and big.mean() < 2e-2
+    assert abs(st["totalExtensionRays"] - sum(stats["ext"])) <= 0.005 * sum(stats["ext"])
+    assert np.abs(flat[..., :3] - acc[..., :3]).mean() > 0.01 * mean

@@ -263,7 +263,7 @@ def clamp_and_fix(c, clamp):
 def render(oracle, meshes, instances, view, width, height, light=None, lights=None, sky=(0, 0, 0), sky_image=None,
            materials=None, prim_materials=None, vertex_normals=None, uvs=None, lods=None, textures=None, spread_angle=0.01,
            max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True, nthreads=8, stats=None,
-           disney=None, material_words=None, tangents=None, alphas=None, blue_noise=None):
+           disney=None, material_words=None, tangents=None, alphas=None, blue_noise=None, material_maps=None, bitangents=None):
     """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
     meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
     point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or the float32[n, 16] table of
@@ -272,7 +272,9 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
     (width, height, texels uint32[], mip_levels); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off).
     disney = oracle.DisneyRef() switches the BSDF to the reference's Disney one (Setting bsdf = 1): material_words =
     uint32[n, 4] (core.disney_words), tangents = per mesh float32[T, 3] (CoreTri::T), alphas = per mesh float32[T, 3]
-    (CoreTri::alpha; consistent normal interpolation, material_shared.h:87-97)."""
+    (CoreTri::alpha; consistent normal interpolation, material_shared.h:87-97).  material_maps = per material None or a dict
+    with "detail" / "normals" / "detail_normals" / "roughness_map" -> dict(texture, scale, uvscale, uvoffset)
+    (material_shared.h:120-169), bitangents = per mesh float32[T, 3] (CoreTri::B, for the normal maps)."""
     npx = width * height
     acc = np.zeros((npx, 4), np.float64)
     pos, p1 = view["pos"].astype(f32), view["p1"].astype(f32)
@@ -301,7 +303,8 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
     if textures:
         off = 0
         chunks = []
-        for (tw, th, tx, mips) in textures:
+        for tex in textures:
+            tw, th, tx, mips = tex[:4]
             tex_rec.append((off, tw, th, mips))
             chunks.append(np.asarray(tx, np.uint32))
             off += len(tx)
@@ -411,11 +414,16 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             mapped = np.zeros(n, bool)
             if materials is not None and textures:
                 mapped = (tex_id >= 0) & (tex_id < len(tex_rec))
-            if vertex_normals is not None or mapped.any() or disney is not None:
+            has_maps = np.zeros(n, bool)
+            if material_maps is not None and textures:
+                for k, mm in enumerate(material_maps):
+                    if mm is not None:
+                        has_maps |= mat == k
+            if vertex_normals is not None or mapped.any() or disney is not None or has_maps.any():
                 for i in np.unique(inst):
                     mesh = inst_mesh[i]
                     has_vn = vertex_normals is not None and vertex_normals[mesh] is not None
-                    sel = np.nonzero((inst == i) & ((smooth & has_vn) | mapped | (disney is not None)))[0]
+                    sel = np.nonzero((inst == i) & ((smooth & has_vn) | mapped | has_maps | (disney is not None)))[0]
                     if len(sel) == 0:
                         continue
                     tri = meshes[mesh][prim[sel]]
@@ -447,13 +455,16 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                         if tangents is not None and tangents[mesh] is not None:
                             tang[sel] = tangents[mesh][prim[sel]]
                     mp = mapped[sel]
+                    maps_here = bool(has_maps[sel].any())
+                    if mp.any() or maps_here:
+                        uv_all = uvs[mesh][prim[sel]].astype(f32) if (uvs is not None and uvs[mesh] is not None) else np.zeros((len(sel), 3, 2), f32)
+                        tu_all = (bw * uv_all[:, 0, 0] + bu * uv_all[:, 1, 0] + bv * uv_all[:, 2, 0]).astype(f32)
+                        tv_all = (bw * uv_all[:, 0, 1] + bu * uv_all[:, 1, 1] + bv * uv_all[:, 2, 1]).astype(f32)
                     if mp.any():
                         # diffuse map (material_shared.h:99-131): trilinear fetch at the ray-cone LOD, alpha below 0.5 = pass through
                         q = sel[mp]
-                        uv = uvs[mesh][prim[q]].astype(f32) if (uvs is not None and uvs[mesh] is not None) else np.zeros((len(q), 3, 2), f32)
                         ld = lods[mesh][prim[q]].astype(f32) if (lods is not None and lods[mesh] is not None) else np.zeros(len(q), f32)
-                        tu = (bw[mp] * uv[:, 0, 0] + bu[mp] * uv[:, 1, 0] + bv[mp] * uv[:, 2, 0]).astype(f32)
-                        tv = (bw[mp] * uv[:, 0, 1] + bu[mp] * uv[:, 1, 1] + bv[mp] * uv[:, 2, 1]).astype(f32)
+                        tu, tv = tu_all[mp], tv_all[mp]
                         with np.errstate(all="ignore"):
                             lam = (ld + np.log2(f32(spread_angle) * t[q] * (f32(1) / np.abs(dot(D[q], N[q]))))).astype(f32)
                         rec = np.array([tex_rec[k] for k in tex_id[q]], np.int64)
@@ -462,6 +473,37 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                         hole = ((mflags[q] & 2) != 0) & (texel[:, 3] < f32(0.5))
                         passthrough[q[hole]] = True
                         color[q[~hole]] = (color[q[~hole]] * texel[~hole, :3]).astype(f32)
+                    if maps_here:
+                        def fetch_map(mm, idx):
+                            o, tw, th, _ = tex_rec[mm["texture"]]
+                            us, uo = mm.get("uvscale", (1.0, 1.0)), mm.get("uvoffset", (0.0, 0.0))
+                            return fetch_texel(tex_pool, (f32(us[0]) * (f32(uo[0]) + tu_all[idx])).astype(f32), (f32(us[1]) * (f32(uo[1]) + tv_all[idx])).astype(f32),
+                                               np.full(len(idx), o, np.int64), np.full(len(idx), tw, np.int64), np.full(len(idx), th, np.int64))
+                        for k in np.unique(mat[sel]):
+                            mm = material_maps[k] if k < len(material_maps) else None
+                            if mm is None:
+                                continue
+                            idx = np.nonzero((mat[sel] == k) & ~passthrough[sel])[0]
+                            if len(idx) == 0:
+                                continue
+                            g = sel[idx]
+                            if "detail" in mm and mapped[g].all():  # additive around 0.5, needs the base map (:120-130)
+                                color[g] = ((color[g] + fetch_map(mm["detail"], idx)[:, :3]).astype(f32) - f32(0.5)).astype(f32)
+                            if "normals" in mm:  # :132-159, with the map's scale field for the xy scale
+                                sn = ((fetch_map(mm["normals"], idx)[:, :3] - f32(0.5)) * f32(2)).astype(f32)
+                                sn[:, :2] = (sn[:, :2] * f32(mm["normals"].get("scale", 1.0))).astype(f32)
+                                if "detail_normals" in mm:
+                                    l1 = ((fetch_map(mm["detail_normals"], idx)[:, :3] - f32(0.5)) * f32(2)).astype(f32)
+                                    l1[:, :2] = (l1[:, :2] * f32(mm["detail_normals"].get("scale", 1.0))).astype(f32)
+                                    sn = (sn + l1).astype(f32)
+                                sn = normalize(sn)
+                                Tt = tangents[mesh][prim[g]].astype(f32)
+                                Bt = bitangents[mesh][prim[g]].astype(f32)
+                                sN[g] = normalize(((Tt * sn[:, 0:1]).astype(f32) + (Bt * sn[:, 1:2]).astype(f32)).astype(f32) + (sN[g] * sn[:, 2:3]).astype(f32))
+                            if "roughness_map" in mm:  # :161-169: the red channel replaces the roughness byte
+                                rb = (fetch_map(mm["roughness_map"], idx)[:, 0] * f32(255)).astype(f32).astype(np.uint32)
+                                rough[g] = np.maximum(f32(0.001), rb.astype(f32) * f32(1.0 / 255.0))
+                                words[g, 0] = (words[g, 0] & np.uint32(0x00ffffff)) | (rb << np.uint32(24))
             if disney is not None:  # a triangle without a tangent gets an arbitrary one (the reference would divide by zero)
                 notan = ~(dot(tang, tang) > 0)
                 tang[notan] = np.where((np.abs(sN[notan, 0]) > f32(0.9))[:, None], np.array([0, 1, 0], f32), np.array([1, 0, 0], f32))
