@@ -281,6 +281,12 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 // smallest t, then (ties) the earliest-queued pair, so the first-visited triangle wins exact ties like the
 // reference's strict `found_t < t` (bvh.cpp:268).
 constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
+#ifndef B200_PREFETCH_NODE
+#define B200_PREFETCH_NODE 0
+#endif
+#ifndef B200_PREFETCH_TRIS
+#define B200_PREFETCH_TRIS 0
+#endif
 #ifndef B200_REFILL_BELOW
 #define B200_REFILL_BELOW 22
 #endif
@@ -456,6 +462,16 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				const uint32_t hm = intersectNode( r, K, n0, n1, n2, n3, n4 );
 				ngroup = make_uint2( n1.x, (hm & 0xff000000u) | (n0.w >> 24) );
 				tgroup = make_uint2( n1.y, hm & 0x00ffffffu );
+#if B200_PREFETCH_NODE
+				if (ngroup.y > 0x00ffffffu)
+				{
+					// the child this lane visits next: start its fetch now (scenes larger than L2)
+					const uint32_t nb = 31 - __clz( ngroup.y ), ns = (nb - 24) ^ (r.octinv4 & 0xffu);
+					const uint4* nn = nodes + (size_t)(ngroup.x + __popc( ngroup.y & 0xffu & ~(0xffffffffu << ns) )) * 5;
+					asm volatile( "prefetch.global.L2 [%0];" ::"l"( nn ) );
+					asm volatile( "prefetch.global.L2 [%0];" ::"l"( nn + 4 ) );
+				}
+#endif
 			}
 			// B. top level: a hit leaf is an instance -- remember what is left here, then descend into its BLAS
 			if (active && instBase < 0 && tgroup.y)
@@ -485,6 +501,13 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					{
 						lastQueued = qtail + __popc( m & lanemask_lt() );
 						ring[lastQueued & (RING_CAP - 1)] = make_uint2( tgroup.x | (lane << 27), tgroup.y );
+#if B200_PREFETCH_TRIS
+						{
+							const float4* tp = tris + (size_t)(tgroup.x + (uint32_t)__ffs( tgroup.y ) - 1) * 3;
+							asm volatile( "prefetch.global.L2 [%0];" ::"l"( tp ) );
+							asm volatile( "prefetch.global.L2 [%0];" ::"l"( tp + 3 * (uint32_t)__popc( tgroup.y ) - 1 ) );
+						}
+#endif
 						if (COUNT) nTris += __popc( tgroup.y );
 					}
 					pendingTris += __reduce_add_sync( 0xffffffffu, has ? (uint32_t)__popc( tgroup.y ) : 0u );
