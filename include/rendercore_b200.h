@@ -133,6 +133,7 @@ typedef struct b200_stats {
 	uint32_t wideNodeCount, triangleCount, instanceCount, tlasNodeCount;
 	uint32_t kernelLaunches;            /* kernels this core has launched since creation */
 	float lastTraceMs;                  /* device time of the last b200_trace_* kernel (CUDA events on the core's stream) */
+	uint32_t bvhCacheHits;              /* meshes whose host-built tree came from the on-disk cache (environment B200_BVH_CACHE = directory) */
 } b200_stats;
 B200_API int b200_get_stats( b200_core* c, b200_stats* out );
 B200_API int b200_set_probe( b200_core* c, int x, int y );

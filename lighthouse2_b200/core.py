@@ -42,7 +42,7 @@ class Stats(C.Structure):
         ("shadowTraceTime", C.c_float), ("shadeTime", C.c_float),
         ("probedInstid", C.c_int32), ("probedTriid", C.c_int32), ("probedDist", C.c_float),
         ("wideNodeCount", C.c_uint32), ("triangleCount", C.c_uint32), ("instanceCount", C.c_uint32), ("tlasNodeCount", C.c_uint32),
-        ("kernelLaunches", C.c_uint32), ("lastTraceMs", C.c_float),
+        ("kernelLaunches", C.c_uint32), ("lastTraceMs", C.c_float), ("bvhCacheHits", C.c_uint32),
     ]
 
     def as_dict(self):

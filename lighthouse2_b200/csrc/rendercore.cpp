@@ -291,7 +291,22 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 		for (int k = 0; k < 3; k++) boxes[i].grow( vertexData + (size_t)(3 * i + k) * 4 );
 	}
 	WideBvh bvh;
-	BuildWideBvh( boxes.data(), T, 3, buildThreads, bvh );
+	// on-disk cache of the host-built tree (bvh_cache.cpp), keyed by the vertex data; B200_BVH_CACHE names the directory
+	static const char* cacheEnv = getenv( "B200_BVH_CACHE" );
+	const bool useCache = cacheEnv && *cacheEnv && T >= 1024;
+	uint64_t cacheKey = 0;
+	bool fromCache = false;
+	if (useCache)
+	{
+		cacheKey = HashBytes( vertexData, (size_t)T * 48, 0xB200 );
+		fromCache = LoadWideBvh( cacheEnv, cacheKey, T, 3, bvh );
+	}
+	if (!fromCache)
+	{
+		BuildWideBvh( boxes.data(), T, 3, buildThreads, bvh );
+		if (useCache) StoreWideBvh( cacheEnv, cacheKey, T, 3, bvh ); // best effort: an unwritable directory only costs the next start-up
+	}
+	else stats.bvhCacheHits++;
 	MeshRec m;
 	m.nodeBase = blasNodeEnd, m.nodeCount = (uint32_t)bvh.nodes.size(), m.triBase = triEnd, m.triCount = T;
 	m.levelStart = bvh.levelStart, m.bounds = bvh.bounds, m.built = true;

@@ -7,6 +7,7 @@
 // triangle buffer in leaf order, and an instance table in top-level leaf order.
 #pragma once
 #include <cstdint>
+#include <string>
 #include <vector>
 
 namespace b200 {
@@ -75,6 +76,11 @@ extern float g_sahPrimCost; // builder tunable: SAH cost of one leaf triangle re
 // maxLeafPrims: 3 for triangles (unary 3-bit count), 1 for instances.  Indices in the result are
 // relative (root = 0, primBase relative to 0); the core rebases them when it places the tree in its pools.
 void BuildWideBvh( const Aabb* primBoxes, uint32_t n, int maxLeafPrims, int threads, WideBvh& out );
+
+// On-disk cache of built trees (bvh_cache.cpp): 64-bit content hash, load (false = absent or failed a check), store.
+uint64_t HashBytes( const void* data, size_t bytes, uint64_t seed );
+bool LoadWideBvh( const std::string& dir, uint64_t key, uint32_t triCount, int maxLeafPrims, WideBvh& out );
+bool StoreWideBvh( const std::string& dir, uint64_t key, uint32_t triCount, int maxLeafPrims, const WideBvh& bvh );
 
 // Re-quantise all child boxes of a wide tree from per-primitive boxes given in ORIGINAL index order
 // (host reference implementation of the GPU refit; used by tests and for TLAS updates).

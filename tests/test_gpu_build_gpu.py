@@ -120,3 +120,46 @@ def test_refit_after_gpu_build_and_second_mesh():
     rep = parity.compare("gpu_refit", hits, port, O, D, *port.trace(O, D, nthreads=8))
     rc.Shutdown()
     parity.assert_parity(rep)
+
+
+def test_bvh_disk_cache_round_trip(tmp_path):
+    """B200_BVH_CACHE (bvh_cache.cpp): the second core takes the host-built tree from disk and traces the
+    same hits; a damaged file is ignored and rebuilt.  (The directory is read once per process: subprocesses.)"""
+    import subprocess
+    import sys
+    script = r'''
+import sys, json, numpy as np
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+from lighthouse2_b200 import core, scenes
+verts = scenes.sphere_field(60_000)
+O, D = scenes.random_rays(50_000, 20.0, seed=5)
+rc = core.RenderCoreB200(0)
+rc.SetGeometry(0, verts); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
+h = rc.TraceClosest(*core.pack_rays(O, D))
+st = rc.GetCoreStats()
+np.save(sys.argv[1], h)
+print(json.dumps(dict(hits=int(st["bvhCacheHits"]), nodes=int(st["wideNodeCount"]), build_ms=float(st["bvhBuildTime"]))))
+''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, B200_BVH_CACHE=str(tmp_path))
+
+    def run(tag):
+        r = subprocess.run([sys.executable, "-c", script, str(tmp_path / (tag + ".npy"))], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        import json
+        return json.loads(r.stdout.strip().splitlines()[-1]), np.load(tmp_path / (tag + ".npy"))
+    a, ha = run("first")
+    files = [f for f in os.listdir(tmp_path) if f.endswith(".b2wb")]
+    assert a["hits"] == 0 and len(files) == 1
+    b, hb = run("second")
+    assert b["hits"] == 1 and b["nodes"] == a["nodes"]
+    assert np.array_equal(ha.view(np.uint32), hb.view(np.uint32))
+    print("bvh cache: build", a["build_ms"], "ms, from cache", b["build_ms"], "ms")
+    # flip one byte in the node payload: the checksum rejects the file, the tree is rebuilt (and the file rewritten)
+    path = tmp_path / files[0]
+    raw = bytearray(path.read_bytes())
+    raw[len(raw) // 2] ^= 0x40
+    path.write_bytes(bytes(raw))
+    c, hc = run("third")
+    assert c["hits"] == 0 and np.array_equal(ha.view(np.uint32), hc.view(np.uint32))
+    d, _ = run("fourth")
+    assert d["hits"] == 1
