@@ -78,6 +78,9 @@ int main( int argc, char** argv )
 		// the table of b200_set_material_table: rgb, roughness | transmission, eta, flags, - | extinction rgb, texture | uv scale, uv offset
 		const float* c = (const float*)r.bytes( 64 );
 		materials[i].color.value.x = c[0], materials[i].color.value.y = c[1], materials[i].color.value.z = c[2];
+		// empty map slots carry textureID -1 (common_classes.h:183,190), which is how a HostMaterial arrives
+		materials[i].detailColor.textureID = materials[i].normals.textureID = materials[i].detailNormals.textureID = -1;
+		materials[i].roughness.textureID = -1;
 		materials[i].color.textureID = (int)c[11];
 		materials[i].color.uvscale.x = c[12], materials[i].color.uvscale.y = c[13], materials[i].color.uvoffset.x = c[14], materials[i].color.uvoffset.y = c[15];
 		materials[i].roughness.value = c[3], materials[i].transmission.value = c[4], materials[i].eta.value = c[5];
