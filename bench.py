@@ -297,27 +297,44 @@ def run_b200(args):
                 ext_rays += w["n"]
 
     # ---- e2e: host buffers through the C ABI (H2D + wave + D2H + sync inside each call) ------------------------
-    e2e_ms = None
+    e2e_ms = e2e_sync_ms = None
     pcie_h2d = 0.0
     if not args.no_e2e:
         lib, h = rc.lib, rc.h
 
-        def e2e_pass():
+        def e2e_pass(queued=True):
+            # the six waves of a step are independent inputs: they are queued back to back (b200_trace_*_async) and collected with
+            # one b200_wait, so that the upload of a wave overlaps the trace and the download of the one before it
             for w in waves:
-                fn = lib.b200_trace_closest if w["kind"] == "closest" else lib.b200_trace_any
+                if queued:
+                    fn = lib.b200_trace_closest_async if w["kind"] == "closest" else lib.b200_trace_any_async
+                else:
+                    fn = lib.b200_trace_closest if w["kind"] == "closest" else lib.b200_trace_any
                 if fn(h, w["hO"].data_ptr(), w["hD"].data_ptr(), w["n"], w["hOut"].data_ptr()):
                     raise RuntimeError(lib.b200_last_error().decode())
+            if queued and lib.b200_wait(h):
+                raise RuntimeError(lib.b200_last_error().decode())
         e2e_steps = max(3, min(args.steps, 10))
-        for _ in range(2):
-            e2e_pass()
-        barrier()
         ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ea.record(stream)
-        for _ in range(e2e_steps):
-            e2e_pass()
-        eb.record(stream)
-        barrier()
-        e2e_ms = ea.elapsed_time(eb) / e2e_steps
+        e2e_modes = {}
+        for queued in (False, True):
+            for _ in range(2):
+                e2e_pass(queued)
+            barrier()
+            ea.record(stream)
+            for _ in range(e2e_steps):
+                e2e_pass(queued)
+            eb.record(stream)
+            barrier()
+            e2e_modes[queued] = ea.elapsed_time(eb) / e2e_steps
+        e2e_ms, e2e_sync_ms = e2e_modes[True], e2e_modes[False]
+        if rank == 0 and args.check:
+            # the queued results against the device-resident pass
+            for w in waves:
+                launch(w)
+            torch.cuda.synchronize()
+            for w in waves:
+                assert torch.equal(w["hOut"].view(torch.int32), w["dOut"].cpu().view(torch.int32)), "queued host-buffer wave differs from the device wave"
         # context for the e2e number: what a plain pinned-memory copy achieves on this box (the e2e floor is h2d_bytes / this)
         big = max(waves, key=lambda w_: w_["n"])
         torch.cuda.synchronize()
@@ -445,7 +462,9 @@ def run_b200(args):
             line["e2e"] = {"value": all_rays_step / (e2e_ms_max * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d,
                            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms_max, "pcie_h2d_gbs_measured": pcie_h2d,
                            "pcie_floor_ms": h2d / (pcie_h2d * 1e9) * 1e3,
-                           "api": "b200_trace_closest / b200_trace_any with pinned host buffers"}
+                           "api": "b200_trace_closest_async / b200_trace_any_async + one b200_wait per step, pinned host buffers (the six waves of a step queued back to back)",
+                           "sync_calls": {"ms_per_step": e2e_sync_ms, "value": (all_rays_step / world) / (e2e_sync_ms * 1e-3) / 1e6,
+                                          "note": "rank 0, b200_trace_closest / b200_trace_any: every wave synchronises before the next one is submitted"}}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_pass(args, verts, args.cpu_sample, steps=2, warmup=1)
             line["cpu_baseline"] = {"value": r["value"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],

@@ -67,6 +67,14 @@ B200_API int b200_setting( b200_core* c, const char* name, float value );
 /* host buffers; H2D + kernel + D2H + synchronise inside the call */
 B200_API int b200_trace_closest( b200_core* c, const float* O4, const float* D4, int n, float* hits );
 B200_API int b200_trace_any( b200_core* c, const float* O4, const float* D4, int n, uint32_t* occludedBits );
+/* queued variants: the call returns once the wave's copies and kernels are enqueued; b200_wait returns when every queued wave has
+ * delivered its results.  Waves queued back to back overlap (upload of wave k+1 while wave k is traced and downloaded; up to
+ * three in flight, then a wave waits for the staging slot of the wave three before it).  Host buffers: pinned (b200_host_alloc),
+ * valid and untouched until b200_wait.  The shape of an OptiX Prime query with RTP_QUERY_HINT_ASYNC + rtpQueryFinish (the
+ * reference issues its Prime queries synchronously, lib/RenderCore_OptixPrime_B/rendercore.cpp:528,562,587). */
+B200_API int b200_trace_closest_async( b200_core* c, const float* O4, const float* D4, int n, float* hits );
+B200_API int b200_trace_any_async( b200_core* c, const float* O4, const float* D4, int n, uint32_t* occludedBits );
+B200_API int b200_wait( b200_core* c );
 /* device buffers (cudaMalloc'ed by anyone in this process); asynchronous on the core's stream.
  * occludedBits must hold (n+31)/32 words; it is cleared by the call. */
 B200_API int b200_trace_closest_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dHits );

@@ -27,6 +27,7 @@ C_ABI_SYMBOLS = [
     "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors", "b200_set_material_table", "b200_set_textures",
     "b200_disney_probe", "b200_set_blue_noise",
     "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
+    "b200_trace_closest_async", "b200_trace_any_async", "b200_wait",
 ]
 
 
@@ -92,6 +93,7 @@ def load_library() -> C.CDLL:
         "b200_disney_probe": ([vp, ip, ip, vp, vp], ip), "b200_set_blue_noise": ([vp, vp, ip], ip),
         "b200_set_accumulator_buffer": ([vp, vp], ip), "b200_finalize": ([vp, C.c_uint32], ip),
         "b200_trace_connect_device": ([vp, vp, vp, ip, vp, vp], ip),
+        "b200_trace_closest_async": ([vp, vp, vp, ip, vp], ip), "b200_trace_any_async": ([vp, vp, vp, ip, vp], ip), "b200_wait": ([vp], ip),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, name)
@@ -300,6 +302,37 @@ class RenderCoreB200:
         bits = np.zeros((n + 31) // 32, np.uint32)
         self._chk(self.lib.b200_trace_any(self.h, O4.ctypes.data, D4.ctypes.data, n, bits.ctypes.data))
         return np.unpackbits(bits.view(np.uint8), bitorder="little")[:n].astype(bool)
+
+    def TraceQueued(self, waves):
+        """Queue several host-buffer waves back to back (b200_trace_*_async) and wait for all of them (b200_wait).
+        waves: [(kind, O4, D4)] with kind "closest" | "any"; returns the result arrays in order.  Buffers are staged in pinned memory."""
+        out, keep = [], []
+        for kind, O4, D4 in waves:
+            O4 = np.ascontiguousarray(O4, np.float32).reshape(-1, 4)
+            D4 = np.ascontiguousarray(D4, np.float32).reshape(-1, 4)
+            n = O4.shape[0]
+            pin = []
+            for a in (O4, D4):
+                p = self.lib.b200_host_alloc(max(a.nbytes, 16))
+                if not p:
+                    raise RuntimeError("b200_host_alloc failed")
+                C.memmove(p, a.ctypes.data, a.nbytes)
+                pin.append(p)
+            nbytes = n * 16 if kind == "closest" else ((n + 31) // 32) * 4
+            pr = self.lib.b200_host_alloc(max(nbytes, 16))
+            fn = self.lib.b200_trace_closest_async if kind == "closest" else self.lib.b200_trace_any_async
+            keep.append((kind, n, nbytes, pin, pr))
+            self._chk(fn(self.h, pin[0], pin[1], n, pr))
+        self._chk(self.lib.b200_wait(self.h))
+        for kind, n, nbytes, pin, pr in keep:
+            raw = np.frombuffer(C.string_at(pr, nbytes), np.uint8).copy()
+            if kind == "closest":
+                out.append(raw.view(np.float32).reshape(n, 4))
+            else:
+                out.append(np.unpackbits(raw, bitorder="little")[:n].astype(bool))
+            for p in pin + [pr]:
+                self.lib.b200_host_free(p)
+        return out
 
     def TraceClosestDevice(self, dO4: int, dD4: int, n: int, dHits: int):
         self._chk(self.lib.b200_trace_closest_device(self.h, dO4, dD4, n, dHits))

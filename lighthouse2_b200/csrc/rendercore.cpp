@@ -116,12 +116,13 @@ RenderCore::~RenderCore()
 	cudaSetDevice( device );
 	cudaDeviceSynchronize();
 	DestroyWavefront( wf );
-	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &vnormPool, &instShadePool, &rayO, &rayD, &hitBuf, &bitBuf, &vertStage, &nodeLo, &nodeHi,
+	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &vnormPool, &instShadePool, &vertStage, &nodeLo, &nodeHi,
 		&stepNodes, &stepTris };
 	for (DeviceBuffer* b : all) b->release();
+	for (int i = 0; i < WAVE_SLOTS; i++) rayO[i].release(), rayD[i].release(), hitBuf[i].release(), bitBuf[i].release();
 	if (evA) cudaEventDestroy( evA );
 	if (evB) cudaEventDestroy( evB );
-	if (copyIn) { cudaStreamDestroy( copyIn ), cudaStreamDestroy( copyOut ), cudaStreamDestroy( stream2 ); for (cudaEvent_t ev : chunkEv) if (ev) cudaEventDestroy( ev ); }
+	if (copyIn) { cudaStreamDestroy( copyIn ), cudaStreamDestroy( copyOut ), cudaStreamDestroy( stream2 ); for (cudaEvent_t ev : chunkEv) if (ev) cudaEventDestroy( ev ); for (cudaEvent_t ev : slotDone) if (ev) cudaEventDestroy( ev ); }
 }
 
 int RenderCore::fail( const char* what, cudaError_t e )
@@ -588,13 +589,16 @@ static int chunkSchedule( int n, int* offsets, int maxChunks, int mode, int part
 	return count;
 }
 
-int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit )
+int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit, bool async )
 {
 	if (n < 0) return fail( "trace: negative ray count" );
 	if (n == 0) return ensureToplevel();
 	if (ensureToplevel()) return 1;
 	cudaError_t e;
 	const size_t rb = (size_t)n * 16, bb = (size_t)((n + 31) / 32) * 4;
+	// staging slot of this wave (see rendercore.h); growing a buffer frees the old one, which waits for the device
+	const int slot = (int)(waveSeq++ % WAVE_SLOTS);
+	DeviceBuffer &rayO = this->rayO[slot], &rayD = this->rayD[slot], &hitBuf = this->hitBuf[slot], &bitBuf = this->bitBuf[slot];
 	DeviceBuffer& outBuf = anyHit ? bitBuf : hitBuf;
 	if ((e = rayO.reserve( rb, false, stream )) != cudaSuccess || (e = rayD.reserve( rb, false, stream )) != cudaSuccess ||
 		(e = outBuf.reserve( anyHit ? bb : rb, false, stream )) != cudaSuccess) return fail( "ray buffers", e );
@@ -605,6 +609,7 @@ int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bo
 		if ((e = cudaStreamCreateWithFlags( &copyIn, cudaStreamNonBlocking )) != cudaSuccess || (e = cudaStreamCreateWithFlags( &copyOut, cudaStreamNonBlocking )) != cudaSuccess ||
 			(e = cudaStreamCreateWithFlags( &stream2, cudaStreamNonBlocking )) != cudaSuccess) return fail( "copy streams", e );
 		for (int i = 0; i < 2 * MAX_CHUNKS + 1; i++) if ((e = cudaEventCreateWithFlags( &chunkEv[i], cudaEventDisableTiming )) != cudaSuccess) return fail( "chunk events", e );
+		for (int i = 0; i < WAVE_SLOTS; i++) if ((e = cudaEventCreateWithFlags( &slotDone[i], cudaEventDisableTiming )) != cudaSuccess) return fail( "slot events", e );
 	}
 	// Small waves over pinned (page-locked) ray planes: the kernel itself fetches the rays over PCIe, no staging copy and no
 	// upload -> trace dependency.  (Measured: wins below ~0.5M rays; above, chunked DMA uploads overlap better.)
@@ -627,9 +632,11 @@ int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bo
 	static const bool traceChunks = getenv( "B200_TRACE_CHUNKS" ) != nullptr; // debugging aid: per-chunk timeline on stderr
 	static cudaEvent_t tev[4 * MAX_CHUNKS + 1];
 	if (traceChunks && !tev[0]) for (cudaEvent_t& t : tev) cudaEventCreate( &t );
-	// the uploads may start once everything queued on the core's stream so far is done (the staging buffers may still be read)
+	// the uploads may start once the wave that had this staging slot is done (its kernels may still read the planes); the first
+	// wave after other work on the core's stream also waits for that
 	cudaEventRecord( chunkEv[join], stream );
-	cudaStreamWaitEvent( copyIn, chunkEv[join], 0 );
+	if (slotUsed[slot]) cudaStreamWaitEvent( copyIn, slotDone[slot], 0 ), cudaStreamWaitEvent( stream, slotDone[slot], 0 );
+	else cudaStreamWaitEvent( copyIn, chunkEv[join], 0 );
 	cudaStreamWaitEvent( stream2, chunkEv[join], 0 );
 	if (traceChunks) cudaEventRecord( tev[4 * MAX_CHUNKS], stream );
 	for (int k = 0; k < nChunks; k++)
@@ -676,6 +683,9 @@ int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bo
 		if (traceChunks) cudaEventRecord( tev[4 * k + 3], copyOut );
 	}
 	if (nChunks > 1 && twoStreams) { cudaEventRecord( chunkEv[join], stream2 ); cudaStreamWaitEvent( stream, chunkEv[join], 0 ); }
+	cudaEventRecord( slotDone[slot], copyOut ); // the downloads wait for their kernels: everything of this wave is done by then
+	slotUsed[slot] = true;
+	if (async) return 0; // b200_wait collects the results
 	if ((e = cudaStreamSynchronize( copyOut )) != cudaSuccess) return fail( anyHit ? "shadow wave" : "extend wave", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( anyHit ? "shadow wave" : "extend wave", e );
 	cudaEventElapsedTime( &stats.lastTraceMs, evA, evB ); // device time of the LAST chunk's kernel
@@ -694,8 +704,24 @@ int RenderCore::hostWave( const float* O4, const float* D4, int n, void* out, bo
 }
 
 // host-buffer variants: H2D, wave, D2H, synchronise (the e2e path of bench.py)
-int RenderCore::TraceClosest( const float* O4, const float* D4, int n, float* hits ) { return hostWave( O4, D4, n, hits, false ); }
-int RenderCore::TraceAny( const float* O4, const float* D4, int n, uint32_t* bits ) { return hostWave( O4, D4, n, bits, true ); }
+int RenderCore::TraceClosest( const float* O4, const float* D4, int n, float* hits ) { return hostWave( O4, D4, n, hits, false, false ); }
+int RenderCore::TraceAny( const float* O4, const float* D4, int n, uint32_t* bits ) { return hostWave( O4, D4, n, bits, true, false ); }
+
+// Queued variants: the call returns once the wave's copies and kernels are enqueued; WaitWaves() returns when every queued wave
+// has delivered its results.  Waves queued back to back overlap: the upload of wave k+1 runs while wave k is traced and its
+// hits go down (the shape of an OptiX Prime query with RTP_QUERY_HINT_ASYNC + rtpQueryFinish; the reference's Prime core
+// issues its queries synchronously, lib/RenderCore_OptixPrime_B/rendercore.cpp:528,562,587).  The host buffers must stay
+// valid and untouched until WaitWaves(); pageable buffers make the copies synchronous, so pin them (b200_host_alloc).
+int RenderCore::TraceClosestAsync( const float* O4, const float* D4, int n, float* hits ) { return hostWave( O4, D4, n, hits, false, true ); }
+int RenderCore::TraceAnyAsync( const float* O4, const float* D4, int n, uint32_t* bits ) { return hostWave( O4, D4, n, bits, true, true ); }
+int RenderCore::WaitWaves()
+{
+	if (!copyOut) return 0;
+	cudaError_t e;
+	if ((e = cudaStreamSynchronize( copyOut )) != cudaSuccess || (e = cudaStreamSynchronize( stream2 )) != cudaSuccess || (e = cudaStreamSynchronize( stream )) != cudaSuccess)
+		return fail( "queued waves", e );
+	return 0;
+}
 
 int RenderCore::ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris )
 {

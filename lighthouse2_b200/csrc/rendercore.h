@@ -64,6 +64,9 @@ public:
 	// raw waves
 	int TraceClosest( const float* O4, const float* D4, int n, float* hits );
 	int TraceAny( const float* O4, const float* D4, int n, uint32_t* bits );
+	int TraceClosestAsync( const float* O4, const float* D4, int n, float* hits ); // queued: see rendercore.cpp
+	int TraceAnyAsync( const float* O4, const float* D4, int n, uint32_t* bits );
+	int WaitWaves();
 	int TraceClosestDevice( const void* dO4, const void* dD4, int n, void* dHits, const uint32_t* dCount = nullptr );
 	int TraceAnyDevice( const void* dO4, const void* dD4, int n, void* dBits, const uint32_t* dCount = nullptr );
 	int TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount = nullptr,
@@ -89,12 +92,18 @@ public:
 
 private:
 	int ensureToplevel();
-	int hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit );
+	int hostWave( const float* O4, const float* D4, int n, void* out, bool anyHit, bool async );
 	int buildOnDevice( int meshIdx, const float* vertexData, uint32_t T, const void* coreTris, double t0 );
 	int uploadVertexNormals( const MeshRec& m, const void* coreTris );
 	static constexpr int MAX_CHUNKS = 12;
 	cudaStream_t copyIn = nullptr, copyOut = nullptr, stream2 = nullptr;
 	cudaEvent_t chunkEv[2 * MAX_CHUNKS + 1] = {};
+	// staging slots of the host-buffer waves: a wave queued with the *_async calls takes the next slot, so that its upload can run
+	// while the previous wave is still being traced and downloaded; a slot is reused once the wave that had it is done
+	static constexpr int WAVE_SLOTS = 3;
+	cudaEvent_t slotDone[WAVE_SLOTS] = {};
+	bool slotUsed[WAVE_SLOTS] = {};
+	uint32_t waveSeq = 0;
 	bool initOk = false;
 	std::string error;
 	int device = 0;
@@ -105,7 +114,7 @@ private:
 	std::vector<InstanceHost> instances;
 	bool tlasDirty = true;
 	// scratch
-	DeviceBuffer rayO, rayD, hitBuf, bitBuf, vertStage, nodeLo, nodeHi, stepNodes, stepTris;
+	DeviceBuffer rayO[WAVE_SLOTS], rayD[WAVE_SLOTS], hitBuf[WAVE_SLOTS], bitBuf[WAVE_SLOTS], vertStage, nodeLo, nodeHi, stepNodes, stepTris;
 	bool countSteps = false, allowRefit = true, gpuBuild = false; // gpuBuild: new meshes get an LBVH built on the device (build.cu)
 	bool zeroCopy = true, twoStreams = true; int pinnedChunks = 1, zeroCopyBelow = 400000; // pinned host ray planes are fetched by the kernel itself (Setting zeroCopy / pinnedChunks)
 	int hostChunks = 4, hostChunkMode = 0; // chunk schedule of the host-buffer waves (Setting hostChunks / hostChunkMode)

@@ -87,6 +87,23 @@ template <int P> __device__ __forceinline__ void qpair( const uint32_t q, const 
 	f0 = __low2float( h ), f1 = __high2float( h );
 }
 
+#ifndef B200_POP_SELECT
+#define B200_POP_SELECT 0
+#endif
+#ifndef B200_WORLD_SMEM
+#define B200_WORLD_SMEM 1 // keep the world-space ray in shared memory for the way out of an instance instead of re-reading the ray planes
+#endif
+#ifndef B200_PREFETCH_TRIS_L1
+#define B200_PREFETCH_TRIS_L1 0
+#endif
+// m with its k highest set bits cleared (k < popc(m)).  A branch-free halving search and fns.b32 (45 SASS instructions) were
+// looked at: both have a longer dependent chain than this loop at the k <= 5 that is typical
+__device__ __forceinline__ uint32_t dropHighest( uint32_t m, uint32_t k )
+{
+	for (; k; k--) m &= ~(0x80000000u >> __clz( m ));
+	return m;
+}
+
 struct RayState {
 	float ox, oy, oz, dx, dy, dz;   // current-space ray (world in the TLAS, object inside an instance)
 	float ix, iy, iz;               // 1/d with zero components replaced by +-1e-18 (slab test only)
@@ -308,6 +325,9 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
 	__shared__ uint32_t sSlot[BLOCK_THREADS];        // flush slot of the winning pair, 0xffffffff = none
 	__shared__ float4 sWorld[BLOCK_THREADS];         // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
+#if B200_WORLD_SMEM
+	__shared__ float4 sWorldO[BLOCK_THREADS], sWorldD[BLOCK_THREADS];
+#endif
 	__shared__ uint2 sRing[WARPS_PER_BLOCK][RING_CAP]; // leaf records: (first triangle | owner lane << 27, 24-bit triangle mask)
 	uint2 lstack[STACK_LOCAL];
 	const uint32_t lane = threadIdx.x & 31, warpBase = threadIdx.x & ~31u;
@@ -367,8 +387,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		uint32_t owner = 0, prim = 0;
 		if (mine)
 		{
-			uint32_t m = ry;
-			for (uint32_t k = lane - rstart; k; k--) m &= ~(0x80000000u >> __clz( m )); // drop the k triangles before mine
+			const uint32_t m = dropHighest( ry, lane - rstart ); // drop the k triangles before mine
 			const uint32_t bit = 31 - __clz( m );
 			owner = warpBase + (rx >> 27);
 			const float4* tp = tris + (size_t)((rx & 0x07ffffffu) + bit) * 3;
@@ -381,9 +400,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		const bool full = lane < nrec && incl <= take;
 		if (lane < nrec && incl > take && incl - cnt < take)
 		{
-			uint32_t m = rec.y;
-			for (uint32_t k = take - (incl - cnt); k; k--) m &= ~(0x80000000u >> __clz( m ));
-			ring[(qhead + lane) & (RING_CAP - 1)].y = m;
+			ring[(qhead + lane) & (RING_CAP - 1)].y = dropHighest( rec.y, take - (incl - cnt) );
 		}
 		qhead += __popc( __ballot_sync( 0xffffffffu, full ) );
 		pendingTris -= take;
@@ -432,6 +449,9 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					r.dx = D4.x, r.dy = D4.y, r.dz = D4.z, r.t = D4.w;
 					setupSlab( r );
 					sWorld[threadIdx.x] = make_float4( r.ix, r.iy, r.iz, __uint_as_float( r.octinv4 ) );
+#if B200_WORLD_SMEM
+					sWorldO[threadIdx.x] = O4, sWorldD[threadIdx.x] = D4;
+#endif
 					ngroup = make_uint2( a.tlasRoot, 0x80000000u ), tgroup = make_uint2( 0, 0 );
 					sp = 0, instBase = -1, curInst = NO_INSTANCE;
 					hitPrim = 0xffffffffu, hitInst = 0, hitBary = 0, nNodes = nTris = 0;
@@ -501,6 +521,13 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					{
 						lastQueued = qtail + __popc( m & lanemask_lt() );
 						ring[lastQueued & (RING_CAP - 1)] = make_uint2( tgroup.x | (lane << 27), tgroup.y );
+#if B200_PREFETCH_TRIS_L1
+						{
+							const float4* tp = tris + (size_t)(tgroup.x + (uint32_t)__ffs( tgroup.y ) - 1) * 3;
+							asm volatile( "prefetch.global.L1 [%0];" ::"l"( tp ) );
+							asm volatile( "prefetch.global.L1 [%0];" ::"l"( tp + 3 * (uint32_t)__popc( tgroup.y ) - 1 ) );
+						}
+#endif
 #if B200_PREFETCH_TRIS
 						{
 							const float4* tp = tris + (size_t)(tgroup.x + (uint32_t)__ffs( tgroup.y ) - 1) * 3;
@@ -528,7 +555,11 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					else if (!terminated)
 					{
 						// bottom level exhausted: back to the world-space ray (t is kept, as in bvh.cpp:612-619)
+#if B200_WORLD_SMEM
+						const float4 O4 = sWorldO[threadIdx.x], D4 = sWorldD[threadIdx.x];
+#else
 						const float4 O4 = __ldg( a.rayO + rayIdx ), D4 = __ldg( a.rayD + rayIdx );
+#endif
 						const float4 W = sWorld[threadIdx.x];
 						r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.dx = D4.x, r.dy = D4.y, r.dz = D4.z;
 						r.ix = W.x, r.iy = W.y, r.iz = W.z, r.octinv4 = __float_as_uint( W.w );
@@ -565,7 +596,13 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					else
 					{
 						const uint2 g = pop();
+#if B200_POP_SELECT
+						const bool isNode = g.y > 0x00ffffffu; // tgroup.y is 0 here
+						ngroup = make_uint2( isNode ? g.x : 0u, isNode ? g.y : 0u );
+						tgroup = make_uint2( isNode ? tgroup.x : g.x, isNode ? 0u : g.y );
+#else
 						if (g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
+#endif
 					}
 				}
 			}

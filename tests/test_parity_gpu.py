@@ -78,6 +78,28 @@ def test_any_hit_matches_closest(oracles):
     rc.Shutdown()
 
 
+def test_queued_waves_equal_the_synchronous_calls():
+    """b200_trace_*_async + b200_wait: seven waves queued back to back (more than the three staging slots, sizes on both sides of the
+    zero-copy and the chunking thresholds, closest and any-hit mixed) return what the synchronous calls return, bit for bit."""
+    case = cases.case_soup(n_tris=40_000, n_rays=1_300_000, seed=77)
+    O, D = case["rays"]
+    rc = cases.load_core(core.RenderCoreB200(0), case)
+    sizes = [1_300_000, 70_001, 450_000, 33, 600_000, 1_000_000, 0, 250_000]
+    kinds = ["closest", "any", "closest", "closest", "any", "closest", "closest", "any"]
+    waves, expect = [], []
+    for i, (n, kind) in enumerate(zip(sizes, kinds)):
+        lo = (i * 37_003) % (len(O) - n + 1)
+        O4, D4 = core.pack_rays(O[lo:lo + n], D[lo:lo + n], tmax=1e34 if kind == "closest" else 6.0)
+        waves.append((kind, O4, D4))
+        expect.append(rc.TraceClosest(O4, D4) if kind == "closest" else rc.TraceAny(O4, D4))
+    for _ in range(2):  # the second round reuses every slot
+        got = rc.TraceQueued(waves)
+        for kind, e, g in zip(kinds, expect, got):
+            assert e.shape == g.shape
+            assert np.array_equal(e.view(np.uint32), g.view(np.uint32)) if kind == "closest" else np.array_equal(e, g)
+    rc.Shutdown()
+
+
 def test_empty_mesh_zero_rays_and_misses():
     rc = core.RenderCoreB200(0)
     case = cases.case_empty()
