@@ -23,7 +23,9 @@
 #include <cuda_fp16.h>
 
 #ifndef B200_HALF_DECODE
-#define B200_HALF_DECODE 1 // node planes: two bytes per PRMT + HADD2.F32 (1) or one PRMT per byte (0); see qpair / qbyte
+#define B200_HALF_DECODE 1 // node planes: two bytes per PRMT + HADD2.F32 (1) or one PRMT per byte (0); see qpair / qbyte.  72 / 48 decode
+                            // instructions per node, and a 60-instruction mix of the two, all trace within 1 % of each other: the kernel is bound by
+                            // the dependent chain of a pass at 6 warps per scheduler, not by instruction issue
 #endif
 
 namespace b200 {
