@@ -379,7 +379,7 @@ def run_b200(args):
             rc.Setting("zeroCopyBelow", 400000); rc.Setting("zeroCopy", 1); rc.Setting("twoStreams", 1); rc.Setting("pinnedChunks", 1); rc.Setting("hostChunks", 4)
 
     # ---- the same scene through Render(): full wavefront frame (ray generation, shade, fused connect), tile-sharded over the
-    #      ranks, accumulator gathered with one NCCL all-reduce.  Reported beside the wave numbers, not as `value`.
+    #      ranks, accumulator gathered by the fused peer-memory pull + finalize kernel (NCCL all-reduce if the peers cannot be mapped).  Reported beside the wave numbers, not as `value`.
     frame = None
     if not args.no_frame:
         from lighthouse2_b200 import multigpu
@@ -414,7 +414,9 @@ def run_b200(args):
                  "mrays_s": fr.item() / (fv[0] * 1e-3) / 1e6, "gather_bytes": args.width * args.height * 16,
                  "rank0_stats": {k: st[k] for k in ("primaryRayCount", "traceTime0", "bounce1RayCount", "traceTime1", "deepRayCount", "traceTimeX",
                                                     "totalShadowRays", "shadowTraceTime", "shadeTime", "renderTime")},
-                 "note": "Render() + NCCL all-reduce of the float4 accumulator, 1 spp, tile-sharded; wall clock incl. host sync per frame"}
+                 "gather": sr.gather if world > 1 else "none",
+                 "note": "Render() + gather of the float4 accumulator (p2p = one kernel pulls the foreign tiles over NVLink peer memory and finalizes the frame; "
+                         "nccl = all-reduce + finalize), 1 spp, tile-sharded; wall clock incl. host sync per frame"}
 
     # ---- reduce over ranks: slowest rank's time, all ranks' rays ------------------------------------------------
     vec = torch.tensor([total_ms, e2e_ms or 0.0, ext_ms] + [cls_ms.get(c, 0.0) for c in ("primary", "shadow", "diffuse")], device=dev, dtype=torch.float64)

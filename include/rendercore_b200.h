@@ -120,6 +120,17 @@ B200_API int b200_set_textures( b200_core* c, const void* coreTexDescs, int coun
  * NULL = the core's own.  After the gather, b200_finalize( total samples ) rebuilds the frame from it. */
 B200_API int b200_set_accumulator_buffer( b200_core* c, void* dAccumulator );
 B200_API int b200_finalize( b200_core* c, uint32_t totalSamples );
+/* Multi-GPU gather over peer memory, for tile-sharded frames (Setting shardIndex / shardCount), one process per GPU of one box.
+ * b200_peer_handle (after b200_set_target, core-owned accumulator) returns 128 bytes: the CUDA IPC handles of this core's accumulator
+ * and of its arrival flags.  The host exchanges the blobs between the ranks (any transport) and gives every core the whole table with
+ * b200_open_peers (entry r = rank r's blob).  Per frame, after b200_render, b200_gather_finalize replaces all-reduce + b200_finalize:
+ * ONE kernel pulls every foreign tile out of its owner's memory over NVLink, stores it into the local accumulator and writes the
+ * finalized frame; the ranks meet on flags in peer memory before and after the pull (a missing peer is an error after ~2 s, not a hang).
+ * The reference has no multi-GPU path (lib/CUDA/shared_host_code/cudatools.h:62-87 picks one device). */
+B200_API int b200_peer_handle( b200_core* c, void* out128 );
+B200_API int b200_open_peers( b200_core* c, const void* handles, int world, int rank );
+B200_API int b200_close_peers( b200_core* c );
+B200_API int b200_gather_finalize( b200_core* c, uint32_t totalSamples );
 /* view: ViewPyramid (68 bytes, common_classes.h:362-385).  converge: 0 = Converge, 1 = Restart */
 B200_API int b200_render( b200_core* c, const void* viewPyramid, int converge );
 /* accumulator float4[w*h] (sum over samples; w = sample count) and the normalised RGBA32F frame */

@@ -28,6 +28,7 @@ C_ABI_SYMBOLS = [
     "b200_disney_probe", "b200_set_blue_noise",
     "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
     "b200_trace_closest_async", "b200_trace_any_async", "b200_wait",
+    "b200_peer_handle", "b200_open_peers", "b200_close_peers", "b200_gather_finalize",
 ]
 
 
@@ -94,6 +95,8 @@ def load_library() -> C.CDLL:
         "b200_set_accumulator_buffer": ([vp, vp], ip), "b200_finalize": ([vp, C.c_uint32], ip),
         "b200_trace_connect_device": ([vp, vp, vp, ip, vp, vp], ip),
         "b200_trace_closest_async": ([vp, vp, vp, ip, vp], ip), "b200_trace_any_async": ([vp, vp, vp, ip, vp], ip), "b200_wait": ([vp], ip),
+        "b200_peer_handle": ([vp, vp], ip), "b200_open_peers": ([vp, vp, ip, ip], ip), "b200_close_peers": ([vp], ip),
+        "b200_gather_finalize": ([vp, C.c_uint32], ip),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, name)
@@ -427,6 +430,22 @@ class RenderCoreB200:
 
     def Finalize(self, total_samples: int):
         self._chk(self.lib.b200_finalize(self.h, total_samples))
+
+    # -- multi-GPU gather over peer memory (b200_peer_handle / b200_open_peers / b200_gather_finalize) --------
+    def PeerHandle(self) -> bytes:
+        buf = C.create_string_buffer(128)
+        self._chk(self.lib.b200_peer_handle(self.h, buf))
+        return buf.raw
+
+    def OpenPeers(self, table: bytes, world: int, rank: int):
+        assert len(table) == 128 * world
+        self._chk(self.lib.b200_open_peers(self.h, table, world, rank))
+
+    def ClosePeers(self):
+        self._chk(self.lib.b200_close_peers(self.h))
+
+    def GatherFinalize(self, total_samples: int):
+        self._chk(self.lib.b200_gather_finalize(self.h, total_samples))
 
     def TraceConnectDevice(self, dO4: int, dD4: int, n: int, dE4: int, dAcc: int):
         self._chk(self.lib.b200_trace_connect_device(self.h, dO4, dD4, n, dE4, dAcc))

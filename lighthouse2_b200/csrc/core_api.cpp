@@ -66,6 +66,10 @@ int b200_set_textures( b200_core* c, const void* coreTexDescs, int count ) { FOR
 int b200_set_blue_noise( b200_core* c, const uint32_t* words, int count ) { FORWARD( c, SetBlueNoise( words, count ) ) }
 int b200_disney_probe( b200_core* c, int mode, int n, const float* in28, float* out8 ) { FORWARD( c, DisneyProbe( mode, n, in28, out8 ) ) }
 int b200_set_accumulator_buffer( b200_core* c, void* dAcc ) { FORWARD( c, SetAccumulatorBuffer( dAcc ) ) }
+int b200_peer_handle( b200_core* c, void* out128 ) { FORWARD( c, PeerHandle( out128 ) ) }
+int b200_open_peers( b200_core* c, const void* handles, int world, int rank ) { FORWARD( c, OpenPeers( handles, world, rank ) ) }
+int b200_close_peers( b200_core* c ) { FORWARD( c, ClosePeers() ) }
+int b200_gather_finalize( b200_core* c, uint32_t totalSamples ) { FORWARD( c, GatherFinalize( totalSamples ) ) }
 int b200_finalize( b200_core* c, uint32_t totalSamples ) { FORWARD( c, Finalize( totalSamples ) ) }
 int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, int n, const void* dE4, void* dAcc ) { FORWARD( c, TraceConnectDevice( dO4, dD4, n, dE4, dAcc ) ) }
 int b200_render( b200_core* c, const void* view, int converge ) { FORWARD( c, Render( view, converge ) ) }

@@ -54,6 +54,10 @@ public:
 	int SetMaterialTable( const float* props16, int count );  // 16 floats per material, see wavefront.cu
 	int SetTextures( const void* coreTexDescs, int count );   // CoreTexDesc[count], host layout, 40 B each; ARGB32 maps are sampled
 	int SetAccumulatorBuffer( void* devicePtr );              // caller-owned float4[w*h] accumulator (multi-GPU gathers), null = own
+	int PeerHandle( void* out128 );                           // multi-GPU gather over peer memory: see wavefront.cu
+	int OpenPeers( const void* handles, int world, int rank );
+	int ClosePeers();
+	int GatherFinalize( uint32_t totalSamples );
 	int Finalize( uint32_t totalSamples );                    // frame = accumulator / totalSamples (after a gather)
 	int Render( const void* viewPyramid, int converge );
 	int ReadAccumulator( float* dst );

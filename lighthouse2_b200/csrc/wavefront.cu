@@ -812,6 +812,63 @@ __global__ void finalizeKernel( const float4* __restrict__ accumulator, float4* 
 	frame[i] = make_float4( a.x * scale, a.y * scale, a.z * scale, 1.0f );
 }
 
+
+// ---- multi-GPU gather over peer memory (tile-sharded frames) -----------------------------------------------------------------
+// Each rank renders its interleaved tiles into ITS OWN accumulator; the other ranks' accumulators are mapped into this process
+// (cudaIpcOpenMemHandle: NVLink peer access).  One kernel per frame then pulls every foreign tile straight out of its owner's
+// memory, stores it into the local accumulator and writes the finalized frame in the same pass: gather + finalize fused, each
+// pixel crosses NVLink once ((G-1)/G of the image per GPU; the all-reduce it replaces moves twice that and needs a separate
+// finalize launch).  Ranks meet before and after the pull on flags in peer memory.
+constexpr int MAX_PEERS = 16;
+struct PeerTable {
+	float4* acc[MAX_PEERS];      // acc[r] = rank r's accumulator (own rank: the local pointer)
+	uint32_t* flags[MAX_PEERS];  // flags[r] = rank r's arrival words, one per sender
+};
+
+// arrival: tell every rank that `rank` has reached `epoch`, then wait until every rank has told us.  One block, one thread per
+// rank.  The stores are system-scope releases after a system fence, so what earlier kernels of this stream wrote (the
+// accumulator) is visible to a peer that has seen the flag.  A peer that never arrives makes the wait give up after ~2 s and
+// raise *timeout, instead of hanging the device.
+__global__ void peerBarrierKernel( const PeerTable peers, const int world, const int rank, const uint32_t epoch, uint32_t* timeout )
+{
+	const int t = threadIdx.x;
+	if (t >= world) return;
+	__threadfence_system();
+	asm volatile( "st.release.sys.global.u32 [%0], %1;" ::"l"( peers.flags[t] + rank ), "r"( epoch ) : "memory" );
+	const uint32_t* mine = peers.flags[rank] + t;
+	const long long t0 = clock64();
+	while (true)
+	{
+		uint32_t v;
+		asm volatile( "ld.acquire.sys.global.u32 %0, [%1];" : "=r"( v ) : "l"( mine ) : "memory" );
+		if ((int32_t)(v - epoch) >= 0) break;
+		if (clock64() - t0 > 4000000000ll) { atomicExch( timeout, 1u ); break; }
+		__nanosleep( 200 );
+	}
+}
+
+__global__ void gatherFinalizeKernel( const PeerTable peers, const int world, const int rank, float4* __restrict__ frame, const uint32_t width,
+	const uint32_t height, const uint32_t tilesX, const float scale )
+{
+	const uint32_t pixels = width * height;
+	float4* const own = peers.acc[rank];
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < pixels; i += gridDim.x * blockDim.x)
+	{
+		const uint32_t x = i % width, y = i / width;
+		const uint32_t owner = ((y / TILE_H) * tilesX + x / TILE_W) % (uint32_t)world; // as generateEyeRaysKernel deals the tiles
+		float4 a;
+		if (owner == (uint32_t)rank) a = own[i];
+		else
+		{
+			// a 32-pixel tile row is 512 contiguous bytes in the owner's memory: full NVLink packets
+			const float4* src = peers.acc[owner] + i;
+			asm volatile( "ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"( a.x ), "=f"( a.y ), "=f"( a.z ), "=f"( a.w ) : "l"( src ) : "memory" );
+			own[i] = a;
+		}
+		frame[i] = make_float4( a.x * scale, a.y * scale, a.z * scale, 1.0f );
+	}
+}
+
 } // namespace
 
 struct WavefrontState {
@@ -837,10 +894,23 @@ struct WavefrontState {
 	cudaEvent_t shadeDone[MAX_PATH_LENGTH + 1] = {}, connectDone[MAX_PATH_LENGTH + 1] = {};
 	int overlapConnect = 1;
 	float4* accumulator() { return accumExternal ? accumExternal : (float4*)accumOwn.ptr; }
+	// peer-memory gather (OpenPeers): the other ranks' accumulators and arrival flags, mapped through CUDA IPC
+	PeerTable peers{};
+	int peerWorld = 0, peerRank = 0;
+	uint32_t peerEpoch = 0;
+	void* peerMapped[2 * MAX_PEERS] = {};
+	DeviceBuffer peerFlags; // MAX_PEERS arrival words + 1 timeout word, written by the peers
+	void closePeers()
+	{
+		for (void*& p : peerMapped) if (p) { cudaIpcCloseMemHandle( p ); p = nullptr; }
+		peerWorld = 0;
+	}
 	~WavefrontState()
 	{
 		DeviceBuffer* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &state[0], &state[1], &info[0], &info[1], &hits, &conO, &conD, &conE, &counters,
 			&accumOwn, &frame, &materials, &lights, &skyImage, &texels, &blueNoise };
+		closePeers();
+		peerFlags.release();
 		for (DeviceBuffer* b : all) b->release();
 		for (cudaEvent_t e : ev) if (e) cudaEventDestroy( e );
 		for (cudaEvent_t e : shadeDone) if (e) cudaEventDestroy( e );
@@ -1285,6 +1355,83 @@ int RenderCore::Finalize( uint32_t totalSamples )
 	stats.kernelLaunches++;
 	cudaError_t e = cudaStreamSynchronize( stream );
 	return e == cudaSuccess ? 0 : fail( "Finalize", e );
+}
+
+// ---- peer-memory gather: PeerHandle -> (exchange the 128-byte blobs between the ranks) -> OpenPeers -> GatherFinalize per frame ----
+// out128: the CUDA IPC handle of this core's own accumulator, then the one of its arrival flags.  The accumulator must be the
+// core's own (cudaMalloc'ed) one and must not be reallocated afterwards: call after SetTarget.
+int RenderCore::PeerHandle( void* out128 )
+{
+	WavefrontState* w = wf;
+	if (!w || w->width == 0) return fail( "PeerHandle: SetTarget has not been called" );
+	if (w->accumExternal) return fail( "PeerHandle: the accumulator is caller-owned (b200_set_accumulator_buffer); peers map the core's own one" );
+	if (!out128) return fail( "PeerHandle: null output" );
+	cudaError_t e;
+	if ((e = w->peerFlags.reserve( (MAX_PEERS + 1) * 4, false, stream )) != cudaSuccess) return fail( "peer flags", e );
+	if ((e = cudaMemsetAsync( w->peerFlags.ptr, 0, (MAX_PEERS + 1) * 4, stream )) != cudaSuccess) return fail( "peer flags", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "peer flags", e );
+	w->peerEpoch = 0;
+	cudaIpcMemHandle_t h[2];
+	static_assert( sizeof( cudaIpcMemHandle_t ) == 64, "IPC handle size" );
+	if ((e = cudaIpcGetMemHandle( &h[0], w->accumOwn.ptr )) != cudaSuccess) return fail( "cudaIpcGetMemHandle(accumulator)", e );
+	if ((e = cudaIpcGetMemHandle( &h[1], w->peerFlags.ptr )) != cudaSuccess) return fail( "cudaIpcGetMemHandle(flags)", e );
+	memcpy( out128, h, 128 );
+	return 0;
+}
+
+// handles: world x 128 bytes, entry r = what rank r's PeerHandle returned (entry `rank` is not opened: it is this core)
+int RenderCore::OpenPeers( const void* handles, int world, int rank )
+{
+	WavefrontState* w = wf;
+	if (!w || w->width == 0 || !w->peerFlags.ptr) return fail( "OpenPeers: call PeerHandle first" );
+	if (!handles || world < 1 || world > MAX_PEERS || rank < 0 || rank >= world) return fail( "OpenPeers: bad arguments" );
+	w->closePeers();
+	for (int r = 0; r < world; r++)
+	{
+		if (r == rank) { w->peers.acc[r] = (float4*)w->accumOwn.ptr, w->peers.flags[r] = (uint32_t*)w->peerFlags.ptr; continue; }
+		cudaIpcMemHandle_t h[2];
+		memcpy( h, (const char*)handles + (size_t)r * 128, 128 );
+		for (int k = 0; k < 2; k++)
+		{
+			void* p = nullptr;
+			cudaError_t e = cudaIpcOpenMemHandle( &p, h[k], cudaIpcMemLazyEnablePeerAccess );
+			if (e != cudaSuccess) { w->closePeers(); return fail( "cudaIpcOpenMemHandle", e ); }
+			w->peerMapped[2 * r + k] = p;
+		}
+		w->peers.acc[r] = (float4*)w->peerMapped[2 * r], w->peers.flags[r] = (uint32_t*)w->peerMapped[2 * r + 1];
+	}
+	w->peerWorld = world, w->peerRank = rank;
+	return 0;
+}
+
+int RenderCore::ClosePeers()
+{
+	if (wf) { cudaStreamSynchronize( stream ); wf->closePeers(); }
+	return 0;
+}
+
+// One frame's gather: arrive (everyone has rendered), pull + finalize, arrive again (everyone has pulled: the accumulators may
+// be written again).  After it the local accumulator holds the whole image, like after the all-reduce it replaces.
+int RenderCore::GatherFinalize( uint32_t totalSamples )
+{
+	WavefrontState* w = wf;
+	if (!w || w->width == 0) return fail( "GatherFinalize: SetTarget has not been called" );
+	if (w->peerWorld < 1) return fail( "GatherFinalize: OpenPeers has not been called" );
+	if (!totalSamples) return fail( "GatherFinalize: zero samples" );
+	if (w->shardCount != w->peerWorld || w->shardIndex != w->peerRank) return fail( "GatherFinalize: shardCount / shardIndex differ from the peer table" );
+	uint32_t* timeout = (uint32_t*)w->peerFlags.ptr + MAX_PEERS;
+	const uint32_t tilesX = ((uint32_t)w->width + TILE_W - 1) / TILE_W;
+	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout );
+	gatherFinalizeKernel<<<smCount * 8, 256, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, (float4*)w->frame.ptr, (uint32_t)w->width, (uint32_t)w->height, tilesX,
+		1.0f / (float)totalSamples );
+	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout );
+	stats.kernelLaunches += 3;
+	uint32_t timedOut = 0;
+	cudaError_t e = cudaMemcpyAsync( &timedOut, timeout, 4, cudaMemcpyDeviceToHost, stream );
+	if (e == cudaSuccess) e = cudaStreamSynchronize( stream );
+	if (e != cudaSuccess) return fail( "GatherFinalize", e );
+	if (timedOut) return fail( "GatherFinalize: a peer did not arrive within the time limit" );
+	return 0;
 }
 
 int RenderCore::ReadAccumulator( float* dst )

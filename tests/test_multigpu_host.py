@@ -58,6 +58,12 @@ def _worker(rank, world, port, w, h, out):
     n = torch.tensor([100.0 * (rank + 1)], dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dist.all_reduce(n, op=dist.ReduceOp.SUM)
+    # the peer-handle table of the peer-memory gather: entry r = rank r's 128-byte blob, on every rank; one failing rank
+    # sends every rank down the NCCL path
+    blob = bytes([rank * 16 + (i % 16) for i in range(128)])
+    table = multigpu.exchange_peer_handles(blob, world)
+    ok = ok and len(table) == 128 * world and all(table[r * 128:(r + 1) * 128] == bytes([r * 16 + (i % 16) for i in range(128)]) for r in range(world))
+    ok = ok and multigpu.all_ranks_ok(True) and not multigpu.all_ranks_ok(rank != 1)
     out[rank] = (ok, float(t), float(n))
     dist.barrier()
     dist.destroy_process_group()

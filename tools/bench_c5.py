@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """BASELINE.json configs[4]: 3840x2160, 16 spp full wavefront frame on N GPUs (torchrun, one process per GPU), C2 scene replicated,
-interleaved-tile sharding, accumulator gathered over NVLink with one NCCL all-reduce.  Rank 0 prints one JSON line.
+interleaved-tile sharding, accumulator gathered over NVLink by the fused peer-memory pull + finalize kernel (--gather nccl: one NCCL all-reduce).  Rank 0 prints one JSON line.
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29577 tools/bench_c5.py [--spp 16] [--frames 3]"""
 import json
 import os
@@ -27,7 +27,8 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     w, h, spp, frames = arg("--width", 3840), arg("--height", 2160), arg("--spp", 16), arg("--frames", 3)
-    sr = multigpu.ShardedRenderer(rank, world, local, mode="tiles")
+    gather = sys.argv[sys.argv.index("--gather") + 1] if "--gather" in sys.argv else "auto"
+    sr = multigpu.ShardedRenderer(rank, world, local, mode="tiles", gather=gather)
     sr.SetGeometry(0, scenes.sphere_field(1_000_000)); sr.SetInstance(0, 0); sr.SetInstance(1, -1); sr.UpdateToplevel()
     sr.SetTarget(w, h, spp)
     sr.SetPointLight(scenes.C2_LIGHT, (4000.0, 4000.0, 3600.0)); sr.SetSky((0.4, 0.5, 0.7)); sr.Setting("maxPathLength", 5); sr.Setting("russianRoulette", 0)
@@ -54,7 +55,9 @@ def main():
         print(json.dumps({"config": f"C5 {w}x{h} x {spp} spp, C2 scene replicated, {world} GPUs tile-sharded", "n_gpus": world, "frames": frames,
                           "ms_per_frame_wall": v[0], "render_ms_max_rank": v[1], "gather_ms": v[2], "rays_per_frame": n.item(),
                           "mrays_s_aggregate": n.item() / (v[0] * 1e-3) / 1e6, "gather_bytes": gbytes,
-                          "gather_busbw_gbs": (2 * (world - 1) / world * gbytes / (v[2] * 1e-3) / 1e9) if world > 1 and v[2] > 0 else None,
+                          "gather": sr.gather if world > 1 else "none",
+                          # bytes each GPU moves over NVLink: the pull reads (G-1)/G of the image once, the all-reduce moves twice that
+                          "gather_busbw_gbs": ((1 if sr.gather == "p2p" else 2) * (world - 1) / world * gbytes / (v[2] * 1e-3) / 1e9) if world > 1 and v[2] > 0 else None,
                           "frame_mean": float(torch.from_numpy(sr.ReadFrame())[..., :3].mean())}), flush=True)
     sr.Shutdown()
     if world > 1:
