@@ -33,7 +33,10 @@ namespace b200 {
 namespace {
 
 constexpr int BLOCK_THREADS = 128;
-constexpr int STACK_SMEM = 8;        // per-lane stack entries kept in shared memory
+#ifndef B200_STACK_SMEM
+#define B200_STACK_SMEM 8
+#endif
+constexpr int STACK_SMEM = B200_STACK_SMEM; // per-lane stack entries kept in shared memory
 constexpr int STACK_LOCAL = 40;      // overflow entries in local memory
 constexpr float REF_EPSILON = 0.0001f; // lib/RenderSystem/common_settings.h:45
 constexpr uint32_t NO_INSTANCE = 0xffffffffu;
@@ -625,9 +628,13 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 
 namespace {
 int gExtendBlocksPerSM = 0, gShadowBlocksPerSM = 0;
+#ifndef B200_SMEM_CARVEOUT
+#define B200_SMEM_CARVEOUT -1 // percent of the 228 KB kept as shared memory (-1: the driver's choice); the rest of the 256 KB is L1
+#endif
 template <typename K> int blocksPerSM( K kernel )
 {
 	int n = 0;
+	if (B200_SMEM_CARVEOUT >= 0) cudaFuncSetAttribute( kernel, cudaFuncAttributePreferredSharedMemoryCarveout, B200_SMEM_CARVEOUT );
 	cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, kernel, BLOCK_THREADS, 0 );
 	return n > 0 ? n : 1;
 }
