@@ -392,8 +392,15 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		uint32_t owner = 0, prim = 0;
 		if (mine)
 		{
-			const uint32_t m = dropHighest( ry, lane - rstart ); // drop the k triangles before mine
-			const uint32_t bit = 31 - __clz( m );
+			// my triangle is the k-th highest set bit of the record's mask, k = lane - rstart.  Walk to it from the nearer end, in
+			// a form where one step is `m &= m - 1` (two dependent instructions): from the top on the bit-reversed mask, else from
+			// the bottom.  Records of up to three triangles need at most one step; the loop runs for the warp's largest count.
+			const uint32_t k = lane - rstart, cnt = __popc( ry );
+			const bool fromTop = 2 * k < cnt;
+			uint32_t m = fromTop ? __brev( ry ) : ry;
+			for (uint32_t j = fromTop ? k : cnt - 1 - k; j; j--) m &= m - 1;
+			const uint32_t low = __ffs( m ) - 1;
+			const uint32_t bit = fromTop ? 31 - low : low;
 			owner = warpBase + (rx >> 27);
 			const float4* tp = tris + (size_t)((rx & 0x07ffffffu) + bit) * 3;
 			const float4 v0 = __ldg( tp ), e1 = __ldg( tp + 1 ), e2 = __ldg( tp + 2 );
