@@ -7,7 +7,7 @@ for v in "$@"; do
 import json
 try:
     d=json.loads(open("gpurun_out/ab_$v.json").read().strip().splitlines()[-1])
-    print("$v", "total %.0f"%d["value"], {k:round(x["mrays_s"]) for k,x in d["rays"].items()}, "check", d.get("check"))
+    print("$v", "total %.0f"%d["value"], {k:round(x["mrays_s"]) for k,x in d["rays"].items()}, "build_s", d["config"]["bvh_build_s"], "nodes", d["config"]["wide_nodes"], "mismatches", sum((d.get("check") or {}).values()))
 except Exception as e: print("$v", "FAILED", e)
 PY
 done
