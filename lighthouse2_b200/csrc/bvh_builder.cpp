@@ -23,7 +23,12 @@ struct Node2 {
 	Aabb b;
 	uint32_t left, right;   // children (inner) ...
 	uint32_t first, count;  // ... or range in the ref array (leaf: count > 0)
+	uint32_t span;          // primitives below this node (its range in the ref array starts at `first` for inner nodes too)
 };
+
+#ifndef B200_DP_LEAVES
+#define B200_DP_LEAVES 1 // 1: the binary tree is split down to single primitives and the collapse decides which subtrees of <= maxLeaf primitives become leaves
+#endif
 
 #ifndef B200_SAH_BINS
 #define B200_SAH_BINS 64 // 16 -> 64 bins: +2 % rays/s on the 1 M-triangle scene (primary +5 %), build 0.36 -> 0.40 s; 128..512 bins and an exact sweep of small ranges (B200_SWEEP_BELOW) add nothing
@@ -52,7 +57,7 @@ struct Builder2 {
 		box.reset(), cbox.reset();
 		for (uint32_t i = first; i < first + count; i++) box.grow( refs[i].b ), cbox.grow( refs[i].c );
 		node.b = box;
-		node.first = first, node.count = count, node.left = node.right = 0;
+		node.first = first, node.count = count, node.span = count, node.left = node.right = 0;
 		if (count == 1) return;
 		// ---- binned SAH over the three axes of the centroid box
 		float bestCost = 3.0e38f;
@@ -129,7 +134,7 @@ struct Builder2 {
 		else if (bestAxis >= 0)
 		{
 			float splitCost = COST_TRAVERSE + COST_PRIM * bestCost / std::max( box.halfArea(), 1e-30f );
-			if ((int)count <= maxLeaf && (float)count * COST_PRIM <= splitCost) return; // cheaper as a leaf
+			if (!B200_DP_LEAVES && (int)count <= maxLeaf && (float)count * COST_PRIM <= splitCost) return; // cheaper as a leaf
 			float scale = (float)BINS / (cbox.hi[bestAxis] - cbox.lo[bestAxis]);
 			float lo = cbox.lo[bestAxis];
 			int a = bestAxis, s = bestSplit;
@@ -266,10 +271,11 @@ struct CollapsePlan {
 	std::vector<float> cost;      // [n*7 + (i-1)]
 	std::vector<uint8_t> choice;  // [n*7 + (i-1)], i >= 2: 0 = "use i-1 roots", k>0 = left gets k roots, right i-k
 	std::vector<uint8_t> split8;  // [n]: left's share of the 8 child slots when n becomes a wide node
+	std::vector<uint8_t> asLeaf;  // [n]: an inner BVH2 node of <= maxLeaf primitives that is cheaper as ONE leaf (B200_DP_LEAVES)
 
-	void compute( const std::vector<Node2>& N2, uint32_t used )
+	void compute( const std::vector<Node2>& N2, uint32_t used, int maxLeaf )
 	{
-		cost.assign( (size_t)used * 7, 0.f ), choice.assign( (size_t)used * 7, 0 ), split8.assign( used, 0 );
+		cost.assign( (size_t)used * 7, 0.f ), choice.assign( (size_t)used * 7, 0 ), split8.assign( used, 0 ), asLeaf.assign( used, 0 );
 		for (int64_t n = (int64_t)used - 1; n >= 0; n--)
 		{
 			const Node2& nd = N2[n];
@@ -290,6 +296,7 @@ struct CollapsePlan {
 			int k8 = 4;
 			c[0] = A * COST_TRAVERSE + distribute( 8, k8 );
 			split8[n] = (uint8_t)k8;
+			if (B200_DP_LEAVES && (int)nd.span <= maxLeaf && A * nd.span * COST_PRIM <= c[0]) c[0] = A * nd.span * COST_PRIM, asLeaf[n] = 1;
 			for (int i = 2; i <= 7; i++)
 			{
 				int k = 1;
@@ -344,7 +351,7 @@ void BuildWideBvh( const Aabb* primBoxes, uint32_t n, int maxLeafPrims, int thre
 	out.bounds = N2[0].b;
 
 	CollapsePlan plan;
-	plan.compute( N2, b2.nodeCount.load() );
+	plan.compute( N2, b2.nodeCount.load(), maxLeafPrims );
 
 	// breadth-first emission: queue entries = (wide node index, BVH2 node index)
 	struct Item { uint32_t wide, n2; };
@@ -363,7 +370,7 @@ void BuildWideBvh( const Aabb* primBoxes, uint32_t n, int maxLeafPrims, int thre
 			uint32_t child[8];
 			int cn = 0;
 			const Node2& root = N2[it.n2];
-			if (root.count > 0) child[cn++] = it.n2; // the whole tree is one leaf
+			if (root.count > 0 || plan.asLeaf[it.n2]) child[cn++] = it.n2; // the whole tree is one leaf
 			else
 			{
 				int k = plan.split8[it.n2];
@@ -387,17 +394,18 @@ void BuildWideBvh( const Aabb* primBoxes, uint32_t n, int maxLeafPrims, int thre
 				int i = childInSlot[s];
 				if (i < 0) continue;
 				const Node2& c = N2[child[i]];
-				desc[s].b = c.b, desc[s].inner = c.count == 0, desc[s].primCount = c.count, desc[s].primOffset = primOffset;
+				const bool inner = c.count == 0 && !plan.asLeaf[child[i]];
+				desc[s].b = c.b, desc[s].inner = inner, desc[s].primCount = inner ? 0 : c.span, desc[s].primOffset = primOffset;
 				slot[s] = &desc[s];
-				if (c.count == 0)
+				if (inner)
 				{
 					next.push_back( { childBase + innerCount, child[i] } );
 					innerCount++;
 				}
 				else
 				{
-					for (uint32_t k = 0; k < c.count; k++) out.primOrder.push_back( b2.refs[c.first + k].id );
-					primOffset += c.count;
+					for (uint32_t k = 0; k < c.span; k++) out.primOrder.push_back( b2.refs[c.first + k].id );
+					primOffset += c.span;
 				}
 			}
 			out.nodes.resize( out.nodes.size() + innerCount );
