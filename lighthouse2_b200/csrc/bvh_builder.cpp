@@ -61,6 +61,7 @@ struct Builder2 {
 		if (count == 1) return;
 		// ---- binned SAH over the three axes of the centroid box
 		float bestCost = 3.0e38f;
+		const int nb = count >= 256 ? BINS : (BINS < 16 ? BINS : 16); // the fine bins pay at the top of the tree, where the ranges are long
 		int bestAxis = -1, bestSplit = 0;
 		for (int a = 0; a < 3; a++)
 		{
@@ -68,12 +69,12 @@ struct Builder2 {
 			if (!(ext > 0)) continue;
 			Aabb binBox[BINS];
 			uint32_t binCount[BINS];
-			for (int k = 0; k < BINS; k++) binBox[k].reset(), binCount[k] = 0;
-			float scale = (float)BINS / ext;
+			for (int k = 0; k < nb; k++) binBox[k].reset(), binCount[k] = 0;
+			float scale = (float)nb / ext;
 			for (uint32_t i = first; i < first + count; i++)
 			{
 				int k = (int)((refs[i].c[a] - cbox.lo[a]) * scale);
-				k = k < 0 ? 0 : (k > BINS - 1 ? BINS - 1 : k);
+				k = k < 0 ? 0 : (k > nb - 1 ? nb - 1 : k);
 				binBox[k].grow( refs[i].b ), binCount[k]++;
 			}
 			float rightArea[BINS];
@@ -81,14 +82,14 @@ struct Builder2 {
 			Aabb acc;
 			acc.reset();
 			uint32_t n = 0;
-			for (int k = BINS - 1; k > 0; k--)
+			for (int k = nb - 1; k > 0; k--)
 			{
 				if (binCount[k]) acc.grow( binBox[k] );
 				n += binCount[k];
 				rightArea[k] = n ? acc.halfArea() : 0, rightCount[k] = n;
 			}
 			acc.reset(), n = 0;
-			for (int k = 0; k < BINS - 1; k++)
+			for (int k = 0; k < nb - 1; k++)
 			{
 				if (binCount[k]) acc.grow( binBox[k] );
 				n += binCount[k];
@@ -135,12 +136,12 @@ struct Builder2 {
 		{
 			float splitCost = COST_TRAVERSE + COST_PRIM * bestCost / std::max( box.halfArea(), 1e-30f );
 			if (!B200_DP_LEAVES && (int)count <= maxLeaf && (float)count * COST_PRIM <= splitCost) return; // cheaper as a leaf
-			float scale = (float)BINS / (cbox.hi[bestAxis] - cbox.lo[bestAxis]);
+			float scale = (float)nb / (cbox.hi[bestAxis] - cbox.lo[bestAxis]);
 			float lo = cbox.lo[bestAxis];
 			int a = bestAxis, s = bestSplit;
 			auto it = std::partition( refs.begin() + first, refs.begin() + first + count, [=]( const Ref& r ) {
 				int k = (int)((r.c[a] - lo) * scale);
-				k = k < 0 ? 0 : (k > BINS - 1 ? BINS - 1 : k);
+				k = k < 0 ? 0 : (k > nb - 1 ? nb - 1 : k);
 				return k <= s;
 			} );
 			mid = (uint32_t)(it - refs.begin());
