@@ -29,6 +29,7 @@ struct TraceArgs {
 	const uint32_t* countPtr;  // optional device-resident ray count (wavefront counters); overrides `count`
 	uint32_t count;
 	uint32_t tlasRoot;         // absolute node index of the top-level root
+	uint32_t singleInstance;   // 1: the scene is one instance (record 0): rays enter it directly, the top-level node is not visited
 	uint32_t magic;            // byte-decode constant, set by the launchers; passed as an argument on purpose, see qbyte() / qpair() in traverse.cu
 	uint32_t* stepNodes;       // optional per-ray counters (COUNT variants)
 	uint32_t* stepTris;

@@ -151,6 +151,7 @@ int RenderCore::Setting( const char* name, float value )
 	if (!strcmp( name, "zeroCopyBelow" )) { zeroCopyBelow = (int)value; return 0; }
 	if (!strcmp( name, "hostChunks" )) { hostChunks = (int)value; return 0; }
 	if (!strcmp( name, "hostChunkMode" )) { hostChunkMode = (int)value; return 0; }
+	if (!strcmp( name, "singleInstanceShortcut" )) { singleInstanceShortcut = value >= 0.5f; return 0; }
 	if (!strcmp( name, "countSteps" )) { countSteps = value >= 0.5f; return 0; }
 	if (!strcmp( name, "refit" )) { allowRefit = value >= 0.5f; return 0; }
 	if (!strcmp( name, "sahPrimCost" )) { if (!(value > 0)) return fail( "Setting sahPrimCost: > 0" ); g_sahPrimCost = value; return 0; }
@@ -503,6 +504,7 @@ TraceArgs RenderCore::baseArgs() const
 	a.nodes = (const uint4*)nodePool.ptr, a.tris = (const float4*)triPool.ptr, a.instances = (const float4*)instPool.ptr;
 	a.fetchCounter = (uint32_t*)fetchCounter.ptr;
 	a.tlasRoot = tlasRoot;
+	a.singleInstance = (instances.size() == 1 && singleInstanceShortcut) ? 1u : 0u;
 	a.magic = 0x4B000000u;
 	return a;
 }

@@ -121,6 +121,7 @@ private:
 	DeviceBuffer rayO[WAVE_SLOTS], rayD[WAVE_SLOTS], hitBuf[WAVE_SLOTS], bitBuf[WAVE_SLOTS], vertStage, nodeLo, nodeHi, stepNodes, stepTris;
 	bool countSteps = false, allowRefit = true, gpuBuild = false; // gpuBuild: new meshes get an LBVH built on the device (build.cu)
 	bool zeroCopy = true, twoStreams = true; int pinnedChunks = 1, zeroCopyBelow = 400000; // pinned host ray planes are fetched by the kernel itself (Setting zeroCopy / pinnedChunks)
+	bool singleInstanceShortcut = true; // a one-instance scene skips the top-level node (Setting singleInstanceShortcut)
 	int hostChunks = 4, hostChunkMode = 0; // chunk schedule of the host-buffer waves (Setting hostChunks / hostChunkMode)
 	int buildThreads = 0;
 	cudaEvent_t evA = nullptr, evB = nullptr;

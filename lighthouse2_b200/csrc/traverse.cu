@@ -464,7 +464,9 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 #if B200_WORLD_SMEM
 					sWorldO[threadIdx.x] = O4, sWorldD[threadIdx.x] = D4;
 #endif
-					ngroup = make_uint2( a.tlasRoot, 0x80000000u ), tgroup = make_uint2( 0, 0 );
+					// a one-instance scene: the ray enters instance record 0 in step A of its first pass; the top-level node (whose
+					// only box is that instance's) is not visited -- the bottom-level root test rejects what it would have rejected
+					ngroup = make_uint2( a.tlasRoot, a.singleInstance ? 0u : 0x80000000u ), tgroup = make_uint2( 0, a.singleInstance );
 					sp = 0, instBase = -1, curInst = NO_INSTANCE;
 					hitPrim = 0xffffffffu, hitInst = 0, hitBary = 0, nNodes = nTris = 0;
 					lastQueued = qhead - 1, terminated = false;
@@ -478,7 +480,25 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		// ---- traversal: every pass = one node step per lane, then queue / flush triangle pairs ------------
 		while (true)
 		{
-			// A. node step (not while leaf triangles of the previous step are still waiting to be queued)
+			// A. top level: a hit leaf is an instance -- remember what is left here, then descend into its BLAS (its root is visited
+			//    by step B of the same pass)
+			if (active && instBase < 0 && tgroup.y)
+			{
+				const uint32_t bit = 31 - __clz( tgroup.y );
+				tgroup.y &= ~(1u << bit);
+				const uint32_t idx = tgroup.x + bit;
+				if (ngroup.y > 0x00ffffffu) push( ngroup );
+				if (tgroup.y) push( tgroup );
+				const float4* rec = a.instances + (size_t)idx * 6;
+				const float4 info = __ldg( rec + 4 );
+				enterInstance<ISECT>( r, rec );
+				mirrorRay();
+				curInst = __float_as_uint( info.y );
+				instBase = sp;
+				ngroup = make_uint2( __float_as_uint( info.x ), 0x80000000u );
+				tgroup = make_uint2( 0, 0 );
+			}
+			// B. node step (not while instance leaves of the previous step are still waiting to be entered)
 			if (active && ngroup.y > 0x00ffffffu && tgroup.y == 0)
 			{
 				const uint32_t hits = ngroup.y, imask = hits & 0xffu;
@@ -504,23 +524,6 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					asm volatile( "prefetch.global.L2 [%0];" ::"l"( nn + 4 ) );
 				}
 #endif
-			}
-			// B. top level: a hit leaf is an instance -- remember what is left here, then descend into its BLAS
-			if (active && instBase < 0 && tgroup.y)
-			{
-				const uint32_t bit = 31 - __clz( tgroup.y );
-				tgroup.y &= ~(1u << bit);
-				const uint32_t idx = tgroup.x + bit;
-				if (ngroup.y > 0x00ffffffu) push( ngroup );
-				if (tgroup.y) push( tgroup );
-				const float4* rec = a.instances + (size_t)idx * 6;
-				const float4 info = __ldg( rec + 4 );
-				enterInstance<ISECT>( r, rec );
-				mirrorRay();
-				curInst = __float_as_uint( info.y );
-				instBase = sp;
-				ngroup = make_uint2( __float_as_uint( info.x ), 0x80000000u );
-				tgroup = make_uint2( 0, 0 );
 			}
 			// C. bottom level: a lane that hit leaf triangles appends ONE record (first triangle, mask, owner) to the warp's
 			//    ring; as soon as 32 triangles are pending the warp tests them, one per lane
