@@ -92,9 +92,6 @@ template <int P> __device__ __forceinline__ void qpair( const uint32_t q, const 
 	f0 = __low2float( h ), f1 = __high2float( h );
 }
 
-#ifndef B200_POP_SELECT
-#define B200_POP_SELECT 0
-#endif
 #ifndef B200_WORLD_SMEM
 #define B200_WORLD_SMEM 1 // keep the world-space ray in shared memory for the way out of an instance instead of re-reading the ray planes
 #endif
@@ -349,7 +346,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	uint32_t qhead = 0, qtail = 0;     // ring sequence numbers of the leaf records (warp-uniform)
 	uint32_t pendingTris = 0;          // triangles in the ring (warp-uniform)
 	uint32_t lastQueued = 0xffffffffu; // sequence number of this lane's newest record
-	bool active = false, exhausted = false, terminated = false;
+	bool active = false, exhausted = false, terminated = false, finished = false;
 	sSlot[threadIdx.x] = 0xffffffffu;
 
 	auto push = [&]( const uint2 g ) {
@@ -442,6 +439,32 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 
 	while (true)
 	{
+		// ---- results of the lanes that retired since the last fetch ------------------------------------
+		if (finished)
+		{
+			if (ANYHIT)
+			{
+				if (a.accumulator)
+				{
+					// fused connect: an unoccluded shadow ray delivers its potential contribution
+					if (hitPrim == 0xffffffffu)
+					{
+						const float4 E = __ldg( a.potentials + rayIdx );
+						float* px = reinterpret_cast<float*>( a.accumulator + __float_as_uint( E.w ) );
+						atomicAdd( px, E.x ), atomicAdd( px + 1, E.y ), atomicAdd( px + 2, E.z );
+					}
+				}
+				else if (hitPrim != 0xffffffffu) atomicOr( a.occluded + (rayIdx >> 5), 1u << (rayIdx & 31) );
+			}
+			else
+			{
+				const bool hit = hitPrim != 0xffffffffu;
+				a.hits[rayIdx] = make_float4( __uint_as_float( hit ? hitBary : 0u ), __uint_as_float( hit ? hitInst : 0u ),
+					__uint_as_float( hitPrim ), hit ? r.t : 1e34f );
+			}
+			if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
+			finished = false;
+		}
 		// ---- ray fetch: idle lanes claim consecutive rays with one aggregated atomic ------------------
 		const uint32_t idleMask = __ballot_sync( 0xffffffffu, !active );
 		if (idleMask && !exhausted)
@@ -559,15 +582,20 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					while (pendingTris >= 32) flush();
 				}
 			}
-			// D. lanes without node work: leave the instance / pop / retire (only once their queued pairs are tested)
+			// D. lanes without node work: leave the instance / pop / retire (only once their queued pairs are tested).  A retired
+			//    lane keeps its result in registers; it is written when the warp next fetches rays (see the top of the outer loop),
+			//    several lanes at a time, so that the per-pass path holds no result stores.  The world-space ray is only restored
+			//    when top-level work is left on the stack.
 			bool waiting = false;
 			if (active && ngroup.y <= 0x00ffffffu && tgroup.y == 0)
 			{
 				const bool pending = (int32_t)(lastQueued - qhead) >= 0;
-				if (terminated || sp == instBase)
+				const bool leaving = terminated || sp == instBase;
+				if (leaving && pending) waiting = true;
+				else if (terminated || sp == 0) active = false, finished = true;
+				else
 				{
-					if (pending) waiting = true;
-					else if (!terminated)
+					if (leaving)
 					{
 						// bottom level exhausted: back to the world-space ray (t is kept, as in bvh.cpp:612-619)
 #if B200_WORLD_SMEM
@@ -580,45 +608,8 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 						r.ix = W.x, r.iy = W.y, r.iz = W.z, r.octinv4 = __float_as_uint( W.w );
 						instBase = -1, curInst = NO_INSTANCE;
 					}
-				}
-				if (!waiting)
-				{
-					if (terminated || sp == 0)
-					{
-						if (ANYHIT)
-						{
-							if (a.accumulator)
-							{
-								// fused connect: an unoccluded shadow ray delivers its potential contribution
-								if (hitPrim == 0xffffffffu)
-								{
-									const float4 E = __ldg( a.potentials + rayIdx );
-									float* px = reinterpret_cast<float*>( a.accumulator + __float_as_uint( E.w ) );
-									atomicAdd( px, E.x ), atomicAdd( px + 1, E.y ), atomicAdd( px + 2, E.z );
-								}
-							}
-							else if (hitPrim != 0xffffffffu) atomicOr( a.occluded + (rayIdx >> 5), 1u << (rayIdx & 31) );
-						}
-						else
-						{
-							const bool hit = hitPrim != 0xffffffffu;
-							a.hits[rayIdx] = make_float4( __uint_as_float( hit ? hitBary : 0u ), __uint_as_float( hit ? hitInst : 0u ),
-								__uint_as_float( hitPrim ), hit ? r.t : 1e34f );
-						}
-						if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
-						active = false;
-					}
-					else
-					{
-						const uint2 g = pop();
-#if B200_POP_SELECT
-						const bool isNode = g.y > 0x00ffffffu; // tgroup.y is 0 here
-						ngroup = make_uint2( isNode ? g.x : 0u, isNode ? g.y : 0u );
-						tgroup = make_uint2( isNode ? tgroup.x : g.x, isNode ? 0u : g.y );
-#else
-						if (g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
-#endif
-					}
+					const uint2 g = pop();
+					if (g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
 				}
 			}
 			// E. flush a partially filled ring when lanes wait on it and little node work is left in the warp
