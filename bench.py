@@ -454,7 +454,7 @@ def run_b200(args):
             "rays": rays,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(),
                          "kernel": "traceKernel<closest> (extend wave)", "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY, "peak_source": peak_src,
-                         "note": "stream roofline of an instruction-issue-bound traversal kernel; see DESIGN.md", "ncu": measured_traffic("extend_ncu")},
+                         "note": "stream roofline of a latency-bound traversal kernel (dependent chain of a pass at 6 warps per scheduler); see DESIGN.md", "ncu": measured_traffic("extend_ncu")},
             "gpu_launches": int(launches),
             "clocks": clock_info,
         }
