@@ -319,16 +319,18 @@ constexpr int RING_CAP = 64;                          // leaf records per warp r
 constexpr int REFILL_BELOW = B200_REFILL_BELOW;      // leave the traversal loop to fetch rays when fewer lanes are active
 constexpr int PARTIAL_BELOW = B200_PARTIAL_BELOW;    // flush a partially filled ring for waiting lanes when fewer lanes have node work
 
-template <int ISECT, bool ANYHIT, bool COUNT>
+// SINGLE: the scene is ONE instance (record 0).  Rays are taken into its space when they are fetched and never come back to
+// the top level: no top-level node visit, no instance step in the pass, no world-space copy of the ray, one-level stack logic.
+template <int ISECT, bool ANYHIT, bool COUNT, bool SINGLE>
 __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel( const TraceArgs a )
 {
 	__shared__ uint2 sstack[STACK_SMEM * BLOCK_THREADS];
 	__shared__ float4 sRayO[BLOCK_THREADS];          // current-space ray of each lane: (ox,oy,oz,tmin)
 	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
 	__shared__ uint32_t sSlot[BLOCK_THREADS];        // flush slot of the winning pair, 0xffffffff = none
-	__shared__ float4 sWorld[BLOCK_THREADS];         // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
+	__shared__ float4 sWorld[SINGLE ? 1 : BLOCK_THREADS]; // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
 #if B200_WORLD_SMEM
-	__shared__ float4 sWorldO[BLOCK_THREADS], sWorldD[BLOCK_THREADS];
+	__shared__ float4 sWorldO[SINGLE ? 1 : BLOCK_THREADS], sWorldD[SINGLE ? 1 : BLOCK_THREADS];
 #endif
 	__shared__ uint2 sRing[WARPS_PER_BLOCK][RING_CAP]; // leaf records: (first triangle | owner lane << 27, 24-bit triangle mask)
 	uint2 lstack[STACK_LOCAL];
@@ -338,6 +340,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	const uint4* __restrict__ nodes = a.nodes;
 	const float4* __restrict__ tris = a.tris;
 	const uint32_t K = a.magic; // see qbyte / qpair; set by the launchers
+	const float4 singleInfo = SINGLE ? __ldg( a.instances + 4 ) : make_float4( 0, 0, 0, 0 ); // (BLAS root, instance id, ..) of record 0
 
 	RayState r = {};
 	uint32_t rayIdx = 0, hitPrim = 0, hitInst = 0, hitBary = 0, curInst = 0, nNodes = 0, nTris = 0;
@@ -430,7 +433,8 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			if (changed)
 			{
 				sSlot[threadIdx.x] = 0xffffffffu;
-				r.t = wT, hitPrim = wPrim, hitBary = wBary, hitInst = curInst;
+				r.t = wT, hitPrim = wPrim, hitBary = wBary;
+				if (!SINGLE) hitInst = curInst;
 				if (ANYHIT) terminated = true, ngroup.y = 0, tgroup.y = 0;
 			}
 		}
@@ -459,7 +463,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			else
 			{
 				const bool hit = hitPrim != 0xffffffffu;
-				a.hits[rayIdx] = make_float4( __uint_as_float( hit ? hitBary : 0u ), __uint_as_float( hit ? hitInst : 0u ),
+				a.hits[rayIdx] = make_float4( __uint_as_float( hit ? hitBary : 0u ), __uint_as_float( hit ? (SINGLE ? __float_as_uint( singleInfo.y ) : hitInst) : 0u ),
 					__uint_as_float( hitPrim ), hit ? r.t : 1e34f );
 			}
 			if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
@@ -482,14 +486,23 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					if (a.hostO) a.stageO[rayIdx] = O4, a.stageD[rayIdx] = D4; // host-buffer wave: the upload happens here
 					r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.tmin = O4.w;
 					r.dx = D4.x, r.dy = D4.y, r.dz = D4.z, r.t = D4.w;
-					setupSlab( r );
-					sWorld[threadIdx.x] = make_float4( r.ix, r.iy, r.iz, __uint_as_float( r.octinv4 ) );
+					if (SINGLE)
+					{
+						// straight into the instance (reference arithmetic of the instance entry).  The top-level node, whose only box is
+						// this instance's, is not visited: the bottom-level root test rejects what it would have rejected
+						enterInstance<ISECT>( r, a.instances );
+						mirrorRay();
+						ngroup = make_uint2( __float_as_uint( singleInfo.x ), 0x80000000u ), tgroup = make_uint2( 0, 0 );
+					}
+					else
+					{
+						setupSlab( r );
+						sWorld[threadIdx.x] = make_float4( r.ix, r.iy, r.iz, __uint_as_float( r.octinv4 ) );
 #if B200_WORLD_SMEM
-					sWorldO[threadIdx.x] = O4, sWorldD[threadIdx.x] = D4;
+						sWorldO[threadIdx.x] = O4, sWorldD[threadIdx.x] = D4;
 #endif
-					// a one-instance scene: the ray enters instance record 0 in step A of its first pass; the top-level node (whose
-					// only box is that instance's) is not visited -- the bottom-level root test rejects what it would have rejected
-					ngroup = make_uint2( a.tlasRoot, a.singleInstance ? 0u : 0x80000000u ), tgroup = make_uint2( 0, a.singleInstance );
+						ngroup = make_uint2( a.tlasRoot, 0x80000000u ), tgroup = make_uint2( 0, 0 );
+					}
 					sp = 0, instBase = -1, curInst = NO_INSTANCE;
 					hitPrim = 0xffffffffu, hitInst = 0, hitBary = 0, nNodes = nTris = 0;
 					lastQueued = qhead - 1, terminated = false;
@@ -505,7 +518,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		{
 			// A. top level: a hit leaf is an instance -- remember what is left here, then descend into its BLAS (its root is visited
 			//    by step B of the same pass)
-			if (active && instBase < 0 && tgroup.y)
+			if (!SINGLE && active && instBase < 0 && tgroup.y)
 			{
 				const uint32_t bit = 31 - __clz( tgroup.y );
 				tgroup.y &= ~(1u << bit);
@@ -522,7 +535,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				tgroup = make_uint2( 0, 0 );
 			}
 			// B. node step (not while instance leaves of the previous step are still waiting to be entered)
-			if (active && ngroup.y > 0x00ffffffu && tgroup.y == 0)
+			if (active && ngroup.y > 0x00ffffffu && (SINGLE || tgroup.y == 0))
 			{
 				const uint32_t hits = ngroup.y, imask = hits & 0xffu;
 				const uint32_t bit = 31 - __clz( hits );
@@ -551,7 +564,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			// C. bottom level: a lane that hit leaf triangles appends ONE record (first triangle, mask, owner) to the warp's
 			//    ring; as soon as 32 triangles are pending the warp tests them, one per lane
 			{
-				const bool has = active && instBase >= 0 && tgroup.y != 0;
+				const bool has = active && (SINGLE || instBase >= 0) && tgroup.y != 0;
 				const uint32_t m = __ballot_sync( 0xffffffffu, has );
 				if (m)
 				{
@@ -587,15 +600,15 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			//    several lanes at a time, so that the per-pass path holds no result stores.  The world-space ray is only restored
 			//    when top-level work is left on the stack.
 			bool waiting = false;
-			if (active && ngroup.y <= 0x00ffffffu && tgroup.y == 0)
+			if (active && ngroup.y <= 0x00ffffffu && (SINGLE || tgroup.y == 0)) // (SINGLE: step C has always taken the triangles)
 			{
 				const bool pending = (int32_t)(lastQueued - qhead) >= 0;
-				const bool leaving = terminated || sp == instBase;
+				const bool leaving = terminated || sp == (SINGLE ? 0 : instBase);
 				if (leaving && pending) waiting = true;
 				else if (terminated || sp == 0) active = false, finished = true;
 				else
 				{
-					if (leaving)
+					if (!SINGLE && leaving)
 					{
 						// bottom level exhausted: back to the world-space ray (t is kept, as in bvh.cpp:612-619)
 #if B200_WORLD_SMEM
@@ -609,7 +622,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 						instBase = -1, curInst = NO_INSTANCE;
 					}
 					const uint2 g = pop();
-					if (g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
+					if (SINGLE || g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
 				}
 			}
 			// E. flush a partially filled ring when lanes wait on it and little node work is left in the warp
@@ -627,17 +640,33 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 
 } // namespace
 
-namespace {
-int gExtendBlocksPerSM = 0, gShadowBlocksPerSM = 0;
 #ifndef B200_SMEM_CARVEOUT
 #define B200_SMEM_CARVEOUT -1 // percent of the 228 KB kept as shared memory (-1: the driver's choice); the rest of the 256 KB is L1
 #endif
-template <typename K> int blocksPerSM( K kernel )
+namespace {
+typedef void ( *TraceKernel )( const TraceArgs );
+// resident CTAs per SM of a kernel instance (asked once per instance)
+int blocksPerSM( TraceKernel kernel )
 {
+	static TraceKernel known[16];
+	static int blocks[16], count = 0;
+	for (int i = 0; i < count; i++) if (known[i] == kernel) return blocks[i];
 	int n = 0;
 	if (B200_SMEM_CARVEOUT >= 0) cudaFuncSetAttribute( kernel, cudaFuncAttributePreferredSharedMemoryCarveout, B200_SMEM_CARVEOUT );
 	cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, kernel, BLOCK_THREADS, 0 );
-	return n > 0 ? n : 1;
+	if (n < 1) n = 1;
+	if (count < 16) known[count] = kernel, blocks[count] = n, count++;
+	return n;
+}
+template <bool ANYHIT> TraceKernel pick( IsectMode mode, bool countSteps, bool single )
+{
+	if (mode == ISECT_REFERENCE)
+	{
+		if (countSteps) return single ? traceKernel<ISECT_REFERENCE, ANYHIT, true, true> : traceKernel<ISECT_REFERENCE, ANYHIT, true, false>;
+		return single ? traceKernel<ISECT_REFERENCE, ANYHIT, false, true> : traceKernel<ISECT_REFERENCE, ANYHIT, false, false>;
+	}
+	if (countSteps) return single ? traceKernel<ISECT_WATERTIGHT, ANYHIT, true, true> : traceKernel<ISECT_WATERTIGHT, ANYHIT, true, false>;
+	return single ? traceKernel<ISECT_WATERTIGHT, ANYHIT, false, true> : traceKernel<ISECT_WATERTIGHT, ANYHIT, false, false>;
 }
 } // namespace
 
@@ -647,11 +676,8 @@ cudaError_t LaunchExtend( const TraceArgs& args, IsectMode mode, bool countSteps
 	a.magic = B200_HALF_DECODE ? 0x64646464u : 0x4B000000u;
 	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
 	if (e != cudaSuccess) return e;
-	void ( *k )( const TraceArgs ) = mode == ISECT_REFERENCE
-		? (countSteps ? traceKernel<ISECT_REFERENCE, false, true> : traceKernel<ISECT_REFERENCE, false, false>)
-		: (countSteps ? traceKernel<ISECT_WATERTIGHT, false, true> : traceKernel<ISECT_WATERTIGHT, false, false>);
-	if (!gExtendBlocksPerSM) gExtendBlocksPerSM = blocksPerSM( traceKernel<ISECT_REFERENCE, false, false> );
-	k<<<smCount * gExtendBlocksPerSM, BLOCK_THREADS, 0, s>>>( a );
+	const TraceKernel k = pick<false>( mode, countSteps, a.singleInstance != 0 );
+	k<<<smCount * blocksPerSM( k ), BLOCK_THREADS, 0, s>>>( a );
 	return cudaGetLastError();
 }
 
@@ -661,9 +687,8 @@ cudaError_t LaunchShadow( const TraceArgs& args, IsectMode mode, int smCount, cu
 	a.magic = B200_HALF_DECODE ? 0x64646464u : 0x4B000000u;
 	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
 	if (e != cudaSuccess) return e;
-	void ( *k )( const TraceArgs ) = mode == ISECT_REFERENCE ? traceKernel<ISECT_REFERENCE, true, false> : traceKernel<ISECT_WATERTIGHT, true, false>;
-	if (!gShadowBlocksPerSM) gShadowBlocksPerSM = blocksPerSM( traceKernel<ISECT_REFERENCE, true, false> );
-	k<<<smCount * gShadowBlocksPerSM, BLOCK_THREADS, 0, s>>>( a );
+	const TraceKernel k = pick<true>( mode, false, a.singleInstance != 0 );
+	k<<<smCount * blocksPerSM( k ), BLOCK_THREADS, 0, s>>>( a );
 	return cudaGetLastError();
 }
 
