@@ -625,15 +625,14 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					if (SINGLE || g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
 				}
 			}
-			// E. flush a partially filled ring when lanes wait on it and little node work is left in the warp
-			if (__ballot_sync( 0xffffffffu, waiting ) && pendingTris)
-			{
-				const uint32_t workMask = __ballot_sync( 0xffffffffu, active && (ngroup.y > 0x00ffffffu || tgroup.y) );
-				if (__popc( workMask ) < PARTIAL_BELOW) while (pendingTris) flush();
-			}
+			// E. one warp reduction counts the waiting lanes, the lanes with work and the active lanes (a byte each)
+			const uint32_t votes = __reduce_add_sync( 0xffffffffu, (waiting ? 1u : 0u) | ((active && (ngroup.y > 0x00ffffffu || tgroup.y)) ? 0x100u : 0u) |
+				(active ? 0x10000u : 0u) );
+			//    flush a partially filled ring when lanes wait on it and little node work is left in the warp
+			if ((votes & 0xffu) && pendingTris && ((votes >> 8) & 0xffu) < PARTIAL_BELOW) while (pendingTris) flush();
 			// F. too few lanes left in this warp and rays remain: go back and refill the idle lanes
-			const uint32_t activeMask = __ballot_sync( 0xffffffffu, active );
-			if (!activeMask || (!exhausted && __popc( activeMask ) < REFILL_BELOW)) break;
+			const uint32_t nActive = votes >> 16;
+			if (!nActive || (!exhausted && nActive < REFILL_BELOW)) break;
 		}
 	}
 }
