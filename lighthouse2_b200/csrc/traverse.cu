@@ -378,14 +378,18 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			const uint32_t up = __shfl_up_sync( 0xffffffffu, incl, d );
 			if (lane >= d) incl += up;
 		}
-		const uint32_t start = incl - cnt, total = __shfl_sync( 0xffffffffu, incl, 31 );
-		const uint32_t take = min( total, 32u );
-		// every record holds >= 1 triangle, so record starts are distinct: bit s of `starts` = a record starts at triangle s;
+		const uint32_t start = incl - cnt;
+		// the 32 records at hand hold all pending triangles, or (more than 32 records, one triangle or more each) at least 32
+		const uint32_t take = min( pendingTris, 32u );
+		// every record holds >= 1 triangle, so record starts are distinct: bit s of `starts` = a record starts at triangle s (bit 0,
+		// always the first record's, carries "a record ends exactly at `take`" through the reduction instead);
 		// the record of tester lane L is the number of starts at or below L, minus one
-		const uint32_t starts = __reduce_or_sync( 0xffffffffu, (lane < nrec && start < 32u) ? 1u << start : 0u );
+		const uint32_t red = __reduce_or_sync( 0xffffffffu, lane < nrec ? ((start - 1u < 31u ? 1u << start : 0u) | (incl == take ? 1u : 0u)) : 0u );
+		const uint32_t starts = red | 1u;
 		const uint32_t ri = min( (uint32_t)__popc( starts & (0xffffffffu >> (31 - lane)) ) - 1u, 31u );
-		const uint32_t rx = __shfl_sync( 0xffffffffu, rec.x, ri ), ry = __shfl_sync( 0xffffffffu, rec.y, ri );
-		const uint32_t rstart = __shfl_sync( 0xffffffffu, start, ri );
+		const uint32_t rx = __shfl_sync( 0xffffffffu, rec.x, ri );
+		const uint32_t pk = __shfl_sync( 0xffffffffu, rec.y | (start << 24), ri ); // 24-bit mask | start (< 32 for every record a tester can have)
+		const uint32_t ry = pk & 0x00ffffffu, rstart = pk >> 24;
 		const bool mine = lane < take;
 		bool hit = false;
 		float tt = 0, u = 0, v = 0;
@@ -409,12 +413,12 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			hit = intersectTriangle<ISECT>( O, D, v0, e1, e2, tt, u, v );
 		}
 		// retire consumed records; the record that straddles the 32-triangle boundary keeps its untested triangles
-		const bool full = lane < nrec && incl <= take;
 		if (lane < nrec && incl > take && incl - cnt < take)
 		{
 			ring[(qhead + lane) & (RING_CAP - 1)].y = dropHighest( rec.y, take - (incl - cnt) );
 		}
-		qhead += __popc( __ballot_sync( 0xffffffffu, full ) );
+		// records used up = records that end at or before `take`: one per start at 1 .. take-1, plus the one that ends exactly there
+		qhead += __popc( starts >> 1 ) + (red & 1u);
 		pendingTris -= take;
 		const uint32_t hitMask = __ballot_sync( 0xffffffffu, hit ); // also orders the mirror reads before the atomics
 		if (hitMask)
