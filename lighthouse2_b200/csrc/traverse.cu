@@ -633,7 +633,13 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			const uint32_t votes = __reduce_add_sync( 0xffffffffu, (waiting ? 1u : 0u) | ((active && (ngroup.y > 0x00ffffffu || tgroup.y)) ? 0x100u : 0u) |
 				(active ? 0x10000u : 0u) );
 			//    flush a partially filled ring when lanes wait on it and little node work is left in the warp
-			if ((votes & 0xffu) && pendingTris && ((votes >> 8) & 0xffu) < PARTIAL_BELOW) while (pendingTris) flush();
+#ifndef B200_EAGER_BELOW
+#define B200_EAGER_BELOW 8
+#endif
+			//    ... or, whoever waits, when so few lanes have node work that the warp is near the end of its rays: their hit distances
+			//    then shrink pass by pass instead of once per 32 triangles, and the last, longest rays cull more
+			const uint32_t nWork = (votes >> 8) & 0xffu;
+			if (pendingTris && (nWork < B200_EAGER_BELOW || ((votes & 0xffu) && nWork < PARTIAL_BELOW))) while (pendingTris) flush();
 			// F. too few lanes left in this warp and rays remain: go back and refill the idle lanes
 			const uint32_t nActive = votes >> 16;
 			if (!nActive || (!exhausted && nActive < REFILL_BELOW)) break;
