@@ -596,7 +596,10 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					if (has) tgroup.y = 0;
 					qtail += __popc( m );
 					__syncwarp();
-					while (pendingTris >= 32) flush();
+#ifndef B200_FLUSH_AT
+#define B200_FLUSH_AT 24 // test the pending triangles as soon as 24 wait (32 per round at most): hit distances shrink earlier, +2 % over 32
+#endif
+					while (pendingTris >= B200_FLUSH_AT) flush();
 				}
 			}
 			// D. lanes without node work: leave the instance / pop / retire (only once their queued pairs are tested).  A retired
