@@ -518,6 +518,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		if (!__any_sync( 0xffffffffu, active )) break;
 
 		// ---- traversal: every pass = one node step per lane, then queue / flush triangle pairs ------------
+		uint32_t votes = 0x00202000u; // "32 lanes active, 32 with work, none waiting": the first pass of a round decides nothing
 		while (true)
 		{
 			// A. top level: a hit leaf is an instance -- remember what is left here, then descend into its BLAS (its root is visited
@@ -632,8 +633,12 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					if (SINGLE || g.y > 0x00ffffffu) ngroup = g; else tgroup = g, ngroup = make_uint2( 0, 0 );
 				}
 			}
-			// E. one warp reduction counts the waiting lanes, the lanes with work and the active lanes (a byte each)
-			const uint32_t votes = __reduce_add_sync( 0xffffffffu, (waiting ? 1u : 0u) | ((active && (ngroup.y > 0x00ffffffu || tgroup.y)) ? 0x100u : 0u) |
+			// E. one warp reduction counts the waiting lanes, the lanes with work and the active lanes (a byte each).  The decisions
+			//    below use the counts of the PREVIOUS pass: the reduction of this pass is issued here and first read a whole pass
+			//    later, so its latency is off the pass's dependent chain; acting one pass late costs nothing (a refill or a partial
+			//    flush starts one pass later, and the loop makes one idle pass before it ends).
+			const uint32_t prev = votes;
+			votes = __reduce_add_sync( 0xffffffffu, (waiting ? 1u : 0u) | ((active && (ngroup.y > 0x00ffffffu || tgroup.y)) ? 0x100u : 0u) |
 				(active ? 0x10000u : 0u) );
 			//    flush a partially filled ring when lanes wait on it and little node work is left in the warp
 #ifndef B200_EAGER_BELOW
@@ -641,10 +646,10 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 #endif
 			//    ... or, whoever waits, when so few lanes have node work that the warp is near the end of its rays: their hit distances
 			//    then shrink pass by pass instead of once per 32 triangles, and the last, longest rays cull more
-			const uint32_t nWork = (votes >> 8) & 0xffu;
-			if (pendingTris && (nWork < B200_EAGER_BELOW || ((votes & 0xffu) && nWork < PARTIAL_BELOW))) while (pendingTris) flush();
+			const uint32_t nWork = (prev >> 8) & 0xffu;
+			if (pendingTris && (nWork < B200_EAGER_BELOW || ((prev & 0xffu) && nWork < PARTIAL_BELOW))) while (pendingTris) flush();
 			// F. too few lanes left in this warp and rays remain: go back and refill the idle lanes
-			const uint32_t nActive = votes >> 16;
+			const uint32_t nActive = prev >> 16;
 			if (!nActive || (!exhausted && nActive < REFILL_BELOW)) break;
 		}
 	}
