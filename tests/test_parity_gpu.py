@@ -100,6 +100,31 @@ def test_queued_waves_equal_the_synchronous_calls():
     rc.Shutdown()
 
 
+def test_one_instance_kernels_equal_the_two_level_kernels():
+    """A scene of one instance runs the SINGLE instances of the kernels (rays enter the instance when fetched, no top-level
+    step); Setting singleInstanceShortcut=0 sends the same scene through the general two-level kernels.  Same bits, closest and any hit,
+    also for a transformed instance."""
+    base = cases.case_soup(n_tris=30_000, n_rays=150_000, seed=91)
+    O, D = base["rays"]
+    M = np.eye(4, dtype=np.float32)
+    M[:3, 3] = (0.25, -0.5, 0.125)
+    for mat in (None, M.reshape(16)):
+        case = dict(base, instances=[(0, mat)])
+        out = []
+        for shortcut in (1, 0):
+            rc = core.RenderCoreB200(0)
+            rc.Setting("singleInstanceShortcut", shortcut)
+            cases.load_core(rc, case)
+            O4, D4 = core.pack_rays(O, D)
+            hits = rc.TraceClosest(O4, D4)
+            O4s, D4s = core.pack_rays(O, D, tmax=5.0)
+            out.append((hits, rc.TraceAny(O4s, D4s)))
+            rc.Shutdown()
+        assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32))
+        assert np.array_equal(out[0][1], out[1][1])
+        assert (core.unpack_hits(out[0][0])["prim"] >= 0).mean() > 0.2
+
+
 def test_empty_mesh_zero_rays_and_misses():
     rc = core.RenderCoreB200(0)
     case = cases.case_empty()
