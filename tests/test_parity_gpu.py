@@ -236,4 +236,21 @@ def test_errors_are_reported_not_swallowed():
     assert lib.b200_trace_closest(h, O4.ctypes.data, D4.ctypes.data, -1, None) != 0                   # negative count
     hits = rc.TraceClosest(O4, D4)                                                                    # and the core still works afterwards
     assert hits.shape == (8, 4)
+    # the queued waves and the peer-memory gather report misuse the same way
+    assert lib.b200_wait(h) == 0                                                                      # nothing queued: not an error
+    assert lib.b200_trace_closest_async(h, O4.ctypes.data, D4.ctypes.data, -1, None) != 0
+    buf = (core.C.c_char * 128)()
+    assert lib.b200_peer_handle(h, buf) != 0 and b"SetTarget" in lib.b200_last_error()                # no target yet
+    assert lib.b200_gather_finalize(h, 1) != 0
+    rc.SetTarget(16, 16, 1)
+    assert lib.b200_gather_finalize(h, 1) != 0 and b"OpenPeers" in lib.b200_last_error()              # peers not mapped
+    assert lib.b200_open_peers(h, buf, 1, 0) != 0 and b"PeerHandle" in lib.b200_last_error()          # handle not taken yet
+    assert lib.b200_peer_handle(h, buf) == 0
+    assert lib.b200_open_peers(h, buf, 40, 0) != 0                                                    # more ranks than the peer table holds
+    assert lib.b200_open_peers(h, buf, 1, 0) == 0                                                     # a world of one: nothing to map
+    rc.Render(view, 1)
+    assert lib.b200_gather_finalize(h, 0) != 0                                                        # zero samples
+    assert lib.b200_gather_finalize(h, 1) == 0                                                        # ... and works as plain finalize
+    assert np.isfinite(rc.ReadFrame()).all()
+    assert lib.b200_close_peers(h) == 0
     rc.Shutdown()
