@@ -308,14 +308,17 @@ __device__ V3 RandomBarycentrics( const float r0 )
 {
 	const uint32_t uf = (uint32_t)(r0 * 4294967296.0f);
 	float ax = 1, ay = 0, bx = 0, by = 1, cx = 0, cy = 0;
+	// every digit picks one of four sub-triangles; written with selects, not branches: the four cases are mixed within a warp (the
+	// branchy form ran all four per step and was a third of the shade kernel's instructions).  Same sums, same bits.
+#pragma unroll 4
 	for (int i = 0; i < 16; i++)
 	{
 		const int d = (uf >> (2 * (15 - i))) & 3;
-		float nax, nay, nbx, nby, ncx, ncy;
-		if (d == 0) nax = (bx + cx) * 0.5f, nay = (by + cy) * 0.5f, nbx = (ax + cx) * 0.5f, nby = (ay + cy) * 0.5f, ncx = (ax + bx) * 0.5f, ncy = (ay + by) * 0.5f;
-		else if (d == 1) nax = ax, nay = ay, nbx = (ax + bx) * 0.5f, nby = (ay + by) * 0.5f, ncx = (ax + cx) * 0.5f, ncy = (ay + cy) * 0.5f;
-		else if (d == 2) nax = (bx + ax) * 0.5f, nay = (by + ay) * 0.5f, nbx = bx, nby = by, ncx = (bx + cx) * 0.5f, ncy = (by + cy) * 0.5f;
-		else nax = (cx + ax) * 0.5f, nay = (cy + ay) * 0.5f, nbx = (cx + bx) * 0.5f, nby = (cy + by) * 0.5f, ncx = cx, ncy = cy;
+		const float abx = (ax + bx) * 0.5f, aby = (ay + by) * 0.5f, acx = (ax + cx) * 0.5f, acy = (ay + cy) * 0.5f;
+		const float bcx = (bx + cx) * 0.5f, bcy = (by + cy) * 0.5f;
+		const float nax = d == 0 ? bcx : d == 1 ? ax : d == 2 ? abx : acx, nay = d == 0 ? bcy : d == 1 ? ay : d == 2 ? aby : acy;
+		const float nbx = d == 0 ? acx : d == 1 ? abx : d == 2 ? bx : bcx, nby = d == 0 ? acy : d == 1 ? aby : d == 2 ? by : bcy;
+		const float ncx = d == 0 ? abx : d == 1 ? acx : d == 2 ? bcx : cx, ncy = d == 0 ? aby : d == 1 ? acy : d == 2 ? bcy : cy;
 		ax = nax, ay = nay, bx = nbx, by = nby, cx = ncx, cy = ncy;
 	}
 	const float rx = (ax + bx + cx) * 0.3333333f, ry = (ay + by + cy) * 0.3333333f;
