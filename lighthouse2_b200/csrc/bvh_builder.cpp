@@ -31,13 +31,9 @@ struct Node2 {
 #endif
 
 #ifndef B200_SAH_BINS
-#define B200_SAH_BINS 64 // 16 -> 64 bins: +2 % rays/s on the 1 M-triangle scene (primary +5 %), build 0.36 -> 0.40 s; 128..512 bins and an exact sweep of small ranges (B200_SWEEP_BELOW) add nothing
+#define B200_SAH_BINS 64 // 16 -> 64 bins: +2 % rays/s on the 1 M-triangle scene (primary +5 %), build 0.36 -> 0.40 s; 128..512 bins and an exact sweep of ranges below 16..64 primitives add nothing
 #endif
 constexpr int BINS = B200_SAH_BINS;
-#ifndef B200_SWEEP_BELOW
-#define B200_SWEEP_BELOW 0
-#endif
-constexpr int SWEEP_BELOW = B200_SWEEP_BELOW > 0 ? B200_SWEEP_BELOW : 1; // ranges of at most this many primitives are split by an exact sweep (0/1: never)
 constexpr float COST_TRAVERSE = 1.0f;
 #define COST_PRIM g_sahPrimCost // cost of a leaf triangle relative to a wide-node visit in the kernels (Setting "sahPrimCost")
 
@@ -98,41 +94,8 @@ struct Builder2 {
 				if (cost < bestCost) bestCost = cost, bestAxis = a, bestSplit = k;
 			}
 		}
-		// ---- small ranges: exact sweep over every split position of every axis (what the bins approximate); the bottom levels hold
-		//      most of the nodes a ray visits, so the better splits there are worth the three short sorts
-		bool swept = false;
-		int sweepAxis = -1, lastSorted = -1;
-		uint32_t sweepLeft = 0;
-		if (count <= (uint32_t)SWEEP_BELOW && bestAxis >= 0)
-		{
-			float rightArea[SWEEP_BELOW];
-			for (int a = 0; a < 3; a++)
-			{
-				if (!(cbox.hi[a] - cbox.lo[a] > 0)) continue;
-				std::sort( refs.begin() + first, refs.begin() + first + count, [a]( const Ref& x, const Ref& y ) { return x.c[a] < y.c[a]; } );
-				lastSorted = a;
-				Aabb acc;
-				acc.reset();
-				for (uint32_t i = count - 1; i > 0; i--) acc.grow( refs[first + i].b ), rightArea[i] = acc.halfArea();
-				acc.reset();
-				for (uint32_t i = 1; i < count; i++)
-				{
-					acc.grow( refs[first + i - 1].b );
-					const float cost = acc.halfArea() * (float)i + rightArea[i] * (float)(count - i);
-					if (cost < bestCost || (cost == bestCost && !swept)) bestCost = cost, sweepAxis = a, sweepLeft = i, swept = true;
-				}
-			}
-			if (swept && sweepAxis != lastSorted) // the range is left sorted along the last axis tried
-				std::sort( refs.begin() + first, refs.begin() + first + count, [=]( const Ref& x, const Ref& y ) { return x.c[sweepAxis] < y.c[sweepAxis]; } );
-		}
 		uint32_t mid;
-		if (swept)
-		{
-			float splitCost = COST_TRAVERSE + COST_PRIM * bestCost / std::max( box.halfArea(), 1e-30f );
-			if ((int)count <= maxLeaf && (float)count * COST_PRIM <= splitCost) return; // cheaper as a leaf
-			mid = first + sweepLeft;
-		}
-		else if (bestAxis >= 0)
+		if (bestAxis >= 0)
 		{
 			float splitCost = COST_TRAVERSE + COST_PRIM * bestCost / std::max( box.halfArea(), 1e-30f );
 			if (!B200_DP_LEAVES && (int)count <= maxLeaf && (float)count * COST_PRIM <= splitCost) return; // cheaper as a leaf

@@ -12,10 +12,14 @@
 //    too few are active (ray-stream compaction by vote + prefix popcount)
 //  * rays are two coalesced float4 planes; hits are one float4
 //  * 8-wide BVH with 8-bit quantised child boxes (wide_bvh.h); five LDG.128 per node; the eight slab
-//    tests decode planes with one PRMT + one FFMA each; octant-ordered child visiting from a hit mask
+//    tests decode planes with PRMT (+ HADD2.F32) and one FFMA each; octant-ordered child visiting from a hit mask
+//  * leaf triangles go through a per-warp ring in shared memory and are tested 32 at a time, one per lane
 //  * traversal stack: (base,mask) groups, first STACK_SMEM entries per lane in shared memory, rest local
 //  * TLAS -> BLAS: an instance leaf transforms the ray (reference arithmetic in ISECT_REFERENCE mode)
-//    and traversal continues in the same loop; leaving the instance reloads the world ray
+//    and traversal continues in the same loop; leaving the instance restores the world ray.  Scenes of
+//    one instance run kernel instances (SINGLE) that take the ray into the instance when it is fetched
+//  * a pass holds what every ray needs every step and nothing else: results are written and rays fetched
+//    between rounds of passes, the warp votes once per pass and reads the vote one pass later
 //
 // Compiled with -fmad=false: every float op below rounds separately unless written as __fmaf_rn, so the
 // ISECT_REFERENCE triangle test and instance entry are bit-identical to the reference's scalar C++.
@@ -92,12 +96,6 @@ template <int P> __device__ __forceinline__ void qpair( const uint32_t q, const 
 	f0 = __low2float( h ), f1 = __high2float( h );
 }
 
-#ifndef B200_WORLD_SMEM
-#define B200_WORLD_SMEM 1 // keep the world-space ray in shared memory for the way out of an instance instead of re-reading the ray planes
-#endif
-#ifndef B200_PREFETCH_TRIS_L1
-#define B200_PREFETCH_TRIS_L1 0
-#endif
 // m with its k highest set bits cleared (k < popc(m)).  A branch-free halving search and fns.b32 (45 SASS instructions) were
 // looked at: both have a longer dependent chain than this loop at the k <= 5 that is typical
 __device__ __forceinline__ uint32_t dropHighest( uint32_t m, uint32_t k )
@@ -300,12 +298,6 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 // smallest t, then (ties) the earliest-queued pair, so the first-visited triangle wins exact ties like the
 // reference's strict `found_t < t` (bvh.cpp:268).
 constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
-#ifndef B200_PREFETCH_NODE
-#define B200_PREFETCH_NODE 0
-#endif
-#ifndef B200_PREFETCH_TRIS
-#define B200_PREFETCH_TRIS 0
-#endif
 #ifndef B200_REFILL_BELOW
 #define B200_REFILL_BELOW 22
 #endif
@@ -314,6 +306,12 @@ constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
 #endif
 #ifndef B200_MIN_BLOCKS
 #define B200_MIN_BLOCKS 6
+#endif
+#ifndef B200_FLUSH_AT
+#define B200_FLUSH_AT 24 // test the pending triangles as soon as 24 wait (32 per round at most): hit distances shrink earlier, +2 % over 32
+#endif
+#ifndef B200_EAGER_BELOW
+#define B200_EAGER_BELOW 8 // test pending triangles every pass when fewer lanes than this have node work
 #endif
 constexpr int RING_CAP = 64;                          // leaf records per warp ring (a pass adds at most 32)
 constexpr int REFILL_BELOW = B200_REFILL_BELOW;      // leave the traversal loop to fetch rays when fewer lanes are active
@@ -329,9 +327,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
 	__shared__ uint32_t sSlot[BLOCK_THREADS];        // flush slot of the winning pair, 0xffffffff = none
 	__shared__ float4 sWorld[SINGLE ? 1 : BLOCK_THREADS]; // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
-#if B200_WORLD_SMEM
-	__shared__ float4 sWorldO[SINGLE ? 1 : BLOCK_THREADS], sWorldD[SINGLE ? 1 : BLOCK_THREADS];
-#endif
+	__shared__ float4 sWorldO[SINGLE ? 1 : BLOCK_THREADS], sWorldD[SINGLE ? 1 : BLOCK_THREADS]; // ... and the ray itself (re-reading the ray planes there cost 2 %)
 	__shared__ uint2 sRing[WARPS_PER_BLOCK][RING_CAP]; // leaf records: (first triangle | owner lane << 27, 24-bit triangle mask)
 	uint2 lstack[STACK_LOCAL];
 	const uint32_t lane = threadIdx.x & 31, warpBase = threadIdx.x & ~31u;
@@ -502,9 +498,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					{
 						setupSlab( r );
 						sWorld[threadIdx.x] = make_float4( r.ix, r.iy, r.iz, __uint_as_float( r.octinv4 ) );
-#if B200_WORLD_SMEM
 						sWorldO[threadIdx.x] = O4, sWorldD[threadIdx.x] = D4;
-#endif
 						ngroup = make_uint2( a.tlasRoot, 0x80000000u ), tgroup = make_uint2( 0, 0 );
 					}
 					sp = 0, instBase = -1, curInst = NO_INSTANCE;
@@ -555,16 +549,6 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				const uint32_t hm = intersectNode( r, K, n0, n1, n2, n3, n4 );
 				ngroup = make_uint2( n1.x, (hm & 0xff000000u) | (n0.w >> 24) );
 				tgroup = make_uint2( n1.y, hm & 0x00ffffffu );
-#if B200_PREFETCH_NODE
-				if (ngroup.y > 0x00ffffffu)
-				{
-					// the child this lane visits next: start its fetch now (scenes larger than L2)
-					const uint32_t nb = 31 - __clz( ngroup.y ), ns = (nb - 24) ^ (r.octinv4 & 0xffu);
-					const uint4* nn = nodes + (size_t)(ngroup.x + __popc( ngroup.y & 0xffu & ~(0xffffffffu << ns) )) * 5;
-					asm volatile( "prefetch.global.L2 [%0];" ::"l"( nn ) );
-					asm volatile( "prefetch.global.L2 [%0];" ::"l"( nn + 4 ) );
-				}
-#endif
 			}
 			// C. bottom level: a lane that hit leaf triangles appends ONE record (first triangle, mask, owner) to the warp's
 			//    ring; as soon as 32 triangles are pending the warp tests them, one per lane
@@ -577,29 +561,12 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					{
 						lastQueued = qtail + __popc( m & lanemask_lt() );
 						ring[lastQueued & (RING_CAP - 1)] = make_uint2( tgroup.x | (lane << 27), tgroup.y );
-#if B200_PREFETCH_TRIS_L1
-						{
-							const float4* tp = tris + (size_t)(tgroup.x + (uint32_t)__ffs( tgroup.y ) - 1) * 3;
-							asm volatile( "prefetch.global.L1 [%0];" ::"l"( tp ) );
-							asm volatile( "prefetch.global.L1 [%0];" ::"l"( tp + 3 * (uint32_t)__popc( tgroup.y ) - 1 ) );
-						}
-#endif
-#if B200_PREFETCH_TRIS
-						{
-							const float4* tp = tris + (size_t)(tgroup.x + (uint32_t)__ffs( tgroup.y ) - 1) * 3;
-							asm volatile( "prefetch.global.L2 [%0];" ::"l"( tp ) );
-							asm volatile( "prefetch.global.L2 [%0];" ::"l"( tp + 3 * (uint32_t)__popc( tgroup.y ) - 1 ) );
-						}
-#endif
 						if (COUNT) nTris += __popc( tgroup.y );
 					}
 					pendingTris += __reduce_add_sync( 0xffffffffu, has ? (uint32_t)__popc( tgroup.y ) : 0u );
 					if (has) tgroup.y = 0;
 					qtail += __popc( m );
 					__syncwarp();
-#ifndef B200_FLUSH_AT
-#define B200_FLUSH_AT 24 // test the pending triangles as soon as 24 wait (32 per round at most): hit distances shrink earlier, +2 % over 32
-#endif
 					while (pendingTris >= B200_FLUSH_AT) flush();
 				}
 			}
@@ -619,11 +586,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					if (!SINGLE && leaving)
 					{
 						// bottom level exhausted: back to the world-space ray (t is kept, as in bvh.cpp:612-619)
-#if B200_WORLD_SMEM
 						const float4 O4 = sWorldO[threadIdx.x], D4 = sWorldD[threadIdx.x];
-#else
-						const float4 O4 = __ldg( a.rayO + rayIdx ), D4 = __ldg( a.rayD + rayIdx );
-#endif
 						const float4 W = sWorld[threadIdx.x];
 						r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.dx = D4.x, r.dy = D4.y, r.dz = D4.z;
 						r.ix = W.x, r.iy = W.y, r.iz = W.z, r.octinv4 = __float_as_uint( W.w );
@@ -641,9 +604,6 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			votes = __reduce_add_sync( 0xffffffffu, (waiting ? 1u : 0u) | ((active && (ngroup.y > 0x00ffffffu || tgroup.y)) ? 0x100u : 0u) |
 				(active ? 0x10000u : 0u) );
 			//    flush a partially filled ring when lanes wait on it and little node work is left in the warp
-#ifndef B200_EAGER_BELOW
-#define B200_EAGER_BELOW 8
-#endif
 			//    ... or, whoever waits, when so few lanes have node work that the warp is near the end of its rays: their hit distances
 			//    then shrink pass by pass instead of once per 32 triangles, and the last, longest rays cull more
 			const uint32_t nWork = (prev >> 8) & 0xffu;
