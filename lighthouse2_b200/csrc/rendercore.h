@@ -104,7 +104,10 @@ private:
 	cudaEvent_t chunkEv[2 * MAX_CHUNKS + 1] = {};
 	// staging slots of the host-buffer waves: a wave queued with the *_async calls takes the next slot, so that its upload can run
 	// while the previous wave is still being traced and downloaded; a slot is reused once the wave that had it is done
-	static constexpr int WAVE_SLOTS = 3;
+#ifndef B200_WAVE_SLOTS
+#define B200_WAVE_SLOTS 3
+#endif
+	static constexpr int WAVE_SLOTS = B200_WAVE_SLOTS;
 	cudaEvent_t slotDone[WAVE_SLOTS] = {};
 	bool slotUsed[WAVE_SLOTS] = {};
 	uint32_t waveSeq = 0;
