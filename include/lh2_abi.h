@@ -67,6 +67,13 @@ static_assert( sizeof( CoreMaterial::Vec3Value ) == 40 && sizeof( CoreMaterial::
 static_assert( sizeof( CoreMaterial ) == 688, "CoreMaterial layout" );
 static_assert( offsetof( CoreMaterial, flags ) == 160 && offsetof( CoreMaterial, absorption ) == 168, "CoreMaterial" );
 static_assert( offsetof( CoreMaterial, reflection ) == 592 && offsetof( CoreMaterial, ior ) == 656, "CoreMaterial" );
+// float2 is ALIGN( 8 ) in the reference (common_types.h:62): four bytes of padding sit in front of Vec3Value::uvscale
+static_assert( offsetof( CoreMaterial::Vec3Value, textureID ) == 12 && offsetof( CoreMaterial::Vec3Value, scale ) == 16, "Vec3Value" );
+static_assert( offsetof( CoreMaterial::Vec3Value, uvscale ) == 24 && offsetof( CoreMaterial::Vec3Value, uvoffset ) == 32, "Vec3Value" );
+static_assert( offsetof( CoreMaterial::ScalarValue, textureID ) == 4 && offsetof( CoreMaterial::ScalarValue, scale ) == 12, "ScalarValue" );
+static_assert( offsetof( CoreMaterial::ScalarValue, uvscale ) == 16 && offsetof( CoreMaterial::ScalarValue, uvoffset ) == 24, "ScalarValue" );
+static_assert( offsetof( CoreMaterial, detailColor ) == 40 && offsetof( CoreMaterial, normals ) == 80 && offsetof( CoreMaterial, detailNormals ) == 120, "CoreMaterial" );
+static_assert( offsetof( CoreMaterial, roughness ) == 304 && offsetof( CoreMaterial, transmission ) == 528 && offsetof( CoreMaterial, eta ) == 560, "CoreMaterial" );
 
 // lib/RenderSystem/common_classes.h:240-269 (host layout)
 enum TexelStorage { ARGB32 = 0, ARGB128, NRM32 };

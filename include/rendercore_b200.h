@@ -153,6 +153,9 @@ typedef struct b200_stats {
 	uint32_t kernelLaunches;            /* kernels this core has launched since creation */
 	float lastTraceMs;                  /* device time of the last b200_trace_* kernel (CUDA events on the core's stream) */
 	uint32_t bvhCacheHits;              /* meshes whose host-built tree came from the on-disk cache (environment B200_BVH_CACHE = directory) */
+	float gatherKernelMs;               /* device time of the last b200_gather_finalize's pull + finalize kernel alone (without the arrival waits) */
+	uint32_t frameGraphLaunches;        /* frames replayed as a CUDA graph since creation (Setting frameGraph) */
+	uint32_t frameChains, framePasses;  /* of the last b200_render: independent wave chains, passes the samples were split into */
 } b200_stats;
 B200_API int b200_get_stats( b200_core* c, b200_stats* out );
 B200_API int b200_set_probe( b200_core* c, int x, int y );

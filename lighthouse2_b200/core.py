@@ -45,6 +45,7 @@ class Stats(C.Structure):
         ("probedInstid", C.c_int32), ("probedTriid", C.c_int32), ("probedDist", C.c_float),
         ("wideNodeCount", C.c_uint32), ("triangleCount", C.c_uint32), ("instanceCount", C.c_uint32), ("tlasNodeCount", C.c_uint32),
         ("kernelLaunches", C.c_uint32), ("lastTraceMs", C.c_float), ("bvhCacheHits", C.c_uint32),
+        ("gatherKernelMs", C.c_float), ("frameGraphLaunches", C.c_uint32), ("frameChains", C.c_uint32), ("framePasses", C.c_uint32),
     ]
 
     def as_dict(self):
@@ -174,8 +175,10 @@ CORE_MATERIAL_DEFAULTS = dict(metallic=0.0, subsurface=0.0, specular=0.5, roughn
                               sheenTint=0.0, clearcoat=0.0, clearcoatGloss=1.0, transmission=0.0, eta=1.0)  # host_material.h
 
 
-# byte offsets of (textureID, scale, uvscale, uvoffset) of detailColor @40, normals @80, detailNormals @120 and roughness @304
-CORE_MATERIAL_MAPS = dict(detail=(52, 56, 60, 68), normals=(92, 96, 100, 108), detail_normals=(132, 136, 140, 148), roughness_map=(308, 316, 320, 328))
+# byte offsets of (textureID, scale, uvscale, uvoffset) of detailColor @40, normals @80, detailNormals @120 (Vec3Value: textureID +12,
+# scale +16, uvscale +24, uvoffset +32 -- float2 is 8-byte aligned in the reference, common_types.h:62) and roughness @304 (ScalarValue:
+# textureID +4, scale +12, uvscale +16, uvoffset +24); tests/cpp/abi_vs_reference.cpp checks them against the reference header
+CORE_MATERIAL_MAPS = dict(detail=(52, 56, 64, 72), normals=(92, 96, 104, 112), detail_normals=(132, 136, 144, 152), roughness_map=(308, 316, 320, 328))
 
 
 def core_materials(materials) -> np.ndarray:

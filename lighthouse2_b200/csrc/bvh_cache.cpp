@@ -81,7 +81,33 @@ bool LoadWideBvh( const std::string& dir, uint64_t key, uint32_t T, int maxLeafP
 		if (p >= T || seen[p]) return false;
 		seen[p] = true;
 	}
-	for (const WideNode& n : out.nodes) if (n.childBase > h.nodeCount || n.primBase > T) return false;
+	// per node: the inner children (one per imask bit, contiguous at childBase) must be nodes of the NEXT level, every leaf slot's
+	// triangle run must end inside the triangle array, slot bytes must be well formed; and the tree must fit the traversal stack
+	if (h.levelCount > MAX_TREE_LEVELS) return false;
+	for (uint32_t level = 0; level + 1 < (uint32_t)out.levelStart.size(); level++)
+		for (uint32_t ni = out.levelStart[level]; ni < out.levelStart[level + 1]; ni++)
+		{
+			const WideNode& n = out.nodes[ni];
+			uint32_t inner = 0, primEnd = 0;
+			for (int s = 0; s < 8; s++)
+			{
+				const uint32_t meta = n.meta[s];
+				const bool isInner = (n.imask >> s) & 1u;
+				if (!meta) { if (isInner) return false; continue; }
+				if (isInner) { if (meta != (0x20u | (24u + (uint32_t)s))) return false; inner++; continue; }
+				const uint32_t unary = meta >> 5, off = meta & 31u;
+				if (unary != 1 && unary != 3 && unary != 7) return false;
+				const uint32_t cnt = unary == 1 ? 1 : unary == 3 ? 2 : 3;
+				if ((int)cnt > maxLeafPrims || off + cnt > 24) return false;
+				if (off + cnt > primEnd) primEnd = off + cnt;
+			}
+			if (primEnd && ((uint64_t)n.primBase + primEnd > T)) return false;
+			if (inner)
+			{
+				if (level + 2 >= (uint32_t)out.levelStart.size()) return false; // the last level has no children
+				if (n.childBase < out.levelStart[level + 1] || (uint64_t)n.childBase + inner > out.levelStart[level + 2]) return false;
+			}
+		}
 	for (int a = 0; a < 3; a++) out.bounds.lo[a] = h.lo[a], out.bounds.hi[a] = h.hi[a];
 	return true;
 }

@@ -7,7 +7,7 @@
 namespace b200 {
 
 // shade-stage records: float4s per triangle in the attribute pool ((vN0,u0) (vN1,u1) (vN2,u2) (v0,v1,v2,LOD) (T,alpha0) (B,alpha1)
-// (alpha2,-,-,-)) and per material in the material table (wavefront.cu::shadeKernel: 6 base float4, then two per extra map)
+// (alpha2, ltriIdx + 1 as integer bits, -,-)) and per material in the material table (wavefront.cu::shadeKernel: 6 base float4, then two per extra map)
 constexpr int TRI_ATTR_STRIDE = 7, MAT_STRIDE = 14;
 
 // Arguments of one extend (closest-hit) or shadow (any-hit) wave.
@@ -25,7 +25,9 @@ struct TraceArgs {
 	uint32_t* occluded;        // 1 bit/ray, pre-cleared, bit set = hit  (shadow); may be null when `accumulator` is set
 	const float4* potentials;  // optional fused connect (shadow): E4 = (rgb, pixelIdx bits) per shadow ray ...
 	float4* accumulator;       // ... added to accumulator[pixelIdx] when the ray is NOT occluded (.optix.cu:137-149, connections.h:23-34)
-	uint32_t* fetchCounter;    // persistent-thread ray fetch counter (zeroed by the launcher)
+	uint32_t* fetchCounter;    // persistent-thread ray fetch counter (zeroed by the launcher, unless fetchCounterNext is set)
+	uint32_t* fetchCounterNext;// optional: the counter of the NEXT wave on this stream; the kernel zeroes it, the launcher then issues no memset
+	                           // (wave chains of a frame alternate between two counters that are zero when the frame starts)
 	const uint32_t* countPtr;  // optional device-resident ray count (wavefront counters); overrides `count`
 	uint32_t count;
 	uint32_t tlasRoot;         // absolute node index of the top-level root

@@ -2,6 +2,7 @@
 // Counterpart of lib/RenderCore_Bart/rendercore.cpp:47-101 (SetGeometry/SetInstance) and of
 // lib/rendercore_optix7/rendercore.cpp:338-428 (SetGeometry/SetInstance/UpdateToplevel) for the B200 core.
 #include "rendercore.h"
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -212,6 +213,11 @@ int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 			memcpy( o + 3, ct, 4 ), memcpy( o + 7, ct + 4, 4 ), memcpy( o + 11, ct + 8, 4 );
 			memcpy( o + 12, ct + 16, 12 ), memcpy( o + 15, ct + 124, 4 );
 			memcpy( o + 16, ct + 80, 12 ), memcpy( o + 19, ct + 112, 4 ), memcpy( o + 20, ct + 96, 12 ), memcpy( o + 23, ct + 116, 4 ), memcpy( o + 24, ct + 120, 4 );
+			// CoreTri::ltriIdx (@12; -1 = not a light, pathtracer.h:139) kept + 1, so that the zero-filled records of meshes without CoreTris mean "unknown"
+			int32_t ltri;
+			memcpy( &ltri, ct + 12, 4 );
+			ltri = ltri >= 0 ? ltri + 1 : 0;
+			memcpy( o + 25, &ltri, 4 );
 		}
 		e = cudaMemcpyAsync( dst, at.data(), at.size() * 4, cudaMemcpyHostToDevice, stream );
 		if (e == cudaSuccess) e = cudaStreamSynchronize( stream ); // the staging vector dies here
@@ -249,6 +255,7 @@ int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T,
 	if (e != cudaSuccess) return fail( "shading upload", e );
 	if ((e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
 		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount )) != cudaSuccess) return fail( "GPU BVH build", e );
+	if ((int)m.levelStart.size() - 1 > MAX_TREE_LEVELS) return fail( "SetGeometry: the device-built tree is deeper than the traversal stack allows (wide_bvh.h MAX_TREE_LEVELS)" );
 	m.built = true;
 	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
 	meshes.push_back( m );
@@ -309,6 +316,7 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 		if (useCache) StoreWideBvh( cacheEnv, cacheKey, T, 3, bvh ); // best effort: an unwritable directory only costs the next start-up
 	}
 	else stats.bvhCacheHits++;
+	if ((int)bvh.levelStart.size() - 1 > MAX_TREE_LEVELS) return fail( "SetGeometry: the tree is deeper than the traversal stack allows (wide_bvh.h MAX_TREE_LEVELS)" );
 	MeshRec m;
 	m.nodeBase = blasNodeEnd, m.nodeCount = (uint32_t)bvh.nodes.size(), m.triBase = triEnd, m.triCount = T;
 	m.levelStart = bvh.levelStart, m.bounds = bvh.bounds, m.built = true;
@@ -457,6 +465,13 @@ int RenderCore::UpdateToplevel()
 	}
 	WideBvh tlas;
 	BuildWideBvh( boxes.data(), N, 1, 1, tlas );
+	{
+		// the kernels' per-lane stack has no bound check: refuse scenes that could overrun it (see wide_bvh.h)
+		int blasLevels = 0;
+		for (uint32_t i = 0; i < N; i++) blasLevels = std::max( blasLevels, (int)meshes[instances[i].mesh].levelStart.size() - 1 );
+		if (blasLevels + 2 * ((int)tlas.levelStart.size() - 1) > TRAVERSAL_STACK_ENTRIES)
+			return fail( "UpdateToplevel: bottom-level + 2 x top-level tree depth exceeds the traversal stack (wide_bvh.h TRAVERSAL_STACK_ENTRIES)" );
+	}
 	std::vector<InstanceRec> recs( N );
 	for (uint32_t j = 0; j < N; j++)
 	{

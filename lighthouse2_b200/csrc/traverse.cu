@@ -24,6 +24,7 @@
 // Compiled with -fmad=false: every float op below rounds separately unless written as __fmaf_rn, so the
 // ISECT_REFERENCE triangle test and instance entry are bit-identical to the reference's scalar C++.
 #include "kernels.h"
+#include "wide_bvh.h"
 #include <cuda_fp16.h>
 
 #ifndef B200_HALF_DECODE
@@ -41,7 +42,7 @@ constexpr int BLOCK_THREADS = 128;
 #define B200_STACK_SMEM 8
 #endif
 constexpr int STACK_SMEM = B200_STACK_SMEM; // per-lane stack entries kept in shared memory
-constexpr int STACK_LOCAL = 40;      // overflow entries in local memory
+constexpr int STACK_LOCAL = TRAVERSAL_STACK_ENTRIES - STACK_SMEM; // overflow entries in local memory; the host checks tree depths against the sum (wide_bvh.h)
 constexpr float REF_EPSILON = 0.0001f; // lib/RenderSystem/common_settings.h:45
 constexpr uint32_t NO_INSTANCE = 0xffffffffu;
 
@@ -347,6 +348,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	uint32_t lastQueued = 0xffffffffu; // sequence number of this lane's newest record
 	bool active = false, exhausted = false, terminated = false, finished = false;
 	sSlot[threadIdx.x] = 0xffffffffu;
+	if (a.fetchCounterNext && blockIdx.x == 0 && threadIdx.x == 0) *a.fetchCounterNext = 0;
 
 	auto push = [&]( const uint2 g ) {
 		if (sp < STACK_SMEM) sstack[sp * BLOCK_THREADS + threadIdx.x] = g; else lstack[sp - STACK_SMEM] = g;
@@ -651,7 +653,7 @@ cudaError_t LaunchExtend( const TraceArgs& args, IsectMode mode, bool countSteps
 {
 	TraceArgs a = args;
 	a.magic = B200_HALF_DECODE ? 0x64646464u : 0x4B000000u;
-	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
+	cudaError_t e = a.fetchCounterNext ? cudaSuccess : cudaMemsetAsync( a.fetchCounter, 0, 4, s );
 	if (e != cudaSuccess) return e;
 	const TraceKernel k = pick<false>( mode, countSteps, a.singleInstance != 0 );
 	k<<<smCount * blocksPerSM( k ), BLOCK_THREADS, 0, s>>>( a );
@@ -662,7 +664,7 @@ cudaError_t LaunchShadow( const TraceArgs& args, IsectMode mode, int smCount, cu
 {
 	TraceArgs a = args;
 	a.magic = B200_HALF_DECODE ? 0x64646464u : 0x4B000000u;
-	cudaError_t e = cudaMemsetAsync( a.fetchCounter, 0, 4, s );
+	cudaError_t e = a.fetchCounterNext ? cudaSuccess : cudaMemsetAsync( a.fetchCounter, 0, 4, s );
 	if (e != cudaSuccess) return e;
 	const TraceKernel k = pick<true>( mode, false, a.singleInstance != 0 );
 	k<<<smCount * blocksPerSM( k ), BLOCK_THREADS, 0, s>>>( a );

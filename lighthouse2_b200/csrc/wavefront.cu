@@ -23,6 +23,7 @@
 // (Setting sampleOffset); per-path random streams depend only on (pixel, sample, bounce), so any sharding gives the same
 // image and the accumulators of all shards simply add up.
 #include "rendercore.h"
+#include "../../include/lh2_abi.h"
 #include <cstring>
 #include <vector>
 
@@ -42,15 +43,15 @@ constexpr int PROBE_BASE = 2 * (MAX_PATH_LENGTH + 1), COUNTER_WORDS = PROBE_BASE
 __host__ __device__ __forceinline__ int extCounter( const int len ) { return 2 * len - 1; }
 __host__ __device__ __forceinline__ int shadowCounter( const int len ) { return 2 * len; }
 
+// What a frame's kernels need, in two parts.  FrameParams is fixed while nothing but the camera moves: it travels as a kernel parameter
+// (constant bank) and is part of the captured frame graph.  PassParams is what changes from frame to frame -- the camera and the
+// sample numbering of each pass -- and lives in device memory: the frame (graph or not) starts with one small upload of all its passes.
 struct FrameParams {
-	float pos[3], p1[3], right[3], up[3]; // right = p2 - p1, up = p3 - p1
 	float sky[3];                         // constant sky (used when no skydome image is set)
-	float aperture, distortion;           // ViewPyramid::aperture (lens radius), ::distortion (barrel distortion; 0 = none)
 	float epsilon, clampValue;
 	uint32_t width, height, pixelCount;
-	uint32_t shardIndex, shardCount, ownTiles, tilesX, tilesY;
-	uint32_t sampleBase, samplesThisPass; // global index of the first sample of this pass
-	uint32_t R0;                          // per-frame RNG salt
+	uint32_t shardIndex, shardCount, tilesX, tilesY;
+	uint32_t chainCount;                  // the shard's tiles are dealt to this many independent chains of waves (local tile t -> chain t % chainCount)
 	uint32_t roulette;                    // Russian roulette on (the reference's behaviour) / off (fixed-depth benchmark passes)
 	uint32_t jitter, materialCount, bounceCap; // bounceCap: 0 = none, 1 = stop after one diffuse bounce (the reference's ENOUGH_BOUNCES), 2 = two
 	int32_t probePixel;
@@ -63,8 +64,29 @@ struct FrameParams {
 	const float4* skyPixels;   // skydome image (rgb, 1), skyWidth x skyHeight; null = constant sky
 	uint32_t skyWidth, skyHeight;
 	const uint32_t* texels;    // ARGB32 texels of all textures, MIP levels behind each other (SetTextures)
-	float spreadAngle;         // ViewPyramid::spreadAngle: ray cone width per unit distance, for the texture LOD
-	const uint32_t* blueNoise; // 5 x 65536 words in the reference's layout (SetBlueNoise); null = xor32 numbers only
+	const uint32_t* blueTable; // 5 x 65536 words in the reference's layout (SetBlueNoise); null = none.  A pass uses it when PassParams::blue is set
+};
+struct PassParams {
+	float pos[3], p1[3], right[3], up[3]; // right = p2 - p1, up = p3 - p1
+	float aperture, distortion;           // ViewPyramid::aperture (lens radius), ::distortion (barrel distortion; 0 = none)
+	float spreadAngle;                    // ViewPyramid::spreadAngle: ray cone width per unit distance, for the texture LOD
+	uint32_t sampleBase, samplesThisPass; // global index of the first sample of this pass
+	uint32_t R0;                          // per-frame RNG salt
+	uint32_t blue;                        // the blue-noise table applies to this pass (not after the sample index wrapped)
+	float finalScale;                     // 1 / samples in the accumulator after this frame (the last pass writes the frame)
+	uint32_t pad[4];
+};
+static_assert( sizeof( PassParams ) == 96, "PassParams: six float4" );
+
+// One chain of waves: a share of the shard's tiles with its own path buffers, counters and streams.  Chains are independent (disjoint
+// pixels), so the tail of one chain's persistent wave kernel is filled by whatever the other chains have in flight.
+struct ChainArgs {
+	const float4 *rayO, *rayD, *state, *info, *hits;   // this wave's paths
+	float4 *rayOout, *rayDout, *stateOut, *infoOut;    // extension rays of the next wave
+	float4 *conO, *conD, *conE;                        // shadow rays: E4 = (potential rgb, contribution slot)
+	float4 *slotS, *slotC;                             // per-path contribution slots of this pass (see accumulateKernel)
+	uint32_t* counters;
+	uint32_t chain, chainTiles;                        // chainTiles: local tiles this chain owns
 };
 
 constexpr uint32_t S_SPECULAR = 1, S_BOUNCED = 2, S_VIASPECULAR = 4, S_BOUNCEDTWICE = 8; // pathtracer.h:29-32
@@ -139,12 +161,13 @@ template <int WARPS> __device__ __forceinline__ void blockAppend2( uint32_t* cou
 
 // ---- primary rays (GPU cores: rendercore_optix7/optix/.optix.cu:66-123, RenderCore_OptixPrime_B/kernels/camera.h:40-94) ----------
 // u = (x + r0) / w, v = (y + r1) / h, P = p1 + u right + v up, O = point on the lens, D = normalize(P - O); optional barrel distortion.
-__global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParams f, float4* __restrict__ rayO, float4* __restrict__ rayD,
-	float4* __restrict__ pathState, float4* __restrict__ pathInfo, uint32_t* counters )
+__global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParams f, const PassParams* __restrict__ pass, const ChainArgs c )
 {
 	__shared__ uint32_t sWarp[9];
-	const uint32_t total = f.ownTiles * TILE_PIXELS * f.samplesThisPass;
+	const PassParams P = *pass;
+	const uint32_t perSample = c.chainTiles * TILE_PIXELS, total = perSample * P.samplesThisPass;
 	const uint32_t stride = gridDim.x * blockDim.x;
+	const uint32_t* const blueTable = P.blue ? f.blueTable : nullptr;
 	for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) // block-uniform trip count (blockAppend synchronises)
 	{
 		const uint32_t job = base + threadIdx.x;
@@ -152,32 +175,31 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 		uint32_t x = 0, y = 0, sample = 0;
 		if (valid)
 		{
-			const uint32_t perSample = f.ownTiles * TILE_PIXELS;
 			sample = job / perSample;
-			const uint32_t q = job - sample * perSample, localTile = q / TILE_PIXELS, inTile = q % TILE_PIXELS;
-			const uint32_t tile = localTile * f.shardCount + f.shardIndex;
+			const uint32_t q = job - sample * perSample, chainTile = q / TILE_PIXELS, inTile = q % TILE_PIXELS;
+			const uint32_t tile = (chainTile * f.chainCount + c.chain) * f.shardCount + f.shardIndex;
 			x = (tile % f.tilesX) * TILE_W + (inTile % TILE_W), y = (tile / f.tilesX) * TILE_H + inTile / TILE_W;
 			valid = x < f.width && y < f.height;
 		}
-		const uint32_t slot = blockAppend<8>( counters + extCounter( 1 ), valid, sWarp );
+		const uint32_t slot = blockAppend<8>( c.counters + extCounter( 1 ), valid, sWarp );
 		if (!valid) continue;
-		const uint32_t pixelIdx = x + y * f.width, pathIdx = pixelIdx + (f.sampleBase + sample) * f.pixelCount;
+		const uint32_t pixelIdx = x + y * f.width, pathIdx = pixelIdx + (P.sampleBase + sample) * f.pixelCount;
 		float r0 = 0.5f, r1 = 0.5f;
-		uint32_t seed = WangHash( pathIdx + f.R0 );
+		uint32_t seed = WangHash( pathIdx + P.R0 );
 		// the first 256 samples of a pixel take their four numbers from the blue-noise table (.optix.cu:66-79)
-		const int sampleIdx = (int)(f.sampleBase + sample);
-		const bool blue = f.blueNoise && sampleIdx < 256;
+		const int sampleIdx = (int)(P.sampleBase + sample);
+		const bool blue = blueTable && sampleIdx < 256;
 		if (f.jitter)
 		{
-			if (blue) r0 = BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 0 ), r1 = BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 1 );
+			if (blue) r0 = BlueNoiseSampler( blueTable, x, y, sampleIdx, 0 ), r1 = BlueNoiseSampler( blueTable, x, y, sampleIdx, 1 );
 			else r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
 		}
 		// thin lens: a point on a 9-blade aperture of radius `aperture` in the screen-parallel plane through pos (RandomPointOnLens, .optix.cu:51-64)
-		float ox = f.pos[0], oy = f.pos[1], oz = f.pos[2];
-		if (f.aperture > 0)
+		float ox = P.pos[0], oy = P.pos[1], oz = P.pos[2];
+		if (P.aperture > 0)
 		{
-			const float l0 = blue ? BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 2 ) : RandomFloat( seed );
-			float l1 = blue ? BlueNoiseSampler( f.blueNoise, x, y, sampleIdx, 3 ) : RandomFloat( seed );
+			const float l0 = blue ? BlueNoiseSampler( blueTable, x, y, sampleIdx, 2 ) : RandomFloat( seed );
+			float l1 = blue ? BlueNoiseSampler( blueTable, x, y, sampleIdx, 3 ) : RandomFloat( seed );
 			const float blade = (float)(int)(l0 * 9);
 			float l2 = (l0 - blade * (1.0f / 9.0f)) * 9.0f;
 			float x1, y1, x2, y2;
@@ -185,28 +207,28 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 			__sincosf( (blade + 1.0f) * 3.14159265358979323846f / 4.5f, &x2, &y2 );
 			if (l1 + l2 > 1) l1 = 1.0f - l1, l2 = 1.0f - l2;
 			const float xr = x1 * l1 + x2 * l2, yr = y1 * l1 + y2 * l2;
-			ox += f.aperture * (f.right[0] * xr + f.up[0] * yr), oy += f.aperture * (f.right[1] * xr + f.up[1] * yr), oz += f.aperture * (f.right[2] * xr + f.up[2] * yr);
+			ox += P.aperture * (P.right[0] * xr + P.up[0] * yr), oy += P.aperture * (P.right[1] * xr + P.up[1] * yr), oz += P.aperture * (P.right[2] * xr + P.up[2] * yr);
 		}
 		float u, v;
-		if (f.distortion == 0) u = ((float)x + r0) / (float)f.width, v = ((float)y + r1) / (float)f.height;
+		if (P.distortion == 0) u = ((float)x + r0) / (float)f.width, v = ((float)y + r1) / (float)f.height;
 		else
 		{
 			// barrel distortion of the pixel position about the screen centre (.optix.cu:88-97)
 			const float tx = (float)x / (float)f.width - 0.5f, ty = (float)y / (float)f.height - 0.5f;
 			const float rr = tx * tx + ty * ty;
-			const float rq = sqrtf( rr ) * (1.0f + f.distortion * rr + f.distortion * rr * rr);
+			const float rq = sqrtf( rr ) * (1.0f + P.distortion * rr + P.distortion * rr * rr);
 			const float theta = atan2f( tx, ty );
 			const float bx = (sinf( theta ) * rq + 0.5f) * (float)f.width, by = (cosf( theta ) * rq + 0.5f) * (float)f.height;
 			u = (bx + r0) / (float)f.width, v = (by + r1) / (float)f.height;
 		}
-		const float dx = f.p1[0] + u * f.right[0] + v * f.up[0] - ox;
-		const float dy = f.p1[1] + u * f.right[1] + v * f.up[1] - oy;
-		const float dz = f.p1[2] + u * f.right[2] + v * f.up[2] - oz;
+		const float dx = P.p1[0] + u * P.right[0] + v * P.up[0] - ox;
+		const float dy = P.p1[1] + u * P.right[1] + v * P.up[1] - oy;
+		const float dz = P.p1[2] + u * P.right[2] + v * P.up[2] - oz;
 		const float il = 1.0f / sqrtf( dx * dx + dy * dy + dz * dz );
-		rayO[slot] = make_float4( ox, oy, oz, f.epsilon );
-		rayD[slot] = make_float4( dx * il, dy * il, dz * il, 1e34f );
-		pathState[slot] = make_float4( 1.f, 1.f, 1.f, 1.f );                      // throughput, postponed bsdf pdf
-		pathInfo[slot] = make_float4( __uint_as_float( pathIdx ), 0.f, 0.f, 0.f ); // pathIdx | flags << 28, normal at the previous vertex
+		c.rayOout[slot] = make_float4( ox, oy, oz, f.epsilon );
+		c.rayDout[slot] = make_float4( dx * il, dy * il, dz * il, 1e34f );
+		c.stateOut[slot] = make_float4( 1.f, 1.f, 1.f, 1.f );                      // throughput, postponed bsdf pdf
+		c.infoOut[slot] = make_float4( __uint_as_float( pathIdx ), 0.f, 0.f, 0.f ); // pathIdx | flags << 28, normal at the previous vertex
 	}
 }
 
@@ -458,16 +480,13 @@ __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 #ifndef B200_SHADE_GRID
 #define B200_SHADE_GRID 2 // resident sets of CTAs per launch
 #endif
-template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200_SHADE_MIN_BLOCKS ) shadeKernel( const FrameParams f, const int pathLength, const int maxPathLength,
-	const float4* __restrict__ rayO, const float4* __restrict__ rayD, const float4* __restrict__ pathState, const float4* __restrict__ pathInfo,
-	const float4* __restrict__ hits,
-	float4* __restrict__ rayOout, float4* __restrict__ rayDout, float4* __restrict__ pathStateOut, float4* __restrict__ pathInfoOut,
-	float4* __restrict__ conO, float4* __restrict__ conD, float4* __restrict__ conE,
-	const float4* __restrict__ shade, const float4* __restrict__ vertexNormals, const float4* __restrict__ instShade, const float4* __restrict__ materials,
-	float4* accumulator, uint32_t* counters )
+template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200_SHADE_MIN_BLOCKS ) shadeKernel( const FrameParams f, const PassParams* __restrict__ pass, const int pathLength, const int maxPathLength,
+	const ChainArgs c, const float4* __restrict__ shade, const float4* __restrict__ vertexNormals, const float4* __restrict__ instShade, const float4* __restrict__ materials )
 {
 	__shared__ uint32_t sWarp[2 * 4 + 2];
+	uint32_t* const counters = c.counters;
 	const uint32_t count = counters[extCounter( pathLength )];
+	// (PassParams fields are read where they are used: uniform, cached loads that cost less than registers held across the whole loop body)
 	const uint32_t stride = gridDim.x * blockDim.x;
 	for (uint32_t base = blockIdx.x * blockDim.x; base < count; base += stride) // block-uniform trip count (blockAppend2 synchronises)
 	{
@@ -475,22 +494,38 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 		bool wantShadow = false, wantExt = false;
 		V3 so = v3( 0.f, 0.f, 0.f ), sl = so, se = so, eo = so, er = so, et = so, en = so;
 		float sdist = 0, epdf = 0;
-		uint32_t pathIdx = 0, pixelIdx = 0, flags = 0;
+		uint32_t pathIdx = 0, pixelIdx = 0, flags = 0, slot = 0;
 		if (job < count)
 		{
-			const float4 O4 = __ldg( rayO + job ), D4 = __ldg( rayD + job ), T4 = __ldg( pathState + job ), P4 = __ldg( pathInfo + job ), hit = __ldg( hits + job );
-			pathIdx = __float_as_uint( P4.x ) & PATHIDX_MASK, flags = __float_as_uint( P4.x ) >> PATHIDX_BITS, pixelIdx = pathIdx % f.pixelCount;
+			const float4 O4 = __ldg( c.rayO + job ), D4 = __ldg( c.rayD + job ), T4 = __ldg( c.state + job ), P4 = __ldg( c.info + job ), hit = __ldg( c.hits + job );
+			pathIdx = __float_as_uint( P4.x ) & PATHIDX_MASK, flags = __float_as_uint( P4.x ) >> PATHIDX_BITS;
+			const uint32_t sampleIdxU = pathIdx / f.pixelCount;
+			pixelIdx = pathIdx - sampleIdxU * f.pixelCount;
+			{
+				// contribution slot of this path = its index when the pass was generated (generateEyeRaysKernel's `job`)
+				const uint32_t pxX = pixelIdx % f.width, pxY = pixelIdx / f.width;
+				const uint32_t tile = (pxY / TILE_H) * f.tilesX + pxX / TILE_W, chainTile = tile / f.shardCount / f.chainCount;
+				slot = (sampleIdxU - __ldg( &pass->sampleBase )) * (c.chainTiles * TILE_PIXELS) + chainTile * TILE_PIXELS + (pxY % TILE_H) * TILE_W + pxX % TILE_W;
+			}
 			const int prim = (int)__float_as_uint( hit.z );
 			const V3 D = v3( D4 ), O = v3( O4 ), lastN = v3( P4.y, P4.z, P4.w );
 			V3 throughput = v3( T4 );
 			const float bsdfPdf = T4.w;
-			float* px = reinterpret_cast<float*>( accumulator + pixelIdx );
-			if (pathLength == 1) atomicAdd( px + 3, prim < 0 ? 10000.f : hit.w ); // depth for the DOF / filter passes (pathtracer.h:74)
+			// The path's own contribution slots (see accumulateKernel).  The first vertex initialises both by plain stores (every path
+			// passes here exactly once, before its first connect wave): slotS with what the vertex adds itself (skydome, a light that was
+			// hit) and the depth for the DOF / filter passes (pathtracer.h:74), slotC with zero.  Later vertices add.  One kernel per wave
+			// touches a slot at most once and the waves are ordered: no race, fixed order.
+			const float depth = prim < 0 ? 10000.f : hit.w;
+			bool stored = false;
+			auto contribute = [&]( const V3 v ) {
+				if (pathLength == 1) c.slotS[slot] = make_float4( v.x, v.y, v.z, depth ), stored = true;
+				else { float* px = reinterpret_cast<float*>( c.slotS + slot ); atomicAdd( px, v.x ), atomicAdd( px + 1, v.y ), atomicAdd( px + 2, v.z ); }
+			};
+			if (pathLength == 1) c.slotC[slot] = make_float4( 0.f, 0.f, 0.f, 0.f );
 			if (prim < 0)
 			{
 				// the path left the scene: skydome (pathtracer.h:77-84)
-				const V3 c = ClampAndFix( throughput * SampleSkydome( f, D ) * (1.0f / bsdfPdf), f.clampValue );
-				atomicAdd( px, c.x ), atomicAdd( px + 1, c.y ), atomicAdd( px + 2, c.z );
+				contribute( ClampAndFix( throughput * SampleSkydome( f, D ) * (1.0f / bsdfPdf), f.clampValue ) );
 			}
 			else
 			{
@@ -569,7 +604,7 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 				if (mflags & M_DIFFUSEMAP)
 				{
 					c3 = __ldg( materials + mat * MAT_STRIDE + 3 ), c4 = __ldg( materials + mat * MAT_STRIDE + 4 );
-					const float lambda = a3.w + log2f( f.spreadAngle * hit.w * (1.0f / fabsf( dot( D, N ) )) );
+					const float lambda = a3.w + log2f( __ldg( &pass->spreadAngle ) * hit.w * (1.0f / fabsf( dot( D, N ) )) );
 					const float4 texel = FetchTexelTrilinear( f.texels, lambda, c3.x * (c3.z + tu), c3.y * (c3.w + tv), __float_as_uint( c2.w ),
 						(int)__float_as_uint( c4.x ), (int)__float_as_uint( c4.y ), (int)__float_as_uint( c1.w ) );
 					if ((mflags & 2u) && texel.w < 0.5f)
@@ -626,9 +661,14 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 						if (pathLength > 1 && !(flags & S_SPECULAR))
 						{
 							// the previous vertex did NEE: weigh this implicit connection against it (MIS)
+							// which light triangle this is: CoreTri::ltriIdx where the mesh came with CoreTris (kept + 1 in the attribute
+							// record; pathtracer.h:139 reads it the same way), else a search for (prim, inst) among the area lights
 							int ltri = -1;
 							float area = 0;
-							for (int i = 0; i < f.areaCount; i++)
+							const int stored = vertexNormals ? __float_as_int( __ldg( vertexNormals + (size_t)(__float_as_uint( info.x ) + prim) * TRI_ATTR_STRIDE + 6 ).y ) - 1 : -1;
+							if (stored >= 0 && stored < f.areaCount && __float_as_int( __ldg( f.areaLights + stored * 6 + 3 ).w ) == prim &&
+								__float_as_int( __ldg( f.areaLights + stored * 6 + 4 ).w ) == (int)inst) ltri = stored, area = __ldg( f.areaLights + stored * 6 + 1 ).w;
+							else for (int i = 0; i < f.areaCount; i++)
 								if (__float_as_int( __ldg( f.areaLights + i * 6 + 3 ).w ) == prim && __float_as_int( __ldg( f.areaLights + i * 6 + 4 ).w ) == (int)inst)
 									ltri = i, area = __ldg( f.areaLights + i * 6 + 1 ).w;
 							const float lightPdf = ltri >= 0 ? (hit.w * hit.w) / (DdotNL * area) : 0.f;    // CalculateLightPDF, lights_shared.h:96-99
@@ -636,14 +676,13 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 							const float w = bsdfPdf + lightPdf * pickProb;
 							c = w > 0 ? c * (1.0f / w) : v3( 0.f, 0.f, 0.f );
 						}
-						c = ClampAndFix( c, f.clampValue );
-						atomicAdd( px, c.x ), atomicAdd( px + 1, c.y ), atomicAdd( px + 2, c.z );
+						contribute( ClampAndFix( c, f.clampValue ) );
 					}
 				}
 				else
 				{
 					if (roughness <= 0.001f || transmission > 0.999f) flags |= S_SPECULAR; else flags &= ~S_SPECULAR; // pathtracer.h:151
-					uint32_t seed = WangHash( pathIdx * 17 + f.R0 + (uint32_t)pathLength * 91771u ); // :154; R0 changes per bounce (rendercore.cpp:716)
+					uint32_t seed = WangHash( pathIdx * 17 + __ldg( &pass->R0 ) + (uint32_t)pathLength * 91771u ); // :154; R0 changes per bounce (rendercore.cpp:716)
 					const float faceDir = dot( D, N ) > 0 ? -1.f : 1.f;
 					const V3 gF = N * faceDir, sF = sN * faceDir; // geometric / shading normal on the side the ray came from
 					if (faceDir == 1) absorption = v3( 0.f, 0.f, 0.f ); // the ray travelled outside the medium (:158)
@@ -652,10 +691,11 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					if (!(flags & S_SPECULAR) && f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0)
 					{
 						// (the reference draws these two from the blue-noise table for the first TWO samples only, pathtracer.h:168)
-						const int sampleIdx = (int)(pathIdx / f.pixelCount), bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
-						const bool blue = f.blueNoise && sampleIdx < 2;
-						const float r0 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 4 + 4 * pathLength ) : RandomFloat( seed );
-						const float r1 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 5 + 4 * pathLength ) : RandomFloat( seed );
+						const int sampleIdx = (int)sampleIdxU, bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
+						const uint32_t* const blueTable = __ldg( &pass->blue ) ? f.blueTable : nullptr;
+						const bool blue = blueTable && sampleIdx < 2;
+						const float r0 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 4 + 4 * pathLength ) : RandomFloat( seed );
+						const float r1 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 5 + 4 * pathLength ) : RandomFloat( seed );
 						float pickProb, lightPdf;
 						V3 lightColor;
 						V3 L = RandomPointOnLight( f, r0, r1, I, sF, pickProb, lightPdf, lightColor ) - I;
@@ -682,10 +722,11 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					const bool enough = (f.bounceCap == 1 && (flags & S_BOUNCED)) || (f.bounceCap == 2 && (flags & S_BOUNCEDTWICE));
 					if (!enough && pathLength < maxPathLength)
 					{
-						const int sampleIdx = (int)(pathIdx / f.pixelCount), bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
-						const bool blue = f.blueNoise && sampleIdx < 256; // pathtracer.h:212-222
-						const float r3 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 6 + 4 * pathLength ) : RandomFloat( seed );
-						const float r4 = blue ? BlueNoiseSampler( f.blueNoise, bx, by, sampleIdx, 7 + 4 * pathLength ) : RandomFloat( seed );
+						const int sampleIdx = (int)sampleIdxU, bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
+						const uint32_t* const blueTable = __ldg( &pass->blue ) ? f.blueTable : nullptr;
+						const bool blue = blueTable && sampleIdx < 256; // pathtracer.h:212-222
+						const float r3 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 6 + 4 * pathLength ) : RandomFloat( seed );
+						const float r4 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 7 + 4 * pathLength ) : RandomFloat( seed );
 						// SampleBSDF (lambert.h:71-123)
 						V3 R = sF, bsdf = v3( 0.f, 0.f, 0.f );
 						float newPdf = 1;
@@ -764,21 +805,22 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					}
 				}
 			}
+			if (pathLength == 1 && !stored) c.slotS[slot] = make_float4( 0.f, 0.f, 0.f, depth );
 		}
 		uint32_t sslot, eslot;
 		blockAppend2<4>( counters + shadowCounter( pathLength ), wantShadow, wantExt, sWarp, sslot, eslot ); // [2 len] shadow, [2 len + 1] = extension of len + 1
 		if (wantShadow)
 		{
-			conO[sslot] = make_float4( so.x, so.y, so.z, f.epsilon );
-			conD[sslot] = make_float4( sl.x, sl.y, sl.z, sdist );
-			conE[sslot] = make_float4( se.x, se.y, se.z, __uint_as_float( pixelIdx ) );
+			c.conO[sslot] = make_float4( so.x, so.y, so.z, f.epsilon );
+			c.conD[sslot] = make_float4( sl.x, sl.y, sl.z, sdist );
+			c.conE[sslot] = make_float4( se.x, se.y, se.z, __uint_as_float( slot ) ); // the connect wave adds to slotC[slot]
 		}
 		if (wantExt)
 		{
-			rayOout[eslot] = make_float4( eo.x, eo.y, eo.z, f.epsilon );
-			rayDout[eslot] = make_float4( er.x, er.y, er.z, 1e34f );
-			pathStateOut[eslot] = make_float4( et.x, et.y, et.z, epdf );
-			pathInfoOut[eslot] = make_float4( __uint_as_float( pathIdx | (flags << PATHIDX_BITS) ), en.x, en.y, en.z );
+			c.rayOout[eslot] = make_float4( eo.x, eo.y, eo.z, f.epsilon );
+			c.rayDout[eslot] = make_float4( er.x, er.y, er.z, 1e34f );
+			c.stateOut[eslot] = make_float4( et.x, et.y, et.z, epdf );
+			c.infoOut[eslot] = make_float4( __uint_as_float( pathIdx | (flags << PATHIDX_BITS) ), en.x, en.y, en.z );
 		}
 	}
 }
@@ -806,6 +848,38 @@ __global__ void disneyProbeKernel( const int n, const int mode, const float* __r
 	o[0] = wiw.x, o[1] = wiw.y, o[2] = wiw.z, o[3] = pdf, o[4] = value.x, o[5] = value.y, o[6] = value.z, o[7] = specular ? 1.f : 0.f;
 }
 
+// Deterministic accumulation.  The reference adds every contribution straight into accumulator[pixel] (non-atomic RMW, racy for
+// spp > 1: connections.h:33); float atomics fix the race but leave the ORDER of a pixel's adds to the scheduler as soon as several
+// samples of a pixel are in flight in one pass, so the same frame would differ in the last bits from run to run and from one sharding
+// to another.  Here every path owns two slots for the pass -- slotS for what its vertices add (shade waves, in wave order), slotC for
+// its next-event contributions (connect waves, in wave order) -- and this kernel folds them into the accumulator, samples in
+// ascending order: acc = ((acc + S_0) + C_0) + S_1 ...  The result depends on neither the pass partition, the chain count nor the
+// tile sharding: a tile-sharded multi-GPU frame is bit-identical to the single-GPU one at any spp.  With `frame` set the kernel also
+// writes the finalized frame (lib/CUDA/shared_kernel_code/finalize_shared.h:29-45) -- the last pass of an unsharded frame.
+__global__ void __launch_bounds__( 256 ) accumulateKernel( const FrameParams f, const PassParams* __restrict__ pass, const uint32_t chain, const uint32_t chainTiles,
+	const float4* __restrict__ slotS, const float4* __restrict__ slotC, float4* __restrict__ accumulator, float4* __restrict__ frame )
+{
+	const uint32_t perSample = chainTiles * TILE_PIXELS, samples = __ldg( &pass->samplesThisPass );
+	const float scale = __ldg( &pass->finalScale );
+	for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < perSample; q += gridDim.x * blockDim.x)
+	{
+		const uint32_t chainTile = q / TILE_PIXELS, inTile = q % TILE_PIXELS;
+		const uint32_t tile = (chainTile * f.chainCount + chain) * f.shardCount + f.shardIndex;
+		const uint32_t x = (tile % f.tilesX) * TILE_W + (inTile % TILE_W), y = (tile / f.tilesX) * TILE_H + inTile / TILE_W;
+		if (x >= f.width || y >= f.height) continue;
+		const uint32_t pixel = x + y * f.width;
+		float4 a = accumulator[pixel];
+		for (uint32_t s = 0; s < samples; s++)
+		{
+			const float4 S = __ldcs( slotS + (size_t)s * perSample + q ), C = __ldcs( slotC + (size_t)s * perSample + q );
+			a.x += S.x, a.y += S.y, a.z += S.z, a.w += S.w;
+			a.x += C.x, a.y += C.y, a.z += C.z;
+		}
+		accumulator[pixel] = a;
+		if (frame) frame[pixel] = make_float4( a.x * scale, a.y * scale, a.z * scale, 1.0f );
+	}
+}
+
 // lib/CUDA/shared_kernel_code/finalize_shared.h:29-45: accumulator * 1/samples -> render target (here: a device buffer)
 __global__ void finalizeKernel( const float4* __restrict__ accumulator, float4* __restrict__ frame, const uint32_t pixels, const float scale )
 {
@@ -831,8 +905,9 @@ struct PeerTable {
 // arrival: tell every rank that `rank` has reached `epoch`, then wait until every rank has told us.  One block, one thread per
 // rank.  The stores are system-scope releases after a system fence, so what earlier kernels of this stream wrote (the
 // accumulator) is visible to a peer that has seen the flag.  A peer that never arrives makes the wait give up after ~2 s and
-// raise *timeout, instead of hanging the device.
-__global__ void peerBarrierKernel( const PeerTable peers, const int world, const int rank, const uint32_t epoch, uint32_t* timeout )
+// raise *timeout, instead of hanging the device (limit: Setting peerTimeoutMs, converted to SM clock ticks by the host); the pull
+// kernel that follows does nothing when the flag is up, and the host clears the flag after reporting the error.
+__global__ void peerBarrierKernel( const PeerTable peers, const int world, const int rank, const uint32_t epoch, uint32_t* timeout, const long long limitTicks )
 {
 	const int t = threadIdx.x;
 	if (t >= world) return;
@@ -845,14 +920,15 @@ __global__ void peerBarrierKernel( const PeerTable peers, const int world, const
 		uint32_t v;
 		asm volatile( "ld.acquire.sys.global.u32 %0, [%1];" : "=r"( v ) : "l"( mine ) : "memory" );
 		if ((int32_t)(v - epoch) >= 0) break;
-		if (clock64() - t0 > 4000000000ll) { atomicExch( timeout, 1u ); break; }
+		if (clock64() - t0 > limitTicks) { atomicExch( timeout, 1u ); break; }
 		__nanosleep( 200 );
 	}
 }
 
 __global__ void gatherFinalizeKernel( const PeerTable peers, const int world, const int rank, float4* __restrict__ frame, const uint32_t width,
-	const uint32_t height, const uint32_t tilesX, const float scale )
+	const uint32_t height, const uint32_t tilesX, const float scale, const uint32_t* __restrict__ timeout )
 {
+	if (*timeout) return; // a peer did not arrive: its tiles may be incomplete, nothing is pulled this frame
 	const uint32_t pixels = width * height;
 	float4* const own = peers.acc[rank];
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < pixels; i += gridDim.x * blockDim.x)
@@ -874,12 +950,66 @@ __global__ void gatherFinalizeKernel( const PeerTable peers, const int world, co
 
 } // namespace
 
+constexpr int MAX_CHAINS = 4;
+constexpr int COUNTER_STRIDE = (COUNTER_WORDS + 15) & ~15; // one chain's counters of one pass (64-byte aligned)
+constexpr int FETCH_BASE = 16;                               // fetch-counter words 16 + 4 chain + {0,1: extend, 2,3: connect}, see enqueueFrame
+
+// growable page-locked host array (the frame's uploads and downloads must not be pageable: they run inside the frame, maybe in a graph)
+struct PinnedBuffer {
+	void* ptr = nullptr;
+	size_t bytes = 0;
+	cudaError_t reserve( size_t need )
+	{
+		if (need <= bytes) return cudaSuccess;
+		if (ptr) cudaFreeHost( ptr );
+		ptr = nullptr, bytes = 0;
+		const size_t cap = (need * 2 + 4095) & ~(size_t)4095;
+		cudaError_t e = cudaHostAlloc( &ptr, cap, cudaHostAllocDefault );
+		if (e == cudaSuccess) bytes = cap;
+		return e;
+	}
+	void release() { if (ptr) cudaFreeHost( ptr ); ptr = nullptr, bytes = 0; }
+};
+
+// One chain of waves (see ChainArgs): buffers for its share of a pass, two streams, the events that order them
+struct Chain {
+	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO[2], conD[2], conE[2], slotS, slotC;
+	uint32_t capacity = 0; // paths per pass the buffers hold
+	cudaStream_t main = nullptr, connect = nullptr;
+	cudaEvent_t shadeDone[MAX_PATH_LENGTH + 1] = {}, connectDone[MAX_PATH_LENGTH + 1] = {}, done = nullptr;
+	DeviceBuffer* all( int i )
+	{
+		DeviceBuffer* b[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &state[0], &state[1], &info[0], &info[1], &hits, &conO[0], &conO[1], &conD[0], &conD[1],
+			&conE[0], &conE[1], &slotS, &slotC };
+		return i < 17 ? b[i] : nullptr;
+	}
+};
+
+// Everything enqueueFrame reads that is not a stream or an event.  Plain data on purpose: its bytes are the key of the captured frame
+// graph -- a frame whose plan equals the previous one's replays the graph, anything else (resolution, spp, lights, a reallocated
+// buffer ...) re-enqueues.  What changes every frame without changing the plan (camera, sample numbering) is in PassParams.
+struct FramePlan {
+	FrameParams f;
+	TraceArgs trace;                 // scene pools (RenderCore::baseArgs)
+	const float4 *shadePool, *vnormPool, *instShadePool, *materials;
+	float4 *accumulator, *frame;
+	PassParams *passDev, *passHost;
+	uint32_t *countersDev, *countersHost, *fetchCounters;
+	struct { float4 *rayO[2], *rayD[2], *state[2], *info[2], *hits, *conO[2], *conD[2], *conE[2], *slotS, *slotC; uint32_t tiles, capacity; } chain[MAX_CHAINS];
+	uint32_t chains, passes, maxLen, overlap, anyLight, bsdf, clearAccumulator, timedPasses;
+	int isect, smCount, shadeGrid;
+};
+
 struct WavefrontState {
 	int width = 0, height = 0, spp = 1, maxPathLength = 5;
 	int shardIndex = 0, shardCount = 1, sampleOffset = 0, jitter = 1;
+	int chains = 0;        // Setting chains: 0 = automatic (by the size of a pass), else 1..MAX_CHAINS
+	int useGraph = 1;      // Setting frameGraph: a frame whose plan repeats is replayed as a CUDA graph
+	int waveTimers = 1;    // Setting waveTimers: per-wave CUDA events for the CoreStats trace / shade times
 	uint32_t pathsPerPass = 32u << 20;
-	uint32_t capacity = 0; // rays per buffer
-	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO, conD, conE, counters, accumOwn, frame, materials, lights, skyImage, texels, blueNoise;
+	Chain chain[MAX_CHAINS];
+	DeviceBuffer counters, passParams, accumOwn, frame, materials, lights, skyImage, texels, blueNoise;
+	PinnedBuffer hostPass, hostCounters;
 	bool haveBlueNoise = false;
 	struct TextureRec { uint32_t offset, width, height, mipLevels; bool valid; };
 	std::vector<TextureRec> textures;
@@ -891,16 +1021,20 @@ struct WavefrontState {
 	int bounceCap = 0, roulette = 1, bsdf = 0; // bsdf: 0 = Lambert + speculars, 1 = Disney principled (rendercore_optix7/kernels/bsdf.h picks one at compile time)
 	uint32_t samplesTaken = 0, frameCounter = 0;
 	int probeX = -1, probeY = -1;
-	cudaEvent_t ev[2 + 6 * MAX_PATH_LENGTH] = {}; // frame begin/end, then per path length: extend begin/end, shade begin/end, connect begin/end
-	// the connect (shadow) wave of bounce k runs on its own stream beside the extend wave of bounce k+1 (Setting overlapConnect)
-	cudaStream_t connectStream = nullptr;
-	cudaEvent_t shadeDone[MAX_PATH_LENGTH + 1] = {}, connectDone[MAX_PATH_LENGTH + 1] = {};
+	cudaEvent_t frameBegin = nullptr, frameEnd = nullptr, fork = nullptr, gatherBegin = nullptr, gatherEnd = nullptr;
+	std::vector<cudaEvent_t> timers; // per (timed pass, chain, path length): extend begin, extend end, shade end, connect begin, connect end
 	int overlapConnect = 1;
+	// the captured frame
+	cudaStream_t captureStream = nullptr;
+	cudaGraphExec_t graphExec = nullptr;
+	std::vector<uint8_t> graphKey, lastKey;
+	uint32_t graphLaunches = 0, graphCaptures = 0;
 	float4* accumulator() { return accumExternal ? accumExternal : (float4*)accumOwn.ptr; }
 	// peer-memory gather (OpenPeers): the other ranks' accumulators and arrival flags, mapped through CUDA IPC
 	PeerTable peers{};
 	int peerWorld = 0, peerRank = 0;
 	uint32_t peerEpoch = 0;
+	float peerTimeoutMs = 2000.f;
 	void* peerMapped[2 * MAX_PEERS] = {};
 	DeviceBuffer peerFlags; // MAX_PEERS arrival words + 1 timeout word, written by the peers
 	void closePeers()
@@ -908,17 +1042,31 @@ struct WavefrontState {
 		for (void*& p : peerMapped) if (p) { cudaIpcCloseMemHandle( p ); p = nullptr; }
 		peerWorld = 0;
 	}
+	void dropGraph()
+	{
+		if (graphExec) cudaGraphExecDestroy( graphExec );
+		graphExec = nullptr, graphKey.clear(), lastKey.clear();
+	}
 	~WavefrontState()
 	{
-		DeviceBuffer* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &state[0], &state[1], &info[0], &info[1], &hits, &conO, &conD, &conE, &counters,
-			&accumOwn, &frame, &materials, &lights, &skyImage, &texels, &blueNoise };
+		DeviceBuffer* all[] = { &counters, &passParams, &accumOwn, &frame, &materials, &lights, &skyImage, &texels, &blueNoise };
 		closePeers();
+		dropGraph();
 		peerFlags.release();
 		for (DeviceBuffer* b : all) b->release();
-		for (cudaEvent_t e : ev) if (e) cudaEventDestroy( e );
-		for (cudaEvent_t e : shadeDone) if (e) cudaEventDestroy( e );
-		for (cudaEvent_t e : connectDone) if (e) cudaEventDestroy( e );
-		if (connectStream) cudaStreamDestroy( connectStream );
+		hostPass.release(), hostCounters.release();
+		for (Chain& c : chain)
+		{
+			for (int i = 0; c.all( i ); i++) c.all( i )->release();
+			for (cudaEvent_t e : c.shadeDone) if (e) cudaEventDestroy( e );
+			for (cudaEvent_t e : c.connectDone) if (e) cudaEventDestroy( e );
+			if (c.done) cudaEventDestroy( c.done );
+			if (c.main) cudaStreamDestroy( c.main );
+			if (c.connect) cudaStreamDestroy( c.connect );
+		}
+		for (cudaEvent_t e : timers) if (e) cudaEventDestroy( e );
+		for (cudaEvent_t e : { frameBegin, frameEnd, fork, gatherBegin, gatherEnd }) if (e) cudaEventDestroy( e );
+		if (captureStream) cudaStreamDestroy( captureStream );
 	}
 };
 
@@ -941,6 +1089,10 @@ int RenderCore::SettingWavefront( const char* name, float value )
 	if (!strcmp( name, "jitter" )) { w->jitter = value >= 0.5f; return 0; }
 	if (!strcmp( name, "clampValue" )) { if (!(value > 0)) return fail( "Setting clampValue: > 0" ); w->clampValue = value; return 0; }
 	if (!strcmp( name, "overlapConnect" )) { w->overlapConnect = value >= 0.5f; return 0; }
+	if (!strcmp( name, "chains" )) { if (v < 0 || v > MAX_CHAINS) return fail( "Setting chains: 0 (automatic) or 1..4" ); w->chains = v; return 0; }
+	if (!strcmp( name, "frameGraph" )) { w->useGraph = value >= 0.5f; if (!w->useGraph) w->dropGraph(); return 0; }
+	if (!strcmp( name, "waveTimers" )) { w->waveTimers = value >= 0.5f; return 0; }
+	if (!strcmp( name, "peerTimeoutMs" )) { if (!(value > 0)) return fail( "Setting peerTimeoutMs: > 0" ); w->peerTimeoutMs = value; return 0; }
 	if (!strcmp( name, "russianRoulette" )) { w->roulette = value >= 0.5f; return 0; }
 	if (!strcmp( name, "bsdf" )) { if (v < 0 || v > 1) return fail( "Setting bsdf: 0 (Lambert, lib/sharedBSDFs/lambert.h) or 1 (Disney, disney.h)" ); w->bsdf = v; return 0; }
 	if (!strcmp( name, "diffuseBounceCap" )) { if (v < 0 || v > 2) return fail( "Setting diffuseBounceCap: 0 (off), 1 or 2" ); w->bounceCap = v; return 0; }
@@ -953,17 +1105,26 @@ int RenderCore::SetTarget( int width, int height, int spp )
 {
 	if (width <= 0 || height <= 0 || spp <= 0) return fail( "SetTarget: width, height and spp must be positive" );
 	WavefrontState* w = state( wf );
-	w->width = width, w->height = height, w->spp = spp;
 	const size_t px = (size_t)width * height;
 	cudaError_t e;
+	// peers have this core's accumulator mapped: if it has to move, the mappings are void on every rank -- close ours; the host
+	// layer exchanges handles again (b200_peer_handle / b200_open_peers) before the next b200_gather_finalize
+	if (w->peerWorld > 0 && px * 16 > w->accumOwn.bytes) { cudaStreamSynchronize( stream ); w->closePeers(); }
+	w->width = width, w->height = height, w->spp = spp;
 	if ((e = w->accumOwn.reserve( px * 16, false, stream )) != cudaSuccess || (e = w->frame.reserve( px * 16, false, stream )) != cudaSuccess) return fail( "SetTarget buffers", e );
-	if ((e = w->counters.reserve( sizeof( uint32_t ) * COUNTER_WORDS, false, stream )) != cudaSuccess) return fail( "SetTarget counters", e );
 	if ((e = cudaMemsetAsync( w->accumulator(), 0, px * 16, stream )) != cudaSuccess) return fail( "SetTarget clear", e );
 	w->samplesTaken = 0;
-	for (cudaEvent_t& ev : w->ev) if (!ev && (e = cudaEventCreate( &ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
-	for (cudaEvent_t& ev : w->shadeDone) if (!ev && (e = cudaEventCreateWithFlags( &ev, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
-	for (cudaEvent_t& ev : w->connectDone) if (!ev && (e = cudaEventCreateWithFlags( &ev, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
-	if (!w->connectStream && (e = cudaStreamCreateWithFlags( &w->connectStream, cudaStreamNonBlocking )) != cudaSuccess) return fail( "connect stream", e );
+	for (cudaEvent_t* ev : { &w->frameBegin, &w->frameEnd }) if (!*ev && (e = cudaEventCreate( ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
+	if (!w->fork && (e = cudaEventCreateWithFlags( &w->fork, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
+	if (!w->captureStream && (e = cudaStreamCreateWithFlags( &w->captureStream, cudaStreamNonBlocking )) != cudaSuccess) return fail( "capture stream", e );
+	for (Chain& c : w->chain)
+	{
+		for (cudaEvent_t& ev : c.shadeDone) if (!ev && (e = cudaEventCreateWithFlags( &ev, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
+		for (cudaEvent_t& ev : c.connectDone) if (!ev && (e = cudaEventCreateWithFlags( &ev, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
+		if (!c.done && (e = cudaEventCreateWithFlags( &c.done, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
+		if (!c.main && (e = cudaStreamCreateWithFlags( &c.main, cudaStreamNonBlocking )) != cudaSuccess) return fail( "chain stream", e );
+		if (!c.connect && (e = cudaStreamCreateWithFlags( &c.connect, cudaStreamNonBlocking )) != cudaSuccess) return fail( "chain stream", e );
+	}
 	return 0;
 }
 
@@ -1059,9 +1220,11 @@ int RenderCore::SetTextures( const void* coreTexDescs, int count )
 }
 
 // CoreAPI_Base::SetMaterials (core_api_base.h:100; after SetTextures, :99): CoreMaterial[count], 688 bytes each
-// (common_classes.h:177-238).  The Lambert stage keeps color.value (offset 0) with its map (textureID 12, uvscale 24, uvoffset 32),
-// flags (160; 1 = SMOOTH, 2 = HASALPHA, host_material.h:66-71), absorption.value (168; stored as 1 - absorption like
-// rendercore_optix7/rendercore.cpp:529-531), roughness.value (304), transmission.value (528) and eta.value (560).
+// (common_classes.h:177-238), read through the restated struct of include/lh2_abi.h (layout pinned there by static_asserts:
+// float2 is 8-byte aligned in the reference, common_types.h:62, so a Vec3Value keeps uvscale at +24 and uvoffset at +32).
+// The Lambert stage keeps color (value + map), flags (1 = SMOOTH, 2 = HASALPHA, host_material.h:66-71), absorption.value (stored as
+// 1 - absorption like rendercore_optix7/rendercore.cpp:529-531), roughness, transmission and eta; the other maps are detailColor,
+// normals, detailNormals and the roughness map.
 int RenderCore::SetMaterials( const void* coreMaterials, int count )
 {
 	if (count < 0 || (count > 0 && !coreMaterials)) return fail( "SetMaterials: bad arguments" );
@@ -1070,34 +1233,31 @@ int RenderCore::SetMaterials( const void* coreMaterials, int count )
 	std::vector<MaterialMap> maps( (size_t)count * 4 );
 	for (int i = 0; i < count; i++)
 	{
-		const char* m = (const char*)coreMaterials + (size_t)i * 688;
-		// the other maps: detailColor @40, normals @80, detailNormals @120 (Vec3Value: textureID +12, scale +16, uvscale +20, uvoffset +28),
-		// roughness @304 (ScalarValue: textureID +4, scale +12, uvscale +16, uvoffset +24)
-		static const int mapAt[4][4] = { { 52, 56, 60, 68 }, { 92, 96, 100, 108 }, { 132, 136, 140, 148 }, { 308, 316, 320, 328 } };
-		for (int k = 0; k < 4; k++)
+		lh2abi::CoreMaterial m;
+		memcpy( &m, (const char*)coreMaterials + (size_t)i * sizeof( m ), sizeof( m ) ); // the caller's array need not be aligned for us
+		const lh2abi::CoreMaterial::Vec3Value* vmaps[3] = { &m.detailColor, &m.normals, &m.detailNormals };
+		for (int k = 0; k < 3; k++)
 		{
 			MaterialMap& mm = maps[(size_t)i * 4 + k];
-			memcpy( &mm.texture, m + mapAt[k][0], 4 ), memcpy( &mm.scale, m + mapAt[k][1], 4 ), memcpy( mm.uvscale, m + mapAt[k][2], 8 ), memcpy( mm.uvoffset, m + mapAt[k][3], 8 );
+			mm.texture = vmaps[k]->textureID, mm.scale = vmaps[k]->scale;
+			mm.uvscale[0] = vmaps[k]->uvscale.x, mm.uvscale[1] = vmaps[k]->uvscale.y, mm.uvoffset[0] = vmaps[k]->uvoffset.x, mm.uvoffset[1] = vmaps[k]->uvoffset.y;
+		}
+		{
+			MaterialMap& mm = maps[(size_t)i * 4 + 3];
+			mm.texture = m.roughness.textureID, mm.scale = m.roughness.scale;
+			mm.uvscale[0] = m.roughness.uvscale.x, mm.uvscale[1] = m.roughness.uvscale.y, mm.uvoffset[0] = m.roughness.uvoffset.x, mm.uvoffset[1] = m.roughness.uvoffset.y;
 		}
 		float* t = &table[(size_t)i * 16];
-		uint32_t flags;
-		int32_t textureID;
-		float absorption[3];
-		memcpy( t, m, 12 ), memcpy( t + 3, m + 304, 4 ), memcpy( t + 4, m + 528, 4 ), memcpy( t + 5, m + 560, 4 ), memcpy( &flags, m + 160, 4 );
-		memcpy( absorption, m + 168, 12 ), memcpy( &textureID, m + 12, 4 ), memcpy( t + 12, m + 24, 16 );
-		t[6] = (float)(flags & 3u);
-		t[8] = 1 - absorption[0], t[9] = 1 - absorption[1], t[10] = 1 - absorption[2];
-		t[11] = (float)textureID;
+		t[0] = m.color.value.x, t[1] = m.color.value.y, t[2] = m.color.value.z, t[3] = m.roughness.value;
+		t[4] = m.transmission.value, t[5] = m.eta.value, t[6] = (float)(m.flags & 3u);
+		t[8] = 1 - m.absorption.value.x, t[9] = 1 - m.absorption.value.y, t[10] = 1 - m.absorption.value.z;
+		t[11] = (float)m.color.textureID;
+		t[12] = m.color.uvscale.x, t[13] = m.color.uvscale.y, t[14] = m.color.uvoffset.x, t[15] = m.color.uvoffset.y;
 		// the Disney parameters as 0.8 fixed point, four to a word (TOUINT4, rendercore_optix7/rendercore.cpp:511-512, 532-534):
-		// ScalarValue::value of metallic @208, subsurface @240, specular @272, roughness @304 | specularTint @336, anisotropic @368,
-		// sheen @400, sheenTint @432 | clearcoat @464, clearcoatGloss @496, transmission @528
-		static const int offsets[11] = { 208, 240, 272, 304, 336, 368, 400, 432, 464, 496, 528 };
-		for (int k = 0; k < 11; k++)
-		{
-			float value;
-			memcpy( &value, m + offsets[k], 4 );
-			words[(size_t)i * 3 + k / 4] += (uint32_t)(value * 255.0f) << (8 * (k & 3));
-		}
+		// metallic, subsurface, specular, roughness | specularTint, anisotropic, sheen, sheenTint | clearcoat, clearcoatGloss, transmission
+		const float disney[11] = { m.metallic.value, m.subsurface.value, m.specular.value, m.roughness.value, m.specularTint.value, m.anisotropic.value,
+			m.sheen.value, m.sheenTint.value, m.clearcoat.value, m.clearcoatGloss.value, m.transmission.value };
+		for (int k = 0; k < 11; k++) words[(size_t)i * 3 + k / 4] += (uint32_t)(disney[k] * 255.0f) << (8 * (k & 3));
 	}
 	return uploadMaterials( table.data(), words.data(), maps.data(), count );
 }
@@ -1207,6 +1367,99 @@ int RenderCore::SetProbe( int x, int y )
 	return 0;
 }
 
+// ---- one frame, enqueued ------------------------------------------------------------------------------------------------
+// Replaces the host-driven wave loop of the reference (lib/rendercore_optix7/rendercore.cpp:692-748: per bounce a launch, a counter
+// read-back and a synchronisation) by ONE enqueue of the whole frame -- all passes, all chains -- with no host involvement between
+// its first and its last operation:
+//   origin:  upload PassParams, clear counters (+ accumulator on Restart) --fork--> chains --join--> counter download
+//   chain c: per pass  generate -> [extend(len) -> shade(len) -> (connect(len) on the chain's second stream)]* -> accumulate
+// Wave sizes live in device counters (TraceArgs::countPtr), grids are persistent, so nothing in the sequence depends on a value the
+// host would have to read; that also makes the sequence capturable as a CUDA graph (`capturing`: timer events become event-record
+// nodes).  Returns the number of kernels enqueued through *launches.
+static cudaError_t enqueueFrame( WavefrontState& w, const FramePlan& p, cudaStream_t origin, const bool capturing, uint32_t* launches )
+{
+	cudaError_t e;
+	uint32_t n = 0;
+	const unsigned recFlags = capturing ? cudaEventRecordExternal : cudaEventRecordDefault;
+	auto timer = [&]( uint32_t pass, uint32_t c, uint32_t len, int k, cudaStream_t s ) {
+		if (pass < p.timedPasses) cudaEventRecordWithFlags( w.timers[((size_t)(pass * p.chains + c) * p.maxLen + (len - 1)) * 5 + k], s, recFlags );
+	};
+	if ((e = cudaMemcpyAsync( p.passDev, p.passHost, sizeof( PassParams ) * p.passes, cudaMemcpyHostToDevice, origin )) != cudaSuccess) return e;
+	if ((e = cudaMemsetAsync( p.countersDev, 0, sizeof( uint32_t ) * COUNTER_STRIDE * p.chains * p.passes, origin )) != cudaSuccess) return e;
+	if ((e = cudaMemsetAsync( p.fetchCounters + FETCH_BASE, 0, sizeof( uint32_t ) * 4 * MAX_CHAINS, origin )) != cudaSuccess) return e;
+	if (p.clearAccumulator && (e = cudaMemsetAsync( p.accumulator, 0, (size_t)p.f.pixelCount * 16, origin )) != cudaSuccess) return e;
+	cudaEventRecordWithFlags( w.frameBegin, origin, recFlags );
+	cudaEventRecord( w.fork, origin );
+	for (uint32_t c = 0; c < p.chains; c++) cudaStreamWaitEvent( w.chain[c].main, w.fork, 0 );
+	const bool overlap = p.overlap && p.anyLight;
+	for (uint32_t pass = 0; pass < p.passes; pass++) for (uint32_t c = 0; c < p.chains; c++)
+	{
+		Chain& ch = w.chain[c];
+		const auto& pc = p.chain[c];
+		if (!pc.tiles) continue;
+		cudaStream_t s = ch.main;
+		const PassParams* passDev = p.passDev + pass;
+		uint32_t* counters = p.countersDev + (size_t)(pass * p.chains + c) * COUNTER_STRIDE;
+		uint32_t* fetch = p.fetchCounters + FETCH_BASE + 4 * c;
+		ChainArgs ca;
+		memset( &ca, 0, sizeof( ca ) );
+		ca.counters = counters, ca.chain = c, ca.chainTiles = pc.tiles, ca.slotS = pc.slotS, ca.slotC = pc.slotC;
+		ca.rayOout = pc.rayO[0], ca.rayDout = pc.rayD[0], ca.stateOut = pc.state[0], ca.infoOut = pc.info[0];
+		generateEyeRaysKernel<<<p.smCount * 4, 256, 0, s>>>( p.f, passDev, ca );
+		n++;
+		int in = 0;
+		for (uint32_t len = 1; len <= p.maxLen; len++)
+		{
+			const int out = in ^ 1, con = (int)(len & 1);
+			// the fetch counter of a wave kernel is zeroed by the wave before it on the same stream (TraceArgs::fetchCounterNext):
+			// two words per stream, used alternately, all zero when the frame starts
+			const uint32_t par = (pass * p.maxLen + len) & 1;
+			TraceArgs a = p.trace;
+			a.rayO = pc.rayO[in], a.rayD = pc.rayD[in], a.hits = pc.hits, a.count = pc.capacity, a.countPtr = counters + extCounter( (int)len );
+			a.fetchCounter = fetch + par, a.fetchCounterNext = fetch + (par ^ 1);
+			timer( pass, c, len, 0, s );
+			if ((e = LaunchExtend( a, (IsectMode)p.isect, false, p.smCount, s )) != cudaSuccess) return e;
+			timer( pass, c, len, 1, s );
+			// shade( len ) writes the shadow rays of set len & 1: connect( len - 2 ) must have read them
+			if (overlap && len >= 3) cudaStreamWaitEvent( s, ch.connectDone[len - 2], 0 );
+			ca.rayO = pc.rayO[in], ca.rayD = pc.rayD[in], ca.state = pc.state[in], ca.info = pc.info[in], ca.hits = pc.hits;
+			ca.rayOout = pc.rayO[out], ca.rayDout = pc.rayD[out], ca.stateOut = pc.state[out], ca.infoOut = pc.info[out];
+			ca.conO = pc.conO[con], ca.conD = pc.conD[con], ca.conE = pc.conE[con];
+			( p.bsdf ? shadeKernel<true> : shadeKernel<false> )<<<p.shadeGrid, 128, 0, s>>>( p.f, passDev, (int)len, (int)p.maxLen, ca, p.shadePool, p.vnormPool,
+				p.instShadePool, p.materials );
+			timer( pass, c, len, 2, s );
+			n += 2;
+			if (p.anyLight)
+			{
+				// connect( len ): shadow wave fused with the add of the unoccluded potentials into the paths' slotC.  On the chain's second
+				// stream it runs beside extend( len + 1 ); nothing waits for it before the end of the pass
+				cudaStream_t cs = overlap ? ch.connect : s;
+				if (overlap) { cudaEventRecord( ch.shadeDone[len], s ); cudaStreamWaitEvent( cs, ch.shadeDone[len], 0 ); }
+				TraceArgs b = p.trace;
+				b.rayO = pc.conO[con], b.rayD = pc.conD[con], b.potentials = pc.conE[con], b.accumulator = pc.slotC, b.count = pc.capacity;
+				b.countPtr = counters + shadowCounter( (int)len );
+				b.fetchCounter = fetch + 2 + par, b.fetchCounterNext = fetch + 2 + (par ^ 1);
+				timer( pass, c, len, 3, cs );
+				if ((e = LaunchShadow( b, (IsectMode)p.isect, p.smCount, cs )) != cudaSuccess) return e;
+				timer( pass, c, len, 4, cs );
+				if (overlap) cudaEventRecord( ch.connectDone[len], cs );
+				n++;
+			}
+			in = out;
+		}
+		if (overlap) cudaStreamWaitEvent( s, ch.connectDone[p.maxLen], 0 ); // the connect stream is in order: the last wave's event covers them all
+		const uint32_t perSample = pc.tiles * TILE_PIXELS;
+		const uint32_t blocks = std::min( (perSample + 255u) / 256u, (uint32_t)p.smCount * 8u );
+		accumulateKernel<<<blocks, 256, 0, s>>>( p.f, passDev, c, pc.tiles, pc.slotS, pc.slotC, p.accumulator, pass + 1 == p.passes ? p.frame : nullptr );
+		n++;
+	}
+	for (uint32_t c = 0; c < p.chains; c++) { cudaEventRecord( w.chain[c].done, w.chain[c].main ); cudaStreamWaitEvent( origin, w.chain[c].done, 0 ); }
+	if ((e = cudaMemcpyAsync( p.countersHost, p.countersDev, sizeof( uint32_t ) * COUNTER_STRIDE * p.chains * p.passes, cudaMemcpyDeviceToHost, origin )) != cudaSuccess) return e;
+	cudaEventRecordWithFlags( w.frameEnd, origin, recFlags );
+	if (launches) *launches = n;
+	return cudaGetLastError();
+}
+
 // CoreAPI_Base::Render (core_api_base.h:94).  converge: 0 = Converge (keep accumulating), 1 = Restart (clear first)
 // (common_classes.h:38-42; lib/rendercore_optix7/rendercore.cpp:627-634).
 int RenderCore::Render( const void* viewPyramid, int converge )
@@ -1217,142 +1470,184 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	if (ensureToplevel()) return 1;
 	cudaError_t e;
 	const float* vp = (const float*)viewPyramid; // pos, p1, p2, p3 (4 x float3), then 5 floats (common_classes.h:362-385)
-	FrameParams f;
-	memset( &f, 0, sizeof( f ) );
-	for (int a = 0; a < 3; a++) f.pos[a] = vp[a], f.p1[a] = vp[3 + a], f.right[a] = vp[6 + a] - vp[3 + a], f.up[a] = vp[9 + a] - vp[3 + a];
+	FramePlan plan;
+	memset( &plan, 0, sizeof( plan ) ); // (padding included: the plan's bytes are compared)
+	FrameParams& f = plan.f;
 	memcpy( f.sky, w->sky, 12 );
-	f.aperture = vp[12], f.spreadAngle = vp[13], f.distortion = vp[16];
 	f.texels = w->texels.bytes ? (const uint32_t*)w->texels.ptr : nullptr;
 	f.clampValue = w->clampValue, f.bounceCap = (uint32_t)w->bounceCap, f.roulette = (uint32_t)w->roulette;
 	f.areaCount = w->lightCounts[0], f.pointCount = w->lightCounts[1], f.spotCount = w->lightCounts[2], f.dirCount = w->lightCounts[3];
 	f.areaLights = (const float4*)w->lights.ptr, f.pointLights = f.areaLights + f.areaCount * 6, f.spotLights = f.pointLights + f.pointCount * 2;
 	f.dirLights = f.spotLights + f.spotCount * 3;
-	const bool anyLight = f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0;
-	const bool overlap = anyLight && w->overlapConnect;
+	plan.anyLight = f.areaCount + f.pointCount + f.spotCount + f.dirCount > 0;
+	plan.overlap = (uint32_t)w->overlapConnect;
 	if (w->skyWidth) f.skyPixels = (const float4*)w->skyImage.ptr, f.skyWidth = w->skyWidth, f.skyHeight = w->skyHeight;
+	f.blueTable = w->haveBlueNoise ? (const uint32_t*)w->blueNoise.ptr : nullptr;
 	f.epsilon = epsilon, f.width = (uint32_t)w->width, f.height = (uint32_t)w->height, f.pixelCount = f.width * f.height;
 	f.tilesX = (f.width + TILE_W - 1) / TILE_W, f.tilesY = (f.height + TILE_H - 1) / TILE_H;
 	const uint32_t nTiles = f.tilesX * f.tilesY;
 	f.shardIndex = (uint32_t)w->shardIndex, f.shardCount = (uint32_t)w->shardCount;
-	f.ownTiles = nTiles > f.shardIndex ? (nTiles - f.shardIndex + f.shardCount - 1) / f.shardCount : 0;
+	const uint32_t ownTiles = nTiles > f.shardIndex ? (nTiles - f.shardIndex + f.shardCount - 1) / f.shardCount : 0;
 	f.jitter = (uint32_t)w->jitter, f.materialCount = w->materialCount;
 	f.probePixel = (w->probeX >= 0 && w->probeY >= 0 && w->probeX < w->width && w->probeY < w->height) ? w->probeX + w->probeY * w->width : -1;
-	const size_t px = (size_t)f.pixelCount;
-	if (converge == 1 || w->samplesTaken == 0)
-	{
-		if ((e = cudaMemsetAsync( w->accumulator(), 0, px * 16, stream )) != cudaSuccess) return fail( "accumulator clear", e );
-		w->samplesTaken = 0;
-	}
+	if ((uint64_t)f.pixelCount * (uint64_t)w->spp > PATHIDX_MASK) return fail( "Render: width * height * spp exceeds 2^28 path indices" );
+	if (converge == 1) w->samplesTaken = 0;
+	plan.clearAccumulator = w->samplesTaken == 0;
 	// paths of this shard per sample; several samples share one pass while they fit
-	const uint32_t perSample = f.ownTiles * TILE_PIXELS;
+	const uint32_t perSample = ownTiles * TILE_PIXELS;
 	uint32_t samplesPerPass = perSample ? w->pathsPerPass / perSample : 1;
 	if (samplesPerPass < 1) samplesPerPass = 1;
 	if (samplesPerPass > (uint32_t)w->spp) samplesPerPass = (uint32_t)w->spp;
-	const uint32_t cap = perSample * samplesPerPass + 32;
-	if (cap > w->capacity)
+	plan.passes = perSample ? ((uint32_t)w->spp + samplesPerPass - 1) / samplesPerPass : 0;
+	// chains: the shard's tiles dealt round robin.  Automatic: two chains once a pass holds enough paths for both to fill the machine
+	// (a chain's waves are persistent grids of 148 x 6 x 128 lanes; below ~4 rays per lane a wave is mostly its own tail)
+	uint32_t chains = w->chains > 0 ? (uint32_t)w->chains : ((uint64_t)perSample * samplesPerPass >= (1u << 20) ? 2u : 1u);
+	if (chains > ownTiles) chains = ownTiles ? ownTiles : 1;
+	plan.chains = f.chainCount = chains;
+	plan.maxLen = (uint32_t)w->maxPathLength, plan.bsdf = (uint32_t)w->bsdf, plan.isect = (int)isect, plan.smCount = smCount;
+	// shade grid = a whole number of resident sets (the loop is grid-strided: with 8 CTAs per SM launched and 5 resident, the second,
+	// partial set ran on a 60 % full machine: shade 0.40 -> 0.36 ms per C2 frame)
+	static int shadeResident[2] = { 0, 0 };
+	if (!shadeResident[w->bsdf ? 1 : 0])
 	{
-		DeviceBuffer* bufs[] = { &w->rayO[0], &w->rayO[1], &w->rayD[0], &w->rayD[1], &w->state[0], &w->state[1], &w->info[0], &w->info[1], &w->hits,
-			&w->conO, &w->conD, &w->conE };
-		for (DeviceBuffer* b : bufs) if ((e = b->reserve( (size_t)cap * 16, false, stream )) != cudaSuccess) return fail( "path buffers", e );
-		w->capacity = cap;
+		int n = 0;
+		if (w->bsdf) cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, shadeKernel<true>, 128, 0 );
+		else cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, shadeKernel<false>, 128, 0 );
+		shadeResident[w->bsdf ? 1 : 0] = n > 0 ? n : 1;
 	}
-	uint32_t* dCounters = (uint32_t*)w->counters.ptr;
-	const int maxLen = w->maxPathLength;
-	memset( &stats.totalRays, 0, (char*)&stats.probedInstid - (char*)&stats.totalRays );
-	cudaEvent_t frameA = w->ev[0], frameB = w->ev[1];
-	cudaEventRecord( frameA, stream );
-	for (uint32_t s0 = 0; s0 < (uint32_t)w->spp; s0 += samplesPerPass)
+	plan.shadeGrid = smCount * shadeResident[w->bsdf ? 1 : 0] * B200_SHADE_GRID;
+	// buffers (grown outside the enqueue: a reallocation synchronises the device)
+	for (uint32_t c = 0; c < chains; c++)
 	{
-		f.samplesThisPass = (uint32_t)w->spp - s0 < samplesPerPass ? (uint32_t)w->spp - s0 : samplesPerPass;
+		Chain& ch = w->chain[c];
+		const uint32_t tiles = ownTiles > c ? (ownTiles - c + chains - 1) / chains : 0;
+		const uint32_t cap = tiles * TILE_PIXELS * samplesPerPass + 32;
+		if (cap > ch.capacity)
+		{
+			for (int i = 0; ch.all( i ); i++) if ((e = ch.all( i )->reserve( (size_t)cap * 16, false, stream )) != cudaSuccess) return fail( "path buffers", e );
+			ch.capacity = cap;
+		}
+		auto& pc = plan.chain[c];
+		pc.tiles = tiles, pc.capacity = tiles * TILE_PIXELS * samplesPerPass;
+		for (int k = 0; k < 2; k++)
+		{
+			pc.rayO[k] = (float4*)ch.rayO[k].ptr, pc.rayD[k] = (float4*)ch.rayD[k].ptr, pc.state[k] = (float4*)ch.state[k].ptr, pc.info[k] = (float4*)ch.info[k].ptr;
+			pc.conO[k] = (float4*)ch.conO[k].ptr, pc.conD[k] = (float4*)ch.conD[k].ptr, pc.conE[k] = (float4*)ch.conE[k].ptr;
+		}
+		pc.hits = (float4*)ch.hits.ptr, pc.slotS = (float4*)ch.slotS.ptr, pc.slotC = (float4*)ch.slotC.ptr;
+	}
+	const size_t counterWords = (size_t)COUNTER_STRIDE * chains * (plan.passes ? plan.passes : 1);
+	if ((e = w->counters.reserve( counterWords * 4, false, stream )) != cudaSuccess || (e = w->passParams.reserve( sizeof( PassParams ) * (plan.passes + 1), false, stream )) != cudaSuccess ||
+		(e = w->hostCounters.reserve( counterWords * 4 )) != cudaSuccess || (e = w->hostPass.reserve( sizeof( PassParams ) * (plan.passes + 1) )) != cudaSuccess)
+		return fail( "frame buffers", e );
+	plan.trace = baseArgs();
+	plan.shadePool = (const float4*)shadePool.ptr, plan.vnormPool = (const float4*)vnormPool.ptr, plan.instShadePool = (const float4*)instShadePool.ptr;
+	plan.materials = (const float4*)w->materials.ptr;
+	plan.accumulator = w->accumulator(), plan.frame = (float4*)w->frame.ptr;
+	plan.passDev = (PassParams*)w->passParams.ptr, plan.passHost = (PassParams*)w->hostPass.ptr;
+	plan.countersDev = (uint32_t*)w->counters.ptr, plan.countersHost = (uint32_t*)w->hostCounters.ptr, plan.fetchCounters = (uint32_t*)fetchCounter.ptr;
+	// per-wave timers: every pass while that stays a few hundred events, else the first pass only (its times are scaled to the frame's
+	// ray counts below)
+	plan.timedPasses = !w->waveTimers ? 0 : (plan.passes * chains * plan.maxLen <= 96 ? plan.passes : 1);
+	const size_t timersNeeded = (size_t)plan.timedPasses * chains * plan.maxLen * 5;
+	while (w->timers.size() < timersNeeded)
+	{
+		cudaEvent_t ev;
+		if ((e = cudaEventCreate( &ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
+		w->timers.push_back( ev );
+	}
+	// this frame's PassParams
+	for (uint32_t pass = 0; pass < plan.passes; pass++)
+	{
+		PassParams& P = plan.passHost[pass];
+		memset( &P, 0, sizeof( P ) );
+		for (int a = 0; a < 3; a++) P.pos[a] = vp[a], P.p1[a] = vp[3 + a], P.right[a] = vp[6 + a] - vp[3 + a], P.up[a] = vp[9 + a] - vp[3 + a];
+		P.aperture = vp[12], P.spreadAngle = vp[13], P.distortion = vp[16];
+		const uint32_t s0 = pass * samplesPerPass;
+		P.samplesThisPass = (uint32_t)w->spp - s0 < samplesPerPass ? (uint32_t)w->spp - s0 : samplesPerPass;
 		// pathIdx = pixel + sample * pixelCount must stay below 2^28 (the path word keeps 4 flag bits): the sample index wraps after `period` samples and the wrap
 		// count goes into the salt instead ("samplesTaken * 7907 + pathLength * 91771" in the reference's shade call)
 		const uint32_t globalSample = (uint32_t)w->sampleOffset + w->samplesTaken + s0;
-		if ((uint64_t)f.pixelCount * (uint64_t)w->spp > PATHIDX_MASK) return fail( "Render: width * height * spp exceeds 2^28 path indices" );
 		const uint32_t period = PATHIDX_MASK / f.pixelCount - (uint32_t)w->spp + 1;
-		f.sampleBase = globalSample % period;
-		f.blueNoise = (w->haveBlueNoise && globalSample < period) ? (const uint32_t*)w->blueNoise.ptr : nullptr; // not after the sample index wrapped
-		f.R0 = (globalSample / period + 1) * 7907u;
-		if ((e = cudaMemsetAsync( dCounters, 0, sizeof( uint32_t ) * COUNTER_WORDS, stream )) != cudaSuccess) return fail( "counter clear", e );
-		const uint32_t paths = perSample * f.samplesThisPass;
-		if (!paths) continue;
-		generateEyeRaysKernel<<<smCount * 4, 256, 0, stream>>>( f, (float4*)w->rayO[0].ptr, (float4*)w->rayD[0].ptr, (float4*)w->state[0].ptr, (float4*)w->info[0].ptr,
-			dCounters );
-		stats.kernelLaunches++;
-		int in = 0;
-		cudaEvent_t* ev = w->ev + 2;
-		for (int len = 1; len <= maxLen; len++)
+		P.sampleBase = globalSample % period;
+		P.blue = (w->haveBlueNoise && globalSample < period) ? 1u : 0u; // not after the sample index wrapped
+		P.R0 = (globalSample / period + 1) * 7907u;
+		P.finalScale = 1.0f / (float)(w->samplesTaken + (uint32_t)w->spp);
+	}
+	memset( &stats.totalRays, 0, (char*)&stats.probedInstid - (char*)&stats.totalRays );
+	if (plan.passes)
+	{
+		// A frame whose plan equals the previous frame's is replayed as a graph (captured on its second appearance, so that one-off
+		// frames never pay for a capture); anything else is enqueued on the streams directly
+		std::vector<uint8_t> key( (const uint8_t*)&plan, (const uint8_t*)&plan + sizeof( plan ) );
+		uint32_t launches = 0;
+		bool launched = false;
+		if (w->useGraph && w->graphExec && key == w->graphKey)
 		{
-			const int out = in ^ 1;
-			cudaEventRecord( ev[0], stream );
-			if (TraceClosestDevice( w->rayO[in].ptr, w->rayD[in].ptr, (int)paths, w->hits.ptr, dCounters + extCounter( len ) )) return 1;
-			cudaEventRecord( ev[1], stream );
-			// shade k adds to the accumulator: it runs after connect k-1 so that every pixel sees its adds in one fixed order
-			if (overlap && len > 1) cudaStreamWaitEvent( stream, w->connectDone[len - 1], 0 );
-			cudaEventRecord( ev[2], stream );
-			// grid = a whole number of resident sets (the loop is grid-strided: with 8 CTAs per SM launched and 5 resident, the second,
-			// partial set ran on a 60 % full machine: shade 0.40 -> 0.36 ms per C2 frame)
-			static int shadeResident[2] = { 0, 0 };
-			if (!shadeResident[w->bsdf ? 1 : 0])
-			{
-				int n = 0;
-				if (w->bsdf) cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, shadeKernel<true>, 128, 0 );
-				else cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, shadeKernel<false>, 128, 0 );
-				shadeResident[w->bsdf ? 1 : 0] = n > 0 ? n : 1;
-			}
-			( w->bsdf ? shadeKernel<true> : shadeKernel<false> )<<<smCount * shadeResident[w->bsdf ? 1 : 0] * B200_SHADE_GRID, 128, 0, stream>>>( f, len, maxLen, (const float4*)w->rayO[in].ptr, (const float4*)w->rayD[in].ptr,
-				(const float4*)w->state[in].ptr, (const float4*)w->info[in].ptr, (const float4*)w->hits.ptr, (float4*)w->rayO[out].ptr, (float4*)w->rayD[out].ptr,
-				(float4*)w->state[out].ptr, (float4*)w->info[out].ptr, (float4*)w->conO.ptr, (float4*)w->conD.ptr, (float4*)w->conE.ptr, (const float4*)shadePool.ptr, (const float4*)vnormPool.ptr, (const float4*)instShadePool.ptr,
-				(const float4*)w->materials.ptr, w->accumulator(), dCounters );
-			stats.kernelLaunches++;
-			cudaEventRecord( ev[3], stream );
-			if (anyLight && overlap)
-			{
-				// connect k on its own stream, beside extend k+1: the tails of the two persistent launches fill each other
-				cudaEventRecord( w->shadeDone[len], stream );
-				cudaStreamWaitEvent( w->connectStream, w->shadeDone[len], 0 );
-				cudaEventRecord( ev[4], w->connectStream );
-				if (TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), dCounters + shadowCounter( len ), w->connectStream, 1 )) return 1;
-				cudaEventRecord( ev[5], w->connectStream );
-				cudaEventRecord( w->connectDone[len], w->connectStream );
-			}
-			else
-			{
-				cudaEventRecord( ev[4], stream );
-				if (anyLight && TraceConnectDevice( w->conO.ptr, w->conD.ptr, (int)paths, w->conE.ptr, w->accumulator(), dCounters + shadowCounter( len ) )) return 1;
-				cudaEventRecord( ev[5], stream );
-			}
-			ev += 6;
-			in = out;
+			if ((e = cudaGraphLaunch( w->graphExec, stream )) != cudaSuccess) return fail( "frame graph launch", e );
+			launched = true, w->graphLaunches++;
 		}
-		if (overlap) cudaStreamWaitEvent( stream, w->connectDone[maxLen], 0 );
-		// per-pass statistics (one synchronisation per pass, not per bounce)
-		uint32_t hc[COUNTER_WORDS];
-		if ((e = cudaMemcpyAsync( hc, dCounters, sizeof( hc ), cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "counter read-back", e );
+		else if (w->useGraph && key == w->lastKey)
+		{
+			cudaGraph_t graph = nullptr;
+			if (w->graphExec) { cudaGraphExecDestroy( w->graphExec ); w->graphExec = nullptr; }
+			cudaStreamSynchronize( stream ); // work the caller queued before this frame is not part of the capture
+			if ((e = cudaStreamBeginCapture( w->captureStream, cudaStreamCaptureModeThreadLocal )) != cudaSuccess) return fail( "frame graph capture", e );
+			e = enqueueFrame( *w, plan, w->captureStream, true, &launches );
+			cudaError_t e2 = cudaStreamEndCapture( w->captureStream, &graph );
+			if (e == cudaSuccess) e = e2;
+			if (e == cudaSuccess) e = cudaGraphInstantiate( &w->graphExec, graph, 0 );
+			if (graph) cudaGraphDestroy( graph );
+			if (e != cudaSuccess) { w->graphExec = nullptr; cudaGetLastError(); return fail( "frame graph capture", e ); }
+			w->graphKey = key, w->graphCaptures++;
+			if ((e = cudaGraphLaunch( w->graphExec, stream )) != cudaSuccess) return fail( "frame graph launch", e );
+			launched = true, w->graphLaunches++;
+		}
+		if (!launched && (e = enqueueFrame( *w, plan, stream, false, &launches )) != cudaSuccess) return fail( "Render", e );
+		w->lastKey.swap( key );
+		launches = 0; // kernels of the frame: per pass and chain one generate, per path length extend + shade (+ connect), one accumulate
+		for (uint32_t c = 0; c < chains; c++) if (plan.chain[c].tiles) launches += plan.passes * (2 + plan.maxLen * (2 + (plan.anyLight ? 1 : 0)));
+		stats.kernelLaunches += launches;
 		if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "Render", e );
-		ev = w->ev + 2;
-		for (int len = 1; len <= maxLen; len++, ev += 6)
+		cudaEventElapsedTime( &stats.renderTime, w->frameBegin, w->frameEnd );
+		// statistics: ray counts of every pass, wave times of the timed ones
+		double timedRays[3] = { 0, 0, 0 }, allRays[3] = { 0, 0, 0 }, timedShadow = 0, allShadow = 0, timedPaths = 0, allPaths = 0; // classes: primary, first bounce, deeper
+		float classMs[3] = { 0, 0, 0 }, shadowMs = 0, shadeMs = 0;
+		for (uint32_t pass = 0; pass < plan.passes; pass++) for (uint32_t c = 0; c < chains; c++)
 		{
-			float tExt = 0, tShade = 0, tShadow = 0;
-			cudaEventElapsedTime( &tExt, ev[0], ev[1] ), cudaEventElapsedTime( &tShade, ev[2], ev[3] ), cudaEventElapsedTime( &tShadow, ev[4], ev[5] );
-			const uint32_t n = hc[extCounter( len )];
-			if (len == 1) stats.primaryRayCount += n, stats.traceTime0 += tExt;
-			else if (len == 2) stats.bounce1RayCount += n, stats.traceTime1 += tExt;
-			else stats.deepRayCount += n, stats.traceTimeX += tExt;
-			stats.totalExtensionRays += n, stats.totalShadowRays += hc[shadowCounter( len )];
-			stats.shadowTraceTime += tShadow, stats.shadeTime += tShade;
+			const uint32_t* hc = plan.countersHost + (size_t)(pass * chains + c) * COUNTER_STRIDE;
+			const bool timed = pass < plan.timedPasses;
+			for (uint32_t len = 1; len <= plan.maxLen; len++)
+			{
+				const uint32_t nExt = hc[extCounter( (int)len )], nShadow = hc[shadowCounter( (int)len )];
+				const int cls = len == 1 ? 0 : len == 2 ? 1 : 2;
+				allRays[cls] += nExt, allShadow += nShadow, allPaths += nExt;
+				if (len == 1) stats.primaryRayCount += nExt; else if (len == 2) stats.bounce1RayCount += nExt; else stats.deepRayCount += nExt;
+				stats.totalExtensionRays += nExt, stats.totalShadowRays += nShadow;
+				if (timed && plan.chain[c].tiles)
+				{
+					const cudaEvent_t* t = &w->timers[((size_t)(pass * chains + c) * plan.maxLen + (len - 1)) * 5];
+					float tExt = 0, tShade = 0, tCon = 0;
+					cudaEventElapsedTime( &tExt, t[0], t[1] ), cudaEventElapsedTime( &tShade, t[1], t[2] );
+					if (plan.anyLight) cudaEventElapsedTime( &tCon, t[3], t[4] );
+					classMs[cls] += tExt, shadeMs += tShade, shadowMs += tCon;
+					timedRays[cls] += nExt, timedShadow += nShadow, timedPaths += nExt;
+				}
+			}
+			if (f.probePixel >= 0 && pass == 0 && hc[PROBE_BASE + 3])
+			{
+				stats.probedInstid = (int32_t)hc[PROBE_BASE], stats.probedTriid = (int32_t)hc[PROBE_BASE + 1];
+				memcpy( &stats.probedDist, &hc[PROBE_BASE + 2], 4 );
+			}
 		}
-		if (f.probePixel >= 0 && s0 == 0 && hc[PROBE_BASE + 3])
-		{
-			stats.probedInstid = (int32_t)hc[PROBE_BASE], stats.probedTriid = (int32_t)hc[PROBE_BASE + 1];
-			memcpy( &stats.probedDist, &hc[PROBE_BASE + 2], 4 );
-		}
+		// (chains and connect waves overlap: a wave's time is its own begin-to-end span, so the class times add up to more than the frame)
+		auto scaled = []( float ms, double timed, double all ) { return timed > 0 ? (float)(ms * all / timed) : 0.f; };
+		stats.traceTime0 = scaled( classMs[0], timedRays[0], allRays[0] ), stats.traceTime1 = scaled( classMs[1], timedRays[1], allRays[1] );
+		stats.traceTimeX = scaled( classMs[2], timedRays[2], allRays[2] );
+		stats.shadowTraceTime = scaled( shadowMs, timedShadow, allShadow ), stats.shadeTime = scaled( shadeMs, timedPaths, allPaths );
 	}
 	w->samplesTaken += (uint32_t)w->spp;
-	finalizeKernel<<<(f.pixelCount + 255) / 256, 256, 0, stream>>>( w->accumulator(), (float4*)w->frame.ptr, f.pixelCount, 1.0f / (float)w->samplesTaken );
-	stats.kernelLaunches++;
-	cudaEventRecord( frameB, stream );
-	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "Render", e );
-	cudaEventElapsedTime( &stats.renderTime, frameA, frameB );
+	stats.frameGraphLaunches = w->graphLaunches, stats.frameChains = plan.chains, stats.framePasses = plan.passes;
 	stats.totalRays = stats.totalExtensionRays + stats.totalShadowRays;
 	w->frameCounter++;
 	return 0;
@@ -1434,16 +1729,29 @@ int RenderCore::GatherFinalize( uint32_t totalSamples )
 	if (w->shardCount != w->peerWorld || w->shardIndex != w->peerRank) return fail( "GatherFinalize: shardCount / shardIndex differ from the peer table" );
 	uint32_t* timeout = (uint32_t*)w->peerFlags.ptr + MAX_PEERS;
 	const uint32_t tilesX = ((uint32_t)w->width + TILE_W - 1) / TILE_W;
-	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout );
+	int clockKHz = 0;
+	cudaDeviceGetAttribute( &clockKHz, cudaDevAttrClockRate, device );
+	const long long limitTicks = (long long)((double)w->peerTimeoutMs * (clockKHz > 0 ? clockKHz : 1965000)); // clock64 ticks at the SM clock
+	cudaError_t e;
+	for (cudaEvent_t* ev : { &w->gatherBegin, &w->gatherEnd }) if (!*ev && (e = cudaEventCreate( ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
+	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout, limitTicks );
+	cudaEventRecord( w->gatherBegin, stream ); // the pull kernel alone (everyone has arrived): what the NVLink figure of bench.py divides by
 	gatherFinalizeKernel<<<smCount * 8, 256, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, (float4*)w->frame.ptr, (uint32_t)w->width, (uint32_t)w->height, tilesX,
-		1.0f / (float)totalSamples );
-	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout );
+		1.0f / (float)totalSamples, timeout );
+	cudaEventRecord( w->gatherEnd, stream );
+	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout, limitTicks );
 	stats.kernelLaunches += 3;
 	uint32_t timedOut = 0;
-	cudaError_t e = cudaMemcpyAsync( &timedOut, timeout, 4, cudaMemcpyDeviceToHost, stream );
+	e = cudaMemcpyAsync( &timedOut, timeout, 4, cudaMemcpyDeviceToHost, stream );
 	if (e == cudaSuccess) e = cudaStreamSynchronize( stream );
 	if (e != cudaSuccess) return fail( "GatherFinalize", e );
-	if (timedOut) return fail( "GatherFinalize: a peer did not arrive within the time limit" );
+	cudaEventElapsedTime( &stats.gatherKernelMs, w->gatherBegin, w->gatherEnd );
+	if (timedOut)
+	{
+		// this frame's gather did not happen (the pull kernel saw the flag and left); the next one starts with a clean flag
+		cudaMemsetAsync( timeout, 0, 4, stream );
+		return fail( "GatherFinalize: a peer did not arrive within the time limit (Setting peerTimeoutMs); the frame was not gathered" );
+	}
 	return 0;
 }
 

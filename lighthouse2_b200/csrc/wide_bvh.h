@@ -62,6 +62,13 @@ struct Aabb {
 	float halfArea() const { float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2]; return x * y + y * z + z * x; }
 };
 
+// Per-lane traversal stack of the wave kernels (traverse.cu: STACK_SMEM + STACK_LOCAL entries, no bound check in the pass).  A visited
+// bottom-level node pushes at most one entry (what is left of its inner-children group), a top-level node at most two (inner group +
+// instance-leaf group), so a scene fits when blasLevels + 2 * tlasLevels <= TRAVERSAL_STACK_ENTRIES.  The core refuses deeper trees
+// (SetGeometry / UpdateToplevel / the cache loader) instead of letting the kernels write past the stack.
+constexpr int TRAVERSAL_STACK_ENTRIES = 48;
+constexpr int MAX_TREE_LEVELS = TRAVERSAL_STACK_ENTRIES - 8; // one mesh's tree; leaves room for a top level of four levels
+
 // Result of a host build (BLAS over triangles or TLAS over instance boxes).
 struct WideBvh {
 	std::vector<WideNode> nodes;         // breadth-first: level L occupies [levelStart[L], levelStart[L+1])
