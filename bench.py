@@ -1,24 +1,31 @@
 #!/usr/bin/env python
 """bench.py -- Mrays/s of the wavefront extend/shadow path (BASELINE.json metric) on B200.
 
-One STEP = one pass of the hot path over one batch of synthetic rays on the C2 scene (BASELINE.json configs[1]:
-tessellated-sphere field, 1 000 000 triangles, 1920x1080): the primary extend wave, the shadow (any-hit) wave
-of one ray per lit primary hit, and the four incoherent diffuse-bounce extend waves (the headline class).
-The ray sets are generated once, outside the timed region (lighthouse2_b200/workload.py), and are resident
-in HBM when the timed region starts.  `value` = all rays of the step / device time (CUDA events, max over
-ranks); `rays` breaks it down per class the way the reference UI does (count / traceTime per wave class,
-apps/imguiapp/main.cpp:230-233).  `e2e` = the same pass through the host-buffer C-ABI calls
-(b200_trace_closest / b200_trace_any: pinned host rays in, host hits out, copies inside the timed region).
+One STEP = one full wavefront frame through the core's public call (Render: ray generation, then per path length the extend wave,
+the shade stage and the fused shadow/connect wave; accumulate + finalize) on the C2 scene (BASELINE.json configs[1]: tessellated-
+sphere field, 1 000 000 triangles) at the size of BASELINE.json configs[4]: 3840x2160 x 16 spp, primary + next-event shadow rays
++ 4 diffuse bounces.  That is the largest configuration that fits one GPU and is also the 8-GPU configuration, so the SAME frame is
+timed at every N (strong scaling): with N ranks the frame is sharded by interleaved 32x8 tiles (scene replicated), and every frame ends
+with the gather of the accumulator over NVLink (one fused peer-memory pull + finalize kernel, wavefront.cu).
+  value  = rays of the frame (all ranks) / time of the slowest rank (CUDA events on the core's stream, barrier + synchronize on both sides)
+  e2e    = the same frames through the host-facing calls b200_render + b200_gather_finalize + b200_read_frame: the view pyramid goes in
+           from host memory, the finished RGBA32F frame comes back into pinned host memory, both inside the timed region
+  check  = every rank renders the frame once unsharded and compares its gathered accumulator with it bit for bit
+Sub-blocks (explanation, not the headline):
+  waves  = the raw extend / shadow waves of a 1080p pass over resident rays, one launch timed at a time (per-class rates: primary, shadow,
+           incoherent diffuse -- the >= 1.5 Grays/s target class); `roofline` is computed from its extend launches (the dominant kernel,
+           timed alone on its launch stream); with N ranks every rank traces its own sample (weak scaling, no collective)
+  e2e_waves = the same waves through the host-buffer calls (pinned rays in, hits out), PCIe-bound
+  cpu_baseline = the reference's own CPU traversal on the host cores over a bounded sample of the wave pass (N = 1 only)
 
-Multi-GPU (torchrun, one process per GPU): the scene is replicated, every rank traces its own sample of the
-frame (rank r = sub-pixel sample r: rays shard by spp) -- weak scaling, no data-path collective.
-
-`--impl reference` times the reference's own CPU traversal (oracle/_ref = unmodified lib/RenderCore_Bart/bvh.cpp
-compiled in place; else the plain-C port) on the box's host cores over a bounded pixel sample of the same pass.
+`--impl reference` times the reference's own CPU traversal (oracle/_ref = unmodified lib/RenderCore_Bart/bvh.cpp compiled in place; else
+the plain-C port) on the box's host cores: every step is the wave pass (primary + shadow + diffuse bounces) of a bounded pixel sample of
+the workload's frame.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -36,27 +43,33 @@ from lighthouse2_b200 import scenes, workload  # noqa: E402
 
 EXTEND_BYTES_PER_RAY = 48.0      # 32 B ray in + 16 B hit out
 SHADOW_BYTES_PER_RAY = 32.125    # 32 B ray in + 1 bit out
+METRIC = "Mrays/s (wavefront extend + shadow + diffuse-bounce waves, C2 1M-triangle scene)"
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tris", type=int, default=1_000_000)
-    ap.add_argument("--width", type=int, default=1920)
-    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--width", type=int, default=3840, help="frame workload")
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--spp", type=int, default=16)
+    ap.add_argument("--wave-width", type=int, default=1920, help="wave leg (per-class rates, roofline)")
+    ap.add_argument("--wave-height", type=int, default=1080)
+    ap.add_argument("--wave-steps", type=int, default=30)
     ap.add_argument("--bounces", type=int, default=4)
     ap.add_argument("--isect", type=int, default=0, help="0 = reference arithmetic (bit-exact parity), 1 = watertight")
     ap.add_argument("--cpu-sample", type=int, default=65536, help="pixels in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-detail", action="store_true", help="per-wave wall time of the host-buffer calls for several chunk schedules (stderr)")
-    ap.add_argument("--no-frame", action="store_true")
+    ap.add_argument("--no-waves", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="skip the bit-identity check of the gathered frame")
+    ap.add_argument("--gather", default="auto", choices=["auto", "p2p", "nccl"])
     ap.add_argument("--setting", action="append", default=[], help="name=value, applied to the core before the scene is built")
     ap.add_argument("--stats", action="store_true", help="also report nodes visited / triangles tested per ray (untimed counting run)")
-    ap.add_argument("--check", action="store_true", help="compare a sample of the GPU hits with the CPU checker")
+    ap.add_argument("--check", action="store_true", help="also compare a sample of every wave's GPU hits with the CPU checker")
     return ap.parse_args()
 
 
@@ -102,13 +115,13 @@ class ClockSampler:
             self.p.kill()
         self.f.flush()
         self.f.seek(0)
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         for line in self.f.read().splitlines():
             c = [x.strip() for x in line.split(",")]
             if len(c) < 8:
                 continue
             try:
-                sm.append(float(c[0])); mx.append(float(c[1]))
+                sm.append(float(c[0])); mx.append(float(c[1])); pw.append(float(c[2]))
             except ValueError:
                 continue
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[4:8]):
@@ -116,20 +129,20 @@ class ClockSampler:
                     reasons.add(name)
         os.unlink(self.f.name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
 def frame_rays(args, sample_index=0):
-    view = scenes.view_pyramid(width=args.width, height=args.height, **scenes.C2_CAMERA)
+    view = scenes.view_pyramid(width=args.wave_width, height=args.wave_height, **scenes.C2_CAMERA)
     # sub-pixel sample position: rank/sample r uses a different (irrational) offset so pixel grids never coincide
     ox = (0.5 + 0.6180339887 * sample_index) % 1.0
     oy = (0.5 + 0.7548776662 * sample_index) % 1.0
-    return scenes.primary_rays(view, args.width, args.height, offset=(ox, oy))
+    return scenes.primary_rays(view, args.wave_width, args.wave_height, offset=(ox, oy))
 
 
 def workload_name(args):
-    return (f"C2 sphere field {args.tris} tris, {args.width}x{args.height} x 1 spp per GPU: primary extend + 1 shadow ray per lit hit + "
-            f"{args.bounces} diffuse-bounce extend waves")
+    return (f"C2 sphere field {args.tris} tris at the C5 frame size {args.width}x{args.height} x {args.spp} spp: full wavefront frame, primary + 1 NEE shadow ray "
+            f"per lit vertex + {args.bounces} diffuse bounces, fixed depth")
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -170,8 +183,8 @@ def cpu_pass(args, verts, n_pixels, steps, warmup, seed=1):
             times.append(t_step)
     sec = float(np.mean(times))
     res = dict(value=total / sec / 1e6, unit="Mrays/s", cores=cores, kind="reference" if kind == "ref" else "port",
-               sample=f"{len(pix)} random pixels of the frame, full pass ({total} rays/step: {counts}), {steps} steps, "
-                      f"{cores} host threads; reference BVH build {o.blas_build_seconds:.1f} s not included",
+               sample=f"the waves of {len(pix)} random pixels of a 1 spp pass over the same scene (primary + shadow + {args.bounces} diffuse bounces: {total} rays/step, "
+                      f"{counts}), {steps} steps, {cores} host threads; reference BVH build {o.blas_build_seconds:.1f} s not included",
                per_class={k: counts[k] * steps / per_class[k] / 1e6 for k in counts if per_class[k] > 0},
                ms_per_step=sec * 1e3, bvh_build_s=o.blas_build_seconds)
     o.close()
@@ -183,12 +196,12 @@ def run_reference(args):
     if rank != 0:
         return
     verts = scenes.sphere_field(args.tris)
-    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 1))
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
     r = cpu_pass(args, verts, args.cpu_sample, steps, warmup)
     line = {
-        "impl": "reference", "metric": "Mrays/s (primary+shadow+diffuse waves, C2 1M-tri scene)", "value": r["value"], "unit": "Mrays/s",
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "Mrays/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "sampled": r["sample"]},
         "rays": {k: {"mrays_s": v} for k, v in r["per_class"].items()},
         "cpu_baseline": {"value": r["value"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
@@ -201,34 +214,8 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------------------------
 # the B200 arm
 # ------------------------------------------------------------------------------------------------------------------
-def run_b200(args):
-    import torch
-    import torch.distributed as dist
-    from lighthouse2_b200 import core
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- RenderCore_B200 has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-
-    rc = core.RenderCoreB200(local)
-    rc.Setting("isectMode", args.isect)
-    for kv in args.setting:
-        rc.Setting(kv.split("=")[0], float(kv.split("=")[1]))
-    verts = scenes.sphere_field(args.tris)
-    t0 = time.perf_counter()
-    rc.SetGeometry(0, verts)
-    rc.SetInstance(0, 0)
-    rc.SetInstance(1, -1)
-    rc.UpdateToplevel()
-    build_s = time.perf_counter() - t0
-
-    # ---- synthetic input: this rank's pass (its own sub-pixel sample), traced by the CUDA core itself -----------
+def wave_leg(args, rc, core, verts, torch, dist, dev, rank, world, barrier):
+    """Raw waves of a 1080p pass over rays resident in HBM, one launch timed at a time; then the same through the host-buffer calls."""
     O, D = frame_rays(args, sample_index=rank)
 
     def gpu_tracer(o_, d_):
@@ -238,9 +225,7 @@ def run_b200(args):
     waves = workload.make_pass(gpu_tracer, verts, O, D, scenes.C2_LIGHT, args.bounces, seed=1 + rank)
     counts = workload.pass_ray_counts(waves)
     total_rays = sum(counts.values())
-
     stream = torch.cuda.current_stream()
-    rc.SetStream(stream.cuda_stream)
     for w in waves:
         n = w["O4"].shape[0]
         w["n"] = n
@@ -259,23 +244,15 @@ def run_b200(args):
         else:
             rc.TraceAnyDevice(w["dO"].data_ptr(), w["dD"].data_ptr(), w["n"], w["dOut"].data_ptr())
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- device-resident pass -------------------------------------------------------------------------------
-    for _ in range(args.warmup):
+    steps = args.wave_steps
+    for _ in range(max(3, args.warmup)):
         for w in waves:
             launch(w)
-    ev = [[(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in waves] for _ in range(args.steps)]
+    ev = [[(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in waves] for _ in range(steps)]
     e_begin, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches0 = rc.GetCoreStats()["kernelLaunches"]
     barrier()
-    clocks = ClockSampler(local) if rank == 0 else None
     e_begin.record(stream)
-    for s in range(args.steps):
+    for s in range(steps):
         for i, w in enumerate(waves):
             ev[s][i][0].record(stream)
             launch(w)
@@ -283,11 +260,9 @@ def run_b200(args):
     e_end.record(stream)
     barrier()
     total_ms = e_begin.elapsed_time(e_end)
-    clock_info = clocks.stop() if clocks else None
-    launches = rc.GetCoreStats()["kernelLaunches"] - launches0
     cls_ms, cls_rays = {}, {}
     ext_ms, ext_rays = 0.0, 0
-    for s in range(args.steps):
+    for s in range(steps):
         for i, w in enumerate(waves):
             ms = ev[s][i][0].elapsed_time(ev[s][i][1])
             cls_ms[w["cls"]] = cls_ms.get(w["cls"], 0.0) + ms
@@ -296,7 +271,7 @@ def run_b200(args):
                 ext_ms += ms
                 ext_rays += w["n"]
 
-    # ---- e2e: host buffers through the C ABI (H2D + wave + D2H + sync inside each call) ------------------------
+    # ---- the same waves through the host-buffer C ABI (H2D + wave + D2H inside each call) --------------------
     e2e_ms = e2e_sync_ms = None
     pcie_h2d = 0.0
     if not args.no_e2e:
@@ -314,7 +289,7 @@ def run_b200(args):
                     raise RuntimeError(lib.b200_last_error().decode())
             if queued and lib.b200_wait(h):
                 raise RuntimeError(lib.b200_last_error().decode())
-        e2e_steps = max(3, min(args.steps, 10))
+        e2e_steps = 10
         ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e2e_modes = {}
         for queued in (False, True):
@@ -328,14 +303,13 @@ def run_b200(args):
             barrier()
             e2e_modes[queued] = ea.elapsed_time(eb) / e2e_steps
         e2e_ms, e2e_sync_ms = e2e_modes[True], e2e_modes[False]
-        if rank == 0 and args.check:
-            # the queued results against the device-resident pass
-            for w in waves:
-                launch(w)
-            torch.cuda.synchronize()
-            for w in waves:
-                assert torch.equal(w["hOut"].view(torch.int32), w["dOut"].cpu().view(torch.int32)), "queued host-buffer wave differs from the device wave"
-        # context for the e2e number: what a plain pinned-memory copy achieves on this box (the e2e floor is h2d_bytes / this)
+        # the queued results against the device-resident pass
+        for w in waves:
+            launch(w)
+        torch.cuda.synchronize()
+        for w in waves:
+            assert torch.equal(w["hOut"].view(torch.int32), w["dOut"].cpu().view(torch.int32)), "queued host-buffer wave differs from the device wave"
+        # context: what a plain pinned-memory copy achieves on this box (the floor of the host-buffer pass is h2d_bytes / this)
         big = max(waves, key=lambda w_: w_["n"])
         torch.cuda.synchronize()
         ea.record(stream)
@@ -345,135 +319,276 @@ def run_b200(args):
         torch.cuda.synchronize()
         pcie_h2d = 5 * big["n"] * 16 / (ea.elapsed_time(eb) * 1e-3) / 1e9
 
-        if args.e2e_detail and rank == 0:
-            def copy_ms(w):  # the wave's own upload alone, and its kernel alone
-                torch.cuda.synchronize(); t0 = time.perf_counter()
-                for _ in range(5):
-                    w["dO"].copy_(w["hO"], non_blocking=True); w["dD"].copy_(w["hD"], non_blocking=True)
-                torch.cuda.synchronize(); up = (time.perf_counter() - t0) / 5 * 1e3
-                t0 = time.perf_counter()
-                for _ in range(5):
-                    launch(w)
-                torch.cuda.synchronize(); k = (time.perf_counter() - t0) / 5 * 1e3
-                t0 = time.perf_counter()
-                for _ in range(5):
-                    w["hOut"].copy_(w["dOut"], non_blocking=True)
-                torch.cuda.synchronize(); dn = (time.perf_counter() - t0) / 5 * 1e3
-                return up, k, dn
-            print("wave            n      up_ms  kern_ms  down_ms", file=sys.stderr)
-            for w in waves:
-                print("%-9s %9d  %7.3f  %7.3f  %7.3f" % ((w["cls"] + str(w["bounce"]), w["n"]) + copy_ms(w)), file=sys.stderr)
-            for zc, two, parts in ((0, 0, 6), (0, 0, 8), (0, 1, 4), (0, 1, 6), (0, 1, 8), (0, 1, 12), (1, 0, 4), (1, 1, 2), (1, 1, 4), (1, 1, 8)):
-                rc.Setting("zeroCopy", zc); rc.Setting("twoStreams", two); rc.Setting("zeroCopyBelow", 1 << 30)
-                rc.Setting("pinnedChunks" if zc else "hostChunks", parts)
-                row = []
-                for w in waves:
-                    fn = lib.b200_trace_closest if w["kind"] == "closest" else lib.b200_trace_any
-                    best = 1e9
-                    for _ in range(6):
-                        t0 = time.perf_counter()
-                        fn(h, w["hO"].data_ptr(), w["hD"].data_ptr(), w["n"], w["hOut"].data_ptr())
-                        best = min(best, (time.perf_counter() - t0) * 1e3)
-                    row.append(best)
-                print("zc %d two %d parts %2d: " % (zc, two, parts) + " ".join("%6.3f" % x for x in row) + "  sum %.3f" % sum(row), file=sys.stderr)
-            rc.Setting("zeroCopyBelow", 400000); rc.Setting("zeroCopy", 1); rc.Setting("twoStreams", 1); rc.Setting("pinnedChunks", 1); rc.Setting("hostChunks", 4)
-
-    # ---- the same scene through Render(): full wavefront frame (ray generation, shade, fused connect), tile-sharded over the
-    #      ranks, accumulator gathered by the fused peer-memory pull + finalize kernel (NCCL all-reduce if the peers cannot be mapped).  Reported beside the wave numbers, not as `value`.
-    frame = None
-    if not args.no_frame:
-        from lighthouse2_b200 import multigpu
-        sr = multigpu.ShardedRenderer(rank, world, local, mode="tiles", existing_core=rc)
-        sr.SetTarget(args.width, args.height, 1)
-        rc.SetPointLight(scenes.C2_LIGHT, (4000.0, 4000.0, 3600.0))
-        rc.SetSky((0.4, 0.5, 0.7))
-        rc.Setting("maxPathLength", args.bounces + 1)
-        rc.Setting("russianRoulette", 0)  # fixed-depth pass: the frame traces the same waves as the wave benchmark above
-        view = scenes.view_pyramid(width=args.width, height=args.height, **scenes.C2_CAMERA)
-        for _ in range(2):
-            sr.Render(view, 1)
-        fsteps = max(3, min(args.steps, 10))
-        barrier()
-        t0 = time.perf_counter()
-        r_ms = g_ms = 0.0
-        rays_f = 0
-        for _ in range(fsteps):
-            a_, b_ = sr.Render(view, 1)
-            r_ms += a_; g_ms += b_
-            rays_f += rc.GetCoreStats()["totalRays"]
-        barrier()
-        wall_ms = (time.perf_counter() - t0) * 1e3 / fsteps
-        st = rc.GetCoreStats()
-        fv = torch.tensor([wall_ms, r_ms / fsteps, g_ms / fsteps], device=dev, dtype=torch.float64)
-        fr = torch.tensor([rays_f / fsteps], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(fv, op=dist.ReduceOp.MAX)
-            dist.all_reduce(fr, op=dist.ReduceOp.SUM)
-        fv = fv.tolist()
-        frame = {"ms_per_frame_wall": fv[0], "render_ms": fv[1], "gather_ms": fv[2], "rays_per_frame": fr.item(),
-                 "mrays_s": fr.item() / (fv[0] * 1e-3) / 1e6, "gather_bytes": args.width * args.height * 16,
-                 "rank0_stats": {k: st[k] for k in ("primaryRayCount", "traceTime0", "bounce1RayCount", "traceTime1", "deepRayCount", "traceTimeX",
-                                                    "totalShadowRays", "shadowTraceTime", "shadeTime", "renderTime")},
-                 "gather": sr.gather if world > 1 else "none",
-                 "note": "Render() + gather of the float4 accumulator (p2p = one kernel pulls the foreign tiles over NVLink peer memory and finalizes the frame; "
-                         "nccl = all-reduce + finalize), 1 spp, tile-sharded; wall clock incl. host sync per frame"}
-
-    # ---- reduce over ranks: slowest rank's time, all ranks' rays ------------------------------------------------
     vec = torch.tensor([total_ms, e2e_ms or 0.0, ext_ms] + [cls_ms.get(c, 0.0) for c in ("primary", "shadow", "diffuse")], device=dev, dtype=torch.float64)
     cnt = torch.tensor([total_rays, ext_rays] + [cls_rays.get(c, 0) for c in ("primary", "shadow", "diffuse")], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(vec, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     vec, cnt = vec.tolist(), cnt.tolist()
-    total_ms, e2e_ms_max, ext_ms = vec[0], vec[1], vec[2]
-    all_rays_step = cnt[0]
-
+    out = None
     if rank == 0:
-        ms_per_step = total_ms / args.steps
-        value = all_rays_step / (ms_per_step * 1e-3) / 1e6
-        peak, peak_src = peaks()
-        # dominant kernel = the extend (closest-hit) wave kernel; algorithmic bytes = 48 B/ray (this rank's launches)
-        my_ext_ms = sum(ev[s][i][0].elapsed_time(ev[s][i][1]) for s in range(args.steps) for i, w in enumerate(waves) if w["kind"] == "closest")
-        my_ext_rays = sum(w["n"] for w in waves if w["kind"] == "closest") * args.steps
-        achieved = my_ext_rays * EXTEND_BYTES_PER_RAY / (my_ext_ms * 1e-3) / 1e9
+        ms_per_step = vec[0] / steps
         rays = {}
         for k, c in enumerate(("primary", "shadow", "diffuse")):
             if cnt[2 + k] > 0 and vec[3 + k] > 0:
-                rays[c] = {"rays_per_step": cnt[2 + k] / args.steps, "mrays_s": cnt[2 + k] / (vec[3 + k] * 1e-3) / 1e6,
+                rays[c] = {"rays_per_step": cnt[2 + k] / steps, "mrays_s": cnt[2 + k] / (vec[3 + k] * 1e-3) / 1e6,
                            "mrays_s_per_gpu": cnt[2 + k] / world / (vec[3 + k] * 1e-3) / 1e6}
-        st = rc.GetCoreStats()
-        line = {
-            "metric": "Mrays/s (primary+shadow+diffuse waves, C2 1M-tri scene)", "value": value, "unit": "Mrays/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args), "isect": "reference-exact" if args.isect == 0 else "watertight",
-                       "sharding": "scene replicated, rank r traces sub-pixel sample r (spp-sharded), no data-path collective",
-                       "l2": "no flush: ray+hit streams of one step (%.0f MB) exceed the 126 MB L2; the scene (%.0f MB nodes + %.0f MB triangles) "
-                             "is meant to stay L2-resident" % (all_rays_step / world * 48 / 1e6, st["wideNodeCount"] * 80 / 1e6, st["triangleCount"] * 48 / 1e6),
-                       "wide_nodes": st["wideNodeCount"], "bvh_build_s": round(build_s, 2)},
-            "rays": rays,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(),
-                         "kernel": "traceKernel<closest> (extend wave)", "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY, "peak_source": peak_src,
-                         "note": "stream roofline of a latency-bound traversal kernel (dependent chain of a pass at 6 warps per scheduler); see DESIGN.md", "ncu": measured_traffic("extend_ncu")},
-            "gpu_launches": int(launches),
-            "clocks": clock_info,
-        }
-        if e2e_ms_max:
+        my_ext_ms = sum(ev[s][i][0].elapsed_time(ev[s][i][1]) for s in range(steps) for i, w in enumerate(waves) if w["kind"] == "closest")
+        my_ext_rays = sum(w["n"] for w in waves if w["kind"] == "closest") * steps
+        my_ext_launches = sum(1 for w in waves if w["kind"] == "closest") * steps
+        out = {"block": {"workload": f"raw waves of a {args.wave_width}x{args.wave_height} x 1 spp pass per GPU over rays resident in HBM: primary extend + 1 shadow ray per lit hit + "
+                                     f"{args.bounces} diffuse-bounce extend waves, every launch timed alone (CUDA events on the launch stream)",
+                         "scaling": "weak (rank r traces sub-pixel sample r; no collective)", "steps": steps, "ms_per_step": ms_per_step,
+                         "mrays_s": cnt[0] / (ms_per_step * 1e-3) / 1e6, "rays": rays},
+               "rays": rays,
+               "extend": {"ms": my_ext_ms, "rays": my_ext_rays, "launches": my_ext_launches}}
+        if vec[1]:
             h2d = sum(w["n"] * 32 for w in waves)
             d2h = sum(w["n"] * 16 if w["kind"] == "closest" else ((w["n"] + 31) // 32) * 4 for w in waves)
-            line["e2e"] = {"value": all_rays_step / (e2e_ms_max * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d,
-                           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms_max, "pcie_h2d_gbs_measured": pcie_h2d,
-                           "pcie_floor_ms": h2d / (pcie_h2d * 1e9) * 1e3,
-                           "api": "b200_trace_closest_async / b200_trace_any_async + one b200_wait per step, pinned host buffers (the six waves of a step queued back to back)",
-                           "sync_calls": {"ms_per_step": e2e_sync_ms, "value": (all_rays_step / world) / (e2e_sync_ms * 1e-3) / 1e6,
-                                          "note": "rank 0, b200_trace_closest / b200_trace_any: every wave synchronises before the next one is submitted"}}
+            out["e2e_waves"] = {"value": cnt[0] / (vec[1] * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                                "ms_per_step": vec[1], "pcie_h2d_gbs_measured": pcie_h2d, "pcie_floor_ms": h2d / (pcie_h2d * 1e9) * 1e3,
+                                "api": "b200_trace_closest_async / b200_trace_any_async + one b200_wait per step, pinned host buffers (the six waves of a step queued back to back)",
+                                "sync_calls": {"ms_per_step": e2e_sync_ms, "value": (cnt[0] / world) / (e2e_sync_ms * 1e-3) / 1e6,
+                                               "note": "rank 0, b200_trace_closest / b200_trace_any: every wave synchronises before the next one is submitted"}}
+    return out, waves
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from lighthouse2_b200 import core, multigpu
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- RenderCore_B200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    rc = core.RenderCoreB200(local)
+    rc.Setting("isectMode", args.isect)
+    for kv in args.setting:
+        rc.Setting(kv.split("=")[0], float(kv.split("=")[1]))
+    verts = scenes.sphere_field(args.tris)
+    t0 = time.perf_counter()
+    rc.SetGeometry(0, verts)
+    rc.SetInstance(0, 0)
+    rc.SetInstance(1, -1)
+    rc.UpdateToplevel()
+    build_s = time.perf_counter() - t0
+    stream = torch.cuda.current_stream()
+    rc.SetStream(stream.cuda_stream)
+
+    # ---- sub-block: the raw waves (per-class rates, roofline of the dominant kernel) -----------------------------
+    waves_out, waves = (None, None)
+    if not args.no_waves:
+        waves_out, waves = wave_leg(args, rc, core, verts, torch, dist, dev, rank, world, barrier)
+
+    # ---- the frame workload: tile-sharded Render() + gather, strong scaling -----------------------------------------
+    W, H, spp = args.width, args.height, args.spp
+    view = scenes.view_pyramid(width=W, height=H, **scenes.C2_CAMERA)
+    sr = multigpu.ShardedRenderer(rank, world, local, mode="tiles", existing_core=rc, gather=args.gather)
+    sr.SetTarget(W, H, spp)
+    rc.SetPointLight(scenes.C2_LIGHT, (4000.0, 4000.0, 3600.0))
+    rc.SetSky((0.4, 0.5, 0.7))
+    rc.Setting("maxPathLength", args.bounces + 1)
+    rc.Setting("russianRoulette", 0)  # fixed depth: every frame traces the same waves
+    lib, h = rc.lib, rc.h
+    vp = core.ViewPyramid()
+    for k in ("pos", "p1", "p2", "p3"):
+        getattr(vp, k)[:] = [float(x) for x in view[k]]
+    vp.aperture, vp.spreadAngle, vp.imagePlane, vp.focalDistance, vp.distortion = 0.0, 0.01, 0.01, 1.0, 0.0
+    import ctypes as C
+    vp_ref = C.byref(vp)
+
+    def chk(code):
+        if code:
+            raise RuntimeError(lib.b200_last_error().decode())
+
+    p2p = world > 1 and sr.gather == "p2p"
+
+    def frame():
+        # one step: this rank's tiles, then the gather (N > 1).  Both calls synchronise their stream before they return.
+        chk(lib.b200_render(h, vp_ref, 1))
+        if p2p:
+            chk(lib.b200_gather_finalize(h, spp))
+        elif world > 1:
+            dist.all_reduce(sr.acc, op=dist.ReduceOp.SUM)
+            chk(lib.b200_finalize(h, spp))
+
+    def digest():
+        a = sr.ReadAccumulator()
+        return hashlib.sha256(np.ascontiguousarray(a).view(np.uint8)).hexdigest()
+
+    # ---- check: the gathered accumulator against this rank's own unsharded render of the same frame -----------------
+    frame_check = None
+    if not args.no_check:
+        if world > 1:
+            rc.Setting("shardCount", 1)
+            chk(lib.b200_render(h, vp_ref, 1))
+            full = digest()
+            rays_full = rc.GetCoreStats()["totalRays"]
+            rc.Setting("shardCount", world)
+            rc.Setting("shardIndex", rank)
+            barrier()
+            frame()
+            ok = digest() == full
+        else:
+            frame()
+            full = digest()
+            rays_full = rc.GetCoreStats()["totalRays"]
+            frame()
+            ok = digest() == full
+        okt = torch.tensor([1 if ok else 0], device=dev, dtype=torch.int32)
+        if world > 1:
+            dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        frame_check = {"result": "bit-identical" if okt.item() else "DIFFERS", "ranks_checked": world, "sha256_16": full[:16],
+                       "what": ("every rank's gathered float4 accumulator == its own unsharded single-GPU render of the frame" if world > 1 else
+                                "two consecutive renders of the frame (run-to-run determinism; with N > 1 the gathered accumulator is compared with an unsharded render)"),
+                       "rays_unsharded": rays_full}
+
+    for _ in range(args.warmup):
+        frame()
+    e_begin, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = rc.GetCoreStats()["kernelLaunches"]
+    barrier()
+    clocks = ClockSampler(local) if rank == 0 else None
+    wall0 = time.perf_counter()
+    e_begin.record(stream)
+    render_ms = gather_ms = gather_kernel_ms = 0.0
+    rays_mine = 0
+    for _ in range(args.steps):
+        chk(lib.b200_render(h, vp_ref, 1))
+        st = rc.GetCoreStats()
+        render_ms += st["renderTime"]
+        rays_mine += st["totalRays"]
+        if p2p:
+            g0.record(stream)
+            chk(lib.b200_gather_finalize(h, spp))
+            g1.record(stream)
+            g1.synchronize()
+            gather_ms += g0.elapsed_time(g1)
+            gather_kernel_ms += rc.GetCoreStats()["gatherKernelMs"]
+        elif world > 1:
+            g0.record(stream)
+            dist.all_reduce(sr.acc, op=dist.ReduceOp.SUM)
+            chk(lib.b200_finalize(h, spp))
+            g1.record(stream)
+            g1.synchronize()
+            gather_ms += g0.elapsed_time(g1)
+    e_end.record(stream)
+    barrier()
+    wall_ms = (time.perf_counter() - wall0) * 1e3
+    total_ms = e_begin.elapsed_time(e_end)
+    clock_info = clocks.stop() if clocks else None
+    st = rc.GetCoreStats()
+    launches = st["kernelLaunches"] - launches0
+
+    # ---- e2e: the same frames with the finished frame read back into pinned host memory every step -------------------
+    e2e_ms = None
+    frame_bytes = W * H * 16
+    if not args.no_e2e:
+        host_frame = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+        e2e_steps = max(3, min(args.steps, 10))
+
+        def e2e_frame():
+            frame()
+            if rank == 0:  # the application (RenderSystem) lives on rank 0 and takes the frame from there
+                chk(lib.b200_read_frame(h, host_frame.data_ptr()))
+        e2e_frame()
+        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ea.record(stream)
+        for _ in range(e2e_steps):
+            e2e_frame()
+        eb.record(stream)
+        barrier()
+        e2e_ms = ea.elapsed_time(eb) / e2e_steps
+        if rank == 0:
+            assert np.isfinite(host_frame.numpy()).all() and float(host_frame[..., :3].mean()) > 0.01
+
+    # ---- reduce over ranks: slowest rank's time, all ranks' rays ------------------------------------------------
+    vec = torch.tensor([total_ms, e2e_ms or 0.0, render_ms, gather_ms, gather_kernel_ms, wall_ms], device=dev, dtype=torch.float64)
+    vmin = vec.clone()
+    cnt = torch.tensor([rays_mine, launches], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(vec, op=dist.ReduceOp.MAX)
+        dist.all_reduce(vmin, op=dist.ReduceOp.MIN)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    vec, vmin, cnt = vec.tolist(), vmin.tolist(), cnt.tolist()
+
+    if rank == 0:
+        steps = args.steps
+        ms_per_step = vec[0] / steps
+        rays_per_frame = cnt[0] / steps
+        value = rays_per_frame / (ms_per_step * 1e-3) / 1e6
+        peak, peak_src = peaks()
+        line = {
+            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world,
+            "steps": steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args), "isect": "reference-exact" if args.isect == 0 else "watertight",
+                       "sharding": ("scene replicated, frame sharded by interleaved 32x8 tiles over %d ranks; per frame one gather of the float4 accumulator over NVLink (%s)"
+                                    % (world, "fused peer-memory pull + finalize kernel" if p2p else "NCCL all-reduce")) if world > 1 else "1 GPU, no sharding",
+                       "l2": "no flush: the path buffers of one pass (%.1f GB of rays, hits, path state and contribution slots per rank) exceed the 126 MB L2 many times over; "
+                             "the scene (%.0f MB nodes + %.0f MB triangles) is meant to stay L2-resident"
+                             % (min(32 << 20, W * H * spp / world) * 272 / 1e9, st["wideNodeCount"] * 80 / 1e6, st["triangleCount"] * 48 / 1e6),
+                       "rays_per_frame": rays_per_frame, "passes_per_frame": st["framePasses"], "wave_chains": st["frameChains"],
+                       "frame_graph_replays": st["frameGraphLaunches"], "wide_nodes": st["wideNodeCount"], "bvh_build_s": round(build_s, 2),
+                       "timed_region_wall_s": vec[5] * 1e-3},
+            "frame_check": frame_check["result"] if frame_check else "skipped",
+            "frame": {"check": frame_check, "render_ms_slowest_rank": vec[2] / steps, "render_ms_fastest_rank": vmin[2] / steps,
+                      "gather": (sr.gather if world > 1 else "none"),
+                      "gather_ms_barrier_to_barrier": vec[3] / steps if world > 1 else 0.0,
+                      "gather_note": "barrier_to_barrier = arrival wait for the slowest rank + pull + second arrival (events around b200_gather_finalize, slowest rank); "
+                                     "kernel = the pull + finalize kernel alone, after everyone has arrived",
+                      "rank0_stats": {k: st[k] for k in ("primaryRayCount", "traceTime0", "bounce1RayCount", "traceTime1", "deepRayCount", "traceTimeX",
+                                                         "totalShadowRays", "shadowTraceTime", "shadeTime", "renderTime")}},
+            "gpu_launches": int(cnt[1]),
+            "clocks": clock_info,
+        }
+        if p2p:
+            gk = vec[4] / steps
+            pulled = frame_bytes * (world - 1) / world
+            line["frame"]["gather_kernel_ms"] = gk
+            line["frame"]["gather_nvlink_gbs_per_gpu"] = pulled / (gk * 1e-3) / 1e9 if gk > 0 else None
+            line["frame"]["gather_bytes_pulled_per_gpu"] = pulled
+        if e2e_ms:
+            line["e2e"] = {"value": rays_per_frame / (vec[1] * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 68 + 96 * st["framePasses"],
+                           "d2h_bytes_per_step": frame_bytes, "ms_per_step": vec[1],
+                           "api": "b200_render (ViewPyramid from host memory) + b200_gather_finalize + b200_read_frame into pinned host memory (rank 0): what the RenderSystem "
+                                  "sees through CoreAPI::Render; the C++ vtable face forwards to the same calls (tests/test_plugin_gpu.py)",
+                           "note": "inputs of this path are a 68-byte view pyramid plus 96 bytes of pass parameters per pass; the output is the finished RGBA32F frame"}
+        if waves_out:
+            ext = waves_out["extend"]
+            achieved = ext["rays"] * EXTEND_BYTES_PER_RAY / (ext["ms"] * 1e-3) / 1e9
+            line["rays"] = waves_out["rays"]
+            line["waves"] = waves_out["block"]
+            if "e2e_waves" in waves_out:
+                line["e2e_waves"] = waves_out["e2e_waves"]
+            line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(),
+                                "kernel": "traceKernel<closest> (extend wave)", "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY,
+                                "algorithmic_bytes_per_launch": ext["rays"] * EXTEND_BYTES_PER_RAY / ext["launches"], "avg_launch_ms": ext["ms"] / ext["launches"],
+                                "launches_timed": ext["launches"], "peak_source": peak_src,
+                                "measured_on": "the extend launches of the `waves` block (each timed alone with CUDA events on its launch stream, rank 0)",
+                                "per_class_mrays_s": {k: v["mrays_s_per_gpu"] for k, v in waves_out["rays"].items()},
+                                "note": "stream roofline of a latency-bound traversal kernel (dependent chain of a pass at 6 warps per scheduler); see DESIGN.md",
+                                "ncu": measured_traffic("extend_ncu")}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_pass(args, verts, args.cpu_sample, steps=2, warmup=1)
             line["cpu_baseline"] = {"value": r["value"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
                                     "per_class": r["per_class"], "bvh_build_s": r["bvh_build_s"]}
-        if frame:
-            line["frame"] = frame
-        if args.stats:
+        if args.stats and waves:
             rc.Setting("countSteps", 1)
             line["steps_per_ray"] = {}
             for w in waves:
@@ -483,10 +598,10 @@ def run_b200(args):
                     line["steps_per_ray"][f"{w['cls']}{w['bounce']}"] = {"nodes": float(nn.mean()), "tris": float(nt.mean()), "nodes_max": int(nn.max()),
                                                                              "nodes_pct": [float(x) for x in np.percentile(nn, [50, 90, 99, 99.9, 99.99])]}
             rc.Setting("countSteps", 0)
-        if args.check:
+        if args.check and waves:
             line["check"] = check_against_cpu(rc, core, verts, waves)
         print(json.dumps(line), flush=True)
-    rc.Shutdown()
+    sr.Shutdown() if world > 1 else rc.Shutdown()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

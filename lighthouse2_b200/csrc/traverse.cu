@@ -165,9 +165,14 @@ __device__ __forceinline__ void enterInstance( RayState& r, const float4* __rest
 // rounded to float equals the IEEE float quotient; bounds (EPSILON, 1/EPSILON) at :43), plus the wave's
 // own (tmin, t) interval.  O = (ox,oy,oz,tmin), D = (dx,dy,dz,t).  Returns true and writes tt,u,v on acceptance
 // (strict found_t < t, bvh.cpp:268).
+// Exact ties (two triangles with bit-identical t: a ray through a shared edge) go to the triangle with the smaller leaf-order index
+// `tri`, whatever order the warp happens to test them in: `bestTri` is the index of the owner's current hit.  (The reference keeps
+// the triangle ITS tree visits first, bvh.cpp:268 -- an order no other tree reproduces, so ties are a documented exception class of
+// the parity checker either way; a rule that does not depend on which rays share a warp makes the wave's output reproducible from
+// run to run, which the bit-identical multi-GPU frame check needs.)
 template <int ISECT>
-__device__ __forceinline__ bool intersectTriangle( const float4 O, const float4 D, const float4 v0, const float4 e1, const float4 e2, float& tOut,
-	float& uOut, float& vOut )
+__device__ __forceinline__ bool intersectTriangle( const float4 O, const float4 D, const float4 v0, const float4 e1, const float4 e2, const uint32_t tri,
+	const uint32_t* bestTri, float& tOut, float& uOut, float& vOut )
 {
 	if (ISECT == ISECT_REFERENCE)
 	{
@@ -182,7 +187,7 @@ __device__ __forceinline__ bool intersectTriangle( const float4 O, const float4 
 		const float v = f * (D.x * qx + D.y * qy + D.z * qz);
 		if (v < 0.0f || u + v > 1.0f) return false;
 		const float tt = f * (e2.x * qx + e2.y * qy + e2.z * qz);
-		if (tt > REF_EPSILON && tt < 1 / REF_EPSILON && tt > O.w && tt < D.w) { tOut = tt, uOut = u, vOut = v; return true; }
+		if (tt > REF_EPSILON && tt < 1 / REF_EPSILON && tt > O.w && (tt < D.w || (tt == D.w && tri < *bestTri))) { tOut = tt, uOut = u, vOut = v; return true; }
 		return false;
 	}
 	else
@@ -202,7 +207,7 @@ __device__ __forceinline__ bool intersectTriangle( const float4 O, const float4 
 		const float v = f * __fmaf_rn( D.x, qx, __fmaf_rn( D.y, qy, D.z * qz ) );
 		if (v < 0.0f || u + v > 1.0f) return false;
 		const float tt = f * __fmaf_rn( e2.x, qx, __fmaf_rn( e2.y, qy, e2.z * qz ) );
-		if (tt > O.w && tt < D.w && tt > 0.0f) { tOut = tt, uOut = u, vOut = v; return true; }
+		if (tt > O.w && (tt < D.w || (tt == D.w && tri < *bestTri)) && tt > 0.0f) { tOut = tt, uOut = u, vOut = v; return true; }
 		return false;
 	}
 }
@@ -210,7 +215,7 @@ __device__ __forceinline__ bool intersectTriangle( const float4 O, const float4 
 
 // One wide-node visit: decode the 8 quantised child boxes and return the octant-ordered hit mask
 // (bits 31..24: inner children in visiting order, bits 23..0: leaf primitives relative to primBase).
-template <int J> __device__ __forceinline__ void testChild( const RayState& r, const uint32_t K, const uint32_t nearx, const uint32_t neary,
+template <int J> __device__ __forceinline__ void testChild( const RayState& r, const float tcull, const uint32_t K, const uint32_t nearx, const uint32_t neary,
 	const uint32_t nearz, const uint32_t farx, const uint32_t fary, const uint32_t farz, const float ax, const float ay, const float az,
 	const float bx, const float by, const float bz, const float axf, const float ayf, const float azf, const float bxf, const float byf,
 	const float bzf, const uint32_t childBits4, const uint32_t bitIndex4, uint32_t& hitmask )
@@ -220,7 +225,7 @@ template <int J> __device__ __forceinline__ void testChild( const RayState& r, c
 	const float tfx = __fmaf_rn( qbyte<J>( farx, K ), axf, bxf ), tfy = __fmaf_rn( qbyte<J>( fary, K ), ayf, byf ),
 				tfz = __fmaf_rn( qbyte<J>( farz, K ), azf, bzf );
 	const float tn = fmaxf( max3f( tnx, tny, tnz ), r.tmin );
-	const float tf = fminf( min3f( tfx, tfy, tfz ), r.t );
+	const float tf = fminf( min3f( tfx, tfy, tfz ), tcull );
 	if (tn <= tf)
 	{
 		const uint32_t bits = (childBits4 >> (8 * J)) & 0xffu, idx = (bitIndex4 >> (8 * J)) & 0xffu;
@@ -235,8 +240,12 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 	const float sx = __uint_as_float( (ew & 0xffu) << 23 ), sy = __uint_as_float( ((ew >> 8) & 0xffu) << 23 ),
 				sz = __uint_as_float( ((ew >> 16) & 0xffu) << 23 );
 	// plane t = (p + b*s - O) * idir = F*A + B with F = 2^23 + 256 b (see qbyte): A = s*idir/256,
-	// B = ((p - O) - 32768 s) * idir.  Far planes are scaled by 1+2^-21 so float rounding can only widen a box.
-	const float WIDEN = 1.0f + 4.76837158e-7f;
+	// B = ((p - O) - 32768 s) * idir.  Far planes are scaled by 1+2^-21 and near planes by 1-2^-21, so that float rounding can only
+	// widen a box: the dominant error is the rounding of (p - O), a few 2^-24 of the plane distance, which for small boxes far from the
+	// ray origin is as large as the quantisation guard band (1/64 cell) -- without the near-plane margin a ray through the very corner
+	// of a leaf box (a ray aimed at a mesh vertex) missed the box about once in 40 000 such rays.  (Plane distances behind the origin
+	// are scaled the wrong way, harmlessly: they lose against tmin >= 0 / make a culled box more culled.)
+	const float WIDEN = 1.0f + 4.76837158e-7f, NARROW = 1.0f - 4.76837158e-7f;
 #if B200_HALF_DECODE
 	// F = 1024 + b: A = s*idir, B = ((p - O) - 1024 s) * idir
 	const float ax = sx * r.ix, ay = sy * r.iy, az = sz * r.iz;
@@ -250,7 +259,14 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 	const float bz = __fmaf_rn( -32768.f, sz, __uint_as_float( n0.z ) - r.oz ) * r.iz;
 #endif
 	const float axf = ax * WIDEN, ayf = ay * WIDEN, azf = az * WIDEN, bxf = bx * WIDEN, byf = by * WIDEN, bzf = bz * WIDEN;
+	const float axn = ax * NARROW, ayn = ay * NARROW, azn = az * NARROW, bxn = bx * NARROW, byn = by * NARROW, bzn = bz * NARROW;
 	const bool nx = r.dx < 0, ny = r.dy < 0, nz = r.dz < 0;
+	// Culling against the current hit distance leaves a margin of 2^-18 t.  A child's entry distance is computed from (p - O) * idir in
+	// floats: its error (a few ulp of t) can exceed the quantisation guard band of a small, distant box, and a box entered at exactly the
+	// hit distance (a triangle lying in its near face) could then be culled or not depending on whether a hit one ulp farther had
+	// already been found -- i.e. on the order in which the warp happened to test triangles.  With the margin the set of triangles
+	// that can win never depends on that order (the wave's output is reproducible; see also the tie rule in intersectTriangle).
+	const float tcull = r.t * (1.0f + 3.81469727e-6f);
 	uint32_t hitmask = 0;
 #pragma unroll
 	for (int i = 0; i < 2; i++)
@@ -273,8 +289,8 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 #pragma unroll
 		for (int j = 0; j < 4; j++)
 		{
-			const float tn = fmaxf( max3f( __fmaf_rn( fnx[j], ax, bx ), __fmaf_rn( fny[j], ay, by ), __fmaf_rn( fnz[j], az, bz ) ), r.tmin );
-			const float tf = fminf( min3f( __fmaf_rn( ffx[j], axf, bxf ), __fmaf_rn( ffy[j], ayf, byf ), __fmaf_rn( ffz[j], azf, bzf ) ), r.t );
+			const float tn = fmaxf( max3f( __fmaf_rn( fnx[j], axn, bxn ), __fmaf_rn( fny[j], ayn, byn ), __fmaf_rn( fnz[j], azn, bzn ) ), r.tmin );
+			const float tf = fminf( min3f( __fmaf_rn( ffx[j], axf, bxf ), __fmaf_rn( ffy[j], ayf, byf ), __fmaf_rn( ffz[j], azf, bzf ) ), tcull );
 			if (tn <= tf)
 			{
 				const uint32_t bits = (childBits4 >> (8 * j)) & 0xffu, idx = (bitIndex4 >> (8 * j)) & 0xffu;
@@ -282,10 +298,10 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 			}
 		}
 #else
-		testChild<0>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
-		testChild<1>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
-		testChild<2>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
-		testChild<3>( r, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<0>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<1>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<2>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<3>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
 #endif
 	}
 	return hitmask;
@@ -296,8 +312,7 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 // appends (owner lane, triangle) pairs to a per-warp ring in shared memory and the warp tests 32 of them at a
 // time, one per lane, against the owners' rays mirrored in shared memory (a lane-divergent `while (triangles)`
 // loop ran with ~3 of 32 lanes active on incoherent rays).  Results go back through two ATOMS.MIN per hit:
-// smallest t, then (ties) the earliest-queued pair, so the first-visited triangle wins exact ties like the
-// reference's strict `found_t < t` (bvh.cpp:268).
+// smallest t, then (exact ties) the smallest leaf-order triangle index -- see intersectTriangle.
 constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
 #ifndef B200_REFILL_BELOW
 #define B200_REFILL_BELOW 22
@@ -326,7 +341,8 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	__shared__ uint2 sstack[STACK_SMEM * BLOCK_THREADS];
 	__shared__ float4 sRayO[BLOCK_THREADS];          // current-space ray of each lane: (ox,oy,oz,tmin)
 	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
-	__shared__ uint32_t sSlot[BLOCK_THREADS];        // flush slot of the winning pair, 0xffffffff = none
+	__shared__ uint32_t sSlot[BLOCK_THREADS];        // winner of a test round: (leaf-order triangle index << 5 | tester lane), 0xffffffff = none
+	__shared__ uint32_t sBestTri[BLOCK_THREADS];     // leaf-order index of the triangle of each lane's current hit (tie rule, see intersectTriangle)
 	__shared__ float4 sWorld[SINGLE ? 1 : BLOCK_THREADS]; // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
 	__shared__ float4 sWorldO[SINGLE ? 1 : BLOCK_THREADS], sWorldD[SINGLE ? 1 : BLOCK_THREADS]; // ... and the ray itself (re-reading the ray planes there cost 2 %)
 	__shared__ uint2 sRing[WARPS_PER_BLOCK][RING_CAP]; // leaf records: (first triangle | owner lane << 27, 24-bit triangle mask)
@@ -391,7 +407,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		const bool mine = lane < take;
 		bool hit = false;
 		float tt = 0, u = 0, v = 0;
-		uint32_t owner = 0, prim = 0;
+		uint32_t owner = 0, prim = 0, tri = 0;
 		if (mine)
 		{
 			// my triangle is the k-th highest set bit of the record's mask, k = lane - rstart.  Walk to it from the nearer end, in
@@ -404,11 +420,12 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			const uint32_t low = __ffs( m ) - 1;
 			const uint32_t bit = fromTop ? 31 - low : low;
 			owner = warpBase + (rx >> 27);
-			const float4* tp = tris + (size_t)((rx & 0x07ffffffu) + bit) * 3;
+			tri = (rx & 0x07ffffffu) + bit;
+			const float4* tp = tris + (size_t)tri * 3;
 			const float4 v0 = __ldg( tp ), e1 = __ldg( tp + 1 ), e2 = __ldg( tp + 2 );
 			const float4 O = sRayO[owner], D = sRayD[owner];
 			prim = __float_as_uint( v0.w );
-			hit = intersectTriangle<ISECT>( O, D, v0, e1, e2, tt, u, v );
+			hit = intersectTriangle<ISECT>( O, D, v0, e1, e2, tri, &sBestTri[owner], tt, u, v );
 		}
 		// retire consumed records; the record that straddles the 32-triangle boundary keeps its untested triangles
 		if (lane < nrec && incl > take && incl - cnt < take)
@@ -424,17 +441,17 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			uint32_t* const tbest = reinterpret_cast<uint32_t*>( &sRayD[owner].w );
 			if (hit) atomicMin( tbest, __float_as_uint( tt ) );
 			__syncwarp();
-			if (hit && *tbest == __float_as_uint( tt )) atomicMin( &sSlot[owner], lane );
+			if (hit && *tbest == __float_as_uint( tt )) atomicMin( &sSlot[owner], (tri << 5) | lane ); // (triangle indices stay below 2^27)
 			__syncwarp();
 			const uint32_t slot = sSlot[threadIdx.x];
 			const bool changed = slot != 0xffffffffu;
-			const uint32_t src = changed ? slot : lane;
+			const uint32_t src = changed ? (slot & 31u) : lane;
 			const uint32_t bary = (uint32_t)(65535.0f * u) + ((uint32_t)(65535.0f * v) << 16);
 			const uint32_t wPrim = __shfl_sync( 0xffffffffu, prim, src ), wBary = __shfl_sync( 0xffffffffu, bary, src );
 			const float wT = __shfl_sync( 0xffffffffu, tt, src );
 			if (changed)
 			{
-				sSlot[threadIdx.x] = 0xffffffffu;
+				sSlot[threadIdx.x] = 0xffffffffu, sBestTri[threadIdx.x] = slot >> 5;
 				r.t = wT, hitPrim = wPrim, hitBary = wBary;
 				if (!SINGLE) hitInst = curInst;
 				if (ANYHIT) terminated = true, ngroup.y = 0, tgroup.y = 0;
@@ -506,6 +523,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					sp = 0, instBase = -1, curInst = NO_INSTANCE;
 					hitPrim = 0xffffffffu, hitInst = 0, hitBary = 0, nNodes = nTris = 0;
 					lastQueued = qhead - 1, terminated = false;
+					sBestTri[threadIdx.x] = 0xffffffffu;
 					active = true;
 				}
 			}

@@ -5,6 +5,7 @@ import numpy as np
 import pytest
 
 import cases
+import parity
 from lighthouse2_b200 import core, scenes, workload
 
 pytestmark = pytest.mark.gpu
@@ -71,6 +72,32 @@ def test_c2_permutation_invariance_and_idempotence(c2):
     perm = np.random.default_rng(9).permutation(len(a))
     c = rc.TraceClosest(np.ascontiguousarray(w["O4"][perm]), np.ascontiguousarray(w["D4"][perm]))
     assert np.array_equal(c.view(np.uint32), a.view(np.uint32)[perm])
+
+
+def test_c2_exact_ties_do_not_depend_on_the_warp(c2):
+    """Rays aimed exactly at mesh vertices and edge midpoints pass through shared edges: several triangles report bit-identical t.
+    The kernel's tie rule (smallest leaf-order index, traverse.cu::intersectTriangle) must make the answer independent of which rays
+    share a warp -- the property the bit-identical multi-GPU frame check of bench.py rests on at hundreds of millions of rays -- and the
+    answer must be one of the tied triangles (checked with the reference arithmetic through the oracle's exhaustive search)."""
+    rc, verts = c2["rc"], c2["verts"]
+    rng = np.random.default_rng(17)
+    tri = verts[rng.choice(len(verts), 400_000, replace=False)]
+    targets = np.concatenate([tri[:200_000, 0], (0.5 * (tri[200_000:, 0] + tri[200_000:, 1])).astype(np.float32)])
+    O = np.tile(np.asarray(scenes.C2_CAMERA["pos"], np.float32), (len(targets), 1)) + rng.normal(0, 0.05, (len(targets), 3)).astype(np.float32)
+    D = scenes._normalize_ref((targets - O).astype(np.float32))
+    O4, D4 = core.pack_rays(O, D, tmin=1e-4)
+    a = rc.TraceClosest(O4, D4)
+    for seed in (1, 2, 3):
+        perm = np.random.default_rng(seed).permutation(len(a))
+        b = rc.TraceClosest(np.ascontiguousarray(O4[perm]), np.ascontiguousarray(D4[perm]))
+        assert np.array_equal(b.view(np.uint32), a.view(np.uint32)[perm]), "a hit depends on the rays it shares a warp with"
+    # against the oracle on a sample: identical, or a documented tie (different triangle, bit-identical reference t)
+    port = cases.load_oracle(dict(meshes=[verts], instances=[(0, None)]), "port")
+    idx = np.sort(rng.choice(len(a), 40_000, replace=False))
+    t, prim, inst = port.trace(O[idx], D[idx], nthreads=8)
+    rep = parity.compare("c2-ties", a[idx], port, O[idx], D[idx], t, prim, inst)
+    print("rays through vertices / edge midpoints:", rep)
+    assert rep["wrong"] == 0, rep  # every difference is a documented class: an exact tie or a box the reference's slab test culled (tests/parity.py)
 
 
 def test_c2_host_chunks_equal_device_wave(c2):
