@@ -136,20 +136,27 @@ struct Builder2 {
 
 } // namespace
 
+// Frame of a node: per axis a power-of-two cell size s = 2^(e-127) and an origin p a little BELOW the box (s/8), chosen so that the box
+// plus s/8 on either side spans at most 255 cells.  The headroom is what lets QuantiseChild keep its guard band on EVERY plane: with
+// p = lo and the tightest s (the first version), the children that touch the node's own bounds -- there is one on every side -- got the
+// planes 0 and 255 by clamping, i.e. no guard at all, and a ray through the very corner of such a box (a ray aimed at a mesh vertex)
+// could lose the box to the rounding of the slab arithmetic (tests/test_fullsize_gpu.py::test_c2_exact_ties_do_not_depend_on_the_warp).
+// refit.cu::frameOf restates this for the device; keep the two in step.
 void QuantiseFrame( const Aabb& box, float p[3], uint8_t e[3] )
 {
 	for (int a = 0; a < 3; a++)
 	{
 		p[a] = box.lo[a];
 		double ext = (double)box.hi[a] - (double)box.lo[a];
-		int ex = -100; // 2^-100: harmless scale for flat axes (every q is 0)
+		int ex = -100; // 2^-100: harmless scale for flat axes (both planes of every child sit at p; the slab test's relative margins apply)
 		if (ext > 0)
 		{
 			int fe;
-			std::frexp( ext / 255.0, &fe ); // ext/255 = m * 2^fe, m in [0.5,1)  ->  2^fe >= ext/255
+			std::frexp( ext / 254.75, &fe ); // ext/254.75 = m * 2^fe, m in [0.5,1)  ->  254.75 * 2^fe >= ext
 			ex = fe;
-			if (std::ldexp( 255.0, ex - 1 ) >= ext) ex--; // m == 0.5 exactly: one less is still enough
+			if (std::ldexp( 254.75, ex - 1 ) >= ext) ex--; // m == 0.5 exactly: one less is still enough
 			if (ex < -100) ex = -100;
+			p[a] = (float)((double)box.lo[a] - std::ldexp( 1.0, ex - 3 )); // (cells below a few ulp of lo: rounds back to lo, the geometry is at float resolution there)
 		}
 		e[a] = (uint8_t)(ex + 127);
 	}

@@ -11,7 +11,7 @@
 namespace b200 {
 
 namespace {
-constexpr uint32_t MAGIC = 0x42573242u /* "B2WB" */, VERSION = 3; // 3: 64 SAH bins, leaves chosen by the collapse
+constexpr uint32_t MAGIC = 0x42573242u /* "B2WB" */, VERSION = 4; // 3: 64 SAH bins, leaves chosen by the collapse; 4: node frames with headroom (QuantiseFrame)
 struct Header {
 	uint32_t magic, version;
 	uint64_t key;

@@ -32,6 +32,8 @@ struct TraceArgs {
 	uint32_t count;
 	uint32_t tlasRoot;         // absolute node index of the top-level root
 	uint32_t singleInstance;   // 1: the scene is one instance (record 0): rays enter it directly, the top-level node is not visited
+	float tlasTScale;          // top-level culling: hit distances are kept in the hit instance's OBJECT-space units (as the reference does); a world-space box
+	                           // entered at distance d can only hold hits of object-space distance >= d / tlasTScale (1 for rigid instances), see UpdateToplevel
 	uint32_t magic;            // byte-decode constant, set by the launchers; passed as an argument on purpose, see qbyte() / qpair() in traverse.cu
 	uint32_t* stepNodes;       // optional per-ray counters (COUNT variants)
 	uint32_t* stepTris;

@@ -16,17 +16,21 @@ namespace b200 {
 
 namespace {
 
-__device__ __forceinline__ uint32_t frameExponent( float lo, float hi )
+// frame of a node along one axis: exponent byte and origin (restates QuantiseFrame of bvh_builder.cpp: s/8 of headroom on both sides, so
+// that every child plane keeps its guard band)
+__device__ __forceinline__ uint32_t frameOf( float lo, float hi, float& p )
 {
 	const double ext = (double)hi - (double)lo;
 	int ex = -100;
+	p = lo;
 	if (ext > 0)
 	{
 		int fe;
-		frexp( ext / 255.0, &fe );
+		frexp( ext / 254.75, &fe );
 		ex = fe;
-		if (ldexp( 255.0, ex - 1 ) >= ext) ex--;
+		if (ldexp( 254.75, ex - 1 ) >= ext) ex--;
 		if (ex < -100) ex = -100;
+		p = (float)((double)lo - ldexp( 1.0, ex - 3 ));
 	}
 	return (uint32_t)(ex + 127);
 }
@@ -96,14 +100,15 @@ __device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t no
 	}
 	if (!valid) return;
 	uint32_t e[3], qlo[3] = { 0, 0, 0 }, qhi[3] = { 0, 0, 0 };
-	for (int c = 0; c < 3; c++) e[c] = frameExponent( nlo[c], nhi[c] );
-	if (meta) for (int c = 0; c < 3; c++) quantise( nlo[c], e[c], lo[c], hi[c], qlo[c], qhi[c] );
+	float fp[3];
+	for (int c = 0; c < 3; c++) e[c] = frameOf( nlo[c], nhi[c], fp[c] );
+	if (meta) for (int c = 0; c < 3; c++) quantise( fp[c], e[c], lo[c], hi[c], qlo[c], qhi[c] );
 	uint8_t* q = reinterpret_cast<uint8_t*>( np + 2 ); // qlox[8] qloy[8] qloz[8] qhix[8] qhiy[8] qhiz[8]
 	q[s] = (uint8_t)qlo[0], q[8 + s] = (uint8_t)qlo[1], q[16 + s] = (uint8_t)qlo[2];
 	q[24 + s] = (uint8_t)qhi[0], q[32 + s] = (uint8_t)qhi[1], q[40 + s] = (uint8_t)qhi[2];
 	if (s == 0)
 	{
-		np[0] = make_uint4( __float_as_uint( nlo[0] ), __float_as_uint( nlo[1] ), __float_as_uint( nlo[2] ),
+		np[0] = make_uint4( __float_as_uint( fp[0] ), __float_as_uint( fp[1] ), __float_as_uint( fp[2] ),
 			e[0] | (e[1] << 8) | (e[2] << 16) | (imask << 24) );
 		a.nodeLo[n] = make_float4( nlo[0], nlo[1], nlo[2], 0 ), a.nodeHi[n] = make_float4( nhi[0], nhi[1], nhi[2], 0 );
 	}

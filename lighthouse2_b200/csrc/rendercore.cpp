@@ -463,6 +463,36 @@ int RenderCore::UpdateToplevel()
 			boxes[i].lo[a] -= pad, boxes[i].hi[a] += pad;
 		}
 	}
+	// Hit distances are kept in the object-space units of the instance that was hit (the ray direction is re-normalised at every
+	// instance, bvh.cpp:607-610, and the reference compares those numbers across instances).  A hit at world distance d inside instance k
+	// has the object-space distance d * |inv_k D| >= d * sigma_min( inv_k ), so a top-level box entered at world distance d can be culled
+	// against the current hit distance t only when d * min_k sigma_min( inv_k ) > t.  For rigid instances the factor is 1.
+	{
+		double smin = 1e300;
+		for (uint32_t i = 0; i < N; i++)
+		{
+			// smallest singular value of the upper 3x3 of inv = sqrt of the smallest eigenvalue of A^T A (symmetric 3x3, closed form)
+			const float* v = instances[i].inv;
+			double B[3][3];
+			for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) B[r][c] = (double)v[r] * v[c] + (double)v[4 + r] * v[4 + c] + (double)v[8 + r] * v[8 + c];
+			const double q = (B[0][0] + B[1][1] + B[2][2]) / 3.0;
+			const double p1 = B[0][1] * B[0][1] + B[0][2] * B[0][2] + B[1][2] * B[1][2];
+			const double p2 = (B[0][0] - q) * (B[0][0] - q) + (B[1][1] - q) * (B[1][1] - q) + (B[2][2] - q) * (B[2][2] - q) + 2.0 * p1;
+			double lmin = q;
+			if (p2 > 1e-300)
+			{
+				const double pp = std::sqrt( p2 / 6.0 );
+				double C[3][3];
+				for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) C[r][c] = (B[r][c] - (r == c ? q : 0.0)) / pp;
+				double det = C[0][0] * (C[1][1] * C[2][2] - C[1][2] * C[2][1]) - C[0][1] * (C[1][0] * C[2][2] - C[1][2] * C[2][0]) + C[0][2] * (C[1][0] * C[2][1] - C[1][1] * C[2][0]);
+				det = std::min( 1.0, std::max( -1.0, det * 0.5 ) );
+				lmin = q + 2.0 * pp * std::cos( std::acos( det ) / 3.0 + 2.0943951023931953 ); // the smallest of the three eigenvalues
+			}
+			smin = std::min( smin, std::sqrt( std::max( lmin, 0.0 ) ) );
+		}
+		// (a margin for the float arithmetic of the instance entry; a degenerate instance switches top-level culling off)
+		tlasTScale = (N && smin > 1e-12) ? (float)std::min( 1.0 / (smin * (1.0 - 1.0 / 4096.0)), 1e30 ) : (N ? 1e30f : 1.0f);
+	}
 	WideBvh tlas;
 	BuildWideBvh( boxes.data(), N, 1, 1, tlas );
 	{
@@ -521,6 +551,7 @@ TraceArgs RenderCore::baseArgs() const
 	a.tlasRoot = tlasRoot;
 	a.singleInstance = (instances.size() == 1 && singleInstanceShortcut) ? 1u : 0u;
 	a.magic = 0x4B000000u;
+	a.tlasTScale = tlasTScale;
 	return a;
 }
 

@@ -117,6 +117,7 @@ private:
 	// acceleration structure pools
 	DeviceBuffer nodePool, triPool, instPool, shadePool, vnormPool, instShadePool; // vnormPool: per-triangle shading attributes (TRI_ATTR_STRIDE float4: vertex normals, uv, LOD, tangent, vertex alphas), only when CoreTris were supplied
 	uint32_t blasNodeEnd = 0, triEnd = 0, tlasRoot = 0, tlasNodeCount = 0;
+	float tlasTScale = 1.0f; // TraceArgs::tlasTScale of the current top level (UpdateToplevel)
 	std::vector<MeshRec> meshes;
 	std::vector<InstanceHost> instances;
 	bool tlasDirty = true;

@@ -233,19 +233,19 @@ template <int J> __device__ __forceinline__ void testChild( const RayState& r, c
 	}
 }
 
-__device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint32_t K, const uint4 n0, const uint4 n1, const uint4 n2,
+__device__ __forceinline__ uint32_t intersectNode( const RayState& r, const float tScale, const uint32_t K, const uint4 n0, const uint4 n1, const uint4 n2,
 	const uint4 n3, const uint4 n4 )
 {
 	const uint32_t ew = n0.w;
 	const float sx = __uint_as_float( (ew & 0xffu) << 23 ), sy = __uint_as_float( ((ew >> 8) & 0xffu) << 23 ),
 				sz = __uint_as_float( ((ew >> 16) & 0xffu) << 23 );
 	// plane t = (p + b*s - O) * idir = F*A + B with F = 2^23 + 256 b (see qbyte): A = s*idir/256,
-	// B = ((p - O) - 32768 s) * idir.  Far planes are scaled by 1+2^-21 and near planes by 1-2^-21, so that float rounding can only
-	// widen a box: the dominant error is the rounding of (p - O), a few 2^-24 of the plane distance, which for small boxes far from the
-	// ray origin is as large as the quantisation guard band (1/64 cell) -- without the near-plane margin a ray through the very corner
-	// of a leaf box (a ray aimed at a mesh vertex) missed the box about once in 40 000 such rays.  (Plane distances behind the origin
-	// are scaled the wrong way, harmlessly: they lose against tmin >= 0 / make a culled box more culled.)
-	const float WIDEN = 1.0f + 4.76837158e-7f, NARROW = 1.0f - 4.76837158e-7f;
+	// B = ((p - O) - 32768 s) * idir.  Two things keep the test conservative.  Every plane carries a guard band of at least 1/64 cell
+	// (QuantiseChild; the node frame has headroom so that no plane loses it to clamping), which covers the 1/512-cell rounding of the
+	// one-FFMA decode.  And the far planes are scaled by 1+2^-20: the other error, the rounding of (p - O), is a few 2^-24 of the plane
+	// distance whatever the cell size, more than the guard band of a small box far from the ray origin; tn <= tf only compares the two,
+	// so a one-sided margin of twice the size serves both.  (A far plane behind the origin moves the wrong way: the box is culled anyway.)
+	const float WIDEN = 1.0f + 9.53674316e-7f;
 #if B200_HALF_DECODE
 	// F = 1024 + b: A = s*idir, B = ((p - O) - 1024 s) * idir
 	const float ax = sx * r.ix, ay = sy * r.iy, az = sz * r.iz;
@@ -259,14 +259,15 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 	const float bz = __fmaf_rn( -32768.f, sz, __uint_as_float( n0.z ) - r.oz ) * r.iz;
 #endif
 	const float axf = ax * WIDEN, ayf = ay * WIDEN, azf = az * WIDEN, bxf = bx * WIDEN, byf = by * WIDEN, bzf = bz * WIDEN;
-	const float axn = ax * NARROW, ayn = ay * NARROW, azn = az * NARROW, bxn = bx * NARROW, byn = by * NARROW, bzn = bz * NARROW;
 	const bool nx = r.dx < 0, ny = r.dy < 0, nz = r.dz < 0;
 	// Culling against the current hit distance leaves a margin of 2^-18 t.  A child's entry distance is computed from (p - O) * idir in
 	// floats: its error (a few ulp of t) can exceed the quantisation guard band of a small, distant box, and a box entered at exactly the
 	// hit distance (a triangle lying in its near face) could then be culled or not depending on whether a hit one ulp farther had
 	// already been found -- i.e. on the order in which the warp happened to test triangles.  With the margin the set of triangles
 	// that can win never depends on that order (the wave's output is reproducible; see also the tie rule in intersectTriangle).
-	const float tcull = r.t * (1.0f + 3.81469727e-6f);
+	// (tScale: 1 + 2^-18 inside an instance; at the top level additionally the factor between world-space distances and the object-space
+	// units r.t is kept in, TraceArgs::tlasTScale)
+	const float tcull = r.t * tScale;
 	uint32_t hitmask = 0;
 #pragma unroll
 	for (int i = 0; i < 2; i++)
@@ -289,7 +290,7 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 #pragma unroll
 		for (int j = 0; j < 4; j++)
 		{
-			const float tn = fmaxf( max3f( __fmaf_rn( fnx[j], axn, bxn ), __fmaf_rn( fny[j], ayn, byn ), __fmaf_rn( fnz[j], azn, bzn ) ), r.tmin );
+			const float tn = fmaxf( max3f( __fmaf_rn( fnx[j], ax, bx ), __fmaf_rn( fny[j], ay, by ), __fmaf_rn( fnz[j], az, bz ) ), r.tmin );
 			const float tf = fminf( min3f( __fmaf_rn( ffx[j], axf, bxf ), __fmaf_rn( ffy[j], ayf, byf ), __fmaf_rn( ffz[j], azf, bzf ) ), tcull );
 			if (tn <= tf)
 			{
@@ -298,10 +299,10 @@ __device__ __forceinline__ uint32_t intersectNode( const RayState& r, const uint
 			}
 		}
 #else
-		testChild<0>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
-		testChild<1>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
-		testChild<2>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
-		testChild<3>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, axn, ayn, azn, bxn, byn, bzn, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<0>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<1>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<2>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
+		testChild<3>( r, tcull, K, nearx, neary, nearz, farx, fary, farz, ax, ay, az, bx, by, bz, axf, ayf, azf, bxf, byf, bzf, childBits4, bitIndex4, hitmask );
 #endif
 	}
 	return hitmask;
@@ -353,6 +354,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	const uint4* __restrict__ nodes = a.nodes;
 	const float4* __restrict__ tris = a.tris;
 	const uint32_t K = a.magic; // see qbyte / qpair; set by the launchers
+	const float tScaleTop = a.tlasTScale * (1.0f + 3.81469727e-6f);
 	const float4 singleInfo = SINGLE ? __ldg( a.instances + 4 ) : make_float4( 0, 0, 0, 0 ); // (BLAS root, instance id, ..) of record 0
 
 	RayState r = {};
@@ -566,7 +568,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				const uint4* np = nodes + (size_t)(nodeBase + rel) * 5;
 				const uint4 n0 = __ldg( np ), n1 = __ldg( np + 1 ), n2 = __ldg( np + 2 ), n3 = __ldg( np + 3 ), n4 = __ldg( np + 4 );
 				if (COUNT) nNodes++;
-				const uint32_t hm = intersectNode( r, K, n0, n1, n2, n3, n4 );
+				const uint32_t hm = intersectNode( r, (!SINGLE && instBase < 0) ? tScaleTop : (1.0f + 3.81469727e-6f), K, n0, n1, n2, n3, n4 );
 				ngroup = make_uint2( n1.x, (hm & 0xff000000u) | (n0.w >> 24) );
 				tgroup = make_uint2( n1.y, hm & 0x00ffffffu );
 			}

@@ -118,9 +118,10 @@ def deforming_sphere(n_tris: int = 100_000, time: float = 0.0, radius: float = 3
 
 
 def lattice_transforms(n: int = 1000, spacing: float = 8.0, time: float = 0.0, rotate: bool = False,
-                       seed: int = DEFAULT_SEED) -> np.ndarray:
+                       seed: int = DEFAULT_SEED, scale=None) -> np.ndarray:
     """C4 instances: n translation-only (bit-exact parity class) or randomly rotated transforms,
-    row-major mat4 with translation in cells 3,7,11 (common_types.h:473,486)."""
+    row-major mat4 with translation in cells 3,7,11 (common_types.h:473,486).  scale = (lo, hi): every instance
+    additionally gets a random non-uniform scale per axis (applied before the rotation)."""
     side = int(round(n ** (1.0 / 3.0)))
     while side ** 3 < n:
         side += 1
@@ -143,6 +144,9 @@ def lattice_transforms(n: int = 1000, spacing: float = 8.0, time: float = 0.0, r
         R[:, 1, 0] = y * x * (1 - c) + z * s; R[:, 1, 1] = c + y * y * (1 - c); R[:, 1, 2] = y * z * (1 - c) - x * s
         R[:, 2, 0] = z * x * (1 - c) - y * s; R[:, 2, 1] = z * y * (1 - c) + x * s; R[:, 2, 2] = c + z * z * (1 - c)
         M[:, :3, :3] = R.astype(np.float32)
+    if scale is not None:
+        S = rng.uniform(scale[0], scale[1], (n, 3)).astype(np.float32)
+        M[:, :3, :3] = M[:, :3, :3] * S[:, None, :]
     return np.ascontiguousarray(M.reshape(n, 16))
 
 

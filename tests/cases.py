@@ -21,13 +21,21 @@ def case_soup(n_tris=2000, n_rays=20000, seed=11):
     return dict(name=f"soup{n_tris}", meshes=[soup], instances=[(0, None)], rays=(O, D))
 
 
-def case_instanced(n_inst=27, n_rays=20000, rotate=False, seed=5):
+def case_instanced(n_inst=27, n_rays=20000, rotate=False, seed=5, scale=None):
     sph = scenes.uv_sphere(20, 11, 1.0)
     grid = scenes.grid_mesh(8, 8)
-    M = scenes.lattice_transforms(n_inst, spacing=3.0, rotate=rotate, seed=seed)
+    M = scenes.lattice_transforms(n_inst, spacing=3.0, rotate=rotate, seed=seed, scale=scale)
     inst = [(i % 2, M[i]) for i in range(n_inst)]
     O, D = scenes.random_rays(n_rays, 6.0, seed=seed + 2)
-    return dict(name="inst%d%s" % (n_inst, "rot" if rotate else ""), meshes=[sph, grid], instances=inst, rays=(O, D))
+    return dict(name="inst%d%s%s" % (n_inst, "rot" if rotate else "", "scaled" if scale else ""), meshes=[sph, grid], instances=inst, rays=(O, D))
+
+
+def case_c4_class(n_inst=1000, n_tris=100_000, time=0.0, rotate=False):
+    """BASELINE.json configs[3] at size: 1000 instances of one 100 000-triangle deforming sphere on a 10 x 10 x 10 lattice
+    (translation-only = the bit-exact parity class; rotate = the second, rotated run of SURVEY.md 8d C4)."""
+    mesh = scenes.deforming_sphere(n_tris, time=time)
+    M = scenes.lattice_transforms(n_inst, spacing=8.0, time=time, rotate=rotate)
+    return dict(name="c4", meshes=[mesh], instances=[(0, M[i]) for i in range(n_inst)])
 
 
 def case_axis_aligned(n_rays=20000, seed=3):

@@ -5,14 +5,41 @@
 // pytest side (tests/test_plugin_gpu.py); the frame and the CoreStats go back the same way.
 //
 //   plugin_host <libRenderCore_B200.so> <scene.bin> <out.bin>
+//
+// Two builds of this file:
+//   * default: the boundary types come from include/lh2_abi.h (the repo's restatement), the library is dlopen'ed by path -- builds anywhere;
+//   * -DHOST_USES_REFERENCE_HEADERS (oracle/Makefile -> oracle/_ref/plugin_host_ref, only where /root/reference exists): the boundary types
+//     are the REFERENCE'S OWN declarations (lib/RenderSystem/rendersystem.h: CoreAPI_Base, CoreTri, CoreMaterial, ViewPyramid, CoreStats
+//     ...) and the core is loaded by the reference's own loader, lib/RenderSystem/core_api_base.cpp compiled in place and linked in:
+//     CoreAPI_Base::CreateCoreAPI( "RenderCore_B200" ) (:119-132).  So the vtable order, CoreStats returned by value, the double Init and
+//     every struct layout are seen through the reference's compiler view, not through ours.  argv[1] is ignored (the loader dlopens
+//     "libRenderCore_B200.so" from LD_LIBRARY_PATH, core_api_base.cpp:97-110).
+#ifdef HOST_USES_REFERENCE_HEADERS
+#include "rendersystem.h"
+#include <cstdarg>
+typedef float3 float3_t;
+typedef float4 float4_t;
+typedef mat4 mat4_t;
+typedef int2 int2_t;
+typedef uchar4 uchar4_t;
+// the one symbol core_api_base.cpp needs from lib/platform/system.cpp (:221-236: message, then exit)
+void FatalError( const char* fmt, ... )
+{
+	va_list args;
+	va_start( args, fmt );
+	vfprintf( stderr, fmt, args );
+	va_end( args );
+	exit( 1 );
+}
+#else
 #include "../../include/lh2_abi.h"
+using namespace lh2abi;
+#endif
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
 #include <vector>
-
-using namespace lh2abi;
 
 static std::vector<char> readAll( const char* path )
 {
@@ -36,6 +63,11 @@ struct Reader {
 int main( int argc, char** argv )
 {
 	if (argc < 4) return 2;
+#ifdef HOST_USES_REFERENCE_HEADERS
+	CoreAPI_Base* api = CoreAPI_Base::CreateCoreAPI( "RenderCore_B200" ); // the reference's loader: dlopen, dlsym CreateCore, createCore(), Init()
+	void* lib = dlopen( "libRenderCore_B200.so", RTLD_NOW | RTLD_NOLOAD ); // the handle the loader keeps to itself, for the read-back symbols below
+	if (!api || !lib) { fprintf( stderr, "CreateCoreAPI failed\n" ); return 3; }
+#else
 	void* lib = dlopen( argv[1], RTLD_NOW | RTLD_GLOBAL );
 	if (!lib) { fprintf( stderr, "dlopen: %s\n", dlerror() ); return 3; }
 	typedef CoreAPI_Base* (*createCoreFunction)();
@@ -45,6 +77,7 @@ int main( int argc, char** argv )
 	if (!createCore || !destroyCore) { fprintf( stderr, "CreateCore / DestroyCore not exported\n" ); return 3; }
 	CoreAPI_Base* api = createCore();
 	api->Init(); // the loader calls Init a second time (core_api_base.cpp:128-129)
+#endif
 
 	std::vector<char> file = readAll( argv[2] );
 	Reader r{ file.data() };
@@ -113,7 +146,9 @@ int main( int argc, char** argv )
 	const CoreDirectionalLight* dir = (const CoreDirectionalLight*)r.bytes( (size_t)nDir * sizeof( CoreDirectionalLight ) );
 	api->SetLights( area, nArea, point, nPoint, spot, nSpot, dir, nDir );
 
-	GLTexture target;
+	// (raw storage: the reference's GLTexture has no default constructor and its real ones call into GL; cores read ID / width / height only)
+	alignas( GLTexture ) static char targetStorage[sizeof( GLTexture )];
+	GLTexture& target = *reinterpret_cast<GLTexture*>( targetStorage );
 	target.ID = 0, target.width = (uint)width, target.height = (uint)height;
 	api->SetTarget( &target, (uint)spp );
 	int2_t probe;
@@ -148,6 +183,8 @@ int main( int argc, char** argv )
 	fwrite( nameBuf, 1, 64, out );
 	fclose( out );
 	api->Shutdown();
-	destroyCore();
+#ifndef HOST_USES_REFERENCE_HEADERS
+	destroyCore(); // (the reference looks DestroyCore up and never calls it, core_api_base.cpp:126)
+#endif
 	return 0;
 }

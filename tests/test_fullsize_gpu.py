@@ -169,6 +169,34 @@ def test_c2_refit_with_same_vertices_is_identity(c2):
     assert np.array_equal(before.view(np.uint32), after.view(np.uint32))
 
 
+def test_c3_10m_against_the_reference_fixture():
+    """BASELINE.json configs[2] at size: the 10 000 000-triangle soup against hit buffers made by the unmodified reference
+    (tests/golden/make_c3_fixture.py: BVH2::Rebuild + Traverse of lib/RenderCore_Bart/bvh.cpp over the same soup): 40 000 primary rays
+    and the four diffuse-bounce waves behind them.  Bit-exact t and triangle ids except the documented classes (tests/parity.py)."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c3_10m.npz")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/c3_10m.npz missing (python tests/golden/make_c3_fixture.py)")
+    g = np.load(path)
+    verts = scenes.triangle_soup(10_000_000)
+    rc = core.RenderCoreB200(0)
+    rc.SetGeometry(0, verts); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
+    total = exceptions = 0
+    for k in range(int(g["waves"])):
+        O, D, t, prim = g["O%d" % k], g["D%d" % k], g["t%d" % k], g["prim%d" % k]
+        h = core.unpack_hits(rc.TraceClosest(*core.pack_rays(O, D, tmin=workload.EPS)))
+        bad = np.flatnonzero((h["prim"] != prim) | (h["t"].view(np.uint32) != t.view(np.uint32)))
+        # a disagreement is acceptable only as a documented class: our hit is CLOSER and is what the reference arithmetic gives for that
+        # triangle (a box the reference's slab test culled), or an exact tie; never a farther hit
+        for i in bad:
+            tri = verts[h["prim"][i]] if h["prim"][i] >= 0 else None
+            assert tri is not None and h["t"][i] <= t[i], (k, i, h["t"][i], t[i], h["prim"][i], prim[i])
+        total += len(t); exceptions += len(bad)
+        print("C3 10M wave %d: %d rays, %d hits, %d exceptions" % (k, len(t), int((prim >= 0).sum()), len(bad)))
+    assert exceptions <= max(1, int(1e-5 * total)), (exceptions, total)
+    rc.Shutdown()
+
+
 def test_c3_class_soup_properties():
     """10M-triangle soup (scene not L2-resident): permutation invariance, any-hit consistency, and a sampled check against
     the reference arithmetic by exhaustive search over the triangles near each reported hit is too slow here -- the oracle

@@ -51,6 +51,88 @@ def test_small_cases_golden(oracles, make):
     parity.assert_parity(rep)
 
 
+@pytest.mark.parametrize("scale", [None, (0.5, 1.8)])
+def test_rotated_and_scaled_instances_vs_exhaustive_search(oracles, scale):
+    """Rotated (and non-uniformly scaled) instances through the general two-level kernels.  The reference's own TLAS is wrong for
+    them -- its leaf bounds transform only two corners of the mesh box (bvh.cpp:579-587) and it misses geometry -- so the checker is
+    the exhaustive search with the reference's instance entry and triangle arithmetic (oracle brute mode: bvh.cpp:607-610 +
+    common.h:19-50 over every triangle of every instance; t is compared across instances in object-space units, as the reference
+    does).  Bar: t bit-exact and (instance, triangle) identical on every ray except exact ties.  The `inst27rot` golden buffer (made
+    by the unmodified reference) must agree wherever the reference found a hit at all: what it found is never closer than ours."""
+    case = cases.case_instanced(rotate=True, scale=scale)
+    O, D = case["rays"]
+    rc = cases.load_core(core.RenderCoreB200(0), case)
+    h = core.unpack_hits(rc.TraceClosest(*core.pack_rays(O, D)))
+    port = cases.load_oracle(case, "port")
+    tb, pb, ib = port.trace(O, D, nthreads=8, mode="brute")
+    same = (h["t"].view(np.uint32) == tb.view(np.uint32)) & (h["prim"] == pb) & ((h["inst"] == ib) | (pb < 0))
+    bad = np.flatnonzero(~same)
+    # what is left must be exact ties: same t bits, another (instance, triangle) whose reference-arithmetic t is that t
+    t_choice = port.t_of(O[bad], D[bad], h["inst"][bad], h["prim"][bad])
+    assert np.array_equal(h["t"][bad].view(np.uint32), tb[bad].view(np.uint32)) and np.array_equal(t_choice.view(np.uint32), tb[bad].view(np.uint32)), \
+        (len(bad), bad[:5], h["t"][bad][:5], tb[bad][:5])
+    assert len(bad) <= max(1, int(1e-4 * len(O))), len(bad)
+    assert (h["prim"] >= 0).mean() > 0.2
+    if scale is None:
+        g = np.load(os.path.join(GOLDEN, "inst27rot.npz"))
+        ref_hit = g["prim"] >= 0
+        assert np.all(h["t"][ref_hit] <= g["t"][ref_hit]), "the reference reports a hit closer than the exhaustive search"
+        agree = (h["t"].view(np.uint32) == g["t"].view(np.uint32)) & (h["prim"] == g["prim"])
+        print("rotated instances: the reference's own TLAS agrees on %.2f %% of the rays (it misses geometry under rotation)" % (100 * agree.mean()))
+    # any-hit through the same kernels
+    tmax = np.random.default_rng(3).uniform(0.5, 12.0, len(O)).astype(np.float32)
+    assert np.array_equal(rc.TraceAny(*core.pack_rays(O, D, tmax=tmax)), tb < tmax)
+    print("rotated%s instances: %d rays, %d exact ties" % (" + scaled" if scale else "", len(O), len(bad)))
+    rc.Shutdown()
+
+
+def test_c4_class_refit_and_toplevel_rebuild_vs_oracle(oracles):
+    """BASELINE.json configs[3] at size: 1000 translation-only instances of a 100 000-triangle deforming sphere; three frames, each
+    with new vertex positions (GPU refit through SetGeometry) and new instance transforms (top-level rebuild), 200 000 primary
+    and 200 000 shadow rays per frame against the reference traversal (the oracle rebuilds its BVHs every frame, which is what the
+    reference does: rendercore.cpp:78,199)."""
+    n_inst, n_tris, n_rays = 1000, 100_000, 200_000
+    rc = core.RenderCoreB200(0)
+    rng = np.random.default_rng(41)
+    view = scenes.view_pyramid(width=1920, height=1080, **scenes.C4_CAMERA)
+    Oall, Dall = scenes.primary_rays(view, 1920, 1080)
+    port = None
+    for frame in range(3):
+        tm = 0.1 * frame
+        case = cases.case_c4_class(n_inst, n_tris, time=tm)
+        rc.SetGeometry(0, case["meshes"][0])  # frame 0 builds, frames 1 and 2 refit on the device
+        for i, (mesh, mat) in enumerate(case["instances"]):
+            rc.SetInstance(i, mesh, mat)
+        rc.SetInstance(n_inst, -1)
+        rc.UpdateToplevel()
+        if frame:
+            assert rc.GetCoreStats()["refitTime"] > 0
+        if port is not None:
+            port.close()
+        port = cases.load_oracle(case, "port")
+        idx = np.sort(rng.choice(len(Oall), n_rays, replace=False))
+        O, D = np.ascontiguousarray(Oall[idx]), np.ascontiguousarray(Dall[idx])
+        hits = rc.TraceClosest(*core.pack_rays(O, D))
+        t, prim, inst = port.trace(O, D, nthreads=8)
+        rep = parity.compare("c4 frame %d" % frame, hits, port, O, D, t, prim, inst)
+        parity.assert_parity(rep)
+        assert (prim >= 0).mean() > 0.3
+        # one shadow ray per hit towards a point light (tmax = distance - 2 eps), any-hit <=> reference closest t < tmax
+        hit = prim >= 0
+        P = O[hit] + D[hit] * t[hit, None] * np.float32(0.999)
+        L = np.asarray((0.0, 80.0, -40.0), np.float32) - P
+        dist = np.linalg.norm(L, axis=1).astype(np.float32)
+        Ld = scenes._normalize_ref(L.astype(np.float32))
+        ts, _, _ = port.trace(P, Ld, nthreads=8)
+        occ = rc.TraceAny(*core.pack_rays(P, Ld, tmin=1e-4, tmax=dist - np.float32(2e-4)))
+        bad = np.flatnonzero(occ != (ts < dist - np.float32(2e-4)))
+        assert len(bad) <= max(1, int(1e-5 * len(P))), (len(bad), bad[:5])
+    st = rc.GetCoreStats()
+    print("C4 class: %d instances, %d BLAS nodes, %d TLAS nodes, refit %.3f ms, top level %.3f ms" % (st["instanceCount"], st["wideNodeCount"], st["tlasNodeCount"], st["refitTime"], st["tlasTime"]))
+    port.close()
+    rc.Shutdown()
+
+
 def test_bigger_soup_vs_oracle(oracles):
     case = cases.case_soup(n_tris=200_000, n_rays=300_000, seed=21)
     rep, _ = _run_case(case, oracles, golden=False)

@@ -50,17 +50,15 @@ def _write_scene(path, sc, view, w, h, spp, frames, probe):
             f.write(np.ascontiguousarray(sc[k], np.float32).tobytes())
 
 
-def test_cpp_host_through_the_vtable_equals_the_c_abi(tmp_path):
+def _run_host_and_compare(tmp_path, exe, env=None):
     sc = _lit_scene()
     w, h, spp, frames = 160, 90, 1, 2
     probe = (w // 2, h // 2)
     view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
-    exe = str(tmp_path / "plugin_host")
-    subprocess.run(["g++", "-std=c++17", "-O1", "-o", exe, os.path.join(HERE, "cpp", "plugin_host.cpp"), "-ldl"], check=True)
     scene_bin, out_bin = str(tmp_path / "scene.bin"), str(tmp_path / "out.bin")
     _write_scene(scene_bin, sc, view, w, h, spp, frames, probe)
-    r = subprocess.run([exe, core.LIB_PATH, scene_bin, out_bin], capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe, core.LIB_PATH, scene_bin, out_bin], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stderr + r.stdout
     raw = open(out_bin, "rb").read()
     n = w * h * 4
     frame = np.frombuffer(raw, np.float32, n).reshape(h, w, 4)
@@ -89,3 +87,22 @@ def test_cpp_host_through_the_vtable_equals_the_c_abi(tmp_path):
     assert (total, ext, shadow) == (st["totalRays"], st["totalExtensionRays"], st["totalShadowRays"])
     assert (probed_inst, probed_tri) == (st["probedInstid"], st["probedTriid"]) and probed_tri >= 0
     assert probed_dist == pytest.approx(st["probedDist"], rel=1e-6)
+
+
+def test_cpp_host_through_the_vtable_equals_the_c_abi(tmp_path):
+    exe = str(tmp_path / "plugin_host")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-o", exe, os.path.join(HERE, "cpp", "plugin_host.cpp"), "-ldl"], check=True)
+    _run_host_and_compare(tmp_path, exe)
+
+
+def test_host_built_from_the_reference_headers_and_loader(tmp_path):
+    """The same host compiled against the REFERENCE'S OWN declarations (lib/RenderSystem/rendersystem.h) and linked with the
+    reference's own loader (lib/RenderSystem/core_api_base.cpp, compiled in place by oracle/Makefile where /root/reference exists;
+    the binary travels to the GPU box): CoreAPI_Base::CreateCoreAPI( "RenderCore_B200" ) finds libRenderCore_B200.so on the library
+    path, and every virtual call, struct and the by-value CoreStats go through the reference's compiler view of the types."""
+    exe = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "plugin_host_ref")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/plugin_host_ref not built (needs /root/reference: make -C oracle)")
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = os.path.dirname(core.LIB_PATH) + os.pathsep + env.get("LD_LIBRARY_PATH", "")
+    _run_host_and_compare(tmp_path, exe, env)
