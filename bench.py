@@ -8,7 +8,7 @@ sphere field, 1 000 000 triangles) at the size of BASELINE.json configs[4]: 3840
 timed at every N (strong scaling): with N ranks the frame is sharded by interleaved 32x8 tiles (scene replicated), and every frame ends
 with the gather of the accumulator over NVLink (one fused peer-memory pull + finalize kernel, wavefront.cu).
   value  = rays of the frame (all ranks) / time of the slowest rank (CUDA events on the core's stream, barrier + synchronize on both sides)
-  e2e    = the same frames through the host-facing calls b200_render + b200_gather_finalize + b200_read_frame: the view pyramid goes in
+  e2e    = the same frames through the host-facing calls b200_render (which ends with the gather) + b200_read_frame: the view pyramid goes in
            from host memory, the finished RGBA32F frame comes back into pinned host memory, both inside the timed region
   check  = every rank renders the frame once unsharded and compares its gathered accumulator with it bit for bit
 Sub-blocks (explanation, not the headline):
@@ -417,11 +417,10 @@ def run_b200(args):
     p2p = world > 1 and sr.gather == "p2p"
 
     def frame():
-        # one step: this rank's tiles, then the gather (N > 1).  Both calls synchronise their stream before they return.
+        # one step: this rank's tiles, then the gather (N > 1).  With open peers b200_render ends with the gather itself (arrival barrier,
+        # pull + finalize kernel, second barrier: the tail of the frame's enqueue); the call synchronises its stream before it returns.
         chk(lib.b200_render(h, vp_ref, 1))
-        if p2p:
-            chk(lib.b200_gather_finalize(h, spp))
-        elif world > 1:
+        if world > 1 and not p2p:
             dist.all_reduce(sr.acc, op=dist.ReduceOp.SUM)
             chk(lib.b200_finalize(h, spp))
 
@@ -470,15 +469,11 @@ def run_b200(args):
     for _ in range(args.steps):
         chk(lib.b200_render(h, vp_ref, 1))
         st = rc.GetCoreStats()
-        render_ms += st["renderTime"]
+        render_ms += st["renderTime"] - st["gatherMs"]
         rays_mine += st["totalRays"]
         if p2p:
-            g0.record(stream)
-            chk(lib.b200_gather_finalize(h, spp))
-            g1.record(stream)
-            g1.synchronize()
-            gather_ms += g0.elapsed_time(g1)
-            gather_kernel_ms += rc.GetCoreStats()["gatherKernelMs"]
+            gather_ms += st["gatherMs"]
+            gather_kernel_ms += st["gatherKernelMs"]
         elif world > 1:
             g0.record(stream)
             dist.all_reduce(sr.acc, op=dist.ReduceOp.SUM)
@@ -550,8 +545,8 @@ def run_b200(args):
             "frame": {"check": frame_check, "render_ms_slowest_rank": vec[2] / steps, "render_ms_fastest_rank": vmin[2] / steps,
                       "gather": (sr.gather if world > 1 else "none"),
                       "gather_ms_barrier_to_barrier": vec[3] / steps if world > 1 else 0.0,
-                      "gather_note": "barrier_to_barrier = arrival wait for the slowest rank + pull + second arrival (events around b200_gather_finalize, slowest rank); "
-                                     "kernel = the pull + finalize kernel alone, after everyone has arrived",
+                      "gather_note": "barrier_to_barrier = from a rank's own arrival to the end of the second arrival: waiting for the slowest rank + pull + finalize (CUDA "
+                                     "events inside the frame, the rank that waited longest); kernel = the pull + finalize kernel alone, after everyone has arrived",
                       "rank0_stats": {k: st[k] for k in ("primaryRayCount", "traceTime0", "bounce1RayCount", "traceTime1", "deepRayCount", "traceTimeX",
                                                          "totalShadowRays", "shadowTraceTime", "shadeTime", "renderTime")}},
             "gpu_launches": int(cnt[1]),
@@ -566,7 +561,7 @@ def run_b200(args):
         if e2e_ms:
             line["e2e"] = {"value": rays_per_frame / (vec[1] * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 68 + 96 * st["framePasses"],
                            "d2h_bytes_per_step": frame_bytes, "ms_per_step": vec[1],
-                           "api": "b200_render (ViewPyramid from host memory) + b200_gather_finalize + b200_read_frame into pinned host memory (rank 0): what the RenderSystem "
+                           "api": "b200_render (ViewPyramid from host memory; ends with the peer-memory gather when N > 1) + b200_read_frame into pinned host memory (rank 0): what the RenderSystem "
                                   "sees through CoreAPI::Render; the C++ vtable face forwards to the same calls (tests/test_plugin_gpu.py)",
                            "note": "inputs of this path are a 68-byte view pyramid plus 96 bytes of pass parameters per pass; the output is the finished RGBA32F frame"}
         if waves_out:

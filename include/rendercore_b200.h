@@ -121,6 +121,11 @@ B200_API int b200_set_textures( b200_core* c, const void* coreTexDescs, int coun
 B200_API int b200_set_accumulator_buffer( b200_core* c, void* dAccumulator );
 B200_API int b200_finalize( b200_core* c, uint32_t totalSamples );
 /* Multi-GPU gather over peer memory, for tile-sharded frames (Setting shardIndex / shardCount), one process per GPU of one box.
+ * Once the peers are open (b200_open_peers) and the frame is sharded over exactly them, b200_render ENDS with the gather: the arrival
+ * barrier, the pull + finalize kernel and the second barrier are the tail of the frame's enqueue (one submission, one synchronisation;
+ * b200_stats.gatherMs / gatherKernelMs), so the frame and the accumulator a rank reads after b200_render are complete -- what a
+ * RenderSystem calling CoreAPI::Render on every rank expects.  Setting gatherInRender = 0 leaves the gather to an explicit
+ * b200_gather_finalize call.
  * b200_peer_handle (after b200_set_target, core-owned accumulator) returns 128 bytes: the CUDA IPC handles of this core's accumulator
  * and of its arrival flags.  The host exchanges the blobs between the ranks (any transport) and gives every core the whole table with
  * b200_open_peers (entry r = rank r's blob).  Per frame, after b200_render, b200_gather_finalize replaces all-reduce + b200_finalize:
@@ -153,9 +158,12 @@ typedef struct b200_stats {
 	uint32_t kernelLaunches;            /* kernels this core has launched since creation */
 	float lastTraceMs;                  /* device time of the last b200_trace_* kernel (CUDA events on the core's stream) */
 	uint32_t bvhCacheHits;              /* meshes whose host-built tree came from the on-disk cache (environment B200_BVH_CACHE = directory) */
-	float gatherKernelMs;               /* device time of the last b200_gather_finalize's pull + finalize kernel alone (without the arrival waits) */
+	float gatherKernelMs;               /* device time of the last gather's pull + finalize kernel alone (without the arrival waits) */
 	uint32_t frameGraphLaunches;        /* frames replayed as a CUDA graph since creation (Setting frameGraph) */
 	uint32_t frameChains, framePasses;  /* of the last b200_render: independent wave chains, passes the samples were split into */
+	float hostEnqueueMs, hostWaitMs, hostTotalMs; /* host clock of the last b200_render: until everything was enqueued, waiting for the device, whole call */
+	float gatherMs;                     /* of the last b200_render that ended with the peer-memory gather: device time from this rank's arrival to the end of the
+	                                       second arrival (waiting for the slowest rank + pull + finalize); 0 when the frame had no gather */
 } b200_stats;
 B200_API int b200_get_stats( b200_core* c, b200_stats* out );
 B200_API int b200_set_probe( b200_core* c, int x, int y );

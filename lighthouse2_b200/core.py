@@ -46,6 +46,7 @@ class Stats(C.Structure):
         ("wideNodeCount", C.c_uint32), ("triangleCount", C.c_uint32), ("instanceCount", C.c_uint32), ("tlasNodeCount", C.c_uint32),
         ("kernelLaunches", C.c_uint32), ("lastTraceMs", C.c_float), ("bvhCacheHits", C.c_uint32),
         ("gatherKernelMs", C.c_float), ("frameGraphLaunches", C.c_uint32), ("frameChains", C.c_uint32), ("framePasses", C.c_uint32),
+        ("hostEnqueueMs", C.c_float), ("hostWaitMs", C.c_float), ("hostTotalMs", C.c_float), ("gatherMs", C.c_float),
     ]
 
     def as_dict(self):

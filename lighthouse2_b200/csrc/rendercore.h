@@ -58,6 +58,7 @@ public:
 	int OpenPeers( const void* handles, int world, int rank );
 	int ClosePeers();
 	int GatherFinalize( uint32_t totalSamples );
+	long long peerLimitTicks() const;
 	int Finalize( uint32_t totalSamples );                    // frame = accumulator / totalSamples (after a gather)
 	int Render( const void* viewPyramid, int converge );
 	int ReadAccumulator( float* dst );

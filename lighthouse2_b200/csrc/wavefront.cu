@@ -24,6 +24,7 @@
 // image and the accumulators of all shards simply add up.
 #include "rendercore.h"
 #include "../../include/lh2_abi.h"
+#include <chrono>
 #include <cstring>
 #include <vector>
 
@@ -907,9 +908,15 @@ struct PeerTable {
 // accumulator) is visible to a peer that has seen the flag.  A peer that never arrives makes the wait give up after ~2 s and
 // raise *timeout, instead of hanging the device (limit: Setting peerTimeoutMs, converted to SM clock ticks by the host); the pull
 // kernel that follows does nothing when the flag is up, and the host clears the flag after reporting the error.
-__global__ void peerBarrierKernel( const PeerTable peers, const int world, const int rank, const uint32_t epoch, uint32_t* timeout, const long long limitTicks )
+// The epoch is a device-resident word of this rank that the kernel itself advances (every rank runs the same sequence of barriers, so the
+// words stay in step): no host-side argument changes from frame to frame, which lets the barrier be part of the captured frame graph.
+__global__ void peerBarrierKernel( const PeerTable peers, const int world, const int rank, uint32_t* epochWord, uint32_t* timeout, const long long limitTicks )
 {
+	__shared__ uint32_t sEpoch;
 	const int t = threadIdx.x;
+	if (t == 0) sEpoch = ++*epochWord;
+	__syncthreads();
+	const uint32_t epoch = sEpoch;
 	if (t >= world) return;
 	__threadfence_system();
 	asm volatile( "st.release.sys.global.u32 [%0], %1;" ::"l"( peers.flags[t] + rank ), "r"( epoch ) : "memory" );
@@ -926,9 +933,10 @@ __global__ void peerBarrierKernel( const PeerTable peers, const int world, const
 }
 
 __global__ void gatherFinalizeKernel( const PeerTable peers, const int world, const int rank, float4* __restrict__ frame, const uint32_t width,
-	const uint32_t height, const uint32_t tilesX, const float scale, const uint32_t* __restrict__ timeout )
+	const uint32_t height, const uint32_t tilesX, const float scaleArg, const PassParams* __restrict__ lastPass, const uint32_t* __restrict__ timeout )
 {
 	if (*timeout) return; // a peer did not arrive: its tiles may be incomplete, nothing is pulled this frame
+	const float scale = lastPass ? __ldg( &lastPass->finalScale ) : scaleArg; // inside a frame: 1 / samples, as the frame's last pass has it
 	const uint32_t pixels = width * height;
 	float4* const own = peers.acc[rank];
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < pixels; i += gridDim.x * blockDim.x)
@@ -998,6 +1006,12 @@ struct FramePlan {
 	struct { float4 *rayO[2], *rayD[2], *state[2], *info[2], *hits, *conO[2], *conD[2], *conE[2], *slotS, *slotC; uint32_t tiles, capacity; } chain[MAX_CHAINS];
 	uint32_t chains, passes, maxLen, overlap, anyLight, bsdf, clearAccumulator, timedPasses;
 	int isect, smCount, shadeGrid;
+	// tile-sharded frame with open peers: the gather over peer memory is the tail of the frame (see enqueueFrame)
+	uint32_t gather;
+	int peerWorld, peerRank;
+	PeerTable peers;
+	uint32_t *peerEpochWord, *peerTimeout, *peerTimeoutHost;
+	long long peerLimitTicks;
 };
 
 struct WavefrontState {
@@ -1006,6 +1020,7 @@ struct WavefrontState {
 	int chains = 0;        // Setting chains: 0 = automatic (by the size of a pass), else 1..MAX_CHAINS
 	int useGraph = 1;      // Setting frameGraph: a frame whose plan repeats is replayed as a CUDA graph
 	int waveTimers = 1;    // Setting waveTimers: per-wave CUDA events for the CoreStats trace / shade times
+	int gatherInRender = 1; // Setting gatherInRender: with open peers, a tile-sharded Render() ends with the peer-memory gather
 	uint32_t pathsPerPass = 32u << 20;
 	Chain chain[MAX_CHAINS];
 	DeviceBuffer counters, passParams, accumOwn, frame, materials, lights, skyImage, texels, blueNoise;
@@ -1021,7 +1036,7 @@ struct WavefrontState {
 	int bounceCap = 0, roulette = 1, bsdf = 0; // bsdf: 0 = Lambert + speculars, 1 = Disney principled (rendercore_optix7/kernels/bsdf.h picks one at compile time)
 	uint32_t samplesTaken = 0, frameCounter = 0;
 	int probeX = -1, probeY = -1;
-	cudaEvent_t frameBegin = nullptr, frameEnd = nullptr, fork = nullptr, gatherBegin = nullptr, gatherEnd = nullptr;
+	cudaEvent_t frameBegin = nullptr, frameEnd = nullptr, fork = nullptr, gatherWait = nullptr, gatherBegin = nullptr, gatherEnd = nullptr;
 	std::vector<cudaEvent_t> timers; // per (timed pass, chain, path length): extend begin, extend end, shade end, connect begin, connect end
 	int overlapConnect = 1;
 	// the captured frame
@@ -1033,7 +1048,6 @@ struct WavefrontState {
 	// peer-memory gather (OpenPeers): the other ranks' accumulators and arrival flags, mapped through CUDA IPC
 	PeerTable peers{};
 	int peerWorld = 0, peerRank = 0;
-	uint32_t peerEpoch = 0;
 	float peerTimeoutMs = 2000.f;
 	void* peerMapped[2 * MAX_PEERS] = {};
 	DeviceBuffer peerFlags; // MAX_PEERS arrival words + 1 timeout word, written by the peers
@@ -1065,7 +1079,7 @@ struct WavefrontState {
 			if (c.connect) cudaStreamDestroy( c.connect );
 		}
 		for (cudaEvent_t e : timers) if (e) cudaEventDestroy( e );
-		for (cudaEvent_t e : { frameBegin, frameEnd, fork, gatherBegin, gatherEnd }) if (e) cudaEventDestroy( e );
+		for (cudaEvent_t e : { frameBegin, frameEnd, fork, gatherWait, gatherBegin, gatherEnd }) if (e) cudaEventDestroy( e );
 		if (captureStream) cudaStreamDestroy( captureStream );
 	}
 };
@@ -1092,6 +1106,7 @@ int RenderCore::SettingWavefront( const char* name, float value )
 	if (!strcmp( name, "chains" )) { if (v < 0 || v > MAX_CHAINS) return fail( "Setting chains: 0 (automatic) or 1..4" ); w->chains = v; return 0; }
 	if (!strcmp( name, "frameGraph" )) { w->useGraph = value >= 0.5f; if (!w->useGraph) w->dropGraph(); return 0; }
 	if (!strcmp( name, "waveTimers" )) { w->waveTimers = value >= 0.5f; return 0; }
+	if (!strcmp( name, "gatherInRender" )) { w->gatherInRender = value >= 0.5f; return 0; }
 	if (!strcmp( name, "peerTimeoutMs" )) { if (!(value > 0)) return fail( "Setting peerTimeoutMs: > 0" ); w->peerTimeoutMs = value; return 0; }
 	if (!strcmp( name, "russianRoulette" )) { w->roulette = value >= 0.5f; return 0; }
 	if (!strcmp( name, "bsdf" )) { if (v < 0 || v > 1) return fail( "Setting bsdf: 0 (Lambert, lib/sharedBSDFs/lambert.h) or 1 (Disney, disney.h)" ); w->bsdf = v; return 0; }
@@ -1114,7 +1129,7 @@ int RenderCore::SetTarget( int width, int height, int spp )
 	if ((e = w->accumOwn.reserve( px * 16, false, stream )) != cudaSuccess || (e = w->frame.reserve( px * 16, false, stream )) != cudaSuccess) return fail( "SetTarget buffers", e );
 	if ((e = cudaMemsetAsync( w->accumulator(), 0, px * 16, stream )) != cudaSuccess) return fail( "SetTarget clear", e );
 	w->samplesTaken = 0;
-	for (cudaEvent_t* ev : { &w->frameBegin, &w->frameEnd }) if (!*ev && (e = cudaEventCreate( ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
+	for (cudaEvent_t* ev : { &w->frameBegin, &w->frameEnd, &w->gatherWait, &w->gatherBegin, &w->gatherEnd }) if (!*ev && (e = cudaEventCreate( ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
 	if (!w->fork && (e = cudaEventCreateWithFlags( &w->fork, cudaEventDisableTiming )) != cudaSuccess) return fail( "cudaEventCreate", e );
 	if (!w->captureStream && (e = cudaStreamCreateWithFlags( &w->captureStream, cudaStreamNonBlocking )) != cudaSuccess) return fail( "capture stream", e );
 	for (Chain& c : w->chain)
@@ -1454,6 +1469,20 @@ static cudaError_t enqueueFrame( WavefrontState& w, const FramePlan& p, cudaStre
 		n++;
 	}
 	for (uint32_t c = 0; c < p.chains; c++) { cudaEventRecord( w.chain[c].done, w.chain[c].main ); cudaStreamWaitEvent( origin, w.chain[c].done, 0 ); }
+	if (p.gather)
+	{
+		// the exchange step of a tile-sharded frame, as the tail of the frame: arrive (everyone's tiles are accumulated), pull the foreign
+		// tiles over NVLink + finalize, arrive again (everyone has pulled: the accumulators may be written by the next frame)
+		cudaEventRecordWithFlags( w.gatherWait, origin, recFlags );
+		peerBarrierKernel<<<1, 32, 0, origin>>>( p.peers, p.peerWorld, p.peerRank, p.peerEpochWord, p.peerTimeout, p.peerLimitTicks );
+		cudaEventRecordWithFlags( w.gatherBegin, origin, recFlags );
+		gatherFinalizeKernel<<<p.smCount * 8, 256, 0, origin>>>( p.peers, p.peerWorld, p.peerRank, p.frame, p.f.width, p.f.height, p.f.tilesX, 0.f,
+			p.passDev + (p.passes - 1), p.peerTimeout );
+		cudaEventRecordWithFlags( w.gatherEnd, origin, recFlags );
+		peerBarrierKernel<<<1, 32, 0, origin>>>( p.peers, p.peerWorld, p.peerRank, p.peerEpochWord, p.peerTimeout, p.peerLimitTicks );
+		if ((e = cudaMemcpyAsync( p.peerTimeoutHost, p.peerTimeout, 4, cudaMemcpyDeviceToHost, origin )) != cudaSuccess) return e;
+		n += 3;
+	}
 	if ((e = cudaMemcpyAsync( p.countersHost, p.countersDev, sizeof( uint32_t ) * COUNTER_STRIDE * p.chains * p.passes, cudaMemcpyDeviceToHost, origin )) != cudaSuccess) return e;
 	cudaEventRecordWithFlags( w.frameEnd, origin, recFlags );
 	if (launches) *launches = n;
@@ -1467,6 +1496,8 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	WavefrontState* w = wf;
 	if (!w || w->width == 0) return fail( "Render: SetTarget has not been called" );
 	if (!viewPyramid) return fail( "Render: null view" );
+	const auto hostT0 = std::chrono::steady_clock::now();
+	auto hostMs = [&]() { return std::chrono::duration<float, std::milli>( std::chrono::steady_clock::now() - hostT0 ).count(); };
 	if (ensureToplevel()) return 1;
 	cudaError_t e;
 	const float* vp = (const float*)viewPyramid; // pos, p1, p2, p3 (4 x float3), then 5 floats (common_classes.h:362-385)
@@ -1538,7 +1569,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	}
 	const size_t counterWords = (size_t)COUNTER_STRIDE * chains * (plan.passes ? plan.passes : 1);
 	if ((e = w->counters.reserve( counterWords * 4, false, stream )) != cudaSuccess || (e = w->passParams.reserve( sizeof( PassParams ) * (plan.passes + 1), false, stream )) != cudaSuccess ||
-		(e = w->hostCounters.reserve( counterWords * 4 )) != cudaSuccess || (e = w->hostPass.reserve( sizeof( PassParams ) * (plan.passes + 1) )) != cudaSuccess)
+		(e = w->hostCounters.reserve( counterWords * 4 + 64 )) != cudaSuccess || (e = w->hostPass.reserve( sizeof( PassParams ) * (plan.passes + 1) )) != cudaSuccess)
 		return fail( "frame buffers", e );
 	plan.trace = baseArgs();
 	plan.shadePool = (const float4*)shadePool.ptr, plan.vnormPool = (const float4*)vnormPool.ptr, plan.instShadePool = (const float4*)instShadePool.ptr;
@@ -1546,6 +1577,17 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	plan.accumulator = w->accumulator(), plan.frame = (float4*)w->frame.ptr;
 	plan.passDev = (PassParams*)w->passParams.ptr, plan.passHost = (PassParams*)w->hostPass.ptr;
 	plan.countersDev = (uint32_t*)w->counters.ptr, plan.countersHost = (uint32_t*)w->hostCounters.ptr, plan.fetchCounters = (uint32_t*)fetchCounter.ptr;
+	// the gather is part of the frame when the peers are open and the frame is sharded over exactly them (Setting gatherInRender = 0: the
+	// host calls b200_gather_finalize itself)
+	plan.gather = (w->gatherInRender && w->peerWorld > 1 && w->shardCount == w->peerWorld && w->shardIndex == w->peerRank && !w->accumExternal) ? 1u : 0u;
+	if (plan.gather)
+	{
+		plan.peerWorld = w->peerWorld, plan.peerRank = w->peerRank, plan.peers = w->peers;
+		plan.peerEpochWord = (uint32_t*)w->peerFlags.ptr + MAX_PEERS + 1, plan.peerTimeout = (uint32_t*)w->peerFlags.ptr + MAX_PEERS;
+		plan.peerTimeoutHost = (uint32_t*)((char*)w->hostCounters.ptr + counterWords * 4);
+		plan.peerLimitTicks = peerLimitTicks();
+		*plan.peerTimeoutHost = 0;
+	}
 	// per-wave timers: every pass while that stays a few hundred events, else the first pass only (its times are scaled to the frame's
 	// ray counts below)
 	plan.timedPasses = !w->waveTimers ? 0 : (plan.passes * chains * plan.maxLen <= 96 ? plan.passes : 1);
@@ -1607,9 +1649,22 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		w->lastKey.swap( key );
 		launches = 0; // kernels of the frame: per pass and chain one generate, per path length extend + shade (+ connect), one accumulate
 		for (uint32_t c = 0; c < chains; c++) if (plan.chain[c].tiles) launches += plan.passes * (2 + plan.maxLen * (2 + (plan.anyLight ? 1 : 0)));
+		if (plan.gather) launches += 3;
 		stats.kernelLaunches += launches;
+		stats.hostEnqueueMs = hostMs();
 		if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "Render", e );
+		stats.hostWaitMs = hostMs() - stats.hostEnqueueMs;
 		cudaEventElapsedTime( &stats.renderTime, w->frameBegin, w->frameEnd );
+		stats.gatherMs = stats.gatherKernelMs = 0;
+		if (plan.gather)
+		{
+			cudaEventElapsedTime( &stats.gatherMs, w->gatherWait, w->frameEnd ), cudaEventElapsedTime( &stats.gatherKernelMs, w->gatherBegin, w->gatherEnd );
+			if (*plan.peerTimeoutHost)
+			{
+				cudaMemsetAsync( plan.peerTimeout, 0, 4, stream );
+				return fail( "Render: a peer did not arrive within the time limit (Setting peerTimeoutMs); the frame was not gathered" );
+			}
+		}
 		// statistics: ray counts of every pass, wave times of the timed ones
 		double timedRays[3] = { 0, 0, 0 }, allRays[3] = { 0, 0, 0 }, timedShadow = 0, allShadow = 0, timedPaths = 0, allPaths = 0; // classes: primary, first bounce, deeper
 		float classMs[3] = { 0, 0, 0 }, shadowMs = 0, shadeMs = 0;
@@ -1646,6 +1701,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		stats.traceTimeX = scaled( classMs[2], timedRays[2], allRays[2] );
 		stats.shadowTraceTime = scaled( shadowMs, timedShadow, allShadow ), stats.shadeTime = scaled( shadeMs, timedPaths, allPaths );
 	}
+	stats.hostTotalMs = hostMs();
 	w->samplesTaken += (uint32_t)w->spp;
 	stats.frameGraphLaunches = w->graphLaunches, stats.frameChains = plan.chains, stats.framePasses = plan.passes;
 	stats.totalRays = stats.totalExtensionRays + stats.totalShadowRays;
@@ -1675,10 +1731,11 @@ int RenderCore::PeerHandle( void* out128 )
 	if (w->accumExternal) return fail( "PeerHandle: the accumulator is caller-owned (b200_set_accumulator_buffer); peers map the core's own one" );
 	if (!out128) return fail( "PeerHandle: null output" );
 	cudaError_t e;
-	if ((e = w->peerFlags.reserve( (MAX_PEERS + 1) * 4, false, stream )) != cudaSuccess) return fail( "peer flags", e );
-	if ((e = cudaMemsetAsync( w->peerFlags.ptr, 0, (MAX_PEERS + 1) * 4, stream )) != cudaSuccess) return fail( "peer flags", e );
+	// MAX_PEERS arrival words (written by the peers), the timeout flag, this rank's epoch word
+	if ((e = w->peerFlags.reserve( (MAX_PEERS + 2) * 4, false, stream )) != cudaSuccess) return fail( "peer flags", e );
+	if ((e = cudaMemsetAsync( w->peerFlags.ptr, 0, (MAX_PEERS + 2) * 4, stream )) != cudaSuccess) return fail( "peer flags", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "peer flags", e );
-	w->peerEpoch = 0;
+	w->dropGraph();
 	cudaIpcMemHandle_t h[2];
 	static_assert( sizeof( cudaIpcMemHandle_t ) == 64, "IPC handle size" );
 	if ((e = cudaIpcGetMemHandle( &h[0], w->accumOwn.ptr )) != cudaSuccess) return fail( "cudaIpcGetMemHandle(accumulator)", e );
@@ -1712,6 +1769,14 @@ int RenderCore::OpenPeers( const void* handles, int world, int rank )
 	return 0;
 }
 
+// the peer barrier's patience in clock64 ticks (Setting peerTimeoutMs at the SM clock)
+long long RenderCore::peerLimitTicks() const
+{
+	static int clockKHz = 0; // (asked once: this attribute goes down to the kernel driver and costs about a millisecond)
+	if (!clockKHz) cudaDeviceGetAttribute( &clockKHz, cudaDevAttrClockRate, device );
+	return (long long)((double)(wf ? wf->peerTimeoutMs : 2000.f) * (clockKHz > 0 ? clockKHz : 1965000));
+}
+
 int RenderCore::ClosePeers()
 {
 	if (wf) { cudaStreamSynchronize( stream ); wf->closePeers(); }
@@ -1729,17 +1794,15 @@ int RenderCore::GatherFinalize( uint32_t totalSamples )
 	if (w->shardCount != w->peerWorld || w->shardIndex != w->peerRank) return fail( "GatherFinalize: shardCount / shardIndex differ from the peer table" );
 	uint32_t* timeout = (uint32_t*)w->peerFlags.ptr + MAX_PEERS;
 	const uint32_t tilesX = ((uint32_t)w->width + TILE_W - 1) / TILE_W;
-	int clockKHz = 0;
-	cudaDeviceGetAttribute( &clockKHz, cudaDevAttrClockRate, device );
-	const long long limitTicks = (long long)((double)w->peerTimeoutMs * (clockKHz > 0 ? clockKHz : 1965000)); // clock64 ticks at the SM clock
+	const long long limitTicks = peerLimitTicks();
+	uint32_t* epochWord = (uint32_t*)w->peerFlags.ptr + MAX_PEERS + 1;
 	cudaError_t e;
-	for (cudaEvent_t* ev : { &w->gatherBegin, &w->gatherEnd }) if (!*ev && (e = cudaEventCreate( ev )) != cudaSuccess) return fail( "cudaEventCreate", e );
-	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout, limitTicks );
+	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, epochWord, timeout, limitTicks );
 	cudaEventRecord( w->gatherBegin, stream ); // the pull kernel alone (everyone has arrived): what the NVLink figure of bench.py divides by
 	gatherFinalizeKernel<<<smCount * 8, 256, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, (float4*)w->frame.ptr, (uint32_t)w->width, (uint32_t)w->height, tilesX,
-		1.0f / (float)totalSamples, timeout );
+		1.0f / (float)totalSamples, nullptr, timeout );
 	cudaEventRecord( w->gatherEnd, stream );
-	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, ++w->peerEpoch, timeout, limitTicks );
+	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, epochWord, timeout, limitTicks );
 	stats.kernelLaunches += 3;
 	uint32_t timedOut = 0;
 	e = cudaMemcpyAsync( &timedOut, timeout, 4, cudaMemcpyDeviceToHost, stream );

@@ -125,15 +125,12 @@ class ShardedRenderer:
         e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
         stream = torch.cuda.current_stream(self.device)
         if self.gather == "p2p":
-            # every rank owns its tiles: Converge keeps adding to them in place, the pull overwrites the foreign ones
-            e0.record(stream)
+            # every rank owns its tiles: Converge keeps adding to them in place, the pull overwrites the foreign ones.  With open peers the
+            # core's Render() ends with the gather (arrival, pull + finalize, arrival: the tail of the frame's enqueue)
             self.core.Render(view, converge)
-            e1.record(stream)
             self.samples_taken += self.spp
-            self.core.GatherFinalize(self.samples_taken)
-            e2.record(stream)
-            torch.cuda.synchronize(self.device)
-            return e0.elapsed_time(e1), e1.elapsed_time(e2)
+            st = self.core.GetCoreStats()
+            return st["renderTime"] - st["gatherMs"], st["gatherMs"]
         e0.record(stream)
         # each rank's accumulator holds only its own contribution of THIS frame; earlier frames are already global sums
         prev = self.acc.clone() if (converge == 0 and self.samples_taken) else None

@@ -95,7 +95,10 @@ def test_c4_class_refit_and_toplevel_rebuild_vs_oracle(oracles):
     rc = core.RenderCoreB200(0)
     rng = np.random.default_rng(41)
     view = scenes.view_pyramid(width=1920, height=1080, **scenes.C4_CAMERA)
-    Oall, Dall = scenes.primary_rays(view, 1920, 1080)
+    # rays through an irrational sub-pixel position: through the pixel centres 3 of 200 000 rays of frame 0 run exactly along an edge shared
+    # by two triangles of the UV sphere (bit-identical t on both: the tie class of tests/parity.py, 1.5e-5 of the rays against a bar of
+    # 1e-5); SURVEY.md section 7 names the remedy used here
+    Oall, Dall = scenes.primary_rays(view, 1920, 1080, offset=(0.6180339887, 0.7548776662))
     port = None
     for frame in range(3):
         tm = 0.1 * frame
