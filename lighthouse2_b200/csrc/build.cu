@@ -149,6 +149,28 @@ __device__ __forceinline__ void loadPlan( const uint32_t ref, const uint32_t* __
 	}
 }
 
+// the plan of one binary node from its two children's plans (see above).  maxLeaf: most primitives a leaf slot can hold (3 triangles, 1 instance)
+__device__ __forceinline__ void mergePlan( const float cl[7], const float cr[7], const float area, const uint32_t count, const uint32_t maxLeaf, const float primCost,
+	float cost[7], uint32_t& bits )
+{
+	bits = 0;
+	float best8 = 3.0e38f;
+	int k8 = 4;
+	for (int k = 1; k < 8; k++) { const float v = cl[k - 1] + cr[8 - k - 1]; if (v < best8) best8 = v, k8 = k; }
+	const float wideCost = area + best8, leafCost = count <= maxLeaf ? area * (float)count * primCost : 3.0e38f;
+	cost[0] = fminf( leafCost, wideCost );
+	bits |= (uint32_t)k8 << 18;
+	if (leafCost <= wideCost) bits |= 1u << 21;
+	for (int r = 2; r <= 7; r++)
+	{
+		float best = 3.0e38f;
+		int bk = 1;
+		for (int k = 1; k < r; k++) { const float v = cl[k - 1] + cr[r - k - 1]; if (v < best) best = v, bk = k; }
+		if (best < cost[r - 2]) cost[r - 1] = best, bits |= (uint32_t)bk << (3 * (r - 2));
+		else cost[r - 1] = cost[r - 2];
+	}
+}
+
 __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, const float4* __restrict__ primLo, const float4* __restrict__ primHi, const int n,
 	const uint32_t* __restrict__ childL, const uint32_t* __restrict__ childR, const uint32_t* __restrict__ rangeCount, const uint32_t* __restrict__ parentInner,
 	const uint32_t* __restrict__ parentLeaf, float4* nodeLo, float4* nodeHi, float4* planLo, float4* planHi, const float primCost, uint32_t* visits )
@@ -176,23 +198,8 @@ __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, cons
 		loadPlan( c[0], sortedPrim, primLo, primHi, planLo, planHi, primCost, cl );
 		loadPlan( c[1], sortedPrim, primLo, primHi, planLo, planHi, primCost, cr );
 		const float ex = nh.x - nl.x, ey = nh.y - nl.y, ez = nh.z - nl.z, area = ex * ey + ey * ez + ez * ex;
-		uint32_t bits = 0;
-		float best8 = 3.0e38f;
-		int k8 = 4;
-		for (int k = 1; k < 8; k++) { const float v = cl[k - 1] + cr[8 - k - 1]; if (v < best8) best8 = v, k8 = k; }
-		const uint32_t count = rangeCount[node];
-		const float wideCost = area + best8, leafCost = count <= 3 ? area * (float)count * primCost : 3.0e38f;
-		cost[0] = fminf( leafCost, wideCost );
-		bits |= (uint32_t)k8 << 18;
-		if (leafCost <= wideCost) bits |= 1u << 21;
-		for (int r = 2; r <= 7; r++)
-		{
-			float best = 3.0e38f;
-			int bk = 1;
-			for (int k = 1; k < r; k++) { const float v = cl[k - 1] + cr[r - k - 1]; if (v < best) best = v, bk = k; }
-			if (best < cost[r - 2]) cost[r - 1] = best, bits |= (uint32_t)bk << (3 * (r - 2));
-			else cost[r - 1] = cost[r - 2];
-		}
+		uint32_t bits;
+		mergePlan( cl, cr, area, rangeCount[node], 3, primCost, cost, bits );
 		__stcg( planLo + node, make_float4( cost[0], cost[1], cost[2], cost[3] ) );
 		__stcg( planHi + node, make_float4( cost[4], cost[5], cost[6], __uint_as_float( bits ) ) );
 		node = parentInner[node];
@@ -203,8 +210,9 @@ struct CollapseArgs {
 	const uint32_t *sortedPrim, *childL, *childR, *rangeFirst, *rangeCount;
 	const float4 *primLo, *primHi, *nodeLo, *nodeHi, *planHi;
 	uint32_t* wideToBinary;   // [maxNodes] binary inner node that wide node w represents
-	uint4* nodes;             // output, relative index 0 = this mesh's root (pool pointer already offset)
-	float4* tris;             // output triangle records (pool pointer already offset): only .w of the first float4 (the primitive tag) is written
+	uint4* nodes;             // output, relative index 0 = this tree's root (pool pointer already offset)
+	uint32_t* primOut;        // output: original primitive index of leaf-order slot j goes to primOut[j * primOutStride] (triangle records: the .w of the
+	uint32_t primOutStride;   //   first float4, stride 12 words; the top level: a plain array of instance ids)
 	uint32_t* counters;       // [0] wide nodes allocated, [1] leaf-order triangle slots allocated, [2] overflow flag
 	uint32_t nodeBase, triBase, maxNodes;
 };
@@ -218,10 +226,8 @@ __device__ __forceinline__ void refBox( const CollapseArgs& a, const uint32_t re
 }
 
 // 5. one level of the top-down collapse: thread w builds wide node `levelBegin + w` from its binary node
-__global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
+__device__ void collapseNode( const CollapseArgs& a, const uint32_t w )
 {
-	const uint32_t w = levelBegin + blockIdx.x * blockDim.x + threadIdx.x;
-	if (w >= levelEnd) return;
 	const uint32_t root = a.wideToBinary[w];
 	uint32_t ref[8], cnt[8];
 	float lo[8][3], hi[8][3];
@@ -332,7 +338,7 @@ __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin,
 			// the subtree's triangles are a contiguous run of the sorted order
 			const uint32_t first = (ref[i] & LEAF) ? (ref[i] & ~LEAF) : a.rangeFirst[ref[i]];
 			for (uint32_t k = 0; k < cnt[i]; k++)
-				a.tris[(size_t)(primBase + off + k) * 3].w = __uint_as_float( a.sortedPrim[first + k] );
+				a.primOut[(size_t)(primBase + off + k) * a.primOutStride] = a.sortedPrim[first + k];
 			off += cnt[i];
 		}
 		if (s < 4) metaLo |= meta << (8 * s); else metaHi |= meta << (8 * (s - 4));
@@ -341,6 +347,310 @@ __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin,
 	np[0] = make_uint4( 0, 0, 0, imask << 24 );
 	np[1] = make_uint4( a.nodeBase + childBase, a.triBase + primBase, metaLo, metaHi );
 	np[2] = np[3] = np[4] = make_uint4( 0, 0, 0, 0 );
+}
+
+__global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
+{
+	const uint32_t w = levelBegin + blockIdx.x * blockDim.x + threadIdx.x;
+	if (w < levelEnd) collapseNode( a, w );
+}
+
+
+// ---- the top level, built by ONE thread block ------------------------------------------------------------------------------------
+// Replaces the per-frame host rebuild (TopLevelBVH::Rebuild, lib/RenderCore_Bart/bvh.cpp:373, called from Render, rendercore.cpp:199;
+// optixAccelBuild of the IAS, lib/rendercore_optix7/rendercore.cpp:426) for scenes of up to MAX_DEVICE_TLAS_INSTANCES instances: world
+// boxes -> Morton keys -> bitonic sort -> Karras radix tree -> bottom-up boxes + collapse plan -> 8-wide collapse -> frames and
+// quantised planes -> instance records in leaf order.  Everything a pass needs at once sits in shared memory; the passes are
+// separated by block barriers, so the whole build is one launch of a few tens of microseconds and the host neither builds nor waits.
+__device__ __forceinline__ uint32_t spread10( uint32_t x )
+{
+	x &= 0x3ffu;
+	x = (x | x << 16) & 0x030000ffu;
+	x = (x | x << 8) & 0x0300f00fu;
+	x = (x | x << 4) & 0x030c30c3u;
+	x = (x | x << 2) & 0x09249249u;
+	return x;
+}
+
+// frame / planes of a node along one axis: QuantiseFrame / QuantiseChild of bvh_builder.cpp (same as refit.cu::frameOf / quantise)
+__device__ __forceinline__ uint32_t tlasFrame( const float lo, const float hi, float& p )
+{
+	const double ext = (double)hi - (double)lo;
+	int ex = -100;
+	p = lo;
+	if (ext > 0)
+	{
+		int fe;
+		frexp( ext / 254.75, &fe );
+		ex = fe;
+		if (ldexp( 254.75, ex - 1 ) >= ext) ex--;
+		if (ex < -100) ex = -100;
+		p = (float)((double)lo - ldexp( 1.0, ex - 3 ));
+	}
+	return (uint32_t)(ex + 127);
+}
+__device__ __forceinline__ void tlasQuantise( const float p, const uint32_t e, const float lo, const float hi, uint32_t& qlo, uint32_t& qhi )
+{
+	const double inv = ldexp( 1.0, 127 - (int)e );
+	const double l = floor( ((double)lo - (double)p) * inv - 1.0 / 64.0 ), h = ceil( ((double)hi - (double)p) * inv + 1.0 / 64.0 );
+	qlo = (uint32_t)(l < 0 ? 0 : (l > 255 ? 255 : l)), qhi = (uint32_t)(h < 0 ? 0 : (h > 255 ? 255 : h));
+}
+
+struct TlasScratch { float4 *primLo, *primHi, *planLo, *planHi, *wideLo, *wideHi; uint32_t *instOrder; };
+
+__global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInput* __restrict__ in, const uint32_t n, const uint32_t P /* power of two >= n */,
+	uint4* nodes, const uint32_t nodeBase, const uint32_t maxNodes, float4* __restrict__ instRecs, float4* __restrict__ instShade, uint32_t* info, const TlasScratch sc,
+	const float primCost )
+{
+	extern __shared__ __align__( 16 ) unsigned char smem[];
+	// shared-memory carve-up (P elements each unless noted)
+	uint64_t* keys = reinterpret_cast<uint64_t*>( smem );
+	float4* nodeLo = reinterpret_cast<float4*>( keys + P );
+	float4* nodeHi = nodeLo + P;
+	uint32_t* sortedPrim = reinterpret_cast<uint32_t*>( nodeHi + P );
+	uint32_t *childL = sortedPrim + P, *childR = childL + P, *rangeFirst = childR + P, *rangeCount = rangeFirst + P, *parentInner = rangeCount + P;
+	uint32_t *parentLeaf = parentInner + P, *visits = parentLeaf + P, *wideToBinary = visits + P; // wideToBinary: P + 8
+	__shared__ int sBounds[6];
+	__shared__ uint32_t sCounters[4], sLevel[66], sLevels;
+	const uint32_t tid = threadIdx.x, T = blockDim.x;
+	if (tid < 6) sBounds[tid] = tid < 3 ? 0x7fffffff : (int)0x80000000;
+	if (tid < 4) sCounters[tid] = tid == 0 ? 1u : 0u; // wide node 0 = the root is taken
+	__syncthreads();
+	// 1. world boxes: all 8 transformed corners of the mesh box (the CPU reference transforms only two, bvh.cpp:579-587: exact for translations,
+	//    too small under rotation) plus an ulp-scale pad, since the kernels transform the RAY instead of the box; centroid bounds
+	for (uint32_t i = tid; i < n; i += T)
+	{
+		const TlasInstanceInput& I = in[i];
+		const float* c = I.transform;
+		float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+		if (I.empty) { lo[0] = hi[0] = c[3], lo[1] = hi[1] = c[7], lo[2] = hi[2] = c[11]; }
+		else
+		{
+			for (int k = 0; k < 8; k++)
+			{
+				const float x = (k & 1) ? I.hi[0] : I.lo[0], y = (k & 2) ? I.hi[1] : I.lo[1], z = (k & 4) ? I.hi[2] : I.lo[2];
+				const float p[3] = { c[0] * x + c[1] * y + c[2] * z + c[3], c[4] * x + c[5] * y + c[6] * z + c[7], c[8] * x + c[9] * y + c[10] * z + c[11] };
+				for (int a = 0; a < 3; a++) lo[a] = fminf( lo[a], p[a] ), hi[a] = fmaxf( hi[a], p[a] );
+			}
+			for (int a = 0; a < 3; a++)
+			{
+				const float pad = 4e-7f * fmaxf( fabsf( lo[a] ), fabsf( hi[a] ) ) + 1e-30f;
+				lo[a] -= pad, hi[a] += pad;
+			}
+		}
+		sc.primLo[i] = make_float4( lo[0], lo[1], lo[2], 0 ), sc.primHi[i] = make_float4( hi[0], hi[1], hi[2], 0 );
+		for (int a = 0; a < 3; a++)
+		{
+			const int o = orderedInt( 0.5f * (lo[a] + hi[a]) );
+			atomicMin( &sBounds[a], o ), atomicMax( &sBounds[3 + a], o );
+		}
+	}
+	__syncthreads();
+	// 2. keys: 30-bit Morton code of the centroid, the instance index below it (unique keys: no ties for the radix tree); padding sorts last
+	for (uint32_t i = tid; i < P; i += T)
+	{
+		uint64_t key = ~0ull;
+		if (i < n)
+		{
+			const float4 lo = sc.primLo[i], hi = sc.primHi[i];
+			const float c[3] = { 0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z) };
+			uint32_t q[3];
+			for (int a = 0; a < 3; a++)
+			{
+				const float mn = orderedFloat( sBounds[a] ), ext = orderedFloat( sBounds[3 + a] ) - mn;
+				const float t = fminf( fmaxf( ext > 0 ? (c[a] - mn) / ext : 0.f, 0.f ), 1.f );
+				const uint32_t g = (uint32_t)(t * 1023.0f);
+				q[a] = g > 1023u ? 1023u : g;
+			}
+			key = ((uint64_t)(spread10( q[0] ) << 2 | spread10( q[1] ) << 1 | spread10( q[2] )) << 32) | i;
+		}
+		keys[i] = key;
+	}
+	__syncthreads();
+	// 3. bitonic sort of the P keys
+	for (uint32_t k = 2; k <= P; k <<= 1)
+		for (uint32_t j = k >> 1; j > 0; j >>= 1)
+		{
+			for (uint32_t i = tid; i < P; i += T)
+			{
+				const uint32_t partner = i ^ j;
+				if (partner > i)
+				{
+					const uint64_t a = keys[i], b = keys[partner];
+					if (((i & k) == 0) == (a > b)) keys[i] = b, keys[partner] = a;
+				}
+			}
+			__syncthreads();
+		}
+	for (uint32_t i = tid; i < n; i += T) sortedPrim[i] = (uint32_t)keys[i], visits[i] = 0;
+	__syncthreads();
+	if (n == 1)
+	{
+		// a single instance: one node with one leaf slot
+		if (tid == 0)
+		{
+			sc.instOrder[0] = sortedPrim[0];
+			nodes[0] = make_uint4( 0, 0, 0, 0 ), nodes[1] = make_uint4( nodeBase, 0, (1u << 5), 0 ), nodes[2] = nodes[3] = nodes[4] = make_uint4( 0, 0, 0, 0 );
+			sCounters[0] = 1, sLevel[0] = 0, sLevel[1] = 1, sLevels = 1;
+		}
+	}
+	else
+	{
+		// 4. Karras radix tree over the sorted keys (no duplicates)
+		for (uint32_t ii = tid; ii + 1 < n; ii += T)
+		{
+			const int i = (int)ii, nn = (int)n;
+			auto delta = [&]( const int a, const int b ) -> int { return (b < 0 || b >= nn) ? -1 : __clzll( (long long)(keys[a] ^ keys[b]) ); };
+			const int d = delta( i, i + 1 ) - delta( i, i - 1 ) >= 0 ? 1 : -1;
+			const int dmin = delta( i, i - d );
+			int lmax = 2;
+			while (delta( i, i + lmax * d ) > dmin) lmax *= 2;
+			int l = 0;
+			for (int t = lmax / 2; t >= 1; t /= 2) if (delta( i, i + (l + t) * d ) > dmin) l += t;
+			const int j = i + l * d, dnode = delta( i, j );
+			int s = 0;
+			for (int div = 2, t = (l + div - 1) / div; ; div *= 2, t = (l + div - 1) / div)
+			{
+				if (delta( i, i + (s + t) * d ) > dnode) s += t;
+				if (t <= 1) break;
+			}
+			const int gamma = i + s * d + min( d, 0 ), first = min( i, j ), last = max( i, j );
+			const uint32_t L = first == gamma ? (LEAF | (uint32_t)gamma) : (uint32_t)gamma;
+			const uint32_t R = last == gamma + 1 ? (LEAF | (uint32_t)(gamma + 1)) : (uint32_t)(gamma + 1);
+			childL[i] = L, childR[i] = R, rangeFirst[i] = (uint32_t)first, rangeCount[i] = (uint32_t)(last - first + 1);
+			if (L & LEAF) parentLeaf[gamma] = ii; else parentInner[gamma] = ii;
+			if (R & LEAF) parentLeaf[gamma + 1] = ii; else parentInner[gamma + 1] = ii;
+			if (i == 0) parentInner[0] = 0xffffffffu;
+		}
+		__syncthreads();
+		// 5. bottom-up: boxes of the binary nodes and the collapse plan (leaf slots hold ONE instance)
+		for (uint32_t i = tid; i < n; i += T)
+		{
+			uint32_t node = parentLeaf[i];
+			while (node != 0xffffffffu)
+			{
+				__threadfence_block();
+				if (atomicAdd( &visits[node], 1u ) == 0) break; // the sibling subtree is not done yet
+				__threadfence_block();
+				float4 lo[2], hi[2];
+				float cl[7], cr[7], cost[7];
+				const uint32_t c[2] = { childL[node], childR[node] };
+				for (int k = 0; k < 2; k++)
+				{
+					float* cc = k ? cr : cl;
+					if (c[k] & LEAF)
+					{
+						const uint32_t p = sortedPrim[c[k] & ~LEAF];
+						lo[k] = sc.primLo[p], hi[k] = sc.primHi[p];
+						const float x = hi[k].x - lo[k].x, y = hi[k].y - lo[k].y, z = hi[k].z - lo[k].z, v = (x * y + y * z + z * x) * primCost;
+						for (int q = 0; q < 7; q++) cc[q] = v;
+					}
+					else
+					{
+						const volatile float *vl = reinterpret_cast<const volatile float*>( &nodeLo[c[k]] ), *vh = reinterpret_cast<const volatile float*>( &nodeHi[c[k]] );
+						lo[k] = make_float4( vl[0], vl[1], vl[2], 0 ), hi[k] = make_float4( vh[0], vh[1], vh[2], 0 );
+						const float4 a = __ldcg( sc.planLo + c[k] ), b = __ldcg( sc.planHi + c[k] );
+						cc[0] = a.x, cc[1] = a.y, cc[2] = a.z, cc[3] = a.w, cc[4] = b.x, cc[5] = b.y, cc[6] = b.z;
+					}
+				}
+				const float4 nl = make_float4( fminf( lo[0].x, lo[1].x ), fminf( lo[0].y, lo[1].y ), fminf( lo[0].z, lo[1].z ), 0 );
+				const float4 nh = make_float4( fmaxf( hi[0].x, hi[1].x ), fmaxf( hi[0].y, hi[1].y ), fmaxf( hi[0].z, hi[1].z ), 0 );
+				nodeLo[node] = nl, nodeHi[node] = nh;
+				const float ex = nh.x - nl.x, ey = nh.y - nl.y, ez = nh.z - nl.z;
+				uint32_t bits;
+				mergePlan( cl, cr, ex * ey + ey * ez + ez * ex, rangeCount[node], 1, primCost, cost, bits );
+				__stcg( sc.planLo + node, make_float4( cost[0], cost[1], cost[2], cost[3] ) );
+				__stcg( sc.planHi + node, make_float4( cost[4], cost[5], cost[6], __uint_as_float( bits ) ) );
+				__threadfence(); // the plan goes through L2
+				node = parentInner[node];
+			}
+		}
+		__syncthreads();
+		// 6. collapse to 8-wide nodes, level by level
+		CollapseArgs a;
+		a.sortedPrim = sortedPrim, a.childL = childL, a.childR = childR, a.rangeFirst = rangeFirst, a.rangeCount = rangeCount;
+		a.primLo = sc.primLo, a.primHi = sc.primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = sc.planHi;
+		a.wideToBinary = wideToBinary, a.nodes = nodes, a.primOut = sc.instOrder, a.primOutStride = 1, a.counters = sCounters;
+		a.nodeBase = nodeBase, a.triBase = 0, a.maxNodes = maxNodes;
+		if (tid == 0) wideToBinary[0] = 0, sLevel[0] = 0, sLevels = 0;
+		__syncthreads();
+		uint32_t begin = 0, end = 1;
+		while (begin < end)
+		{
+			for (uint32_t w = begin + tid; w < end; w += T) collapseNode( a, w );
+			__syncthreads();
+			if (tid == 0) sLevel[++sLevels] = end;
+			begin = end, end = min( sCounters[0], maxNodes );
+			__syncthreads();
+			if (sLevels >= 64) break;
+		}
+	}
+	__syncthreads();
+	// 7. boxes, frames and quantised planes, deepest level first (a leaf slot's box is its instance's world box)
+	const uint32_t nodeCount = sCounters[0] < maxNodes ? sCounters[0] : maxNodes, levels = sLevels;
+	for (int level = (int)levels - 1; level >= 0; level--)
+	{
+		for (uint32_t w = sLevel[level] + tid; w < sLevel[level + 1]; w += T)
+		{
+			uint4* np = nodes + (size_t)w * 5;
+			const uint4 n0 = np[0], n1 = np[1];
+			const uint32_t imask = n0.w >> 24;
+			float clo[8][3], chi[8][3], nlo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, nhi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+			uint32_t used = 0;
+			for (uint32_t s = 0; s < 8; s++)
+			{
+				const uint32_t meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
+				if (!meta) continue;
+				float4 l, h;
+				if (imask & (1u << s))
+				{
+					const uint32_t child = n1.x + __popc( imask & ((1u << s) - 1u) ) - nodeBase;
+					l = __ldcg( sc.wideLo + child ), h = __ldcg( sc.wideHi + child );
+				}
+				else
+				{
+					const uint32_t inst = __ldcg( sc.instOrder + n1.y + (meta & 31u) );
+					l = sc.primLo[inst], h = sc.primHi[inst];
+				}
+				used |= 1u << s;
+				clo[s][0] = l.x, clo[s][1] = l.y, clo[s][2] = l.z, chi[s][0] = h.x, chi[s][1] = h.y, chi[s][2] = h.z;
+				for (int c = 0; c < 3; c++) nlo[c] = fminf( nlo[c], clo[s][c] ), nhi[c] = fmaxf( nhi[c], chi[s][c] );
+			}
+			uint32_t e[3];
+			float fp[3];
+			for (int c = 0; c < 3; c++) e[c] = tlasFrame( nlo[c], nhi[c], fp[c] );
+			uint8_t q[48];
+			for (int i = 0; i < 48; i++) q[i] = 0;
+			for (uint32_t s = 0; s < 8; s++) if (used & (1u << s))
+				for (int c = 0; c < 3; c++)
+				{
+					uint32_t ql, qh;
+					tlasQuantise( fp[c], e[c], clo[s][c], chi[s][c], ql, qh );
+					q[8 * c + s] = (uint8_t)ql, q[24 + 8 * c + s] = (uint8_t)qh;
+				}
+			np[0] = make_uint4( __float_as_uint( fp[0] ), __float_as_uint( fp[1] ), __float_as_uint( fp[2] ), e[0] | (e[1] << 8) | (e[2] << 16) | (imask << 24) );
+			const uint32_t* qw = reinterpret_cast<const uint32_t*>( q );
+			np[2] = make_uint4( qw[0], qw[1], qw[2], qw[3] ), np[3] = make_uint4( qw[4], qw[5], qw[6], qw[7] ), np[4] = make_uint4( qw[8], qw[9], qw[10], qw[11] );
+			__stcg( sc.wideLo + w, make_float4( nlo[0], nlo[1], nlo[2], 0 ) ), __stcg( sc.wideHi + w, make_float4( nhi[0], nhi[1], nhi[2], 0 ) );
+		}
+		__threadfence();
+		__syncthreads();
+	}
+	// 8. instance records in leaf order (wide_bvh.h InstanceRec) and the shading-time table by instance id (rendercore.cpp)
+	for (uint32_t j = tid; j < n; j += T)
+	{
+		const uint32_t id = __ldcg( sc.instOrder + j );
+		const TlasInstanceInput& I = in[id];
+		float4* r = instRecs + (size_t)j * 6;
+		for (int k = 0; k < 4; k++) r[k] = make_float4( I.inv[4 * k], I.inv[4 * k + 1], I.inv[4 * k + 2], I.inv[4 * k + 3] );
+		r[4] = make_float4( __uint_as_float( I.blasRoot ), __uint_as_float( id ), __uint_as_float( I.meshId ), __uint_as_float( I.flags ) );
+		r[5] = make_float4( 0, 0, 0, 0 );
+		const TlasInstanceInput& S = in[j];
+		float4* sh = instShade + (size_t)j * 4;
+		for (int k = 0; k < 3; k++) sh[k] = make_float4( S.transform[4 * k], S.transform[4 * k + 1], S.transform[4 * k + 2], S.transform[4 * k + 3] );
+		sh[3] = make_float4( __uint_as_float( S.triBase ), __uint_as_float( S.meshId ), 0, 0 );
+	}
+	if (tid == 0) info[0] = nodeCount, info[1] = levels, info[2] = (sCounters[2] || sCounters[0] > maxNodes || levels >= 64) ? 1u : 0u, info[3] = 0;
 }
 
 } // namespace
@@ -393,7 +703,7 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	CollapseArgs a;
 	a.sortedPrim = vals2, a.childL = childL, a.childR = childR, a.rangeFirst = first, a.rangeCount = count;
 	a.primLo = primLo, a.primHi = primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = planHi;
-	a.wideToBinary = w2b, a.nodes = nodes, a.tris = tris, a.counters = counters;
+	a.wideToBinary = w2b, a.nodes = nodes, a.primOut = reinterpret_cast<uint32_t*>( tris ) + 3, a.primOutStride = 12, a.counters = counters;
 	a.nodeBase = nodeBase, a.triBase = triBase, a.maxNodes = maxNodes;
 	levelStart.clear();
 	levelStart.push_back( 0 );
@@ -410,6 +720,35 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	}
 	nodeCount = end;
 	return done( cudaSuccess );
+}
+
+size_t TlasScratchBytes( uint32_t n )
+{
+	return (size_t)(n + 16) * (6 * 16 + 4) + 256;
+}
+
+cudaError_t LaunchTlasBuild( const TlasInstanceInput* dInstances, uint32_t n, uint4* nodes, uint32_t nodeBase, uint32_t maxNodes, float4* instRecs, float4* instShade,
+	uint32_t* info, void* scratch, float primCost, cudaStream_t s )
+{
+	if (n == 0 || n > MAX_DEVICE_TLAS_INSTANCES) return cudaErrorInvalidValue;
+	uint32_t P = 2;
+	while (P < n) P <<= 1;
+	const size_t smem = (size_t)P * (8 + 32 + 4 * 9) + 64; // keys, binary node boxes, nine uint32 arrays (wideToBinary with 8 spare entries)
+	static size_t allowed = 0;
+	cudaError_t e;
+	if (smem > allowed)
+	{
+		if ((e = cudaFuncSetAttribute( tlasBuildKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem )) != cudaSuccess) return e;
+		allowed = smem;
+	}
+	TlasScratch sc;
+	char* p = (char*)scratch;
+	const size_t stride = (size_t)(n + 16) * 16;
+	sc.primLo = (float4*)p, sc.primHi = (float4*)(p + stride), sc.planLo = (float4*)(p + 2 * stride), sc.planHi = (float4*)(p + 3 * stride);
+	sc.wideLo = (float4*)(p + 4 * stride), sc.wideHi = (float4*)(p + 5 * stride), sc.instOrder = (uint32_t*)(p + 6 * stride);
+	const int threads = P < 64 ? 64 : (P > 1024 ? 1024 : (int)P);
+	tlasBuildKernel<<<1, threads, smem, s>>>( dInstances, n, P, nodes, nodeBase, maxNodes, instRecs, instShade, info, sc, primCost );
+	return cudaGetLastError();
 }
 
 } // namespace b200

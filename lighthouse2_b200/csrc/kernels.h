@@ -62,4 +62,22 @@ cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t 
 cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, float4* tris, uint32_t nodeBase, uint32_t triBase, uint32_t maxNodes,
 	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount );
 
+// ---- top-level build on the device (build.cu::tlasBuildKernel) -----------------------------------------------------------------
+// what the host hands over per instance (in instance-id order); the kernel derives world boxes, tree, instance records and the
+// shading-time instance table from it
+struct TlasInstanceInput {
+	float transform[16];      // row-major mat4 (common_types.h:469-632)
+	float inv[16];            // mat4::Inverted of it, computed on the host with the reference's arithmetic (rendercore.cpp::Mat4Inverted)
+	float lo[3]; uint32_t blasRoot;   // object-space bounds of the mesh, absolute node index of its root
+	float hi[3]; uint32_t triBase;    //   ... first triangle of the mesh in the pools
+	uint32_t meshId, flags, empty, pad; // flags: bit0 = inv is affine; empty: the mesh has no triangles (its box is the instance's origin)
+};
+static_assert( sizeof( TlasInstanceInput ) == 176, "TlasInstanceInput: eleven float4" );
+constexpr uint32_t MAX_DEVICE_TLAS_INSTANCES = 2048; // one CTA builds the whole top level in shared memory; larger scenes use the host builder
+// nodes: pool pointer of the top-level root; instRecs: 6 float4 per instance, leaf order; instShade: 4 float4 per instance id; info[0..3] = node count,
+// level count, overflow flag, -.  scratch: at least TlasScratchBytes( n ) bytes.  One launch, asynchronous.
+size_t TlasScratchBytes( uint32_t n );
+cudaError_t LaunchTlasBuild( const TlasInstanceInput* dInstances, uint32_t n, uint4* nodes, uint32_t nodeBase, uint32_t maxNodes, float4* instRecs, float4* instShade,
+	uint32_t* info, void* scratch, float primCost, cudaStream_t s );
+
 } // namespace b200

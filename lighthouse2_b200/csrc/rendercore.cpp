@@ -58,6 +58,27 @@ void Mat4Inverted( const float* c, float* out )
 	}
 }
 
+// smallest singular value of the upper 3x3 of a row-major 4x4: sqrt of the smallest eigenvalue of A^T A (symmetric 3x3, closed form)
+static double SmallestSingularValue3x3( const float* v )
+{
+	double B[3][3];
+	for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) B[r][c] = (double)v[r] * v[c] + (double)v[4 + r] * v[4 + c] + (double)v[8 + r] * v[8 + c];
+	const double q = (B[0][0] + B[1][1] + B[2][2]) / 3.0;
+	const double p1 = B[0][1] * B[0][1] + B[0][2] * B[0][2] + B[1][2] * B[1][2];
+	const double p2 = (B[0][0] - q) * (B[0][0] - q) + (B[1][1] - q) * (B[1][1] - q) + (B[2][2] - q) * (B[2][2] - q) + 2.0 * p1;
+	double lmin = q;
+	if (p2 > 1e-300)
+	{
+		const double pp = std::sqrt( p2 / 6.0 );
+		double C[3][3];
+		for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) C[r][c] = (B[r][c] - (r == c ? q : 0.0)) / pp;
+		double det = C[0][0] * (C[1][1] * C[2][2] - C[1][2] * C[2][1]) - C[0][1] * (C[1][0] * C[2][2] - C[1][2] * C[2][0]) + C[0][2] * (C[1][0] * C[2][1] - C[1][1] * C[2][0]);
+		det = std::min( 1.0, std::max( -1.0, det * 0.5 ) );
+		lmin = q + 2.0 * pp * std::cos( std::acos( det ) / 3.0 + 2.0943951023931953 ); // the smallest of the three eigenvalues
+	}
+	return std::sqrt( std::max( lmin, 0.0 ) );
+}
+
 // ---- DeviceBuffer -------------------------------------------------------------------------------------
 cudaError_t DeviceBuffer::reserve( size_t need, bool keep, cudaStream_t s )
 {
@@ -118,8 +139,9 @@ RenderCore::~RenderCore()
 	cudaDeviceSynchronize();
 	DestroyWavefront( wf );
 	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &vnormPool, &instShadePool, &vertStage, &nodeLo, &nodeHi,
-		&stepNodes, &stepTris };
+		&stepNodes, &stepTris, &tlasIn, &tlasScratch, &tlasInfo };
 	for (DeviceBuffer* b : all) b->release();
+	tlasStage.release();
 	for (int i = 0; i < WAVE_SLOTS; i++) rayO[i].release(), rayD[i].release(), hitBuf[i].release(), bitBuf[i].release();
 	if (evA) cudaEventDestroy( evA );
 	if (evB) cudaEventDestroy( evB );
@@ -146,6 +168,7 @@ int RenderCore::Setting( const char* name, float value )
 	// B200-specific keys
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
 	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 0.5f; return 0; }
+	if (!strcmp( name, "deviceTlas" )) { deviceTlas = value >= 0.5f; tlasDirty = true; return 0; }
 	if (!strcmp( name, "twoStreams" )) { twoStreams = value >= 0.5f; return 0; }
 	if (!strcmp( name, "zeroCopy" )) { zeroCopy = value >= 0.5f; return 0; }
 	if (!strcmp( name, "pinnedChunks" )) { pinnedChunks = (int)value; return 0; }
@@ -431,6 +454,7 @@ int RenderCore::SetInstance( int instanceIdx, int modelIdx, const float* transfo
 	static const float ident[16] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
 	memcpy( in.transform, transform ? transform : ident, 64 );
 	Mat4Inverted( in.transform, in.inv );
+	in.sigmaMin = SmallestSingularValue3x3( in.inv );
 	tlasDirty = true;
 	return 0;
 }
@@ -441,6 +465,17 @@ int RenderCore::UpdateToplevel()
 {
 	const double t0 = nowMs();
 	const uint32_t N = (uint32_t)instances.size();
+	// Hit distances are kept in the object-space units of the instance that was hit (the ray direction is re-normalised at every
+	// instance, bvh.cpp:607-610, and the reference compares those numbers across instances).  A hit at world distance d inside instance k
+	// has the object-space distance d * |inv_k D| >= d * sigma_min( inv_k ), so a top-level box entered at world distance d can be culled
+	// against the current hit distance t only when d * min_k sigma_min( inv_k ) > t.  For rigid instances the factor is 1.
+	{
+		double smin = 1e300;
+		for (uint32_t i = 0; i < N; i++) smin = std::min( smin, instances[i].sigmaMin );
+		// (a margin for the float arithmetic of the instance entry; a degenerate instance switches top-level culling off)
+		tlasTScale = (N && smin > 1e-12) ? (float)std::min( 1.0 / (smin * (1.0 - 1.0 / 4096.0)), 1e30 ) : (N ? 1e30f : 1.0f);
+	}
+	if (deviceTlas && N >= 1 && N <= MAX_DEVICE_TLAS_INSTANCES) return updateToplevelDevice( N, t0 );
 	std::vector<Aabb> boxes( N );
 	for (uint32_t i = 0; i < N; i++)
 	{
@@ -462,36 +497,6 @@ int RenderCore::UpdateToplevel()
 			const float pad = 4e-7f * fmaxf( fabsf( boxes[i].lo[a] ), fabsf( boxes[i].hi[a] ) ) + 1e-30f;
 			boxes[i].lo[a] -= pad, boxes[i].hi[a] += pad;
 		}
-	}
-	// Hit distances are kept in the object-space units of the instance that was hit (the ray direction is re-normalised at every
-	// instance, bvh.cpp:607-610, and the reference compares those numbers across instances).  A hit at world distance d inside instance k
-	// has the object-space distance d * |inv_k D| >= d * sigma_min( inv_k ), so a top-level box entered at world distance d can be culled
-	// against the current hit distance t only when d * min_k sigma_min( inv_k ) > t.  For rigid instances the factor is 1.
-	{
-		double smin = 1e300;
-		for (uint32_t i = 0; i < N; i++)
-		{
-			// smallest singular value of the upper 3x3 of inv = sqrt of the smallest eigenvalue of A^T A (symmetric 3x3, closed form)
-			const float* v = instances[i].inv;
-			double B[3][3];
-			for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) B[r][c] = (double)v[r] * v[c] + (double)v[4 + r] * v[4 + c] + (double)v[8 + r] * v[8 + c];
-			const double q = (B[0][0] + B[1][1] + B[2][2]) / 3.0;
-			const double p1 = B[0][1] * B[0][1] + B[0][2] * B[0][2] + B[1][2] * B[1][2];
-			const double p2 = (B[0][0] - q) * (B[0][0] - q) + (B[1][1] - q) * (B[1][1] - q) + (B[2][2] - q) * (B[2][2] - q) + 2.0 * p1;
-			double lmin = q;
-			if (p2 > 1e-300)
-			{
-				const double pp = std::sqrt( p2 / 6.0 );
-				double C[3][3];
-				for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) C[r][c] = (B[r][c] - (r == c ? q : 0.0)) / pp;
-				double det = C[0][0] * (C[1][1] * C[2][2] - C[1][2] * C[2][1]) - C[0][1] * (C[1][0] * C[2][2] - C[1][2] * C[2][0]) + C[0][2] * (C[1][0] * C[2][1] - C[1][1] * C[2][0]);
-				det = std::min( 1.0, std::max( -1.0, det * 0.5 ) );
-				lmin = q + 2.0 * pp * std::cos( std::acos( det ) / 3.0 + 2.0943951023931953 ); // the smallest of the three eigenvalues
-			}
-			smin = std::min( smin, std::sqrt( std::max( lmin, 0.0 ) ) );
-		}
-		// (a margin for the float arithmetic of the instance entry; a degenerate instance switches top-level culling off)
-		tlasTScale = (N && smin > 1e-12) ? (float)std::min( 1.0 / (smin * (1.0 - 1.0 / 4096.0)), 1e30 ) : (N ? 1e30f : 1.0f);
 	}
 	WideBvh tlas;
 	BuildWideBvh( boxes.data(), N, 1, 1, tlas );
@@ -532,6 +537,51 @@ int RenderCore::UpdateToplevel()
 	if ((e = instShadePool.reserve( (size_t)(N + 1) * 64, false, stream )) != cudaSuccess) return fail( "instance shading pool", e );
 	if (N && (e = cudaMemcpyAsync( instShadePool.ptr, ish.data(), (size_t)N * 64, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "instance shading upload", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "UpdateToplevel sync", e );
+	tlasDirty = false;
+	stats.tlasTime = (float)(nowMs() - t0);
+	stats.instanceCount = N, stats.tlasNodeCount = tlasNodeCount;
+	return 0;
+}
+
+// The top level built by one thread block on the device (build.cu::tlasBuildKernel): the host hands over the instances' matrices and
+// mesh bounds (176 bytes each, from a pinned staging array) and reads back four words (node count, level count, overflow flag).
+int RenderCore::updateToplevelDevice( uint32_t N, double t0 )
+{
+	cudaError_t e;
+	const uint32_t maxNodes = N + 8;
+	if ((e = tlasStage.reserve( (size_t)N * sizeof( TlasInstanceInput ) + 64 )) != cudaSuccess) return fail( "top-level staging", e );
+	TlasInstanceInput* in = (TlasInstanceInput*)tlasStage.ptr;
+	uint32_t* hostInfo = (uint32_t*)((char*)tlasStage.ptr + (size_t)N * sizeof( TlasInstanceInput ));
+	int blasLevels = 0;
+	for (uint32_t i = 0; i < N; i++)
+	{
+		const InstanceHost& h = instances[i];
+		const MeshRec& m = meshes[h.mesh];
+		TlasInstanceInput& t = in[i];
+		memcpy( t.transform, h.transform, 64 ), memcpy( t.inv, h.inv, 64 );
+		for (int a = 0; a < 3; a++) t.lo[a] = m.bounds.lo[a], t.hi[a] = m.bounds.hi[a];
+		t.blasRoot = m.nodeBase, t.triBase = m.triBase, t.meshId = (uint32_t)h.mesh;
+		t.flags = (h.inv[12] == 0 && h.inv[13] == 0 && h.inv[14] == 0 && h.inv[15] == 1) ? 1u : 0u;
+		t.empty = m.triCount == 0 ? 1u : 0u, t.pad = 0;
+		blasLevels = std::max( blasLevels, (int)m.levelStart.size() - 1 );
+	}
+	tlasRoot = blasNodeEnd;
+	if ((e = nodePool.reserve( (size_t)(tlasRoot + maxNodes + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
+	if ((e = instPool.reserve( (size_t)(N + 1) * 96, false, stream )) != cudaSuccess) return fail( "instance pool", e );
+	if ((e = instShadePool.reserve( (size_t)(N + 1) * 64, false, stream )) != cudaSuccess) return fail( "instance shading pool", e );
+	if ((e = tlasIn.reserve( (size_t)N * sizeof( TlasInstanceInput ), false, stream )) != cudaSuccess || (e = tlasScratch.reserve( TlasScratchBytes( N ), false, stream )) != cudaSuccess ||
+		(e = tlasInfo.reserve( 64, false, stream )) != cudaSuccess) return fail( "top-level buffers", e );
+	if ((e = cudaMemcpyAsync( tlasIn.ptr, in, (size_t)N * sizeof( TlasInstanceInput ), cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "instance upload", e );
+	if ((e = LaunchTlasBuild( (const TlasInstanceInput*)tlasIn.ptr, N, (uint4*)((char*)nodePool.ptr + (size_t)tlasRoot * 80), tlasRoot, maxNodes, (float4*)instPool.ptr,
+		(float4*)instShadePool.ptr, (uint32_t*)tlasInfo.ptr, tlasScratch.ptr, 1.0f, stream )) != cudaSuccess) return fail( "top-level build kernel", e );
+	stats.kernelLaunches++;
+	if ((e = cudaMemcpyAsync( hostInfo, tlasInfo.ptr, 16, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "top-level info", e );
+	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "UpdateToplevel sync", e );
+	if (hostInfo[2]) return fail( "UpdateToplevel: the device top-level build overflowed its node budget" );
+	tlasNodeCount = hostInfo[0];
+	// the kernels' per-lane stack has no bound check: refuse scenes that could overrun it (see wide_bvh.h)
+	if (blasLevels + 2 * (int)hostInfo[1] > TRAVERSAL_STACK_ENTRIES)
+		return fail( "UpdateToplevel: bottom-level + 2 x top-level tree depth exceeds the traversal stack (wide_bvh.h TRAVERSAL_STACK_ENTRIES)" );
 	tlasDirty = false;
 	stats.tlasTime = (float)(nowMs() - t0);
 	stats.instanceCount = N, stats.tlasNodeCount = tlasNodeCount;

@@ -17,6 +17,23 @@ struct DeviceBuffer {
 	void release();
 };
 
+// growable page-locked host array (uploads and downloads that run inside a frame or beside kernels must not be pageable)
+struct PinnedBuffer {
+	void* ptr = nullptr;
+	size_t bytes = 0;
+	cudaError_t reserve( size_t need )
+	{
+		if (need <= bytes) return cudaSuccess;
+		if (ptr) cudaFreeHost( ptr );
+		ptr = nullptr, bytes = 0;
+		const size_t cap = (need * 2 + 4095) & ~(size_t)4095;
+		cudaError_t e = cudaHostAlloc( &ptr, cap, cudaHostAllocDefault );
+		if (e == cudaSuccess) bytes = cap;
+		return e;
+	}
+	void release() { if (ptr) cudaFreeHost( ptr ); ptr = nullptr, bytes = 0; }
+};
+
 struct MeshRec {
 	uint32_t nodeBase = 0, nodeCount = 0, triBase = 0, triCount = 0;
 	std::vector<uint32_t> levelStart; // relative to nodeBase
@@ -24,7 +41,7 @@ struct MeshRec {
 	bool built = false;
 };
 
-struct InstanceHost { int mesh = -1; float transform[16]; float inv[16]; };
+struct InstanceHost { int mesh = -1; float transform[16]; float inv[16]; double sigmaMin = 1; /* smallest singular value of inv's 3x3 */ };
 
 struct WavefrontState; // wavefront.cu
 
@@ -122,6 +139,10 @@ private:
 	std::vector<MeshRec> meshes;
 	std::vector<InstanceHost> instances;
 	bool tlasDirty = true;
+	bool deviceTlas = true;   // Setting deviceTlas: the top level is built on the device (build.cu::tlasBuildKernel) when it fits one thread block
+	DeviceBuffer tlasIn, tlasScratch, tlasInfo;
+	PinnedBuffer tlasStage;   // TlasInstanceInput[N], then 4 info words
+	int updateToplevelDevice( uint32_t N, double t0 );
 	// scratch
 	DeviceBuffer rayO[WAVE_SLOTS], rayD[WAVE_SLOTS], hitBuf[WAVE_SLOTS], bitBuf[WAVE_SLOTS], vertStage, nodeLo, nodeHi, stepNodes, stepTris;
 	bool countSteps = false, allowRefit = true, gpuBuild = false; // gpuBuild: new meshes get an LBVH built on the device (build.cu)

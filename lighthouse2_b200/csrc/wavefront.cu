@@ -962,23 +962,6 @@ constexpr int MAX_CHAINS = 4;
 constexpr int COUNTER_STRIDE = (COUNTER_WORDS + 15) & ~15; // one chain's counters of one pass (64-byte aligned)
 constexpr int FETCH_BASE = 16;                               // fetch-counter words 16 + 4 chain + {0,1: extend, 2,3: connect}, see enqueueFrame
 
-// growable page-locked host array (the frame's uploads and downloads must not be pageable: they run inside the frame, maybe in a graph)
-struct PinnedBuffer {
-	void* ptr = nullptr;
-	size_t bytes = 0;
-	cudaError_t reserve( size_t need )
-	{
-		if (need <= bytes) return cudaSuccess;
-		if (ptr) cudaFreeHost( ptr );
-		ptr = nullptr, bytes = 0;
-		const size_t cap = (need * 2 + 4095) & ~(size_t)4095;
-		cudaError_t e = cudaHostAlloc( &ptr, cap, cudaHostAllocDefault );
-		if (e == cudaSuccess) bytes = cap;
-		return e;
-	}
-	void release() { if (ptr) cudaFreeHost( ptr ); ptr = nullptr, bytes = 0; }
-};
-
 // One chain of waves (see ChainArgs): buffers for its share of a pass, two streams, the events that order them
 struct Chain {
 	DeviceBuffer rayO[2], rayD[2], state[2], info[2], hits, conO[2], conD[2], conE[2], slotS, slotC;

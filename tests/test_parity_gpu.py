@@ -136,6 +136,30 @@ def test_c4_class_refit_and_toplevel_rebuild_vs_oracle(oracles):
     rc.Shutdown()
 
 
+@pytest.mark.parametrize("n_inst", [1, 2, 3, 9, 27, 500, 2048])
+def test_device_toplevel_equals_host_toplevel(n_inst):
+    """The top level built by one thread block on the device (build.cu::tlasBuildKernel: Morton keys, bitonic sort, radix tree, SAH
+    collapse, quantised planes, instance records) gives the hits of the host-built one, bit for bit (any conservative hierarchy does:
+    the closest hit does not depend on the tree), for rotated and scaled instances, from 1 instance to the largest count one block takes."""
+    sph = scenes.uv_sphere(12, 7, 1.0)
+    grid = scenes.grid_mesh(4, 4)
+    M = scenes.lattice_transforms(n_inst, spacing=3.0, rotate=True, seed=8, scale=(0.6, 1.5))
+    case = dict(name="tlas", meshes=[sph, grid], instances=[(i % 2, M[i]) for i in range(n_inst)])
+    O, D = scenes.random_rays(100_000, 2.0 + 1.5 * round(n_inst ** (1 / 3)), seed=12)
+    out = []
+    for device in (0, 1):
+        rc = core.RenderCoreB200(0)
+        rc.Setting("deviceTlas", device)
+        cases.load_core(rc, case)
+        out.append(rc.TraceClosest(*core.pack_rays(O, D)))
+        st = rc.GetCoreStats()
+        assert st["instanceCount"] == n_inst and st["tlasNodeCount"] >= 1
+        print("instances %d, deviceTlas %d: %d top-level nodes, %.3f ms" % (n_inst, device, st["tlasNodeCount"], st["tlasTime"]))
+        rc.Shutdown()
+    assert (core.unpack_hits(out[0])["prim"] >= 0).mean() > 0.02
+    assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
+
+
 def test_bigger_soup_vs_oracle(oracles):
     case = cases.case_soup(n_tris=200_000, n_rays=300_000, seed=21)
     rep, _ = _run_case(case, oracles, golden=False)
