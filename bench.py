@@ -65,6 +65,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-waves", action="store_true")
+    ap.add_argument("--no-refit", action="store_true")
     ap.add_argument("--no-check", action="store_true", help="skip the bit-identity check of the gathered frame")
     ap.add_argument("--gather", default="auto", choices=["auto", "p2p", "nccl"])
     ap.add_argument("--setting", action="append", default=[], help="name=value, applied to the core before the scene is built")
@@ -579,6 +580,23 @@ def run_b200(args):
                                 "per_class_mrays_s": {k: v["mrays_s_per_gpu"] for k, v in waves_out["rays"].items()},
                                 "note": "stream roofline of a latency-bound traversal kernel (dependent chain of a pass at 6 warps per scheduler); see DESIGN.md",
                                 "ncu": measured_traffic("extend_ncu")}
+        if not args.no_refit:
+            # the north_star's refit kernel on the same mesh: new positions already on the device, one launch that climbs the tree
+            # (refit.cu::refitWalkKernel); bytes by SURVEY.md 8(d)'s formula: 48 B per triangle (3 x float4 vertex read) + one read and one write per node
+            v4 = np.ones((verts.shape[0] * 3, 4), np.float32)
+            v4[:, :3] = verts.reshape(-1, 3)
+            dv = torch.from_numpy(v4).to(dev)
+            ms = []
+            for _ in range(12):
+                rc.RefitDevice(0, dv.data_ptr(), v4.shape[0])
+                ms.append(rc.GetCoreStats()["refitTime"])
+            ms = float(np.mean(ms[2:]))
+            nodes = st["wideNodeCount"]
+            b = 48 * verts.shape[0] + 2 * 80 * nodes
+            line["refit"] = {"workload": "GPU refit of the C2 mesh (%d triangles, %d wide nodes), vertices resident on the device" % (verts.shape[0], nodes), "ms": ms,
+                             "launches": 1, "bytes_survey_formula": b, "gbs": b / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": b / (ms * 1e-3) / 1e9 / peak,
+                             "bytes_with_writes": 144 * verts.shape[0] + 224 * nodes,
+                             "note": "survey formula = 48 T + 2 x 80 x nodes; with the record / shading-normal writes and the per-node float boxes the kernel moves 144 T + 224 nodes"}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_pass(args, verts, args.cpu_sample, steps=2, warmup=1)
             line["cpu_baseline"] = {"value": r["value"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],

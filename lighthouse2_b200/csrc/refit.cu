@@ -10,11 +10,18 @@
 //   float box from scratch; an 8-lane shuffle reduction gives the node box; each lane re-quantises its own child against the
 //   new frame (double arithmetic, same formulas as QuantiseFrame/QuantiseChild in bvh_builder.cpp).
 //   Bytes: per triangle 16 (record .w) + 48 (vertices) read, 48 + 16 written; per node 80 read + 80 written + 32 scratch.
+//   refitWalkKernel does the whole tree in ONE launch: an 8-lane group starts at every node without inner children and climbs -- the
+//   group that delivers the last child box of a node (one atomic counter per node) goes on with that node.  No launch per level (a
+//   1 M-triangle tree has 16 levels of ~6 us launch latency each; C4's 100 K-triangle mesh was nothing but launch latency) and no
+//   grid-wide barrier: the critical path is the depth of the tree times one node step.
 #include "kernels.h"
 
 namespace b200 {
 
 namespace {
+
+// 2^k as a double, k within the normal range (what ldexp( 1.0, k ) returns, without the library call)
+__device__ __forceinline__ double pow2( const int k ) { return __hiloint2double( (k + 1023) << 20, 0 ); }
 
 // frame of a node along one axis: exponent byte and origin (restates QuantiseFrame of bvh_builder.cpp: s/8 of headroom on both sides, so
 // that every child plane keeps its guard band)
@@ -25,12 +32,12 @@ __device__ __forceinline__ uint32_t frameOf( float lo, float hi, float& p )
 	p = lo;
 	if (ext > 0)
 	{
-		int fe;
-		frexp( ext / 254.75, &fe );
+		// frexp( ext / 254.75 ): the exponent field of the double (no denormals here: ext comes from floats), + 1 for the [0.5, 1) mantissa
+		const int fe = ((__double2hiint( ext / 254.75 ) >> 20) & 0x7ff) - 1022;
 		ex = fe;
-		if (ldexp( 254.75, ex - 1 ) >= ext) ex--;
+		if (pow2( ex - 1 ) * 254.75 >= ext) ex--;
 		if (ex < -100) ex = -100;
-		p = (float)((double)lo - ldexp( 1.0, ex - 3 ));
+		p = (float)((double)lo - pow2( ex - 3 ));
 	}
 	return (uint32_t)(ex + 127);
 }
@@ -38,14 +45,15 @@ __device__ __forceinline__ uint32_t frameOf( float lo, float hi, float& p )
 __device__ __forceinline__ void quantise( float p, uint32_t e, float lo, float hi, uint32_t& qlo, uint32_t& qhi )
 {
 	const double guard = 1.0 / 64.0;
-	const double inv = ldexp( 1.0, 127 - (int)e );
+	const double inv = pow2( 127 - (int)e );
 	double l = floor( ((double)lo - (double)p) * inv - guard ), h = ceil( ((double)hi - (double)p) * inv + guard );
 	qlo = (uint32_t)(l < 0 ? 0 : (l > 255 ? 255 : l));
 	qhi = (uint32_t)(h < 0 ? 0 : (h > 255 ? 255 : h));
 }
 
 // one child slot of one node; all 8 lanes of a node's group call this together (valid or not), groups are 8-aligned in the warp
-__device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t node, const uint32_t s, const bool valid, const uint32_t levelBegin )
+template <bool COHERENT /* child boxes come from groups of the same launch: read them from L2 */>
+__device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t node, const uint32_t s, const bool valid, const uint32_t levelBegin, const uint32_t mask = 0xffffffffu )
 {
 	const uint32_t n = valid ? node : levelBegin;
 	uint4* np = a.nodes + (size_t)(a.nodeBase + n) * 5;
@@ -59,7 +67,7 @@ __device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t no
 		{
 			// absolute child index -> index relative to this mesh's scratch
 			const uint32_t child = n1.x + __popc( imask & ((1u << s) - 1u) ) - a.nodeBase;
-			const float4 cl = a.nodeLo[child], ch = a.nodeHi[child];
+			const float4 cl = COHERENT ? __ldcg( a.nodeLo + child ) : a.nodeLo[child], ch = COHERENT ? __ldcg( a.nodeHi + child ) : a.nodeHi[child];
 			lo[0] = cl.x, lo[1] = cl.y, lo[2] = cl.z, hi[0] = ch.x, hi[1] = ch.y, hi[2] = ch.z;
 		}
 		else
@@ -95,7 +103,7 @@ __device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t no
 	for (int c = 0; c < 3; c++)
 	{
 		float l = lo[c], h = hi[c];
-		for (int d = 1; d < 8; d <<= 1) l = fminf( l, __shfl_xor_sync( 0xffffffffu, l, d ) ), h = fmaxf( h, __shfl_xor_sync( 0xffffffffu, h, d ) );
+		for (int d = 1; d < 8; d <<= 1) l = fminf( l, __shfl_xor_sync( mask, l, d ) ), h = fmaxf( h, __shfl_xor_sync( mask, h, d ) );
 		nlo[c] = l, nhi[c] = h;
 	}
 	if (!valid) return;
@@ -118,7 +126,7 @@ __global__ void refitLevelKernel( const RefitArgs a, const uint32_t levelBegin, 
 {
 	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t node = levelBegin + (gid >> 3);
-	refitSlot( a, node, gid & 7, node < levelEnd, levelBegin ); // whole 8-lane groups are valid or not, so the shuffles stay converged per group
+	refitSlot<false>( a, node, gid & 7, node < levelEnd, levelBegin ); // whole 8-lane groups are valid or not, so the shuffles stay converged per group
 }
 
 // the small top levels in ONE launch: a single CTA walks them bottom-up with a block barrier between levels
@@ -131,14 +139,70 @@ __global__ void __launch_bounds__( 1024 ) refitTopKernel( const RefitArgs a, con
 		for (uint32_t i = threadIdx.x; i < ((slots + 1023u) & ~1023u); i += 1024)
 		{
 			const uint32_t node = begin + (i >> 3);
-			refitSlot( a, node, i & 7, node < end, begin );
+			refitSlot<false>( a, node, i & 7, node < end, begin );
 		}
 		__threadfence_block();
 		__syncthreads();
 	}
 }
 
+// parentInfo[n] = parent of node n (relative to the mesh's root; NO_PARENT for the root) | number of inner children of that parent << 28
+constexpr uint32_t NO_PARENT = 0x0fffffffu;
+__global__ void refitParentsKernel( const uint4* __restrict__ nodes, const uint32_t nodeBase, const uint32_t nodeCount, uint32_t* __restrict__ parentInfo, uint32_t* __restrict__ arrived )
+{
+	const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+	if (n >= nodeCount) return;
+	if (n == 0) parentInfo[0] = NO_PARENT;
+	arrived[n] = 0;
+	const uint4* np = nodes + (size_t)(nodeBase + n) * 5;
+	const uint32_t imask = np[0].w >> 24, inner = __popc( imask ), first = np[1].x - nodeBase;
+	for (uint32_t k = 0; k < inner; k++) parentInfo[first + k] = n | (inner << 28);
+}
+
+// the whole tree in one launch: see the file comment.  Eight lanes per node; the four groups of a warp climb independently (group masks).
+__global__ void __launch_bounds__( 256 ) refitWalkKernel( const RefitArgs a, const uint32_t nodeCount, const uint32_t* __restrict__ parentInfo, uint32_t* arrived )
+{
+	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, s = lane & 7;
+	const uint32_t mask = 0xffu << (lane & 24);
+	uint32_t node = gid >> 3;
+	if (node >= nodeCount) return; // (whole groups)
+	if (a.nodes[(size_t)(a.nodeBase + node) * 5].w >> 24) return; // has inner children: the group that brings the last of them continues here
+	while (true)
+	{
+		refitSlot<true>( a, node, s, true, 0, mask );
+		const uint32_t info = __ldg( parentInfo + node ), parent = info & NO_PARENT;
+		if (parent == NO_PARENT) return;
+		// the node's box and planes must be visible before the arrival is: every lane fences its own stores, then one lane counts
+		__threadfence();
+		__syncwarp( mask );
+		uint32_t last = 0;
+		if (s == 0)
+		{
+			last = atomicAdd( arrived + parent, 1u ) + 1 == (info >> 28) ? 1u : 0u;
+			if (last) arrived[parent] = 0; // ready for the next refit (nobody else touches this counter any more)
+		}
+		last = __shfl_sync( mask, last, lane & 24 );
+		if (!last) return;
+		__threadfence();
+		node = parent;
+	}
+}
+
 } // namespace
+
+cudaError_t LaunchRefitParents( const uint4* nodes, uint32_t nodeBase, uint32_t nodeCount, uint32_t* parentInfo, uint32_t* arrived, cudaStream_t s )
+{
+	if (!nodeCount) return cudaSuccess;
+	refitParentsKernel<<<(nodeCount + 255) / 256, 256, 0, s>>>( nodes, nodeBase, nodeCount, parentInfo, arrived );
+	return cudaGetLastError();
+}
+
+cudaError_t LaunchRefitWalk( const RefitArgs& a, uint32_t nodeCount, const uint32_t* parentInfo, uint32_t* arrived, cudaStream_t s )
+{
+	if (!nodeCount) return cudaSuccess;
+	refitWalkKernel<<<(nodeCount * 8 + 255) / 256, 256, 0, s>>>( a, nodeCount, parentInfo, arrived );
+	return cudaGetLastError();
+}
 
 // levels [0, nTop) of `levelStart` (root first) in one launch; nTop <= 16
 cudaError_t LaunchRefitTop( const RefitArgs& a, const uint32_t* levelStart, int nTop, cudaStream_t s )

@@ -141,6 +141,7 @@ RenderCore::~RenderCore()
 	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &vnormPool, &instShadePool, &vertStage, &nodeLo, &nodeHi,
 		&stepNodes, &stepTris, &tlasIn, &tlasScratch, &tlasInfo };
 	for (DeviceBuffer* b : all) b->release();
+	for (MeshRec& m : meshes) m.refitParents.release(), m.refitArrived.release();
 	tlasStage.release();
 	for (int i = 0; i < WAVE_SLOTS; i++) rayO[i].release(), rayD[i].release(), hitBuf[i].release(), bitBuf[i].release();
 	if (evA) cudaEventDestroy( evA );
@@ -178,6 +179,7 @@ int RenderCore::Setting( const char* name, float value )
 	if (!strcmp( name, "singleInstanceShortcut" )) { singleInstanceShortcut = value >= 0.5f; return 0; }
 	if (!strcmp( name, "countSteps" )) { countSteps = value >= 0.5f; return 0; }
 	if (!strcmp( name, "refit" )) { allowRefit = value >= 0.5f; return 0; }
+	if (!strcmp( name, "refitWalk" )) { refitWalk = value >= 0.5f; return 0; }
 	if (!strcmp( name, "sahPrimCost" )) { if (!(value > 0)) return fail( "Setting sahPrimCost: > 0" ); g_sahPrimCost = value; return 0; }
 	if (!strcmp( name, "buildThreads" )) { buildThreads = value < 1 ? 1 : (int)value; return 0; }
 	return SettingWavefront( name, value );
@@ -279,6 +281,7 @@ int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T,
 	if ((e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
 		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount )) != cudaSuccess) return fail( "GPU BVH build", e );
 	if ((int)m.levelStart.size() - 1 > MAX_TREE_LEVELS) return fail( "SetGeometry: the device-built tree is deeper than the traversal stack allows (wide_bvh.h MAX_TREE_LEVELS)" );
+	if (prepareRefit( m )) return 1;
 	m.built = true;
 	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
 	meshes.push_back( m );
@@ -311,6 +314,7 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 			return fail( "SetGeometry: rebuild (refit=0) is only supported for the most recently added mesh" );
 		// rebuild of the last mesh: drop it and fall through to a fresh build
 		blasNodeEnd = meshes[meshIdx].nodeBase, triEnd = meshes[meshIdx].triBase;
+		meshes.back().refitParents.release(), meshes.back().refitArrived.release();
 		meshes.pop_back();
 	}
 	const double t0 = nowMs();
@@ -363,6 +367,7 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	if ((e = cudaMemcpyAsync( (char*)nodePool.ptr + (size_t)m.nodeBase * 80, bvh.nodes.data(), (size_t)m.nodeCount * 80, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "node upload", e );
 	if (T && (e = cudaMemcpyAsync( (char*)triPool.ptr + (size_t)m.triBase * 48, tris.data(), (size_t)T * 48, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "triangle upload", e );
 	if (T && (e = cudaMemcpyAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, shade.data(), (size_t)T * 16, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "shading upload", e );
+	if (prepareRefit( m )) return 1;
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "SetGeometry sync", e ); // the staging vectors die here
 	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
 	meshes.push_back( m );
@@ -390,6 +395,18 @@ int RenderCore::Refit( int meshIdx, const float* vertexData, int vertexCount )
 	return RefitDevice( meshIdx, vertStage.ptr, vertexCount, true );
 }
 
+// parent links and arrival counters of a freshly placed tree, for the single-launch refit
+int RenderCore::prepareRefit( MeshRec& m )
+{
+	cudaError_t e;
+	if ((e = m.refitParents.reserve( (size_t)(m.nodeCount + 1) * 4, false, stream )) != cudaSuccess || (e = m.refitArrived.reserve( (size_t)(m.nodeCount + 1) * 4, false, stream )) != cudaSuccess)
+		return fail( "refit links", e );
+	if ((e = LaunchRefitParents( (const uint4*)nodePool.ptr, m.nodeBase, m.nodeCount, (uint32_t*)m.refitParents.ptr, (uint32_t*)m.refitArrived.ptr, stream )) != cudaSuccess)
+		return fail( "refit links", e );
+	stats.kernelLaunches++;
+	return 0;
+}
+
 int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, bool boundsKnown )
 {
 	if (meshIdx < 0 || meshIdx >= (int)meshes.size() || !meshes[meshIdx].built) return fail( "Refit: unknown mesh" );
@@ -403,6 +420,14 @@ int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, b
 	a.nodeLo = (float4*)nodeLo.ptr, a.nodeHi = (float4*)nodeHi.ptr, a.shade = (float4*)shadePool.ptr;
 	a.nodeBase = m.nodeBase, a.triBase = m.triBase, a.triCount = m.triCount;
 	cudaEventRecord( evA, stream );
+	if (refitWalk && m.refitParents.ptr)
+	{
+		// one launch: groups start at the nodes without inner children and climb
+		if ((e = LaunchRefitWalk( a, m.nodeCount, (const uint32_t*)m.refitParents.ptr, (uint32_t*)m.refitArrived.ptr, stream )) != cudaSuccess) return fail( "refit", e );
+		stats.kernelLaunches++;
+	}
+	else
+	{
 	// deepest level first; the tiny top levels (at most 16 nodes each) share one single-CTA launch
 	const int levels = (int)m.levelStart.size() - 1;
 	int nTop = 0;
@@ -416,6 +441,7 @@ int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, b
 	{
 		if ((e = LaunchRefitTop( a, m.levelStart.data(), nTop, stream )) != cudaSuccess) return fail( "refit top levels", e );
 		stats.kernelLaunches++;
+	}
 	}
 	cudaEventRecord( evB, stream );
 	if (!boundsKnown)

@@ -39,6 +39,7 @@ struct MeshRec {
 	std::vector<uint32_t> levelStart; // relative to nodeBase
 	Aabb bounds;                      // object-space bounds of the current vertex positions
 	bool built = false;
+	DeviceBuffer refitParents, refitArrived; // per node: parent | inner children of the parent << 28; arrival counter (refit.cu::refitWalkKernel)
 };
 
 struct InstanceHost { int mesh = -1; float transform[16]; float inv[16]; double sigmaMin = 1; /* smallest singular value of inv's 3x3 */ };
@@ -145,6 +146,8 @@ private:
 	int updateToplevelDevice( uint32_t N, double t0 );
 	// scratch
 	DeviceBuffer rayO[WAVE_SLOTS], rayD[WAVE_SLOTS], hitBuf[WAVE_SLOTS], bitBuf[WAVE_SLOTS], vertStage, nodeLo, nodeHi, stepNodes, stepTris;
+	bool refitWalk = true; // Setting refitWalk: the refit is one launch that climbs the tree (1) or one launch per level (0)
+	int prepareRefit( MeshRec& m );
 	bool countSteps = false, allowRefit = true, gpuBuild = false; // gpuBuild: new meshes get an LBVH built on the device (build.cu)
 	bool zeroCopy = true, twoStreams = true; int pinnedChunks = 1, zeroCopyBelow = 400000; // pinned host ray planes are fetched by the kernel itself (Setting zeroCopy / pinnedChunks)
 	bool singleInstanceShortcut = true; // a one-instance scene skips the top-level node (Setting singleInstanceShortcut)

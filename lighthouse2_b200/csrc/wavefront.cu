@@ -35,6 +35,27 @@ namespace {
 constexpr int TILE_W = 32, TILE_H = 8, TILE_PIXELS = TILE_W * TILE_H;
 constexpr float PI = 3.14159265358979323846f, INVPI = 0.31830988618379067154f, TWOPI = 6.28318530717958647692f;
 
+// Tile numbering.  Tiles are dealt to shards (and, inside a shard, to chains) round robin by tile index.  Numbering the tiles row by
+// row would hand every shard the same tile COLUMNS in every row whenever the number of tile columns is a multiple of the shard count
+// (3840 / 32 = 120 columns, 8 GPUs): vertical stripes, which follow the scene's content -- the slowest of 8 ranks then rendered 12 % longer
+// than the fastest.  So row ty is rotated by ty * skew columns, skew odd and coprime with the shard count: diagonal stripes.
+__host__ __device__ __forceinline__ uint32_t tileIndex( const uint32_t tx, const uint32_t ty, const uint32_t tilesX, const uint32_t skew )
+{
+	return ty * tilesX + (tx + ty * skew) % tilesX;
+}
+__host__ __device__ __forceinline__ void tileCoords( const uint32_t tile, const uint32_t tilesX, const uint32_t skew, uint32_t& tx, uint32_t& ty )
+{
+	ty = tile / tilesX;
+	tx = (tile % tilesX + tilesX - (ty * skew) % tilesX) % tilesX;
+}
+static uint32_t tileSkewFor( uint32_t shards )
+{
+	auto gcd = []( uint32_t a, uint32_t b ) { while (b) { const uint32_t t = a % b; a = b, b = t; } return a; };
+	uint32_t s = 3;
+	while (gcd( s, shards ? shards : 1 ) != 1) s += 2;
+	return s;
+}
+
 constexpr int MAX_PATH_LENGTH = 16; // MAXPATHLENGTH of the optix7 core (core_settings.h:24)
 // Device-resident wave counters (the reference's Counters, core_settings.h:103-117), uint32 words:
 //   [2 len - 1] = extension rays of path length len (written by generate for len = 1, by shade( len - 1 ) otherwise)
@@ -51,7 +72,7 @@ struct FrameParams {
 	float sky[3];                         // constant sky (used when no skydome image is set)
 	float epsilon, clampValue;
 	uint32_t width, height, pixelCount;
-	uint32_t shardIndex, shardCount, tilesX, tilesY;
+	uint32_t shardIndex, shardCount, tilesX, tilesY, tileSkew; // tile numbering: see tileIndex
 	uint32_t chainCount;                  // the shard's tiles are dealt to this many independent chains of waves (local tile t -> chain t % chainCount)
 	uint32_t roulette;                    // Russian roulette on (the reference's behaviour) / off (fixed-depth benchmark passes)
 	uint32_t jitter, materialCount, bounceCap; // bounceCap: 0 = none, 1 = stop after one diffuse bounce (the reference's ENOUGH_BOUNCES), 2 = two
@@ -179,7 +200,9 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 			sample = job / perSample;
 			const uint32_t q = job - sample * perSample, chainTile = q / TILE_PIXELS, inTile = q % TILE_PIXELS;
 			const uint32_t tile = (chainTile * f.chainCount + c.chain) * f.shardCount + f.shardIndex;
-			x = (tile % f.tilesX) * TILE_W + (inTile % TILE_W), y = (tile / f.tilesX) * TILE_H + inTile / TILE_W;
+			uint32_t tx, ty;
+			tileCoords( tile, f.tilesX, f.tileSkew, tx, ty );
+			x = tx * TILE_W + (inTile % TILE_W), y = ty * TILE_H + inTile / TILE_W;
 			valid = x < f.width && y < f.height;
 		}
 		const uint32_t slot = blockAppend<8>( c.counters + extCounter( 1 ), valid, sWarp );
@@ -505,7 +528,7 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 			{
 				// contribution slot of this path = its index when the pass was generated (generateEyeRaysKernel's `job`)
 				const uint32_t pxX = pixelIdx % f.width, pxY = pixelIdx / f.width;
-				const uint32_t tile = (pxY / TILE_H) * f.tilesX + pxX / TILE_W, chainTile = tile / f.shardCount / f.chainCount;
+				const uint32_t tile = tileIndex( pxX / TILE_W, pxY / TILE_H, f.tilesX, f.tileSkew ), chainTile = tile / f.shardCount / f.chainCount;
 				slot = (sampleIdxU - __ldg( &pass->sampleBase )) * (c.chainTiles * TILE_PIXELS) + chainTile * TILE_PIXELS + (pxY % TILE_H) * TILE_W + pxX % TILE_W;
 			}
 			const int prim = (int)__float_as_uint( hit.z );
@@ -866,7 +889,9 @@ __global__ void __launch_bounds__( 256 ) accumulateKernel( const FrameParams f, 
 	{
 		const uint32_t chainTile = q / TILE_PIXELS, inTile = q % TILE_PIXELS;
 		const uint32_t tile = (chainTile * f.chainCount + chain) * f.shardCount + f.shardIndex;
-		const uint32_t x = (tile % f.tilesX) * TILE_W + (inTile % TILE_W), y = (tile / f.tilesX) * TILE_H + inTile / TILE_W;
+		uint32_t tx, ty;
+		tileCoords( tile, f.tilesX, f.tileSkew, tx, ty );
+		const uint32_t x = tx * TILE_W + (inTile % TILE_W), y = ty * TILE_H + inTile / TILE_W;
 		if (x >= f.width || y >= f.height) continue;
 		const uint32_t pixel = x + y * f.width;
 		float4 a = accumulator[pixel];
@@ -933,7 +958,7 @@ __global__ void peerBarrierKernel( const PeerTable peers, const int world, const
 }
 
 __global__ void gatherFinalizeKernel( const PeerTable peers, const int world, const int rank, float4* __restrict__ frame, const uint32_t width,
-	const uint32_t height, const uint32_t tilesX, const float scaleArg, const PassParams* __restrict__ lastPass, const uint32_t* __restrict__ timeout )
+	const uint32_t height, const uint32_t tilesX, const uint32_t tileSkew, const float scaleArg, const PassParams* __restrict__ lastPass, const uint32_t* __restrict__ timeout )
 {
 	if (*timeout) return; // a peer did not arrive: its tiles may be incomplete, nothing is pulled this frame
 	const float scale = lastPass ? __ldg( &lastPass->finalScale ) : scaleArg; // inside a frame: 1 / samples, as the frame's last pass has it
@@ -942,7 +967,7 @@ __global__ void gatherFinalizeKernel( const PeerTable peers, const int world, co
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < pixels; i += gridDim.x * blockDim.x)
 	{
 		const uint32_t x = i % width, y = i / width;
-		const uint32_t owner = ((y / TILE_H) * tilesX + x / TILE_W) % (uint32_t)world; // as generateEyeRaysKernel deals the tiles
+		const uint32_t owner = tileIndex( x / TILE_W, y / TILE_H, tilesX, tileSkew ) % (uint32_t)world; // as generateEyeRaysKernel deals the tiles
 		float4 a;
 		if (owner == (uint32_t)rank) a = own[i];
 		else
@@ -1459,7 +1484,7 @@ static cudaError_t enqueueFrame( WavefrontState& w, const FramePlan& p, cudaStre
 		cudaEventRecordWithFlags( w.gatherWait, origin, recFlags );
 		peerBarrierKernel<<<1, 32, 0, origin>>>( p.peers, p.peerWorld, p.peerRank, p.peerEpochWord, p.peerTimeout, p.peerLimitTicks );
 		cudaEventRecordWithFlags( w.gatherBegin, origin, recFlags );
-		gatherFinalizeKernel<<<p.smCount * 8, 256, 0, origin>>>( p.peers, p.peerWorld, p.peerRank, p.frame, p.f.width, p.f.height, p.f.tilesX, 0.f,
+		gatherFinalizeKernel<<<p.smCount * 8, 256, 0, origin>>>( p.peers, p.peerWorld, p.peerRank, p.frame, p.f.width, p.f.height, p.f.tilesX, p.f.tileSkew, 0.f,
 			p.passDev + (p.passes - 1), p.peerTimeout );
 		cudaEventRecordWithFlags( w.gatherEnd, origin, recFlags );
 		peerBarrierKernel<<<1, 32, 0, origin>>>( p.peers, p.peerWorld, p.peerRank, p.peerEpochWord, p.peerTimeout, p.peerLimitTicks );
@@ -1500,7 +1525,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	f.epsilon = epsilon, f.width = (uint32_t)w->width, f.height = (uint32_t)w->height, f.pixelCount = f.width * f.height;
 	f.tilesX = (f.width + TILE_W - 1) / TILE_W, f.tilesY = (f.height + TILE_H - 1) / TILE_H;
 	const uint32_t nTiles = f.tilesX * f.tilesY;
-	f.shardIndex = (uint32_t)w->shardIndex, f.shardCount = (uint32_t)w->shardCount;
+	f.shardIndex = (uint32_t)w->shardIndex, f.shardCount = (uint32_t)w->shardCount, f.tileSkew = tileSkewFor( f.shardCount );
 	const uint32_t ownTiles = nTiles > f.shardIndex ? (nTiles - f.shardIndex + f.shardCount - 1) / f.shardCount : 0;
 	f.jitter = (uint32_t)w->jitter, f.materialCount = w->materialCount;
 	f.probePixel = (w->probeX >= 0 && w->probeY >= 0 && w->probeX < w->width && w->probeY < w->height) ? w->probeX + w->probeY * w->width : -1;
@@ -1783,7 +1808,7 @@ int RenderCore::GatherFinalize( uint32_t totalSamples )
 	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, epochWord, timeout, limitTicks );
 	cudaEventRecord( w->gatherBegin, stream ); // the pull kernel alone (everyone has arrived): what the NVLink figure of bench.py divides by
 	gatherFinalizeKernel<<<smCount * 8, 256, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, (float4*)w->frame.ptr, (uint32_t)w->width, (uint32_t)w->height, tilesX,
-		1.0f / (float)totalSamples, nullptr, timeout );
+		tileSkewFor( (uint32_t)w->peerWorld ), 1.0f / (float)totalSamples, nullptr, timeout );
 	cudaEventRecord( w->gatherEnd, stream );
 	peerBarrierKernel<<<1, 32, 0, stream>>>( w->peers, w->peerWorld, w->peerRank, epochWord, timeout, limitTicks );
 	stats.kernelLaunches += 3;

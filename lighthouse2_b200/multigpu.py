@@ -20,10 +20,21 @@ def tile_grid(width: int, height: int):
     return (width + TILE_W - 1) // TILE_W, (height + TILE_H - 1) // TILE_H
 
 
+def tile_skew(shard_count: int) -> int:
+    """Row ty of the tile grid is rotated by ty * skew columns before the tiles are numbered (wavefront.cu::tileIndex): the smallest odd
+    number >= 3 that is coprime with the shard count, so that the shards' tiles form diagonal, not vertical, stripes."""
+    import math
+    s = 3
+    while math.gcd(s, max(shard_count, 1)) != 1:
+        s += 2
+    return s
+
+
 def tile_owner_map(width: int, height: int, shard_count: int) -> np.ndarray:
     """int32[h, w]: which shard renders each pixel (tile t -> shard t % shard_count), as wavefront.cu assigns them."""
     tx, ty = tile_grid(width, height)
-    tiles = np.arange(tx * ty, dtype=np.int64).reshape(ty, tx) % shard_count
+    col, row = np.meshgrid(np.arange(tx, dtype=np.int64), np.arange(ty, dtype=np.int64))
+    tiles = (row * tx + (col + row * tile_skew(shard_count)) % tx) % shard_count
     return np.repeat(np.repeat(tiles, TILE_H, axis=0), TILE_W, axis=1)[:height, :width].astype(np.int32)
 
 

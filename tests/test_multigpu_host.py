@@ -25,15 +25,26 @@ def test_tile_partition(size, shards):
     assert counts.sum() == w * h
     if w * h >= 1920 * 1080:
         assert counts.max() / counts.min() < 1.02, "interleaved tiles balance the shards"
-    # restate the kernel's mapping (generateEyeRaysKernel): local tile lt of shard i is global tile lt*shards + i
+    # restate the kernel's mapping (generateEyeRaysKernel + tileCoords of wavefront.cu): local tile lt of shard i is global tile
+    # lt * shards + i, and tile t sits in row t // tx at column (t % tx - row * skew) mod tx
     tx, ty = multigpu.tile_grid(w, h)
+    skew = multigpu.tile_skew(shards)
+    seen = np.zeros((ty, tx), np.int32)
     for i in range(shards):
         own_tiles = (tx * ty - i + shards - 1) // shards if tx * ty > i else 0
         lt = np.arange(own_tiles)
         t = lt * shards + i
         assert (t < tx * ty).all()
-        x0, y0 = (t % tx) * multigpu.TILE_W, (t // tx) * multigpu.TILE_H
+        row = t // tx
+        col = (t % tx - row * skew) % tx
+        seen[row, col] += 1
+        x0, y0 = col * multigpu.TILE_W, row * multigpu.TILE_H
         assert (owner[np.minimum(y0, h - 1), np.minimum(x0, w - 1)] == i).all()
+    assert (seen == 1).all(), "every tile belongs to exactly one shard"
+    if shards > 1 and ty >= 2 * shards and tx >= shards:
+        # no shard owns a whole column of tiles (what the row-by-row numbering did whenever shards divides the column count)
+        tile_owner = owner[::multigpu.TILE_H, ::multigpu.TILE_W]
+        assert all(len(np.unique(tile_owner[:, c])) > 1 for c in range(tile_owner.shape[1]))
 
 
 def _free_port():
