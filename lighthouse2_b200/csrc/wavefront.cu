@@ -130,6 +130,24 @@ __device__ __forceinline__ float BlueNoiseSampler( const uint32_t* __restrict__ 
 	return (0.5f + (float)value) * (1.0f / 256.0f);
 }
 
+// sin and cos of x >= 0 from separately rounded float operations only (this file is compiled with -fmad=false): quadrant reduction with
+// a two-constant pi/2, then degree-9 / degree-8 polynomials on [-pi/4, pi/4]; absolute error about 1e-7.  The reference's cores call the
+// hardware approximation __sincosf (tools_shared.h:250-256, .optix.cu:51-64), whose bits no host code can reproduce: with it the frames of
+// the CPU restatement (tests/wavefront_ref.py) forked from the device's on a last-bit difference of a bounce direction in a fraction of a
+// per cent of the pixels.  tests/wavefront_ref.py::sincos_det restates this function operation by operation, so the two sides agree to the bit.
+__device__ __forceinline__ void SinCosDet( const float x, float& s, float& c )
+{
+	const float kf = rintf( x * 0.636619772f );
+	const int k = (int)kf;
+	float r = x - kf * 1.5707963705062866f;
+	r = r - kf * -4.371139000186243e-8f;
+	const float r2 = r * r;
+	const float sp = r + (r * r2) * (-0.16666667f + r2 * (0.0083333310f + r2 * (-0.00019840874f + r2 * 2.7525562e-6f)));
+	const float cp = 1.0f + r2 * (-0.5f + r2 * (0.041666638f + r2 * (-0.0013888378f + r2 * 2.4760495e-5f)));
+	const float ss = (k & 1) ? cp : sp, cc = (k & 1) ? sp : cp;
+	s = (k & 2) ? -ss : ss, c = ((k + 1) & 2) ? -cc : cc;
+}
+
 __device__ __forceinline__ uint32_t laneMaskLt()
 {
 	uint32_t m;
@@ -227,8 +245,8 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 			const float blade = (float)(int)(l0 * 9);
 			float l2 = (l0 - blade * (1.0f / 9.0f)) * 9.0f;
 			float x1, y1, x2, y2;
-			__sincosf( blade * 3.14159265358979323846f / 4.5f, &x1, &y1 );
-			__sincosf( (blade + 1.0f) * 3.14159265358979323846f / 4.5f, &x2, &y2 );
+			SinCosDet( blade * 3.14159265358979323846f / 4.5f, x1, y1 );
+			SinCosDet( (blade + 1.0f) * 3.14159265358979323846f / 4.5f, x2, y2 );
 			if (l1 + l2 > 1) l1 = 1.0f - l1, l2 = 1.0f - l2;
 			const float xr = x1 * l1 + x2 * l2, yr = y1 * l1 + y2 * l2;
 			ox += P.aperture * (P.right[0] * xr + P.up[0] * yr), oy += P.aperture * (P.right[1] * xr + P.up[1] * yr), oz += P.aperture * (P.right[2] * xr + P.up[2] * yr);
@@ -802,7 +820,7 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 								const float r5 = (r3 - pReflect) / (1 - pReflect), r6 = (r4 - transmission) / (1 - transmission);
 								const float term1 = TWOPI * r5, term2 = sqrtf( 1 - r6 ); // DiffuseReflectionCosWeighted, tools_shared.h:250-256
 								float sn, cs;
-								__sincosf( term1, &sn, &cs );
+								SinCosDet( term1, sn, cs );
 								Tangent2World( cs * term2, sn * term2, sqrtf( r6 ), sF.x, sF.y, sF.z, R.x, R.y, R.z );
 								R = normalize( R );
 								newPdf = fmaxf( 0.0f, dot( R, sF ) ) * INVPI;

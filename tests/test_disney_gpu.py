@@ -177,11 +177,10 @@ def test_disney_frame_matches_reference_bsdf_restatement(ref, roulette):
     print("disney image: mean", mean, "rmse", rmse, "pixels off by >2%:", int(big.sum()), "of", w * h,
           "rays gpu", st["totalExtensionRays"], st["totalShadowRays"], "ref", sum(stats["ext"]), sum(stats["shadow"]))
     assert np.isfinite(acc).all() and mean > 0.05
-    assert rmse <= 1e-2 * mean, (rmse, mean)
-    assert big.mean() < 2e-2
+    assert rmse <= 1e-4 * mean, (rmse, mean)  # the stated image bar; measured 8e-6 .. 2e-5 (the BSDF checker runs libm sin / cos)
+    assert big.sum() == 0
     assert np.allclose(acc[..., 3], img[..., 3], rtol=1e-5)
-    assert abs(st["totalExtensionRays"] - sum(stats["ext"])) <= 0.005 * sum(stats["ext"])
-    assert abs(st["totalShadowRays"] - sum(stats["shadow"])) <= 0.005 * sum(stats["shadow"])
+    assert st["totalExtensionRays"] == sum(stats["ext"]) and st["totalShadowRays"] == sum(stats["shadow"])
 
 
 # ---- the other maps of GetShadingData: detail colour, normal map + detail normal map, roughness map (material_shared.h:120-169) ---
@@ -254,6 +253,6 @@ def test_detail_normal_and_roughness_maps(ref, bsdf):
     big = np.abs(acc[..., :3] - img[..., :3]).max(axis=2) > 0.02 * mean
     print("mapped image (bsdf %d): mean" % bsdf, mean, "rmse", rmse, "pixels off by >2%:", int(big.sum()), "rays", st["totalExtensionRays"], sum(stats["ext"]),
           "vs unmapped", float(np.abs(flat[..., :3] - acc[..., :3]).mean()))
-    assert np.isfinite(acc).all() and rmse <= 1e-2 * mean and big.mean() < 2e-2
-    assert abs(st["totalExtensionRays"] - sum(stats["ext"])) <= 0.005 * sum(stats["ext"])
+    assert np.isfinite(acc).all() and rmse <= 1e-4 * mean and big.sum() == 0  # measured 2e-6 (Lambert), 4e-5 (Disney)
+    assert st["totalExtensionRays"] == sum(stats["ext"])
     assert np.abs(flat[..., :3] - acc[..., :3]).mean() > 0.01 * mean

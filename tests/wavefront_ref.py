@@ -32,6 +32,22 @@ def random_float(seed):
     return seed, (seed.astype(f32) * f32(2.3283064365387e-10)).astype(f32)
 
 
+def sincos_det(x):
+    """wavefront.cu::SinCosDet operation by operation (float32, every operation rounded on its own): the device frames and this
+    restatement then agree on every bounce direction to the bit, where the hardware __sincosf of the reference cannot be restated."""
+    x = np.asarray(x, f32)
+    kf = np.rint(x * f32(0.636619772)).astype(f32)
+    k = kf.astype(np.int64)
+    r = (x - kf * f32(1.5707963705062866)).astype(f32)
+    r = (r - kf * f32(-4.371139000186243e-8)).astype(f32)
+    r2 = (r * r).astype(f32)
+    sp = (r + (r * r2) * (f32(-0.16666667) + r2 * (f32(0.0083333310) + r2 * (f32(-0.00019840874) + r2 * f32(2.7525562e-6))))).astype(f32)
+    cp = (f32(1.0) + r2 * (f32(-0.5) + r2 * (f32(0.041666638) + r2 * (f32(-0.0013888378) + r2 * f32(2.4760495e-5))))).astype(f32)
+    odd = (k & 1) != 0
+    ss, cc = np.where(odd, cp, sp), np.where(odd, sp, cp)
+    return np.where((k & 2) != 0, -ss, ss).astype(f32), np.where(((k + 1) & 2) != 0, -cc, cc).astype(f32)
+
+
 def safe_origin(I, R, N, eps):
     parallel = f32(1) - np.abs(np.einsum("ij,ij->i", N, R)).astype(f32)
     v = (parallel * parallel)[:, None]
@@ -334,7 +350,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             blade = (l0 * f32(9)).astype(np.int32).astype(f32)
             l2 = ((l0 - blade * f32(1.0 / 9.0)) * f32(9)).astype(f32)
             a1, a2 = blade * f32(np.pi) / f32(4.5), (blade + f32(1)) * f32(np.pi) / f32(4.5)
-            x1, y1, x2, y2 = np.sin(a1), np.cos(a1), np.sin(a2), np.cos(a2)
+            (x1, y1), (x2, y2) = sincos_det(a1), sincos_det(a2)
             swap = (l1 + l2) > 1
             l1, l2 = np.where(swap, f32(1) - l1, l1).astype(f32), np.where(swap, f32(1) - l2, l2).astype(f32)
             xr, yr = (x1 * l1 + x2 * l2).astype(f32), (y1 * l1 + y2 * l2).astype(f32)
@@ -639,7 +655,8 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                 r5 = ((r3 - p_reflect) / (f32(1) - p_reflect)).astype(f32)
                 r6 = ((r4 - transmission) / (f32(1) - transmission)).astype(f32)
                 term1, term2 = TWOPI * r5, np.sqrt(f32(1) - r6)
-                V = np.stack([np.cos(term1) * term2, np.sin(term1) * term2, np.sqrt(r6)], axis=1).astype(f32)
+                sn_, cs_ = sincos_det(term1)
+                V = np.stack([cs_ * term2, sn_ * term2, np.sqrt(r6)], axis=1).astype(f32)
                 R_diff = normalize(tangent2world(V, fN))
                 diffuse = ~trans & ~spec_o
                 R = np.where((reflect_t | spec_o)[:, None], R_refl, np.where(refract_t[:, None], R_refr, R_diff)).astype(f32)
