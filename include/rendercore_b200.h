@@ -75,6 +75,20 @@ B200_API int b200_trace_any( b200_core* c, const float* O4, const float* D4, int
 B200_API int b200_trace_closest_async( b200_core* c, const float* O4, const float* D4, int n, float* hits );
 B200_API int b200_trace_any_async( b200_core* c, const float* O4, const float* D4, int n, uint32_t* occludedBits );
 B200_API int b200_wait( b200_core* c );
+/* The extend wave over host buffers WITHOUT ANY ALLOCATION.  This entry point has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and results as b200_trace_closest (bit for bit), but the wave kernel's scratch -- its fetch counter
+ * and the device staging of the two ray planes and the hit records -- is a file-scope static device array of fixed size (traverse.cu)
+ * instead of the core's growable buffers, and nothing on the path calls cudaMalloc, cudaFree or an allocating routine.
+ *   limit : n <= B200_NOALLOC_MAX_RAYS; a larger n is rejected with an error (split the wave or use b200_trace_closest).  The array
+ *           (256 B + 48 B per ray = 3 MB) is held by every GPU that loads the library until the process exits.
+ *   state : the scene must be built and its top level current (b200_update_toplevel) -- a stale top level is an error here, because
+ *           rebuilding it may grow pools.
+ *   races : all calls share the one array, which keeps the last call's contents (the call clears what must start at zero); two calls that
+ *           overlap on the GPU -- other streams, other cores on the same device, other threads -- race.  The call synchronises its stream
+ *           before it returns. */
+#define B200_NOALLOC_MAX_RAYS 65536
+B200_API int b200_trace_closest_noalloc( b200_core* c, const float* O4, const float* D4, int n, float* hits );
 /* device buffers (cudaMalloc'ed by anyone in this process); asynchronous on the core's stream.
  * occludedBits must hold (n+31)/32 words; it is cleared by the call. */
 B200_API int b200_trace_closest_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dHits );

@@ -28,6 +28,7 @@ C_ABI_SYMBOLS = [
     "b200_disney_probe", "b200_set_blue_noise",
     "b200_set_accumulator_buffer", "b200_finalize", "b200_trace_connect_device",
     "b200_trace_closest_async", "b200_trace_any_async", "b200_wait",
+    "b200_trace_closest_noalloc",
     "b200_peer_handle", "b200_open_peers", "b200_close_peers", "b200_gather_finalize",
 ]
 
@@ -97,6 +98,7 @@ def load_library() -> C.CDLL:
         "b200_set_accumulator_buffer": ([vp, vp], ip), "b200_finalize": ([vp, C.c_uint32], ip),
         "b200_trace_connect_device": ([vp, vp, vp, ip, vp, vp], ip),
         "b200_trace_closest_async": ([vp, vp, vp, ip, vp], ip), "b200_trace_any_async": ([vp, vp, vp, ip, vp], ip), "b200_wait": ([vp], ip),
+        "b200_trace_closest_noalloc": ([vp, vp, vp, ip, vp], ip),
         "b200_peer_handle": ([vp, vp], ip), "b200_open_peers": ([vp, vp, ip, ip], ip), "b200_close_peers": ([vp], ip),
         "b200_gather_finalize": ([vp, C.c_uint32], ip),
     }

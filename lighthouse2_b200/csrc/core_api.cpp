@@ -47,6 +47,7 @@ int b200_trace_any( b200_core* c, const float* O4, const float* D4, int n, uint3
 int b200_trace_closest_async( b200_core* c, const float* O4, const float* D4, int n, float* hits ) { FORWARD( c, TraceClosestAsync( O4, D4, n, hits ) ) }
 int b200_trace_any_async( b200_core* c, const float* O4, const float* D4, int n, uint32_t* bits ) { FORWARD( c, TraceAnyAsync( O4, D4, n, bits ) ) }
 int b200_wait( b200_core* c ) { FORWARD( c, WaitWaves() ) }
+int b200_trace_closest_noalloc( b200_core* c, const float* O4, const float* D4, int n, float* hits ) { FORWARD( c, TraceClosestNoAlloc( O4, D4, n, hits ) ) }
 int b200_trace_closest_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dHits ) { FORWARD( c, TraceClosestDevice( dO4, dD4, n, dHits ) ) }
 int b200_trace_any_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dBits ) { FORWARD( c, TraceAnyDevice( dO4, dD4, n, dBits ) ) }
 int b200_read_step_counters( b200_core* c, int n, uint32_t* nodes, uint32_t* tris ) { FORWARD( c, ReadStepCounters( n, nodes, tris ) ) }

@@ -45,6 +45,12 @@ enum IsectMode { ISECT_REFERENCE = 0, ISECT_WATERTIGHT = 1 };
 cudaError_t LaunchExtend( const TraceArgs& a, IsectMode mode, bool countSteps, int smCount, cudaStream_t s );
 cudaError_t LaunchShadow( const TraceArgs& a, IsectMode mode, int smCount, cudaStream_t s );
 
+// The extend wave over host buffers with the kernel's scratch (fetch counter, device staging of rays and hits) in a file-scope device
+// array of fixed size: no cudaMalloc / cudaFree anywhere on the path (traverse.cu).  n <= NOALLOC_MAX_RAYS; synchronises `s` before returning.
+constexpr uint32_t NOALLOC_MAX_RAYS = 65536; // 256 B + 48 B per ray = 3 MB of device memory per GPU that loads the library
+cudaError_t TraceClosestNoAlloc( const TraceArgs& base, IsectMode mode, int smCount, int device, const float* hostO4, const float* hostD4, uint32_t n, float* hostHits,
+	cudaStream_t s );
+
 // ---- refit (refit.cu) -------------------------------------------------------------------------------
 struct RefitArgs {
 	uint4* nodes;              // this mesh's nodes (absolute pool pointer)

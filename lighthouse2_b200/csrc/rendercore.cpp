@@ -847,6 +847,24 @@ int RenderCore::WaitWaves()
 	return 0;
 }
 
+// b200_trace_closest_noalloc: the extend wave over host buffers without any allocation.  No counterpart in the reference:
+// nothing on this path calls cudaMalloc, cudaFree or a routine that allocates -- which is also why a
+// stale top level is an error here instead of being rebuilt (UpdateToplevel grows pools).
+int RenderCore::TraceClosestNoAlloc( const float* O4, const float* D4, int n, float* hits )
+{
+	if (n < 0) return fail( "b200_trace_closest_noalloc: negative ray count" );
+	if ((uint32_t)n > NOALLOC_MAX_RAYS)
+		return fail( "b200_trace_closest_noalloc: " + std::to_string( n ) + " rays exceed the fixed scratch of B200_NOALLOC_MAX_RAYS = " + std::to_string( NOALLOC_MAX_RAYS ) +
+			" rays (split the wave, or use b200_trace_closest)" );
+	if (n > 0 && (!O4 || !D4 || !hits)) return fail( "b200_trace_closest_noalloc: null buffer" );
+	if (tlasDirty) return fail( "b200_trace_closest_noalloc: the top level is out of date; call b200_update_toplevel first (this entry point must not allocate)" );
+	if (n == 0) return 0;
+	const cudaError_t e = b200::TraceClosestNoAlloc( baseArgs(), isect, smCount, device, O4, D4, (uint32_t)n, hits, stream );
+	if (e != cudaSuccess) return fail( "b200_trace_closest_noalloc", e );
+	stats.kernelLaunches++;
+	return 0;
+}
+
 int RenderCore::ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris )
 {
 	if (!stepNodes.ptr || stepNodes.bytes < (size_t)n * 4) return fail( "ReadStepCounters: no counters (Setting countSteps=1, then trace)" );

@@ -90,6 +90,7 @@ public:
 	int TraceClosestAsync( const float* O4, const float* D4, int n, float* hits ); // queued: see rendercore.cpp
 	int TraceAnyAsync( const float* O4, const float* D4, int n, uint32_t* bits );
 	int WaitWaves();
+	int TraceClosestNoAlloc( const float* O4, const float* D4, int n, float* hits ); // b200_trace_closest_noalloc: see traverse.cu
 	int TraceClosestDevice( const void* dO4, const void* dD4, int n, void* dHits, const uint32_t* dCount = nullptr );
 	int TraceAnyDevice( const void* dO4, const void* dD4, int n, void* dBits, const uint32_t* dCount = nullptr );
 	int TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount = nullptr,

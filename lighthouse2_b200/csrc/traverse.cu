@@ -680,6 +680,64 @@ cudaError_t LaunchExtend( const TraceArgs& args, IsectMode mode, bool countSteps
 	return cudaGetLastError();
 }
 
+// ---- the extend wave without any allocation (b200_trace_closest_noalloc) ---------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid it).  The wave kernel's scratch -- the persistent-thread fetch counter
+// and the device staging of the ray planes and the hit records of a host-buffer wave -- lives in ONE file-scope device array of a
+// fixed size instead of the core's growable cudaMalloc'ed buffers (rendercore.cpp::hostWave).  Every GPU that loads the library holds
+// the array until exit; every call shares it and it keeps the last call's contents, so the fetch counter is cleared by every call and
+// two calls that overlap on the GPU (different streams, different cores on one device) race.
+// Layout: [0, 256) fetch counter word | O4 plane | D4 plane | hit records, each NOALLOC_MAX_RAYS x 16 bytes.
+static __device__ __align__( 256 ) unsigned char g_noAllocScratch[256 + (size_t)NOALLOC_MAX_RAYS * 48];
+
+// In host code the array's NAME is a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress, asked once
+// per device with that device current.
+static cudaError_t noAllocScratchAddress( int device, unsigned char** out )
+{
+	constexpr int MAX_DEVICES = 64;
+	static unsigned char* address[MAX_DEVICES] = {};
+	if (device < 0 || device >= MAX_DEVICES) return cudaErrorInvalidDevice;
+	if (!address[device])
+	{
+		void* p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress( &p, g_noAllocScratch );
+		if (e != cudaSuccess) return e;
+		address[device] = (unsigned char*)p;
+	}
+	*out = address[device];
+	return cudaSuccess;
+}
+
+cudaError_t TraceClosestNoAlloc( const TraceArgs& base, IsectMode mode, int smCount, int device, const float* hostO4, const float* hostD4, uint32_t n, float* hostHits,
+	cudaStream_t s )
+{
+	if (n > NOALLOC_MAX_RAYS) return cudaErrorInvalidValue;
+	if (n == 0) return cudaSuccess;
+	int previous = -1;
+	cudaError_t e = cudaGetDevice( &previous );
+	if (e != cudaSuccess) return e;
+	if (previous != device && (e = cudaSetDevice( device )) != cudaSuccess) return e;
+	unsigned char* scratch = nullptr;
+	e = noAllocScratchAddress( device, &scratch );
+	if (e == cudaSuccess)
+	{
+		float4* dO = reinterpret_cast<float4*>( scratch + 256 );
+		float4* dD = dO + NOALLOC_MAX_RAYS;
+		float4* dHits = dD + NOALLOC_MAX_RAYS;
+		TraceArgs a = base;
+		a.rayO = dO, a.rayD = dD, a.hits = dHits, a.count = n, a.countPtr = nullptr;
+		a.hostO = a.hostD = nullptr, a.stageO = a.stageD = nullptr, a.stepNodes = a.stepTris = nullptr;
+		a.fetchCounter = reinterpret_cast<uint32_t*>( scratch ), a.fetchCounterNext = nullptr; // LaunchExtend zeroes the counter: the array keeps the last call's value
+		e = cudaMemcpyAsync( dO, hostO4, (size_t)n * 16, cudaMemcpyHostToDevice, s );
+		if (e == cudaSuccess) e = cudaMemcpyAsync( dD, hostD4, (size_t)n * 16, cudaMemcpyHostToDevice, s );
+		if (e == cudaSuccess) e = LaunchExtend( a, mode, false, smCount, s );
+		if (e == cudaSuccess) e = cudaMemcpyAsync( hostHits, dHits, (size_t)n * 16, cudaMemcpyDeviceToHost, s );
+		if (e == cudaSuccess) e = cudaStreamSynchronize( s );
+	}
+	if (previous != device) cudaSetDevice( previous );
+	return e;
+}
+
 cudaError_t LaunchShadow( const TraceArgs& args, IsectMode mode, int smCount, cudaStream_t s )
 {
 	TraceArgs a = args;
