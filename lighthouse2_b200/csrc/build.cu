@@ -409,7 +409,12 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 	float4* nodeHi = nodeLo + P;
 	uint32_t* sortedPrim = reinterpret_cast<uint32_t*>( nodeHi + P );
 	uint32_t *childL = sortedPrim + P, *childR = childL + P, *rangeFirst = childR + P, *rangeCount = rangeFirst + P, *parentInner = rangeCount + P;
-	uint32_t *parentLeaf = parentInner + P, *visits = parentLeaf + P, *wideToBinary = visits + P; // wideToBinary: P + 8
+	uint32_t *parentLeaf = parentInner + P, *visits = parentLeaf + P, *wideToBinary = visits + P; // wideToBinary: P + 16
+	// the collapse plan of the binary nodes (32 bytes each).  In shared memory: the bottom-up pass is a chain as long as the tree is deep, walked by
+	// ONE thread at the end, and with the plans in global scratch every link of it paid two L2 round trips and a device-wide fence (two thirds of
+	// the kernel's 269 us at 1000 instances, ncu source view of round 2)
+	float4* planLo = reinterpret_cast<float4*>( wideToBinary + P + 16 );
+	float4* planHi = planLo + P;
 	__shared__ int sBounds[6];
 	__shared__ uint32_t sCounters[4], sLevel[66], sLevels;
 	const uint32_t tid = threadIdx.x, T = blockDim.x;
@@ -549,7 +554,8 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 					{
 						const volatile float *vl = reinterpret_cast<const volatile float*>( &nodeLo[c[k]] ), *vh = reinterpret_cast<const volatile float*>( &nodeHi[c[k]] );
 						lo[k] = make_float4( vl[0], vl[1], vl[2], 0 ), hi[k] = make_float4( vh[0], vh[1], vh[2], 0 );
-						const float4 a = __ldcg( sc.planLo + c[k] ), b = __ldcg( sc.planHi + c[k] );
+						const volatile float *pa = reinterpret_cast<const volatile float*>( &planLo[c[k]] ), *pb = reinterpret_cast<const volatile float*>( &planHi[c[k]] );
+						const float4 a = make_float4( pa[0], pa[1], pa[2], pa[3] ), b = make_float4( pb[0], pb[1], pb[2], 0 );
 						cc[0] = a.x, cc[1] = a.y, cc[2] = a.z, cc[3] = a.w, cc[4] = b.x, cc[5] = b.y, cc[6] = b.z;
 					}
 				}
@@ -559,17 +565,16 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 				const float ex = nh.x - nl.x, ey = nh.y - nl.y, ez = nh.z - nl.z;
 				uint32_t bits;
 				mergePlan( cl, cr, ex * ey + ey * ez + ez * ex, rangeCount[node], 1, primCost, cost, bits );
-				__stcg( sc.planLo + node, make_float4( cost[0], cost[1], cost[2], cost[3] ) );
-				__stcg( sc.planHi + node, make_float4( cost[4], cost[5], cost[6], __uint_as_float( bits ) ) );
-				__threadfence(); // the plan goes through L2
-				node = parentInner[node];
+				planLo[node] = make_float4( cost[0], cost[1], cost[2], cost[3] );
+				planHi[node] = make_float4( cost[4], cost[5], cost[6], __uint_as_float( bits ) );
+				node = parentInner[node]; // (the block-level fence at the top of the loop orders the stores before the arrival)
 			}
 		}
 		__syncthreads();
 		// 6. collapse to 8-wide nodes, level by level
 		CollapseArgs a;
 		a.sortedPrim = sortedPrim, a.childL = childL, a.childR = childR, a.rangeFirst = rangeFirst, a.rangeCount = rangeCount;
-		a.primLo = sc.primLo, a.primHi = sc.primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = sc.planHi;
+		a.primLo = sc.primLo, a.primHi = sc.primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = planHi;
 		a.wideToBinary = wideToBinary, a.nodes = nodes, a.primOut = sc.instOrder, a.primOutStride = 1, a.counters = sCounters;
 		a.nodeBase = nodeBase, a.triBase = 0, a.maxNodes = maxNodes;
 		if (tid == 0) wideToBinary[0] = 0, sLevel[0] = 0, sLevels = 0;
@@ -731,9 +736,9 @@ cudaError_t LaunchTlasBuild( const TlasInstanceInput* dInstances, uint32_t n, ui
 	uint32_t* info, void* scratch, float primCost, cudaStream_t s )
 {
 	if (n == 0 || n > MAX_DEVICE_TLAS_INSTANCES) return cudaErrorInvalidValue;
-	uint32_t P = 2;
+	uint32_t P = 4; // (at least 4: the float4 arrays behind the uint32 ones stay 16-byte aligned)
 	while (P < n) P <<= 1;
-	const size_t smem = (size_t)P * (8 + 32 + 4 * 9) + 64; // keys, binary node boxes, nine uint32 arrays (wideToBinary with 8 spare entries)
+	const size_t smem = (size_t)P * (8 + 32 + 4 * 9 + 32) + 64; // keys, binary node boxes, nine uint32 arrays (wideToBinary with 16 spare entries), collapse plans
 	static size_t allowed = 0;
 	cudaError_t e;
 	if (smem > allowed)

@@ -223,3 +223,107 @@ class DisneyRef:
         out = np.zeros((len(alpha), 3), np.float32)
         self.lib.ref_consistent_normal(len(alpha), self._c(D), self._c(iN), self._c(alpha), out)
         return out
+
+
+SHADE_REF_SO = os.path.join(HERE, "_ref", "liboracle_shade_ref.so")
+
+
+def have_shade_ref() -> bool:
+    return os.path.exists(SHADE_REF_SO)
+
+
+class ShadeRef:
+    """The reference's own Lambert BSDF and light-sampling helpers (lib/sharedBSDFs/lambert.h, lib/CUDA/shared_kernel_code/
+    lights_shared.h, unmodified, compiled for the host by oracle/Makefile; see ref_shade_driver.cpp), over arrays.  Materials the way
+    the reference's ShadingData holds them: color[n,3], transmittance[n,3], params uint32[n,4] (roughness in bits 24..31 of word 0,
+    transmission in bits 16..23 of word 2, eta as float bits in word 3).  Lights: the record arrays of lighthouse2_b200/lights.py."""
+
+    def __init__(self):
+        if not os.path.exists(SHADE_REF_SO):
+            build()
+        if not os.path.exists(SHADE_REF_SO):
+            raise RuntimeError("oracle/_ref/liboracle_shade_ref.so is missing and /root/reference is not here to build it")
+        lib = C.CDLL(SHADE_REF_SO)
+        u = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+        lib.ref_lambert_sample.argtypes = [C.c_int, _f, _f, u, _f, _f, _f, _f, _f, _f, _f, _f, _i, _f]
+        lib.ref_lambert_evaluate.argtypes = [C.c_int, _f, _f, u, _f, _f, _f, _f, _f]
+        lib.ref_set_lights.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        lib.ref_set_lights.restype = C.c_int
+        lib.ref_random_barycentrics.argtypes = [C.c_int, _f, _f]
+        lib.ref_random_point_on_light.argtypes = [C.c_int, _f, _f, _f, _f, _f, _f, _f, _f]
+        lib.ref_light_pick_prob.argtypes = [C.c_int, _i, _f, _f, _f, _f]
+        lib.ref_calculate_light_pdf.argtypes = [C.c_int, _f, _f, _f, _f, _f]
+        lib.ref_safe_origin.argtypes = [C.c_int, _f, _f, _f, C.c_float, _f]
+        self.lib = lib
+        self._lights = None
+
+    @staticmethod
+    def _c(a, dt=np.float32):
+        return np.ascontiguousarray(a, dt)
+
+    @staticmethod
+    def params(roughness, transmission, eta):
+        """uint32[n,4] parameter words as the cores pack them (TOUINT4, rendercore_optix7/rendercore.cpp:511-512)."""
+        r = (np.asarray(roughness, np.float32) * np.float32(255.0)).astype(np.uint32)
+        t = (np.asarray(transmission, np.float32) * np.float32(255.0)).astype(np.uint32)
+        out = np.zeros((len(r), 4), np.uint32)
+        out[:, 0] = r << np.uint32(24)
+        out[:, 2] = t << np.uint32(16)
+        out[:, 3] = np.asarray(eta, np.float32).view(np.uint32)
+        return out
+
+    def sample(self, color, transmittance, params, iN, N, wow, distance, r3, r4):
+        """SampleBSDF (lambert.h:71-123) -> (wiw[n,3], pdf[n], specular[n] bool, value[n,3])"""
+        n = len(r3)
+        wiw, pdf, spec, value = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32), np.zeros((n, 3), np.float32)
+        c = self._c
+        self.lib.ref_lambert_sample(n, c(color), c(transmittance), c(params, np.uint32), c(iN), c(N), c(wow), c(distance), c(r3), c(r4), wiw, pdf, spec, value)
+        return wiw, pdf, spec != 0, value
+
+    def evaluate(self, color, transmittance, params, iN, wow, wiw):
+        """EvaluateBSDF (lambert.h:58-69) -> (value[n,3], pdf[n])"""
+        n = len(wiw)
+        pdf, value = np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+        c = self._c
+        self.lib.ref_lambert_evaluate(n, c(color), c(transmittance), c(params, np.uint32), c(iN), c(wow), c(wiw), pdf, value)
+        return value, pdf
+
+    def set_lights(self, area=None, point=None, spot=None, directional=None):
+        arrs = []
+        for a, width in ((area, 24), (point, 8), (spot, 12), (directional, 8)):
+            arrs.append(np.zeros((0, width), np.float32) if a is None else np.ascontiguousarray(a, np.float32).reshape(-1, width))
+        self._lights = arrs  # (the library copies; kept for symmetry)
+        args = []
+        for a in arrs:
+            args += [a.ctypes.data if len(a) else None, len(a)]
+        if self.lib.ref_set_lights(*args):
+            raise ValueError("the reference keeps light potentials in float[MAXISLIGHTS = 8] (lights_shared.h:25,124,177): more than 8 lights overrun it")
+
+    def random_barycentrics(self, r0):
+        out = np.zeros((len(r0), 3), np.float32)
+        self.lib.ref_random_barycentrics(len(r0), self._c(r0), out)
+        return out
+
+    def random_point_on_light(self, r0, r1, I, N):
+        """RandomPointOnLight (lights_shared.h:171-262) -> P, pickProb, lightPdf, lightColor (NaN where the reference leaves it unset)"""
+        n = len(r0)
+        P, pick, pdf, col = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+        c = self._c
+        self.lib.ref_random_point_on_light(n, c(r0), c(r1), c(I), c(N), P, pick, pdf, col)
+        return P, pick, pdf, col
+
+    def light_pick_prob(self, idx, O, N, I):
+        out = np.zeros(len(idx), np.float32)
+        self.lib.ref_light_pick_prob(len(idx), self._c(idx, np.int32), self._c(O), self._c(N), self._c(I), out)
+        return out
+
+    def calculate_light_pdf(self, D, t, area, light_normal):
+        out = np.zeros(len(t), np.float32)
+        self.lib.ref_calculate_light_pdf(len(t), self._c(D), self._c(t), self._c(area), self._c(light_normal), out)
+        return out
+
+    def safe_origin(self, O, R, N, eps):
+        out = np.zeros((len(O), 3), np.float32)
+        self.lib.ref_safe_origin(len(O), self._c(O), self._c(R), self._c(N), float(eps), out)
+        return out
+

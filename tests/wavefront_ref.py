@@ -194,6 +194,66 @@ def random_point_on_light(lights, r0, r1, I, N):
     return P, pick, pdf.astype(f32), col
 
 
+def lambert_sample(color, absorption, rough, transmission, eta, fN, gF, face, D, t, r3, r4):
+    """SampleBSDF of lib/sharedBSDFs/lambert.h:71-123 over arrays, as the shade stage calls it (pathtracer.h:219).  fN / gF: shading and
+    geometric normal on the side the ray came from (iN * flip, N * flip of the reference), face: +1 outside, -1 inside the medium, D: ray
+    direction (wo = -D), t: distance travelled (Beer absorption).  Returns R, pdf, specular, bsdf value, dot(fN, R).  One deviation,
+    shared with the device code: on total internal reflection the reference returns a zero value with pdf 1 (the path lives on with a zero
+    throughput); here the pdf is 0 and the path ends.  Diffuse directions come from sincos_det, the reference's from __sincosf."""
+    p_reflect = (f32(1) - rough).astype(f32)
+    ddotn = dot(D, fN)
+    R_refl = (D - fN * (f32(2) * ddotn)[:, None]).astype(f32)
+    trans = r4 < transmission
+    with np.errstate(all="ignore"):
+        # dielectric branch (lambert.h:84-103)
+        eio = np.where(face < 0, f32(1) / eta, eta).astype(f32)
+        c = -ddotn
+        e2 = np.where(c < 0, f32(1) / eio, eio).astype(f32)
+        c = np.abs(c)
+        sinT2 = (e2 * e2 * (f32(1) - c * c)).astype(f32)
+        ldn = np.sqrt(np.maximum(f32(0), f32(1) - sinT2)).astype(f32)
+        ra, rb = (c - e2 * ldn) / (c + e2 * ldn), (ldn - e2 * c) / (ldn + e2 * c)
+        F = np.where(sinT2 <= 1, f32(0.5) * (ra * ra + rb * rb), f32(1)).astype(f32)
+        beer = np.exp(-absorption * (t * f32(2))[:, None]).astype(f32)
+        cosI = np.abs(ddotn)
+        sin2T = (eio * eio * np.maximum(f32(0), f32(1) - cosI * cosI)).astype(f32)
+        tir = sin2T >= 1
+        R_refr = (D * eio[:, None] + fN * (eio * cosI - np.sqrt(np.maximum(f32(0), f32(1) - sin2T)))[:, None]).astype(f32)
+        reflect_t = trans & (r3 < F)
+        refract_t = trans & ~(r3 < F) & ~tir
+        dead_tir = trans & ~(r3 < F) & tir
+        # opaque branch
+        spec_o = ~trans & (r3 < p_reflect)
+        r5 = ((r3 - p_reflect) / (f32(1) - p_reflect)).astype(f32)
+        r6 = ((r4 - transmission) / (f32(1) - transmission)).astype(f32)
+        term1, term2 = TWOPI * r5, np.sqrt(f32(1) - r6)
+        sn_, cs_ = sincos_det(term1)
+        V = np.stack([cs_ * term2, sn_ * term2, np.sqrt(r6)], axis=1).astype(f32)
+        R_diff = normalize(tangent2world(V, fN))
+        diffuse = ~trans & ~spec_o
+        R = np.where((reflect_t | spec_o)[:, None], R_refl, np.where(refract_t[:, None], R_refr, R_diff)).astype(f32)
+        cosr = dot(fN, R)
+        inv_cos = (f32(1) / np.abs(cosr))[:, None]
+        bsdf = np.where(trans[:, None], color * beer * inv_cos, np.where(spec_o[:, None], color * inv_cos, color * INVPI)).astype(f32)
+        new_pdf = np.where(diffuse, np.maximum(f32(0), cosr) * INVPI, f32(1)).astype(f32)
+    new_pdf = np.where(dead_tir, f32(0), new_pdf)
+    new_pdf = np.where(~refract_t & (dot(gF, R) <= 0), f32(0), new_pdf)
+    return R, new_pdf, ~diffuse, bsdf, cosr
+
+
+def light_pick_prob(lights, ltri, O, N, I):
+    """LightPickProb (lights_shared.h:122-138): the probability that next-event estimation at (O, N) would have picked area light `ltri`,
+    seen at point I; 0 where ltri < 0.  (The reference sums into a fixed float[8] and overruns it with more lights; nothing is stored here.)"""
+    n = len(O)
+    with np.errstate(all="ignore"):
+        pot = lights.potentials(O, N, P=I)
+        ssum = np.zeros(n, f32)
+        for k in range(pot.shape[1]):
+            ssum = (ssum + pot[:, k]).astype(f32)
+        mine = pot[np.arange(n), np.maximum(ltri, 0)] if pot.shape[1] else np.zeros(n, f32)
+        return np.where((ltri >= 0) & (ssum > 0), mine / ssum, f32(0)).astype(f32)
+
+
 def sample_skydome(D, sky, sky_image):
     """tools_shared.h:185-192."""
     if sky_image is None:
@@ -552,12 +612,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                         ltri[match], area[match] = li, a[7]
                     with np.errstate(all="ignore"):
                         light_pdf = np.where(ltri >= 0, (t[e] * t[e]) / (ddn * area), f32(0)).astype(f32)
-                        pot = lights.potentials(O[e], lastN[e], P=I[e])
-                        ssum = np.zeros(len(e), f32)
-                        for k in range(pot.shape[1]):
-                            ssum = (ssum + pot[:, k]).astype(f32)
-                        mine = pot[np.arange(len(e)), np.maximum(ltri, 0)] if pot.shape[1] else np.zeros(len(e), f32)
-                        pick = np.where((ltri >= 0) & (ssum > 0), mine / ssum, f32(0)).astype(f32)
+                        pick = light_pick_prob(lights, ltri, O[e], lastN[e], I[e])
                         w = (pdf_prev[e] + light_pdf * pick).astype(f32)
                         cm = np.where((w > 0)[:, None], c * (f32(1) / w)[:, None], f32(0)).astype(f32)
                     c = np.where(mis[:, None], cm, c)
@@ -628,45 +683,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             else:
                 seed, r3 = random_float(seed)
                 seed, r4 = random_float(seed)
-            p_reflect = (f32(1) - rough).astype(f32)
-            ddotn = dot(D, fN)
-            R_refl = (D - fN * (f32(2) * ddotn)[:, None]).astype(f32)
-            trans = r4 < transmission
-            with np.errstate(all="ignore"):
-                # dielectric branch (lambert.h:84-103)
-                eio = np.where(face < 0, f32(1) / eta, eta).astype(f32)
-                c = -ddotn
-                e2 = np.where(c < 0, f32(1) / eio, eio).astype(f32)
-                c = np.abs(c)
-                sinT2 = (e2 * e2 * (f32(1) - c * c)).astype(f32)
-                ldn = np.sqrt(np.maximum(f32(0), f32(1) - sinT2)).astype(f32)
-                ra, rb = (c - e2 * ldn) / (c + e2 * ldn), (ldn - e2 * c) / (ldn + e2 * c)
-                F = np.where(sinT2 <= 1, f32(0.5) * (ra * ra + rb * rb), f32(1)).astype(f32)
-                beer = np.exp(-absorption * (t * f32(2))[:, None]).astype(f32)
-                cosI = np.abs(ddotn)
-                sin2T = (eio * eio * np.maximum(f32(0), f32(1) - cosI * cosI)).astype(f32)
-                tir = sin2T >= 1
-                R_refr = (D * eio[:, None] + fN * (eio * cosI - np.sqrt(np.maximum(f32(0), f32(1) - sin2T)))[:, None]).astype(f32)
-                reflect_t = trans & (r3 < F)
-                refract_t = trans & ~(r3 < F) & ~tir
-                dead_tir = trans & ~(r3 < F) & tir
-                # opaque branch
-                spec_o = ~trans & (r3 < p_reflect)
-                r5 = ((r3 - p_reflect) / (f32(1) - p_reflect)).astype(f32)
-                r6 = ((r4 - transmission) / (f32(1) - transmission)).astype(f32)
-                term1, term2 = TWOPI * r5, np.sqrt(f32(1) - r6)
-                sn_, cs_ = sincos_det(term1)
-                V = np.stack([cs_ * term2, sn_ * term2, np.sqrt(r6)], axis=1).astype(f32)
-                R_diff = normalize(tangent2world(V, fN))
-                diffuse = ~trans & ~spec_o
-                R = np.where((reflect_t | spec_o)[:, None], R_refl, np.where(refract_t[:, None], R_refr, R_diff)).astype(f32)
-                cosr = dot(fN, R)
-                inv_cos = (f32(1) / np.abs(cosr))[:, None]
-                bsdf = np.where(trans[:, None], color * beer * inv_cos, np.where(spec_o[:, None], color * inv_cos, color * INVPI)).astype(f32)
-                new_pdf = np.where(diffuse, np.maximum(f32(0), cosr) * INVPI, f32(1)).astype(f32)
-            new_pdf = np.where(dead_tir, f32(0), new_pdf)
-            new_pdf = np.where(~refract_t & (dot(gF, R) <= 0), f32(0), new_pdf)
-            spec = ~diffuse
+            R, new_pdf, spec, bsdf, cosr = lambert_sample(color, absorption, rough, transmission, eta, fN, gF, face, D, t, r3, r4)
             if disney is not None:
                 # SampleBSDF( shadingData, fN, N, T, -D, HIT_T, r3, r4, ... ) (pathtracer.h:219); total internal reflection ends the path
                 R, new_pdf, spec, bsdf = disney.sample(color, absorption, disney_tint(base_color), words, sN, N, tang, (D * f32(-1)).astype(f32), t, r3, r4)
