@@ -296,24 +296,31 @@ __device__ void collapseNode( const CollapseArgs& a, const uint32_t w )
 		nlo[c] = lo[0][c], nhi[c] = hi[0][c];
 		for (int i = 1; i < n; i++) nlo[c] = fminf( nlo[c], lo[i][c] ), nhi[c] = fmaxf( nhi[c], hi[i][c] );
 	}
+	// (the child's offset from the node centre is computed once per child and the eight signed sums once per (slot, child) pair; the n
+	// greedy rounds then only compare.  Recomputing them inside the rounds -- 8 x n x n x 3 steps -- made this loop a quarter of all
+	// instructions of the one-block top-level build, where the first levels of the tree have 1, 8, ... nodes and as many busy threads.
+	// Same sums, same scan order, same strict <: the slots, and with them the trees, are the ones the first version chose.)
 	int childInSlot[8] = { -1, -1, -1, -1, -1, -1, -1, -1 };
-	uint32_t done = 0;
+	float score[8][8];
+	for (int i = 0; i < n; i++)
+	{
+		float rel[3];
+		for (int c = 0; c < 3; c++) rel[c] = 0.5f * (lo[i][c] + hi[i][c]) - 0.5f * (nlo[c] + nhi[c]);
+		for (int s = 0; s < 8; s++)
+		{
+			float d = 0;
+			for (int c = 0; c < 3; c++) d += ((s >> (2 - c)) & 1) ? -rel[c] : rel[c];
+			score[s][i] = d;
+		}
+	}
+	uint32_t done = 0, freeSlots = 0xffu;
 	for (int k = 0; k < n; k++)
 	{
 		float best = 3.0e38f;
 		int bs = 0, bi = 0;
-		for (int s = 0; s < 8; s++) if (childInSlot[s] < 0)
-			for (int i = 0; i < n; i++) if (!(done & (1u << i)))
-			{
-				float d = 0;
-				for (int c = 0; c < 3; c++)
-				{
-					const float rel = 0.5f * (lo[i][c] + hi[i][c]) - 0.5f * (nlo[c] + nhi[c]);
-					d += ((s >> (2 - c)) & 1) ? -rel : rel;
-				}
-				if (d < best) best = d, bs = s, bi = i;
-			}
-		childInSlot[bs] = bi, done |= 1u << bi;
+		for (int s = 0; s < 8; s++) if (freeSlots & (1u << s))
+			for (int i = 0; i < n; i++) if (!(done & (1u << i)) && score[s][i] < best) best = score[s][i], bs = s, bi = i;
+		childInSlot[bs] = bi, done |= 1u << bi, freeSlots &= ~(1u << bs);
 	}
 	uint32_t innerCount = 0, leafPrims = 0;
 	for (int i = 0; i < n; i++) if (innerChild[i]) innerCount++; else leafPrims += cnt[i];
@@ -380,18 +387,17 @@ __device__ __forceinline__ uint32_t tlasFrame( const float lo, const float hi, f
 	p = lo;
 	if (ext > 0)
 	{
-		int fe;
-		frexp( ext / 254.75, &fe );
-		ex = fe;
-		if (ldexp( 254.75, ex - 1 ) >= ext) ex--;
+		// frexp( ext / 254.75 ): the exponent field of the double, + 1 for the [0.5, 1) mantissa (no denormals: ext comes from floats)
+		ex = ((__double2hiint( ext / 254.75 ) >> 20) & 0x7ff) - 1022;
+		if (__hiloint2double( (ex - 1 + 1023) << 20, 0 ) * 254.75 >= ext) ex--;
 		if (ex < -100) ex = -100;
-		p = (float)((double)lo - ldexp( 1.0, ex - 3 ));
+		p = (float)((double)lo - __hiloint2double( (ex - 3 + 1023) << 20, 0 ));
 	}
 	return (uint32_t)(ex + 127);
 }
 __device__ __forceinline__ void tlasQuantise( const float p, const uint32_t e, const float lo, const float hi, uint32_t& qlo, uint32_t& qhi )
 {
-	const double inv = ldexp( 1.0, 127 - (int)e );
+	const double inv = __hiloint2double( (127 - (int)e + 1023) << 20, 0 ); // 2^(127 - e)
 	const double l = floor( ((double)lo - (double)p) * inv - 1.0 / 64.0 ), h = ceil( ((double)hi - (double)p) * inv + 1.0 / 64.0 );
 	qlo = (uint32_t)(l < 0 ? 0 : (l > 255 ? 255 : l)), qhi = (uint32_t)(h < 0 ? 0 : (h > 255 ? 255 : h));
 }
@@ -418,6 +424,10 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 	__shared__ int sBounds[6];
 	__shared__ uint32_t sCounters[4], sLevel[66], sLevels;
 	const uint32_t tid = threadIdx.x, T = blockDim.x;
+	// phase clock of thread 0 (SM cycles since the start), kept in info[4..12]: boxes, keys, sort, radix tree, bottom-up, collapse, planes, records
+	const long long clock0 = clock64();
+	int phase = 4;
+	auto stamp = [&]() { if (tid == 0 && phase < 13) info[phase] = (uint32_t)(clock64() - clock0); phase++; };
 	if (tid < 6) sBounds[tid] = tid < 3 ? 0x7fffffff : (int)0x80000000;
 	if (tid < 4) sCounters[tid] = tid == 0 ? 1u : 0u; // wide node 0 = the root is taken
 	__syncthreads();
@@ -451,6 +461,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		}
 	}
 	__syncthreads();
+	stamp();
 	// 2. keys: 30-bit Morton code of the centroid, the instance index below it (unique keys: no ties for the radix tree); padding sorts last
 	for (uint32_t i = tid; i < P; i += T)
 	{
@@ -472,6 +483,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		keys[i] = key;
 	}
 	__syncthreads();
+	stamp();
 	// 3. bitonic sort of the P keys
 	for (uint32_t k = 2; k <= P; k <<= 1)
 		for (uint32_t j = k >> 1; j > 0; j >>= 1)
@@ -489,6 +501,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		}
 	for (uint32_t i = tid; i < n; i += T) sortedPrim[i] = (uint32_t)keys[i], visits[i] = 0;
 	__syncthreads();
+	stamp();
 	if (n == 1)
 	{
 		// a single instance: one node with one leaf slot
@@ -528,6 +541,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 			if (i == 0) parentInner[0] = 0xffffffffu;
 		}
 		__syncthreads();
+		stamp();
 		// 5. bottom-up: boxes of the binary nodes and the collapse plan (leaf slots hold ONE instance)
 		for (uint32_t i = tid; i < n; i += T)
 		{
@@ -571,6 +585,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 			}
 		}
 		__syncthreads();
+		stamp();
 		// 6. collapse to 8-wide nodes, level by level
 		CollapseArgs a;
 		a.sortedPrim = sortedPrim, a.childL = childL, a.childR = childR, a.rangeFirst = rangeFirst, a.rangeCount = rangeCount;
@@ -591,25 +606,28 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		}
 	}
 	__syncthreads();
-	// 7. boxes, frames and quantised planes, deepest level first (a leaf slot's box is its instance's world box)
+	if (n == 1) phase = 9; else stamp();
+	// 7. boxes, frames and quantised planes, deepest level first (a leaf slot's box is its instance's world box).  Eight lanes per node,
+	//    lane s owns child slot s (as refit.cu::refitSlot does): the node box is an 8-lane shuffle reduction, every lane quantises its own child
 	const uint32_t nodeCount = sCounters[0] < maxNodes ? sCounters[0] : maxNodes, levels = sLevels;
 	for (int level = (int)levels - 1; level >= 0; level--)
 	{
-		for (uint32_t w = sLevel[level] + tid; w < sLevel[level + 1]; w += T)
+		const uint32_t begin = sLevel[level], slots = (sLevel[level + 1] - begin) * 8;
+		for (uint32_t i = tid; i < ((slots + T - 1) / T) * T; i += T) // (whole warps iterate: the shuffles below need every lane of a group's warp)
 		{
+			const bool valid = i < slots;
+			const uint32_t w = begin + (valid ? i >> 3 : 0), slot = i & 7;
 			uint4* np = nodes + (size_t)w * 5;
 			const uint4 n0 = np[0], n1 = np[1];
 			const uint32_t imask = n0.w >> 24;
-			float clo[8][3], chi[8][3], nlo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, nhi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
-			uint32_t used = 0;
-			for (uint32_t s = 0; s < 8; s++)
+			const uint32_t meta = ((slot < 4 ? n1.z : n1.w) >> (8 * (slot & 3))) & 0xffu;
+			float clo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, chi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+			if (valid && meta)
 			{
-				const uint32_t meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
-				if (!meta) continue;
 				float4 l, h;
-				if (imask & (1u << s))
+				if (imask & (1u << slot))
 				{
-					const uint32_t child = n1.x + __popc( imask & ((1u << s) - 1u) ) - nodeBase;
+					const uint32_t child = n1.x + __popc( imask & ((1u << slot) - 1u) ) - nodeBase;
 					l = __ldcg( sc.wideLo + child ), h = __ldcg( sc.wideHi + child );
 				}
 				else
@@ -617,30 +635,32 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 					const uint32_t inst = __ldcg( sc.instOrder + n1.y + (meta & 31u) );
 					l = sc.primLo[inst], h = sc.primHi[inst];
 				}
-				used |= 1u << s;
-				clo[s][0] = l.x, clo[s][1] = l.y, clo[s][2] = l.z, chi[s][0] = h.x, chi[s][1] = h.y, chi[s][2] = h.z;
-				for (int c = 0; c < 3; c++) nlo[c] = fminf( nlo[c], clo[s][c] ), nhi[c] = fmaxf( nhi[c], chi[s][c] );
+				clo[0] = l.x, clo[1] = l.y, clo[2] = l.z, chi[0] = h.x, chi[1] = h.y, chi[2] = h.z;
 			}
-			uint32_t e[3];
-			float fp[3];
-			for (int c = 0; c < 3; c++) e[c] = tlasFrame( nlo[c], nhi[c], fp[c] );
-			uint8_t q[48];
-			for (int i = 0; i < 48; i++) q[i] = 0;
-			for (uint32_t s = 0; s < 8; s++) if (used & (1u << s))
-				for (int c = 0; c < 3; c++)
-				{
-					uint32_t ql, qh;
-					tlasQuantise( fp[c], e[c], clo[s][c], chi[s][c], ql, qh );
-					q[8 * c + s] = (uint8_t)ql, q[24 + 8 * c + s] = (uint8_t)qh;
-				}
-			np[0] = make_uint4( __float_as_uint( fp[0] ), __float_as_uint( fp[1] ), __float_as_uint( fp[2] ), e[0] | (e[1] << 8) | (e[2] << 16) | (imask << 24) );
-			const uint32_t* qw = reinterpret_cast<const uint32_t*>( q );
-			np[2] = make_uint4( qw[0], qw[1], qw[2], qw[3] ), np[3] = make_uint4( qw[4], qw[5], qw[6], qw[7] ), np[4] = make_uint4( qw[8], qw[9], qw[10], qw[11] );
-			__stcg( sc.wideLo + w, make_float4( nlo[0], nlo[1], nlo[2], 0 ) ), __stcg( sc.wideHi + w, make_float4( nhi[0], nhi[1], nhi[2], 0 ) );
+			uint32_t e[3], ql[3] = { 0, 0, 0 }, qh[3] = { 0, 0, 0 };
+			float fp[3], nlo[3], nhi[3];
+			for (int c = 0; c < 3; c++)
+			{
+				float lo = clo[c], hi = chi[c];
+				for (int d = 1; d < 8; d <<= 1) lo = fminf( lo, __shfl_xor_sync( 0xffffffffu, lo, d ) ), hi = fmaxf( hi, __shfl_xor_sync( 0xffffffffu, hi, d ) );
+				nlo[c] = lo, nhi[c] = hi;
+				e[c] = tlasFrame( lo, hi, fp[c] );
+				if (valid && meta) tlasQuantise( fp[c], e[c], clo[c], chi[c], ql[c], qh[c] );
+			}
+			if (!valid) continue;
+			uint8_t* q = reinterpret_cast<uint8_t*>( np + 2 ); // qlox[8] qloy[8] qloz[8] qhix[8] qhiy[8] qhiz[8]
+			q[slot] = (uint8_t)ql[0], q[8 + slot] = (uint8_t)ql[1], q[16 + slot] = (uint8_t)ql[2];
+			q[24 + slot] = (uint8_t)qh[0], q[32 + slot] = (uint8_t)qh[1], q[40 + slot] = (uint8_t)qh[2];
+			if (slot == 0)
+			{
+				np[0] = make_uint4( __float_as_uint( fp[0] ), __float_as_uint( fp[1] ), __float_as_uint( fp[2] ), e[0] | (e[1] << 8) | (e[2] << 16) | (imask << 24) );
+				__stcg( sc.wideLo + w, make_float4( nlo[0], nlo[1], nlo[2], 0 ) ), __stcg( sc.wideHi + w, make_float4( nhi[0], nhi[1], nhi[2], 0 ) );
+			}
 		}
 		__threadfence();
 		__syncthreads();
 	}
+	stamp();
 	// 8. instance records in leaf order (wide_bvh.h InstanceRec) and the shading-time table by instance id (rendercore.cpp)
 	for (uint32_t j = tid; j < n; j += T)
 	{
@@ -655,6 +675,8 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		for (int k = 0; k < 3; k++) sh[k] = make_float4( S.transform[4 * k], S.transform[4 * k + 1], S.transform[4 * k + 2], S.transform[4 * k + 3] );
 		sh[3] = make_float4( __uint_as_float( S.triBase ), __uint_as_float( S.meshId ), 0, 0 );
 	}
+	__syncthreads();
+	stamp();
 	if (tid == 0) info[0] = nodeCount, info[1] = levels, info[2] = (sCounters[2] || sCounters[0] > maxNodes || levels >= 64) ? 1u : 0u, info[3] = 0;
 }
 

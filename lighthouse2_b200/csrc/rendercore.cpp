@@ -601,8 +601,12 @@ int RenderCore::updateToplevelDevice( uint32_t N, double t0 )
 	if ((e = LaunchTlasBuild( (const TlasInstanceInput*)tlasIn.ptr, N, (uint4*)((char*)nodePool.ptr + (size_t)tlasRoot * 80), tlasRoot, maxNodes, (float4*)instPool.ptr,
 		(float4*)instShadePool.ptr, (uint32_t*)tlasInfo.ptr, tlasScratch.ptr, 1.0f, stream )) != cudaSuccess) return fail( "top-level build kernel", e );
 	stats.kernelLaunches++;
-	if ((e = cudaMemcpyAsync( hostInfo, tlasInfo.ptr, 16, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "top-level info", e );
+	if ((e = cudaMemcpyAsync( hostInfo, tlasInfo.ptr, 64, cudaMemcpyDeviceToHost, stream )) != cudaSuccess) return fail( "top-level info", e );
 	if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "UpdateToplevel sync", e );
+	static const bool tlasTiming = getenv( "B200_TLAS_TIMING" ) != nullptr; // debugging aid: the kernel's phase clock (SM cycles) on stderr
+	if (tlasTiming)
+		fprintf( stderr, "[tlas] n=%u nodes=%u levels=%u cycles: boxes %u keys %u sort %u tree %u bottom-up %u collapse %u planes %u records %u\n", N, hostInfo[0], hostInfo[1],
+			hostInfo[4], hostInfo[5], hostInfo[6], hostInfo[7], hostInfo[8], hostInfo[9], hostInfo[10], hostInfo[11] );
 	if (hostInfo[2]) return fail( "UpdateToplevel: the device top-level build overflowed its node budget" );
 	tlasNodeCount = hostInfo[0];
 	// the kernels' per-lane stack has no bound check: refuse scenes that could overrun it (see wide_bvh.h)
