@@ -18,10 +18,11 @@ from lighthouse2_b200 import core, scenes  # noqa: E402
 
 
 def stats_line(name, rc, frames, extra):
-    # per-class rates: waves one after the other (overlapConnect = 0), so that each event pair times one wave alone;
+    # per-class rates: waves one after the other (overlapConnect = 0, one chain), so that each event pair times one wave alone;
     # frame time: the default schedule (connect wave of bounce k beside the extend wave of bounce k+1)
     acc = {}
     rc.Setting("overlapConnect", 0)
+    rc.Setting("chains", 1)  # one chain, so that no wave of another chain runs inside a wave's event span
     for _ in range(2):
         rc.Render(extra["view"], 1)
     for _ in range(frames):
@@ -32,6 +33,7 @@ def stats_line(name, rc, frames, extra):
                 acc[k] = acc.get(k, 0) + v
     serial_render_ms = acc["renderTime"] / frames
     rc.Setting("overlapConnect", 1)
+    rc.Setting("chains", 0)
     for _ in range(2):
         rc.Render(extra["view"], 1)
     t0 = time.perf_counter()
