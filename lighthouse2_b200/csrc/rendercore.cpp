@@ -180,6 +180,7 @@ int RenderCore::Setting( const char* name, float value )
 	if (!strcmp( name, "countSteps" )) { countSteps = value >= 0.5f; return 0; }
 	if (!strcmp( name, "refit" )) { allowRefit = value >= 0.5f; return 0; }
 	if (!strcmp( name, "refitWalk" )) { refitWalk = value >= 0.5f; return 0; }
+	if (!strcmp( name, "l2Persist" )) { if (value < 0 || value > 1) return fail( "Setting l2Persist: 0 (off) .. 1 (fraction of the L2 that may be set aside)" ); l2Persist = value; return 0; }
 	if (!strcmp( name, "sahPrimCost" )) { if (!(value > 0)) return fail( "Setting sahPrimCost: > 0" ); g_sahPrimCost = value; return 0; }
 	if (!strcmp( name, "buildThreads" )) { buildThreads = value < 1 ? 1 : (int)value; return 0; }
 	return SettingWavefront( name, value );
@@ -620,6 +621,35 @@ int RenderCore::updateToplevelDevice( uint32_t N, double t0 )
 
 int RenderCore::ensureToplevel() { return tlasDirty ? UpdateToplevel() : 0; }
 
+
+// Setting l2Persist: an access-policy window over the node pool on stream `s` (see rendercore.h).  The set-aside is a device-wide limit.
+int RenderCore::applyL2Window( cudaStream_t s )
+{
+	cudaStreamAttrValue attr;
+	memset( &attr, 0, sizeof( attr ) );
+	if (l2Persist <= 0 || !nodePool.ptr)
+	{
+		attr.accessPolicyWindow.num_bytes = 0; // no window
+		cudaStreamSetAttribute( s, cudaStreamAttributeAccessPolicyWindow, &attr );
+		cudaGetLastError();
+		return 0;
+	}
+	int maxPersist = 0, maxWindow = 0;
+	cudaDeviceGetAttribute( &maxPersist, cudaDevAttrMaxPersistingL2CacheSize, device );
+	cudaDeviceGetAttribute( &maxWindow, cudaDevAttrMaxAccessPolicyWindowSize, device );
+	const size_t setAside = (size_t)((double)maxPersist * l2Persist);
+	cudaError_t e = cudaDeviceSetLimit( cudaLimitPersistingL2CacheSize, setAside );
+	if (e != cudaSuccess) return fail( "cudaLimitPersistingL2CacheSize", e );
+	const size_t poolBytes = (size_t)(blasNodeEnd + tlasNodeCount) * 80;
+	const size_t window = std::min( poolBytes, (size_t)maxWindow );
+	attr.accessPolicyWindow.base_ptr = nodePool.ptr;
+	attr.accessPolicyWindow.num_bytes = window;
+	attr.accessPolicyWindow.hitRatio = window ? (float)std::min( 1.0, (double)setAside / (double)window ) : 0.f;
+	attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+	attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+	if ((e = cudaStreamSetAttribute( s, cudaStreamAttributeAccessPolicyWindow, &attr )) != cudaSuccess) return fail( "access policy window", e );
+	return 0;
+}
 
 // ---- the raw waves -------------------------------------------------------------------------------------
 TraceArgs RenderCore::baseArgs() const

@@ -77,6 +77,10 @@ public:
 	int ClosePeers();
 	int GatherFinalize( uint32_t totalSamples );
 	long long peerLimitTicks() const;
+	// Setting l2Persist: fraction of the L2 set aside for persisting lines (0 = off); streams that run wave kernels then carry an access
+	// policy window over the node pool (the top of the tree is what every ray touches).  For scenes that do not fit the 126 MB L2.
+	int applyL2Window( cudaStream_t s );
+	float l2Persist = 0.f;
 	int Finalize( uint32_t totalSamples );                    // frame = accumulator / totalSamples (after a gather)
 	int Render( const void* viewPyramid, int converge );
 	int ReadAccumulator( float* dst );

@@ -324,6 +324,10 @@ constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
 #ifndef B200_MIN_BLOCKS
 #define B200_MIN_BLOCKS 6
 #endif
+#ifndef B200_STREAM_RAYS
+#define B200_STREAM_RAYS 1 // rays are fetched and results stored with the evict-first policy (ld.global.cs / st.global.cs): they are touched once, and
+                            // on scenes larger than L2 (C3: 581 MB) every line they do not claim is a node or triangle line that stays
+#endif
 #ifndef B200_FLUSH_AT
 #define B200_FLUSH_AT 24 // test the pending triangles as soon as 24 wait (32 per round at most): hit distances shrink earlier, +2 % over 32
 #endif
@@ -484,8 +488,13 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			else
 			{
 				const bool hit = hitPrim != 0xffffffffu;
-				a.hits[rayIdx] = make_float4( __uint_as_float( hit ? hitBary : 0u ), __uint_as_float( hit ? (SINGLE ? __float_as_uint( singleInfo.y ) : hitInst) : 0u ),
+				const float4 record = make_float4( __uint_as_float( hit ? hitBary : 0u ), __uint_as_float( hit ? (SINGLE ? __float_as_uint( singleInfo.y ) : hitInst) : 0u ),
 					__uint_as_float( hitPrim ), hit ? r.t : 1e34f );
+#if B200_STREAM_RAYS
+				__stcs( a.hits + rayIdx, record );
+#else
+				a.hits[rayIdx] = record;
+#endif
 			}
 			if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
 			finished = false;
@@ -503,7 +512,11 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				rayIdx = base + __popc( idleMask & lanemask_lt() );
 				if (rayIdx < total)
 				{
+#if B200_STREAM_RAYS
+					const float4 O4 = __ldcs( (a.hostO ? a.hostO : a.rayO) + rayIdx ), D4 = __ldcs( (a.hostO ? a.hostD : a.rayD) + rayIdx );
+#else
 					const float4 O4 = __ldg( (a.hostO ? a.hostO : a.rayO) + rayIdx ), D4 = __ldg( (a.hostO ? a.hostD : a.rayD) + rayIdx );
+#endif
 					if (a.hostO) a.stageO[rayIdx] = O4, a.stageD[rayIdx] = D4; // host-buffer wave: the upload happens here
 					r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.tmin = O4.w;
 					r.dx = D4.x, r.dy = D4.y, r.dz = D4.z, r.t = D4.w;

@@ -1032,6 +1032,7 @@ struct FramePlan {
 	struct { float4 *rayO[2], *rayD[2], *state[2], *info[2], *hits, *conO[2], *conD[2], *conE[2], *slotS, *slotC; uint32_t tiles, capacity; } chain[MAX_CHAINS];
 	uint32_t chains, passes, maxLen, overlap, anyLight, bsdf, clearAccumulator, timedPasses;
 	int isect, smCount, shadeGrid;
+	float l2Persist;
 	// tile-sharded frame with open peers: the gather over peer memory is the tail of the frame (see enqueueFrame)
 	uint32_t gather;
 	int peerWorld, peerRank;
@@ -1065,6 +1066,8 @@ struct WavefrontState {
 	cudaEvent_t frameBegin = nullptr, frameEnd = nullptr, fork = nullptr, gatherWait = nullptr, gatherBegin = nullptr, gatherEnd = nullptr;
 	std::vector<cudaEvent_t> timers; // per (timed pass, chain, path length): extend begin, extend end, shade end, connect begin, connect end
 	int overlapConnect = 1;
+	float l2PersistApplied = 0.f;
+	const void* l2WindowNodes = nullptr;
 	// the captured frame
 	cudaStream_t captureStream = nullptr;
 	cudaGraphExec_t graphExec = nullptr;
@@ -1643,6 +1646,13 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		P.finalScale = 1.0f / (float)(w->samplesTaken + (uint32_t)w->spp);
 	}
 	memset( &stats.totalRays, 0, (char*)&stats.probedInstid - (char*)&stats.totalRays );
+	plan.l2Persist = l2Persist;
+	if (l2Persist != w->l2PersistApplied || plan.trace.nodes != w->l2WindowNodes)
+	{
+		// (the streams the wave kernels of a frame run on; part of the plan, so a change re-captures the graph)
+		for (Chain& c : w->chain) if (c.main && (applyL2Window( c.main ) || applyL2Window( c.connect ))) return 1;
+		w->l2PersistApplied = l2Persist, w->l2WindowNodes = plan.trace.nodes;
+	}
 	if (plan.passes)
 	{
 		// A frame whose plan equals the previous frame's is replayed as a graph (captured on its second appearance, so that one-off

@@ -91,9 +91,14 @@ def c1(frames):
     rc.Shutdown()
 
 
+EXTRA_SETTINGS = [a.split("=") for a in sys.argv[1:] if "=" in a and not a.startswith("--")]  # name=value applied to the C3 core
+
+
 def c3(frames, n_tris=10_000_000, gpu_build=0):
     rc = core.RenderCoreB200(0)
     rc.Setting("gpuBuild", gpu_build)
+    for k, v in EXTRA_SETTINGS:
+        rc.Setting(k, float(v))
     t0 = time.perf_counter()
     verts = scenes.triangle_soup(n_tris)
     t1 = time.perf_counter()
@@ -150,7 +155,7 @@ def c4(frames, n_inst=1000, n_tris=100_000):
 
 
 if __name__ == "__main__":
-    args = [a for a in sys.argv[1:] if not a.startswith("--") and not a.isdigit()] or ["c1", "c3", "c4"]
+    args = [a for a in sys.argv[1:] if not a.startswith("--") and not a.isdigit() and "=" not in a] or ["c1", "c3", "c4"]
     frames = int(sys.argv[sys.argv.index("--frames") + 1]) if "--frames" in sys.argv else 5
     for a in args:
         {"c1": c1, "c3": c3, "c3gpu": lambda f: c3(f, gpu_build=1), "c4": c4, "refit": refit_c2}[a](frames)
