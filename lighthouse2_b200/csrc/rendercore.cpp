@@ -128,7 +128,7 @@ RenderCore::RenderCore( int dev ) : device( dev )
 	if ((e = cudaEventCreate( &evA )) != cudaSuccess || (e = cudaEventCreate( &evB )) != cudaSuccess) { fail( "cudaEventCreate", e ); return; }
 	if ((e = fetchCounter.reserve( 256, false, 0 )) != cudaSuccess) { fail( "cudaMalloc", e ); return; }
 	buildThreads = (int)std::thread::hardware_concurrency();
-	if (buildThreads < 1) buildThreads = 1;
+	buildThreads = buildThreads < 1 ? 1 : (buildThreads > 64 ? 64 : buildThreads); // (the passes are memory-bound well before 64)
 	initOk = true;
 }
 
@@ -192,10 +192,10 @@ int RenderCore::Setting( const char* name, float value )
 // else from the vertices) + CoreTri::material (:67); what the shade stage reads via instanceTriangles[PRIMIDX]
 // in the reference (lib/rendercore_optix7/kernels/pathtracer.h:70-100)
 struct ShadeRec { float n[3]; uint32_t material; };
-static void makeShadeRecords( const float* vertexData, const uint32_t T, const void* coreTris, std::vector<ShadeRec>& shade )
+static void makeShadeRecords( const float* vertexData, const uint32_t T, const void* coreTris, std::vector<ShadeRec>& shade, int threads )
 {
 	shade.resize( T );
-	for (uint32_t i = 0; i < T; i++)
+	ParallelRange( threads, T, 65536, [&]( size_t begin, size_t end ) { for (size_t i = begin; i < end; i++)
 	{
 		const float *p0 = vertexData + (size_t)i * 12, *p1 = p0 + 4, *p2 = p0 + 8;
 		const float e1[3] = { p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2] }, e2[3] = { p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2] };
@@ -210,7 +210,7 @@ static void makeShadeRecords( const float* vertexData, const uint32_t T, const v
 			if (N[0] * N[0] + N[1] * N[1] + N[2] * N[2] > 0.5f) shade[i].n[0] = N[0], shade[i].n[1] = N[1], shade[i].n[2] = N[2];
 			memcpy( &shade[i].material, ct + 28, 4 );
 		}
-	}
+	} } );
 }
 
 // per-triangle shading attributes of a mesh from its CoreTris (common_classes.h:57-91): vertex normals vN0/vN1/vN2 (offsets 32/48/64) for
@@ -231,7 +231,7 @@ int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 	{
 		// CoreTri (common_classes.h:62-83): u0..2 @0, v0..2 @16, vN0 @32, vN1 @48, vN2 @64, T @80, B @96, alpha @112 (w = LOD)
 		std::vector<float> at( (size_t)m.triCount * TRI_ATTR_STRIDE * 4, 0.f );
-		for (uint32_t i = 0; i < m.triCount; i++)
+		ParallelRange( buildThreads, m.triCount, 65536, [&]( size_t begin, size_t end ) { for (size_t i = begin; i < end; i++)
 		{
 			const char* ct = (const char*)coreTris + (size_t)i * 176;
 			float* o = &at[(size_t)i * TRI_ATTR_STRIDE * 4];
@@ -244,7 +244,7 @@ int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 			memcpy( &ltri, ct + 12, 4 );
 			ltri = ltri >= 0 ? ltri + 1 : 0;
 			memcpy( o + 25, &ltri, 4 );
-		}
+		} } );
 		e = cudaMemcpyAsync( dst, at.data(), at.size() * 4, cudaMemcpyHostToDevice, stream );
 		if (e == cudaSuccess) e = cudaStreamSynchronize( stream ); // the staging vector dies here
 	}
@@ -321,12 +321,13 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	const double t0 = nowMs();
 	const uint32_t T = (uint32_t)triangleCount;
 	if (gpuBuild && T >= 64) return buildOnDevice( meshIdx, vertexData, T, coreTris, t0 );
+	// (the passes over all triangles of a large mesh -- here, in the builder and in the staging below -- run on buildThreads threads)
 	std::vector<Aabb> boxes( T );
-	for (uint32_t i = 0; i < T; i++)
+	ParallelRange( buildThreads, T, 65536, [&]( size_t begin, size_t end ) { for (size_t i = begin; i < end; i++)
 	{
 		boxes[i].reset();
 		for (int k = 0; k < 3; k++) boxes[i].grow( vertexData + (size_t)(3 * i + k) * 4 );
-	}
+	} } );
 	WideBvh bvh;
 	// on-disk cache of the host-built tree (bvh_cache.cpp), keyed by the vertex data; B200_BVH_CACHE names the directory
 	static const char* cacheEnv = getenv( "B200_BVH_CACHE" );
@@ -351,16 +352,16 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	for (WideNode& n : bvh.nodes) n.childBase += m.nodeBase, n.primBase += m.triBase; // absolute pool indices
 	if ((uint64_t)m.triBase + T + 32 >= (1ull << 27)) return fail( "SetGeometry: more than 2^27 triangles in one core (queue entries carry 27-bit triangle indices)" );
 	std::vector<WideTri> tris( T );
-	for (uint32_t j = 0; j < T; j++)
+	ParallelRange( buildThreads, T, 65536, [&]( size_t begin, size_t end ) { for (size_t j = begin; j < end; j++)
 	{
 		const uint32_t prim = bvh.primOrder[j];
 		const float *p0 = vertexData + (size_t)prim * 12, *p1 = p0 + 4, *p2 = p0 + 8;
 		WideTri& t = tris[j];
 		t.prim = prim, t.pad1 = t.pad2 = 0;
 		for (int a = 0; a < 3; a++) t.v0[a] = p0[a], t.e1[a] = p1[a] - p0[a], t.e2[a] = p2[a] - p0[a];
-	}
+	} } );
 	std::vector<ShadeRec> shade;
-	makeShadeRecords( vertexData, T, coreTris, shade );
+	makeShadeRecords( vertexData, T, coreTris, shade, buildThreads );
 	cudaError_t e;
 	if ((e = nodePool.reserve( (size_t)(m.nodeBase + m.nodeCount + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
 	if ((e = triPool.reserve( (size_t)(m.triBase + T + 1) * 48, true, stream )) != cudaSuccess) return fail( "triangle pool", e );

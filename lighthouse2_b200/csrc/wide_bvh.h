@@ -6,8 +6,11 @@
 // relative to the node's own origin/power-of-two scale (80-byte nodes, five 16-byte loads), a
 // triangle buffer in leaf order, and an instance table in top-level leaf order.
 #pragma once
+#include <algorithm>
+#include <atomic>
 #include <cstdint>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace b200 {
@@ -68,6 +71,25 @@ struct Aabb {
 // (SetGeometry / UpdateToplevel / the cache loader) instead of letting the kernels write past the stack.
 constexpr int TRAVERSAL_STACK_ENTRIES = 48;
 constexpr int MAX_TREE_LEVELS = TRAVERSAL_STACK_ENTRIES - 8; // one mesh's tree; leaves room for a top level of four levels
+
+// Host loops over large meshes (builder passes, staging of triangle / shading records): fn( item ) for every item in [0, items), handed
+// out one at a time to at most `threads` threads, the calling one included.  `perThread` = how many items make a thread worth starting.
+template <class F> void ParallelFor( int threads, size_t items, F&& fn, size_t perThread = 1 )
+{
+	const size_t use = std::min<size_t>( threads > 1 ? (size_t)threads : 1, items / (perThread ? perThread : 1) );
+	if (use <= 1) { for (size_t i = 0; i < items; i++) fn( i ); return; }
+	std::atomic<size_t> next{ 0 };
+	auto body = [&] { for (size_t i; (i = next.fetch_add( 1 )) < items;) fn( i ); };
+	std::vector<std::thread> pool;
+	for (size_t t = 1; t < use; t++) pool.emplace_back( body );
+	body();
+	for (std::thread& t : pool) t.join();
+}
+// the same over [0, n) in ranges of `grain`: fn( begin, end )
+template <class F> void ParallelRange( int threads, size_t n, size_t grain, F&& fn )
+{
+	ParallelFor( threads, (n + grain - 1) / grain, [&]( size_t g ) { fn( g * grain, std::min( n, (g + 1) * grain ) ); }, 2 );
+}
 
 // Result of a host build (BLAS over triangles or TLAS over instance boxes).
 struct WideBvh {
