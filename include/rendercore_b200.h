@@ -119,7 +119,7 @@ B200_API int b200_set_material_colors( b200_core* c, const float* rgba, int coun
  * 2 HASALPHA), 0 | extinction rgb (1 - CoreMaterial::absorption), diffuse texture index or -1 | uv scale xy, uv offset xy */
 B200_API int b200_set_material_table( b200_core* c, const float* props16, int count );
 /* CoreAPI_Base::SetTextures (core_api_base.h:98): CoreTexDesc[count] in the host layout (40 bytes, common_classes.h:246-269); call before
- * the materials.  ARGB32 maps are copied (MIP levels included) and sampled as the diffuse map of the materials that name them */
+ * the materials.  ARGB32 / NRM32 / ARGB128 (HDR, float4 texels) maps are copied (MIP levels included) and sampled by the materials that name them */
 /* Blue-noise sampling (BLUENOISE, rendercore_optix7/core_settings.h:29): the table the reference's cores build in Init
  * (rendercore_optix7/rendercore.cpp:258-267; 5 * 65536 words: Sobol sequence, scrambling tile at 65536, ranking tile at 3 * 65536).
  * With a table set, the first 256 samples of a pixel draw the pixel / lens position and the BSDF sample from it and the first two
@@ -178,6 +178,7 @@ typedef struct b200_stats {
 	float hostEnqueueMs, hostWaitMs, hostTotalMs; /* host clock of the last b200_render: until everything was enqueued, waiting for the device, whole call */
 	float gatherMs;                     /* of the last b200_render that ended with the peer-memory gather: device time from this rank's arrival to the end of the
 	                                       second arrival (waiting for the slowest rank + pull + finalize); 0 when the frame had no gather */
+	uint32_t argb32TexelCount, argb128TexelCount, nrm32TexelCount; /* CoreStats (core_api_base.h:38-40): texels of the last b200_set_textures per storage */
 } b200_stats;
 B200_API int b200_get_stats( b200_core* c, b200_stats* out );
 B200_API int b200_set_probe( b200_core* c, int x, int y );

@@ -48,6 +48,7 @@ class Stats(C.Structure):
         ("kernelLaunches", C.c_uint32), ("lastTraceMs", C.c_float), ("bvhCacheHits", C.c_uint32),
         ("gatherKernelMs", C.c_float), ("frameGraphLaunches", C.c_uint32), ("frameChains", C.c_uint32), ("framePasses", C.c_uint32),
         ("hostEnqueueMs", C.c_float), ("hostWaitMs", C.c_float), ("hostTotalMs", C.c_float), ("gatherMs", C.c_float),
+        ("argb32TexelCount", C.c_uint32), ("argb128TexelCount", C.c_uint32), ("nrm32TexelCount", C.c_uint32),
     ]
 
     def as_dict(self):
@@ -419,16 +420,17 @@ class RenderCoreB200:
 
     def SetTextures(self, textures):
         """CoreAPI_Base::SetTextures.  textures: list of (width, height, texels uint32[pixelCount] ARGB32 with the MIP levels
-        behind each other, mip_levels[, storage]); storage 0 = ARGB32 (default), 2 = NRM32 (normal maps).  Builds the
-        CoreTexDesc array (40 bytes each, common_classes.h:246-269)."""
+        behind each other, mip_levels[, storage]); storage 0 = ARGB32 (default), 2 = NRM32 (normal maps), 1 = ARGB128 (HDR: texels are
+        float32[pixelCount, 4]).  Builds the CoreTexDesc array (40 bytes each, common_classes.h:246-269)."""
         descs = np.zeros((len(textures), 10), np.uint32)
         keep = []
         for i, tex in enumerate(textures):
             w, h, texels, mips = tex[:4]
-            t = np.ascontiguousarray(texels, np.uint32)
+            storage = tex[4] if len(tex) > 4 else 0
+            t = np.ascontiguousarray(texels, np.float32).reshape(-1, 4) if storage == 1 else np.ascontiguousarray(texels, np.uint32)
             keep.append(t)
             descs[i, 0:2] = np.array([t.ctypes.data], np.uint64).view(np.uint32)
-            descs[i, 2], descs[i, 3], descs[i, 5], descs[i, 7], descs[i, 8] = w, h, len(t), mips, (tex[4] if len(tex) > 4 else 0)
+            descs[i, 2], descs[i, 3], descs[i, 5], descs[i, 7], descs[i, 8] = w, h, len(t), mips, storage
         self._chk(self.lib.b200_set_textures(self.h, descs.ctypes.data if len(textures) else None, len(textures)))
 
     def SetAccumulatorBuffer(self, dptr: int):

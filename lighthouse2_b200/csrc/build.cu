@@ -22,6 +22,10 @@
 #ifndef B200_DP_COLLAPSE
 #define B200_DP_COLLAPSE 1 // children of a wide node from the SAH dynamic programme (1) or by opening the largest child (0)
 #endif
+#ifndef B200_GROUP_COLLAPSE
+#define B200_GROUP_COLLAPSE 1 // 1: eight lanes per wide node (collapseNodeGroup); 0: one thread per node (collapseNode, the first version, kept for A/B)
+#endif
+#define B200_USE_GROUP_COLLAPSE (B200_GROUP_COLLAPSE && B200_DP_COLLAPSE)
 #include <vector>
 
 namespace b200 {
@@ -226,6 +230,7 @@ __device__ __forceinline__ void refBox( const CollapseArgs& a, const uint32_t re
 }
 
 // 5. one level of the top-down collapse: thread w builds wide node `levelBegin + w` from its binary node
+#if !B200_USE_GROUP_COLLAPSE
 __device__ void collapseNode( const CollapseArgs& a, const uint32_t w )
 {
 	const uint32_t root = a.wideToBinary[w];
@@ -355,11 +360,158 @@ __device__ void collapseNode( const CollapseArgs& a, const uint32_t w )
 	np[1] = make_uint4( a.nodeBase + childBase, a.triBase + primBase, metaLo, metaHi );
 	np[2] = np[3] = np[4] = make_uint4( 0, 0, 0, 0 );
 }
+#endif
+
+// The same step by EIGHT LANES per wide node: lane i of the group holds child i in registers, what collapseNode keeps in dynamically
+// indexed local arrays (lo / hi / score / stack: hundreds of dependent local-memory accesses per node, which is what the one-block
+// top-level build spent two thirds of its time in -- its first levels have 1, 8, ... nodes and as many busy threads).  Same forest walk,
+// same sums in the same order, same strict-< scan order of the greedy slot assignment: the nodes are bit for bit those of
+// collapseNode (tests/test_parity_gpu.py holds the device-built top level against the host builder's).
+// Called by all eight lanes of a group together; `gmask` names them in the warp, `sub` = lane within the group.
+__device__ void collapseNodeGroup( const CollapseArgs& a, const uint32_t w, const uint32_t sub, const uint32_t gmask )
+{
+	const uint32_t gbase = (threadIdx.x & 31u) - sub;
+	const uint32_t root = a.wideToBinary[w];
+	// the forest the plan chose (see collapseNode); the walk is the same in all eight lanes, stack entry j lives in lane j, child n goes to lane n
+	uint32_t myRef = 0, myBits = 0, stRef = 0, stAllow = 0;
+	uint32_t n = 0, sp = 2;
+	{
+		const uint32_t k8 = (__float_as_uint( a.planHi[root].w ) >> 18) & 7u;
+		if (sub == 0) stRef = a.childR[root], stAllow = 8 - k8;
+		if (sub == 1) stRef = a.childL[root], stAllow = k8;
+	}
+	while (sp)
+	{
+		--sp;
+		const uint32_t m = __shfl_sync( gmask, stRef, gbase + sp );
+		uint32_t allow = __shfl_sync( gmask, stAllow, gbase + sp ), bits = 0;
+		if (!(m & LEAF))
+		{
+			bits = __float_as_uint( a.planHi[m].w );
+			while (allow > 1 && ((bits >> (3 * (allow - 2))) & 7u) == 0) allow--;
+		}
+		if ((m & LEAF) || allow == 1)
+		{
+			if (sub == n) myRef = m, myBits = bits;
+			n++;
+		}
+		else
+		{
+			const uint32_t k = (bits >> (3 * (allow - 2))) & 7u, right = a.childR[m], left = a.childL[m];
+			if (sub == sp) stRef = right, stAllow = allow - k;
+			sp++;
+			if (sub == sp) stRef = left, stAllow = k;
+			sp++;
+		}
+	}
+	const bool have = sub < n;
+	const bool inner = have && !(myRef & LEAF) && !((myBits >> 21) & 1u);
+	float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+	uint32_t cnt = 0;
+	if (have) refBox( a, myRef, lo, hi, cnt );
+	// node box: min / max over the children (any order gives the same floats)
+	float nlo[3], nhi[3];
+#pragma unroll
+	for (int c = 0; c < 3; c++)
+	{
+		nlo[c] = lo[c], nhi[c] = hi[c];
+#pragma unroll
+		for (int d = 1; d < 8; d <<= 1) nlo[c] = fminf( nlo[c], __shfl_xor_sync( gmask, nlo[c], d ) ), nhi[c] = fmaxf( nhi[c], __shfl_xor_sync( gmask, nhi[c], d ) );
+	}
+	// my child's eight signed sums, then n greedy rounds: the smallest (score, slot, child) in the scan order of collapseNode
+	float score[8];
+	{
+		float rel[3];
+#pragma unroll
+		for (int c = 0; c < 3; c++) rel[c] = 0.5f * (lo[c] + hi[c]) - 0.5f * (nlo[c] + nhi[c]);
+#pragma unroll
+		for (int s = 0; s < 8; s++)
+		{
+			float d = 0;
+#pragma unroll
+			for (int c = 0; c < 3; c++) d += ((s >> (2 - c)) & 1) ? -rel[c] : rel[c];
+			score[s] = d;
+		}
+	}
+	uint32_t freeSlots = 0xffu, mySlot = 8;
+	bool done = !have;
+	for (uint32_t k = 0; k < n; k++)
+	{
+		float best = 3.0e38f;
+		uint32_t key = 0xffu; // slot << 3 | child: the scan order among equal scores
+#pragma unroll
+		for (int s = 0; s < 8; s++) if (!done && (freeSlots & (1u << s)) && score[s] < best) best = score[s], key = ((uint32_t)s << 3) | sub;
+#pragma unroll
+		for (int d = 1; d < 8; d <<= 1)
+		{
+			const float ob = __shfl_xor_sync( gmask, best, d );
+			const uint32_t ok = __shfl_xor_sync( gmask, key, d );
+			if (ob < best || (ob == best && ok < key)) best = ob, key = ok;
+		}
+		const uint32_t bs = (key >> 3) & 7u, bi = key & 7u;
+		if (sub == bi) mySlot = bs, done = true;
+		freeSlots &= ~(1u << bs);
+	}
+	// children and primitives of this node: one claim each for the group
+	const uint32_t innerBits = (__ballot_sync( gmask, inner ) >> gbase) & 0xffu, innerCount = __popc( innerBits );
+	uint32_t leafPrims = inner ? 0u : cnt;
+#pragma unroll
+	for (int d = 1; d < 8; d <<= 1) leafPrims += __shfl_xor_sync( gmask, leafPrims, d );
+	uint32_t childBase = 0, primBase = 0;
+	if (sub == 0)
+	{
+		childBase = innerCount ? atomicAdd( a.counters, innerCount ) : 0;
+		primBase = leafPrims ? atomicAdd( a.counters + 1, leafPrims ) : 0;
+	}
+	childBase = __shfl_sync( gmask, childBase, gbase ), primBase = __shfl_sync( gmask, primBase, gbase );
+	if (childBase + innerCount > a.maxNodes) { if (sub == 0) atomicExch( a.counters + 2, 1u ); return; }
+	// place in slot order: inner children before mine, leaf primitives before mine
+	const uint32_t packed = have ? (0x80000000u | mySlot | (inner ? 8u : 0u) | (cnt << 4)) : 0u;
+	uint32_t innerBefore = 0, off = 0;
+#pragma unroll
+	for (int j = 0; j < 8; j++)
+	{
+		const uint32_t o = __shfl_sync( gmask, packed, gbase + j );
+		if ((o & 0x80000000u) && (o & 7u) < mySlot) { if (o & 8u) innerBefore++; else off += (o >> 4) & 0x07ffffffu; }
+	}
+	uint32_t imask = 0, metaLo = 0, metaHi = 0;
+	if (have)
+	{
+		uint32_t meta;
+		if (inner)
+		{
+			imask = 1u << mySlot, meta = 0x20u | (24u + mySlot);
+			a.wideToBinary[childBase + innerBefore] = myRef;
+		}
+		else
+		{
+			meta = (((1u << cnt) - 1u) << 5) | off;
+			const uint32_t first = (myRef & LEAF) ? (myRef & ~LEAF) : a.rangeFirst[myRef]; // the subtree's primitives are a contiguous run of the sorted order
+			for (uint32_t k = 0; k < cnt; k++) a.primOut[(size_t)(primBase + off + k) * a.primOutStride] = a.sortedPrim[first + k];
+		}
+		if (mySlot < 4) metaLo = meta << (8 * mySlot); else metaHi = meta << (8 * (mySlot - 4));
+	}
+#pragma unroll
+	for (int d = 1; d < 8; d <<= 1)
+		imask |= __shfl_xor_sync( gmask, imask, d ), metaLo |= __shfl_xor_sync( gmask, metaLo, d ), metaHi |= __shfl_xor_sync( gmask, metaHi, d );
+	if (sub == 0)
+	{
+		uint4* np = a.nodes + (size_t)w * 5;
+		np[0] = make_uint4( 0, 0, 0, imask << 24 );
+		np[1] = make_uint4( a.nodeBase + childBase, a.triBase + primBase, metaLo, metaHi );
+		np[2] = np[3] = np[4] = make_uint4( 0, 0, 0, 0 );
+	}
+}
 
 __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
 {
+#if B200_USE_GROUP_COLLAPSE
+	const uint32_t w = levelBegin + (blockIdx.x * blockDim.x + threadIdx.x) / 8, sub = threadIdx.x & 7u;
+	if (w < levelEnd) collapseNodeGroup( a, w, sub, 0xffu << ((threadIdx.x & 31u) - sub) );
+#else
 	const uint32_t w = levelBegin + blockIdx.x * blockDim.x + threadIdx.x;
 	if (w < levelEnd) collapseNode( a, w );
+#endif
 }
 
 
@@ -597,7 +749,11 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		uint32_t begin = 0, end = 1;
 		while (begin < end)
 		{
+#if B200_USE_GROUP_COLLAPSE
+			for (uint32_t w = begin + tid / 8; w < end; w += T / 8) collapseNodeGroup( a, w, tid & 7u, 0xffu << ((tid & 31u) - (tid & 7u)) );
+#else
 			for (uint32_t w = begin + tid; w < end; w += T) collapseNode( a, w );
+#endif
 			__syncthreads();
 			if (tid == 0) sLevel[++sLevels] = end;
 			begin = end, end = min( sCounters[0], maxNodes );
@@ -737,7 +893,7 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	uint32_t begin = 0, end = 1;
 	while (begin < end)
 	{
-		collapseKernel<<<(end - begin + 127) / 128, 128, 0, s>>>( a, begin, end );
+		collapseKernel<<<((end - begin) * (B200_USE_GROUP_COLLAPSE ? 8 : 1) + 127) / 128, 128, 0, s>>>( a, begin, end );
 		uint32_t h[3];
 		if ((e = cudaMemcpyAsync( h, counters, 12, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
 		if ((e = cudaStreamSynchronize( s )) != cudaSuccess) return done( e );

@@ -125,6 +125,7 @@ public:
 		s.deepRayCount = b.deepRayCount, s.traceTimeX = b.traceTimeX * 0.001f;
 		s.shadowTraceTime = b.shadowTraceTime * 0.001f, s.shadeTime = b.shadeTime * 0.001f;
 		s.probedInstid = b.probedInstid, s.probedTriid = b.probedTriid, s.probedDist = b.probedDist;
+		s.argb32TexelCount = b.argb32TexelCount, s.argb128TexelCount = b.argb128TexelCount, s.nrm32TexelCount = b.nrm32TexelCount;
 		return s;
 	}
 	void Init() override

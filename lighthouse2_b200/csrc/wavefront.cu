@@ -1,4 +1,4 @@
-// wavefront.cu -- the frame around the two waves: ray generation, minimal diffuse shade, fused connect, finalize.
+// wavefront.cu -- the frame around the two waves: ray generation, the shade stage, fused connect, accumulate, finalize, gather.
 //
 // Re-implements, for the B200 core, the host-driven wave loop of the reference GPU cores
 // (lib/rendercore_optix7/rendercore.cpp:621-770; Prime variant lib/RenderCore_OptixPrime_B/rendercore.cpp:463-609):
@@ -11,14 +11,14 @@
 //     with atomicAdd; the reference's `accumulator[pixelIdx] += E` is a non-atomic RMW that races for spp > 1,
 //     .optix.cu:148, connections.h:33)
 //   * output goes to a device RGBA32F buffer (no GL texture exists on this box)
-//   * the shade stage follows the reference's shadeKernel (lib/rendercore_optix7/kernels/pathtracer.h:54-240) with its
-//     Lambert BSDF (lib/sharedBSDFs/lambert.h: diffuse + pure specular reflection by roughness): area / point / spot /
-//     directional lights picked by potential contribution, MIS between NEE and emissive hits, postponed BSDF pdf,
-//     dielectric transmission (Fresnel, refraction, Beer absorption), interpolated vertex normals for SMOOTH materials,
-//     ARGB32 diffuse maps (trilinear over the MIP chain at the ray-cone LOD) with alpha pass-through, Russian roulette, HDR
-//     skydome lookup, intensity clamp.  Left out: normal / roughness / specularity / detail maps, HDR (ARGB128) maps, the
-//     consistent-normal correction, the Disney BSDF, blue-noise tables (a data file of the reference) -- every random number
-//     is the WangHash/xor32 stream
+//   * the shade stage follows the reference's shadeKernel (lib/rendercore_optix7/kernels/pathtracer.h:54-240) with either of its
+//     BSDFs -- Lambert (lib/sharedBSDFs/lambert.h) or Disney (disney.h, in disney.cuh; Setting "bsdf") --: area / point / spot /
+//     directional lights picked by potential contribution, MIS between NEE and emissive hits, postponed BSDF pdf, dielectric
+//     transmission (Fresnel, refraction, Beer absorption), interpolated vertex normals for SMOOTH materials, the maps of
+//     material_shared.h:100-170 (diffuse trilinear over the MIP chain at the ray-cone LOD with alpha pass-through, detail, normal,
+//     detail normal, roughness) from ARGB32 / NRM32 / ARGB128 texels, Russian roulette, HDR skydome lookup, intensity clamp,
+//     blue-noise tables supplied by the host (SetBlueNoise), else the WangHash / xor32 stream.  Left out: the specularity map
+//     (uploaded but never sampled by the reference either) and the consistent-normal correction
 // Pixels can be sharded over several cores/GPUs by interleaved 32x8 tiles (Setting shardIndex/shardCount) or by sample
 // (Setting sampleOffset); per-path random streams depend only on (pixel, sample, bounce), so any sharding gives the same
 // image and the accumulators of all shards simply add up.
@@ -468,6 +468,12 @@ __device__ __forceinline__ float4 TexelToFloat4( const uint32_t t )
 	const float r = 1.0f / 256.0f;
 	return make_float4( (float)(t & 255u) * r, (float)((t >> 8) & 255u) * r, (float)((t >> 16) & 255u) * r, (float)(t >> 24) * r );
 }
+// The texel pool.  ARGB32 / NRM32 textures sit in it as one word per texel; an ARGB128 (HDR) texture as four floats per texel
+// at a 16-byte aligned place, its offset counted in float4s and marked by bit 31 (SetTextures).  The reference keeps three pools
+// (rendercore.cpp:434-505) and its FetchTexel takes the storage as an argument (sampling_shared.h:35-36) -- which none of its callers
+// passes as ARGB128 (material_shared.h:121-169, sampling_shared.h:218-259), so there a material that names an HDR texture reads the
+// argb32 pool at the HDR texture's offset; here it gets the HDR texels.
+constexpr uint32_t TEXEL_HDR = 0x80000000u;
 __device__ float4 FetchTexel( const uint32_t* __restrict__ texels, const float tu, const float tv, const uint32_t o, const int w, const int h )
 {
 	const float tcx = fmaxf( tu + 1000, 0.0f ) * (float)w - 0.5f, tcy = fmaxf( tv + 1000, 0.0f ) * (float)h - 0.5f;
@@ -475,8 +481,18 @@ __device__ float4 FetchTexel( const uint32_t* __restrict__ texels, const float t
 	const float fu = tcx - floorf( tcx ), fv = tcy - floorf( tcy );
 	const float w0 = (1 - fu) * (1 - fv), w1 = fu * (1 - fv), w2 = (1 - fu) * fv, w3 = 1 - (w0 + w1 + w2);
 	const int iu1 = (iu + 1) % w, iv1 = (iv + 1) % h;
-	const float4 p0 = TexelToFloat4( __ldg( texels + o + iu + iv * w ) ), p1 = TexelToFloat4( __ldg( texels + o + iu1 + iv * w ) );
-	const float4 p2 = TexelToFloat4( __ldg( texels + o + iu + iv1 * w ) ), p3 = TexelToFloat4( __ldg( texels + o + iu1 + iv1 * w ) );
+	const int i0 = iu + iv * w, i1 = iu1 + iv * w, i2 = iu + iv1 * w, i3 = iu1 + iv1 * w;
+	float4 p0, p1, p2, p3;
+	if (o & TEXEL_HDR)
+	{
+		const float4* __restrict__ hdr = reinterpret_cast<const float4*>( texels ) + (o & ~TEXEL_HDR);
+		p0 = __ldg( hdr + i0 ), p1 = __ldg( hdr + i1 ), p2 = __ldg( hdr + i2 ), p3 = __ldg( hdr + i3 );
+	}
+	else
+	{
+		const uint32_t* __restrict__ ldr = texels + o;
+		p0 = TexelToFloat4( __ldg( ldr + i0 ) ), p1 = TexelToFloat4( __ldg( ldr + i1 ) ), p2 = TexelToFloat4( __ldg( ldr + i2 ) ), p3 = TexelToFloat4( __ldg( ldr + i3 ) );
+	}
 	return make_float4( p0.x * w0 + p1.x * w1 + p2.x * w2 + p3.x * w3, p0.y * w0 + p1.y * w1 + p2.y * w2 + p3.y * w3,
 		p0.z * w0 + p1.z * w1 + p2.z * w2 + p3.z * w3, p0.w * w0 + p1.w * w1 + p2.w * w2 + p3.w * w3 );
 }
@@ -1235,12 +1251,14 @@ int RenderCore::SetSkyData( const float* rgb, int width, int height )
 // CoreAPI_Base::SetTextures (core_api_base.h:98): CoreTexDesc[count] in the host layout (common_classes.h:246-269, 40 bytes: data
 // pointer, width, height, flags, pixelCount, firstPixel, MIPlevels, storage).  ARGB32 textures are copied, MIP levels included, into
 // one texel pool (what SyncStorageType does, lib/rendercore_optix7/rendercore.cpp:447-505), NRM32 normal maps beside them (the
-// reference keeps a second pool with the same texel format); ARGB128 (HDR) textures are not sampled here.
+// reference keeps a second pool with the same texel format) and ARGB128 (HDR) textures as float4 texels at 16-byte aligned places of the
+// same pool (see LoadTexel).
 int RenderCore::SetTextures( const void* coreTexDescs, int count )
 {
 	WavefrontState* w = state( wf );
 	if (count < 0 || (count > 0 && !coreTexDescs)) return fail( "SetTextures: bad arguments" );
 	w->textures.assign( (size_t)count, WavefrontState::TextureRec{ 0, 0, 0, 0, false } );
+	stats.argb32TexelCount = stats.argb128TexelCount = stats.nrm32TexelCount = 0;
 	std::vector<uint32_t> pool;
 	for (int i = 0; i < count; i++)
 	{
@@ -1248,14 +1266,28 @@ int RenderCore::SetTextures( const void* coreTexDescs, int count )
 		const uint32_t* data;
 		uint32_t width, height, pixelCount, mips, storage;
 		memcpy( &data, d, 8 ), memcpy( &width, d + 8, 4 ), memcpy( &height, d + 12, 4 ), memcpy( &pixelCount, d + 20, 4 ), memcpy( &mips, d + 28, 4 ), memcpy( &storage, d + 32, 4 );
-		if ((storage != 0 /* ARGB32 */ && storage != 2 /* NRM32: the same four bytes per texel */) || !data || !width || !height) continue;
+		if (storage > 2 || !data || !width || !height) continue;
+		const bool hdr = storage == 1; /* ARGB128: float4 texels; ARGB32 (0) and NRM32 (2): four bytes per texel */
 		// the levels actually present: level k has (w >> k)(h >> k) texels
 		uint32_t have = 0, need = 0, ww = width, hh = height;
 		while (have < (mips ? mips : 1) && ww && hh && need + ww * hh <= pixelCount) need += ww * hh, ww >>= 1, hh >>= 1, have++;
 		if (!have) return fail( "SetTextures: pixelCount smaller than width * height" );
-		w->textures[i] = { (uint32_t)pool.size(), width, height, have, true };
-		pool.insert( pool.end(), data, data + need );
+		if (hdr)
+		{
+			pool.resize( (pool.size() + 3) & ~(size_t)3, 0u );
+			if (pool.size() / 4 + need >= TEXEL_HDR) return fail( "SetTextures: texel pool too large" );
+			w->textures[i] = { (uint32_t)(pool.size() / 4) | TEXEL_HDR, width, height, have, true };
+			pool.insert( pool.end(), data, data + (size_t)need * 4 );
+			stats.argb128TexelCount += need;
+		}
+		else
+		{
+			w->textures[i] = { (uint32_t)pool.size(), width, height, have, true };
+			pool.insert( pool.end(), data, data + need );
+			(storage == 0 ? stats.argb32TexelCount : stats.nrm32TexelCount) += need;
+		}
 	}
+	if (pool.size() >= TEXEL_HDR) return fail( "SetTextures: texel pool too large" );
 	cudaError_t e;
 	if ((e = w->texels.reserve( pool.size() * 4 + 64, false, stream )) != cudaSuccess) return fail( "texel pool", e );
 	if (!pool.empty() && (e = cudaMemcpyAsync( w->texels.ptr, pool.data(), pool.size() * 4, cudaMemcpyHostToDevice, stream )) != cudaSuccess) return fail( "texel upload", e );

@@ -267,6 +267,48 @@ def test_lit_frame_matches_cpu_restatement(cap, roulette):
     rc.Shutdown()
 
 
+def test_hdr_texture_matches_cpu_restatement():
+    """ARGB128 (HDR) storage (common_classes.h:240-269; SyncStorageType, rendercore_optix7/rendercore.cpp:434-505): the floor's diffuse
+    map as float4 texels, values above 1 and an alpha channel that cuts holes, beside an ARGB32 texture in the same pool (so that
+    the 16-byte alignment of the HDR texels is exercised).  The sampler is FetchTexel's ARGB128 branch (sampling_shared.h:55-59)."""
+    sc = _lit_scene()
+    rng = np.random.default_rng(5)
+    hdr = np.empty((16 * 16, 4), np.float32)
+    hdr[:, :3] = rng.uniform(0.05, 2.5, (256, 3))
+    hdr[:, 3] = np.where(rng.uniform(size=256) < 0.2, 0.0, 1.0)
+    # texture 0: three odd ARGB32 texels (never sampled: keeps the HDR texture off a 16-byte boundary before padding); texture 1: the HDR map
+    sc["textures"] = [(3, 1, np.array([0xff102030, 0xff405060, 0xff708090], np.uint32), 1), (16, 16, hdr, 1, 1)]
+    sc["materials"] = sc["materials"].copy()
+    sc["materials"][sc["materials"][:, 11] == 0, 11] = 1
+    w, h = 160, 90
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    rc = _lit_core(sc, w, h, spp=2)
+    st0 = rc.GetCoreStats()
+    assert (st0["argb32TexelCount"], st0["argb128TexelCount"], st0["nrm32TexelCount"]) == (3, 256, 0)
+    rc.Render(view, converge=1)
+    acc, st = rc.ReadAccumulator(), rc.GetCoreStats()
+    rc.Shutdown()
+    port = cases.load_oracle(dict(sc["case"], rays=None), "port")
+    stats = {}
+    ref = wavefront_ref.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
+                               lights=wavefront_ref.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
+                               materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
+                               uvs=sc["uvs"], lods=sc["lods"], textures=sc["textures"], max_path_length=5, spp=2, stats=stats)
+    mean = float(ref[..., :3].mean())
+    rmse = float(np.sqrt(np.mean((acc[..., :3] - ref[..., :3]) ** 2)))
+    big = np.abs(acc[..., :3] - ref[..., :3]).max(axis=2) > 0.02 * mean
+    print("hdr-mapped image: mean", mean, "rmse", rmse, "pixels off by >2%:", int(big.sum()), "rays", st["totalExtensionRays"], sum(stats["ext"]))
+    assert rmse <= 1e-4 * mean and big.sum() == 0
+    assert st["totalExtensionRays"] == sum(stats["ext"]) and st["totalShadowRays"] == sum(stats["shadow"])
+    # and the map is really sampled: the ARGB32 version of the scene gives another image
+    base = _lit_scene()
+    rc = _lit_core(base, w, h, spp=2)
+    rc.Render(view, converge=1)
+    ldr = rc.ReadAccumulator()
+    rc.Shutdown()
+    assert np.abs(ldr[..., :3] - acc[..., :3]).mean() > 0.01 * mean
+
+
 def test_blue_noise_sampling_matches_cpu_restatement():
     """BLUENOISE of the reference's cores (pathtracer.h:168-222, .optix.cu:66-79): with a table set, the first 256 samples
     draw the lens point and the BSDF sample from it and the first two the light sample.  The table here is synthetic (the

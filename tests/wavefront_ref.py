@@ -269,8 +269,17 @@ def sample_skydome(D, sky, sky_image):
     return out
 
 
+def decode_texels(tex):
+    """One texture (width, height, texels, mip_levels[, storage]) as float32[n, 4]: ARGB32 / NRM32 words through
+    __uchar4_to_float4 (sampling_shared.h:29-33: bytes / 256), ARGB128 (storage 1) texels as they are (:55-59)."""
+    if len(tex) > 4 and tex[4] == 1:
+        return np.asarray(tex[2], f32).reshape(-1, 4)
+    t = np.asarray(tex[2], np.uint32)
+    return np.stack([(t & 255), (t >> 8) & 255, (t >> 16) & 255, t >> 24], axis=1).astype(f32) * f32(1.0 / 256.0)
+
+
 def fetch_texel(texels, tu, tv, o, w, h):
-    """sampling_shared.h:36-76 (BILINEAR, ARGB32); o, w, h are arrays (per ray)."""
+    """sampling_shared.h:36-76 (BILINEAR); o, w, h are arrays (per ray); texels = float32[N, 4], see decode_texels."""
     tcx = (np.maximum(tu + f32(1000), f32(0)) * w.astype(f32) - f32(0.5)).astype(f32)
     tcy = (np.maximum(tv + f32(1000), f32(0)) * h.astype(f32) - f32(0.5)).astype(f32)
     iu, iv = tcx.astype(np.int64) % w, tcy.astype(np.int64) % h
@@ -280,8 +289,7 @@ def fetch_texel(texels, tu, tv, o, w, h):
     iu1, iv1 = (iu + 1) % w, (iv + 1) % h
 
     def px(x, y):
-        t = texels[o + x + y * w]
-        return np.stack([(t & 255), (t >> 8) & 255, (t >> 16) & 255, t >> 24], axis=1).astype(f32) * f32(1.0 / 256.0)
+        return texels[o + x + y * w]
     return (px(iu, iv) * w0[:, None] + px(iu1, iv) * w1[:, None] + px(iu, iv1) * w2[:, None] + px(iu1, iv1) * w3[:, None]).astype(f32)
 
 
@@ -345,7 +353,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
     point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or the float32[n, 16] table of
     b200_set_material_table; prim_materials = per mesh uint32[T] material index (default 0); vertex_normals = per mesh
     float32[T, 3, 3] or None; uvs = per mesh float32[T, 3, 2] or None, lods = per mesh float32[T] or None; textures = list of
-    (width, height, texels uint32[], mip_levels); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off).
+    (width, height, texels uint32[], mip_levels[, storage]) (storage 1: HDR, texels float32[n, 4]); sky_image = float32[h, w, 3] skydome.  Pixel-centre rays (jitter off).
     disney = oracle.DisneyRef() switches the BSDF to the reference's Disney one (Setting bsdf = 1): material_words =
     uint32[n, 4] (core.disney_words), tangents = per mesh float32[T, 3] (CoreTri::T), alphas = per mesh float32[T, 3]
     (CoreTri::alpha; consistent normal interpolation, material_shared.h:87-97).  material_maps = per material None or a dict
@@ -375,15 +383,15 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             full = np.zeros((len(materials), 16), f32)
             full[:, :4], full[:, 5], full[:, 11], full[:, 12:14] = materials, 1, -1, 1
             materials = full
-    tex_pool, tex_rec = np.zeros(1, np.uint32), []
+    tex_pool, tex_rec = np.zeros((1, 4), f32), []
     if textures:
         off = 0
         chunks = []
         for tex in textures:
             tw, th, tx, mips = tex[:4]
             tex_rec.append((off, tw, th, mips))
-            chunks.append(np.asarray(tx, np.uint32))
-            off += len(tx)
+            chunks.append(decode_texels(tex))
+            off += len(chunks[-1])
         tex_pool = np.concatenate(chunks)
     invs = [np.linalg.inv(m.astype(np.float64)).astype(f32) for m in mats]
 
