@@ -18,7 +18,7 @@
 //     material_shared.h:100-170 (diffuse trilinear over the MIP chain at the ray-cone LOD with alpha pass-through, detail, normal,
 //     detail normal, roughness) from ARGB32 / NRM32 / ARGB128 texels, Russian roulette, HDR skydome lookup, intensity clamp,
 //     blue-noise tables supplied by the host (SetBlueNoise), else the WangHash / xor32 stream.  Left out: the specularity map
-//     (uploaded but never sampled by the reference either) and the consistent-normal correction
+//     (uploaded but never sampled by the reference either); the consistent-normal correction is applied with the Disney BSDF only
 // Pixels can be sharded over several cores/GPUs by interleaved 32x8 tiles (Setting shardIndex/shardCount) or by sample
 // (Setting sampleOffset); per-path random streams depend only on (pixel, sample, bounce), so any sharding gives the same
 // image and the accumulators of all shards simply add up.
