@@ -183,6 +183,21 @@ typedef struct b200_stats {
 B200_API int b200_get_stats( b200_core* c, b200_stats* out );
 B200_API int b200_set_probe( b200_core* c, int x, int y );
 
+/* ---- the SVGF-style filter and TAA, stage by stage, on caller-owned DEVICE buffers of w * h elements (current device, default stream,
+ * synchronous).  b200_render runs the same kernels on the core's own buffers when Setting "filter" is on; these entry points are for hosts
+ * that keep the buffers themselves and for the tests, which hold every stage against the reference's kernels.  Replaces prepareFilter /
+ * applyFilter / TAApass / unsharpenTAA / finalizeNoTAA (lib/CUDA/shared_kernel_code/finalize_shared.h:178-196, 371-377, 425-431, 463-467,
+ * 481-485).  Buffers: accumulator float4[2wh] (direct plane, indirect plane), features uint4, worldPos / deltaDepth / shading / moments /
+ * A / B / C / pixels / frame float4, motion float2; prevView = pos, p1, p2, p3 of the previous frame's view pyramid (12 floats, host). */
+B200_API int b200_filter_prepare( const void* accumulator, void* features, const void* worldPos, const void* prevWorldPos, void* shading, void* motion, void* moments,
+	const void* prevMoments, const void* deltaDepth, const float* prevView, float j0, float j1, float prevj0, float prevj1, int w, int h, unsigned spp,
+	float directClamp, float indirectClamp, int camIsStationary );
+B200_API int b200_filter_reconstruct( const void* features, const void* prevWorldPos, const void* worldPos, const void* deltaDepth, const void* motion,
+	const void* moments, const void* A, const void* B, void* C, int w, int h, int phase, int lastPass );
+B200_API int b200_filter_taa( const void* pixels, const void* prevPixels, const void* motion, void* out, int w, int h ); /* out != pixels */
+B200_API int b200_filter_unsharpen( const void* pixels, void* frame, int w, int h );
+B200_API int b200_filter_finish_no_taa( const void* pixels, void* frame, int w, int h );
+
 /* the core behind CreateCore() (NULL before CreateCore): lets a headless host read frames / stats of the plugin instance */
 B200_API b200_core* b200_plugin_core( void );
 

@@ -30,6 +30,7 @@ C_ABI_SYMBOLS = [
     "b200_trace_closest_async", "b200_trace_any_async", "b200_wait",
     "b200_trace_closest_noalloc",
     "b200_peer_handle", "b200_open_peers", "b200_close_peers", "b200_gather_finalize",
+    "b200_filter_prepare", "b200_filter_reconstruct", "b200_filter_taa", "b200_filter_unsharpen", "b200_filter_finish_no_taa",
 ]
 
 
@@ -102,6 +103,9 @@ def load_library() -> C.CDLL:
         "b200_trace_closest_noalloc": ([vp, vp, vp, ip, vp], ip),
         "b200_peer_handle": ([vp, vp], ip), "b200_open_peers": ([vp, vp, ip, ip], ip), "b200_close_peers": ([vp], ip),
         "b200_gather_finalize": ([vp, C.c_uint32], ip),
+        "b200_filter_prepare": ([vp] * 9 + [vp] + [C.c_float] * 4 + [ip, ip, C.c_uint32, C.c_float, C.c_float, ip], ip),
+        "b200_filter_reconstruct": ([vp] * 9 + [ip, ip, ip, ip], ip),
+        "b200_filter_taa": ([vp, vp, vp, vp, ip, ip], ip), "b200_filter_unsharpen": ([vp, vp, ip, ip], ip), "b200_filter_finish_no_taa": ([vp, vp, ip, ip], ip),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, name)

@@ -52,6 +52,55 @@ int b200_trace_closest_device( b200_core* c, const void* dO4, const void* dD4, i
 int b200_trace_any_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dBits ) { FORWARD( c, TraceAnyDevice( dO4, dD4, n, dBits ) ) }
 int b200_read_step_counters( b200_core* c, int n, uint32_t* nodes, uint32_t* tris ) { FORWARD( c, ReadStepCounters( n, nodes, tris ) ) }
 
+// ---- the filter's stages on caller-owned DEVICE buffers (filter.cu); current device, default stream, synchronous
+static int filterDone( const char* what, cudaError_t e )
+{
+	if (e == cudaSuccess) e = cudaDeviceSynchronize();
+	if (e != cudaSuccess) { gLastError = std::string( what ) + ": " + cudaGetErrorString( e ); return 1; }
+	return 0;
+}
+static FilterFrame filterFrame( const void* accumulator, void* features, const void* worldPos, const void* prevWorldPos, const void* deltaDepth, void* shading,
+	void* motion, void* moments, const void* prevMoments, int w, int h )
+{
+	FilterFrame f;
+	f.accumulator = (const float4*)accumulator, f.features = (uint4*)features, f.worldPos = (const float4*)worldPos, f.prevWorldPos = (const float4*)prevWorldPos;
+	f.deltaDepth = (const float4*)deltaDepth, f.shading = (float4*)shading, f.motion = (float2*)motion, f.moments = (float4*)moments;
+	f.prevMoments = (const float4*)prevMoments, f.width = w, f.height = h;
+	return f;
+}
+int b200_filter_prepare( const void* accumulator, void* features, const void* worldPos, const void* prevWorldPos, void* shading, void* motion, void* moments,
+	const void* prevMoments, const void* deltaDepth, const float* prevView, float j0, float j1, float prevj0, float prevj1, int w, int h, unsigned spp,
+	float directClamp, float indirectClamp, int camIsStationary )
+{
+	if (!accumulator || !features || !worldPos || !prevWorldPos || !shading || !motion || !moments || !prevMoments || !deltaDepth || !prevView || w < 1 || h < 1 || !spp)
+	{ gLastError = "b200_filter_prepare: bad arguments"; return 1; }
+	const FilterFrame f = filterFrame( accumulator, features, worldPos, prevWorldPos, deltaDepth, shading, motion, moments, prevMoments, w, h );
+	return filterDone( "b200_filter_prepare", LaunchFilterPrepare( f, MakeFilterReprojection( prevView, h, j0, j1, prevj0, prevj1, spp, directClamp, indirectClamp, camIsStationary ), 0 ) );
+}
+int b200_filter_reconstruct( const void* features, const void* prevWorldPos, const void* worldPos, const void* deltaDepth, const void* motion, const void* moments,
+	const void* A, const void* B, void* C, int w, int h, int phase, int lastPass )
+{
+	if (!features || !prevWorldPos || !worldPos || !deltaDepth || !motion || !moments || !A || !C || (phase == 1 && !B) || w < 1 || h < 1 || phase < 1 || phase > 8)
+	{ gLastError = "b200_filter_reconstruct: bad arguments"; return 1; }
+	const FilterFrame f = filterFrame( nullptr, (void*)features, worldPos, prevWorldPos, deltaDepth, nullptr, (void*)motion, (void*)moments, nullptr, w, h );
+	return filterDone( "b200_filter_reconstruct", LaunchFilterReconstruct( f, (const float4*)A, (const float4*)B, (float4*)C, phase, lastPass, 0 ) );
+}
+int b200_filter_taa( const void* pixels, const void* prevPixels, const void* motion, void* out, int w, int h )
+{
+	if (!pixels || !prevPixels || !motion || !out || out == pixels || w < 1 || h < 1) { gLastError = "b200_filter_taa: bad arguments (out must not be pixels)"; return 1; }
+	return filterDone( "b200_filter_taa", LaunchFilterTaa( (const float4*)pixels, (const float4*)prevPixels, (const float2*)motion, (float4*)out, w, h, 0 ) );
+}
+int b200_filter_unsharpen( const void* pixels, void* frame, int w, int h )
+{
+	if (!pixels || !frame || w < 1 || h < 1) { gLastError = "b200_filter_unsharpen: bad arguments"; return 1; }
+	return filterDone( "b200_filter_unsharpen", LaunchFilterUnsharpen( (const float4*)pixels, (float4*)frame, w, h, 0 ) );
+}
+int b200_filter_finish_no_taa( const void* pixels, void* frame, int w, int h )
+{
+	if (!pixels || !frame || w < 1 || h < 1) { gLastError = "b200_filter_finish_no_taa: bad arguments"; return 1; }
+	return filterDone( "b200_filter_finish_no_taa", LaunchFilterFinishNoTaa( (const float4*)pixels, (float4*)frame, w, h, 0 ) );
+}
+
 int b200_set_target( b200_core* c, int w, int h, int spp ) { FORWARD( c, SetTarget( w, h, spp ) ) }
 int b200_set_point_light( b200_core* c, const float* p, const float* r ) { FORWARD( c, SetPointLight( p, r ) ) }
 int b200_set_sky( b200_core* c, const float* r ) { FORWARD( c, SetSky( r ) ) }

@@ -90,4 +90,33 @@ size_t TlasScratchBytes( uint32_t n );
 cudaError_t LaunchTlasBuild( const TlasInstanceInput* dInstances, uint32_t n, uint4* nodes, uint32_t nodeBase, uint32_t maxNodes, float4* instRecs, float4* instShade,
 	uint32_t* info, void* scratch, float primCost, cudaStream_t s );
 
+// ---- SVGF-style filter + TAA (filter.cu; lib/CUDA/shared_kernel_code/finalize_shared.h:102-483) -------------------------------------------
+// the per-pixel buffers of a filtered frame (device pointers, width * height elements; accumulator: two planes, direct then indirect)
+struct FilterFrame {
+	const float4* accumulator;
+	uint4* features;             // x: albedo 10:11:11, y: packed normal (+ specular flag), z: depth, w: history length (4 bits) | specular flags << 4 | material << 6
+	const float4* worldPos;      // xyz: first non-specular vertex, w: packed normal
+	const float4* prevWorldPos;  // ... of the previous frame
+	const float4* deltaDepth;    // zw: depth derivatives along x and y
+	float4* shading;             // out: demodulated direct + indirect light, packed (see packLight)
+	float2* motion;              // out: where the pixel was in the previous frame (+ 0.5)
+	float4* moments;             // out: luminance moments (direct, direct^2, indirect, indirect^2)
+	const float4* prevMoments;
+	int width, height;
+};
+struct FilterReprojection {
+	float4 prevPos, prevE, prevRight, prevUp; // the previous camera: position (w: plane offset), view direction, scaled screen axes (w: offsets)
+	float j0, j1, prevj0, prevj1;             // TAA jitter of this and the previous frame
+	float pixelValueScale, directClamp, indirectClamp;
+	int camIsStationary;
+};
+FilterReprojection MakeFilterReprojection( const float* prevView /* pos, p1, p2, p3 */, int height, float j0, float j1, float prevj0, float prevj1, uint32_t spp,
+	float directClamp, float indirectClamp, int camIsStationary );
+cudaError_t LaunchFilterPrepare( const FilterFrame& f, const FilterReprojection& r, cudaStream_t s );
+// A -> C, one a-trous pass (phase 1, 2, 3: steps 1, 2, 4); B = the previous frame's phase-1 output (read by phase 1 only)
+cudaError_t LaunchFilterReconstruct( const FilterFrame& f, const float4* A, const float4* B, float4* C, int phase, int lastPass, cudaStream_t s );
+cudaError_t LaunchFilterTaa( const float4* pixels, const float4* prevPixels, const float2* motion, float4* out, int w, int h, cudaStream_t s ); // out != pixels
+cudaError_t LaunchFilterUnsharpen( const float4* pixels, float4* frame, int w, int h, cudaStream_t s );
+cudaError_t LaunchFilterFinishNoTaa( const float4* pixels, float4* frame, int w, int h, cudaStream_t s );
+
 } // namespace b200

@@ -327,3 +327,56 @@ class ShadeRef:
         self.lib.ref_safe_origin(len(O), self._c(O), self._c(R), self._c(N), float(eps), out)
         return out
 
+
+
+FILTER_REF_SO = os.path.join(HERE, "_ref", "liboracle_filter_ref.so")
+
+
+def have_filter_ref() -> bool:
+    return os.path.exists(FILTER_REF_SO)
+
+
+class FilterRef:
+    """The reference's own SVGF-style filter and TAA kernels (lib/CUDA/shared_kernel_code/finalize_shared.h:102-483), compiled in
+    place by nvcc (oracle/ref_filter_driver.cu).  CUDA code: usable on a GPU box only.  Every argument that names a buffer is a DEVICE
+    pointer (int); the calls synchronise."""
+
+    def __init__(self):
+        if not have_filter_ref():
+            if os.path.isdir("/root/reference"):
+                build()
+            if not have_filter_ref():
+                raise RuntimeError("oracle/_ref/liboracle_filter_ref.so is missing and /root/reference is not here to build it")
+        lib = C.CDLL(FILTER_REF_SO)
+        vp, ip, fl, u = C.c_void_p, C.c_int, C.c_float, C.c_uint
+        lib.ref_prepare_filter.argtypes = [vp] * 9 + [_f] + [fl] * 4 + [ip, ip, u, fl, fl, ip]
+        lib.ref_apply_filter.argtypes = [vp] * 9 + [u, u, ip, u]
+        lib.ref_taa_pass.argtypes = [vp] * 5 + [u, u]
+        lib.ref_unsharpen_taa.argtypes = [vp, vp, u, u]
+        lib.ref_finalize_no_taa.argtypes = [vp, vp, u, u]
+        for fn in (lib.ref_prepare_filter, lib.ref_apply_filter, lib.ref_taa_pass, lib.ref_unsharpen_taa, lib.ref_finalize_no_taa):
+            fn.restype = ip
+        self.lib = lib
+
+    @staticmethod
+    def _ok(code, what):
+        if code:
+            raise RuntimeError("reference filter: %s failed" % what)
+
+    def prepare(self, accumulator, features, world_pos, prev_world_pos, shading, motion, moments, prev_moments, delta_depth, prev_view, j, prev_j, w, h, spp,
+                clamp_direct, clamp_indirect, stationary):
+        view = np.ascontiguousarray(prev_view, np.float32).reshape(12)
+        self._ok(self.lib.ref_prepare_filter(accumulator, features, world_pos, prev_world_pos, shading, motion, moments, prev_moments, delta_depth, view,
+                                             j[0], j[1], prev_j[0], prev_j[1], w, h, spp, clamp_direct, clamp_indirect, int(stationary)), "prepareFilter")
+
+    def apply(self, features, prev_world_pos, world_pos, delta_depth, motion, moments, A, B, Cout, w, h, phase, last):
+        self._ok(self.lib.ref_apply_filter(features, prev_world_pos, world_pos, delta_depth, motion, moments, A, B, Cout, w, h, phase, int(last)), "applyFilter")
+
+    def taa(self, pixels, prev_pixels, world_pos, prev_world_pos, motion, w, h):
+        self._ok(self.lib.ref_taa_pass(pixels, prev_pixels, world_pos, prev_world_pos, motion, w, h), "TAApass")
+
+    def unsharpen(self, pixels, out, w, h):
+        self._ok(self.lib.ref_unsharpen_taa(pixels, out, w, h), "unsharpenTAA")
+
+    def finalize_no_taa(self, pixels, out, w, h):
+        self._ok(self.lib.ref_finalize_no_taa(pixels, out, w, h), "finalizeNoTAA")
