@@ -179,9 +179,19 @@ typedef struct b200_stats {
 	float gatherMs;                     /* of the last b200_render that ended with the peer-memory gather: device time from this rank's arrival to the end of the
 	                                       second arrival (waiting for the slowest rank + pull + finalize); 0 when the frame had no gather */
 	uint32_t argb32TexelCount, argb128TexelCount, nrm32TexelCount; /* CoreStats (core_api_base.h:38-40): texels of the last b200_set_textures per storage */
+	float filterTime;                   /* ms, the reconstruction filter + TAA of the last b200_render (Setting filterCore); 0 when it did not run */
 } b200_stats;
 B200_API int b200_get_stats( b200_core* c, b200_stats* out );
 B200_API int b200_set_probe( b200_core* c, int x, int y );
+
+/* Filter mode.  Setting "filterCore" = 1 makes the core render as the reference's lib/RenderCore_Optix7Filter does: the keys "filter", "TAA",
+ * "clampDirect", "clampIndirect" (sent to every core every frame, rendersystem.cpp:231-236) are then honoured (rendercore.cpp:648-670) -- paths
+ * stop after one diffuse bounce, the accumulator restarts every frame, the first sample writes per-pixel features and the frame goes through
+ * the reconstruction filter and TAA (filter.cu).  With filterCore = 0 (default) the four keys are accepted and ignored, as lib/rendercore_optix7
+ * does.  b200_read_filter_buffer: the per-pixel buffers of the last filtered frame -- which = 0 features (uint4: albedo 10:11:11, packed normal,
+ * depth bits, history | specular << 4 | material << 6), 1 world position + packed normal, 2 depth derivatives (zw), 3 indirect accumulator
+ * plane, 4 motion vectors (float2), 5 luminance moments, 6 first reconstruction pass (packed), 7 TAA history; 16 bytes per pixel, motion 8. */
+B200_API int b200_read_filter_buffer( b200_core* c, int which, void* dst );
 
 /* ---- the SVGF-style filter and TAA, stage by stage, on caller-owned DEVICE buffers of w * h elements (current device, default stream,
  * synchronous).  b200_render runs the same kernels on the core's own buffers when Setting "filter" is on; these entry points are for hosts

@@ -30,7 +30,7 @@ C_ABI_SYMBOLS = [
     "b200_trace_closest_async", "b200_trace_any_async", "b200_wait",
     "b200_trace_closest_noalloc",
     "b200_peer_handle", "b200_open_peers", "b200_close_peers", "b200_gather_finalize",
-    "b200_filter_prepare", "b200_filter_reconstruct", "b200_filter_taa", "b200_filter_unsharpen", "b200_filter_finish_no_taa",
+    "b200_read_filter_buffer", "b200_filter_prepare", "b200_filter_reconstruct", "b200_filter_taa", "b200_filter_unsharpen", "b200_filter_finish_no_taa",
 ]
 
 
@@ -49,7 +49,7 @@ class Stats(C.Structure):
         ("kernelLaunches", C.c_uint32), ("lastTraceMs", C.c_float), ("bvhCacheHits", C.c_uint32),
         ("gatherKernelMs", C.c_float), ("frameGraphLaunches", C.c_uint32), ("frameChains", C.c_uint32), ("framePasses", C.c_uint32),
         ("hostEnqueueMs", C.c_float), ("hostWaitMs", C.c_float), ("hostTotalMs", C.c_float), ("gatherMs", C.c_float),
-        ("argb32TexelCount", C.c_uint32), ("argb128TexelCount", C.c_uint32), ("nrm32TexelCount", C.c_uint32),
+        ("argb32TexelCount", C.c_uint32), ("argb128TexelCount", C.c_uint32), ("nrm32TexelCount", C.c_uint32), ("filterTime", C.c_float),
     ]
 
     def as_dict(self):
@@ -103,6 +103,7 @@ def load_library() -> C.CDLL:
         "b200_trace_closest_noalloc": ([vp, vp, vp, ip, vp], ip),
         "b200_peer_handle": ([vp, vp], ip), "b200_open_peers": ([vp, vp, ip, ip], ip), "b200_close_peers": ([vp], ip),
         "b200_gather_finalize": ([vp, C.c_uint32], ip),
+        "b200_read_filter_buffer": ([vp, ip, vp], ip),
         "b200_filter_prepare": ([vp] * 9 + [vp] + [C.c_float] * 4 + [ip, ip, C.c_uint32, C.c_float, C.c_float, ip], ip),
         "b200_filter_reconstruct": ([vp] * 9 + [ip, ip, ip, ip], ip),
         "b200_filter_taa": ([vp, vp, vp, vp, ip, ip], ip), "b200_filter_unsharpen": ([vp, vp, ip, ip], ip), "b200_filter_finish_no_taa": ([vp, vp, ip, ip], ip),
@@ -473,6 +474,12 @@ class RenderCoreB200:
     def ReadAccumulator(self) -> np.ndarray:
         out = np.empty((self.height, self.width, 4), np.float32)
         self._chk(self.lib.b200_read_accumulator(self.h, out.ctypes.data))
+        return out
+
+    def ReadFilterBuffer(self, which: int) -> np.ndarray:
+        """A per-pixel buffer of the last filtered frame (Setting filterCore): see b200_read_filter_buffer."""
+        out = np.empty((self.height, self.width, 2 if which == 4 else 4), np.uint32 if which == 0 else np.float32)
+        self._chk(self.lib.b200_read_filter_buffer(self.h, which, out.ctypes.data))
         return out
 
     def ReadFrame(self) -> np.ndarray:

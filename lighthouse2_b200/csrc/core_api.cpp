@@ -125,6 +125,7 @@ int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, i
 int b200_render( b200_core* c, const void* view, int converge ) { FORWARD( c, Render( view, converge ) ) }
 int b200_read_accumulator( b200_core* c, float* dst ) { FORWARD( c, ReadAccumulator( dst ) ) }
 int b200_read_frame( b200_core* c, float* dst ) { FORWARD( c, ReadFrame( dst ) ) }
+int b200_read_filter_buffer( b200_core* c, int which, void* dst ) { FORWARD( c, ReadFilterBuffer( which, dst ) ) }
 void* b200_device_accumulator( b200_core* c ) { return (c && c->rc) ? c->rc->DeviceAccumulator() : nullptr; }
 int b200_get_stats( b200_core* c, b200_stats* out ) { GUARD( c ) if (!out) { gLastError = "null stats"; return 1; } c->rc->GetStats( out ); return 0; }
 int b200_set_probe( b200_core* c, int x, int y ) { FORWARD( c, SetProbe( x, y ) ) }
@@ -174,6 +175,7 @@ public:
 		s.deepRayCount = b.deepRayCount, s.traceTimeX = b.traceTimeX * 0.001f;
 		s.shadowTraceTime = b.shadowTraceTime * 0.001f, s.shadeTime = b.shadeTime * 0.001f;
 		s.probedInstid = b.probedInstid, s.probedTriid = b.probedTriid, s.probedDist = b.probedDist;
+		s.filterTime = b.filterTime * 0.001f;
 		s.argb32TexelCount = b.argb32TexelCount, s.argb128TexelCount = b.argb128TexelCount, s.nrm32TexelCount = b.nrm32TexelCount;
 		return s;
 	}

@@ -164,8 +164,7 @@ int RenderCore::Setting( const char* name, float value )
 {
 	// keys sent every frame by RenderSystem::Render (lib/RenderSystem/rendersystem.cpp:231-236)
 	if (!strcmp( name, "epsilon" )) { epsilon = value; return 0; }
-	if (!strcmp( name, "clampDirect" ) || !strcmp( name, "clampIndirect" ) || !strcmp( name, "filter" ) || !strcmp( name, "TAA" ))
-		return 0; // accepted; used by the filtering cores only (clampValue goes to the shade stage, wavefront.cu)
+	// ("clampDirect", "clampIndirect", "filter", "TAA": with the frame settings in wavefront.cu -- honoured when Setting filterCore is on)
 	// B200-specific keys
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
 	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 0.5f; return 0; }

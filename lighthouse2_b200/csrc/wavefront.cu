@@ -87,6 +87,11 @@ struct FrameParams {
 	uint32_t skyWidth, skyHeight;
 	const uint32_t* texels;    // ARGB32 texels of all textures, MIP levels behind each other (SetTextures)
 	const uint32_t* blueTable; // 5 x 65536 words in the reference's layout (SetBlueNoise); null = none.  A pass uses it when PassParams::blue is set
+	// filter mode (Setting "filter"; the reference's lib/RenderCore_Optix7Filter): what the first sample of a pixel finds at its first
+	// non-specular vertex, for the reconstruction filter (filter.cu) -- and the accumulator holds two planes, direct and indirect light
+	uint4* features;           // x: albedo 10:11:11, y: packed normal + specular flag, z: depth, w: history length | specular << 4 | material << 6; null = filter off
+	float4* worldPos;          // xyz + packed normal
+	float4* deltaDepth;        // zw: depth derivatives along x and y
 };
 struct PassParams {
 	float pos[3], p1[3], right[3], up[3]; // right = p2 - p1, up = p3 - p1
@@ -109,6 +114,7 @@ struct ChainArgs {
 	float4 *slotS, *slotC;                             // per-path contribution slots of this pass (see accumulateKernel)
 	uint32_t* counters;
 	uint32_t chain, chainTiles;                        // chainTiles: local tiles this chain owns
+	uint32_t indirectOffset;                           // filter mode: the slots of a path's indirect light (after its diffuse bounce) lie this far behind its direct ones
 };
 
 constexpr uint32_t S_SPECULAR = 1, S_BOUNCED = 2, S_VIASPECULAR = 4, S_BOUNCEDTWICE = 8; // pathtracer.h:29-32
@@ -231,7 +237,8 @@ __global__ void __launch_bounds__( 256 ) generateEyeRaysKernel( const FrameParam
 		// the first 256 samples of a pixel take their four numbers from the blue-noise table (.optix.cu:66-79)
 		const int sampleIdx = (int)(P.sampleBase + sample);
 		const bool blue = blueTable && sampleIdx < 256;
-		if (f.jitter)
+		if (f.jitter == 2) r0 = r1 = 0; // filter mode: the pixel's corner; the sub-pixel offset is in p1 (Optix7Filter/optix/.optix.cu:84-88, rendercore.cpp:733-742)
+		else if (f.jitter)
 		{
 			if (blue) r0 = BlueNoiseSampler( blueTable, x, y, sampleIdx, 0 ), r1 = BlueNoiseSampler( blueTable, x, y, sampleIdx, 1 );
 			else r0 = RandomFloat( seed ), r1 = RandomFloat( seed );
@@ -538,7 +545,24 @@ __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 #ifndef B200_SHADE_GRID
 #define B200_SHADE_GRID 2 // resident sets of CTAs per launch
 #endif
-template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200_SHADE_MIN_BLOCKS ) shadeKernel( const FrameParams f, const PassParams* __restrict__ pass, const int pathLength, const int maxPathLength,
+// filter-mode helpers: packing formats of the feature buffers (lib/CUDA/shared_kernel_code/tools_shared.h:122-183)
+__device__ __forceinline__ uint32_t PackNormal2( const V3 N )
+{
+	const uint32_t x = min( (uint32_t)((N.x + 1) * 511), 1023u ), y = min( (uint32_t)((N.y + 1) * 511), 1023u ), z = min( (uint32_t)((N.z + 1) * 511), 1023u );
+	return (x << 2) + (y << 12) + (z << 22);
+}
+__device__ __forceinline__ uint32_t HDRtoRGB32( const V3 c )
+{
+	return ((uint32_t)(1023.0f * fminf( 1.0f, c.x )) << 22) + ((uint32_t)(2047.0f * fminf( 1.0f, c.y )) << 11) + (uint32_t)(2047.0f * fminf( 1.0f, c.z ));
+}
+__device__ __forceinline__ V3 RGB32toHDR( const uint32_t c )
+{
+	return v3( (float)(c >> 22) * (1.0f / 1023.0f), (float)((c >> 11) & 2047u) * (1.0f / 2047.0f), (float)(c & 2047u) * (1.0f / 2047.0f) );
+}
+
+// FILTER: the shade stage of the reference's filtering core (lib/RenderCore_Optix7Filter/kernels/pathtracer.h): the same path tracer, plus
+// the feature buffers written by the first sample of every pixel and light split into what arrives before and after the diffuse bounce
+template <bool DISNEY, bool FILTER> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200_SHADE_MIN_BLOCKS ) shadeKernel( const FrameParams f, const PassParams* __restrict__ pass, const int pathLength, const int maxPathLength,
 	const ChainArgs c, const float4* __restrict__ shade, const float4* __restrict__ vertexNormals, const float4* __restrict__ instShade, const float4* __restrict__ materials )
 {
 	__shared__ uint32_t sWarp[2 * 4 + 2];
@@ -575,15 +599,49 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 			// touches a slot at most once and the waves are ordered: no race, fixed order.
 			const float depth = prim < 0 ? 10000.f : hit.w;
 			bool stored = false;
+			// filter mode: what a path gathers after its diffuse bounce is indirect light and goes to the second plane (pathtracer.h:93)
+			if (FILTER && (flags & S_BOUNCED)) slot += c.indirectOffset;
 			auto contribute = [&]( const V3 v ) {
 				if (pathLength == 1) c.slotS[slot] = make_float4( v.x, v.y, v.z, depth ), stored = true;
 				else { float* px = reinterpret_cast<float*>( c.slotS + slot ); atomicAdd( px, v.x ), atomicAdd( px + 1, v.y ), atomicAdd( px + 2, v.z ); }
 			};
 			if (pathLength == 1) c.slotC[slot] = make_float4( 0.f, 0.f, 0.f, 0.f );
+			if (FILTER && pathLength == 1) c.slotS[slot + c.indirectOffset] = c.slotC[slot + c.indirectOffset] = make_float4( 0.f, 0.f, 0.f, 0.f );
+			// filter mode: the feature record of the pixel, written by its first sample up to the first non-specular vertex (:96-104)
+			const bool firstHit = FILTER && !(flags & S_BOUNCED) && sampleIdxU == 0;
+			const uint32_t viaSpecular = (flags & S_VIASPECULAR) ? 1u : 0u;
+			auto packFeatures = [&]( const uint32_t albedo, const uint32_t packedNormal, const uint32_t material ) {
+				uint4* ft = f.features + pixelIdx;
+				*ft = make_uint4( albedo, packedNormal, __float_as_uint( hit.w ), (viaSpecular << 4) + (material << 6) + (ft->w & 15u) ); // (the history length stays)
+			};
+			auto depthDerivatives = [&]( const V3 P, const V3 n ) {
+				// the depth the neighbouring pixels' rays would find on the plane of this surface (:48-58; plane and camera both in world space here --
+				// the reference takes the triangle from object space, the same thing for untransformed instances)
+				const V3 pos = v3( __ldg( &pass->pos[0] ), __ldg( &pass->pos[1] ), __ldg( &pass->pos[2] ) ), p1 = v3( __ldg( &pass->p1[0] ), __ldg( &pass->p1[1] ), __ldg( &pass->p1[2] ) );
+				const V3 right = v3( __ldg( &pass->right[0] ), __ldg( &pass->right[1] ), __ldg( &pass->right[2] ) ), up = v3( __ldg( &pass->up[0] ), __ldg( &pass->up[1] ), __ldg( &pass->up[2] ) );
+				const float px = (float)(pixelIdx % f.width), py = (float)(pixelIdx / f.width), plane = dot( P - pos, n );
+				const V3 dx = normalize( (p1 + right * ((px + 0.5f + 1) * (1.0f / (float)f.width)) + up * ((py + 0.5f) * (1.0f / (float)f.height))) - pos );
+				const V3 dy = normalize( (p1 + right * ((px + 0.5f) * (1.0f / (float)f.width)) + up * ((py + 0.5f + 1) * (1.0f / (float)f.height))) - pos );
+				f.deltaDepth[pixelIdx] = make_float4( 0, 0, plane / dot( n, dx ) - hit.w, plane / dot( n, dy ) - hit.w );
+			};
+			if (firstHit && pathLength == 1)
+			{
+				f.features[pixelIdx] = make_uint4( 0, 0, __float_as_uint( 1e34f ), f.features[pixelIdx].w & 15u );
+				f.worldPos[pixelIdx] = make_float4( 0, 0, 0, 0 ), f.deltaDepth[pixelIdx] = make_float4( 0, 0, 0, 0 );
+			}
 			if (prim < 0)
 			{
 				// the path left the scene: skydome (pathtracer.h:77-84)
-				contribute( ClampAndFix( throughput * SampleSkydome( f, D ) * (1.0f / bsdfPdf), f.clampValue ) );
+				const V3 sky = ClampAndFix( throughput * SampleSkydome( f, D ) * (1.0f / bsdfPdf), f.clampValue );
+				contribute( sky );
+				if (firstHit)
+				{
+					// the path ends before a diffuse vertex: something reasonable for the filter (:115-123)
+					const uint32_t pn = PackNormal2( D * -1.0f ) + viaSpecular;
+					packFeatures( HDRtoRGB32( sky ), pn, 0 );
+					const V3 far = O + D * 50000.0f;
+					f.worldPos[pixelIdx] = make_float4( far.x, far.y, far.z, __uint_as_float( pn ) ), f.deltaDepth[pixelIdx] = make_float4( 0, 0, 0, 0 );
+				}
 			}
 			else
 			{
@@ -668,6 +726,12 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					if ((mflags & 2u) && texel.w < 0.5f)
 					{
 						// pathtracer.h:104-116: the path continues in the same direction from just behind the surface, state unchanged
+						if (firstHit && pathLength == maxPathLength) // it ends here: store something sensible, or alpha does not reproject (:143-154)
+						{
+							const uint32_t pn = PackNormal2( N ) + viaSpecular;
+							packFeatures( 0, pn, 0 );
+							f.worldPos[pixelIdx] = make_float4( I.x, I.y, I.z, __uint_as_float( pn ) );
+						}
 						if (pathLength < maxPathLength)
 						{
 							const V3 po = I + D * f.epsilon;
@@ -707,10 +771,20 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					roughness = fmaxf( 0.001f, (float)(uint32_t)(FetchMap( f.texels, materials + mat * MAT_STRIDE + 12, tu, tv ).x * 255.0f) * (1.0f / 255.0f) );
 					if (DISNEY) dd.roughness = roughness;
 				}
+				// (FILTERINGCORE, material_shared.h:172-177: no channel of the albedo may be zero, the filter divides by it)
+				if (FILTER && !(mflags & 0x80000000u)) color = v3( fmaxf( 0.05f, color.x ), fmaxf( 0.05f, color.y ), fmaxf( 0.05f, color.z ) );
 				if (mflags & 0x80000000u) {}
 				else
 				if (color.x > 1.0f || color.y > 1.0f || color.z > 1.0f)
 				{
+					if (firstHit)
+					{
+						// the path ends on a light: finish the feature record with what there is (:193-201)
+						const uint32_t pn = PackNormal2( N ) + viaSpecular;
+						packFeatures( HDRtoRGB32( color ), pn, mat );
+						f.worldPos[pixelIdx] = make_float4( I.x, I.y, I.z, __uint_as_float( pn ) );
+						depthDerivatives( I, N );
+					}
 					// the path ends on a light (pathtracer.h:120-148); lights are single sided
 					const float DdotNL = -dot( D, N );
 					if (DdotNL > 0)
@@ -741,6 +815,22 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 				{
 					if (roughness <= 0.001f || transmission > 0.999f) flags |= S_SPECULAR; else flags &= ~S_SPECULAR; // pathtracer.h:151
 					uint32_t seed = WangHash( pathIdx * 17 + __ldg( &pass->R0 ) + (uint32_t)pathLength * 91771u ); // :154; R0 changes per bounce (rendercore.cpp:716)
+					if (firstHit)
+					{
+						if (flags & S_SPECULAR) f.features[pixelIdx].x = HDRtoRGB32( color ); // a mirror: its tint, multiplied into the albedo of the first diffuse vertex behind it (:215-219)
+						else
+						{
+							// the first diffuse vertex: albedo, normal, depth, world position (:221-231).  (The reference negates the shading normal
+							// here whichever side was hit -- `flip ? -fN : fN` with flip = +-1 -- and the filter only ever compares these normals
+							// with each other; kept.)
+							V3 albedo = color;
+							if (viaSpecular) albedo = albedo * RGB32toHDR( f.features[pixelIdx].x );
+							const uint32_t pn = PackNormal2( sN * -1.0f ) + viaSpecular;
+							packFeatures( HDRtoRGB32( albedo ), pn, mat );
+							f.worldPos[pixelIdx] = make_float4( I.x, I.y, I.z, __uint_as_float( pn ) );
+							depthDerivatives( I, N );
+						}
+					}
 					const float faceDir = dot( D, N ) > 0 ? -1.f : 1.f;
 					const V3 gF = N * faceDir, sF = sN * faceDir; // geometric / shading normal on the side the ray came from
 					if (faceDir == 1) absorption = v3( 0.f, 0.f, 0.f ); // the ray travelled outside the medium (:158)
@@ -778,6 +868,13 @@ template <bool DISNEY> __global__ void __launch_bounds__( 128, DISNEY ? 4 : B200
 					}
 					// extension (:201-239)
 					const bool enough = (f.bounceCap == 1 && (flags & S_BOUNCED)) || (f.bounceCap == 2 && (flags & S_BOUNCEDTWICE));
+					if (firstHit && !enough && pathLength == maxPathLength)
+					{
+						// the depth cap ends the path before the feature record was finished for good (:289-298)
+						const uint32_t pn = PackNormal2( N ) + viaSpecular;
+						packFeatures( 0, pn, 0 );
+						f.worldPos[pixelIdx] = make_float4( I.x, I.y, I.z, __uint_as_float( pn ) );
+					}
 					if (!enough && pathLength < maxPathLength)
 					{
 						const int sampleIdx = (int)sampleIdxU, bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
@@ -915,7 +1012,7 @@ __global__ void disneyProbeKernel( const int n, const int mode, const float* __r
 // tile sharding: a tile-sharded multi-GPU frame is bit-identical to the single-GPU one at any spp.  With `frame` set the kernel also
 // writes the finalized frame (lib/CUDA/shared_kernel_code/finalize_shared.h:29-45) -- the last pass of an unsharded frame.
 __global__ void __launch_bounds__( 256 ) accumulateKernel( const FrameParams f, const PassParams* __restrict__ pass, const uint32_t chain, const uint32_t chainTiles,
-	const float4* __restrict__ slotS, const float4* __restrict__ slotC, float4* __restrict__ accumulator, float4* __restrict__ frame )
+	const float4* __restrict__ slotS, const float4* __restrict__ slotC, float4* __restrict__ accumulator, float4* __restrict__ frame, const uint32_t indirectOffset )
 {
 	const uint32_t perSample = chainTiles * TILE_PIXELS, samples = __ldg( &pass->samplesThisPass );
 	const float scale = __ldg( &pass->finalScale );
@@ -928,15 +1025,19 @@ __global__ void __launch_bounds__( 256 ) accumulateKernel( const FrameParams f, 
 		const uint32_t x = tx * TILE_W + (inTile % TILE_W), y = ty * TILE_H + inTile / TILE_W;
 		if (x >= f.width || y >= f.height) continue;
 		const uint32_t pixel = x + y * f.width;
-		float4 a = accumulator[pixel];
-		for (uint32_t s = 0; s < samples; s++)
+		for (uint32_t plane = 0; plane < (f.features ? 2u : 1u); plane++) // filter mode: direct light, then indirect (the slots indirectOffset further on)
 		{
-			const float4 S = __ldcs( slotS + (size_t)s * perSample + q ), C = __ldcs( slotC + (size_t)s * perSample + q );
-			a.x += S.x, a.y += S.y, a.z += S.z, a.w += S.w;
-			a.x += C.x, a.y += C.y, a.z += C.z;
+			const float4 *planeS = slotS + (size_t)plane * indirectOffset, *planeC = slotC + (size_t)plane * indirectOffset;
+			float4 a = accumulator[pixel + plane * f.pixelCount];
+			for (uint32_t s = 0; s < samples; s++)
+			{
+				const float4 S = __ldcs( planeS + (size_t)s * perSample + q ), C = __ldcs( planeC + (size_t)s * perSample + q );
+				a.x += S.x, a.y += S.y, a.z += S.z, a.w += S.w;
+				a.x += C.x, a.y += C.y, a.z += C.z;
+			}
+			accumulator[pixel + plane * f.pixelCount] = a;
+			if (frame && !f.features) frame[pixel] = make_float4( a.x * scale, a.y * scale, a.z * scale, 1.0f );
 		}
-		accumulator[pixel] = a;
-		if (frame) frame[pixel] = make_float4( a.x * scale, a.y * scale, a.z * scale, 1.0f );
 	}
 }
 
@@ -1038,8 +1139,17 @@ struct Chain {
 // Everything enqueueFrame reads that is not a stream or an event.  Plain data on purpose: its bytes are the key of the captured frame
 // graph -- a frame whose plan equals the previous one's replays the graph, anything else (resolution, spp, lights, a reallocated
 // buffer ...) re-enqueues.  What changes every frame without changing the plan (camera, sample numbering) is in PassParams.
+// the filter's share of a frame: this frame's reprojection constants and which of the ping-pong buffers plays which part
+struct FilterPlan {
+	FilterReprojection reprojection;
+	float4 *prevWorldPos, *shading, *prevPixels, *taaOut, *moments, *prevMoments, *filteredIn, *filteredOut;
+	float2* motion;
+	uint32_t taa;
+};
+
 struct FramePlan {
 	FrameParams f;
+	FilterPlan filter;               // used when f.features is set
 	TraceArgs trace;                 // scene pools (RenderCore::baseArgs)
 	const float4 *shadePool, *vnormPool, *instShadePool, *materials;
 	float4 *accumulator, *frame;
@@ -1079,6 +1189,18 @@ struct WavefrontState {
 	int bounceCap = 0, roulette = 1, bsdf = 0; // bsdf: 0 = Lambert + speculars, 1 = Disney principled (rendercore_optix7/kernels/bsdf.h picks one at compile time)
 	uint32_t samplesTaken = 0, frameCounter = 0;
 	int probeX = -1, probeY = -1;
+	// Filter mode.  filterCore = 1 makes the core behave as the reference's RenderCore_Optix7Filter: the keys "filter", "TAA", "clampDirect" and
+	// "clampIndirect", which the RenderSystem sends to every core every frame (rendersystem.cpp:231-236), are then honoured as that core honours
+	// them (rendercore.cpp:648-670; defaults rendercore.h:30-33).  With filterCore = 0, the default, they are accepted and ignored, as in
+	// lib/rendercore_optix7.
+	int filterCore = 0, filterOn = 1, taaOn = 1;
+	float filterClampDirect = 2.5f, filterClampIndirect = 15.0f;
+	DeviceBuffer features, worldPos[2], deltaDepth, shading[2], taaOut, motion, moments[2], filtered[2];
+	uint32_t filterPixels = 0;       // the size the filter buffers were made (and cleared) for
+	int filterFlip = 0;              // which of the pairs is "current" this frame
+	uint32_t frameCycle = 0;         // TAA jitter: four sub-pixel offsets in turn (rendercore.cpp:733-737)
+	float prevView[12] = {}, prevJ0 = 0, prevJ1 = 0;
+	cudaEvent_t filterBegin = nullptr, filterEnd = nullptr;
 	cudaEvent_t frameBegin = nullptr, frameEnd = nullptr, fork = nullptr, gatherWait = nullptr, gatherBegin = nullptr, gatherEnd = nullptr;
 	std::vector<cudaEvent_t> timers; // per (timed pass, chain, path length): extend begin, extend end, shade end, connect begin, connect end
 	int overlapConnect = 1;
@@ -1108,7 +1230,8 @@ struct WavefrontState {
 	}
 	~WavefrontState()
 	{
-		DeviceBuffer* all[] = { &counters, &passParams, &accumOwn, &frame, &materials, &lights, &skyImage, &texels, &blueNoise };
+		DeviceBuffer* all[] = { &counters, &passParams, &accumOwn, &frame, &materials, &lights, &skyImage, &texels, &blueNoise, &features, &worldPos[0], &worldPos[1],
+			&deltaDepth, &shading[0], &shading[1], &taaOut, &motion, &moments[0], &moments[1], &filtered[0], &filtered[1] };
 		closePeers();
 		dropGraph();
 		peerFlags.release();
@@ -1124,7 +1247,7 @@ struct WavefrontState {
 			if (c.connect) cudaStreamDestroy( c.connect );
 		}
 		for (cudaEvent_t e : timers) if (e) cudaEventDestroy( e );
-		for (cudaEvent_t e : { frameBegin, frameEnd, fork, gatherWait, gatherBegin, gatherEnd }) if (e) cudaEventDestroy( e );
+		for (cudaEvent_t e : { frameBegin, frameEnd, fork, gatherWait, gatherBegin, gatherEnd, filterBegin, filterEnd }) if (e) cudaEventDestroy( e );
 		if (captureStream) cudaStreamDestroy( captureStream );
 	}
 };
@@ -1154,6 +1277,11 @@ int RenderCore::SettingWavefront( const char* name, float value )
 	if (!strcmp( name, "gatherInRender" )) { w->gatherInRender = value >= 0.5f; return 0; }
 	if (!strcmp( name, "peerTimeoutMs" )) { if (!(value > 0)) return fail( "Setting peerTimeoutMs: > 0" ); w->peerTimeoutMs = value; return 0; }
 	if (!strcmp( name, "russianRoulette" )) { w->roulette = value >= 0.5f; return 0; }
+	if (!strcmp( name, "filterCore" )) { w->filterCore = value >= 0.5f; return 0; }
+	if (!strcmp( name, "filter" )) { w->filterOn = value != 0; return 0; }
+	if (!strcmp( name, "TAA" )) { w->taaOn = value != 0; return 0; }
+	if (!strcmp( name, "clampDirect" )) { w->filterClampDirect = value; return 0; }
+	if (!strcmp( name, "clampIndirect" )) { w->filterClampIndirect = value; return 0; }
 	if (!strcmp( name, "bsdf" )) { if (v < 0 || v > 1) return fail( "Setting bsdf: 0 (Lambert, lib/sharedBSDFs/lambert.h) or 1 (Disney, disney.h)" ); w->bsdf = v; return 0; }
 	if (!strcmp( name, "diffuseBounceCap" )) { if (v < 0 || v > 2) return fail( "Setting diffuseBounceCap: 0 (off), 1 or 2" ); w->bounceCap = v; return 0; }
 	if (!strcmp( name, "pathsPerPass" )) { if (value < 1024) return fail( "Setting pathsPerPass: >= 1024" ); w->pathsPerPass = (uint32_t)value; return 0; }
@@ -1443,6 +1571,13 @@ int RenderCore::SetProbe( int x, int y )
 	return 0;
 }
 
+typedef void ( *ShadeKernel )( const FrameParams, const PassParams*, const int, const int, const ChainArgs, const float4*, const float4*, const float4*, const float4* );
+static ShadeKernel pickShade( const bool disney, const bool filter )
+{
+	if (filter) return disney ? shadeKernel<true, true> : shadeKernel<false, true>;
+	return disney ? shadeKernel<true, false> : shadeKernel<false, false>;
+}
+
 // ---- one frame, enqueued ------------------------------------------------------------------------------------------------
 // Replaces the host-driven wave loop of the reference (lib/rendercore_optix7/rendercore.cpp:692-748: per bounce a launch, a counter
 // read-back and a synchronisation) by ONE enqueue of the whole frame -- all passes, all chains -- with no host involvement between
@@ -1463,7 +1598,7 @@ static cudaError_t enqueueFrame( WavefrontState& w, const FramePlan& p, cudaStre
 	if ((e = cudaMemcpyAsync( p.passDev, p.passHost, sizeof( PassParams ) * p.passes, cudaMemcpyHostToDevice, origin )) != cudaSuccess) return e;
 	if ((e = cudaMemsetAsync( p.countersDev, 0, sizeof( uint32_t ) * COUNTER_STRIDE * p.chains * p.passes, origin )) != cudaSuccess) return e;
 	if ((e = cudaMemsetAsync( p.fetchCounters + FETCH_BASE, 0, sizeof( uint32_t ) * 4 * MAX_CHAINS, origin )) != cudaSuccess) return e;
-	if (p.clearAccumulator && (e = cudaMemsetAsync( p.accumulator, 0, (size_t)p.f.pixelCount * 16, origin )) != cudaSuccess) return e;
+	if (p.clearAccumulator && (e = cudaMemsetAsync( p.accumulator, 0, (size_t)p.f.pixelCount * 16 * (p.f.features ? 2 : 1), origin )) != cudaSuccess) return e;
 	cudaEventRecordWithFlags( w.frameBegin, origin, recFlags );
 	cudaEventRecord( w.fork, origin );
 	for (uint32_t c = 0; c < p.chains; c++) cudaStreamWaitEvent( w.chain[c].main, w.fork, 0 );
@@ -1480,6 +1615,7 @@ static cudaError_t enqueueFrame( WavefrontState& w, const FramePlan& p, cudaStre
 		ChainArgs ca;
 		memset( &ca, 0, sizeof( ca ) );
 		ca.counters = counters, ca.chain = c, ca.chainTiles = pc.tiles, ca.slotS = pc.slotS, ca.slotC = pc.slotC;
+		ca.indirectOffset = p.f.features ? pc.capacity : 0;
 		ca.rayOout = pc.rayO[0], ca.rayDout = pc.rayD[0], ca.stateOut = pc.state[0], ca.infoOut = pc.info[0];
 		generateEyeRaysKernel<<<p.smCount * 4, 256, 0, s>>>( p.f, passDev, ca );
 		n++;
@@ -1501,7 +1637,7 @@ static cudaError_t enqueueFrame( WavefrontState& w, const FramePlan& p, cudaStre
 			ca.rayO = pc.rayO[in], ca.rayD = pc.rayD[in], ca.state = pc.state[in], ca.info = pc.info[in], ca.hits = pc.hits;
 			ca.rayOout = pc.rayO[out], ca.rayDout = pc.rayD[out], ca.stateOut = pc.state[out], ca.infoOut = pc.info[out];
 			ca.conO = pc.conO[con], ca.conD = pc.conD[con], ca.conE = pc.conE[con];
-			( p.bsdf ? shadeKernel<true> : shadeKernel<false> )<<<p.shadeGrid, 128, 0, s>>>( p.f, passDev, (int)len, (int)p.maxLen, ca, p.shadePool, p.vnormPool,
+			pickShade( p.bsdf != 0, p.f.features != nullptr )<<<p.shadeGrid, 128, 0, s>>>( p.f, passDev, (int)len, (int)p.maxLen, ca, p.shadePool, p.vnormPool,
 				p.instShadePool, p.materials );
 			timer( pass, c, len, 2, s );
 			n += 2;
@@ -1526,10 +1662,31 @@ static cudaError_t enqueueFrame( WavefrontState& w, const FramePlan& p, cudaStre
 		if (overlap) cudaStreamWaitEvent( s, ch.connectDone[p.maxLen], 0 ); // the connect stream is in order: the last wave's event covers them all
 		const uint32_t perSample = pc.tiles * TILE_PIXELS;
 		const uint32_t blocks = std::min( (perSample + 255u) / 256u, (uint32_t)p.smCount * 8u );
-		accumulateKernel<<<blocks, 256, 0, s>>>( p.f, passDev, c, pc.tiles, pc.slotS, pc.slotC, p.accumulator, pass + 1 == p.passes ? p.frame : nullptr );
+		accumulateKernel<<<blocks, 256, 0, s>>>( p.f, passDev, c, pc.tiles, pc.slotS, pc.slotC, p.accumulator, pass + 1 == p.passes ? p.frame : nullptr, ca.indirectOffset );
 		n++;
 	}
 	for (uint32_t c = 0; c < p.chains; c++) { cudaEventRecord( w.chain[c].done, w.chain[c].main ); cudaStreamWaitEvent( origin, w.chain[c].done, 0 ); }
+	if (p.f.features)
+	{
+		// the reconstruction filter and TAA (lib/RenderCore_Optix7Filter/rendercore.cpp:827-861) on the frame's two accumulator planes
+		const FilterPlan& fp = p.filter;
+		FilterFrame ff;
+		ff.accumulator = p.accumulator, ff.features = p.f.features, ff.worldPos = p.f.worldPos, ff.prevWorldPos = fp.prevWorldPos, ff.deltaDepth = p.f.deltaDepth;
+		ff.shading = fp.shading, ff.motion = fp.motion, ff.moments = fp.moments, ff.prevMoments = fp.prevMoments, ff.width = (int)p.f.width, ff.height = (int)p.f.height;
+		cudaEventRecordWithFlags( w.filterBegin, origin, recFlags );
+		if ((e = LaunchFilterPrepare( ff, fp.reprojection, origin )) != cudaSuccess) return e;
+		if ((e = LaunchFilterReconstruct( ff, fp.shading, fp.filteredIn, fp.filteredOut, 1, 0, origin )) != cudaSuccess) return e; // filteredIn: the previous frame's first-pass output
+		if ((e = LaunchFilterReconstruct( ff, fp.filteredOut, nullptr, fp.filteredIn, 2, 0, origin )) != cudaSuccess) return e;
+		if ((e = LaunchFilterReconstruct( ff, fp.filteredIn, nullptr, fp.shading, 3, 1, origin )) != cudaSuccess) return e;
+		if (fp.taa)
+		{
+			if ((e = LaunchFilterTaa( fp.shading, fp.prevPixels, fp.motion, fp.taaOut, ff.width, ff.height, origin )) != cudaSuccess) return e;
+			if ((e = LaunchFilterUnsharpen( fp.taaOut, p.frame, ff.width, ff.height, origin )) != cudaSuccess) return e;
+		}
+		else if ((e = LaunchFilterFinishNoTaa( fp.shading, p.frame, ff.width, ff.height, origin )) != cudaSuccess) return e;
+		cudaEventRecordWithFlags( w.filterEnd, origin, recFlags );
+		n += fp.taa ? 6 : 5;
+	}
 	if (p.gather)
 	{
 		// the exchange step of a tile-sharded frame, as the tail of the frame: arrive (everyone's tiles are accumulated), pull the foreign
@@ -1581,6 +1738,42 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	f.shardIndex = (uint32_t)w->shardIndex, f.shardCount = (uint32_t)w->shardCount, f.tileSkew = tileSkewFor( f.shardCount );
 	const uint32_t ownTiles = nTiles > f.shardIndex ? (nTiles - f.shardIndex + f.shardCount - 1) / f.shardCount : 0;
 	f.jitter = (uint32_t)w->jitter, f.materialCount = w->materialCount;
+	// ---- filter mode: the frame as lib/RenderCore_Optix7Filter renders it (rendercore.cpp:677-742): accumulator cleared every frame, paths stop
+	//      after one diffuse bounce, no Russian roulette, pinhole camera through the pixel corners of a view shifted by the TAA jitter
+	const bool filtering = w->filterCore && w->filterOn;
+	float j0 = 0, j1 = 0;
+	if (filtering)
+	{
+		if (f.shardCount != 1 || w->accumExternal) return fail( "Render: the filter needs the whole frame on one core (shardCount 1, own accumulator)" );
+		if (w->peerWorld > 0) return fail( "Render: close the peers before switching the filter on (the accumulator gets a second plane)" );
+		const size_t px = f.pixelCount;
+		if ((e = w->accumOwn.reserve( px * 32, false, stream )) != cudaSuccess) return fail( "accumulator planes", e );
+		DeviceBuffer* sixteen[] = { &w->features, &w->worldPos[0], &w->worldPos[1], &w->deltaDepth, &w->shading[0], &w->shading[1], &w->taaOut, &w->moments[0], &w->moments[1],
+			&w->filtered[0], &w->filtered[1] };
+		for (DeviceBuffer* b : sixteen) if ((e = b->reserve( px * 16, false, stream )) != cudaSuccess) return fail( "filter buffers", e );
+		if ((e = w->motion.reserve( px * 8, false, stream )) != cudaSuccess) return fail( "filter buffers", e );
+		if (w->filterPixels != f.pixelCount)
+		{
+			// a new size: no history (history length 0 in features.w, previous positions nowhere near)
+			for (DeviceBuffer* b : sixteen) if ((e = cudaMemsetAsync( b->ptr, 0, px * 16, stream )) != cudaSuccess) return fail( "filter buffers", e );
+			cudaMemsetAsync( w->motion.ptr, 0, px * 8, stream );
+			w->filterPixels = f.pixelCount, w->frameCycle = 0, w->prevJ0 = w->prevJ1 = 0;
+			memcpy( w->prevView, vp, 48 );
+		}
+		if (!w->filterBegin && ((e = cudaEventCreate( &w->filterBegin )) != cudaSuccess || (e = cudaEventCreate( &w->filterEnd )) != cudaSuccess)) return fail( "cudaEventCreate", e );
+		static const float haltonx[4] = { 0.3f, 0.7f, 0.2f, 0.8f }, haltony[4] = { 0.2f, 0.8f, 0.7f, 0.3f };
+		if (w->taaOn) j0 = haltonx[w->frameCycle], j1 = haltony[w->frameCycle];
+		w->frameCycle = (w->frameCycle + 1) & 3;
+		f.bounceCap = 1, f.roulette = 0, f.jitter = 2;
+		const int cur = w->filterFlip, old = cur ^ 1;
+		f.features = (uint4*)w->features.ptr, f.worldPos = (float4*)w->worldPos[cur].ptr, f.deltaDepth = (float4*)w->deltaDepth.ptr;
+		FilterPlan& fp = plan.filter;
+		fp.prevWorldPos = (float4*)w->worldPos[old].ptr, fp.shading = (float4*)w->shading[cur].ptr, fp.prevPixels = (float4*)w->shading[old].ptr, fp.taaOut = (float4*)w->taaOut.ptr;
+		fp.moments = (float4*)w->moments[cur].ptr, fp.prevMoments = (float4*)w->moments[old].ptr;
+		fp.filteredIn = (float4*)w->filtered[cur].ptr, fp.filteredOut = (float4*)w->filtered[old].ptr, fp.motion = (float2*)w->motion.ptr, fp.taa = w->taaOn ? 1u : 0u;
+		fp.reprojection = MakeFilterReprojection( w->prevView, (int)f.height, j0, j1, w->prevJ0, w->prevJ1, (uint32_t)w->spp, w->filterClampDirect, w->filterClampIndirect, converge == 1 ? 0 : 1 );
+		converge = 1; // (rendercore.cpp:682-688: with the filter on the accumulator starts from zero every frame)
+	}
 	f.probePixel = (w->probeX >= 0 && w->probeY >= 0 && w->probeX < w->width && w->probeY < w->height) ? w->probeX + w->probeY * w->width : -1;
 	if ((uint64_t)f.pixelCount * (uint64_t)w->spp > PATHIDX_MASK) return fail( "Render: width * height * spp exceeds 2^28 path indices" );
 	if (converge == 1) w->samplesTaken = 0;
@@ -1599,15 +1792,15 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 	plan.maxLen = (uint32_t)w->maxPathLength, plan.bsdf = (uint32_t)w->bsdf, plan.isect = (int)isect, plan.smCount = smCount;
 	// shade grid = a whole number of resident sets (the loop is grid-strided: with 8 CTAs per SM launched and 5 resident, the second,
 	// partial set ran on a 60 % full machine: shade 0.40 -> 0.36 ms per C2 frame)
-	static int shadeResident[2] = { 0, 0 };
-	if (!shadeResident[w->bsdf ? 1 : 0])
+	static int shadeResident[4] = { 0, 0, 0, 0 };
+	const int shadeKind = (w->bsdf ? 1 : 0) + (filtering ? 2 : 0);
+	if (!shadeResident[shadeKind])
 	{
 		int n = 0;
-		if (w->bsdf) cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, shadeKernel<true>, 128, 0 );
-		else cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, shadeKernel<false>, 128, 0 );
-		shadeResident[w->bsdf ? 1 : 0] = n > 0 ? n : 1;
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor( &n, pickShade( w->bsdf != 0, filtering ), 128, 0 );
+		shadeResident[shadeKind] = n > 0 ? n : 1;
 	}
-	plan.shadeGrid = smCount * shadeResident[w->bsdf ? 1 : 0] * B200_SHADE_GRID;
+	plan.shadeGrid = smCount * shadeResident[shadeKind] * B200_SHADE_GRID;
 	// buffers (grown outside the enqueue: a reallocation synchronises the device)
 	for (uint32_t c = 0; c < chains; c++)
 	{
@@ -1619,6 +1812,9 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 			for (int i = 0; ch.all( i ); i++) if ((e = ch.all( i )->reserve( (size_t)cap * 16, false, stream )) != cudaSuccess) return fail( "path buffers", e );
 			ch.capacity = cap;
 		}
+		// filter mode: a second set of contribution slots behind the first, for the indirect light
+		if (filtering && ((e = ch.slotS.reserve( (size_t)cap * 32, false, stream )) != cudaSuccess || (e = ch.slotC.reserve( (size_t)cap * 32, false, stream )) != cudaSuccess))
+			return fail( "path buffers", e );
 		auto& pc = plan.chain[c];
 		pc.tiles = tiles, pc.capacity = tiles * TILE_PIXELS * samplesPerPass;
 		for (int k = 0; k < 2; k++)
@@ -1666,6 +1862,12 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		memset( &P, 0, sizeof( P ) );
 		for (int a = 0; a < 3; a++) P.pos[a] = vp[a], P.p1[a] = vp[3 + a], P.right[a] = vp[6 + a] - vp[3 + a], P.up[a] = vp[9 + a] - vp[3 + a];
 		P.aperture = vp[12], P.spreadAngle = vp[13], P.distortion = vp[16];
+		if (filtering)
+		{
+			// jitteredView: p1 + (j0 / width) right + (j1 / height) up; no lens, no distortion (rendercore.cpp:738-746)
+			for (int a = 0; a < 3; a++) P.p1[a] = vp[3 + a] + ((j0 / (float)f.width) * P.right[a] + (j1 / (float)f.height) * P.up[a]);
+			P.aperture = 0, P.distortion = 0;
+		}
 		const uint32_t s0 = pass * samplesPerPass;
 		P.samplesThisPass = (uint32_t)w->spp - s0 < samplesPerPass ? (uint32_t)w->spp - s0 : samplesPerPass;
 		// pathIdx = pixel + sample * pixelCount must stay below 2^28 (the path word keeps 4 flag bits): the sample index wraps after `period` samples and the wrap
@@ -1723,6 +1925,17 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		if ((e = cudaStreamSynchronize( stream )) != cudaSuccess) return fail( "Render", e );
 		stats.hostWaitMs = hostMs() - stats.hostEnqueueMs;
 		cudaEventElapsedTime( &stats.renderTime, w->frameBegin, w->frameEnd );
+		stats.filterTime = 0;
+		if (filtering)
+		{
+			// what this frame leaves for the next one (rendercore.cpp:855-861, :878): the blended image as TAA history, world positions, moments and
+			// the first reconstruction pass change places with their predecessors
+			cudaEventElapsedTime( &stats.filterTime, w->filterBegin, w->filterEnd );
+			if (w->taaOn) std::swap( w->taaOut, w->shading[w->filterFlip] );
+			w->filterFlip ^= 1;
+			w->prevJ0 = j0, w->prevJ1 = j1;
+			memcpy( w->prevView, vp, 48 );
+		}
 		stats.gatherMs = stats.gatherKernelMs = 0;
 		if (plan.gather)
 		{
@@ -1902,6 +2115,35 @@ int RenderCore::ReadFrame( float* dst )
 	cudaError_t e = cudaMemcpyAsync( dst, w->frame.ptr, (size_t)w->width * w->height * 16, cudaMemcpyDeviceToHost, stream );
 	if (e == cudaSuccess) e = cudaStreamSynchronize( stream );
 	return e == cudaSuccess ? 0 : fail( "ReadFrame", e );
+}
+
+// The per-pixel buffers of the last filtered frame (feature outputs for a host that wants them, and the tests): 0 features (uint4), 1 world
+// positions, 2 depth derivatives, 3 the indirect accumulator plane, 4 motion (float2), 5 luminance moments, 6 the first reconstruction pass
+// (packed light, the next frame's history), 7 the TAA history image.  16 bytes per pixel but for the motion vectors (8).
+int RenderCore::ReadFilterBuffer( int which, void* dst )
+{
+	WavefrontState* w = wf;
+	if (!w || w->width == 0 || !w->filterPixels) return fail( "ReadFilterBuffer: no filtered frame has been rendered" );
+	if (!dst) return fail( "ReadFilterBuffer: null destination" );
+	const size_t px = (size_t)w->width * w->height;
+	const int last = w->filterFlip ^ 1; // Render flipped the pairs when the frame was done
+	const void* src = nullptr;
+	size_t bytes = px * 16;
+	switch (which)
+	{
+	case 0: src = w->features.ptr; break;
+	case 1: src = w->worldPos[last].ptr; break;
+	case 2: src = w->deltaDepth.ptr; break;
+	case 3: src = (const char*)w->accumOwn.ptr + px * 16; break;
+	case 4: src = w->motion.ptr, bytes = px * 8; break;
+	case 5: src = w->moments[last].ptr; break;
+	case 6: src = w->filtered[w->filterFlip].ptr; break; // (this frame's "filteredOut" is the next frame's "filteredIn")
+	case 7: src = w->shading[last].ptr; break;
+	default: return fail( "ReadFilterBuffer: buffers 0..7" );
+	}
+	cudaError_t e = cudaMemcpyAsync( dst, src, bytes, cudaMemcpyDeviceToHost, stream );
+	if (e == cudaSuccess) e = cudaStreamSynchronize( stream );
+	return e == cudaSuccess ? 0 : fail( "ReadFilterBuffer", e );
 }
 
 void* RenderCore::DeviceAccumulator() { return wf ? (void*)wf->accumulator() : nullptr; }

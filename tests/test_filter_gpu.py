@@ -225,3 +225,123 @@ def test_taa_and_the_two_finishes_match_the_reference_kernels(ref, lib):
         assert fn(p(want), p(out), W, H) == 0, lib.b200_last_error().decode()
         close(name, host(out), host(out_ref), float(host(out_ref).max()), share=0.0, atol_rel=1e-6)
         assert (host(out_ref)[0] == 0).all() and (host(out_ref)[:, 0] == 0).all() and host(out_ref)[1:-1, 1:-1, :3].min() > 0  # the border stays unwritten
+
+
+# ---- the filtered frame through Render() ---------------------------------------------------------------------------------------------
+def _filter_scene_core(w, h, spp, **settings):
+    import test_wavefront_gpu as twg
+    sc = twg._lit_scene()
+    rc = twg._lit_core(sc, w, h, spp=spp, filterCore=1, **settings)
+    return sc, rc
+
+
+def test_filter_mode_frame_inputs_match_the_cpu_restatement():
+    """What the shade stage hands to the filter (lib/RenderCore_Optix7Filter/kernels/pathtracer.h): direct and indirect accumulator planes
+    and the feature buffers of the first sample, against tests/wavefront_ref.py in filter mode (one diffuse bounce, no roulette, rays through
+    the pixel corners of the jittered view)."""
+    import cases
+    import wavefront_ref
+    from lighthouse2_b200 import scenes
+    w, h, spp = 160, 90, 2
+    sc, rc = _filter_scene_core(w, h, spp, TAA=1)
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    rc.Render(view, converge=0)
+    st = rc.GetCoreStats()
+    direct, indirect = rc.ReadAccumulator(), rc.ReadFilterBuffer(3)
+    feat, wpos, dd = rc.ReadFilterBuffer(0), rc.ReadFilterBuffer(1), rc.ReadFilterBuffer(2)
+    frame = rc.ReadFrame()
+    rc.Shutdown()
+    port = cases.load_oracle(dict(sc["case"], rays=None), "port")
+    out, stats = {}, {}
+    ref = wavefront_ref.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
+                               lights=wavefront_ref.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
+                               materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
+                               uvs=sc["uvs"], lods=sc["lods"], textures=sc["textures"], max_path_length=5, spp=spp, bounce_cap=1, roulette=False, stats=stats,
+                               filter_out=out, filter_jitter=(0.3, 0.2))  # the first frame's TAA jitter (rendercore.cpp:733-736)
+    mean = float(ref[..., :3].mean() + out["indirect"][..., :3].mean())
+    for name, got, want in (("direct", direct, ref), ("indirect", indirect, out["indirect"])):
+        rmse = float(np.sqrt(np.mean((got[..., :3] - want[..., :3]) ** 2)))
+        print(name, "plane: mean", float(want[..., :3].mean()), "rmse", rmse)
+        assert rmse <= 1e-4 * mean, (name, rmse, mean)
+    assert out["indirect"][..., :3].mean() > 0.02 * mean and np.allclose(direct[..., 3], ref[..., 3], rtol=1e-5)
+    assert st["totalExtensionRays"] == sum(stats["ext"]) and st["totalShadowRays"] == sum(stats["shadow"])
+    # albedo, packed normal, specular flags and material: as integers; the depth: as a float (the primary rays of the two sides differ in the last bit
+    # here and there); the history length (low four bits of w) belongs to the filter's prepare stage, which has already run
+    same = (feat[..., :2] == out["features"][..., :2]).all(axis=2) & ((feat[..., 3] >> 4) == (out["features"][..., 3] >> 4))
+    print("feature records equal: %.5f" % same.mean(), "kinds:", np.unique(feat[..., 3] >> 6).tolist(), "specular-first pixels:", int(((feat[..., 3] >> 4) & 3 != 0).sum()))
+    assert same.mean() > 0.999  # (a quantised normal or albedo component may fall on the other side of a step)
+    depth_ok = np.isclose(feat[..., 2].view(np.float32), out["features"][..., 2].view(np.float32), rtol=1e-5)
+    print("depths equal to 1e-5: %.5f" % depth_ok.mean())
+    assert depth_ok.mean() > 0.999
+    same &= depth_ok
+    assert ((feat[..., 3] >> 4) & 3 != 0).sum() > 50 and len(np.unique(feat[..., 3] >> 6)) >= 5
+    assert np.array_equal(wpos[..., 3].view(np.uint32)[same], out["world_pos"][..., 3].view(np.uint32)[same])
+    a, b = wpos[..., :3][same], out["world_pos"][..., :3][same]
+    assert (np.abs(a - b).max(axis=1) <= 1e-5 * np.linalg.norm(b, axis=1) + 1e-3).all()  # (a miss stores a point 50000 units away)
+    ok = same & np.isfinite(out["delta_depth"]).all(axis=2)
+    dd_ok = np.isclose(dd[..., 2:], out["delta_depth"][..., 2:], rtol=1e-3, atol=1e-4).all(axis=2)[ok]
+    print("depth derivatives equal to 1e-3: %.5f" % dd_ok.mean(), "non-zero: %.3f" % (dd[..., 2] != 0).mean())
+    assert dd_ok.mean() > 0.995 and (dd[..., 2] != 0).mean() > 0.1  # (most of this view is sky)
+    assert np.isfinite(frame[1:-1, 1:-1, :3]).all() and frame[1:-1, 1:-1, :3].mean() > 0.01 and st["filterTime"] > 0
+
+
+@pytest.mark.parametrize("taa", [1, 0])
+def test_filtered_frames_follow_the_reference_pipeline(ref, taa):
+    """Three frames with a moving camera through Render() with the filter on; after each, the reference's host sequence
+    (lib/RenderCore_Optix7Filter/rendercore.cpp:827-861: prepare, three passes, TAA + unsharp mask or the plain finish, the swaps) is replayed
+    with the reference's kernels on the frame's own inputs (accumulator planes and feature buffers read back from the core) and must give the
+    frame the core produced."""
+    from lighthouse2_b200 import scenes
+    w, h, spp = 160, 96, 2
+    sc, rc = _filter_scene_core(w, h, spp, TAA=taa, clampDirect=2.5, clampIndirect=15.0)
+    p = lambda t: t.data_ptr()
+    z4 = lambda: torch.zeros(h, w, 4, device="cuda")
+    prev_world, prev_moments, history, prev_pixels = z4(), z4(), z4(), z4()
+    hx, hy = (0.3, 0.7, 0.2, 0.8), (0.2, 0.8, 0.7, 0.3)
+    prev_view, prev_j = None, (0.0, 0.0)
+    for k in range(3):
+        cam = dict(scenes.C1_CAMERA)
+        cam["pos"] = tuple(np.asarray(cam["pos"], np.float32) + np.array([0.04 * k, 0.01 * k, 0.0], np.float32))
+        view = scenes.view_pyramid(width=w, height=h, **cam)
+        rc.Render(view, converge=1 if k == 0 else 0)
+        frame = rc.ReadFrame()
+        acc = np.stack([rc.ReadAccumulator(), rc.ReadFilterBuffer(3)])
+        feat_after, wpos, dd = rc.ReadFilterBuffer(0), rc.ReadFilterBuffer(1), rc.ReadFilterBuffer(2)
+        vnow = np.array([view["pos"], view["p1"], view["p2"], view["p3"]], np.float32)
+        if prev_view is None:
+            prev_view = vnow
+        j = (hx[k], hy[k]) if taa else (0.0, 0.0)
+        # the feature buffer as it was BEFORE prepare: the history length is what the reference's own prepare left last frame
+        feat_in = feat_after.copy()
+        feat_in[..., 3] = (feat_in[..., 3] & ~np.uint32(15)) | (hist_len if k else np.zeros((h, w), np.uint32))
+        d_feat, d_acc, d_world, d_dd = dev(feat_in), dev(acc), dev(wpos), dev(dd)
+        shading, motion, moments, f_out, f_in2 = z4(), torch.zeros(h, w, 2, device="cuda"), z4(), z4(), z4()
+        ref.prepare(p(d_acc), p(d_feat), p(d_world), p(prev_world), p(shading), p(motion), p(moments), p(prev_moments), p(d_dd), prev_view, j, prev_j, w, h, spp, 2.5, 15.0, k != 0)
+        hist_len = host(d_feat, np.uint32)[..., 3] & np.uint32(15)
+        assert np.array_equal(hist_len, feat_after[..., 3] & np.uint32(15)) or (hist_len == (feat_after[..., 3] & 15)).mean() > 0.998
+        ref.apply(p(d_feat), p(prev_world), p(d_world), p(d_dd), p(motion), p(moments), p(shading), p(history), p(f_out), w, h, 1, 0)
+        ref.apply(p(d_feat), p(prev_world), p(d_world), p(d_dd), p(motion), p(moments), p(f_out), p(history), p(f_in2), w, h, 2, 0)
+        ref.apply(p(d_feat), p(prev_world), p(d_world), p(d_dd), p(motion), p(moments), p(f_in2), p(history), p(shading), w, h, 3, 1)
+        want = z4()
+        if taa:
+            # (the reference blends in place, with a race on its 3x3 window: its result is one of many; the core's own blend is checked against
+            # it in test_taa_...; here the core's TAA history stands in so that the pipeline around it is held to the strict bar)
+            blended = dev(rc.ReadFilterBuffer(7))
+            ref.unsharpen(p(blended), p(want), w, h)
+            prev_pixels = blended
+        else:
+            ref.finalize_no_taa(p(shading), p(want), w, h)
+            prev_pixels = shading
+        close("frame %d (TAA %d)" % (k, taa), frame, host(want), float(max(host(want)[..., :3].max(), 1e-3)), share=0.004)
+        packed_close("first reconstruction pass %d" % k, rc.ReadFilterBuffer(6), host(f_out), share=0.004)
+        if taa and k:
+            # the blend itself: the core's history image against the reference's racy in-place result on the same inputs
+            racy = shading.clone()
+            ref.taa(p(racy), p(last_blended), p(d_world), p(prev_world), p(motion), w, h)
+            diff = np.abs(host(racy) - host(blended)).max(axis=2)
+            print("TAA blend, frame %d: pixels equal to 1e-4: %.4f" % (k, (diff <= 1e-4).mean()))
+            assert (diff <= 1e-4).mean() > 0.8
+        last_blended = prev_pixels
+        prev_world, prev_moments, history, prev_view, prev_j = d_world, moments, f_out, vnow, j
+        assert frame[1:-1, 1:-1, :3].mean() > 0.01
+    rc.Shutdown()

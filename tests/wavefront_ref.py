@@ -347,7 +347,8 @@ def clamp_and_fix(c, clamp):
 def render(oracle, meshes, instances, view, width, height, light=None, lights=None, sky=(0, 0, 0), sky_image=None,
            materials=None, prim_materials=None, vertex_normals=None, uvs=None, lods=None, textures=None, spread_angle=0.01,
            max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True, nthreads=8, stats=None,
-           disney=None, material_words=None, tangents=None, alphas=None, blue_noise=None, material_maps=None, bitangents=None):
+           disney=None, material_words=None, tangents=None, alphas=None, blue_noise=None, material_maps=None, bitangents=None,
+           filter_out=None, filter_jitter=(0.0, 0.0)):
     """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
     meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
     point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or the float32[n, 16] table of
@@ -358,11 +359,45 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
     uint32[n, 4] (core.disney_words), tangents = per mesh float32[T, 3] (CoreTri::T), alphas = per mesh float32[T, 3]
     (CoreTri::alpha; consistent normal interpolation, material_shared.h:87-97).  material_maps = per material None or a dict
     with "detail" / "normals" / "detail_normals" / "roughness_map" -> dict(texture, scale, uvscale, uvoffset)
-    (material_shared.h:120-169), bitangents = per mesh float32[T, 3] (CoreTri::B, for the normal maps)."""
+    (material_shared.h:120-169), bitangents = per mesh float32[T, 3] (CoreTri::B, for the normal maps).
+    filter_out = {}: the frame as the reference's filtering core renders it (lib/RenderCore_Optix7Filter/kernels/pathtracer.h;
+    pass bounce_cap=1, roulette=False): rays through the pixel CORNERS of the view shifted by filter_jitter pixels, no lens; light that
+    arrives after the diffuse bounce goes to a second accumulator; the first sample writes the feature buffers.  Filled with
+    "indirect" float32[h, w, 4], "features" uint32[h, w, 4] (history bits zero), "world_pos" float32[h, w, 4], "delta_depth" float32[h, w, 4]."""
     npx = width * height
     acc = np.zeros((npx, 4), np.float64)
+    filt = filter_out is not None
+    acc2 = np.zeros((npx, 4), np.float64)
+    feat = np.zeros((npx, 4), np.uint32)
+    wpos, ddep = np.zeros((npx, 4), f32), np.zeros((npx, 4), f32)
     pos, p1 = view["pos"].astype(f32), view["p1"].astype(f32)
     right, up = (view["p2"] - view["p1"]).astype(f32), (view["p3"] - view["p1"]).astype(f32)
+    if filt:
+        p1 = (p1 + ((f32(filter_jitter[0]) / f32(width)) * right + (f32(filter_jitter[1]) / f32(height)) * up)).astype(f32)
+
+    def pack_normal2(n):
+        q = [np.minimum(((n[:, k] + f32(1)) * f32(511)).astype(np.int64), 1023).astype(np.uint32) for k in range(3)]
+        return (q[0] << np.uint32(2)) + (q[1] << np.uint32(12)) + (q[2] << np.uint32(22))
+
+    def hdr_to_rgb32(c):
+        c = np.minimum(f32(1), c.astype(f32))
+        return ((f32(1023) * c[:, 0]).astype(np.uint32) << np.uint32(22)) + ((f32(2047) * c[:, 1]).astype(np.uint32) << np.uint32(11)) + (f32(2047) * c[:, 2]).astype(np.uint32)
+
+    def rgb32_to_hdr(c):
+        return np.stack([(c >> np.uint32(22)).astype(f32) * f32(1.0 / 1023.0), ((c >> np.uint32(11)) & np.uint32(2047)).astype(f32) * f32(1.0 / 2047.0),
+                         (c & np.uint32(2047)).astype(f32) * f32(1.0 / 2047.0)], axis=1).astype(f32)
+
+    def store_features(px, albedo, pn, t, via, mat_id, Iw=None, Nw=None):
+        feat[px, 0], feat[px, 1], feat[px, 2], feat[px, 3] = albedo, pn, t.astype(f32).view(np.uint32), (via << np.uint32(4)) + (np.asarray(mat_id).astype(np.uint32) << np.uint32(6))
+        if Iw is not None:
+            wpos[px, :3], wpos[px, 3] = Iw, pn.view(f32)
+        if Nw is not None:  # depth derivatives: the neighbouring pixels' rays on the plane of this surface (pathtracer.h:48-58)
+            fx, fy = (px % width).astype(f32), (px // width).astype(f32)
+            plane = dot((Iw - pos[None]).astype(f32), Nw)
+            dx = normalize(((p1[None] + right[None] * ((fx + f32(1.5)) * f32(1.0 / width))[:, None]).astype(f32) + up[None] * ((fy + f32(0.5)) * f32(1.0 / height))[:, None] - pos[None]).astype(f32))
+            dy = normalize(((p1[None] + right[None] * ((fx + f32(0.5)) * f32(1.0 / width))[:, None]).astype(f32) + up[None] * ((fy + f32(1.5)) * f32(1.0 / height))[:, None] - pos[None]).astype(f32))
+            with np.errstate(all="ignore"):
+                ddep[px, 2], ddep[px, 3] = (plane / dot(Nw, dx) - t).astype(f32), (plane / dot(Nw, dy) - t).astype(f32)
     clamp = f32(clamp)
     if lights is None:
         lights = Lights()
@@ -395,8 +430,12 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
         tex_pool = np.concatenate(chunks)
     invs = [np.linalg.inv(m.astype(np.float64)).astype(f32) for m in mats]
 
-    def add(px, c):
-        np.add.at(acc, (px, slice(0, 3)), c.astype(np.float64))
+    def add(px, c, indirect=None):
+        if indirect is None or not filt:
+            np.add.at(acc, (px, slice(0, 3)), c.astype(np.float64))
+        else:
+            np.add.at(acc, (px[~indirect], slice(0, 3)), c[~indirect].astype(np.float64))
+            np.add.at(acc2, (px[indirect], slice(0, 3)), c[indirect].astype(np.float64))
 
     for s in range(spp):
         sample = sample_offset + s
@@ -407,6 +446,10 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
         u, v = (x + f32(0.5)) / f32(width), (y + f32(0.5)) / f32(height)
         O = np.broadcast_to(pos, (npx, 3)).astype(f32).copy()
         aperture, distortion = f32(view.get("aperture", 0.0)), f32(view.get("distortion", 0.0))
+        if filt:  # Optix7Filter/optix/.optix.cu:84-88
+            u, v, aperture, distortion = x / f32(width), y / f32(height), f32(0), f32(0)
+            if s == 0:
+                feat[:, 2] = f32(1e34).view(np.uint32)
         if aperture > 0:  # RandomPointOnLens (rendercore_optix7/optix/.optix.cu:51-64); jitter is off, so the lens takes the first two numbers
             seed = wang_hash(path_idx + R0)
             if blue_noise is not None and sample < 256:
@@ -446,13 +489,24 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             miss = prim < 0
             if length == 1:
                 np.add.at(acc, (px, 3), np.where(miss, 10000.0, t.astype(np.float64)))
+            bounced = (flags & S_BOUNCED) != 0      # as the wave starts: which accumulator plane its light goes to (pathtracer.h:93)
+            first = np.full(len(O), filt and s == 0) & ~bounced
+            via = ((flags & S_VIASPECULAR) != 0).astype(np.uint32)
             with np.errstate(all="ignore"):
-                add(px[miss], clamp_and_fix((T[miss] * sample_skydome(D[miss], sky, sky_image) * (f32(1) / pdf_prev[miss])[:, None]).astype(f32), clamp))
+                sky_c = clamp_and_fix((T[miss] * sample_skydome(D[miss], sky, sky_image) * (f32(1) / pdf_prev[miss])[:, None]).astype(f32), clamp)
+                add(px[miss], sky_c, bounced[miss])
+            fm = first[miss]
+            if fm.any():  # the path ends before a diffuse vertex (:115-123)
+                Dm, Om = D[miss][fm], O[miss][fm]
+                store_features(px[miss][fm], hdr_to_rgb32(sky_c[fm]), pack_normal2((Dm * f32(-1)).astype(f32)) + via[miss][fm], np.full(int(fm.sum()), 1e34, f32), via[miss][fm], 0,
+                               (Om + f32(50000) * Dm).astype(f32))
+                ddep[px[miss][fm]] = 0
             h = ~miss
             if not h.any():
                 break
             O, D, T, t, prim, inst, path_idx, px = O[h], D[h], T[h], t[h], prim[h], inst[h], path_idx[h], px[h]
             pdf_prev, flags, lastN = pdf_prev[h], flags[h], lastN[h]
+            bounced, first, via = bounced[h], first[h], via[h]
             n = len(O)
             N = np.empty_like(O)
             sN = np.empty_like(O)
@@ -599,8 +653,14 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                 Tpt = T[pt].copy()
                 Tpt[~np.isfinite(Tpt.sum(axis=1))] = 0
                 carry = ((I[pt] + D[pt] * EPS).astype(f32), D[pt], Tpt, pdf_prev[pt], flags[pt], lastN[pt], path_idx[pt])
+            if filt and passthrough.any() and length == max_path_length:  # it ends here: store something sensible (:143-154)
+                q = np.nonzero(passthrough & first)[0]
+                store_features(px[q], 0, pack_normal2(N[q]) + via[q], t[q], via[q], 0, I[q])
+            if filt:  # FILTERINGCORE (material_shared.h:172-177)
+                color = np.maximum(f32(0.05), color).astype(f32)
             if passthrough.any():
                 kp = ~passthrough
+                bounced, first, via, mat = bounced[kp], first[kp], via[kp], mat[kp]
                 O, D, T, t, prim, inst, path_idx, px, N, sN, I, color, rough = (a[kp] for a in (O, D, T, t, prim, inst, path_idx, px, N, sN, I, color, rough))
                 words, base_color, tang = words[kp], base_color[kp], tang[kp]
                 pdf_prev, flags, lastN, transmission, eta, absorption = (a[kp] for a in (pdf_prev, flags, lastN, transmission, eta, absorption))
@@ -626,7 +686,10 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                     c = np.where(mis[:, None], cm, c)
                 c = clamp_and_fix(c, clamp)
                 front = ddn > 0
-                add(px[e][front], c[front])
+                add(px[e][front], c[front], bounced[e][front])
+                q = e[first[e]]
+                if len(q):  # the path ends on a light (:193-201)
+                    store_features(px[q], hdr_to_rgb32(color[q]), pack_normal2(N[q]) + via[q], t[q], via[q], mat[q], I[q], N[q])
             keep = ~emissive
             if not keep.any():
                 if carry is None:
@@ -637,8 +700,18 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             sN, transmission, eta, absorption = sN[keep], transmission[keep], eta[keep], absorption[keep]
             words, base_color, tang = words[keep], base_color[keep], tang[keep]
             pdf_prev, flags, lastN = pdf_prev[keep], flags[keep], lastN[keep]
+            bounced, first, via, mat = bounced[keep], first[keep], via[keep], mat[keep]
             n = len(O)
             flags = np.where((rough <= f32(0.001)) | (transmission > f32(0.999)), flags | S_SPECULAR, flags & ~np.uint32(S_SPECULAR)).astype(np.uint32)
+            if first.any():  # :211-232
+                spec_now = (flags & S_SPECULAR) != 0
+                q = np.nonzero(first & spec_now)[0]
+                feat[px[q], 0] = hdr_to_rgb32(color[q])
+                q = np.nonzero(first & ~spec_now)[0]
+                albedo = color[q].copy()
+                vq = via[q] != 0
+                albedo[vq] = (albedo[vq] * rgb32_to_hdr(feat[px[q][vq], 0])).astype(f32)
+                store_features(px[q], hdr_to_rgb32(albedo), pack_normal2((sN[q] * f32(-1)).astype(f32)) + via[q], t[q], via[q], mat[q], I[q], N[q])
             seed = wang_hash(path_idx * np.uint32(17) + R0 + np.uint32(length) * np.uint32(91771))
             face = np.where(dot(D, N) > 0, f32(-1), f32(1))
             gF = (N * face[:, None]).astype(f32)   # geometric normal on the side the ray came from
@@ -680,10 +753,13 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                         stats.setdefault("shadow", []).append(int(ok.sum()))
                     ts, _, _ = oracle.trace(So, L[ok], nthreads=nthreads)
                     vis = ~(ts < tmax)
-                    add(px[q][ok][vis], E[ok][vis])
+                    add(px[q][ok][vis], E[ok][vis], bounced[q][ok][vis])
             # ---- extension (pathtracer.h:201-239, SampleBSDF of lambert.h with TRANSMISSION = 0)
             enough = ((bounce_cap == 1) & ((flags & S_BOUNCED) != 0)) | ((bounce_cap == 2) & ((flags & S_BOUNCEDTWICE) != 0))
             if length == max_path_length:
+                q = np.nonzero(first & ~enough)[0]
+                if len(q):  # the depth cap ends the path before the feature record was finished (:289-298)
+                    store_features(px[q], 0, pack_normal2(N[q]) + via[q], t[q], via[q], 0, I[q])
                 break
             if blue_noise is not None and sample < 256:  # pathtracer.h:212-217
                 r3 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 6 + 4 * length)
@@ -713,4 +789,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             O, D, T, pdf_prev, flags, lastN, path_idx = newO[alive], R[alive], newT[alive], new_pdf[alive], flags[alive], fN[alive], path_idx[alive]
             if carry is not None:
                 O, D, T, pdf_prev, flags, lastN, path_idx = (np.concatenate([a, b]) for a, b in zip((O, D, T, pdf_prev, flags, lastN, path_idx), carry))
+    if filt:
+        filter_out.update(indirect=acc2.reshape(height, width, 4).astype(f32), features=feat.reshape(height, width, 4), world_pos=wpos.reshape(height, width, 4),
+                          delta_depth=ddep.reshape(height, width, 4))
     return acc.reshape(height, width, 4).astype(f32)
