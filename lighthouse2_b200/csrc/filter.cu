@@ -252,12 +252,17 @@ __global__ void __launch_bounds__( 64, 6 ) reconstructKernel( const FilterFrame 
 			const uint4 tapFeature = f.features[tap];
 			const float wDist = (float)(uu * uu + vv * vv) * (-1.0f / 7.5f);
 			const F3 tapDirect = directOf( light ), tapIndirect = indirectOf( light );
+			// normal edge stop.  (powf as in the reference, not seven squarings: on flat regions every tap carries the same quantised light and the
+			// weighted mean lands exactly on a step of the 5:11 packing -- a last-bit change of a weight then moves 12 % of the channels by one step.
+			// Measured: the squarings save 0.2 of 1.1 ms at 1080p; the bit-equal output was kept.)
 			float wNormal = powf( fmaxf( 0.0f, dot( unpackNormal( tapFeature.y ), localNormal ) ), 128 );
 			// depth: the error against the plane through the pixel; not too strict, or curved surfaces break up
 			const float expected = localDepth + ddx * (float)(uu * step) + ddy * (float)(vv * step);
 			const float wDepth = fabsf( expected - __uint_as_float( tapFeature.z ) ) / fmaxf( 0.00001f, (0.5f + phase * 0.5f) * fabsf( expected - localDepth ) );
-			// albedo similarity, other materials all but excluded (the product is formed in double, as the reference's literal makes it)
-			wNormal = (float)((double)wNormal * ((tapFeature.w >> 4) != localMaterial ? 0.0001 : (double)dot( localColor, unpackAlbedo( tapFeature.x ) )));
+			// albedo similarity, other materials all but excluded.  (The reference's `? 0.0001 : dot` is a double expression: the product of two
+			// floats formed in double and rounded back is the float product, so only the constant's branch needs the double multiply.)
+			if ((tapFeature.w >> 4) != localMaterial) wNormal = (float)((double)wNormal * 0.0001);
+			else wNormal *= dot( localColor, unpackAlbedo( tapFeature.x ) );
 			float wd = wNormal * __expf( fabsf( localDirect - luminance( tapDirect ) ) * kDirect + wDist - wDepth );
 			float wi = wNormal * __expf( fabsf( localIndirect - luminance( tapIndirect ) ) * kIndirect + wDist - wDepth );
 			if (!isfinite( wd )) wd = 0;
