@@ -197,7 +197,17 @@ public:
 		// headless: only width/height are read (no GL object exists on this box)
 		CHK( SetTarget( (int)target->width, (int)target->height, (int)spp ) );
 	}
-	void Setting( const char* name, float value ) override { gCore->Setting( name, value ); /* unknown keys are ignored like the reference cores do */ }
+	void Setting( const char* name, float value ) override
+	{
+		// unknown keys are ignored, as the reference cores ignore them (rendercore_optix7/rendercore.cpp:597-615); a KNOWN key with a value it cannot take
+		// is reported -- the method is void and the RenderSystem sends its keys every frame, so: on stderr, the first time each
+		if (gCore->Setting( name, value ) && gCore->Error().rfind( "Setting: unknown key", 0 ) != 0)
+		{
+			static std::string reported;
+			const std::string key = std::string( "|" ) + (name ? name : "") + "|";
+			if (reported.find( key ) == std::string::npos) reported += key, fprintf( stderr, "RenderCore_B200: %s (value %g ignored)\n", gCore->Error().c_str(), value );
+		}
+	}
 	void Render( const ViewPyramid& view, const Convergence converge ) override { CHK( Render( &view, (int)converge ) ); }
 	void Shutdown() override { delete gCore; gCore = nullptr; }
 	void SetTextures( const CoreTexDesc* tex, const int textureCount ) override { CHK( SetTextures( tex, textureCount ) ); }
