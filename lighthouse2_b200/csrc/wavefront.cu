@@ -542,6 +542,11 @@ __device__ __forceinline__ V3 ClampAndFix( V3 c, const float clampValue )
 #ifndef B200_SHADE_MIN_BLOCKS
 #define B200_SHADE_MIN_BLOCKS 5
 #endif
+#ifndef B200_SHADE_COMPACT
+#define B200_SHADE_COMPACT 0 // 1: the paths of a block are shaded hits first, misses after (see shadeKernel).  Measured on the 4K x 16 spp frame: lanes per
+                             // instruction go up, time does not (shade 104.1 -> 105.1 ms summed over the chains, frame 126.6 -> 127.4 ms): the kernel
+                             // waits for its scattered record loads, not for issue slots.  Off.
+#endif
 #ifndef B200_SHADE_GRID
 #define B200_SHADE_GRID 2 // resident sets of CTAs per launch
 #endif
@@ -566,13 +571,44 @@ template <bool DISNEY, bool FILTER> __global__ void __launch_bounds__( 128, DISN
 	const ChainArgs c, const float4* __restrict__ shade, const float4* __restrict__ vertexNormals, const float4* __restrict__ instShade, const float4* __restrict__ materials )
 {
 	__shared__ uint32_t sWarp[2 * 4 + 2];
+#if B200_SHADE_COMPACT
+	__shared__ uint32_t sGroup[8];
+	__shared__ uint8_t sOrder[128];
+#endif
 	uint32_t* const counters = c.counters;
 	const uint32_t count = counters[extCounter( pathLength )];
 	// (PassParams fields are read where they are used: uniform, cached loads that cost less than registers held across the whole loop body)
 	const uint32_t stride = gridDim.x * blockDim.x;
 	for (uint32_t base = blockIdx.x * blockDim.x; base < count; base += stride) // block-uniform trip count (blockAppend2 synchronises)
 	{
+#if B200_SHADE_COMPACT
+		// The block's 128 paths, regrouped: those that hit something first, those that left the scene behind them.  On the bounce waves half
+		// of the paths end on the sky after a handful of instructions while their neighbours in the warp work through materials, next event
+		// estimation and the BSDF (13-19 of 32 lanes per instruction before this); grouped, the long path runs in full warps.  The order
+		// in which paths are shaded changes nothing in the image: every path adds to slots of its own (accumulateKernel).
+		uint32_t job;
+		{
+			const uint32_t mine = base + threadIdx.x;
+			const bool valid = mine < count, isHit = valid && (int)__float_as_uint( __ldg( &c.hits[mine].z ) ) >= 0;
+			const uint32_t mh = __ballot_sync( 0xffffffffu, isHit ), mm = __ballot_sync( 0xffffffffu, valid && !isHit ), warp = threadIdx.x >> 5;
+			if ((threadIdx.x & 31) == 0) sGroup[warp] = __popc( mh ), sGroup[4 + warp] = __popc( mm );
+			__syncthreads();
+			uint32_t hitsBefore = 0, missesBefore = 0, hitsTotal = 0;
+#pragma unroll
+			for (uint32_t i = 0; i < 4; i++)
+			{
+				if (i < warp) hitsBefore += sGroup[i], missesBefore += sGroup[4 + i];
+				hitsTotal += sGroup[i];
+			}
+			if (isHit) sOrder[hitsBefore + __popc( mh & laneMaskLt() )] = (uint8_t)threadIdx.x;
+			else if (valid) sOrder[hitsTotal + missesBefore + __popc( mm & laneMaskLt() )] = (uint8_t)threadIdx.x;
+			__syncthreads();
+			// (threads beyond the wave's last path keep an index past the end, as before)
+			job = base + threadIdx.x < count ? base + sOrder[threadIdx.x] : base + threadIdx.x;
+		}
+#else
 		const uint32_t job = base + threadIdx.x;
+#endif
 		bool wantShadow = false, wantExt = false;
 		V3 so = v3( 0.f, 0.f, 0.f ), sl = so, se = so, eo = so, er = so, et = so, en = so;
 		float sdist = 0, epdf = 0;
