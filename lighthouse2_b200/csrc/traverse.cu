@@ -331,6 +331,9 @@ constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
 #ifndef B200_FLUSH_AT
 #define B200_FLUSH_AT 24 // test the pending triangles as soon as 24 wait (32 per round at most): hit distances shrink earlier, +2 % over 32
 #endif
+#ifndef B200_DRAIN_PREFETCH
+#define B200_DRAIN_PREFETCH 0 // n > 0: a warp that has run out of rays and has fewer than n lanes active prefetches its next node (see B' in the pass)
+#endif
 #ifndef B200_EAGER_BELOW
 #define B200_EAGER_BELOW 8 // test pending triangles every pass when fewer lanes than this have node work
 #endif
@@ -585,6 +588,25 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				ngroup = make_uint2( n1.x, (hm & 0xff000000u) | (n0.w >> 24) );
 				tgroup = make_uint2( n1.y, hm & 0x00ffffffu );
 			}
+#if B200_DRAIN_PREFETCH
+			// B'. the end of a wave: a few rays walk alone and every pass is one dependent chain -- node fetch, test, triangle fetch, test --
+			//     at L2 latency.  The node of the NEXT pass is already known here (the nearest inner hit, else the top of the stack): ask for
+			//     its lines now, so that the fetch runs beside the triangle round of this pass instead of behind it.  Only when the warp has
+			//     run out of rays and of parallelism (the prefetch costs issue slots, which the bulk of the wave does not have to spare).
+			if (exhausted && (votes >> 16) < B200_DRAIN_PREFETCH && active)
+			{
+				uint2 g = ngroup;
+				if (g.y <= 0x00ffffffu && sp > (SINGLE ? 0 : (instBase < 0 ? 0 : instBase)))
+					g = sp - 1 < STACK_SMEM ? sstack[(sp - 1) * BLOCK_THREADS + threadIdx.x] : lstack[sp - 1 - STACK_SMEM];
+				if (g.y > 0x00ffffffu)
+				{
+					const uint32_t bit = 31 - __clz( g.y ), slot = (bit - 24) ^ (r.octinv4 & 0xffu);
+					const uint4* next = nodes + (size_t)(g.x + __popc( g.y & 0xffu & ~(0xffffffffu << slot) )) * 5;
+					asm volatile( "prefetch.global.L1 [%0];" ::"l"( next ) );
+					asm volatile( "prefetch.global.L1 [%0];" ::"l"( next + 4 ) );
+				}
+			}
+#endif
 			// C. bottom level: a lane that hit leaf triangles appends ONE record (first triangle, mask, owner) to the warp's
 			//    ring; as soon as 32 triangles are pending the warp tests them, one per lane
 			{
