@@ -101,7 +101,8 @@ struct PassParams {
 	uint32_t R0;                          // per-frame RNG salt
 	uint32_t blue;                        // the blue-noise table applies to this pass (not after the sample index wrapped)
 	float finalScale;                     // 1 / samples in the accumulator after this frame (the last pass writes the frame)
-	uint32_t pad[4];
+	uint32_t blueSlot;                    // filter mode: added to the sample index of the shade stage's blue-noise lookups, + 1 per frame (Optix7Filter/rendercore.cpp:860)
+	uint32_t pad[3];
 };
 static_assert( sizeof( PassParams ) == 96, "PassParams: six float4" );
 
@@ -878,8 +879,9 @@ template <bool DISNEY, bool FILTER> __global__ void __launch_bounds__( 128, DISN
 						const int sampleIdx = (int)sampleIdxU, bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
 						const uint32_t* const blueTable = __ldg( &pass->blue ) ? f.blueTable : nullptr;
 						const bool blue = blueTable && sampleIdx < 2;
-						const float r0 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 4 + 4 * pathLength ) : RandomFloat( seed );
-						const float r1 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 5 + 4 * pathLength ) : RandomFloat( seed );
+						const int blueIdx = FILTER ? sampleIdx + (int)__ldg( &pass->blueSlot ) : sampleIdx; // Optix7Filter/kernels/pathtracer.h:248-249
+						const float r0 = blue ? BlueNoiseSampler( blueTable, bx, by, blueIdx, 4 + 4 * pathLength ) : RandomFloat( seed );
+						const float r1 = blue ? BlueNoiseSampler( blueTable, bx, by, blueIdx, 5 + 4 * pathLength ) : RandomFloat( seed );
 						float pickProb, lightPdf;
 						V3 lightColor;
 						V3 L = RandomPointOnLight( f, r0, r1, I, sF, pickProb, lightPdf, lightColor ) - I;
@@ -916,8 +918,9 @@ template <bool DISNEY, bool FILTER> __global__ void __launch_bounds__( 128, DISN
 						const int sampleIdx = (int)sampleIdxU, bx = (int)(pixelIdx % f.width), by = (int)(pixelIdx / f.width);
 						const uint32_t* const blueTable = __ldg( &pass->blue ) ? f.blueTable : nullptr;
 						const bool blue = blueTable && sampleIdx < 256; // pathtracer.h:212-222
-						const float r3 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 6 + 4 * pathLength ) : RandomFloat( seed );
-						const float r4 = blue ? BlueNoiseSampler( blueTable, bx, by, sampleIdx, 7 + 4 * pathLength ) : RandomFloat( seed );
+						const int blueIdx = FILTER ? sampleIdx + (int)__ldg( &pass->blueSlot ) : sampleIdx; // :306-307
+						const float r3 = blue ? BlueNoiseSampler( blueTable, bx, by, blueIdx, 6 + 4 * pathLength ) : RandomFloat( seed );
+						const float r4 = blue ? BlueNoiseSampler( blueTable, bx, by, blueIdx, 7 + 4 * pathLength ) : RandomFloat( seed );
 						// SampleBSDF (lambert.h:71-123)
 						V3 R = sF, bsdf = v3( 0.f, 0.f, 0.f );
 						float newPdf = 1;
@@ -1235,6 +1238,7 @@ struct WavefrontState {
 	uint32_t filterPixels = 0;       // the size the filter buffers were made (and cleared) for
 	int filterFlip = 0;              // which of the pairs is "current" this frame
 	uint32_t frameCycle = 0;         // TAA jitter: four sub-pixel offsets in turn (rendercore.cpp:733-737)
+	uint32_t blueSlot = 0, filterFrames = 0; // blue-noise slot of the next filtered frame (+ 1 per frame, mod 256); filtered frames rendered so far
 	float prevView[12] = {}, prevJ0 = 0, prevJ1 = 0;
 	cudaEvent_t filterBegin = nullptr, filterEnd = nullptr;
 	cudaEvent_t frameBegin = nullptr, frameEnd = nullptr, fork = nullptr, gatherWait = nullptr, gatherBegin = nullptr, gatherEnd = nullptr;
@@ -1914,6 +1918,14 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 		P.blue = (w->haveBlueNoise && globalSample < period) ? 1u : 0u; // not after the sample index wrapped
 		P.R0 = (globalSample / period + 1) * 7907u;
 		P.finalScale = 1.0f / (float)(w->samplesTaken + (uint32_t)w->spp);
+		if (filtering)
+		{
+			// Every filtered frame starts from sample 0 with the same seed (rendercore.cpp:687 "same seed means same noise"): in the reference the
+			// frames differ through the rotating blue-noise slot alone.  A host that has supplied the tables gets exactly that; without
+			// them the salt changes with the frame instead, or the temporal filter would average a still noise pattern.
+			P.blueSlot = w->blueSlot;
+			if (!w->haveBlueNoise) P.R0 = (w->filterFrames + 1) * 7907u;
+		}
 	}
 	memset( &stats.totalRays, 0, (char*)&stats.probedInstid - (char*)&stats.totalRays );
 	plan.l2Persist = l2Persist;
@@ -1970,6 +1982,7 @@ int RenderCore::Render( const void* viewPyramid, int converge )
 			if (w->taaOn) std::swap( w->taaOut, w->shading[w->filterFlip] );
 			w->filterFlip ^= 1;
 			w->prevJ0 = j0, w->prevJ1 = j1;
+			w->blueSlot = (w->blueSlot + 1) & 255u, w->filterFrames++;
 			memcpy( w->prevView, vp, 48 );
 		}
 		stats.gatherMs = stats.gatherKernelMs = 0;

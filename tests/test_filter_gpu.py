@@ -345,3 +345,38 @@ def test_filtered_frames_follow_the_reference_pipeline(ref, taa):
         prev_world, prev_moments, history, prev_view, prev_j = d_world, moments, f_out, vnow, j
         assert frame[1:-1, 1:-1, :3].mean() > 0.01
     rc.Shutdown()
+
+
+def test_filtered_frames_do_not_repeat_their_noise():
+    """Every filtered frame starts from sample 0 with the same seed (lib/RenderCore_Optix7Filter/rendercore.cpp:687); in the reference the frames
+    differ through the blue-noise slot that moves on by one per frame (:860, pathtracer.h:248-249, 306-307).  With a table set, the second
+    frame of a still camera must be the restatement's frame with blue_slot = 1; without a table the salt changes instead."""
+    import cases
+    import wavefront_ref
+    from lighthouse2_b200 import scenes
+    w, h, spp = 96, 54, 1
+    view = scenes.view_pyramid(width=w, height=h, **scenes.C1_CAMERA)
+    table = np.random.default_rng(78).integers(0, 256, 5 * 65536).astype(np.uint32)
+    for with_table in (True, False):
+        sc, rc = _filter_scene_core(w, h, spp, TAA=1)  # (with the TAA jitter: corner rays of the unshifted view run along the mesh's edges in the middle column)
+        if with_table:
+            rc.SetBlueNoise(table)
+        planes = []
+        for k in range(2):
+            rc.Render(view, converge=0)
+            planes.append((rc.ReadAccumulator(), rc.ReadFilterBuffer(3)))
+        rc.Shutdown()
+        assert np.abs(planes[0][0][..., :3] - planes[1][0][..., :3]).mean() > 1e-3  # the noise moved
+        port = cases.load_oracle(dict(sc["case"], rays=None), "port")
+        out = {}
+        kw = dict(blue_noise=table, blue_slot=1) if with_table else dict(salt=2 * 7907)
+        ref = wavefront_ref.render(port, sc["case"]["meshes"], sc["case"]["instances"], view, w, h,
+                                   lights=wavefront_ref.Lights(sc["area"], sc["point"], sc["spot"], sc["dir"]), sky_image=sc["sky"],
+                                   materials=sc["materials"], prim_materials=sc["prim_materials"], vertex_normals=sc["vertex_normals"],
+                                   uvs=sc["uvs"], lods=sc["lods"], textures=sc["textures"], max_path_length=5, spp=spp, bounce_cap=1, roulette=False,
+                                   filter_out=out, filter_jitter=(0.7, 0.8), **kw)  # the second frame's jitter (rendercore.cpp:733-736)
+        mean = float(ref[..., :3].mean() + out["indirect"][..., :3].mean())
+        for name, got, want in (("direct", planes[1][0], ref), ("indirect", planes[1][1], out["indirect"])):
+            rmse = float(np.sqrt(np.mean((got[..., :3] - want[..., :3]) ** 2)))
+            print("second frame,", "table" if with_table else "no table", name, "rmse", rmse, "of mean", mean)
+            assert rmse <= 1e-4 * mean

@@ -348,7 +348,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
            materials=None, prim_materials=None, vertex_normals=None, uvs=None, lods=None, textures=None, spread_angle=0.01,
            max_path_length=5, spp=1, sample_offset=0, clamp=10.0, bounce_cap=0, roulette=True, nthreads=8, stats=None,
            disney=None, material_words=None, tangents=None, alphas=None, blue_noise=None, material_maps=None, bitangents=None,
-           filter_out=None, filter_jitter=(0.0, 0.0)):
+           filter_out=None, filter_jitter=(0.0, 0.0), blue_slot=0, salt=7907):
     """Returns the accumulator float32[h, w, 4] (rgb sums over samples, w = depth sum of the primary hits).
     meshes: list of verts[T,3,3]; instances: list of (mesh, mat16 or None); light = (pos3, radiance3) shortcut for one
     point light, or lights = Lights(...); materials = float32[n, 4] (albedo rgb, roughness) or the float32[n, 16] table of
@@ -363,7 +363,8 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
     filter_out = {}: the frame as the reference's filtering core renders it (lib/RenderCore_Optix7Filter/kernels/pathtracer.h;
     pass bounce_cap=1, roulette=False): rays through the pixel CORNERS of the view shifted by filter_jitter pixels, no lens; light that
     arrives after the diffuse bounce goes to a second accumulator; the first sample writes the feature buffers.  Filled with
-    "indirect" float32[h, w, 4], "features" uint32[h, w, 4] (history bits zero), "world_pos" float32[h, w, 4], "delta_depth" float32[h, w, 4]."""
+    "indirect" float32[h, w, 4], "features" uint32[h, w, 4] (history bits zero), "world_pos" float32[h, w, 4], "delta_depth" float32[h, w, 4].
+    blue_slot is added to the sample index of the shade stage's blue-noise lookups (the filtering core rotates it per frame); salt = R0."""
     npx = width * height
     acc = np.zeros((npx, 4), np.float64)
     filt = filter_out is not None
@@ -439,7 +440,7 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
 
     for s in range(spp):
         sample = sample_offset + s
-        R0 = np.uint32(7907)
+        R0 = np.uint32(salt)
         pix = np.arange(npx, dtype=np.uint32)
         path_idx = (pix + np.uint32(sample) * np.uint32(npx)).astype(np.uint32)
         x, y = (pix % width).astype(f32), (pix // width).astype(f32)
@@ -723,8 +724,8 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
             nee = (flags & S_SPECULAR) == 0
             if lights.count > 0 and nee.any():
                 if blue_noise is not None and sample < 2:  # pathtracer.h:168-173
-                    r0 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 4 + 4 * length)
-                    r1 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 5 + 4 * length)
+                    r0 = blue_noise_sampler(blue_noise, px % width, px // width, sample + blue_slot, 4 + 4 * length)
+                    r1 = blue_noise_sampler(blue_noise, px % width, px // width, sample + blue_slot, 5 + 4 * length)
                 else:
                     seed_n, r0 = random_float(seed.copy())
                     seed_n, r1 = random_float(seed_n)
@@ -762,8 +763,8 @@ def render(oracle, meshes, instances, view, width, height, light=None, lights=No
                     store_features(px[q], 0, pack_normal2(N[q]) + via[q], t[q], via[q], 0, I[q])
                 break
             if blue_noise is not None and sample < 256:  # pathtracer.h:212-217
-                r3 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 6 + 4 * length)
-                r4 = blue_noise_sampler(blue_noise, px % width, px // width, sample, 7 + 4 * length)
+                r3 = blue_noise_sampler(blue_noise, px % width, px // width, sample + blue_slot, 6 + 4 * length)
+                r4 = blue_noise_sampler(blue_noise, px % width, px // width, sample + blue_slot, 7 + 4 * length)
             else:
                 seed, r3 = random_float(seed)
                 seed, r4 = random_float(seed)
