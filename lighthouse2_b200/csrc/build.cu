@@ -587,15 +587,20 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 	//    too small under rotation) plus an ulp-scale pad, since the kernels transform the RAY instead of the box; centroid bounds
 	for (uint32_t i = tid; i < n; i += T)
 	{
-		const TlasInstanceInput& I = in[i];
-		const float* c = I.transform;
+		// (the 176-byte input record as eleven 16-byte loads: three rows of the transform, the two bounds, the flag word -- read field by
+		// field, with the records 176 bytes apart, every scalar load of the warp touched its own sector)
+		const float4* I4 = reinterpret_cast<const float4*>( in + i );
+		const float4 t0 = __ldg( I4 ), t1 = __ldg( I4 + 1 ), t2 = __ldg( I4 + 2 ), blo = __ldg( I4 + 8 ), bhi = __ldg( I4 + 9 );
+		const bool empty = __float_as_uint( __ldg( I4 + 10 ).z ) != 0;
+		const float c[12] = { t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w, t2.x, t2.y, t2.z, t2.w };
 		float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
-		if (I.empty) { lo[0] = hi[0] = c[3], lo[1] = hi[1] = c[7], lo[2] = hi[2] = c[11]; }
+		if (empty) { lo[0] = hi[0] = c[3], lo[1] = hi[1] = c[7], lo[2] = hi[2] = c[11]; }
 		else
 		{
+#pragma unroll
 			for (int k = 0; k < 8; k++)
 			{
-				const float x = (k & 1) ? I.hi[0] : I.lo[0], y = (k & 2) ? I.hi[1] : I.lo[1], z = (k & 4) ? I.hi[2] : I.lo[2];
+				const float x = (k & 1) ? bhi.x : blo.x, y = (k & 2) ? bhi.y : blo.y, z = (k & 4) ? bhi.z : blo.z;
 				const float p[3] = { c[0] * x + c[1] * y + c[2] * z + c[3], c[4] * x + c[5] * y + c[6] * z + c[7], c[8] * x + c[9] * y + c[10] * z + c[11] };
 				for (int a = 0; a < 3; a++) lo[a] = fminf( lo[a], p[a] ), hi[a] = fmaxf( hi[a], p[a] );
 			}
@@ -821,15 +826,18 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 	for (uint32_t j = tid; j < n; j += T)
 	{
 		const uint32_t id = __ldcg( sc.instOrder + j );
-		const TlasInstanceInput& I = in[id];
+		const float4* I4 = reinterpret_cast<const float4*>( in + id ); // 16-byte loads and stores throughout (see step 1)
 		float4* r = instRecs + (size_t)j * 6;
-		for (int k = 0; k < 4; k++) r[k] = make_float4( I.inv[4 * k], I.inv[4 * k + 1], I.inv[4 * k + 2], I.inv[4 * k + 3] );
-		r[4] = make_float4( __uint_as_float( I.blasRoot ), __uint_as_float( id ), __uint_as_float( I.meshId ), __uint_as_float( I.flags ) );
+#pragma unroll
+		for (int k = 0; k < 4; k++) r[k] = __ldg( I4 + 4 + k ); // inv
+		const float4 word = __ldg( I4 + 10 );                    // meshId, flags, empty, -
+		r[4] = make_float4( __ldg( I4 + 8 ).w /* blasRoot */, __uint_as_float( id ), word.x, word.y );
 		r[5] = make_float4( 0, 0, 0, 0 );
-		const TlasInstanceInput& S = in[j];
+		const float4* S4 = reinterpret_cast<const float4*>( in + j );
 		float4* sh = instShade + (size_t)j * 4;
-		for (int k = 0; k < 3; k++) sh[k] = make_float4( S.transform[4 * k], S.transform[4 * k + 1], S.transform[4 * k + 2], S.transform[4 * k + 3] );
-		sh[3] = make_float4( __uint_as_float( S.triBase ), __uint_as_float( S.meshId ), 0, 0 );
+#pragma unroll
+		for (int k = 0; k < 3; k++) sh[k] = __ldg( S4 + k );   // transform rows
+		sh[3] = make_float4( __ldg( S4 + 9 ).w /* triBase */, __ldg( S4 + 10 ).x /* meshId */, 0, 0 );
 	}
 	__syncthreads();
 	stamp();
