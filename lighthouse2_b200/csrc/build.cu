@@ -18,6 +18,7 @@
 #include "kernels.h"
 #include "wide_bvh.h"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #ifndef B200_DP_COLLAPSE
 #define B200_DP_COLLAPSE 1 // children of a wide node from the SAH dynamic programme (1) or by opening the largest child (0)
@@ -210,8 +211,124 @@ __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, cons
 	}
 }
 
+// ---- 3b / 4b. agglomerative alternative to the radix tree: PLOC (Meister, Bittner: "Parallel Locally-Ordered Clustering for Bounding Volume
+// Hierarchy Construction", TVCG 2018).  The clusters -- at first the triangles in Morton order -- each look for the neighbour within
+// `radius` places along the curve whose union with them has the smallest surface; pairs that chose each other merge into a binary node;
+// the survivors are compacted, still in curve order, and the round repeats until one cluster is left.  The tree is built bottom-up by
+// surface area instead of top-down by key bits: the Morton order only decides who may meet whom.  Binary nodes are numbered from the
+// back (the last merge, the root, gets index 0, where the collapse starts) and receive box, primitive count and collapse plan as they
+// are made -- the jobs of radixTreeKernel and binaryBoxesKernel.
+struct PlocClusters { uint32_t* ref; float4 *lo, *hi; }; // ref: LEAF | sorted position, or a binary node
+
+__global__ void plocInitKernel( const uint32_t* __restrict__ sortedPrim, const float4* __restrict__ primLo, const float4* __restrict__ primHi, const uint32_t n, const PlocClusters c )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint32_t p = sortedPrim[i];
+	c.ref[i] = LEAF | i, c.lo[i] = primLo[p], c.hi[i] = primHi[p];
+}
+
+template <int RADIUS> __global__ void __launch_bounds__( 256 ) plocNearestKernel( const PlocClusters c, const uint32_t* __restrict__ nPtr, uint32_t* __restrict__ nearest )
+{
+	__shared__ float4 sLo[256 + 2 * RADIUS], sHi[256 + 2 * RADIUS];
+	const uint32_t n = *nPtr;
+	const int blockFirst = (int)(blockIdx.x * 256);
+	if (blockFirst >= (int)n) return;
+	for (int t = threadIdx.x; t < 256 + 2 * RADIUS; t += 256)
+	{
+		const int j = blockFirst - RADIUS + t;
+		if (j >= 0 && j < (int)n) sLo[t] = c.lo[j], sHi[t] = c.hi[j];
+	}
+	__syncthreads();
+	const int i = blockFirst + (int)threadIdx.x;
+	if (i >= (int)n) return;
+	const float4 lo = sLo[threadIdx.x + RADIUS], hi = sHi[threadIdx.x + RADIUS];
+	// Among equal areas the nearer place wins, and among the two places at distance d the one that pairs the clusters up in aligned
+	// blocks of d (even block: the partner above, odd block: below).  That order guarantees that the smallest pair of a round is mutual
+	// (the build always advances) and that a run of identical boxes -- coincident triangles -- halves per round instead of losing one
+	// pair per round.
+	float best = 3.0e38f;
+	int bestJ = -1;
+#pragma unroll
+	for (int d = 1; d <= RADIUS; d++)
+	{
+		const int up = ((i / d) & 1) == 0 ? d : -d;
+#pragma unroll
+		for (int side = 0; side < 2; side++)
+		{
+			const int o = side ? -up : up, j = i + o;
+			if (j < 0 || j >= (int)n) continue;
+			const float4 l = sLo[(int)threadIdx.x + RADIUS + o], h = sHi[(int)threadIdx.x + RADIUS + o];
+			const float x = fmaxf( hi.x, h.x ) - fminf( lo.x, l.x ), y = fmaxf( hi.y, h.y ) - fminf( lo.y, l.y ), z = fmaxf( hi.z, h.z ) - fminf( lo.z, l.z );
+			const float area = x * y + y * z + z * x;
+			if (area < best) best = area, bestJ = j;
+		}
+	}
+	nearest[i] = (uint32_t)bestJ;
+}
+
+// pairs that chose each other merge (the lower index does the work and keeps the place); flag = the cluster lives on
+__global__ void plocMergeKernel( const PlocClusters c, const uint32_t* __restrict__ nPtr, const uint32_t* __restrict__ nearest, uint32_t* __restrict__ flag,
+	uint32_t* __restrict__ mergeCounter, const uint32_t T, const uint32_t* __restrict__ sortedPrim, const float4* __restrict__ primLo, const float4* __restrict__ primHi,
+	uint32_t* __restrict__ childL, uint32_t* __restrict__ childR, uint32_t* __restrict__ rangeCount, float4* __restrict__ nodeLo, float4* __restrict__ nodeHi,
+	float4* __restrict__ planLo, float4* __restrict__ planHi, const float primCost )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, n = *nPtr;
+	if (i >= n) return;
+	const uint32_t j = nearest[i];
+	if (j >= n || nearest[j] != i) { flag[i] = 1; return; }
+	if (j < i) { flag[i] = 0; return; }
+	const uint32_t node = T - 2 - atomicAdd( mergeCounter, 1u );
+	const uint32_t L = c.ref[i], R = c.ref[j];
+	const float4 ll = c.lo[i], lh = c.hi[i], rl = c.lo[j], rh = c.hi[j];
+	const float4 nl = make_float4( fminf( ll.x, rl.x ), fminf( ll.y, rl.y ), fminf( ll.z, rl.z ), 0 ), nh = make_float4( fmaxf( lh.x, rh.x ), fmaxf( lh.y, rh.y ), fmaxf( lh.z, rh.z ), 0 );
+	const uint32_t count = ((L & LEAF) ? 1u : rangeCount[L]) + ((R & LEAF) ? 1u : rangeCount[R]);
+	childL[node] = L, childR[node] = R, rangeCount[node] = count, nodeLo[node] = nl, nodeHi[node] = nh;
+	float cl[7], cr[7], cost[7];
+	loadPlan( L, sortedPrim, primLo, primHi, planLo, planHi, primCost, cl );
+	loadPlan( R, sortedPrim, primLo, primHi, planLo, planHi, primCost, cr );
+	const float ex = nh.x - nl.x, ey = nh.y - nl.y, ez = nh.z - nl.z;
+	uint32_t bits;
+	mergePlan( cl, cr, ex * ey + ey * ez + ez * ex, count, 3, primCost, cost, bits );
+	planLo[node] = make_float4( cost[0], cost[1], cost[2], cost[3] ), planHi[node] = make_float4( cost[4], cost[5], cost[6], __uint_as_float( bits ) );
+	c.ref[i] = node, c.lo[i] = nl, c.hi[i] = nh, flag[i] = 1;
+}
+
+// survivors move up, in order (offsets = exclusive sum of the flags); the last thread leaves the new count
+__global__ void plocCompactKernel( const PlocClusters in, const PlocClusters out, uint32_t* __restrict__ nPtr, const uint32_t nOld, const uint32_t* __restrict__ flag,
+	const uint32_t* __restrict__ offset )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= nOld) return;
+	if (flag[i]) { const uint32_t o = offset[i]; out.ref[o] = in.ref[i], out.lo[o] = in.lo[i], out.hi[o] = in.hi[i]; }
+	if (i == nOld - 1) *nPtr = offset[i] + flag[i];
+}
+
+// the (at most three) primitives of a subtree that became a leaf slot, left to right.  (For the radix tree that is a contiguous run of the
+// sorted order; the agglomerative builder below merges clusters that are near each other but not adjacent, so the tree is walked.)
+__device__ __forceinline__ uint32_t leafSlotPrims( const uint32_t* __restrict__ childL, const uint32_t* __restrict__ childR, const uint32_t ref, uint32_t out[3] )
+{
+	if (ref & LEAF) { out[0] = ref & ~LEAF; return 1; }
+	uint32_t n = 0;
+	const uint32_t c[2] = { childL[ref], childR[ref] };
+#pragma unroll
+	for (int k = 0; k < 2; k++)
+	{
+		if (c[k] & LEAF) { if (n < 3) out[n] = c[k] & ~LEAF; n++; }
+		else
+		{
+			const uint32_t l = childL[c[k]], r = childR[c[k]]; // a subtree of two: both are leaves
+			if (n < 3) out[n] = l & ~LEAF;
+			n++;
+			if (n < 3) out[n] = r & ~LEAF;
+			n++;
+		}
+	}
+	return n < 3 ? n : 3;
+}
+
 struct CollapseArgs {
-	const uint32_t *sortedPrim, *childL, *childR, *rangeFirst, *rangeCount;
+	const uint32_t *sortedPrim, *childL, *childR, *rangeCount;
 	const float4 *primLo, *primHi, *nodeLo, *nodeHi, *planHi;
 	uint32_t* wideToBinary;   // [maxNodes] binary inner node that wide node w represents
 	uint4* nodes;             // output, relative index 0 = this tree's root (pool pointer already offset)
@@ -348,9 +465,10 @@ __device__ void collapseNode( const CollapseArgs& a, const uint32_t w )
 		{
 			meta = (((1u << cnt[i]) - 1u) << 5) | off;
 			// the subtree's triangles are a contiguous run of the sorted order
-			const uint32_t first = (ref[i] & LEAF) ? (ref[i] & ~LEAF) : a.rangeFirst[ref[i]];
+			uint32_t at[3];
+			leafSlotPrims( a.childL, a.childR, ref[i], at );
 			for (uint32_t k = 0; k < cnt[i]; k++)
-				a.primOut[(size_t)(primBase + off + k) * a.primOutStride] = a.sortedPrim[first + k];
+				a.primOut[(size_t)(primBase + off + k) * a.primOutStride] = a.sortedPrim[at[k]];
 			off += cnt[i];
 		}
 		if (s < 4) metaLo |= meta << (8 * s); else metaHi |= meta << (8 * (s - 4));
@@ -486,8 +604,9 @@ __device__ void collapseNodeGroup( const CollapseArgs& a, const uint32_t w, cons
 		else
 		{
 			meta = (((1u << cnt) - 1u) << 5) | off;
-			const uint32_t first = (myRef & LEAF) ? (myRef & ~LEAF) : a.rangeFirst[myRef]; // the subtree's primitives are a contiguous run of the sorted order
-			for (uint32_t k = 0; k < cnt; k++) a.primOut[(size_t)(primBase + off + k) * a.primOutStride] = a.sortedPrim[first + k];
+			uint32_t at[3];
+			leafSlotPrims( a.childL, a.childR, myRef, at );
+			for (uint32_t k = 0; k < cnt; k++) a.primOut[(size_t)(primBase + off + k) * a.primOutStride] = a.sortedPrim[at[k]];
 		}
 		if (mySlot < 4) metaLo = meta << (8 * mySlot); else metaHi = meta << (8 * (mySlot - 4));
 	}
@@ -745,7 +864,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		stamp();
 		// 6. collapse to 8-wide nodes, level by level
 		CollapseArgs a;
-		a.sortedPrim = sortedPrim, a.childL = childL, a.childR = childR, a.rangeFirst = rangeFirst, a.rangeCount = rangeCount;
+		a.sortedPrim = sortedPrim, a.childL = childL, a.childR = childR, a.rangeCount = rangeCount;
 		a.primLo = sc.primLo, a.primHi = sc.primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = planHi;
 		a.wideToBinary = wideToBinary, a.nodes = nodes, a.primOut = sc.instOrder, a.primOutStride = 1, a.counters = sCounters;
 		a.nodeBase = nodeBase, a.triBase = 0, a.maxNodes = maxNodes;
@@ -849,8 +968,11 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 // Builds the wide-BVH topology of `T` triangles (dVerts = float4[3T], device) into nodes[0 .. nodeCount) / tris[0 .. T) (pool pointers
 // already offset to this mesh's base; indices stored in the nodes are absolute: + nodeBase / + triBase).  levelStart (relative,
 // size levels + 1) and nodeCount are returned for the refit, which the caller runs next.  T >= 4.
+#ifndef B200_PLOC_RADIUS
+#define B200_PLOC_RADIUS 16
+#endif
 cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, float4* tris, uint32_t nodeBase, uint32_t triBase, uint32_t maxNodes,
-	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount )
+	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount, int builder )
 {
 	cudaError_t e;
 	char* scratch = nullptr;
@@ -866,6 +988,16 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	const size_t oParI = take( (size_t)T * 4 ), oParL = take( (size_t)T * 4 ), oVisits = take( (size_t)T * 4 );
 	const size_t oNodeLo = take( (size_t)T * 16 ), oNodeHi = take( (size_t)T * 16 ), oPlanLo = take( (size_t)T * 16 ), oPlanHi = take( (size_t)T * 16 );
 	const size_t oW2B = take( (size_t)maxNodes * 4 + 64 ), oSmall = take( 256 );
+	// the agglomerative builder: two sets of clusters (reference + box), nearest neighbours, survivor flags and their running sum
+	const bool ploc = builder == 2;
+	size_t scanBytes = 0;
+	if (ploc) cub::DeviceScan::ExclusiveSum( nullptr, scanBytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)T, s );
+	size_t oCRef[2] = { 0, 0 }, oCLo[2] = { 0, 0 }, oCHi[2] = { 0, 0 }, oNearest = 0, oFlag = 0, oOffset = 0, oScan = 0;
+	if (ploc)
+	{
+		for (int k = 0; k < 2; k++) oCRef[k] = take( (size_t)T * 4 ), oCLo[k] = take( (size_t)T * 16 ), oCHi[k] = take( (size_t)T * 16 );
+		oNearest = take( (size_t)T * 4 ), oFlag = take( (size_t)T * 4 ), oOffset = take( (size_t)T * 4 ), oScan = take( scanBytes );
+	}
 	if ((e = cudaMallocAsync( (void**)&scratch, off, s )) != cudaSuccess) return e;
 	float4 *primLo = (float4*)(scratch + oPrimLo), *primHi = (float4*)(scratch + oPrimHi), *nodeLo = (float4*)(scratch + oNodeLo), *nodeHi = (float4*)(scratch + oNodeHi);
 	float4 *planLo = (float4*)(scratch + oPlanLo), *planHi = (float4*)(scratch + oPlanHi);
@@ -888,11 +1020,38 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	primBoundsKernel<<<blocks, 256, 0, s>>>( dVerts, T, primLo, primHi, cbounds );
 	mortonKernel<<<blocks, 256, 0, s>>>( primLo, primHi, T, cbounds, keys, vals );
 	if ((e = cub::DeviceRadixSort::SortPairs( scratch + oSort, sortBytes, keys, keys2, vals, vals2, (int)T, 0, 63, s )) != cudaSuccess) return done( e );
-	radixTreeKernel<<<blocks, 256, 0, s>>>( keys2, (int)T, childL, childR, first, count, parI, parL );
-	binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, count, parI, parL, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost, visits );
+	if (!ploc)
+	{
+		radixTreeKernel<<<blocks, 256, 0, s>>>( keys2, (int)T, childL, childR, first, count, parI, parL );
+		binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, count, parI, parL, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost, visits );
+	}
+	else
+	{
+		PlocClusters cl[2];
+		for (int k = 0; k < 2; k++) cl[k].ref = (uint32_t*)(scratch + oCRef[k]), cl[k].lo = (float4*)(scratch + oCLo[k]), cl[k].hi = (float4*)(scratch + oCHi[k]);
+		uint32_t *nearest = (uint32_t*)(scratch + oNearest), *flag = (uint32_t*)(scratch + oFlag), *offset = (uint32_t*)(scratch + oOffset);
+		uint32_t *nPtr = counters + 8, *mergeCounter = counters + 9; // (the 256-byte block of small values)
+		const uint32_t init[2] = { T, 0 };
+		if ((e = cudaMemcpyAsync( nPtr, init, 8, cudaMemcpyHostToDevice, s )) != cudaSuccess) return done( e );
+		plocInitKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, T, cl[0] );
+		uint32_t n = T;
+		int cur = 0;
+		for (int round = 0; n > 1; round++)
+		{
+			if (round > 4096) return done( cudaErrorUnknown ); // (every round merges at least its smallest pair)
+			const uint32_t b = (n + 255) / 256;
+			plocNearestKernel<B200_PLOC_RADIUS><<<b, 256, 0, s>>>( cl[cur], nPtr, nearest );
+			plocMergeKernel<<<b, 256, 0, s>>>( cl[cur], nPtr, nearest, flag, mergeCounter, T, vals2, primLo, primHi, childL, childR, count, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost );
+			if ((e = cub::DeviceScan::ExclusiveSum( scratch + oScan, scanBytes, flag, offset, (int)n, s )) != cudaSuccess) return done( e );
+			plocCompactKernel<<<b, 256, 0, s>>>( cl[cur], cl[cur ^ 1], nPtr, n, flag, offset );
+			if ((e = cudaMemcpyAsync( &n, nPtr, 4, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
+			if ((e = cudaStreamSynchronize( s )) != cudaSuccess) return done( e );
+			cur ^= 1;
+		}
+	}
 	if ((e = cudaGetLastError()) != cudaSuccess) return done( e );
 	CollapseArgs a;
-	a.sortedPrim = vals2, a.childL = childL, a.childR = childR, a.rangeFirst = first, a.rangeCount = count;
+	a.sortedPrim = vals2, a.childL = childL, a.childR = childR, a.rangeCount = count;
 	a.primLo = primLo, a.primHi = primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = planHi;
 	a.wideToBinary = w2b, a.nodes = nodes, a.primOut = reinterpret_cast<uint32_t*>( tris ) + 3, a.primOutStride = 12, a.counters = counters;
 	a.nodeBase = nodeBase, a.triBase = triBase, a.maxNodes = maxNodes;

@@ -167,7 +167,7 @@ int RenderCore::Setting( const char* name, float value )
 	// ("clampDirect", "clampIndirect", "filter", "TAA": with the frame settings in wavefront.cu -- honoured when Setting filterCore is on)
 	// B200-specific keys
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
-	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 0.5f; return 0; }
+	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 1.5f ? 2 : (value >= 0.5f ? 1 : 0); return 0; } // 1: LBVH, 2: PLOC (build.cu)
 	if (!strcmp( name, "deviceTlas" )) { deviceTlas = value >= 0.5f; tlasDirty = true; return 0; }
 	if (!strcmp( name, "twoStreams" )) { twoStreams = value >= 0.5f; return 0; }
 	if (!strcmp( name, "zeroCopy" )) { zeroCopy = value >= 0.5f; return 0; }
@@ -279,7 +279,7 @@ int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T,
 	else e = cudaMemsetAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, 0, (size_t)T * 16, stream );
 	if (e != cudaSuccess) return fail( "shading upload", e );
 	if ((e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
-		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount )) != cudaSuccess) return fail( "GPU BVH build", e );
+		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild )) != cudaSuccess) return fail( "GPU BVH build", e );
 	if ((int)m.levelStart.size() - 1 > MAX_TREE_LEVELS) return fail( "SetGeometry: the device-built tree is deeper than the traversal stack allows (wide_bvh.h MAX_TREE_LEVELS)" );
 	if (prepareRefit( m )) return 1;
 	m.built = true;

@@ -154,7 +154,8 @@ private:
 	DeviceBuffer rayO[WAVE_SLOTS], rayD[WAVE_SLOTS], hitBuf[WAVE_SLOTS], bitBuf[WAVE_SLOTS], vertStage, nodeLo, nodeHi, stepNodes, stepTris;
 	bool refitWalk = true; // Setting refitWalk: the refit is one launch that climbs the tree (1) or one launch per level (0)
 	int prepareRefit( MeshRec& m );
-	bool countSteps = false, allowRefit = true, gpuBuild = false; // gpuBuild: new meshes get an LBVH built on the device (build.cu)
+	bool countSteps = false, allowRefit = true;
+	int gpuBuild = 0; // new meshes get their tree built on the device (build.cu): 1 = Morton radix tree (LBVH), 2 = agglomerative clustering (PLOC)
 	bool zeroCopy = true, twoStreams = true; int pinnedChunks = 1, zeroCopyBelow = 400000; // pinned host ray planes are fetched by the kernel itself (Setting zeroCopy / pinnedChunks)
 	bool singleInstanceShortcut = true; // a one-instance scene skips the top-level node (Setting singleInstanceShortcut)
 	int hostChunks = 4, hostChunkMode = 0; // chunk schedule of the host-buffer waves (Setting hostChunks / hostChunkMode)

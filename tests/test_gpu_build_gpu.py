@@ -1,5 +1,5 @@
-"""GPU BVH build (Setting gpuBuild = 1; lighthouse2_b200/csrc/build.cu): Morton sort + binary radix tree + 8-wide collapse on
-the device, boxes by the refit.  A different tree than the host SAH builder's, the same hits: checked against the golden
+"""GPU BVH build (Setting gpuBuild = 1: Morton sort + binary radix tree, = 2: Morton sort + agglomerative clustering along the
+curve (PLOC); lighthouse2_b200/csrc/build.cu), then the 8-wide collapse on the device, boxes by the refit.  Every test runs with both.  A different tree than the host SAH builder's, the same hits: checked against the golden
 buffers / the CPU oracle and against the SAH-built core, including duplicate centroids, instancing, refit after the build,
 and a second mesh appended behind a GPU-built one."""
 import os
@@ -13,11 +13,18 @@ from lighthouse2_b200 import core, scenes
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+BUILDER = 1
+
+
+@pytest.fixture(autouse=True, params=[1, 2], ids=["lbvh", "ploc"])
+def _builder(request):
+    global BUILDER
+    BUILDER = request.param
 
 
 def _gpu_core(case):
     rc = core.RenderCoreB200(0)
-    rc.Setting("gpuBuild", 1)
+    rc.Setting("gpuBuild", BUILDER)
     return cases.load_core(rc, case)
 
 
@@ -64,7 +71,7 @@ def test_gpu_tree_equals_sah_tree_on_the_sphere_field():
     Or, Dr = scenes.random_rays(400_000, 60.0, seed=8)
     O, D = np.concatenate([O, Or]), np.concatenate([D, Dr])
     out = []
-    for gpu in (0, 1):
+    for gpu in (0, BUILDER):
         rc = core.RenderCoreB200(0)
         rc.Setting("gpuBuild", gpu)
         rc.SetGeometry(0, verts); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
@@ -110,7 +117,7 @@ def test_refit_after_gpu_build_and_second_mesh():
     O, D = scenes.random_rays(60_000, 6.0, seed=31)
     moved = (sph * np.float32(1.0) + np.float32(0.15) * np.sin(sph[..., ::-1] * np.float32(3.0))).astype(np.float32)
     rc = core.RenderCoreB200(0)
-    rc.Setting("gpuBuild", 1)
+    rc.Setting("gpuBuild", BUILDER)
     cases.load_core(rc, dict(meshes=[sph, grid], instances=inst))
     rc.SetGeometry(0, moved)  # same triangle count: refit of the GPU-built tree
     rc.UpdateToplevel()
