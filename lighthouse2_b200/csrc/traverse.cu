@@ -331,6 +331,12 @@ constexpr int WARPS_PER_BLOCK = BLOCK_THREADS / 32;
 #ifndef B200_FLUSH_AT
 #define B200_FLUSH_AT 24 // test the pending triangles as soon as 24 wait (32 per round at most): hit distances shrink earlier, +2 % over 32
 #endif
+#ifndef B200_STEAL
+#define B200_STEAL 0 // 1: at the end of a wave, lanes without a ray take over stack entries of the rays still walking (one-instance kernels; see "work
+                     // donation" in the pass).  Correct (the parity suite passes with it) and measured: the isolated 1080p bounce waves gain 5 %
+                     // (2185 -> 2299 Mrays/s), frames gain nothing (their chains already fill each other's tails) and the large waves lose 2.7 % to
+                     // the extra state in the pass (4K frame 127.0 -> 130.4 ms).  Off.
+#endif
 #ifndef B200_DRAIN_PREFETCH
 #define B200_DRAIN_PREFETCH 0 // n > 0: a warp that has run out of rays and has fewer than n lanes active prefetches its next node (see B' in the pass)
 #endif
@@ -351,6 +357,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
 	__shared__ uint32_t sSlot[BLOCK_THREADS];        // winner of a test round: (leaf-order triangle index << 5 | tester lane), 0xffffffff = none
 	__shared__ uint32_t sBestTri[BLOCK_THREADS];     // leaf-order index of the triangle of each lane's current hit (tie rule, see intersectTriangle)
+	__shared__ uint32_t sHelp[BLOCK_THREADS];        // work donation: helpers still walking for this lane's ray; bit 31: the ray is over (any-hit), helpers stop
 	__shared__ float4 sWorld[SINGLE ? 1 : BLOCK_THREADS]; // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
 	__shared__ float4 sWorldO[SINGLE ? 1 : BLOCK_THREADS], sWorldD[SINGLE ? 1 : BLOCK_THREADS]; // ... and the ray itself (re-reading the ray planes there cost 2 %)
 	__shared__ uint2 sRing[WARPS_PER_BLOCK][RING_CAP]; // leaf records: (first triangle | owner lane << 27, 24-bit triangle mask)
@@ -372,7 +379,11 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	uint32_t pendingTris = 0;          // triangles in the ring (warp-uniform)
 	uint32_t lastQueued = 0xffffffffu; // sequence number of this lane's newest record
 	bool active = false, exhausted = false, terminated = false, finished = false;
+	constexpr bool STEAL = B200_STEAL && SINGLE && !COUNT;
+	bool helping = false;            // this lane walks a donated part of another lane's ray
+	uint32_t ownerLane = lane;       // the lane whose ray this lane's triangle records belong to (its own, unless helping)
 	sSlot[threadIdx.x] = 0xffffffffu;
+	sHelp[threadIdx.x] = 0;
 	if (a.fetchCounterNext && blockIdx.x == 0 && threadIdx.x == 0) *a.fetchCounterNext = 0;
 
 	auto push = [&]( const uint2 g ) {
@@ -464,16 +475,19 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				r.t = wT, hitPrim = wPrim, hitBary = wBary;
 				if (!SINGLE) hitInst = curInst;
 				if (ANYHIT) terminated = true, ngroup.y = 0, tgroup.y = 0;
+				if (ANYHIT && STEAL) atomicOr( &sHelp[threadIdx.x], 0x80000000u );
 			}
 		}
 		__syncwarp();
+		if (STEAL && helping)
+		{
+			// a helper culls against the distance of the ray it works for (kept in the mirror by the atomics above)
+			r.t = sRayD[warpBase + ownerLane].w;
+			if (ANYHIT && (sHelp[warpBase + ownerLane] & 0x80000000u)) ngroup.y = 0, tgroup.y = 0, sp = 0;
+		}
 	};
 
-	while (true)
-	{
-		// ---- results of the lanes that retired since the last fetch ------------------------------------
-		if (finished)
-		{
+	auto writeResult = [&]() {
 			if (ANYHIT)
 			{
 				if (a.accumulator)
@@ -501,7 +515,12 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 			}
 			if (COUNT) a.stepNodes[rayIdx] = nNodes, a.stepTris[rayIdx] = nTris;
 			finished = false;
-		}
+	};
+
+	while (true)
+	{
+		// ---- results of the lanes that retired since the last fetch ------------------------------------
+		if (finished) writeResult();
 		// ---- ray fetch: idle lanes claim consecutive rays with one aggregated atomic ------------------
 		const uint32_t idleMask = __ballot_sync( 0xffffffffu, !active );
 		if (idleMask && !exhausted)
@@ -542,6 +561,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					hitPrim = 0xffffffffu, hitInst = 0, hitBary = 0, nNodes = nTris = 0;
 					lastQueued = qhead - 1, terminated = false;
 					sBestTri[threadIdx.x] = 0xffffffffu;
+					if (STEAL) sHelp[threadIdx.x] = 0;
 					active = true;
 				}
 			}
@@ -553,6 +573,46 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 		uint32_t votes = 0x00202000u; // "32 lanes active, 32 with work, none waiting": the first pass of a round decides nothing
 		while (true)
 		{
+			// Work donation.  When the wave has no rays left to hand out, its end is a few long rays walking alone, each pass one dependent
+			// chain at memory latency, while the other lanes of their warps idle (T(n) = 38 us + n / 3.27 Grays/s: the constant).  An idle lane
+			// then takes the newest stack entry of a lane that still walks and traverses that subtree FOR the same ray: the ray is in the
+			// shared-memory mirror anyway (the triangle testers read it there), hits come home through the mirror's atomicMin and the owner's
+			// slot word exactly as a tester's do, and the owner retires only when its helpers have.  Which lane finds a hit never shows in
+			// the result (tie rule, cull margin).  One-instance kernels only: a helper works in the instance's space, which the owner of a
+			// two-level ray leaves and re-enters.
+			if (STEAL && exhausted)
+			{
+				if (ANYHIT && helping && (sHelp[warpBase + ownerLane] & 0x80000000u)) ngroup.y = 0, tgroup.y = 0, sp = 0; // the shadow ray has found its occluder
+				if (finished) writeResult(); // (a retired lane's result still sits in the registers a helper needs)
+				const uint32_t idleMask = __ballot_sync( 0xffffffffu, !active );
+				if (idleMask)
+				{
+					const bool canGive = active && !terminated && sp > 0;
+					const uint32_t donorMask = __ballot_sync( 0xffffffffu, canGive );
+					if (donorMask)
+					{
+						const uint32_t pairs = min( __popc( idleMask ), __popc( donorMask ) );
+						uint2 g = make_uint2( 0, 0 );
+						if (canGive && (uint32_t)__popc( donorMask & lanemask_lt() ) < pairs) g = pop();
+						const uint32_t rank = __popc( idleMask & lanemask_lt() );
+						const bool take = !active && rank < pairs;
+						const uint32_t from = take ? __fns( donorMask, 0, rank + 1 ) : lane;
+						const uint32_t gx = __shfl_sync( 0xffffffffu, g.x, from ), gy = __shfl_sync( 0xffffffffu, g.y, from );
+						const uint32_t forLane = __shfl_sync( 0xffffffffu, ownerLane, from );
+						if (take)
+						{
+							ownerLane = forLane, helping = true;
+							const float4 O4 = sRayO[warpBase + ownerLane], D4 = sRayD[warpBase + ownerLane];
+							r.ox = O4.x, r.oy = O4.y, r.oz = O4.z, r.tmin = O4.w, r.dx = D4.x, r.dy = D4.y, r.dz = D4.z, r.t = D4.w;
+							setupSlab( r );
+							ngroup = make_uint2( gx, gy ), tgroup = make_uint2( 0, 0 );
+							sp = 0, lastQueued = qhead - 1, terminated = false, active = true;
+							atomicAdd( &sHelp[warpBase + ownerLane], 1u );
+						}
+						__syncwarp();
+					}
+				}
+			}
 			// A. top level: a hit leaf is an instance -- remember what is left here, then descend into its BLAS (its root is visited
 			//    by step B of the same pass)
 			if (!SINGLE && active && instBase < 0 && tgroup.y)
@@ -617,7 +677,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 					if (has)
 					{
 						lastQueued = qtail + __popc( m & lanemask_lt() );
-						ring[lastQueued & (RING_CAP - 1)] = make_uint2( tgroup.x | (lane << 27), tgroup.y );
+						ring[lastQueued & (RING_CAP - 1)] = make_uint2( tgroup.x | ((STEAL ? ownerLane : lane) << 27), tgroup.y );
 						if (COUNT) nTris += __popc( tgroup.y );
 					}
 					pendingTris += __reduce_add_sync( 0xffffffffu, has ? (uint32_t)__popc( tgroup.y ) : 0u );
@@ -637,6 +697,13 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 				const bool pending = (int32_t)(lastQueued - qhead) >= 0;
 				const bool leaving = terminated || sp == (SINGLE ? 0 : instBase);
 				if (leaving && pending) waiting = true;
+				else if (STEAL && helping && (terminated || sp == 0))
+				{
+					// a helper is done when its subtree is and its records are tested: it reports back and is idle again
+					atomicSub( &sHelp[warpBase + ownerLane], 1u );
+					active = false, helping = false, ownerLane = lane;
+				}
+				else if (STEAL && (terminated || sp == 0) && (sHelp[threadIdx.x] & 0x7fffffffu)) waiting = true; // the ray's helpers are still walking
 				else if (terminated || sp == 0) active = false, finished = true;
 				else
 				{
