@@ -357,7 +357,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	__shared__ float4 sRayD[BLOCK_THREADS];          //                                  (dx,dy,dz,t); .w is ATOMS.MIN'ed as uint bits
 	__shared__ uint32_t sSlot[BLOCK_THREADS];        // winner of a test round: (leaf-order triangle index << 5 | tester lane), 0xffffffff = none
 	__shared__ uint32_t sBestTri[BLOCK_THREADS];     // leaf-order index of the triangle of each lane's current hit (tie rule, see intersectTriangle)
-	__shared__ uint32_t sHelp[BLOCK_THREADS];        // work donation: helpers still walking for this lane's ray; bit 31: the ray is over (any-hit), helpers stop
+	__shared__ uint32_t sHelp[B200_STEAL && SINGLE ? BLOCK_THREADS : 1]; // work donation: helpers still walking for this lane's ray; bit 31: the ray is over (any-hit), helpers stop
 	__shared__ float4 sWorld[SINGLE ? 1 : BLOCK_THREADS]; // world-space (1/d, octant) of each lane's ray, restored when it leaves an instance
 	__shared__ float4 sWorldO[SINGLE ? 1 : BLOCK_THREADS], sWorldD[SINGLE ? 1 : BLOCK_THREADS]; // ... and the ray itself (re-reading the ray planes there cost 2 %)
 	__shared__ uint2 sRing[WARPS_PER_BLOCK][RING_CAP]; // leaf records: (first triangle | owner lane << 27, 24-bit triangle mask)
@@ -383,7 +383,7 @@ __global__ void __launch_bounds__( BLOCK_THREADS, B200_MIN_BLOCKS ) traceKernel(
 	bool helping = false;            // this lane walks a donated part of another lane's ray
 	uint32_t ownerLane = lane;       // the lane whose ray this lane's triangle records belong to (its own, unless helping)
 	sSlot[threadIdx.x] = 0xffffffffu;
-	sHelp[threadIdx.x] = 0;
+	if (STEAL) sHelp[threadIdx.x] = 0;
 	if (a.fetchCounterNext && blockIdx.x == 0 && threadIdx.x == 0) *a.fetchCounterNext = 0;
 
 	auto push = [&]( const uint2 g ) {
