@@ -66,6 +66,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-waves", action="store_true")
     ap.add_argument("--no-refit", action="store_true")
+    ap.add_argument("--no-filter", action="store_true")
     ap.add_argument("--no-check", action="store_true", help="skip the bit-identity check of the gathered frame")
     ap.add_argument("--gather", default="auto", choices=["auto", "p2p", "nccl"])
     ap.add_argument("--setting", action="append", default=[], help="name=value, applied to the core before the scene is built")
@@ -597,6 +598,23 @@ def run_b200(args):
                              "launches": 1, "bytes_survey_formula": b, "gbs": b / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": b / (ms * 1e-3) / 1e9 / peak,
                              "bytes_with_writes": 144 * verts.shape[0] + 224 * nodes,
                              "note": "survey formula = 48 T + 2 x 80 x nodes; with the record / shading-normal writes and the per-node float boxes the kernel moves 144 T + 224 nodes"}
+        if world == 1 and not args.no_filter:
+            # filter mode (Setting filterCore: the reference's RenderCore_Optix7Filter -- one diffuse bounce, per-pixel features, SVGF-style
+            # reconstruction + TAA, filter.cu) on the same scene at the wave leg's size, 1 spp: device time of the filter and of the frame
+            rc.SetAccumulatorBuffer(0)  # (the one-rank renderer above rendered into a torch buffer: the filter keeps its own two planes)
+            rc.SetTarget(args.wave_width, args.wave_height, 1)
+            rc.Setting("filterCore", 1)
+            fview = scenes.view_pyramid(width=args.wave_width, height=args.wave_height, **scenes.C2_CAMERA)
+            fms, rms = [], []
+            for _ in range(8):
+                rc.Render(fview, converge=0)
+                fst = rc.GetCoreStats()
+                fms.append(fst["filterTime"]), rms.append(fst["renderTime"])
+            rc.Setting("filterCore", 0)
+            px = args.wave_width * args.wave_height
+            line["filter"] = {"workload": "C2 scene %dx%d x 1 spp in filter mode (TAA on)" % (args.wave_width, args.wave_height), "filter_ms": float(np.median(fms[2:])),
+                              "frame_ms": float(np.median(rms[2:])), "kernels": 6, "mpixels_s": px / (float(np.median(fms[2:])) * 1e-3) / 1e6,
+                              "note": "prepare is HBM-bound (78 % of the peak), the three reconstruction passes are issue-bound (profiles/r02_ncu_filter.txt)"}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_pass(args, verts, args.cpu_sample, steps=2, warmup=1)
             line["cpu_baseline"] = {"value": r["value"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
