@@ -99,6 +99,9 @@ B200_API int b200_trace_connect_device( b200_core* c, const void* dO4, const voi
 /* per-ray traversal counters of the LAST b200_trace_closest call with Setting("countSteps",1):
  * nodes visited and triangles tested (the analogue of the reference's `int* c`, bvh.cpp:259) */
 B200_API int b200_read_step_counters( b200_core* c, int n, uint32_t* nodesVisited, uint32_t* trisTested );
+/* the mesh trees as they lie in HBM (diagnostics; the reference keeps its BVH on the host, bvh.h:60-76): which = 0 the 80-byte wide
+ * nodes [0, b200_stats.wideNodeCount), 1 the 48-byte triangle records [0, b200_stats.triangleCount); bytes <= the used part */
+B200_API int b200_read_tree( b200_core* c, int which, void* dst, size_t bytes );
 
 /* ---- frame: SetTarget / SetLights / Render / GetCoreStats (core_api_base.h:84-96,102-105) ---- */
 B200_API int b200_set_target( b200_core* c, int width, int height, int spp );

@@ -21,7 +21,7 @@ CSRC = os.path.join(HERE, "csrc")
 C_ABI_SYMBOLS = [
     "b200_create", "b200_destroy", "b200_last_error", "b200_set_stream", "b200_set_geometry", "b200_set_instance",
     "b200_update_toplevel", "b200_refit", "b200_refit_device", "b200_setting", "b200_trace_closest", "b200_trace_any",
-    "b200_trace_closest_device", "b200_trace_any_device", "b200_read_step_counters", "b200_set_target",
+    "b200_trace_closest_device", "b200_trace_any_device", "b200_read_step_counters", "b200_read_tree", "b200_set_target",
     "b200_set_point_light", "b200_set_sky", "b200_set_lights", "b200_set_sky_data", "b200_render", "b200_read_accumulator", "b200_read_frame",
     "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
     "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors", "b200_set_material_table", "b200_set_textures",
@@ -89,7 +89,7 @@ def load_library() -> C.CDLL:
         "b200_setting": ([vp, C.c_char_p, C.c_float], ip),
         "b200_trace_closest": ([vp, vp, vp, ip, vp], ip), "b200_trace_any": ([vp, vp, vp, ip, vp], ip),
         "b200_trace_closest_device": ([vp, vp, vp, ip, vp], ip), "b200_trace_any_device": ([vp, vp, vp, ip, vp], ip),
-        "b200_read_step_counters": ([vp, ip, vp, vp], ip),
+        "b200_read_step_counters": ([vp, ip, vp, vp], ip), "b200_read_tree": ([vp, ip, vp, C.c_size_t], ip),
         "b200_set_target": ([vp, ip, ip, ip], ip), "b200_set_point_light": ([vp, vp, vp], ip), "b200_set_sky": ([vp, vp], ip),
         "b200_set_lights": ([vp, vp, ip, vp, ip, vp, ip, vp, ip], ip), "b200_set_sky_data": ([vp, vp, ip, ip], ip),
         "b200_render": ([vp, vp, ip], ip), "b200_read_accumulator": ([vp, vp], ip), "b200_read_frame": ([vp, vp], ip),
@@ -354,6 +354,15 @@ class RenderCoreB200:
 
     def TraceAnyDevice(self, dO4: int, dD4: int, n: int, dBits: int):
         self._chk(self.lib.b200_trace_any_device(self.h, dO4, dD4, n, dBits))
+
+    def ReadTree(self):
+        """(wide nodes uint32[n, 20], triangle records uint32[t, 12]) of the mesh trees as they lie in HBM."""
+        st = self.GetCoreStats()
+        nodes = np.empty((st["wideNodeCount"], 20), np.uint32)
+        tris = np.empty((st["triangleCount"], 12), np.uint32)
+        self._chk(self.lib.b200_read_tree(self.h, 0, nodes.ctypes.data, nodes.nbytes))
+        self._chk(self.lib.b200_read_tree(self.h, 1, tris.ctypes.data, tris.nbytes))
+        return nodes, tris
 
     def StepCounters(self, n: int):
         a = np.empty(n, np.uint32)

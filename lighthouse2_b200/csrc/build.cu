@@ -336,6 +336,10 @@ struct CollapseArgs {
 	uint32_t primOutStride;   //   first float4, stride 12 words; the top level: a plain array of instance ids)
 	uint32_t* counters;       // [0] wide nodes allocated, [1] leaf-order triangle slots allocated, [2] overflow flag
 	uint32_t nodeBase, triBase, maxNodes;
+	// deterministic placement (the mesh builder): levelTotals[i] = (inner children << 32 | leaf primitives) of all wide nodes of the level before the i-th;
+	// null = children and primitives are claimed with atomicAdd in whatever order the groups arrive (the one-block top-level build)
+	const unsigned long long* levelTotals;
+	uint32_t levelBegin, levelChildBase, levelPrimBase;
 };
 
 __device__ __forceinline__ void refBox( const CollapseArgs& a, const uint32_t ref, float lo[3], float hi[3], uint32_t& count )
@@ -486,12 +490,12 @@ __device__ void collapseNode( const CollapseArgs& a, const uint32_t w )
 // same sums in the same order, same strict-< scan order of the greedy slot assignment: the nodes are bit for bit those of
 // collapseNode (tests/test_parity_gpu.py holds the device-built top level against the host builder's).
 // Called by all eight lanes of a group together; `gmask` names them in the warp, `sub` = lane within the group.
-__device__ void collapseNodeGroup( const CollapseArgs& a, const uint32_t w, const uint32_t sub, const uint32_t gmask )
+// the forest the plan chose for wide node w (see collapseNode); the walk is the same in all eight lanes of the group, stack entry j lives in lane j,
+// child n goes to lane n.  Returns the number of children.
+__device__ __forceinline__ uint32_t forestWalk( const CollapseArgs& a, const uint32_t w, const uint32_t sub, const uint32_t gmask, const uint32_t gbase, uint32_t& myRef, uint32_t& myBits )
 {
-	const uint32_t gbase = (threadIdx.x & 31u) - sub;
 	const uint32_t root = a.wideToBinary[w];
-	// the forest the plan chose (see collapseNode); the walk is the same in all eight lanes, stack entry j lives in lane j, child n goes to lane n
-	uint32_t myRef = 0, myBits = 0, stRef = 0, stAllow = 0;
+	uint32_t stRef = 0, stAllow = 0;
 	uint32_t n = 0, sp = 2;
 	{
 		const uint32_t k8 = (__float_as_uint( a.planHi[root].w ) >> 18) & 7u;
@@ -522,6 +526,28 @@ __device__ void collapseNodeGroup( const CollapseArgs& a, const uint32_t w, cons
 			sp++;
 		}
 	}
+	return n;
+}
+
+// first pass of a level in the deterministic mode: how many inner children and leaf primitives wide node w will claim
+__device__ void collapseCountGroup( const CollapseArgs& a, const uint32_t w, const uint32_t sub, const uint32_t gmask, unsigned long long* __restrict__ out )
+{
+	const uint32_t gbase = (threadIdx.x & 31u) - sub;
+	uint32_t myRef = 0, myBits = 0;
+	const uint32_t n = forestWalk( a, w, sub, gmask, gbase, myRef, myBits );
+	const bool have = sub < n, inner = have && !(myRef & LEAF) && !((myBits >> 21) & 1u);
+	uint32_t leafPrims = (have && !inner) ? ((myRef & LEAF) ? 1u : a.rangeCount[myRef]) : 0u;
+#pragma unroll
+	for (int d = 1; d < 8; d <<= 1) leafPrims += __shfl_xor_sync( gmask, leafPrims, d );
+	const uint32_t innerCount = __popc( (__ballot_sync( gmask, inner ) >> gbase) & 0xffu );
+	if (sub == 0) out[w - a.levelBegin] = ((unsigned long long)innerCount << 32) | leafPrims;
+}
+
+__device__ void collapseNodeGroup( const CollapseArgs& a, const uint32_t w, const uint32_t sub, const uint32_t gmask )
+{
+	const uint32_t gbase = (threadIdx.x & 31u) - sub;
+	uint32_t myRef = 0, myBits = 0;
+	const uint32_t n = forestWalk( a, w, sub, gmask, gbase, myRef, myBits );
 	const bool have = sub < n;
 	const bool inner = have && !(myRef & LEAF) && !((myBits >> 21) & 1u);
 	float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
@@ -578,8 +604,18 @@ __device__ void collapseNodeGroup( const CollapseArgs& a, const uint32_t w, cons
 	uint32_t childBase = 0, primBase = 0;
 	if (sub == 0)
 	{
-		childBase = innerCount ? atomicAdd( a.counters, innerCount ) : 0;
-		primBase = leafPrims ? atomicAdd( a.counters + 1, leafPrims ) : 0;
+		if (a.levelTotals)
+		{
+			// the level's nodes in order: what the nodes before this one claim is known (collapseCountGroup + a running sum)
+			const unsigned long long before = a.levelTotals[w - a.levelBegin];
+			childBase = a.levelChildBase + (uint32_t)(before >> 32), primBase = a.levelPrimBase + (uint32_t)before;
+			atomicMax( a.counters, childBase + innerCount ), atomicMax( a.counters + 1, primBase + leafPrims ); // (the level's last node leaves the totals)
+		}
+		else
+		{
+			childBase = innerCount ? atomicAdd( a.counters, innerCount ) : 0;
+			primBase = leafPrims ? atomicAdd( a.counters + 1, leafPrims ) : 0;
+		}
 	}
 	childBase = __shfl_sync( gmask, childBase, gbase ), primBase = __shfl_sync( gmask, primBase, gbase );
 	if (childBase + innerCount > a.maxNodes) { if (sub == 0) atomicExch( a.counters + 2, 1u ); return; }
@@ -620,6 +656,12 @@ __device__ void collapseNodeGroup( const CollapseArgs& a, const uint32_t w, cons
 		np[1] = make_uint4( a.nodeBase + childBase, a.triBase + primBase, metaLo, metaHi );
 		np[2] = np[3] = np[4] = make_uint4( 0, 0, 0, 0 );
 	}
+}
+
+__global__ void collapseCountKernel( const CollapseArgs a, const uint32_t levelBegin, const uint32_t levelEnd, unsigned long long* __restrict__ out )
+{
+	const uint32_t w = levelBegin + (blockIdx.x * blockDim.x + threadIdx.x) / 8, sub = threadIdx.x & 7u;
+	if (w < levelEnd) collapseCountGroup( a, w, sub, 0xffu << ((threadIdx.x & 31u) - sub), out );
 }
 
 __global__ void collapseKernel( const CollapseArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
@@ -868,6 +910,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 		a.primLo = sc.primLo, a.primHi = sc.primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = planHi;
 		a.wideToBinary = wideToBinary, a.nodes = nodes, a.primOut = sc.instOrder, a.primOutStride = 1, a.counters = sCounters;
 		a.nodeBase = nodeBase, a.triBase = 0, a.maxNodes = maxNodes;
+		a.levelTotals = nullptr, a.levelBegin = a.levelChildBase = a.levelPrimBase = 0;
 		if (tid == 0) wideToBinary[0] = 0, sLevel[0] = 0, sLevels = 0;
 		__syncthreads();
 		uint32_t begin = 0, end = 1;
@@ -988,6 +1031,10 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	const size_t oParI = take( (size_t)T * 4 ), oParL = take( (size_t)T * 4 ), oVisits = take( (size_t)T * 4 );
 	const size_t oNodeLo = take( (size_t)T * 16 ), oNodeHi = take( (size_t)T * 16 ), oPlanLo = take( (size_t)T * 16 ), oPlanHi = take( (size_t)T * 16 );
 	const size_t oW2B = take( (size_t)maxNodes * 4 + 64 ), oSmall = take( 256 );
+	// per-level claims of the collapse and their running sum (children << 32 | primitives per wide node)
+	size_t totalBytes = 0;
+	cub::DeviceScan::ExclusiveSum( nullptr, totalBytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)maxNodes, s );
+	const size_t oClaims = take( (size_t)maxNodes * 8 ), oTotals = take( (size_t)maxNodes * 8 ), oTotalScan = take( totalBytes );
 	// the agglomerative builder: two sets of clusters (reference + box), nearest neighbours, survivor flags and their running sum
 	const bool ploc = builder == 2;
 	size_t scanBytes = 0;
@@ -1055,18 +1102,32 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	a.primLo = primLo, a.primHi = primHi, a.nodeLo = nodeLo, a.nodeHi = nodeHi, a.planHi = planHi;
 	a.wideToBinary = w2b, a.nodes = nodes, a.primOut = reinterpret_cast<uint32_t*>( tris ) + 3, a.primOutStride = 12, a.counters = counters;
 	a.nodeBase = nodeBase, a.triBase = triBase, a.maxNodes = maxNodes;
+	unsigned long long *claims = (unsigned long long*)(scratch + oClaims), *totals = (unsigned long long*)(scratch + oTotals);
+	a.levelTotals = B200_USE_GROUP_COLLAPSE ? totals : nullptr, a.levelBegin = 0, a.levelChildBase = 1, a.levelPrimBase = 0;
 	levelStart.clear();
 	levelStart.push_back( 0 );
 	uint32_t begin = 0, end = 1;
 	while (begin < end)
 	{
-		collapseKernel<<<((end - begin) * (B200_USE_GROUP_COLLAPSE ? 8 : 1) + 127) / 128, 128, 0, s>>>( a, begin, end );
+		const uint32_t levelBlocks = ((end - begin) * (B200_USE_GROUP_COLLAPSE ? 8 : 1) + 127) / 128;
+		if (a.levelTotals)
+		{
+			// the same bytes every time: each node's place follows from the claims of the nodes before it in the level, not from the order
+			// in which the groups reach an atomicAdd.  Hits do not depend on the placement (traverse.cu's tie rule), but a rebuilt mesh and
+			// the copies of a mesh on several ranks then share one layout (same cache behaviour, comparable dumps), and siblings of
+			// neighbouring parents sit next to each other
+			a.levelBegin = begin;
+			collapseCountKernel<<<levelBlocks, 128, 0, s>>>( a, begin, end, claims );
+			if ((e = cub::DeviceScan::ExclusiveSum( scratch + oTotalScan, totalBytes, claims, totals, (int)(end - begin), s )) != cudaSuccess) return done( e );
+		}
+		collapseKernel<<<levelBlocks, 128, 0, s>>>( a, begin, end );
 		uint32_t h[3];
 		if ((e = cudaMemcpyAsync( h, counters, 12, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
 		if ((e = cudaStreamSynchronize( s )) != cudaSuccess) return done( e );
 		if (h[2] || h[0] > maxNodes) return done( cudaErrorMemoryAllocation ); // more wide nodes than reserved
 		levelStart.push_back( end );
 		begin = end, end = h[0];
+		a.levelChildBase = h[0], a.levelPrimBase = h[1];
 	}
 	nodeCount = end;
 	return done( cudaSuccess );

@@ -51,6 +51,7 @@ int b200_trace_closest_noalloc( b200_core* c, const float* O4, const float* D4, 
 int b200_trace_closest_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dHits ) { FORWARD( c, TraceClosestDevice( dO4, dD4, n, dHits ) ) }
 int b200_trace_any_device( b200_core* c, const void* dO4, const void* dD4, int n, void* dBits ) { FORWARD( c, TraceAnyDevice( dO4, dD4, n, dBits ) ) }
 int b200_read_step_counters( b200_core* c, int n, uint32_t* nodes, uint32_t* tris ) { FORWARD( c, ReadStepCounters( n, nodes, tris ) ) }
+int b200_read_tree( b200_core* c, int which, void* dst, size_t bytes ) { FORWARD( c, ReadTree( which, dst, bytes ) ) }
 
 // ---- the filter's stages on caller-owned DEVICE buffers (filter.cu); current device, default stream, synchronous
 static int filterDone( const char* what, cudaError_t e )

@@ -908,6 +908,16 @@ int RenderCore::ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris )
 	return 0;
 }
 
+int RenderCore::ReadTree( int which, void* dst, size_t bytes )
+{
+	// the mesh trees as they lie in HBM: 80-byte wide nodes [0, wideNodeCount) or 48-byte triangle records [0, triangleCount)
+	const DeviceBuffer& pool = which == 0 ? nodePool : triPool;
+	const size_t used = which == 0 ? (size_t)blasNodeEnd * 80 : (size_t)triEnd * 48;
+	if (which < 0 || which > 1 || bytes > used || !pool.ptr) return fail( "ReadTree: which = 0 (nodes) | 1 (triangles), bytes within the used part of the pool" );
+	const cudaError_t e = cudaMemcpy( dst, pool.ptr, bytes, cudaMemcpyDeviceToHost );
+	return e == cudaSuccess ? 0 : fail( "ReadTree", e );
+}
+
 void RenderCore::GetStats( b200_stats* out )
 {
 	// lastTraceMs of the device-pointer waves is resolved lazily here (the events may still be in flight)

@@ -100,6 +100,7 @@ public:
 	int TraceAnyDevice( const void* dO4, const void* dD4, int n, void* dBits, const uint32_t* dCount = nullptr );
 	int TraceConnectDevice( const void* dO4, const void* dD4, int n, const void* dE4, void* dAccumulator, const uint32_t* dCount = nullptr,
 		cudaStream_t onStream = nullptr, int counterSlot = 0 );
+	int ReadTree( int which, void* dst, size_t bytes );
 	int ReadStepCounters( int n, uint32_t* nodes, uint32_t* tris );
 	int Refit( int meshIdx, const float* vertexData, int vertexCount );
 	int RefitDevice( int meshIdx, const void* dVerts, int vertexCount, bool boundsKnown );

@@ -129,6 +129,23 @@ def test_refit_after_gpu_build_and_second_mesh():
     parity.assert_parity(rep)
 
 
+def test_gpu_built_tree_is_the_same_bytes_every_time():
+    """The device collapse places children and primitives by a running sum over the level (build.cu: collapseCountKernel + scan), not by
+    the order in which thread groups reach an atomic: the same mesh gives the same node and triangle bytes on every build."""
+    verts = scenes.triangle_soup(300_000, seed=5)
+    trees = []
+    for _ in range(3):
+        rc = core.RenderCoreB200(0)
+        rc.Setting("gpuBuild", BUILDER)
+        cases.load_core(rc, dict(meshes=[verts], instances=[(0, None)]))
+        trees.append(rc.ReadTree())
+        rc.Shutdown()
+    for nodes, tris in trees[1:]:
+        assert nodes.shape == trees[0][0].shape and np.array_equal(nodes, trees[0][0])
+        assert np.array_equal(tris, trees[0][1])
+    assert np.array_equal(np.sort(trees[0][1][:, 3]), np.arange(verts.shape[0], dtype=np.uint32))  # every primitive exactly once
+
+
 def test_bvh_disk_cache_round_trip(tmp_path):
     """B200_BVH_CACHE (bvh_cache.cpp): the second core takes the host-built tree from disk and traces the
     same hits; a damaged file is ignored and rebuilt.  (The directory is read once per process: subprocesses.)"""
