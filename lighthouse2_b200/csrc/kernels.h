@@ -63,10 +63,11 @@ struct RefitArgs {
 };
 cudaError_t LaunchRefitTop( const RefitArgs& a, const uint32_t* levelStart, int nTop, cudaStream_t s ); // levels [0,nTop) in one launch
 cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t levelEnd, cudaStream_t s );
-// the whole tree in one launch (refit.cu::refitWalkKernel).  parentInfo / arrived: one word per node of the mesh each, filled once per topology by
-// LaunchRefitParents (nodes = pool pointer, nodeBase = the mesh's root)
-cudaError_t LaunchRefitParents( const uint4* nodes, uint32_t nodeBase, uint32_t nodeCount, uint32_t* parentInfo, uint32_t* arrived, cudaStream_t s );
-cudaError_t LaunchRefitWalk( const RefitArgs& a, uint32_t nodeCount, const uint32_t* parentInfo, uint32_t* arrived, cudaStream_t s );
+// the whole tree in one launch (refit.cu::refitWalkKernel).  parentInfo / arrived / stashOf: one word per node of the mesh each, filled once per
+// topology by LaunchRefitParents (nodes = pool pointer, nodeBase = the mesh's root), which also leaves in *stashCount (device) the number of
+// nodes with inner children; stash = 16 float4 (the eight slot boxes) for each of those
+cudaError_t LaunchRefitParents( const uint4* nodes, uint32_t nodeBase, uint32_t nodeCount, uint32_t* parentInfo, uint32_t* arrived, uint32_t* stashOf, uint32_t* stashCount, cudaStream_t s );
+cudaError_t LaunchRefitWalk( const RefitArgs& a, uint32_t nodeCount, const uint32_t* parentInfo, uint32_t* arrived, const uint32_t* stashOf, float4* stash, cudaStream_t s );
 
 // ---- GPU build of the wide-BVH topology (build.cu); the caller runs the refit afterwards -----------------------
 cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, float4* tris, uint32_t nodeBase, uint32_t triBase, uint32_t maxNodes,

@@ -32,10 +32,11 @@ __device__ __forceinline__ uint32_t frameOf( float lo, float hi, float& p )
 	p = lo;
 	if (ext > 0)
 	{
-		// frexp( ext / 254.75 ): the exponent field of the double (no denormals here: ext comes from floats), + 1 for the [0.5, 1) mantissa
-		const int fe = ((__double2hiint( ext / 254.75 ) >> 20) & 0x7ff) - 1022;
-		ex = fe;
-		if (pow2( ex - 1 ) * 254.75 >= ext) ex--;
+		// QuantiseFrame's frexp( ext / 254.75 ) and its m == 0.5 correction amount to: the smallest ex with 254.75 * 2^ex >= ext.  With
+		// ext = m * 2^E, m in [1, 2) (no denormals here: ext comes from floats) and 254.75 = 1.990234375 * 2^7 that is E - 7 or E - 6,
+		// decided by one exact product: no division
+		ex = ((__double2hiint( ext ) >> 20) & 0x7ff) - 1023 - 7;
+		if (pow2( ex ) * 254.75 < ext) ex++;
 		if (ex < -100) ex = -100;
 		p = (float)((double)lo - pow2( ex - 3 ));
 	}
@@ -51,54 +52,52 @@ __device__ __forceinline__ void quantise( float p, uint32_t e, float lo, float h
 	qhi = (uint32_t)(h < 0 ? 0 : (h > 255 ? 255 : h));
 }
 
-// one child slot of one node; all 8 lanes of a node's group call this together (valid or not), groups are 8-aligned in the warp
-template <bool COHERENT /* child boxes come from groups of the same launch: read them from L2 */>
-__device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t node, const uint32_t s, const bool valid, const uint32_t levelBegin, const uint32_t mask = 0xffffffffu )
+// a leaf slot: the lane owns the slot's <= 3 triangles.  Gathers their new vertices ONCE (original primitive order), rewrites the
+// leaf-order records {v0|prim, e1, e2} and the shading normal, and bounds them.  (All the primitive indices first, then all the vertices:
+// one round trip to memory each for the slot, not one per triangle.)
+__device__ __forceinline__ void leafSlotBox( const RefitArgs& a, const uint4 n1, const uint32_t meta, float lo[3], float hi[3] )
 {
-	const uint32_t n = valid ? node : levelBegin;
-	uint4* np = a.nodes + (size_t)(a.nodeBase + n) * 5;
-	const uint4 n0 = np[0], n1 = np[1];
-	const uint32_t imask = n0.w >> 24;
-	const uint32_t meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
-	float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
-	if (meta)
+	const uint32_t cnt = __popc( meta >> 5 ), first = n1.y + (meta & 31u);
+	float4* const tp0 = a.tris + (size_t)first * 3;
+	uint32_t prims[3];
+	float4 v[3][3];
+#pragma unroll
+	for (uint32_t k = 0; k < 3; k++) prims[k] = k < cnt ? __float_as_uint( tp0[k * 3].w ) : 0u;
+#pragma unroll
+	for (uint32_t k = 0; k < 3; k++) if (k < cnt)
 	{
-		if (imask & (1u << s))
-		{
-			// absolute child index -> index relative to this mesh's scratch
-			const uint32_t child = n1.x + __popc( imask & ((1u << s) - 1u) ) - a.nodeBase;
-			const float4 cl = COHERENT ? __ldcg( a.nodeLo + child ) : a.nodeLo[child], ch = COHERENT ? __ldcg( a.nodeHi + child ) : a.nodeHi[child];
-			lo[0] = cl.x, lo[1] = cl.y, lo[2] = cl.z, hi[0] = ch.x, hi[1] = ch.y, hi[2] = ch.z;
-		}
-		else
-		{
-			// leaf slot: this lane owns the slot's <= 3 triangles.  Gather their new vertices ONCE (original primitive order),
-			// rewrite the leaf-order records {v0|prim, e1, e2} and the shading normal, and bound them.
-			const uint32_t cnt = __popc( meta >> 5 ), first = n1.y + (meta & 31u);
-			for (uint32_t k = 0; k < cnt; k++)
-			{
-				float4* tp = a.tris + (size_t)(first + k) * 3;
-				const uint32_t prim = __float_as_uint( tp[0].w );
-				const float4* vp = a.verts + (size_t)prim * 3;
-				const float4 p0 = __ldg( vp ), p1 = __ldg( vp + 1 ), p2 = __ldg( vp + 2 );
-				const float e1x = p1.x - p0.x, e1y = p1.y - p0.y, e1z = p1.z - p0.z, e2x = p2.x - p0.x, e2y = p2.y - p0.y, e2z = p2.z - p0.z;
-				tp[0] = make_float4( p0.x, p0.y, p0.z, __uint_as_float( prim ) );
-				tp[1] = make_float4( e1x, e1y, e1z, 0.f );
-				tp[2] = make_float4( e2x, e2y, e2z, 0.f );
-				if (a.shade)
-				{
-					float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
-					const float l2 = nx * nx + ny * ny + nz * nz, il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
-					float4* sp = a.shade + a.triBase + prim;
-					*sp = make_float4( nx * il, ny * il, nz * il, sp->w );
-				}
-				lo[0] = fminf( lo[0], fminf( p0.x, fminf( p1.x, p2.x ) ) ), lo[1] = fminf( lo[1], fminf( p0.y, fminf( p1.y, p2.y ) ) );
-				lo[2] = fminf( lo[2], fminf( p0.z, fminf( p1.z, p2.z ) ) );
-				hi[0] = fmaxf( hi[0], fmaxf( p0.x, fmaxf( p1.x, p2.x ) ) ), hi[1] = fmaxf( hi[1], fmaxf( p0.y, fmaxf( p1.y, p2.y ) ) );
-				hi[2] = fmaxf( hi[2], fmaxf( p0.z, fmaxf( p1.z, p2.z ) ) );
-			}
-		}
+		const float4* vp = a.verts + (size_t)prims[k] * 3;
+		v[k][0] = __ldg( vp ), v[k][1] = __ldg( vp + 1 ), v[k][2] = __ldg( vp + 2 );
 	}
+#pragma unroll
+	for (uint32_t k = 0; k < 3; k++) if (k < cnt)
+	{
+		float4* tp = tp0 + k * 3;
+		const uint32_t prim = prims[k];
+		const float4 p0 = v[k][0], p1 = v[k][1], p2 = v[k][2];
+		const float e1x = p1.x - p0.x, e1y = p1.y - p0.y, e1z = p1.z - p0.z, e2x = p2.x - p0.x, e2y = p2.y - p0.y, e2z = p2.z - p0.z;
+		tp[0] = make_float4( p0.x, p0.y, p0.z, __uint_as_float( prim ) );
+		tp[1] = make_float4( e1x, e1y, e1z, 0.f );
+		tp[2] = make_float4( e2x, e2y, e2z, 0.f );
+		if (a.shade)
+		{
+			float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
+			const float l2 = nx * nx + ny * ny + nz * nz, il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
+			float4* sp = a.shade + a.triBase + prim;
+			*sp = make_float4( nx * il, ny * il, nz * il, sp->w );
+		}
+		lo[0] = fminf( lo[0], fminf( p0.x, fminf( p1.x, p2.x ) ) ), lo[1] = fminf( lo[1], fminf( p0.y, fminf( p1.y, p2.y ) ) );
+		lo[2] = fminf( lo[2], fminf( p0.z, fminf( p1.z, p2.z ) ) );
+		hi[0] = fmaxf( hi[0], fmaxf( p0.x, fmaxf( p1.x, p2.x ) ) ), hi[1] = fmaxf( hi[1], fmaxf( p0.y, fmaxf( p1.y, p2.y ) ) );
+		hi[2] = fmaxf( hi[2], fmaxf( p0.z, fmaxf( p1.z, p2.z ) ) );
+	}
+}
+
+// the boxes of the eight slots are known (lane s holds slot s; empty = inverted box): node box by an 8-lane shuffle reduction, the
+// node's frame, every lane's planes against it; lane 0 writes the frame and the float box for the parent.  All 8 lanes of the group.
+__device__ __forceinline__ void finishNode( const RefitArgs& a, const uint32_t n, const uint32_t s, const uint32_t mask, const uint32_t imask, const uint32_t meta,
+	const float lo[3], const float hi[3], const bool valid = true )
+{
 	float nlo[3], nhi[3];
 	for (int c = 0; c < 3; c++)
 	{
@@ -107,6 +106,7 @@ __device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t no
 		nlo[c] = l, nhi[c] = h;
 	}
 	if (!valid) return;
+	uint4* np = a.nodes + (size_t)(a.nodeBase + n) * 5;
 	uint32_t e[3], qlo[3] = { 0, 0, 0 }, qhi[3] = { 0, 0, 0 };
 	float fp[3];
 	for (int c = 0; c < 3; c++) e[c] = frameOf( nlo[c], nhi[c], fp[c] );
@@ -122,11 +122,35 @@ __device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t no
 	}
 }
 
+// one child slot of one node, level by level (the children's boxes come from an earlier launch or an earlier barrier); all 8 lanes of a
+// node's group call this together (valid or not), groups are 8-aligned in the warp
+__device__ __forceinline__ void refitSlot( const RefitArgs& a, const uint32_t node, const uint32_t s, const bool valid, const uint32_t levelBegin )
+{
+	const uint32_t n = valid ? node : levelBegin;
+	const uint4* np = a.nodes + (size_t)(a.nodeBase + n) * 5;
+	const uint32_t imask = np[0].w >> 24;
+	const uint4 n1 = np[1];
+	const uint32_t meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
+	float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+	if (meta)
+	{
+		if (imask & (1u << s))
+		{
+			// absolute child index -> index relative to this mesh's scratch
+			const uint32_t child = n1.x + __popc( imask & ((1u << s) - 1u) ) - a.nodeBase;
+			const float4 cl = a.nodeLo[child], ch = a.nodeHi[child];
+			lo[0] = cl.x, lo[1] = cl.y, lo[2] = cl.z, hi[0] = ch.x, hi[1] = ch.y, hi[2] = ch.z;
+		}
+		else leafSlotBox( a, n1, meta, lo, hi );
+	}
+	finishNode( a, n, s, 0xffffffffu, imask, meta, lo, hi, valid );
+}
+
 __global__ void refitLevelKernel( const RefitArgs a, const uint32_t levelBegin, const uint32_t levelEnd )
 {
 	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t node = levelBegin + (gid >> 3);
-	refitSlot<false>( a, node, gid & 7, node < levelEnd, levelBegin ); // whole 8-lane groups are valid or not, so the shuffles stay converged per group
+	refitSlot( a, node, gid & 7, node < levelEnd, levelBegin ); // whole 8-lane groups are valid or not, so the shuffles stay converged per group
 }
 
 // the small top levels in ONE launch: a single CTA walks them bottom-up with a block barrier between levels
@@ -139,16 +163,18 @@ __global__ void __launch_bounds__( 1024 ) refitTopKernel( const RefitArgs a, con
 		for (uint32_t i = threadIdx.x; i < ((slots + 1023u) & ~1023u); i += 1024)
 		{
 			const uint32_t node = begin + (i >> 3);
-			refitSlot<false>( a, node, i & 7, node < end, begin );
+			refitSlot( a, node, i & 7, node < end, begin );
 		}
 		__threadfence_block();
 		__syncthreads();
 	}
 }
 
-// parentInfo[n] = parent of node n (relative to the mesh's root; NO_PARENT for the root) | number of inner children of that parent << 28
+// parentInfo[n] = parent of node n (relative to the mesh's root; NO_PARENT for the root) | number of inner children of that parent << 28;
+// stashOf[n] = a dense number for every node WITH inner children (its place in the walk's slot-box stash); *stashCount = how many
 constexpr uint32_t NO_PARENT = 0x0fffffffu;
-__global__ void refitParentsKernel( const uint4* __restrict__ nodes, const uint32_t nodeBase, const uint32_t nodeCount, uint32_t* __restrict__ parentInfo, uint32_t* __restrict__ arrived )
+__global__ void refitParentsKernel( const uint4* __restrict__ nodes, const uint32_t nodeBase, const uint32_t nodeCount, uint32_t* __restrict__ parentInfo, uint32_t* __restrict__ arrived,
+	uint32_t* __restrict__ stashOf, uint32_t* stashCount )
 {
 	const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
 	if (n >= nodeCount) return;
@@ -157,50 +183,104 @@ __global__ void refitParentsKernel( const uint4* __restrict__ nodes, const uint3
 	const uint4* np = nodes + (size_t)(nodeBase + n) * 5;
 	const uint32_t imask = np[0].w >> 24, inner = __popc( imask ), first = np[1].x - nodeBase;
 	for (uint32_t k = 0; k < inner; k++) parentInfo[first + k] = n | (inner << 28);
+	stashOf[n] = inner ? atomicAdd( stashCount, 1u ) : 0xffffffffu;
 }
 
-// the whole tree in one launch: see the file comment.  Eight lanes per node; the four groups of a warp climb independently (group masks).
-__global__ void __launch_bounds__( 256 ) refitWalkKernel( const RefitArgs a, const uint32_t nodeCount, const uint32_t* __restrict__ parentInfo, uint32_t* arrived )
+// The whole tree in one launch: see the file comment.  Eight lanes per node; the four groups of a warp go their own ways (group masks).
+// Every group first does the triangles of its node's leaf slots -- that is the streaming part, and nothing in it waits for anybody.
+// A node without inner children is finished with that.  A node WITH inner children parks its leaf-slot boxes in the stash and counts as
+// one more arrival at itself; whoever arrives last at a node -- its own group or the group that brings the last child -- finishes it
+// (child boxes from the scratch boxes, leaf-slot boxes from the stash) and goes on to the parent.
+__global__ void __launch_bounds__( 256, 4 ) refitWalkKernel( const RefitArgs a, const uint32_t nodeCount, const uint32_t* __restrict__ parentInfo, uint32_t* arrived,
+	const uint32_t* __restrict__ stashOf, float4* stash )
 {
 	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, s = lane & 7;
 	const uint32_t mask = 0xffu << (lane & 24);
-	uint32_t node = gid >> 3;
-	if (node >= nodeCount) return; // (whole groups)
-	if (a.nodes[(size_t)(a.nodeBase + node) * 5].w >> 24) return; // has inner children: the group that brings the last of them continues here
-	while (true)
+	if ((gid >> 3) >= nodeCount) return; // (whole groups)
+	// deepest nodes first (nodes are stored breadth-first): their way up is the longest and runs beside the triangle work of the shallower ones
+	uint32_t node = nodeCount - 1 - (gid >> 3);
+	const uint4* np = a.nodes + (size_t)(a.nodeBase + node) * 5;
+	uint32_t imask = np[0].w >> 24;
+	uint4 n1 = np[1];
+	uint32_t info = __ldg( parentInfo + node );
+	uint32_t meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
+	float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+	if (meta && !(imask & (1u << s))) leafSlotBox( a, n1, meta, lo, hi );
+	bool own = true; // the slot boxes in lo / hi are this group's own work (not yet: the children's)
+	if (imask)
 	{
-		refitSlot<true>( a, node, s, true, 0, mask );
-		const uint32_t info = __ldg( parentInfo + node ), parent = info & NO_PARENT;
-		if (parent == NO_PARENT) return;
-		// the node's box and planes must be visible before the arrival is: every lane fences its own stores, then one lane counts
-		__threadfence();
+		float4* st = stash + (size_t)__ldg( stashOf + node ) * 16;
+		st[s] = make_float4( lo[0], lo[1], lo[2], 0 ), st[8 + s] = make_float4( hi[0], hi[1], hi[2], 0 );
 		__syncwarp( mask );
 		uint32_t last = 0;
 		if (s == 0)
 		{
-			last = atomicAdd( arrived + parent, 1u ) + 1 == (info >> 28) ? 1u : 0u;
-			if (last) arrived[parent] = 0; // ready for the next refit (nobody else touches this counter any more)
+			__threadfence(); // (cumulative: the seven other lanes' stash stores are ordered before it by the barrier)
+			last = atomicAdd( arrived + node, 1u ) == __popc( imask ) ? 1u : 0u;
+			if (last) __threadfence(), arrived[node] = 0; // (the fence before the reset: it then has no store of ours to wait for)
 		}
-		last = __shfl_sync( mask, last, lane & 24 );
-		if (!last) return;
-		__threadfence();
-		node = parent;
+		if (!__shfl_sync( mask, last, lane & 24 )) return;
+	}
+	while (true)
+	{
+		// (a) finish `node`: every child has delivered.  Inner slots take the child's box; leaf slots have theirs (own) or fetch it from the stash
+		if (meta)
+		{
+			if (imask & (1u << s))
+			{
+				const uint32_t child = n1.x + __popc( imask & ((1u << s) - 1u) ) - a.nodeBase; // absolute child index -> relative to this mesh's scratch
+				const float4 cl = __ldcg( a.nodeLo + child ), ch = __ldcg( a.nodeHi + child );
+				lo[0] = cl.x, lo[1] = cl.y, lo[2] = cl.z, hi[0] = ch.x, hi[1] = ch.y, hi[2] = ch.z;
+			}
+			else if (!own)
+			{
+				const float4* st = stash + (size_t)__ldg( stashOf + node ) * 16;
+				const float4 cl = __ldcg( st + s ), ch = __ldcg( st + 8 + s );
+				lo[0] = cl.x, lo[1] = cl.y, lo[2] = cl.z, hi[0] = ch.x, hi[1] = ch.y, hi[2] = ch.z;
+			}
+		}
+		// the way up is a chain of dependent round trips to L2; what does not depend on this node's result is asked for before it:
+		// the parent's topology words and its own parent link (nobody writes them before the last arrival -- and that may be us)
+		const uint32_t parent = info & NO_PARENT;
+		uint32_t pn0w = 0, pinfo = 0;
+		uint4 pn1 = make_uint4( 0, 0, 0, 0 );
+		if (parent != NO_PARENT)
+		{
+			const uint4* pp = a.nodes + (size_t)(a.nodeBase + parent) * 5;
+			pn0w = __ldcg( &pp[0].w ), pn1 = __ldcg( pp + 1 ), pinfo = __ldg( parentInfo + parent );
+		}
+		finishNode( a, node, s, mask, imask, meta, lo, hi );
+		if (parent == NO_PARENT) return;
+		// (b) deliver: the node's box (lane 0 wrote it) must be visible before the arrival is; the planes and the frame are read by nobody in this launch
+		uint32_t last = 0;
+		if (s == 0)
+		{
+			__threadfence();
+			last = atomicAdd( arrived + parent, 1u ) == (info >> 28) ? 1u : 0u; // (inner children + the parent's own group)
+			if (last) __threadfence(), arrived[parent] = 0; // the siblings' boxes are read after this; counter ready for the next refit (nobody else touches it any more)
+		}
+		if (!__shfl_sync( mask, last, lane & 24 )) return;
+		node = parent, imask = pn0w >> 24, n1 = pn1, info = pinfo, own = false;
+		meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
+		lo[0] = lo[1] = lo[2] = 3.0e38f, hi[0] = hi[1] = hi[2] = -3.0e38f;
 	}
 }
 
 } // namespace
 
-cudaError_t LaunchRefitParents( const uint4* nodes, uint32_t nodeBase, uint32_t nodeCount, uint32_t* parentInfo, uint32_t* arrived, cudaStream_t s )
+cudaError_t LaunchRefitParents( const uint4* nodes, uint32_t nodeBase, uint32_t nodeCount, uint32_t* parentInfo, uint32_t* arrived, uint32_t* stashOf, uint32_t* stashCount, cudaStream_t s )
 {
 	if (!nodeCount) return cudaSuccess;
-	refitParentsKernel<<<(nodeCount + 255) / 256, 256, 0, s>>>( nodes, nodeBase, nodeCount, parentInfo, arrived );
+	cudaError_t e = cudaMemsetAsync( stashCount, 0, 4, s );
+	if (e != cudaSuccess) return e;
+	refitParentsKernel<<<(nodeCount + 255) / 256, 256, 0, s>>>( nodes, nodeBase, nodeCount, parentInfo, arrived, stashOf, stashCount );
 	return cudaGetLastError();
 }
 
-cudaError_t LaunchRefitWalk( const RefitArgs& a, uint32_t nodeCount, const uint32_t* parentInfo, uint32_t* arrived, cudaStream_t s )
+cudaError_t LaunchRefitWalk( const RefitArgs& a, uint32_t nodeCount, const uint32_t* parentInfo, uint32_t* arrived, const uint32_t* stashOf, float4* stash, cudaStream_t s )
 {
 	if (!nodeCount) return cudaSuccess;
-	refitWalkKernel<<<(nodeCount * 8 + 255) / 256, 256, 0, s>>>( a, nodeCount, parentInfo, arrived );
+	refitWalkKernel<<<(nodeCount * 8 + 255) / 256, 256, 0, s>>>( a, nodeCount, parentInfo, arrived, stashOf, stash );
 	return cudaGetLastError();
 }
 

@@ -141,7 +141,7 @@ RenderCore::~RenderCore()
 	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &vnormPool, &instShadePool, &vertStage, &nodeLo, &nodeHi,
 		&stepNodes, &stepTris, &tlasIn, &tlasScratch, &tlasInfo };
 	for (DeviceBuffer* b : all) b->release();
-	for (MeshRec& m : meshes) m.refitParents.release(), m.refitArrived.release();
+	for (MeshRec& m : meshes) m.refitParents.release(), m.refitArrived.release(), m.refitStash.release();
 	tlasStage.release();
 	for (int i = 0; i < WAVE_SLOTS; i++) rayO[i].release(), rayD[i].release(), hitBuf[i].release(), bitBuf[i].release();
 	if (evA) cudaEventDestroy( evA );
@@ -314,7 +314,7 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 			return fail( "SetGeometry: rebuild (refit=0) is only supported for the most recently added mesh" );
 		// rebuild of the last mesh: drop it and fall through to a fresh build
 		blasNodeEnd = meshes[meshIdx].nodeBase, triEnd = meshes[meshIdx].triBase;
-		meshes.back().refitParents.release(), meshes.back().refitArrived.release();
+		meshes.back().refitParents.release(), meshes.back().refitArrived.release(), meshes.back().refitStash.release();
 		meshes.pop_back();
 	}
 	const double t0 = nowMs();
@@ -400,11 +400,18 @@ int RenderCore::Refit( int meshIdx, const float* vertexData, int vertexCount )
 int RenderCore::prepareRefit( MeshRec& m )
 {
 	cudaError_t e;
-	if ((e = m.refitParents.reserve( (size_t)(m.nodeCount + 1) * 4, false, stream )) != cudaSuccess || (e = m.refitArrived.reserve( (size_t)(m.nodeCount + 1) * 4, false, stream )) != cudaSuccess)
+	// refitParents = parent links | stash numbers | their count (one buffer); the stash holds the eight slot boxes of every node with inner children
+	const size_t n1 = (size_t)m.nodeCount + 1;
+	if ((e = m.refitParents.reserve( (2 * n1 + 1) * 4, false, stream )) != cudaSuccess || (e = m.refitArrived.reserve( n1 * 4, false, stream )) != cudaSuccess)
 		return fail( "refit links", e );
-	if ((e = LaunchRefitParents( (const uint4*)nodePool.ptr, m.nodeBase, m.nodeCount, (uint32_t*)m.refitParents.ptr, (uint32_t*)m.refitArrived.ptr, stream )) != cudaSuccess)
+	uint32_t* links = (uint32_t*)m.refitParents.ptr;
+	if ((e = LaunchRefitParents( (const uint4*)nodePool.ptr, m.nodeBase, m.nodeCount, links, (uint32_t*)m.refitArrived.ptr, links + n1, links + 2 * n1, stream )) != cudaSuccess)
 		return fail( "refit links", e );
 	stats.kernelLaunches++;
+	uint32_t innerNodes = 0;
+	if ((e = cudaMemcpyAsync( &innerNodes, links + 2 * n1, 4, cudaMemcpyDeviceToHost, stream )) != cudaSuccess || (e = cudaStreamSynchronize( stream )) != cudaSuccess)
+		return fail( "refit links", e );
+	if ((e = m.refitStash.reserve( ((size_t)innerNodes + 1) * 256, false, stream )) != cudaSuccess) return fail( "refit stash", e );
 	return 0;
 }
 
@@ -423,8 +430,9 @@ int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, b
 	cudaEventRecord( evA, stream );
 	if (refitWalk && m.refitParents.ptr)
 	{
-		// one launch: groups start at the nodes without inner children and climb
-		if ((e = LaunchRefitWalk( a, m.nodeCount, (const uint32_t*)m.refitParents.ptr, (uint32_t*)m.refitArrived.ptr, stream )) != cudaSuccess) return fail( "refit", e );
+		// one launch: every group does its node's triangles, the last to arrive at a node finishes it and climbs
+		const uint32_t* links = (const uint32_t*)m.refitParents.ptr;
+		if ((e = LaunchRefitWalk( a, m.nodeCount, links, (uint32_t*)m.refitArrived.ptr, links + m.nodeCount + 1, (float4*)m.refitStash.ptr, stream )) != cudaSuccess) return fail( "refit", e );
 		stats.kernelLaunches++;
 	}
 	else
