@@ -623,7 +623,7 @@ def run_b200(args):
             rc.Setting("countSteps", 1)
             line["steps_per_ray"] = {}
             for w in waves:
-                if w["kind"] == "closest":
+                if w["kind"] in ("closest", "any"):  # (shadow rays counted as closest-hit rays over their segment: the walk without the early exit)
                     rc.TraceClosest(w["O4"], w["D4"])
                     nn, nt = rc.StepCounters(w["n"])
                     line["steps_per_ray"][f"{w['cls']}{w['bounce']}"] = {"nodes": float(nn.mean()), "tris": float(nt.mean()), "nodes_max": int(nn.max()),

@@ -211,6 +211,179 @@ __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, cons
 	}
 }
 
+// ---- 3c. SAH bottoms under the radix tree (builder 3).  The Morton splits are good at cutting a scene into compact chunks and poor at
+// the last levels, where the order along the curve, not the surface area, decides which triangles share a node -- and that is where the
+// rays spend their steps (the host builder's trees trace 4 % faster than the radix tree's; a SAH top over radix subtrees changed nothing:
+// profiles/r02_experiments.md).  So: every maximal radix subtree of at most SAHB_CLUSTER triangles is rebuilt from its root down by
+// binned SAH (16 bins on each axis, the split with the smallest area * count sum over the three axes), one warp per subtree, the
+// triangles' boxes in shared memory.  The new subtree lives in the places of the old one: the radix subtree over sorted positions
+// [f, l] rooted at r uses the inner-node indices [f, l] without one end, r is one of the ends, so [f + 1, l - 1] are free for the
+// others; the sorted order is permuted inside [f, l] only.  binaryBoxesKernel and the collapse then run as for the plain radix tree.
+#ifndef SAHB_CLUSTER
+#define SAHB_CLUSTER 256
+#endif
+#ifndef SAHB_BINS_N
+#define SAHB_BINS_N 16
+#endif
+constexpr int SAHB_BINS = SAHB_BINS_N, SAHB_WARPS = SAHB_CLUSTER <= 256 ? 4 : (SAHB_CLUSTER <= 512 ? 2 : 1); // (shared memory: 56 bytes per triangle and warp)
+
+__global__ void sahbRootsKernel( const uint32_t n, const uint32_t* __restrict__ rangeCount, const uint32_t* __restrict__ parentInner, uint32_t* __restrict__ roots, uint32_t* rootCount )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i + 1 >= n) return;
+	const uint32_t cnt = rangeCount[i], par = parentInner[i];
+	if (cnt > SAHB_CLUSTER || cnt < 3) return; // (a pair has one shape)
+	if (par != 0xffffffffu && rangeCount[par] <= SAHB_CLUSTER) return; // inside a larger subtree that is rebuilt as a whole
+	roots[atomicAdd( rootCount, 1u )] = i;
+}
+
+struct SahbWarp {
+	float lo[2][3][SAHB_CLUSTER], hi[2][3][SAHB_CLUSTER]; // the triangles' boxes: [0] in tree order, [1] scratch of the partition
+	uint32_t prim[2][SAHB_CLUSTER];
+	int binLo[3][SAHB_BINS][3], binHi[3][SAHB_BINS][3], binCount[3][SAHB_BINS];
+	uint32_t stackId[24], stackBegin[24], stackCount[24];
+};
+
+__global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint32_t* __restrict__ roots, const uint32_t* __restrict__ rootCount, uint32_t* __restrict__ sortedPrim,
+	const float4* __restrict__ primLo, const float4* __restrict__ primHi, uint32_t* __restrict__ childL, uint32_t* __restrict__ childR, const uint32_t* __restrict__ rangeFirst,
+	uint32_t* __restrict__ rangeCount, uint32_t* __restrict__ parentInner, uint32_t* __restrict__ parentLeaf )
+{
+	extern __shared__ __align__( 16 ) unsigned char sahbSmem[];
+	SahbWarp& w = reinterpret_cast<SahbWarp*>( sahbSmem )[threadIdx.x >> 5];
+	const uint32_t lane = threadIdx.x & 31, job = blockIdx.x * SAHB_WARPS + (threadIdx.x >> 5);
+	if (job >= *rootCount) return; // (whole warps)
+	const uint32_t root = roots[job], first = rangeFirst[root], total = rangeCount[root];
+	for (uint32_t j = lane; j < total; j += 32)
+	{
+		const uint32_t p = sortedPrim[first + j];
+		const float4 l = primLo[p], h = primHi[p];
+		w.prim[0][j] = p, w.lo[0][0][j] = l.x, w.lo[0][1][j] = l.y, w.lo[0][2][j] = l.z, w.hi[0][0][j] = h.x, w.hi[0][1][j] = h.y, w.hi[0][2][j] = h.z;
+	}
+	uint32_t nextId = first + 1, sp = 0;
+	uint32_t id = root, begin = 0, count = total;
+	__syncwarp();
+	while (true)
+	{
+		// ---- one node: `count` >= 2 triangles at [begin, begin + count) of the tree order
+		uint32_t nl = count >> 1; // the fallback: halves in curve order
+		if (count > 2)
+		{
+			// centroid bounds (twice the centroid: lo + hi)
+			float cmin[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, cmax[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+			for (uint32_t j = begin + lane; j < begin + count; j += 32)
+				for (int a = 0; a < 3; a++) { const float c = w.lo[0][a][j] + w.hi[0][a][j]; cmin[a] = fminf( cmin[a], c ), cmax[a] = fmaxf( cmax[a], c ); }
+			for (int a = 0; a < 3; a++) for (int d = 16; d; d >>= 1)
+				cmin[a] = fminf( cmin[a], __shfl_xor_sync( 0xffffffffu, cmin[a], d ) ), cmax[a] = fmaxf( cmax[a], __shfl_xor_sync( 0xffffffffu, cmax[a], d ) );
+			float scale[3];
+			for (int a = 0; a < 3; a++) scale[a] = cmax[a] > cmin[a] ? (float)SAHB_BINS * 0.999f / (cmax[a] - cmin[a]) : 0.f;
+			for (uint32_t t = lane; t < 3 * SAHB_BINS; t += 32)
+			{
+				int* bl = &w.binLo[0][0][0] + t * 3, *bh = &w.binHi[0][0][0] + t * 3;
+				bl[0] = bl[1] = bl[2] = 0x7fffffff, bh[0] = bh[1] = bh[2] = (int)0x80000000, (&w.binCount[0][0])[t] = 0;
+			}
+			__syncwarp();
+			for (uint32_t j = begin + lane; j < begin + count; j += 32)
+			{
+				int l[3], h[3];
+				for (int a = 0; a < 3; a++) l[a] = orderedInt( w.lo[0][a][j] ), h[a] = orderedInt( w.hi[0][a][j] );
+				for (int a = 0; a < 3; a++)
+				{
+					const int b = min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) );
+					for (int k = 0; k < 3; k++) atomicMin( &w.binLo[a][b][k], l[k] ), atomicMax( &w.binHi[a][b][k], h[k] );
+					atomicAdd( &w.binCount[a][b], 1 );
+				}
+			}
+			__syncwarp();
+			// candidates: axis a, the bins up to and including b go left (b < BINS - 1); 3 * 15 = 45 of them over the 32 lanes
+			float bestCost = 3.0e38f;
+			uint32_t bestCand = 0xffffffffu, bestLeft = 0;
+			for (uint32_t t = lane; t < 3 * (SAHB_BINS - 1); t += 32)
+			{
+				const int a = t / (SAHB_BINS - 1), b = t % (SAHB_BINS - 1);
+				if (scale[a] == 0.f) continue;
+				float ll[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, lh[3] = { -3.0e38f, -3.0e38f, -3.0e38f }, rl[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, rh[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+				int cl = 0, cr = 0;
+				for (int k = 0; k < SAHB_BINS; k++)
+				{
+					const int c = w.binCount[a][k];
+					if (!c) continue;
+					if (k <= b) { cl += c; for (int x = 0; x < 3; x++) ll[x] = fminf( ll[x], orderedFloat( w.binLo[a][k][x] ) ), lh[x] = fmaxf( lh[x], orderedFloat( w.binHi[a][k][x] ) ); }
+					else { cr += c; for (int x = 0; x < 3; x++) rl[x] = fminf( rl[x], orderedFloat( w.binLo[a][k][x] ) ), rh[x] = fmaxf( rh[x], orderedFloat( w.binHi[a][k][x] ) ); }
+				}
+				if (!cl || !cr) continue;
+				const float lx = lh[0] - ll[0], ly = lh[1] - ll[1], lz = lh[2] - ll[2], rx = rh[0] - rl[0], ry = rh[1] - rl[1], rz = rh[2] - rl[2];
+				const float cost = (lx * ly + ly * lz + lz * lx) * (float)cl + (rx * ry + ry * rz + rz * rx) * (float)cr;
+				if (cost < bestCost) bestCost = cost, bestCand = t, bestLeft = (uint32_t)cl;
+			}
+			for (int d = 16; d; d >>= 1)
+			{
+				const float oc = __shfl_xor_sync( 0xffffffffu, bestCost, d );
+				const uint32_t ot = __shfl_xor_sync( 0xffffffffu, bestCand, d ), ol = __shfl_xor_sync( 0xffffffffu, bestLeft, d );
+				if (oc < bestCost || (oc == bestCost && ot < bestCand)) bestCost = oc, bestCand = ot, bestLeft = ol;
+			}
+			if (bestCand != 0xffffffffu)
+			{
+				// stable partition through the scratch copy
+				const int a = bestCand / (SAHB_BINS - 1), b = bestCand % (SAHB_BINS - 1);
+				nl = bestLeft;
+				uint32_t doneL = 0, doneR = 0;
+				for (uint32_t j0 = begin; j0 < begin + count; j0 += 32)
+				{
+					const uint32_t j = j0 + lane;
+					const bool have = j < begin + count;
+					const bool left = have && min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) ) <= b;
+					const uint32_t ml = __ballot_sync( 0xffffffffu, left ), mr = __ballot_sync( 0xffffffffu, have && !left ), below = (1u << lane) - 1u;
+					if (have)
+					{
+						const uint32_t to = left ? begin + doneL + __popc( ml & below ) : begin + nl + doneR + __popc( mr & below );
+						w.prim[1][to] = w.prim[0][j];
+						for (int x = 0; x < 3; x++) w.lo[1][x][to] = w.lo[0][x][j], w.hi[1][x][to] = w.hi[0][x][j];
+					}
+					doneL += __popc( ml ), doneR += __popc( mr );
+				}
+				__syncwarp();
+				for (uint32_t j = begin + lane; j < begin + count; j += 32)
+				{
+					w.prim[0][j] = w.prim[1][j];
+					for (int x = 0; x < 3; x++) w.lo[0][x][j] = w.lo[1][x][j], w.hi[0][x][j] = w.hi[1][x][j];
+				}
+				__syncwarp();
+			}
+		}
+		// ---- the node's links; children with one triangle are leaves, the others get the next free indices
+		const uint32_t nr = count - nl;
+		const uint32_t idL = nl > 1 ? nextId : 0, idR = nr > 1 ? nextId + (nl > 1 ? 1u : 0u) : 0;
+		nextId += (nl > 1 ? 1u : 0u) + (nr > 1 ? 1u : 0u);
+		if (lane == 0)
+		{
+			const uint32_t L = nl > 1 ? idL : (LEAF | (first + begin)), R = nr > 1 ? idR : (LEAF | (first + begin + nl));
+			childL[id] = L, childR[id] = R, rangeCount[id] = count;
+			if (nl > 1) parentInner[idL] = id; else parentLeaf[first + begin] = id;
+			if (nr > 1) parentInner[idR] = id; else parentLeaf[first + begin + nl] = id;
+		}
+		// the smaller side first, the larger one waits: the stack stays below log2( SAHB_CLUSTER ) + 1 entries
+		const bool leftFirst = nl <= nr;
+		const uint32_t aId = leftFirst ? idL : idR, aBegin = leftFirst ? begin : begin + nl, aCount = leftFirst ? nl : nr;
+		const uint32_t bId = leftFirst ? idR : idL, bBegin = leftFirst ? begin + nl : begin, bCount = leftFirst ? nr : nl;
+		if (bCount > 1 && aCount > 1)
+		{
+			if (lane == 0) w.stackId[sp] = bId, w.stackBegin[sp] = bBegin, w.stackCount[sp] = bCount;
+			sp++;
+			__syncwarp();
+		}
+		if (aCount > 1) id = aId, begin = aBegin, count = aCount;
+		else if (bCount > 1) id = bId, begin = bBegin, count = bCount;
+		else
+		{
+			if (!sp) break;
+			sp--;
+			id = w.stackId[sp], begin = w.stackBegin[sp], count = w.stackCount[sp];
+		}
+	}
+	__syncwarp();
+	for (uint32_t j = lane; j < total; j += 32) sortedPrim[first + j] = w.prim[0][j];
+}
+
 // ---- 3b / 4b. agglomerative alternative to the radix tree: PLOC (Meister, Bittner: "Parallel Locally-Ordered Clustering for Bounding Volume
 // Hierarchy Construction", TVCG 2018).  The clusters -- at first the triangles in Morton order -- each look for the neighbour within
 // `radius` places along the curve whose union with them has the smallest surface; pairs that chose each other merge into a binary node;
@@ -1070,6 +1243,22 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	if (!ploc)
 	{
 		radixTreeKernel<<<blocks, 256, 0, s>>>( keys2, (int)T, childL, childR, first, count, parI, parL );
+		if (builder == 3)
+		{
+			// SAH bottoms: the list of subtree roots in the (now free) second key array, its length in the block of small values
+			uint32_t *roots = (uint32_t*)keys, *rootCount = counters + 8;
+			if ((e = cudaMemsetAsync( rootCount, 0, 4, s )) != cudaSuccess) return done( e );
+			sahbRootsKernel<<<blocks, 256, 0, s>>>( T, count, parI, roots, rootCount );
+			static bool allowed = false;
+			const size_t smem = sizeof( SahbWarp ) * SAHB_WARPS;
+			if (!allowed)
+			{
+				if ((e = cudaFuncSetAttribute( sahbBuildKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem )) != cudaSuccess) return done( e );
+				allowed = true;
+			}
+			// (at most T / 3 roots: every one of them has at least three triangles; warps beyond the count leave at once)
+			sahbBuildKernel<<<(T / 3 + SAHB_WARPS) / SAHB_WARPS, SAHB_WARPS * 32, smem, s>>>( roots, rootCount, vals2, primLo, primHi, childL, childR, first, count, parI, parL );
+		}
 		binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, count, parI, parL, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost, visits );
 	}
 	else

@@ -167,7 +167,7 @@ int RenderCore::Setting( const char* name, float value )
 	// ("clampDirect", "clampIndirect", "filter", "TAA": with the frame settings in wavefront.cu -- honoured when Setting filterCore is on)
 	// B200-specific keys
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
-	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 1.5f ? 2 : (value >= 0.5f ? 1 : 0); return 0; } // 1: LBVH, 2: PLOC (build.cu)
+	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 2.5f ? 3 : (value >= 1.5f ? 2 : (value >= 0.5f ? 1 : 0)); return 0; } // 1: LBVH, 2: PLOC, 3: LBVH with SAH bottoms (build.cu)
 	if (!strcmp( name, "deviceTlas" )) { deviceTlas = value >= 0.5f; tlasDirty = true; return 0; }
 	if (!strcmp( name, "twoStreams" )) { twoStreams = value >= 0.5f; return 0; }
 	if (!strcmp( name, "zeroCopy" )) { zeroCopy = value >= 0.5f; return 0; }

@@ -16,7 +16,7 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 BUILDER = 1
 
 
-@pytest.fixture(autouse=True, params=[1, 2], ids=["lbvh", "ploc"])
+@pytest.fixture(autouse=True, params=[1, 2, 3], ids=["lbvh", "ploc", "sahb"])
 def _builder(request):
     global BUILDER
     BUILDER = request.param
