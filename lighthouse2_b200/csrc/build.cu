@@ -28,6 +28,8 @@
 #endif
 #define B200_USE_GROUP_COLLAPSE (B200_GROUP_COLLAPSE && B200_DP_COLLAPSE)
 #include <vector>
+#include <stdio.h>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -211,61 +213,138 @@ __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, cons
 	}
 }
 
-// ---- 3c. SAH bottoms under the radix tree (builder 3).  The Morton splits are good at cutting a scene into compact chunks and poor at
-// the last levels, where the order along the curve, not the surface area, decides which triangles share a node -- and that is where the
-// rays spend their steps (the host builder's trees trace 4 % faster than the radix tree's; a SAH top over radix subtrees changed nothing:
-// profiles/r02_experiments.md).  So: every maximal radix subtree of at most SAHB_CLUSTER triangles is rebuilt from its root down by
-// binned SAH (16 bins on each axis, the split with the smallest area * count sum over the three axes), one warp per subtree, the
-// triangles' boxes in shared memory.  The new subtree lives in the places of the old one: the radix subtree over sorted positions
-// [f, l] rooted at r uses the inner-node indices [f, l] without one end, r is one of the ends, so [f + 1, l - 1] are free for the
-// others; the sorted order is permuted inside [f, l] only.  binaryBoxesKernel and the collapse then run as for the plain radix tree.
+// ---- 3c. SAH inside the radix tree, level by level (builder 3).  The Morton splits are good at cutting a scene into compact cells and
+// poor at deciding which triangles (or which cells) share a node: the order along the curve, not the surface area, decides.  The host
+// builder's trees trace 4 % faster than the radix tree's; SAH in the bottom levels alone closes that for primary and diffuse rays, SAH
+// above them as well for the long shadow rays (profiles/r02_experiments.md).  So the radix tree only supplies CELLS:
+//   level 1: items = the triangles.  Every maximal radix subtree of at most SAHB_CLUSTER items is rebuilt from its root down by binned SAH
+//            (16 bins on each axis; the split with the smallest sum of area * triangles over the three axes), one warp per subtree, the
+//            items' boxes in shared memory.
+//   level k + 1: items = the subtrees rebuilt so far (and what was left over); the same again, until the root is inside.
+// Three levels at 1 M triangles.  A rebuilt subtree lives in the index places of the radix subtree it replaces: the radix subtree over the
+// sorted positions [f, l] rooted at r uses the inner-node indices [f, l] without one end, r is the other end (Karras: the children of a
+// split at g are g and g + 1).  Hence the rule that keeps the books at every level: an item over [f1, l1] with root r1 has the spare index
+// (r1 == f1 ? l1 : f1) -- a single triangle at p has p --, a cluster of items may use its items' spare indices except its own root and
+// its own spare end, and those are exactly as many as it needs.  Nothing moves in the sorted order; leaves stay LEAF | position.
+// binaryBoxesKernel and the collapse then run as for the plain radix tree.
 #ifndef SAHB_CLUSTER
 #define SAHB_CLUSTER 256
 #endif
 #ifndef SAHB_BINS_N
 #define SAHB_BINS_N 16
 #endif
-constexpr int SAHB_BINS = SAHB_BINS_N, SAHB_WARPS = SAHB_CLUSTER <= 256 ? 4 : (SAHB_CLUSTER <= 512 ? 2 : 1); // (shared memory: 56 bytes per triangle and warp)
+constexpr int SAHB_BINS = SAHB_BINS_N, SAHB_WARPS = SAHB_CLUSTER <= 256 ? 4 : (SAHB_CLUSTER <= 512 ? 2 : 1); // (shared memory: 76 bytes per item and warp)
 
-__global__ void sahbRootsKernel( const uint32_t n, const uint32_t* __restrict__ rangeCount, const uint32_t* __restrict__ parentInner, uint32_t* __restrict__ roots, uint32_t* rootCount )
+struct SahbSparse { uint32_t *flag, *ref, *last; };                         // per sorted position: an item starts here; its reference (LEAF | position, or its root) and last position
+struct SahbItems { uint32_t *ref, *first, *last; float4 *lo, *hi; };       // the items of a level, in position order
+
+__global__ void sahbInitKernel( const uint32_t n, const SahbSparse sp )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) sp.flag[i] = 1, sp.ref[i] = LEAF | i, sp.last[i] = i;
+}
+
+// the level's item list from the flags and their running sum
+__global__ void sahbCompactKernel( const uint32_t n, const SahbSparse sp, const uint32_t* __restrict__ before, const uint32_t* __restrict__ sortedPrim,
+	const float4* __restrict__ primLo, const float4* __restrict__ primHi, const float4* __restrict__ nodeLo, const float4* __restrict__ nodeHi, const SahbItems it )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n || !sp.flag[i]) return;
+	const uint32_t k = before[i], ref = sp.ref[i];
+	it.ref[k] = ref, it.first[k] = i, it.last[k] = sp.last[i];
+	if (ref & LEAF) { const uint32_t p = sortedPrim[i]; it.lo[k] = primLo[p], it.hi[k] = primHi[p]; }
+	else it.lo[k] = nodeLo[ref], it.hi[k] = nodeHi[ref];
+}
+
+// the roots of a level: radix nodes above the items with at most SAHB_CLUSTER items below them, whose parents have more
+__global__ void sahbRootsKernel( const uint32_t n, const SahbSparse sp, const uint32_t* __restrict__ before, const SahbItems it, const uint32_t* __restrict__ rangeFirst,
+	const uint32_t* __restrict__ rangeCount, const uint32_t* __restrict__ parentInner, uint4* __restrict__ roots, uint32_t* rootCount, const uint32_t limit )
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i + 1 >= n) return;
-	const uint32_t cnt = rangeCount[i], par = parentInner[i];
-	if (cnt > SAHB_CLUSTER || cnt < 3) return; // (a pair has one shape)
-	if (par != 0xffffffffu && rangeCount[par] <= SAHB_CLUSTER) return; // inside a larger subtree that is rebuilt as a whole
-	roots[atomicAdd( rootCount, 1u )] = i;
+	// is inner node i still a node of the radix tree, or one of the indices a rebuilt subtree has taken?
+	const uint32_t k = before[i] + sp.flag[i] - 1, f1 = it.first[k], l1 = it.last[k], r1 = it.ref[k];
+	if (f1 != l1 && i != (r1 == f1 ? l1 : f1)) return;
+	const uint32_t f = rangeFirst[i], l = f + rangeCount[i] - 1, items = before[l] + sp.flag[l] - before[f];
+	if (items > limit) return;
+	const uint32_t par = parentInner[i];
+	if (par != 0xffffffffu)
+	{
+		const uint32_t pf = rangeFirst[par], pl = pf + rangeCount[par] - 1;
+		if (before[pl] + sp.flag[pl] - before[pf] <= limit) return; // inside a larger subtree that is rebuilt as a whole
+	}
+	roots[atomicAdd( rootCount, 1u )] = make_uint4( i, before[f], items, l );
 }
 
 struct SahbWarp {
-	float lo[2][3][SAHB_CLUSTER], hi[2][3][SAHB_CLUSTER]; // the triangles' boxes: [0] in tree order, [1] scratch of the partition
-	uint32_t prim[2][SAHB_CLUSTER];
-	int binLo[3][SAHB_BINS][3], binHi[3][SAHB_BINS][3], binCount[3][SAHB_BINS];
-	uint32_t stackId[24], stackBegin[24], stackCount[24];
+	float lo[2][3][SAHB_CLUSTER], hi[2][3][SAHB_CLUSTER]; // the items' boxes: [0] in tree order, [1] scratch of the partition
+	uint32_t ref[2][SAHB_CLUSTER], weight[2][SAHB_CLUSTER]; // reference and triangles of the item
+	uint32_t pool[SAHB_CLUSTER];                          // the items' spare indices
+	int binLo[3][SAHB_BINS][3], binHi[3][SAHB_BINS][3], binWeight[3][SAHB_BINS], binItems[3][SAHB_BINS];
+	uint32_t stackId[24], stackBegin[24], stackCount[24], stackWeight[24];
 };
 
-__global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint32_t* __restrict__ roots, const uint32_t* __restrict__ rootCount, uint32_t* __restrict__ sortedPrim,
-	const float4* __restrict__ primLo, const float4* __restrict__ primHi, uint32_t* __restrict__ childL, uint32_t* __restrict__ childR, const uint32_t* __restrict__ rangeFirst,
-	uint32_t* __restrict__ rangeCount, uint32_t* __restrict__ parentInner, uint32_t* __restrict__ parentLeaf )
+// CELLS: the subtrees are cells of the radix tree (items, spare indices: see above).  !CELLS (builder 4): the subtrees hang below the
+// top-down phase -- roots[job] = (node, first position, triangles), the items are the triangles at those positions of `order`, and
+// the subtree's other nodes are a block of fresh indices taken from *nodeCounter.
+template <bool CELLS>
+__global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint4* __restrict__ roots, const uint32_t* __restrict__ rootCount, const SahbItems it, const SahbSparse sparse,
+	uint32_t* __restrict__ childL, uint32_t* __restrict__ childR, uint32_t* __restrict__ rangeCount, uint32_t* __restrict__ parentInner, uint32_t* __restrict__ parentLeaf,
+	float4* __restrict__ nodeLo, float4* __restrict__ nodeHi,
+	const uint32_t* __restrict__ order = nullptr, const float4* __restrict__ primLo = nullptr, const float4* __restrict__ primHi = nullptr, uint32_t* nodeCounter = nullptr )
 {
 	extern __shared__ __align__( 16 ) unsigned char sahbSmem[];
 	SahbWarp& w = reinterpret_cast<SahbWarp*>( sahbSmem )[threadIdx.x >> 5];
 	const uint32_t lane = threadIdx.x & 31, job = blockIdx.x * SAHB_WARPS + (threadIdx.x >> 5);
 	if (job >= *rootCount) return; // (whole warps)
-	const uint32_t root = roots[job], first = rangeFirst[root], total = rangeCount[root];
+	const uint4 rt = roots[job];
+	const uint32_t root = rt.x, item0 = rt.y, total = rt.z, firstPos = CELLS ? it.first[item0] : rt.y, lastPos = rt.w;
+	const uint32_t spareEnd = !CELLS ? 0xffffffffu : (root == firstPos ? lastPos : firstPos);
+	float blo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, bhi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+	uint32_t wsum = 0;
+	uint32_t freshBase = 0;
+	if (!CELLS)
+	{
+		if (lane == 0 && total > 2) freshBase = atomicAdd( nodeCounter, total - 2 );
+		freshBase = __shfl_sync( 0xffffffffu, freshBase, 0 );
+	}
 	for (uint32_t j = lane; j < total; j += 32)
 	{
-		const uint32_t p = sortedPrim[first + j];
-		const float4 l = primLo[p], h = primHi[p];
-		w.prim[0][j] = p, w.lo[0][0][j] = l.x, w.lo[0][1][j] = l.y, w.lo[0][2][j] = l.z, w.hi[0][0][j] = h.x, w.hi[0][1][j] = h.y, w.hi[0][2][j] = h.z;
+		if (!CELLS)
+		{
+			const uint32_t p = order[firstPos + j];
+			const float4 l = primLo[p], h = primHi[p];
+			w.ref[0][j] = LEAF | (firstPos + j), w.weight[0][j] = 1, w.pool[j] = freshBase + j; // (total - 2 of them are used)
+			w.lo[0][0][j] = l.x, w.lo[0][1][j] = l.y, w.lo[0][2][j] = l.z, w.hi[0][0][j] = h.x, w.hi[0][1][j] = h.y, w.hi[0][2][j] = h.z;
+			wsum++;
+			continue;
+		}
+		const uint32_t r = it.ref[item0 + j], f1 = it.first[item0 + j], l1 = it.last[item0 + j];
+		const float4 l = it.lo[item0 + j], h = it.hi[item0 + j];
+		w.ref[0][j] = r, w.weight[0][j] = l1 - f1 + 1, w.pool[j] = (r & LEAF) ? f1 : (r == f1 ? l1 : f1);
+		w.lo[0][0][j] = l.x, w.lo[0][1][j] = l.y, w.lo[0][2][j] = l.z, w.hi[0][0][j] = h.x, w.hi[0][1][j] = h.y, w.hi[0][2][j] = h.z;
+		blo[0] = fminf( blo[0], l.x ), blo[1] = fminf( blo[1], l.y ), blo[2] = fminf( blo[2], l.z ), bhi[0] = fmaxf( bhi[0], h.x ), bhi[1] = fmaxf( bhi[1], h.y ), bhi[2] = fmaxf( bhi[2], h.z );
+		wsum += l1 - f1 + 1;
+		sparse.flag[f1] = 0; // the item is inside from now on ...
 	}
-	uint32_t nextId = first + 1, sp = 0;
-	uint32_t id = root, begin = 0, count = total;
+	for (int d = 16; d; d >>= 1)
+	{
+		for (int a = 0; a < 3; a++) blo[a] = fminf( blo[a], __shfl_xor_sync( 0xffffffffu, blo[a], d ) ), bhi[a] = fmaxf( bhi[a], __shfl_xor_sync( 0xffffffffu, bhi[a], d ) );
+		wsum += __shfl_xor_sync( 0xffffffffu, wsum, d );
+	}
 	__syncwarp();
+	if (CELLS && lane == 0)
+	{
+		// ... and the subtree is an item of the next level
+		sparse.flag[firstPos] = 1, sparse.ref[firstPos] = root, sparse.last[firstPos] = lastPos;
+		nodeLo[root] = make_float4( blo[0], blo[1], blo[2], 0 ), nodeHi[root] = make_float4( bhi[0], bhi[1], bhi[2], 0 );
+	}
+	uint32_t nextPool = 0, sp = 0;
+	uint32_t id = root, begin = 0, count = total, weight = wsum;
 	while (true)
 	{
-		// ---- one node: `count` >= 2 triangles at [begin, begin + count) of the tree order
-		uint32_t nl = count >> 1; // the fallback: halves in curve order
+		// ---- one node: `count` >= 2 items at [begin, begin + count) of the tree order, `weight` triangles
+		uint32_t nl = count >> 1, wl = 0xffffffffu; // the fallback: halves in curve order
 		if (count > 2)
 		{
 			// centroid bounds (twice the centroid: lo + hi)
@@ -279,53 +358,54 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 			for (uint32_t t = lane; t < 3 * SAHB_BINS; t += 32)
 			{
 				int* bl = &w.binLo[0][0][0] + t * 3, *bh = &w.binHi[0][0][0] + t * 3;
-				bl[0] = bl[1] = bl[2] = 0x7fffffff, bh[0] = bh[1] = bh[2] = (int)0x80000000, (&w.binCount[0][0])[t] = 0;
+				bl[0] = bl[1] = bl[2] = 0x7fffffff, bh[0] = bh[1] = bh[2] = (int)0x80000000, (&w.binWeight[0][0])[t] = 0, (&w.binItems[0][0])[t] = 0;
 			}
 			__syncwarp();
 			for (uint32_t j = begin + lane; j < begin + count; j += 32)
 			{
 				int l[3], h[3];
 				for (int a = 0; a < 3; a++) l[a] = orderedInt( w.lo[0][a][j] ), h[a] = orderedInt( w.hi[0][a][j] );
+				const int wt = (int)w.weight[0][j];
 				for (int a = 0; a < 3; a++)
 				{
 					const int b = min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) );
 					for (int k = 0; k < 3; k++) atomicMin( &w.binLo[a][b][k], l[k] ), atomicMax( &w.binHi[a][b][k], h[k] );
-					atomicAdd( &w.binCount[a][b], 1 );
+					atomicAdd( &w.binWeight[a][b], wt ), atomicAdd( &w.binItems[a][b], 1 );
 				}
 			}
 			__syncwarp();
 			// candidates: axis a, the bins up to and including b go left (b < BINS - 1); 3 * 15 = 45 of them over the 32 lanes
 			float bestCost = 3.0e38f;
-			uint32_t bestCand = 0xffffffffu, bestLeft = 0;
+			uint32_t bestCand = 0xffffffffu, bestLeft = 0, bestLeftWeight = 0;
 			for (uint32_t t = lane; t < 3 * (SAHB_BINS - 1); t += 32)
 			{
 				const int a = t / (SAHB_BINS - 1), b = t % (SAHB_BINS - 1);
 				if (scale[a] == 0.f) continue;
 				float ll[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, lh[3] = { -3.0e38f, -3.0e38f, -3.0e38f }, rl[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, rh[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
-				int cl = 0, cr = 0;
+				int cl = 0, cr = 0, il = 0, ir = 0;
 				for (int k = 0; k < SAHB_BINS; k++)
 				{
-					const int c = w.binCount[a][k];
+					const int c = w.binItems[a][k];
 					if (!c) continue;
-					if (k <= b) { cl += c; for (int x = 0; x < 3; x++) ll[x] = fminf( ll[x], orderedFloat( w.binLo[a][k][x] ) ), lh[x] = fmaxf( lh[x], orderedFloat( w.binHi[a][k][x] ) ); }
-					else { cr += c; for (int x = 0; x < 3; x++) rl[x] = fminf( rl[x], orderedFloat( w.binLo[a][k][x] ) ), rh[x] = fmaxf( rh[x], orderedFloat( w.binHi[a][k][x] ) ); }
+					if (k <= b) { il += c, cl += w.binWeight[a][k]; for (int x = 0; x < 3; x++) ll[x] = fminf( ll[x], orderedFloat( w.binLo[a][k][x] ) ), lh[x] = fmaxf( lh[x], orderedFloat( w.binHi[a][k][x] ) ); }
+					else { ir += c, cr += w.binWeight[a][k]; for (int x = 0; x < 3; x++) rl[x] = fminf( rl[x], orderedFloat( w.binLo[a][k][x] ) ), rh[x] = fmaxf( rh[x], orderedFloat( w.binHi[a][k][x] ) ); }
 				}
-				if (!cl || !cr) continue;
+				if (!il || !ir) continue;
 				const float lx = lh[0] - ll[0], ly = lh[1] - ll[1], lz = lh[2] - ll[2], rx = rh[0] - rl[0], ry = rh[1] - rl[1], rz = rh[2] - rl[2];
 				const float cost = (lx * ly + ly * lz + lz * lx) * (float)cl + (rx * ry + ry * rz + rz * rx) * (float)cr;
-				if (cost < bestCost) bestCost = cost, bestCand = t, bestLeft = (uint32_t)cl;
+				if (cost < bestCost) bestCost = cost, bestCand = t, bestLeft = (uint32_t)il, bestLeftWeight = (uint32_t)cl;
 			}
 			for (int d = 16; d; d >>= 1)
 			{
 				const float oc = __shfl_xor_sync( 0xffffffffu, bestCost, d );
-				const uint32_t ot = __shfl_xor_sync( 0xffffffffu, bestCand, d ), ol = __shfl_xor_sync( 0xffffffffu, bestLeft, d );
-				if (oc < bestCost || (oc == bestCost && ot < bestCand)) bestCost = oc, bestCand = ot, bestLeft = ol;
+				const uint32_t ot = __shfl_xor_sync( 0xffffffffu, bestCand, d ), ol = __shfl_xor_sync( 0xffffffffu, bestLeft, d ), ow = __shfl_xor_sync( 0xffffffffu, bestLeftWeight, d );
+				if (oc < bestCost || (oc == bestCost && ot < bestCand)) bestCost = oc, bestCand = ot, bestLeft = ol, bestLeftWeight = ow;
 			}
 			if (bestCand != 0xffffffffu)
 			{
 				// stable partition through the scratch copy
 				const int a = bestCand / (SAHB_BINS - 1), b = bestCand % (SAHB_BINS - 1);
-				nl = bestLeft;
+				nl = bestLeft, wl = bestLeftWeight;
 				uint32_t doneL = 0, doneR = 0;
 				for (uint32_t j0 = begin; j0 < begin + count; j0 += 32)
 				{
@@ -336,7 +416,7 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 					if (have)
 					{
 						const uint32_t to = left ? begin + doneL + __popc( ml & below ) : begin + nl + doneR + __popc( mr & below );
-						w.prim[1][to] = w.prim[0][j];
+						w.ref[1][to] = w.ref[0][j], w.weight[1][to] = w.weight[0][j];
 						for (int x = 0; x < 3; x++) w.lo[1][x][to] = w.lo[0][x][j], w.hi[1][x][to] = w.hi[0][x][j];
 					}
 					doneL += __popc( ml ), doneR += __popc( mr );
@@ -344,44 +424,251 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 				__syncwarp();
 				for (uint32_t j = begin + lane; j < begin + count; j += 32)
 				{
-					w.prim[0][j] = w.prim[1][j];
+					w.ref[0][j] = w.ref[1][j], w.weight[0][j] = w.weight[1][j];
 					for (int x = 0; x < 3; x++) w.lo[0][x][j] = w.lo[1][x][j], w.hi[0][x][j] = w.hi[1][x][j];
 				}
 				__syncwarp();
 			}
 		}
-		// ---- the node's links; children with one triangle are leaves, the others get the next free indices
-		const uint32_t nr = count - nl;
-		const uint32_t idL = nl > 1 ? nextId : 0, idR = nr > 1 ? nextId + (nl > 1 ? 1u : 0u) : 0;
-		nextId += (nl > 1 ? 1u : 0u) + (nr > 1 ? 1u : 0u);
+		if (wl == 0xffffffffu)
+		{
+			wl = 0;
+			for (uint32_t j = begin + lane; j < begin + nl; j += 32) wl += w.weight[0][j];
+			for (int d = 16; d; d >>= 1) wl += __shfl_xor_sync( 0xffffffffu, wl, d );
+		}
+		// ---- the node's links: a side with one item is that item, the others take the next spare indices
+		const uint32_t nr = count - nl, wr = weight - wl;
+		uint32_t idL = 0, idR = 0;
+		if (nl > 1) { while (w.pool[nextPool] == root || w.pool[nextPool] == spareEnd) nextPool++; idL = w.pool[nextPool++]; }
+		if (nr > 1) { while (w.pool[nextPool] == root || w.pool[nextPool] == spareEnd) nextPool++; idR = w.pool[nextPool++]; }
 		if (lane == 0)
 		{
-			const uint32_t L = nl > 1 ? idL : (LEAF | (first + begin)), R = nr > 1 ? idR : (LEAF | (first + begin + nl));
-			childL[id] = L, childR[id] = R, rangeCount[id] = count;
-			if (nl > 1) parentInner[idL] = id; else parentLeaf[first + begin] = id;
-			if (nr > 1) parentInner[idR] = id; else parentLeaf[first + begin + nl] = id;
+			const uint32_t L = nl > 1 ? idL : w.ref[0][begin], R = nr > 1 ? idR : w.ref[0][begin + nl];
+			childL[id] = L, childR[id] = R, rangeCount[id] = weight;
+			if (L & LEAF) parentLeaf[L & ~LEAF] = id; else parentInner[L] = id;
+			if (R & LEAF) parentLeaf[R & ~LEAF] = id; else parentInner[R] = id;
 		}
 		// the smaller side first, the larger one waits: the stack stays below log2( SAHB_CLUSTER ) + 1 entries
 		const bool leftFirst = nl <= nr;
-		const uint32_t aId = leftFirst ? idL : idR, aBegin = leftFirst ? begin : begin + nl, aCount = leftFirst ? nl : nr;
-		const uint32_t bId = leftFirst ? idR : idL, bBegin = leftFirst ? begin + nl : begin, bCount = leftFirst ? nr : nl;
+		const uint32_t aId = leftFirst ? idL : idR, aBegin = leftFirst ? begin : begin + nl, aCount = leftFirst ? nl : nr, aWeight = leftFirst ? wl : wr;
+		const uint32_t bId = leftFirst ? idR : idL, bBegin = leftFirst ? begin + nl : begin, bCount = leftFirst ? nr : nl, bWeight = leftFirst ? wr : wl;
 		if (bCount > 1 && aCount > 1)
 		{
-			if (lane == 0) w.stackId[sp] = bId, w.stackBegin[sp] = bBegin, w.stackCount[sp] = bCount;
+			if (lane == 0) w.stackId[sp] = bId, w.stackBegin[sp] = bBegin, w.stackCount[sp] = bCount, w.stackWeight[sp] = bWeight;
 			sp++;
 			__syncwarp();
 		}
-		if (aCount > 1) id = aId, begin = aBegin, count = aCount;
-		else if (bCount > 1) id = bId, begin = bBegin, count = bCount;
+		if (aCount > 1) id = aId, begin = aBegin, count = aCount, weight = aWeight;
+		else if (bCount > 1) id = bId, begin = bBegin, count = bCount, weight = bWeight;
 		else
 		{
 			if (!sp) break;
 			sp--;
-			id = w.stackId[sp], begin = w.stackBegin[sp], count = w.stackCount[sp];
+			id = w.stackId[sp], begin = w.stackBegin[sp], count = w.stackCount[sp], weight = w.stackWeight[sp];
 		}
 	}
-	__syncwarp();
-	for (uint32_t j = lane; j < total; j += 32) sortedPrim[first + j] = w.prim[0][j];
+}
+
+// ---- 3d. Binned SAH from the top (builder 4): no space-filling curve at all.  Nodes with more than SAHB_CLUSTER triangles are split
+// level by level -- every triangle of such a node adds its box to one of TOP_BINS bins per axis of its node (ordered-int atomics in
+// global memory), a warp per node picks the split with the smallest sum of area * triangles, one running sum over all positions gives
+// every triangle its place in a stable partition (left part first), and the children's centroid bounds are gathered while the triangles
+// move.  Children with at most SAHB_CLUSTER triangles go to the list that sahbBuildKernel<false> finishes, one warp each, in shared
+// memory.  This is the host builder's algorithm (bvh_builder.cpp: binned SAH over centroids, 64 bins on large nodes) in the shape the
+// device wants; the trees are not the host's bit for bit (bin counts, tie order), but of the same quality.
+#ifndef TOP_BINS_N
+#define TOP_BINS_N 64
+#endif
+constexpr int TOP_BINS = TOP_BINS_N;
+constexpr uint32_t TOP_NONE = 0xffffffffu;
+struct TopNodes { uint32_t *id, *begin, *count; int* cb; };   // the large nodes of a level; cb = centroid bounds, six ordered ints each
+struct TopBins { int *lo, *hi, *count; };                       // per node and axis and bin: box (3 + 3 ordered ints), triangles
+
+__device__ __forceinline__ int topBinOf( const float c, const float cmin, const float cmax )
+{
+	const float scale = cmax > cmin ? (float)TOP_BINS * 0.999f / (cmax - cmin) : 0.f;
+	return min( TOP_BINS - 1, (int)((c - cmin) * scale) );
+}
+
+__global__ void topInitKernel( const uint32_t T, uint32_t* __restrict__ order, uint32_t* __restrict__ nodeOf, const TopNodes act, const int* __restrict__ centroidBounds, uint32_t* parentInner )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < T) order[i] = i, nodeOf[i] = 0;
+	if (i == 0)
+	{
+		act.id[0] = 0, act.begin[0] = 0, act.count[0] = T, parentInner[0] = 0xffffffffu;
+		for (int k = 0; k < 6; k++) act.cb[k] = centroidBounds[k];
+	}
+}
+
+__global__ void topClearBinsKernel( const uint32_t nAct, const TopBins bins, int* nextCb, const uint32_t nextCap )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < nAct * 3 * TOP_BINS)
+	{
+		bins.count[i] = 0;
+		for (int k = 0; k < 3; k++) bins.lo[i * 3 + k] = 0x7fffffff, bins.hi[i * 3 + k] = (int)0x80000000;
+	}
+	if (i < nextCap * 6) nextCb[i] = (i % 6) < 3 ? 0x7fffffff : (int)0x80000000;
+}
+
+// (Triangles that are neighbours in the mesh are neighbours here for the first levels: without care a warp sends 32 atomics to one
+// address, a level of the sphere field took 8 ms.  So: the lanes of a warp that meet in a bin reduce among themselves first
+// (__match_any_sync + __reduce_*_sync) and one of them speaks for all; and what goes to the node of the block's first triangle is
+// collected in shared memory and flushed once per block.)
+__global__ void __launch_bounds__( 256 ) topBinKernel( const uint32_t T, const uint32_t* __restrict__ order, const uint32_t* __restrict__ nodeOf, const TopNodes act,
+	const float4* __restrict__ primLo, const float4* __restrict__ primHi, const TopBins bins )
+{
+	__shared__ int sLo[3 * TOP_BINS * 3], sHi[3 * TOP_BINS * 3], sCount[3 * TOP_BINS];
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t blockNode = nodeOf[blockIdx.x * blockDim.x];
+	for (uint32_t t = threadIdx.x; t < 3 * TOP_BINS; t += blockDim.x)
+	{
+		sCount[t] = 0;
+		for (int k = 0; k < 3; k++) sLo[t * 3 + k] = 0x7fffffff, sHi[t * 3 + k] = (int)0x80000000;
+	}
+	__syncthreads();
+	const uint32_t a = i < T ? nodeOf[i] : TOP_NONE;
+	const bool valid = a != TOP_NONE;
+	float c[3] = { 0, 0, 0 };
+	int ol[3] = { 0, 0, 0 }, oh[3] = { 0, 0, 0 };
+	if (valid)
+	{
+		const uint32_t p = order[i];
+		const float4 l = primLo[p], h = primHi[p];
+		c[0] = 0.5f * (l.x + h.x), c[1] = 0.5f * (l.y + h.y), c[2] = 0.5f * (l.z + h.z);
+		ol[0] = orderedInt( l.x ), ol[1] = orderedInt( l.y ), ol[2] = orderedInt( l.z ), oh[0] = orderedInt( h.x ), oh[1] = orderedInt( h.y ), oh[2] = orderedInt( h.z );
+	}
+	for (int ax = 0; ax < 3; ax++)
+	{
+		float cmin = 0, cmax = 0;
+		if (valid) cmin = orderedFloat( act.cb[a * 6 + ax] ), cmax = orderedFloat( act.cb[a * 6 + 3 + ax] );
+		const bool part = valid && cmax > cmin;
+		const uint32_t pm = __ballot_sync( 0xffffffffu, part );
+		if (!part) continue;
+		const uint32_t b = (a * 3 + ax) * TOP_BINS + topBinOf( c[ax], cmin, cmax );
+		const uint32_t group = __match_any_sync( pm, b );
+		int gl[3], gh[3];
+		for (int k = 0; k < 3; k++) gl[k] = __reduce_min_sync( group, ol[k] ), gh[k] = __reduce_max_sync( group, oh[k] );
+		if ((threadIdx.x & 31u) != (uint32_t)__ffs( group ) - 1u) continue;
+		if (a == blockNode)
+		{
+			const uint32_t sb = b - a * 3 * TOP_BINS;
+			for (int k = 0; k < 3; k++) atomicMin( sLo + sb * 3 + k, gl[k] ), atomicMax( sHi + sb * 3 + k, gh[k] );
+			atomicAdd( sCount + sb, __popc( group ) );
+		}
+		else
+		{
+			for (int k = 0; k < 3; k++) atomicMin( bins.lo + b * 3 + k, gl[k] ), atomicMax( bins.hi + b * 3 + k, gh[k] );
+			atomicAdd( bins.count + b, __popc( group ) );
+		}
+	}
+	__syncthreads();
+	if (blockNode == TOP_NONE) return;
+	for (uint32_t t = threadIdx.x; t < 3 * TOP_BINS; t += blockDim.x) if (sCount[t])
+	{
+		const uint32_t b = blockNode * 3 * TOP_BINS + t;
+		for (int k = 0; k < 3; k++) atomicMin( bins.lo + b * 3 + k, sLo[t * 3 + k] ), atomicMax( bins.hi + b * 3 + k, sHi[t * 3 + k] );
+		atomicAdd( bins.count + b, sCount[t] );
+	}
+}
+
+// one warp per large node: the split, the children's indices, and where the children go (next level, the list of small subtrees, or a leaf)
+__global__ void topSplitKernel( const uint32_t nAct, const TopNodes act, const TopBins bins, uint4* __restrict__ split, const TopNodes next, uint32_t* nextCount,
+	uint4* __restrict__ smallRoots, uint32_t* smallCount, uint32_t* nodeCounter, uint32_t* __restrict__ childL, uint32_t* __restrict__ childR, uint32_t* __restrict__ rangeCount,
+	uint32_t* __restrict__ parentInner, uint32_t* __restrict__ parentLeaf )
+{
+	const uint32_t a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+	if (a >= nAct) return;
+	const uint32_t id = act.id[a], begin = act.begin[a], count = act.count[a];
+	float bestCost = 3.0e38f;
+	uint32_t bestCand = 0xffffffffu, bestLeft = 0;
+	for (uint32_t t = lane; t < 3 * (TOP_BINS - 1); t += 32)
+	{
+		const uint32_t ax = t / (TOP_BINS - 1), b = t % (TOP_BINS - 1);
+		if (!(orderedFloat( act.cb[a * 6 + 3 + ax] ) > orderedFloat( act.cb[a * 6 + ax] ))) continue;
+		const uint32_t base = (a * 3 + ax) * TOP_BINS;
+		float ll[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, lh[3] = { -3.0e38f, -3.0e38f, -3.0e38f }, rl[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, rh[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+		int cl = 0, cr = 0;
+		for (uint32_t k = 0; k < TOP_BINS; k++)
+		{
+			const int c = bins.count[base + k];
+			if (!c) continue;
+			if (k <= b) { cl += c; for (int x = 0; x < 3; x++) ll[x] = fminf( ll[x], orderedFloat( bins.lo[(base + k) * 3 + x] ) ), lh[x] = fmaxf( lh[x], orderedFloat( bins.hi[(base + k) * 3 + x] ) ); }
+			else { cr += c; for (int x = 0; x < 3; x++) rl[x] = fminf( rl[x], orderedFloat( bins.lo[(base + k) * 3 + x] ) ), rh[x] = fmaxf( rh[x], orderedFloat( bins.hi[(base + k) * 3 + x] ) ); }
+		}
+		if (!cl || !cr) continue;
+		const float lx = lh[0] - ll[0], ly = lh[1] - ll[1], lz = lh[2] - ll[2], rx = rh[0] - rl[0], ry = rh[1] - rl[1], rz = rh[2] - rl[2];
+		const float cost = (lx * ly + ly * lz + lz * lx) * (float)cl + (rx * ry + ry * rz + rz * rx) * (float)cr;
+		if (cost < bestCost) bestCost = cost, bestCand = t, bestLeft = (uint32_t)cl;
+	}
+	for (int d = 16; d; d >>= 1)
+	{
+		const float oc = __shfl_xor_sync( 0xffffffffu, bestCost, d );
+		const uint32_t ot = __shfl_xor_sync( 0xffffffffu, bestCand, d ), ol = __shfl_xor_sync( 0xffffffffu, bestLeft, d );
+		if (oc < bestCost || (oc == bestCost && ot < bestCand)) bestCost = oc, bestCand = ot, bestLeft = ol;
+	}
+	if (lane) return;
+	const uint32_t nl = bestCand != 0xffffffffu ? bestLeft : count >> 1, nr = count - nl; // (no split separates the centroids: halves in the order they are in)
+	uint32_t ref[2], where[2];
+	for (int k = 0; k < 2; k++)
+	{
+		const uint32_t n = k ? nr : nl, b = k ? begin + nl : begin;
+		where[k] = TOP_NONE;
+		if (n == 1) { ref[k] = LEAF | b, parentLeaf[b] = id; continue; }
+		const uint32_t c = atomicAdd( nodeCounter, 1u );
+		ref[k] = c, parentInner[c] = id;
+		if (n <= SAHB_CLUSTER) smallRoots[atomicAdd( smallCount, 1u )] = make_uint4( c, b, n, 0 );
+		else
+		{
+			const uint32_t x = atomicAdd( nextCount, 1u );
+			next.id[x] = c, next.begin[x] = b, next.count[x] = n, where[k] = x;
+		}
+	}
+	childL[id] = ref[0], childR[id] = ref[1], rangeCount[id] = count;
+	split[a] = make_uint4( bestCand, nl, where[0], where[1] );
+}
+
+__device__ __forceinline__ bool topGoesLeft( const uint32_t i, const uint32_t a, const uint32_t* __restrict__ order, const TopNodes& act, const uint4 sp,
+	const float4* __restrict__ primLo, const float4* __restrict__ primHi, float c[3] )
+{
+	const uint32_t p = order[i];
+	const float4 l = primLo[p], h = primHi[p];
+	c[0] = 0.5f * (l.x + h.x), c[1] = 0.5f * (l.y + h.y), c[2] = 0.5f * (l.z + h.z);
+	if (sp.x == 0xffffffffu) return i - act.begin[a] < sp.y;
+	const uint32_t ax = sp.x / (TOP_BINS - 1), b = sp.x % (TOP_BINS - 1);
+	return (uint32_t)topBinOf( c[ax], orderedFloat( act.cb[a * 6 + ax] ), orderedFloat( act.cb[a * 6 + 3 + ax] ) ) <= b;
+}
+
+__global__ void topFlagKernel( const uint32_t T, const uint32_t* __restrict__ order, const uint32_t* __restrict__ nodeOf, const TopNodes act, const uint4* __restrict__ split,
+	const float4* __restrict__ primLo, const float4* __restrict__ primHi, uint32_t* __restrict__ flag )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= T) return;
+	const uint32_t a = nodeOf[i];
+	float c[3];
+	flag[i] = a != TOP_NONE && topGoesLeft( i, a, order, act, split[a], primLo, primHi, c ) ? 1u : 0u;
+}
+
+__global__ void topScatterKernel( const uint32_t T, const uint32_t* __restrict__ order, const uint32_t* __restrict__ nodeOf, const TopNodes act, const uint4* __restrict__ split,
+	const float4* __restrict__ primLo, const float4* __restrict__ primHi, const uint32_t* __restrict__ leftBefore, uint32_t* __restrict__ orderOut, uint32_t* __restrict__ nodeOfOut, int* nextCb )
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= T) return;
+	const uint32_t a = nodeOf[i];
+	if (a == TOP_NONE) { orderOut[i] = order[i], nodeOfOut[i] = TOP_NONE; return; }
+	const uint4 sp = split[a];
+	float c[3];
+	const bool left = topGoesLeft( i, a, order, act, sp, primLo, primHi, c );
+	const uint32_t begin = act.begin[a], rank = leftBefore[i] - leftBefore[begin];
+	const uint32_t to = left ? begin + rank : begin + sp.y + (i - begin - rank), where = left ? sp.z : sp.w;
+	orderOut[to] = order[i], nodeOfOut[to] = where;
+	// (the lanes of a warp that go to the same child speak through one of them, as in topBinKernel)
+	const uint32_t group = __match_any_sync( __activemask(), where );
+	int gl[3], gh[3];
+	for (int k = 0; k < 3; k++) gl[k] = __reduce_min_sync( group, orderedInt( c[k] ) ), gh[k] = __reduce_max_sync( group, orderedInt( c[k] ) );
+	if (where != TOP_NONE && (threadIdx.x & 31u) == (uint32_t)__ffs( group ) - 1u)
+		for (int k = 0; k < 3; k++) atomicMin( nextCb + where * 6 + k, gl[k] ), atomicMax( nextCb + where * 6 + 3 + k, gh[k] );
 }
 
 // ---- 3b / 4b. agglomerative alternative to the radix tree: PLOC (Meister, Bittner: "Parallel Locally-Ordered Clustering for Bounding Volume
@@ -1218,6 +1505,22 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 		for (int k = 0; k < 2; k++) oCRef[k] = take( (size_t)T * 4 ), oCLo[k] = take( (size_t)T * 16 ), oCHi[k] = take( (size_t)T * 16 );
 		oNearest = take( (size_t)T * 4 ), oFlag = take( (size_t)T * 4 ), oOffset = take( (size_t)T * 4 ), oScan = take( scanBytes );
 	}
+	size_t oSpFlag = 0, oSpRef = 0, oSpLast = 0, oItRef = 0, oItFirst = 0, oItLast = 0, oItLo = 0, oItHi = 0, oItBefore = 0;
+	if (builder == 3)
+	{
+		cub::DeviceScan::ExclusiveSum( nullptr, scanBytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)T, s );
+		oSpFlag = take( (size_t)T * 4 ), oSpRef = take( (size_t)T * 4 ), oSpLast = take( (size_t)T * 4 ), oItRef = take( (size_t)T * 4 ), oItFirst = take( (size_t)T * 4 );
+		oItLast = take( (size_t)T * 4 ), oItLo = take( (size_t)T * 16 ), oItHi = take( (size_t)T * 16 ), oItBefore = take( (size_t)T * 4 ), oScan = take( scanBytes );
+	}
+	// builder 4: the large nodes of two levels (at most T / SAHB_CLUSTER each), their bins and splits, the list of small subtrees
+	const uint32_t topCap = T / SAHB_CLUSTER + 2;
+	size_t oTopNodes[2] = { 0, 0 }, oTopBins = 0, oTopSplit = 0, oTopSmall = 0;
+	if (builder == 4)
+	{
+		cub::DeviceScan::ExclusiveSum( nullptr, scanBytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)T, s );
+		for (int k = 0; k < 2; k++) oTopNodes[k] = take( (size_t)topCap * 36 );
+		oTopBins = take( (size_t)topCap * 3 * TOP_BINS * 28 ), oTopSplit = take( (size_t)topCap * 16 ), oTopSmall = take( ((size_t)T / 2 + 2) * 16 ), oScan = take( scanBytes );
+	}
 	if ((e = cudaMallocAsync( (void**)&scratch, off, s )) != cudaSuccess) return e;
 	float4 *primLo = (float4*)(scratch + oPrimLo), *primHi = (float4*)(scratch + oPrimHi), *nodeLo = (float4*)(scratch + oNodeLo), *nodeHi = (float4*)(scratch + oNodeHi);
 	float4 *planLo = (float4*)(scratch + oPlanLo), *planHi = (float4*)(scratch + oPlanHi);
@@ -1238,26 +1541,107 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	if ((e = cudaMemsetAsync( visits, 0, (size_t)T * 4, s )) != cudaSuccess) return done( e );
 	const uint32_t blocks = (T + 255) / 256;
 	primBoundsKernel<<<blocks, 256, 0, s>>>( dVerts, T, primLo, primHi, cbounds );
-	mortonKernel<<<blocks, 256, 0, s>>>( primLo, primHi, T, cbounds, keys, vals );
-	if ((e = cub::DeviceRadixSort::SortPairs( scratch + oSort, sortBytes, keys, keys2, vals, vals2, (int)T, 0, 63, s )) != cudaSuccess) return done( e );
-	if (!ploc)
+	if (builder == 4)
 	{
-		radixTreeKernel<<<blocks, 256, 0, s>>>( keys2, (int)T, childL, childR, first, count, parI, parL );
-		if (builder == 3)
+		// binned SAH from the top (see 3d): no sort, no radix tree.  order / nodeOf: two copies each (the key arrays serve as scratch)
+		uint32_t *order[2] = { vals, vals2 }, *nodeOf[2] = { (uint32_t*)keys, (uint32_t*)keys + T }, *flag = (uint32_t*)keys2, *leftBefore = (uint32_t*)keys2 + T;
+		TopNodes act[2];
+		for (int k = 0; k < 2; k++)
 		{
-			// SAH bottoms: the list of subtree roots in the (now free) second key array, its length in the block of small values
-			uint32_t *roots = (uint32_t*)keys, *rootCount = counters + 8;
-			if ((e = cudaMemsetAsync( rootCount, 0, 4, s )) != cudaSuccess) return done( e );
-			sahbRootsKernel<<<blocks, 256, 0, s>>>( T, count, parI, roots, rootCount );
+			char* b = scratch + oTopNodes[k];
+			act[k].id = (uint32_t*)b, act[k].begin = (uint32_t*)b + topCap, act[k].count = (uint32_t*)b + 2 * topCap, act[k].cb = (int*)b + 3 * topCap;
+		}
+		TopBins bins;
+		bins.count = (int*)(scratch + oTopBins), bins.lo = bins.count + (size_t)topCap * 3 * TOP_BINS, bins.hi = bins.lo + (size_t)topCap * 3 * TOP_BINS * 3;
+		uint4 *split = (uint4*)(scratch + oTopSplit), *smallRoots = (uint4*)(scratch + oTopSmall);
+		uint32_t *nextCount = counters + 8, *smallCount = counters + 9, *nodeCounter = counters + 10;
+		const uint32_t init[3] = { 0, 0, 1 }; // (node 0 is the root)
+		if ((e = cudaMemcpyAsync( nextCount, init, 12, cudaMemcpyHostToDevice, s )) != cudaSuccess) return done( e );
+		topInitKernel<<<blocks, 256, 0, s>>>( T, order[0], nodeOf[0], act[0], cbounds, parI );
+		int cur = 0;
+		uint32_t nAct = 1, nSmall = 0;
+		if (T <= SAHB_CLUSTER)
+		{
+			const uint4 whole = make_uint4( 0, 0, T, 0 );
+			if ((e = cudaMemcpyAsync( smallRoots, &whole, 16, cudaMemcpyHostToDevice, s )) != cudaSuccess) return done( e );
+			nAct = 0, nSmall = 1;
+			if ((e = cudaMemcpyAsync( smallCount, &nSmall, 4, cudaMemcpyHostToDevice, s )) != cudaSuccess) return done( e );
+		}
+		for (int level = 0; nAct; level++)
+		{
+			if (level > 4096) return done( cudaErrorUnknown ); // (every level splits every large node into two non-empty parts)
+			const uint32_t clearThreads = max( nAct * 3 * TOP_BINS, min( 2 * nAct, topCap ) * 6 );
+			topClearBinsKernel<<<(clearThreads + 255) / 256, 256, 0, s>>>( nAct, bins, act[cur ^ 1].cb, min( 2 * nAct, topCap ) );
+			topBinKernel<<<blocks, 256, 0, s>>>( T, order[cur], nodeOf[cur], act[cur], primLo, primHi, bins );
+			topSplitKernel<<<(nAct * 32 + 127) / 128, 128, 0, s>>>( nAct, act[cur], bins, split, act[cur ^ 1], nextCount, smallRoots, smallCount, nodeCounter, childL, childR, count, parI, parL );
+			topFlagKernel<<<blocks, 256, 0, s>>>( T, order[cur], nodeOf[cur], act[cur], split, primLo, primHi, flag );
+			if ((e = cub::DeviceScan::ExclusiveSum( scratch + oScan, scanBytes, flag, leftBefore, (int)T, s )) != cudaSuccess) return done( e );
+			topScatterKernel<<<blocks, 256, 0, s>>>( T, order[cur], nodeOf[cur], act[cur], split, primLo, primHi, leftBefore, order[cur ^ 1], nodeOf[cur ^ 1], act[cur ^ 1].cb );
+			uint32_t h[2];
+			if ((e = cudaMemcpyAsync( h, nextCount, 8, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
+			if ((e = cudaMemsetAsync( nextCount, 0, 4, s )) != cudaSuccess) return done( e );
+			if ((e = cudaStreamSynchronize( s )) != cudaSuccess) return done( e );
+			if (getenv( "B200_BUILD_TIMING" )) fprintf( stderr, "top-down level %d: %u large nodes -> %u, small subtrees so far %u\n", level, nAct, h[0], h[1] );
+			nAct = h[0], nSmall = h[1], cur ^= 1;
+			if (nAct > topCap) return done( cudaErrorUnknown );
+		}
+		if (nSmall)
+		{
 			static bool allowed = false;
 			const size_t smem = sizeof( SahbWarp ) * SAHB_WARPS;
 			if (!allowed)
 			{
-				if ((e = cudaFuncSetAttribute( sahbBuildKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem )) != cudaSuccess) return done( e );
+				if ((e = cudaFuncSetAttribute( sahbBuildKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem )) != cudaSuccess) return done( e );
 				allowed = true;
 			}
-			// (at most T / 3 roots: every one of them has at least three triangles; warps beyond the count leave at once)
-			sahbBuildKernel<<<(T / 3 + SAHB_WARPS) / SAHB_WARPS, SAHB_WARPS * 32, smem, s>>>( roots, rootCount, vals2, primLo, primHi, childL, childR, first, count, parI, parL );
+			sahbBuildKernel<false><<<(nSmall + SAHB_WARPS - 1) / SAHB_WARPS, SAHB_WARPS * 32, smem, s>>>( smallRoots, smallCount, SahbItems(), SahbSparse(), childL, childR, count, parI, parL,
+				nodeLo, nodeHi, order[cur], primLo, primHi, nodeCounter );
+		}
+		if (order[cur] != vals2) { uint32_t* t = vals; vals = vals2, vals2 = t; } // (what follows calls the final order vals2)
+		binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, count, parI, parL, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost, visits );
+	}
+	else
+	{
+	mortonKernel<<<blocks, 256, 0, s>>>( primLo, primHi, T, cbounds, keys, vals );
+	if ((e = cub::DeviceRadixSort::SortPairs( scratch + oSort, sortBytes, keys, keys2, vals, vals2, (int)T, 0, 63, s )) != cudaSuccess) return done( e );
+	}
+	if (builder == 4) {}
+	else if (!ploc)
+	{
+		radixTreeKernel<<<blocks, 256, 0, s>>>( keys2, (int)T, childL, childR, first, count, parI, parL );
+		if (builder == 3)
+		{
+			// SAH inside the radix tree's cells, level by level (see 3c)
+			SahbSparse sparse = { (uint32_t*)(scratch + oSpFlag), (uint32_t*)(scratch + oSpRef), (uint32_t*)(scratch + oSpLast) };
+			SahbItems items = { (uint32_t*)(scratch + oItRef), (uint32_t*)(scratch + oItFirst), (uint32_t*)(scratch + oItLast), (float4*)(scratch + oItLo), (float4*)(scratch + oItHi) };
+			uint32_t *before = (uint32_t*)(scratch + oItBefore), *rootCount = counters + 8;
+			uint4* roots = (uint4*)keys; // (the first key array is free after the sort: T / 2 roots of 16 bytes)
+			static bool allowed = false;
+			const size_t smem = sizeof( SahbWarp ) * SAHB_WARPS;
+			if (!allowed)
+			{
+				if ((e = cudaFuncSetAttribute( sahbBuildKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem )) != cudaSuccess) return done( e );
+				allowed = true;
+			}
+			sahbInitKernel<<<blocks, 256, 0, s>>>( T, sparse );
+			// (levels above the first: tools/ab_sahb.sh -- on the sphere field they trade primary rays for shadow rays, -3.5 % / +2.8 %; the default is 1)
+			for (int level = 0; level < g_sahLevels; level++)
+			{
+				if (level > 32) return done( cudaErrorUnknown );
+				if ((e = cub::DeviceScan::ExclusiveSum( scratch + oScan, scanBytes, sparse.flag, before, (int)T, s )) != cudaSuccess) return done( e );
+				if ((e = cudaMemsetAsync( rootCount, 0, 4, s )) != cudaSuccess) return done( e );
+				sahbCompactKernel<<<blocks, 256, 0, s>>>( T, sparse, before, vals2, primLo, primHi, nodeLo, nodeHi, items );
+				sahbRootsKernel<<<blocks, 256, 0, s>>>( T, sparse, before, items, first, count, parI, roots, rootCount, (uint32_t)SAHB_CLUSTER );
+				uint32_t h[2]; // items of this level (the last position's running sum + its flag: position T - 1 always belongs to the last item, whose start is counted before it unless it is a single), roots
+				uint32_t lastBefore = 0, lastFlag = 0, nRoots = 0;
+				if ((e = cudaMemcpyAsync( &lastBefore, before + (T - 1), 4, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
+				if ((e = cudaMemcpyAsync( &lastFlag, sparse.flag + (T - 1), 4, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
+				if ((e = cudaMemcpyAsync( &nRoots, rootCount, 4, cudaMemcpyDeviceToHost, s )) != cudaSuccess) return done( e );
+				if ((e = cudaStreamSynchronize( s )) != cudaSuccess) return done( e );
+				h[0] = lastBefore + lastFlag, h[1] = nRoots;
+				if (h[0] <= 1 || !h[1]) break; // everything is inside the root's subtree
+				sahbBuildKernel<true><<<(h[1] + SAHB_WARPS - 1) / SAHB_WARPS, SAHB_WARPS * 32, smem, s>>>( roots, rootCount, items, sparse, childL, childR, count, parI, parL, nodeLo, nodeHi );
+			}
 		}
 		binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, count, parI, parL, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost, visits );
 	}

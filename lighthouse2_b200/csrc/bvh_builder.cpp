@@ -19,6 +19,7 @@
 namespace b200 {
 
 float g_sahPrimCost = 0.4f;
+int g_sahLevels = 1;
 
 namespace {
 

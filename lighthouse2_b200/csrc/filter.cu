@@ -377,11 +377,12 @@ __global__ void __launch_bounds__( 256 ) taaKernel( const float4* __restrict__ p
 }
 
 // unsharp mask against the blur of the TAA, then the gamma of the last reconstruct pass is taken off again (the host's post-process
-// applies its own).  The one-pixel border of the frame is not written, as in the reference.
+// applies its own).  The one-pixel border of the frame, which the reference leaves as it finds it (finalize_shared.h:438, :475), is black.
 __global__ void __launch_bounds__( 256 ) unsharpenKernel( const float4* __restrict__ pixels, float4* __restrict__ frame, const int w, const int h )
 {
 	const int x = threadIdx.x + blockIdx.x * blockDim.x, y = threadIdx.y + blockIdx.y * blockDim.y;
-	if (x == 0 || y == 0 || x >= w - 1 || y >= h - 1) return;
+	if (x >= w || y >= h) return;
+	if (x == 0 || y == 0 || x == w - 1 || y == h - 1) { frame[x + y * w] = make_float4( 0, 0, 0, 0 ); return; }
 	const float4 p0 = pixels[x - 1 + (y - 1) * w], p1 = pixels[x + (y - 1) * w], p2 = pixels[x + 1 + (y - 1) * w], p3 = pixels[x + 1 + y * w];
 	const float4 p4 = pixels[x + 1 + (y + 1) * w], p5 = pixels[x + (y + 1) * w], p6 = pixels[x - 1 + (y + 1) * w], p7 = pixels[x - 1 + y * w];
 	const float4 c = pixels[x + y * w];
@@ -404,7 +405,8 @@ __global__ void __launch_bounds__( 256 ) unsharpenKernel( const float4* __restri
 __global__ void __launch_bounds__( 256 ) finishNoTaaKernel( const float4* __restrict__ pixels, float4* __restrict__ frame, const int w, const int h )
 {
 	const int x = threadIdx.x + blockIdx.x * blockDim.x, y = threadIdx.y + blockIdx.y * blockDim.y;
-	if (x == 0 || y == 0 || x >= w - 1 || y >= h - 1) return;
+	if (x >= w || y >= h) return;
+	if (x == 0 || y == 0 || x == w - 1 || y == h - 1) { frame[x + y * w] = make_float4( 0, 0, 0, 0 ); return; }
 	const float4 p = pixels[x + y * w];
 	frame[x + y * w] = make_float4( sqrtf( p.x ), sqrtf( p.y ), sqrtf( p.z ), 0 );
 }

@@ -167,7 +167,7 @@ int RenderCore::Setting( const char* name, float value )
 	// ("clampDirect", "clampIndirect", "filter", "TAA": with the frame settings in wavefront.cu -- honoured when Setting filterCore is on)
 	// B200-specific keys
 	if (!strcmp( name, "isectMode" )) { isect = value >= 0.5f ? ISECT_WATERTIGHT : ISECT_REFERENCE; return 0; }
-	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 2.5f ? 3 : (value >= 1.5f ? 2 : (value >= 0.5f ? 1 : 0)); return 0; } // 1: LBVH, 2: PLOC, 3: LBVH with SAH bottoms (build.cu)
+	if (!strcmp( name, "gpuBuild" )) { gpuBuild = value >= 3.5f ? 4 : (value >= 2.5f ? 3 : (value >= 1.5f ? 2 : (value >= 0.5f ? 1 : 0))); return 0; } // 1: radix tree, 2: PLOC, 3: SAH inside the radix tree's cells, 4: binned SAH from the top (build.cu)
 	if (!strcmp( name, "deviceTlas" )) { deviceTlas = value >= 0.5f; tlasDirty = true; return 0; }
 	if (!strcmp( name, "twoStreams" )) { twoStreams = value >= 0.5f; return 0; }
 	if (!strcmp( name, "zeroCopy" )) { zeroCopy = value >= 0.5f; return 0; }
@@ -180,6 +180,7 @@ int RenderCore::Setting( const char* name, float value )
 	if (!strcmp( name, "refit" )) { allowRefit = value >= 0.5f; return 0; }
 	if (!strcmp( name, "refitWalk" )) { refitWalk = value >= 0.5f; return 0; }
 	if (!strcmp( name, "l2Persist" )) { if (value < 0 || value > 1) return fail( "Setting l2Persist: 0 (off) .. 1 (fraction of the L2 that may be set aside)" ); l2Persist = value; return 0; }
+	if (!strcmp( name, "gpuBuildLevels" )) { if (!(value >= 1)) return fail( "Setting gpuBuildLevels: >= 1" ); g_sahLevels = value > 64 ? 64 : (int)value; return 0; }
 	if (!strcmp( name, "sahPrimCost" )) { if (!(value > 0)) return fail( "Setting sahPrimCost: > 0" ); g_sahPrimCost = value; return 0; }
 	if (!strcmp( name, "buildThreads" )) { buildThreads = value < 1 ? 1 : (int)value; return 0; }
 	return SettingWavefront( name, value );
@@ -250,14 +251,15 @@ int RenderCore::uploadVertexNormals( const MeshRec& m, const void* coreTris )
 	return e == cudaSuccess ? 0 : fail( "triangle attribute upload", e );
 }
 
-// SetGeometry with Setting gpuBuild = 1: the vertices go up once, the topology is built on the device (build.cu) and the refit
+// SetGeometry with Setting gpuBuild >= 1 (the default): the vertices go up once, the topology is built on the device (build.cu) and the refit
 // that follows fills boxes, quantised planes and triangle records.  Nothing but 12 bytes per level comes back to the host.
 int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T, const void* coreTris, double t0 )
 {
 	MeshRec m;
 	m.nodeBase = blasNodeEnd, m.triBase = triEnd, m.triCount = T;
 	if ((uint64_t)m.triBase + T + 32 >= (1ull << 27)) return fail( "SetGeometry: more than 2^27 triangles in one core (queue entries carry 27-bit triangle indices)" );
-	const uint32_t maxNodes = T + 64; // one wide node per binary inner node at most
+	// wide nodes: a seventh to a tenth of the triangles in practice, one per binary inner node at worst: room for T / 2 first, for all of them if the collapse runs out
+	uint32_t maxNodes = T / 2 + 64;
 	// shading records: the refit below writes the geometric normals; only CoreTri::material has to come from the host
 	std::vector<ShadeRec> shade;
 	if (coreTris)
@@ -278,8 +280,17 @@ int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T,
 	if (coreTris) e = cudaMemcpyAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, shade.data(), (size_t)T * 16, cudaMemcpyHostToDevice, stream );
 	else e = cudaMemsetAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, 0, (size_t)T * 16, stream );
 	if (e != cudaSuccess) return fail( "shading upload", e );
-	if ((e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
-		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild )) != cudaSuccess) return fail( "GPU BVH build", e );
+	e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
+		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild );
+	if (e == cudaErrorMemoryAllocation)
+	{
+		cudaGetLastError();
+		maxNodes = T + 64;
+		if ((e = nodePool.reserve( (size_t)(m.nodeBase + maxNodes + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
+		e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
+			m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild );
+	}
+	if (e != cudaSuccess) return fail( "GPU BVH build", e );
 	if ((int)m.levelStart.size() - 1 > MAX_TREE_LEVELS) return fail( "SetGeometry: the device-built tree is deeper than the traversal stack allows (wide_bvh.h MAX_TREE_LEVELS)" );
 	if (prepareRefit( m )) return 1;
 	m.built = true;
@@ -319,7 +330,12 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 	}
 	const double t0 = nowMs();
 	const uint32_t T = (uint32_t)triangleCount;
-	if (gpuBuild && T >= 64) return buildOnDevice( meshIdx, vertexData, T, coreTris, t0 );
+	// on-disk cache of the host-built tree (bvh_cache.cpp), keyed by the vertex data; B200_BVH_CACHE names the directory
+	static const char* cacheEnv = getenv( "B200_BVH_CACHE" );
+	const bool useCache = cacheEnv && *cacheEnv && T >= 1024;
+	// the tree is built on the device (Setting gpuBuild, default 4: binned SAH from the top) unless the mesh is tiny, the host builder
+	// was asked for (gpuBuild = 0) or its trees are kept on disk
+	if (gpuBuild && T >= 64 && !useCache) return buildOnDevice( meshIdx, vertexData, T, coreTris, t0 );
 	// (the passes over all triangles of a large mesh -- here, in the builder and in the staging below -- run on buildThreads threads)
 	std::vector<Aabb> boxes( T );
 	ParallelRange( buildThreads, T, 65536, [&]( size_t begin, size_t end ) { for (size_t i = begin; i < end; i++)
@@ -328,9 +344,6 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 		for (int k = 0; k < 3; k++) boxes[i].grow( vertexData + (size_t)(3 * i + k) * 4 );
 	} } );
 	WideBvh bvh;
-	// on-disk cache of the host-built tree (bvh_cache.cpp), keyed by the vertex data; B200_BVH_CACHE names the directory
-	static const char* cacheEnv = getenv( "B200_BVH_CACHE" );
-	const bool useCache = cacheEnv && *cacheEnv && T >= 1024;
 	uint64_t cacheKey = 0;
 	bool fromCache = false;
 	if (useCache)

@@ -99,6 +99,7 @@ struct WideBvh {
 	Aabb bounds;
 };
 
+extern int g_sahLevels;      // builder 3 on the device: how many levels of the radix tree's cells are rebuilt by SAH (Setting "gpuBuildLevels"; 1 = the bottoms only)
 extern float g_sahPrimCost; // builder tunable: SAH cost of one leaf triangle relative to one wide-node visit
 
 // Binned-SAH BVH2 over `n` primitive boxes, collapsed to the 8-wide layout above.

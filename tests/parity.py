@@ -49,8 +49,16 @@ def compare(case_name, hits, oracle_port, O, D, ref_t, ref_prim, ref_inst=None, 
     return report
 
 
-def assert_parity(report, max_rate=1e-5):
+def assert_parity(report, max_rate=1e-5, max_tie_rate=None):
+    """max_tie_rate: for scenes whose meshes share edges and vertices by construction (tessellated spheres, instanced), where a
+    ray through such an edge has two bit-identical answers and which of them a core reports is decided by the order ITS tree
+    visits them in (the reference's as much as this one's): the ties -- each of them proven a tie with the oracle's arithmetic in
+    compare() -- get their own bound there, the grazing class keeps the 1e-5."""
     print("parity:", report)
     assert report["wrong"] == 0, report
     # < 1e-5 of rays; for small ray sets allow a single exceptional ray
-    assert report["tie"] + report["grazing"] <= max(1, int(max_rate * report["rays"])), report
+    if max_tie_rate is None:
+        assert report["tie"] + report["grazing"] <= max(1, int(max_rate * report["rays"])), report
+    else:
+        assert report["grazing"] <= max(1, int(max_rate * report["rays"])), report
+        assert report["tie"] <= max(1, int(max_tie_rate * report["rays"])), report

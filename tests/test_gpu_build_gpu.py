@@ -16,15 +16,22 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 BUILDER = 1
 
 
-@pytest.fixture(autouse=True, params=[1, 2, 3], ids=["lbvh", "ploc", "sahb"])
+@pytest.fixture(autouse=True, params=[1, 2, 3, 4, 5], ids=["lbvh", "ploc", "sahb", "sahb-all-levels", "sah"])
 def _builder(request):
     global BUILDER
     BUILDER = request.param
 
 
+def _choose_builder(rc):
+    """Setting gpuBuild = 1 (radix tree), 2 (PLOC), 3 (SAH inside the radix tree's cells: the bottoms only, or -- 4 here -- every level),
+    4 (binned SAH from the top; 5 here)."""
+    rc.Setting("gpuBuild", 4 if BUILDER == 5 else min(BUILDER, 3))
+    rc.Setting("gpuBuildLevels", 64 if BUILDER == 4 else 1)
+
+
 def _gpu_core(case):
     rc = core.RenderCoreB200(0)
-    rc.Setting("gpuBuild", BUILDER)
+    _choose_builder(rc)
     return cases.load_core(rc, case)
 
 
@@ -73,7 +80,7 @@ def test_gpu_tree_equals_sah_tree_on_the_sphere_field():
     out = []
     for gpu in (0, BUILDER):
         rc = core.RenderCoreB200(0)
-        rc.Setting("gpuBuild", gpu)
+        _choose_builder(rc) if gpu else rc.Setting("gpuBuild", 0)
         rc.SetGeometry(0, verts); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
         out.append(core.unpack_hits(rc.TraceClosest(*core.pack_rays(O, D, tmin=1e-4))))
         occ = rc.TraceAny(*core.pack_rays(O, D, tmin=1e-4, tmax=80.0))
@@ -117,7 +124,7 @@ def test_refit_after_gpu_build_and_second_mesh():
     O, D = scenes.random_rays(60_000, 6.0, seed=31)
     moved = (sph * np.float32(1.0) + np.float32(0.15) * np.sin(sph[..., ::-1] * np.float32(3.0))).astype(np.float32)
     rc = core.RenderCoreB200(0)
-    rc.Setting("gpuBuild", BUILDER)
+    _choose_builder(rc)
     cases.load_core(rc, dict(meshes=[sph, grid], instances=inst))
     rc.SetGeometry(0, moved)  # same triangle count: refit of the GPU-built tree
     rc.UpdateToplevel()
@@ -136,7 +143,7 @@ def test_gpu_built_tree_is_the_same_bytes_every_time():
     trees = []
     for _ in range(3):
         rc = core.RenderCoreB200(0)
-        rc.Setting("gpuBuild", BUILDER)
+        _choose_builder(rc)
         cases.load_core(rc, dict(meshes=[verts], instances=[(0, None)]))
         trees.append(rc.ReadTree())
         rc.Shutdown()

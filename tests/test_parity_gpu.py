@@ -118,7 +118,9 @@ def test_c4_class_refit_and_toplevel_rebuild_vs_oracle(oracles):
         hits = rc.TraceClosest(*core.pack_rays(O, D))
         t, prim, inst = port.trace(O, D, nthreads=8)
         rep = parity.compare("c4 frame %d" % frame, hits, port, O, D, t, prim, inst)
-        parity.assert_parity(rep)
+        # (1000 instances of a tessellated sphere: rays through shared edges.  At most 2 of 200 000 rays with the host-built tree, 5 with the
+        # device-built one that is the default now -- the count is a property of who visits which triangle first, not of an error)
+        parity.assert_parity(rep, max_tie_rate=1e-4)
         assert (prim >= 0).mean() > 0.3
         # one shadow ray per hit towards a point light (tmax = distance - 2 eps), any-hit <=> reference closest t < tmax
         hit = prim >= 0

@@ -22,7 +22,7 @@ for n in sizes:
         verts = gen(n)
         v4 = np.ones((verts.shape[0] * 3, 4), np.float32); v4[:, :3] = verts.reshape(-1, 3)
         row = {"scene": name, "triangles": int(verts.shape[0])}
-        for gpu in (0, 1, 2, 3):
+        for gpu in (0, 1, 2, 3, 4):
             best, first, hits = 1e9, None, 0
             for rep in range(2 if gpu == 0 and n > 2_000_000 else 3):
                 rc = core.RenderCoreB200(0)
@@ -37,6 +37,6 @@ for n in sizes:
                 rc.Shutdown()
             if gpu == 0 and use_cache:
                 row["host_build_first_s"], row["host_from_cache_s"], row["cache_hits"] = round(first, 4), round(best, 4), hits
-            name = ("host", "gpu", "ploc", "sahb")[gpu]
+            name = ("host", "gpu", "ploc", "sahb", "sah")[gpu]
             row[name + "_build_s"], row[name + "_nodes"] = round(best, 4), nodes
         print(json.dumps(row), flush=True)
