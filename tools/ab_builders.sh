@@ -1,5 +1,6 @@
 #!/bin/bash
-# Trace rates by the tree they run on: host SAH builder (Setting gpuBuild = 0), Morton radix tree (1), agglomerative clustering (2).
+# Trace rates by the tree they run on: host SAH builder (Setting gpuBuild = 0), Morton radix tree (1), agglomerative clustering (2);
+# tools/ab_sahb.sh has the SAH builders (3, 4).
 # C2 scene: the 1080p waves and the 4K frame of bench.py; C3 soup (10 M triangles): the 1080p frame of tools/bench_configs.py.
 for g in 0 1 2 0 2; do
   python bench.py --no-cpu-baseline --no-e2e --no-check --no-refit --steps 5 --warmup 2 --wave-steps 30 --setting gpuBuild=$g 2>/dev/null | tail -1 | python -c "
