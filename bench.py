@@ -598,6 +598,24 @@ def run_b200(args):
                              "launches": 1, "bytes_survey_formula": b, "gbs": b / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": b / (ms * 1e-3) / 1e9 / peak,
                              "bytes_with_writes": 144 * verts.shape[0] + 224 * nodes,
                              "note": "survey formula = 48 T + 2 x 80 x nodes; with the record / shading-normal writes and the per-node float boxes the kernel moves 144 T + 224 nodes"}
+            # the build itself: SetGeometry wall time of a fresh core, vertex upload, tree, refit fill and read-back of the
+            # root box included; the default builder (build.cu, binned SAH on the device) and the host builder (bvh_builder.cpp) on this box's threads
+            def build_ms(setting):
+                best = 1e9
+                for _ in range(3):
+                    rb = core.RenderCoreB200(local)
+                    rb.Setting("gpuBuild", setting)
+                    t0 = time.perf_counter()
+                    rb.SetGeometry(0, v4)
+                    best = min(best, (time.perf_counter() - t0) * 1e3)
+                    n = rb.GetCoreStats()["wideNodeCount"]
+                    rb.Shutdown()
+                return best, n
+            dms, dn = build_ms(4)
+            hms, hn = build_ms(0)
+            line["build"] = {"workload": "SetGeometry of the C2 mesh (%d triangles), wall time, best of 3" % verts.shape[0], "device_sah_ms": dms, "device_wide_nodes": dn,
+                             "host_builder_ms": hms, "host_wide_nodes": hn, "host_threads": os.cpu_count(),
+                             "note": "the timed frames run on the default (device-built) tree; trace rate against the host-built tree: profiles/r02_experiments.md"}
         if world == 1 and not args.no_filter:
             # filter mode (Setting filterCore: the reference's RenderCore_Optix7Filter -- one diffuse bounce, per-pixel features, SVGF-style
             # reconstruction + TAA, filter.cu) on the same scene at the wave leg's size, 1 spp: device time of the filter and of the frame

@@ -368,7 +368,7 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 				const int wt = (int)w.weight[0][j];
 				for (int a = 0; a < 3; a++)
 				{
-					const int b = min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) );
+					const int b = max( 0, min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) ) );
 					for (int k = 0; k < 3; k++) atomicMin( &w.binLo[a][b][k], l[k] ), atomicMax( &w.binHi[a][b][k], h[k] );
 					atomicAdd( &w.binWeight[a][b], wt ), atomicAdd( &w.binItems[a][b], 1 );
 				}
@@ -411,7 +411,7 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 				{
 					const uint32_t j = j0 + lane;
 					const bool have = j < begin + count;
-					const bool left = have && min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) ) <= b;
+					const bool left = have && max( 0, min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) ) ) <= b;
 					const uint32_t ml = __ballot_sync( 0xffffffffu, left ), mr = __ballot_sync( 0xffffffffu, have && !left ), below = (1u << lane) - 1u;
 					if (have)
 					{
@@ -487,7 +487,7 @@ struct TopBins { int *lo, *hi, *count; };                       // per node and 
 __device__ __forceinline__ int topBinOf( const float c, const float cmin, const float cmax )
 {
 	const float scale = cmax > cmin ? (float)TOP_BINS * 0.999f / (cmax - cmin) : 0.f;
-	return min( TOP_BINS - 1, (int)((c - cmin) * scale) );
+	return max( 0, min( TOP_BINS - 1, (int)((c - cmin) * scale) ) ); // (max: a centroid that is not a number must not name a bin outside the node's)
 }
 
 __global__ void topInitKernel( const uint32_t T, uint32_t* __restrict__ order, uint32_t* __restrict__ nodeOf, const TopNodes act, const int* __restrict__ centroidBounds, uint32_t* parentInner )

@@ -17,3 +17,7 @@ ncu --set full --clock-control none --import-source on -k regex:'shadeKernel|acc
 python tools/bench_configs.py refit c4 --frames 3 > gpurun_out/r02_cfg_plain.jsonl 2> gpurun_out/r02_cfg_plain.err || exit 1
 ncu --set full --clock-control none --import-source on -k regex:'refitWalkKernel|tlasBuildKernel|refitParents' -c 10 -f -o gpurun_out/r02_update python tools/bench_configs.py refit c4 --frames 3 > gpurun_out/r02_ncu_update.log 2>&1
 ls -la gpurun_out/*.ncu-rep
+# the default mesh builder (binned SAH on the device) and the refit as it is at the end of the round
+python tools/probes/build_once.py > gpurun_out/r02_build_plain.log 2>&1 || exit 1
+ncu --set full --clock-control none --import-source on -k regex:'top.*Kernel|sahb.*Kernel|binaryBoxesKernel|collapse.*Kernel|refitWalkKernel|primBoundsKernel' -c 120 -f -o gpurun_out/r02_build python tools/probes/build_once.py > gpurun_out/r02_ncu_build.log 2>&1
+python tools/ncu_kernel_summary.py gpurun_out/r02_build.ncu-rep --json gpurun_out/r02_ncu_build.json > gpurun_out/r02_ncu_build.txt
