@@ -63,6 +63,54 @@ def test_small_cases_golden_with_gpu_built_tree(make):
     parity.assert_parity(rep)
 
 
+@pytest.mark.parametrize("n_tris", [64, 65, 100, 255, 256, 257, 258, 300, 511, 513, 1000, 4097])
+def test_sizes_around_the_builders_thresholds(n_tris):
+    """64 triangles is the smallest mesh the device builds, 256 the largest subtree a warp finishes in shared memory: every size
+    around them, against the exhaustive search of the oracle (which needs no tree)."""
+    case = cases.case_soup(n_tris=n_tris, n_rays=20_000, seed=100 + n_tris)
+    O, D = case["rays"]
+    rc = _gpu_core(case)
+    h = core.unpack_hits(rc.TraceClosest(*core.pack_rays(O, D)))
+    port = cases.load_oracle(case, "port")
+    tb, pb, _ = port.trace(O, D, nthreads=8, mode="brute")
+    rc.Shutdown()
+    assert np.array_equal(h["t"].view(np.uint32), tb.view(np.uint32))
+    assert (h["prim"] != pb).mean() < 1e-3 and (pb >= 0).sum() > 50  # (ids may differ on exact ties only: t is bit-equal)
+
+
+@pytest.mark.parametrize("shape", ["identical", "one-line", "flat", "two-clumps", "huge-and-tiny"])
+def test_degenerate_distributions(shape):
+    """Inputs on which a split search finds nothing to separate, or almost nothing: all triangles the same, all centroids on a line or in
+    a plane, two far clumps, one triangle a million times the size of the others.  The build must end and the hits must be the exhaustive
+    search's."""
+    rng = np.random.default_rng(77)
+    n = 3000
+    tri = np.asarray([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    if shape == "identical":
+        verts = np.repeat(tri[None], n, axis=0)
+    elif shape == "one-line":
+        verts = tri[None] * np.float32(0.3) + np.stack([np.linspace(-5, 5, n), np.zeros(n), np.zeros(n)], 1).astype(np.float32)[:, None, :]
+    elif shape == "flat":
+        off = np.stack([rng.uniform(-5, 5, n), rng.uniform(-5, 5, n), np.zeros(n)], 1).astype(np.float32)
+        verts = tri[None] * np.float32(0.3) + off[:, None, :]
+    elif shape == "two-clumps":
+        off = rng.normal(0, 0.05, (n, 3)).astype(np.float32) + np.where(np.arange(n)[:, None] % 2 == 0, -4.0, 4.0).astype(np.float32)
+        verts = tri[None] * np.float32(0.1) + off[:, None, :]
+    else:
+        verts = scenes.triangle_soup(n, seed=3, extent=1.0, edge=1e-3)
+        verts[0] = np.asarray([[-4e3, -4e3, 2], [4e3, -4e3, 2], [0, 6e3, 2]], np.float32)
+    verts = np.ascontiguousarray(verts, np.float32)
+    O, D = scenes.random_rays(30_000, 6.0, seed=9)
+    case = dict(name=shape, meshes=[verts], instances=[(0, None)], rays=(O, D))
+    rc = _gpu_core(case)
+    h = core.unpack_hits(rc.TraceClosest(*core.pack_rays(O, D)))
+    port = cases.load_oracle(case, "port")
+    tb, pb, _ = port.trace(O, D, nthreads=8, mode="brute")
+    rc.Shutdown()
+    assert np.array_equal(h["t"].view(np.uint32), tb.view(np.uint32)), shape
+    assert (pb >= 0).any()
+
+
 def test_bigger_soup_vs_oracle_with_gpu_built_tree():
     rep, _ = _against_oracle(cases.case_soup(n_tris=200_000, n_rays=300_000, seed=21), golden=False)
     parity.assert_parity(rep)
