@@ -28,6 +28,7 @@
 #endif
 #define B200_USE_GROUP_COLLAPSE (B200_GROUP_COLLAPSE && B200_DP_COLLAPSE)
 #include <vector>
+#include <chrono>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -233,7 +234,7 @@ __global__ void binaryBoxesKernel( const uint32_t* __restrict__ sortedPrim, cons
 #ifndef SAHB_BINS_N
 #define SAHB_BINS_N 16
 #endif
-constexpr int SAHB_BINS = SAHB_BINS_N, SAHB_WARPS = SAHB_CLUSTER <= 256 ? 4 : (SAHB_CLUSTER <= 512 ? 2 : 1); // (shared memory: 76 bytes per item and warp)
+constexpr int SAHB_BINS = SAHB_BINS_N, SAHB_WARPS = SAHB_CLUSTER <= 256 ? 4 : (SAHB_CLUSTER <= 1024 ? 2 : 1); // (shared memory: 38 bytes per item and warp)
 
 struct SahbSparse { uint32_t *flag, *ref, *last; };                         // per sorted position: an item starts here; its reference (LEAF | position, or its root) and last position
 struct SahbItems { uint32_t *ref, *first, *last; float4 *lo, *hi; };       // the items of a level, in position order
@@ -277,9 +278,10 @@ __global__ void sahbRootsKernel( const uint32_t n, const SahbSparse sp, const ui
 }
 
 struct SahbWarp {
-	float lo[2][3][SAHB_CLUSTER], hi[2][3][SAHB_CLUSTER]; // the items' boxes: [0] in tree order, [1] scratch of the partition
-	uint32_t ref[2][SAHB_CLUSTER], weight[2][SAHB_CLUSTER]; // reference and triangles of the item
+	float lo[3][SAHB_CLUSTER], hi[3][SAHB_CLUSTER];      // the items' boxes, where they were loaded: a split moves indices, not boxes
+	uint32_t ref[SAHB_CLUSTER], weight[SAHB_CLUSTER];     // reference and triangles of the item
 	uint32_t pool[SAHB_CLUSTER];                          // the items' spare indices
+	uint16_t order[2][SAHB_CLUSTER];                      // the items in tree order: [0] current, [1] scratch of the partition
 	int binLo[3][SAHB_BINS][3], binHi[3][SAHB_BINS][3], binWeight[3][SAHB_BINS], binItems[3][SAHB_BINS];
 	uint32_t stackId[24], stackBegin[24], stackCount[24], stackWeight[24];
 };
@@ -314,15 +316,15 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 		{
 			const uint32_t p = order[firstPos + j];
 			const float4 l = primLo[p], h = primHi[p];
-			w.ref[0][j] = LEAF | (firstPos + j), w.weight[0][j] = 1, w.pool[j] = freshBase + j; // (total - 2 of them are used)
-			w.lo[0][0][j] = l.x, w.lo[0][1][j] = l.y, w.lo[0][2][j] = l.z, w.hi[0][0][j] = h.x, w.hi[0][1][j] = h.y, w.hi[0][2][j] = h.z;
+			w.ref[j] = LEAF | (firstPos + j), w.weight[j] = 1, w.pool[j] = freshBase + j, w.order[0][j] = (uint16_t)j; // (total - 2 of them are used)
+			w.lo[0][j] = l.x, w.lo[1][j] = l.y, w.lo[2][j] = l.z, w.hi[0][j] = h.x, w.hi[1][j] = h.y, w.hi[2][j] = h.z;
 			wsum++;
 			continue;
 		}
 		const uint32_t r = it.ref[item0 + j], f1 = it.first[item0 + j], l1 = it.last[item0 + j];
 		const float4 l = it.lo[item0 + j], h = it.hi[item0 + j];
-		w.ref[0][j] = r, w.weight[0][j] = l1 - f1 + 1, w.pool[j] = (r & LEAF) ? f1 : (r == f1 ? l1 : f1);
-		w.lo[0][0][j] = l.x, w.lo[0][1][j] = l.y, w.lo[0][2][j] = l.z, w.hi[0][0][j] = h.x, w.hi[0][1][j] = h.y, w.hi[0][2][j] = h.z;
+		w.ref[j] = r, w.weight[j] = l1 - f1 + 1, w.pool[j] = (r & LEAF) ? f1 : (r == f1 ? l1 : f1), w.order[0][j] = (uint16_t)j;
+		w.lo[0][j] = l.x, w.lo[1][j] = l.y, w.lo[2][j] = l.z, w.hi[0][j] = h.x, w.hi[1][j] = h.y, w.hi[2][j] = h.z;
 		blo[0] = fminf( blo[0], l.x ), blo[1] = fminf( blo[1], l.y ), blo[2] = fminf( blo[2], l.z ), bhi[0] = fmaxf( bhi[0], h.x ), bhi[1] = fmaxf( bhi[1], h.y ), bhi[2] = fmaxf( bhi[2], h.z );
 		wsum += l1 - f1 + 1;
 		sparse.flag[f1] = 0; // the item is inside from now on ...
@@ -350,7 +352,10 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 			// centroid bounds (twice the centroid: lo + hi)
 			float cmin[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, cmax[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
 			for (uint32_t j = begin + lane; j < begin + count; j += 32)
-				for (int a = 0; a < 3; a++) { const float c = w.lo[0][a][j] + w.hi[0][a][j]; cmin[a] = fminf( cmin[a], c ), cmax[a] = fmaxf( cmax[a], c ); }
+			{
+				const uint32_t o = w.order[0][j];
+				for (int a = 0; a < 3; a++) { const float c = w.lo[a][o] + w.hi[a][o]; cmin[a] = fminf( cmin[a], c ), cmax[a] = fmaxf( cmax[a], c ); }
+			}
 			for (int a = 0; a < 3; a++) for (int d = 16; d; d >>= 1)
 				cmin[a] = fminf( cmin[a], __shfl_xor_sync( 0xffffffffu, cmin[a], d ) ), cmax[a] = fmaxf( cmax[a], __shfl_xor_sync( 0xffffffffu, cmax[a], d ) );
 			float scale[3];
@@ -364,11 +369,12 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 			for (uint32_t j = begin + lane; j < begin + count; j += 32)
 			{
 				int l[3], h[3];
-				for (int a = 0; a < 3; a++) l[a] = orderedInt( w.lo[0][a][j] ), h[a] = orderedInt( w.hi[0][a][j] );
-				const int wt = (int)w.weight[0][j];
+				const uint32_t o = w.order[0][j];
+				for (int a = 0; a < 3; a++) l[a] = orderedInt( w.lo[a][o] ), h[a] = orderedInt( w.hi[a][o] );
+				const int wt = (int)w.weight[o];
 				for (int a = 0; a < 3; a++)
 				{
-					const int b = max( 0, min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) ) );
+					const int b = max( 0, min( SAHB_BINS - 1, (int)((w.lo[a][o] + w.hi[a][o] - cmin[a]) * scale[a]) ) );
 					for (int k = 0; k < 3; k++) atomicMin( &w.binLo[a][b][k], l[k] ), atomicMax( &w.binHi[a][b][k], h[k] );
 					atomicAdd( &w.binWeight[a][b], wt ), atomicAdd( &w.binItems[a][b], 1 );
 				}
@@ -411,29 +417,25 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 				{
 					const uint32_t j = j0 + lane;
 					const bool have = j < begin + count;
-					const bool left = have && max( 0, min( SAHB_BINS - 1, (int)((w.lo[0][a][j] + w.hi[0][a][j] - cmin[a]) * scale[a]) ) ) <= b;
+					const uint32_t o = have ? w.order[0][j] : 0;
+					const bool left = have && max( 0, min( SAHB_BINS - 1, (int)((w.lo[a][o] + w.hi[a][o] - cmin[a]) * scale[a]) ) ) <= b;
 					const uint32_t ml = __ballot_sync( 0xffffffffu, left ), mr = __ballot_sync( 0xffffffffu, have && !left ), below = (1u << lane) - 1u;
 					if (have)
 					{
 						const uint32_t to = left ? begin + doneL + __popc( ml & below ) : begin + nl + doneR + __popc( mr & below );
-						w.ref[1][to] = w.ref[0][j], w.weight[1][to] = w.weight[0][j];
-						for (int x = 0; x < 3; x++) w.lo[1][x][to] = w.lo[0][x][j], w.hi[1][x][to] = w.hi[0][x][j];
+						w.order[1][to] = (uint16_t)o;
 					}
 					doneL += __popc( ml ), doneR += __popc( mr );
 				}
 				__syncwarp();
-				for (uint32_t j = begin + lane; j < begin + count; j += 32)
-				{
-					w.ref[0][j] = w.ref[1][j], w.weight[0][j] = w.weight[1][j];
-					for (int x = 0; x < 3; x++) w.lo[0][x][j] = w.lo[1][x][j], w.hi[0][x][j] = w.hi[1][x][j];
-				}
+				for (uint32_t j = begin + lane; j < begin + count; j += 32) w.order[0][j] = w.order[1][j];
 				__syncwarp();
 			}
 		}
 		if (wl == 0xffffffffu)
 		{
 			wl = 0;
-			for (uint32_t j = begin + lane; j < begin + nl; j += 32) wl += w.weight[0][j];
+			for (uint32_t j = begin + lane; j < begin + nl; j += 32) wl += w.weight[w.order[0][j]];
 			for (int d = 16; d; d >>= 1) wl += __shfl_xor_sync( 0xffffffffu, wl, d );
 		}
 		// ---- the node's links: a side with one item is that item, the others take the next spare indices
@@ -443,7 +445,7 @@ __global__ void __launch_bounds__( SAHB_WARPS * 32 ) sahbBuildKernel( const uint
 		if (nr > 1) { while (w.pool[nextPool] == root || w.pool[nextPool] == spareEnd) nextPool++; idR = w.pool[nextPool++]; }
 		if (lane == 0)
 		{
-			const uint32_t L = nl > 1 ? idL : w.ref[0][begin], R = nr > 1 ? idR : w.ref[0][begin + nl];
+			const uint32_t L = nl > 1 ? idL : w.ref[w.order[0][begin]], R = nr > 1 ? idR : w.ref[w.order[0][begin + nl]];
 			childL[id] = L, childR[id] = R, rangeCount[id] = weight;
 			if (L & LEAF) parentLeaf[L & ~LEAF] = id; else parentInner[L] = id;
 			if (R & LEAF) parentLeaf[R & ~LEAF] = id; else parentInner[R] = id;
@@ -583,24 +585,56 @@ __global__ void topSplitKernel( const uint32_t nAct, const TopNodes act, const T
 	const uint32_t id = act.id[a], begin = act.begin[a], count = act.count[a];
 	float bestCost = 3.0e38f;
 	uint32_t bestCand = 0xffffffffu, bestLeft = 0;
-	for (uint32_t t = lane; t < 3 * (TOP_BINS - 1); t += 32)
+	// every lane holds TOP_BINS / 32 neighbouring bins of the axis; the union of the bins up to a candidate (from the left) and of the
+	// bins behind it (from the right) are two warp scans, not a loop over the bins per candidate (which made this kernel the second longest
+	// of the build while the first levels have 1, 2, 4 ... nodes: profiles/r02_ncu_build.txt).  min / max: the order of the unions does
+	// not change a bit of them.
+	constexpr int PER = TOP_BINS / 32;
+	static_assert( TOP_BINS % 32 == 0, "topSplitKernel: a whole number of bins per lane" );
+	struct Part { float lo[3], hi[3]; int n; };
+	auto join = []( Part& x, const Part& y ) { for (int k = 0; k < 3; k++) x.lo[k] = fminf( x.lo[k], y.lo[k] ), x.hi[k] = fmaxf( x.hi[k], y.hi[k] ); x.n += y.n; };
+	auto shift = [lane]( const Part& x, const int d, const bool up ) {
+		Part y;
+		for (int k = 0; k < 3; k++)
+			y.lo[k] = up ? __shfl_up_sync( 0xffffffffu, x.lo[k], d ) : __shfl_down_sync( 0xffffffffu, x.lo[k], d ),
+			y.hi[k] = up ? __shfl_up_sync( 0xffffffffu, x.hi[k], d ) : __shfl_down_sync( 0xffffffffu, x.hi[k], d );
+		y.n = up ? __shfl_up_sync( 0xffffffffu, x.n, d ) : __shfl_down_sync( 0xffffffffu, x.n, d );
+		if (up ? (int)lane < d : (int)lane + d > 31) { for (int k = 0; k < 3; k++) y.lo[k] = 3.0e38f, y.hi[k] = -3.0e38f; y.n = 0; }
+		return y;
+	};
+	for (uint32_t ax = 0; ax < 3; ax++)
 	{
-		const uint32_t ax = t / (TOP_BINS - 1), b = t % (TOP_BINS - 1);
 		if (!(orderedFloat( act.cb[a * 6 + 3 + ax] ) > orderedFloat( act.cb[a * 6 + ax] ))) continue;
-		const uint32_t base = (a * 3 + ax) * TOP_BINS;
-		float ll[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, lh[3] = { -3.0e38f, -3.0e38f, -3.0e38f }, rl[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, rh[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
-		int cl = 0, cr = 0;
-		for (uint32_t k = 0; k < TOP_BINS; k++)
+		const uint32_t base = (a * 3 + ax) * TOP_BINS + lane * PER;
+		Part bin[PER], left[PER], right[PER];
+		for (int k = 0; k < PER; k++)
 		{
-			const int c = bins.count[base + k];
-			if (!c) continue;
-			if (k <= b) { cl += c; for (int x = 0; x < 3; x++) ll[x] = fminf( ll[x], orderedFloat( bins.lo[(base + k) * 3 + x] ) ), lh[x] = fmaxf( lh[x], orderedFloat( bins.hi[(base + k) * 3 + x] ) ); }
-			else { cr += c; for (int x = 0; x < 3; x++) rl[x] = fminf( rl[x], orderedFloat( bins.lo[(base + k) * 3 + x] ) ), rh[x] = fmaxf( rh[x], orderedFloat( bins.hi[(base + k) * 3 + x] ) ); }
+			bin[k].n = bins.count[base + k];
+			for (int x = 0; x < 3; x++)
+				bin[k].lo[x] = bin[k].n ? orderedFloat( bins.lo[(base + k) * 3 + x] ) : 3.0e38f, bin[k].hi[x] = bin[k].n ? orderedFloat( bins.hi[(base + k) * 3 + x] ) : -3.0e38f;
 		}
-		if (!cl || !cr) continue;
-		const float lx = lh[0] - ll[0], ly = lh[1] - ll[1], lz = lh[2] - ll[2], rx = rh[0] - rl[0], ry = rh[1] - rl[1], rz = rh[2] - rl[2];
-		const float cost = (lx * ly + ly * lz + lz * lx) * (float)cl + (rx * ry + ry * rz + rz * rx) * (float)cr;
-		if (cost < bestCost) bestCost = cost, bestCand = t, bestLeft = (uint32_t)cl;
+		// left[k] = bins 0 .. this lane's k-th, right[k] = this lane's k-th .. the last bin
+		left[0] = bin[0];
+		for (int k = 1; k < PER; k++) left[k] = left[k - 1], join( left[k], bin[k] );
+		right[PER - 1] = bin[PER - 1];
+		for (int k = PER - 2; k >= 0; k--) right[k] = right[k + 1], join( right[k], bin[k] );
+		Part fromLeft = left[PER - 1], fromRight = right[0]; // inclusive scans over the lanes' totals ...
+		for (int d = 1; d < 32; d <<= 1) { const Part l = shift( fromLeft, d, true ), r = shift( fromRight, d, false ); join( fromLeft, l ), join( fromRight, r ); }
+		const Part before = shift( fromLeft, 1, true ), after = shift( fromRight, 1, false ); // ... made exclusive
+		for (int k = 0; k < PER; k++) join( left[k], before ), join( right[k], after );
+		const Part nextRight = shift( right[0], 1, false ); // the suffix that starts at the next lane's first bin
+		for (int k = 0; k < PER; k++)
+		{
+			const uint32_t g = lane * PER + k; // the bins up to and including g go left
+			if (g >= TOP_BINS - 1) continue;
+			const Part& L = left[k];
+			const Part& R = k + 1 < PER ? right[k + 1 < PER ? k + 1 : 0] : nextRight;
+			if (!L.n || !R.n) continue;
+			const float lx = L.hi[0] - L.lo[0], ly = L.hi[1] - L.lo[1], lz = L.hi[2] - L.lo[2], rx = R.hi[0] - R.lo[0], ry = R.hi[1] - R.lo[1], rz = R.hi[2] - R.lo[2];
+			const float cost = (lx * ly + ly * lz + lz * lx) * (float)L.n + (rx * ry + ry * rz + rz * rx) * (float)R.n;
+			const uint32_t t = ax * (TOP_BINS - 1) + g;
+			if (cost < bestCost || (cost == bestCost && t < bestCand)) bestCost = cost, bestCand = t, bestLeft = (uint32_t)L.n;
+		}
 	}
 	for (int d = 16; d; d >>= 1)
 	{
@@ -1475,7 +1509,7 @@ __global__ void __launch_bounds__( 1024 ) tlasBuildKernel( const TlasInstanceInp
 #define B200_PLOC_RADIUS 16
 #endif
 cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, float4* tris, uint32_t nodeBase, uint32_t triBase, uint32_t maxNodes,
-	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount, int builder )
+	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount, int builder, void** keptScratch, size_t* keptBytes )
 {
 	cudaError_t e;
 	char* scratch = nullptr;
@@ -1521,7 +1555,27 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 		for (int k = 0; k < 2; k++) oTopNodes[k] = take( (size_t)topCap * 36 );
 		oTopBins = take( (size_t)topCap * 3 * TOP_BINS * 28 ), oTopSplit = take( (size_t)topCap * 16 ), oTopSmall = take( ((size_t)T / 2 + 2) * 16 ), oScan = take( scanBytes );
 	}
-	if ((e = cudaMallocAsync( (void**)&scratch, off, s )) != cudaSuccess) return e;
+	static const bool timing = getenv( "B200_BUILD_TIMING" ) != nullptr;
+	auto clockNow = [] { return std::chrono::duration<double, std::milli>( std::chrono::steady_clock::now().time_since_epoch() ).count(); };
+	double tMark = clockNow();
+	auto mark = [&]( const char* what ) { if (!timing) return; cudaStreamSynchronize( s ); const double t = clockNow(); fprintf( stderr, "  topology: %s %.2f ms\n", what, t - tMark ); tMark = t; };
+	// the caller may own the scratch (a core that rebuilds its meshes keeps it between builds: allocating and freeing 190 MB per million
+	// triangles was 10 of the 16 ms of a build); otherwise it lives for this call
+	const bool kept = keptScratch && keptBytes;
+	if (kept)
+	{
+		if (*keptBytes < off)
+		{
+			if (*keptScratch) cudaStreamSynchronize( s ), cudaFree( *keptScratch );
+			*keptScratch = nullptr, *keptBytes = 0;
+			if ((e = cudaMalloc( keptScratch, off )) != cudaSuccess) return e;
+			*keptBytes = off;
+		}
+		scratch = (char*)*keptScratch;
+	}
+	else if ((e = cudaMallocAsync( (void**)&scratch, off, s )) != cudaSuccess) return e;
+	if (timing) fprintf( stderr, "  topology: %.1f MB of scratch\n", off / 1048576.0 );
+	mark( "scratch allocation" );
 	float4 *primLo = (float4*)(scratch + oPrimLo), *primHi = (float4*)(scratch + oPrimHi), *nodeLo = (float4*)(scratch + oNodeLo), *nodeHi = (float4*)(scratch + oNodeHi);
 	float4 *planLo = (float4*)(scratch + oPlanLo), *planHi = (float4*)(scratch + oPlanHi);
 	uint64_t *keys = (uint64_t*)(scratch + oKeys), *keys2 = (uint64_t*)(scratch + oKeys2);
@@ -1530,7 +1584,7 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 	uint32_t *parI = (uint32_t*)(scratch + oParI), *parL = (uint32_t*)(scratch + oParL), *visits = (uint32_t*)(scratch + oVisits), *w2b = (uint32_t*)(scratch + oW2B);
 	int* cbounds = (int*)(scratch + oSmall);
 	uint32_t* counters = (uint32_t*)(scratch + oSmall + 64);
-	auto done = [&]( cudaError_t err ) { cudaFreeAsync( scratch, s ); return err; };
+	auto done = [&]( cudaError_t err ) { if (!kept) cudaFreeAsync( scratch, s ); return err; };
 
 	const int initBounds[6] = { 0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000 };
 	const uint32_t initCounters[4] = { 1, 0, 0, 0 }; // wide node 0 = the root is taken
@@ -1585,6 +1639,7 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 			nAct = h[0], nSmall = h[1], cur ^= 1;
 			if (nAct > topCap) return done( cudaErrorUnknown );
 		}
+		mark( "large nodes, level by level" );
 		if (nSmall)
 		{
 			static bool allowed = false;
@@ -1598,6 +1653,7 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 				nodeLo, nodeHi, order[cur], primLo, primHi, nodeCounter );
 		}
 		if (order[cur] != vals2) { uint32_t* t = vals; vals = vals2, vals2 = t; } // (what follows calls the final order vals2)
+		mark( "small subtrees" );
 		binaryBoxesKernel<<<blocks, 256, 0, s>>>( vals2, primLo, primHi, (int)T, childL, childR, count, parI, parL, nodeLo, nodeHi, planLo, planHi, g_sahPrimCost, visits );
 	}
 	else
@@ -1669,6 +1725,7 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 			cur ^= 1;
 		}
 	}
+	mark( "binary tree, boxes and plans" );
 	if ((e = cudaGetLastError()) != cudaSuccess) return done( e );
 	CollapseArgs a;
 	a.sortedPrim = vals2, a.childL = childL, a.childR = childR, a.rangeCount = count;
@@ -1703,6 +1760,7 @@ cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, fl
 		a.levelChildBase = h[0], a.levelPrimBase = h[1];
 	}
 	nodeCount = end;
+	mark( "collapse" );
 	return done( cudaSuccess );
 }
 

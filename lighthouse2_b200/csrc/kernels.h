@@ -71,7 +71,8 @@ cudaError_t LaunchRefitWalk( const RefitArgs& a, uint32_t nodeCount, const uint3
 
 // ---- GPU build of the wide-BVH topology (build.cu); the caller runs the refit afterwards -----------------------
 cudaError_t GpuBuildTopology( const float4* dVerts, uint32_t T, uint4* nodes, float4* tris, uint32_t nodeBase, uint32_t triBase, uint32_t maxNodes,
-	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount, int builder /* 1: Morton radix tree (LBVH), 2: agglomerative clustering along the curve (PLOC) */ );
+	cudaStream_t s, std::vector<uint32_t>& levelStart, uint32_t& nodeCount, int builder /* 1: Morton radix tree (LBVH), 2: agglomerative clustering along the curve (PLOC), 3: SAH inside the radix tree's cells, 4: binned SAH from the top */,
+	void** keptScratch = nullptr, size_t* keptBytes = nullptr /* scratch owned by the caller and reused between builds (grown as needed); null: allocated and freed inside */ );
 
 // ---- top-level build on the device (build.cu::tlasBuildKernel) -----------------------------------------------------------------
 // what the host hands over per instance (in instance-id order); the kernel derives world boxes, tree, instance records and the

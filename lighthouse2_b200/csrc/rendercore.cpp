@@ -143,6 +143,7 @@ RenderCore::~RenderCore()
 	for (DeviceBuffer* b : all) b->release();
 	for (MeshRec& m : meshes) m.refitParents.release(), m.refitArrived.release(), m.refitStash.release();
 	tlasStage.release();
+	if (buildScratch) cudaFree( buildScratch );
 	for (int i = 0; i < WAVE_SLOTS; i++) rayO[i].release(), rayD[i].release(), hitBuf[i].release(), bitBuf[i].release();
 	if (evA) cudaEventDestroy( evA );
 	if (evB) cudaEventDestroy( evB );
@@ -280,24 +281,34 @@ int RenderCore::buildOnDevice( int meshIdx, const float* vertexData, uint32_t T,
 	if (coreTris) e = cudaMemcpyAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, shade.data(), (size_t)T * 16, cudaMemcpyHostToDevice, stream );
 	else e = cudaMemsetAsync( (char*)shadePool.ptr + (size_t)m.triBase * 16, 0, (size_t)T * 16, stream );
 	if (e != cudaSuccess) return fail( "shading upload", e );
+	// B200_BUILD_TIMING=1: where the time of a device build goes (each mark waits for the stream)
+	static const bool timing = getenv( "B200_BUILD_TIMING" ) != nullptr;
+	double tMark = nowMs();
+	auto mark = [&]( const char* what ) { if (!timing) return; cudaStreamSynchronize( stream ); const double t = nowMs(); fprintf( stderr, "device build, %u triangles: %s %.2f ms\n", T, what, t - tMark ); tMark = t; };
+	if (timing) fprintf( stderr, "device build, %u triangles: host side before the upload %.2f ms\n", T, tMark - t0 );
+	mark( "pools + upload" );
 	e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
-		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild );
+		m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild, &buildScratch, &buildScratchBytes );
+	mark( "topology" );
 	if (e == cudaErrorMemoryAllocation)
 	{
 		cudaGetLastError();
 		maxNodes = T + 64;
 		if ((e = nodePool.reserve( (size_t)(m.nodeBase + maxNodes + 64) * 80, true, stream )) != cudaSuccess) return fail( "node pool", e );
 		e = GpuBuildTopology( (const float4*)vertStage.ptr, T, (uint4*)((char*)nodePool.ptr + (size_t)m.nodeBase * 80), (float4*)((char*)triPool.ptr + (size_t)m.triBase * 48),
-			m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild );
+			m.nodeBase, m.triBase, maxNodes, stream, m.levelStart, m.nodeCount, gpuBuild, &buildScratch, &buildScratchBytes );
 	}
 	if (e != cudaSuccess) return fail( "GPU BVH build", e );
 	if ((int)m.levelStart.size() - 1 > MAX_TREE_LEVELS) return fail( "SetGeometry: the device-built tree is deeper than the traversal stack allows (wide_bvh.h MAX_TREE_LEVELS)" );
 	if (prepareRefit( m )) return 1;
+	mark( "refit links" );
 	m.built = true;
 	blasNodeEnd = m.nodeBase + m.nodeCount, triEnd = m.triBase + T;
 	meshes.push_back( m );
 	if (uploadVertexNormals( m, coreTris )) return 1;
 	if (RefitDevice( meshIdx, vertStage.ptr, (int)(3 * T), false )) return 1; // boxes, planes, triangle records; fetches the root box
+	mark( "attributes + refit" );
+	if (!keepBuildScratch && buildScratch) cudaStreamSynchronize( stream ), cudaFree( buildScratch ), buildScratch = nullptr, buildScratchBytes = 0;
 	stats.bvhBuildTime += (float)(nowMs() - t0);
 	stats.wideNodeCount = blasNodeEnd, stats.triangleCount = triEnd;
 	return 0;
@@ -323,7 +334,8 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 			return fail( "SetGeometry: changing the triangle count is only supported for the most recently added mesh" );
 		if (meshIdx != (int)meshes.size() - 1 && !allowRefit)
 			return fail( "SetGeometry: rebuild (refit=0) is only supported for the most recently added mesh" );
-		// rebuild of the last mesh: drop it and fall through to a fresh build
+		// rebuild of the last mesh: drop it and fall through to a fresh build (a scene that does this once will do it again: the builder's scratch stays)
+		keepBuildScratch = true;
 		blasNodeEnd = meshes[meshIdx].nodeBase, triEnd = meshes[meshIdx].triBase;
 		meshes.back().refitParents.release(), meshes.back().refitArrived.release(), meshes.back().refitStash.release();
 		meshes.pop_back();

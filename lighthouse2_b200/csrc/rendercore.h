@@ -157,6 +157,8 @@ private:
 	bool refitWalk = true; // Setting refitWalk: the refit is one launch that climbs the tree (1) or one launch per level (0)
 	int prepareRefit( MeshRec& m );
 	bool countSteps = false, allowRefit = true;
+	void* buildScratch = nullptr; size_t buildScratchBytes = 0; // scratch of the device builder, kept between builds once a mesh has been REbuilt (dynamic scenes), freed after the build otherwise
+	bool keepBuildScratch = false;
 	int gpuBuild = 4; // new meshes get their tree built on the device (build.cu): 4 = binned SAH from the top (default), 3 = SAH inside the cells of a Morton radix tree, 1 = the radix tree itself (LBVH), 2 = agglomerative clustering (PLOC); 0 = the host builder (bvh_builder.cpp)
 	bool zeroCopy = true, twoStreams = true; int pinnedChunks = 1, zeroCopyBelow = 400000; // pinned host ray planes are fetched by the kernel itself (Setting zeroCopy / pinnedChunks)
 	bool singleInstanceShortcut = true; // a one-instance scene skips the top-level node (Setting singleInstanceShortcut)

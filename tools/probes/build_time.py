@@ -20,4 +20,13 @@ for gen in (scenes.sphere_field, scenes.triangle_soup):
         best = min(best, time.perf_counter() - t0)
         n = rc.GetCoreStats()["wideNodeCount"]
         rc.Shutdown()
-    print("%s %d triangles: %.2f ms, %d wide nodes" % (gen.__name__, verts.shape[0], best * 1e3, n))
+    # a scene that rebuilds: the same core, the triangle count changes from call to call (so SetGeometry cannot refit)
+    rc = core.RenderCoreB200(0)
+    rc.SetGeometry(0, v4)
+    again = 1e9
+    for k in range(6):
+        t0 = time.perf_counter()
+        rc.SetGeometry(0, v4[:-3] if k % 2 == 0 else v4)
+        again = min(again, time.perf_counter() - t0)
+    rc.Shutdown()
+    print("%s %d triangles: fresh core %.2f ms, rebuild in the same core %.2f ms, %d wide nodes" % (gen.__name__, verts.shape[0], best * 1e3, again * 1e3, n))
