@@ -115,6 +115,8 @@ def c3(frames, n_tris=10_000_000, gpu_build=0):
 
 def c4(frames, n_inst=1000, n_tris=100_000):
     rc = core.RenderCoreB200(0)
+    for k, v in EXTRA_SETTINGS:
+        rc.Setting(k, float(v))
     rc.SetGeometry(0, scenes.deforming_sphere(n_tris, time=0.0))
     M = scenes.lattice_transforms(n_inst, spacing=8.0, time=0.0)
     for i in range(n_inst):
