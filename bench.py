@@ -8,7 +8,7 @@ sphere field, 1 000 000 triangles) at the size of BASELINE.json configs[4]: 3840
 timed at every N (strong scaling): with N ranks the frame is sharded by interleaved 32x8 tiles (scene replicated), and every frame ends
 with the gather of the accumulator over NVLink (one fused peer-memory pull + finalize kernel, wavefront.cu).
   value  = rays of the frame (all ranks) / time of the slowest rank (CUDA events on the core's stream, barrier + synchronize on both sides)
-  e2e    = the same frames through the host-facing calls b200_render (which ends with the gather) + b200_read_frame: the view pyramid goes in
+  e2e    = the same frames through the host-facing calls b200_render (which ends with the gather) + b200_read_frame_async: the view pyramid goes in
            from host memory, the finished RGBA32F frame comes back into pinned host memory, both inside the timed region
   check  = every rank renders the frame once unsharded and compares its gathered accumulator with it bit for bit
 Sub-blocks (explanation, not the headline):
@@ -492,27 +492,40 @@ def run_b200(args):
     launches = st["kernelLaunches"] - launches0
 
     # ---- e2e: the same frames with the finished frame read back into pinned host memory every step -------------------
-    e2e_ms = None
+    e2e_ms = e2e_blocking_ms = None
     frame_bytes = W * H * 16
     if not args.no_e2e:
-        host_frame = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+        host_frames = [torch.empty((H, W, 4), dtype=torch.float32).pin_memory() for _ in range(2)]
         e2e_steps = max(3, min(args.steps, 10))
 
-        def e2e_frame():
-            frame()
-            if rank == 0:  # the application (RenderSystem) lives on rank 0 and takes the frame from there
-                chk(lib.b200_read_frame(h, host_frame.data_ptr()))
-        e2e_frame()
-        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        ea.record(stream)
-        for _ in range(e2e_steps):
-            e2e_frame()
-        eb.record(stream)
-        barrier()
-        e2e_ms = ea.elapsed_time(eb) / e2e_steps
+        # every step: Render() (the view pyramid and the pass parameters go up) and the finished frame into page-locked host memory on rank 0, where
+        # the application (RenderSystem) lives.  b200_read_frame_async lets frame k travel while frame k + 1 renders (two host buffers, as a
+        # display loop would hold them); the timed region ends when the last frame has arrived.  The blocking call is timed beside it.
+        def e2e_run(blocking):
+            def step(k):
+                frame()
+                if rank == 0:
+                    if blocking:
+                        chk(lib.b200_read_frame(h, host_frames[k & 1].data_ptr()))
+                    else:
+                        chk(lib.b200_read_frame_async(h, host_frames[k & 1].data_ptr()))
+            step(0)
+            chk(lib.b200_wait_frame(h))
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            ea.record(stream)
+            for k in range(e2e_steps):
+                step(k)
+            chk(lib.b200_wait_frame(h))
+            eb.record(stream)
+            barrier()
+            return ea.elapsed_time(eb) / e2e_steps
+        e2e_blocking_ms = e2e_run(True)
+        e2e_ms = e2e_run(False)
         if rank == 0:
-            assert np.isfinite(host_frame.numpy()).all() and float(host_frame[..., :3].mean()) > 0.01
+            for hf in host_frames:
+                assert np.isfinite(hf.numpy()).all() and float(hf[..., :3].mean()) > 0.01
+            assert torch.equal(host_frames[0], host_frames[1])  # (the same view, the same samples: restarted frames)
 
     # ---- reduce over ranks: slowest rank's time, all ranks' rays ------------------------------------------------
     vec = torch.tensor([total_ms, e2e_ms or 0.0, render_ms, gather_ms, gather_kernel_ms, wall_ms], device=dev, dtype=torch.float64)
@@ -563,7 +576,10 @@ def run_b200(args):
         if e2e_ms:
             line["e2e"] = {"value": rays_per_frame / (vec[1] * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 68 + 96 * st["framePasses"],
                            "d2h_bytes_per_step": frame_bytes, "ms_per_step": vec[1],
-                           "api": "b200_render (ViewPyramid from host memory; ends with the peer-memory gather when N > 1) + b200_read_frame into pinned host memory (rank 0): what the RenderSystem "
+                           "blocking_read": {"ms_per_step": e2e_blocking_ms, "value": rays_per_frame / (e2e_blocking_ms * 1e-3) / 1e6,
+                                             "note": "b200_read_frame after every b200_render (rank 0's clock): the frame crosses the bus before the next one starts"},
+                           "api": "b200_render (ViewPyramid from host memory; ends with the peer-memory gather when N > 1) + b200_read_frame_async into two alternating pinned host buffers "
+                                  "(rank 0; frame k travels while frame k + 1 renders, b200_wait_frame closes the timed region): what the RenderSystem "
                                   "sees through CoreAPI::Render; the C++ vtable face forwards to the same calls (tests/test_plugin_gpu.py)",
                            "note": "inputs of this path are a 68-byte view pyramid plus 96 bytes of pass parameters per pass; the output is the finished RGBA32F frame"}
         if waves_out:

@@ -158,6 +158,11 @@ B200_API int b200_render( b200_core* c, const void* viewPyramid, int converge );
 /* accumulator float4[w*h] (sum over samples; w = sample count) and the normalised RGBA32F frame */
 B200_API int b200_read_accumulator( b200_core* c, float* dst );
 B200_API int b200_read_frame( b200_core* c, float* dst );
+/* the same without waiting: the frame leaves on a stream of its own (dst: page-locked host memory, or the copy is not asynchronous) while the next
+ * b200_render runs; b200_wait_frame returns when the last frame asked for has arrived.  (The reference presents through a GL texture,
+ * rendercore.cpp:857-870: a host that wants the pixels has no faster way there either.) */
+B200_API int b200_read_frame_async( b200_core* c, float* dst );
+B200_API int b200_wait_frame( b200_core* c );
 B200_API void* b200_device_accumulator( b200_core* c ); /* device pointer, for NCCL gathers by the host layer */
 /* stats: the CoreStats fields (core_api_base.h:30-61) flattened; see struct below */
 typedef struct b200_stats {

@@ -22,7 +22,7 @@ C_ABI_SYMBOLS = [
     "b200_create", "b200_destroy", "b200_last_error", "b200_set_stream", "b200_set_geometry", "b200_set_instance",
     "b200_update_toplevel", "b200_refit", "b200_refit_device", "b200_setting", "b200_trace_closest", "b200_trace_any",
     "b200_trace_closest_device", "b200_trace_any_device", "b200_read_step_counters", "b200_read_tree", "b200_set_target",
-    "b200_set_point_light", "b200_set_sky", "b200_set_lights", "b200_set_sky_data", "b200_render", "b200_read_accumulator", "b200_read_frame",
+    "b200_set_point_light", "b200_set_sky", "b200_set_lights", "b200_set_sky_data", "b200_render", "b200_read_accumulator", "b200_read_frame", "b200_read_frame_async", "b200_wait_frame",
     "b200_device_accumulator", "b200_get_stats", "b200_set_probe", "b200_plugin_core", "b200_host_alloc",
     "b200_host_free", "CreateCore", "DestroyCore", "b200_set_materials", "b200_set_material_colors", "b200_set_material_table", "b200_set_textures",
     "b200_disney_probe", "b200_set_blue_noise",
@@ -92,7 +92,7 @@ def load_library() -> C.CDLL:
         "b200_read_step_counters": ([vp, ip, vp, vp], ip), "b200_read_tree": ([vp, ip, vp, C.c_size_t], ip),
         "b200_set_target": ([vp, ip, ip, ip], ip), "b200_set_point_light": ([vp, vp, vp], ip), "b200_set_sky": ([vp, vp], ip),
         "b200_set_lights": ([vp, vp, ip, vp, ip, vp, ip, vp, ip], ip), "b200_set_sky_data": ([vp, vp, ip, ip], ip),
-        "b200_render": ([vp, vp, ip], ip), "b200_read_accumulator": ([vp, vp], ip), "b200_read_frame": ([vp, vp], ip),
+        "b200_render": ([vp, vp, ip], ip), "b200_read_accumulator": ([vp, vp], ip), "b200_read_frame": ([vp, vp], ip), "b200_read_frame_async": ([vp, vp], ip), "b200_wait_frame": ([vp], ip),
         "b200_device_accumulator": ([vp], vp), "b200_get_stats": ([vp, C.POINTER(Stats)], ip), "b200_set_probe": ([vp, ip, ip], ip),
         "b200_plugin_core": ([], vp), "b200_host_alloc": ([C.c_uint64], vp), "b200_host_free": ([vp], None),
         "b200_set_materials": ([vp, vp, ip], ip), "b200_set_material_colors": ([vp, vp, ip], ip), "b200_set_material_table": ([vp, vp, ip], ip), "b200_set_textures": ([vp, vp, ip], ip),
@@ -495,6 +495,13 @@ class RenderCoreB200:
         out = np.empty((self.height, self.width, 4), np.float32)
         self._chk(self.lib.b200_read_frame(self.h, out.ctypes.data))
         return out
+
+    def ReadFrameAsync(self, dst_ptr: int):
+        """The frame leaves for `dst_ptr` (page-locked host memory, width * height float4) beside the next Render(); WaitFrame() before it is read."""
+        self._chk(self.lib.b200_read_frame_async(self.h, dst_ptr))
+
+    def WaitFrame(self):
+        self._chk(self.lib.b200_wait_frame(self.h))
 
     def DeviceAccumulator(self) -> int:
         return self.lib.b200_device_accumulator(self.h) or 0

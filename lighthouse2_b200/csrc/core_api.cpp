@@ -126,6 +126,8 @@ int b200_trace_connect_device( b200_core* c, const void* dO4, const void* dD4, i
 int b200_render( b200_core* c, const void* view, int converge ) { FORWARD( c, Render( view, converge ) ) }
 int b200_read_accumulator( b200_core* c, float* dst ) { FORWARD( c, ReadAccumulator( dst ) ) }
 int b200_read_frame( b200_core* c, float* dst ) { FORWARD( c, ReadFrame( dst ) ) }
+int b200_read_frame_async( b200_core* c, float* dst ) { FORWARD( c, ReadFrameAsync( dst ) ) }
+int b200_wait_frame( b200_core* c ) { FORWARD( c, WaitFrame() ) }
 int b200_read_filter_buffer( b200_core* c, int which, void* dst ) { FORWARD( c, ReadFilterBuffer( which, dst ) ) }
 void* b200_device_accumulator( b200_core* c ) { return (c && c->rc) ? c->rc->DeviceAccumulator() : nullptr; }
 int b200_get_stats( b200_core* c, b200_stats* out ) { GUARD( c ) if (!out) { gLastError = "null stats"; return 1; } c->rc->GetStats( out ); return 0; }

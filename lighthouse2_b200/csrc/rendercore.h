@@ -86,6 +86,8 @@ public:
 	int Render( const void* viewPyramid, int converge );
 	int ReadAccumulator( float* dst );
 	int ReadFrame( float* dst );
+	int ReadFrameAsync( float* dst );
+	int WaitFrame();
 	int ReadFilterBuffer( int which, void* dst ); // the per-pixel buffers of the last filtered frame (wavefront.cu)
 	void* DeviceAccumulator();
 	int SetProbe( int x, int y );

@@ -380,3 +380,28 @@ def test_lens_and_distortion_match_cpu_restatement():
     mean = float(ref[..., :3].mean())
     assert float(np.sqrt(np.mean((acc[..., :3] - ref[..., :3]) ** 2))) <= 2e-2 * mean
     rc.Shutdown()
+
+
+def test_async_frame_readback_equals_the_blocking_one():
+    """b200_read_frame_async / b200_wait_frame: the frame leaves beside the next Render().  Two frames in a row into two page-locked
+    buffers, the second asked for while the first may still be on the bus; both equal what the blocking call returns."""
+    import torch
+    rc = core.RenderCoreB200(0)
+    rc.SetGeometry(0, scenes.sphere_field(20_000)); rc.SetInstance(0, 0); rc.SetInstance(1, -1); rc.UpdateToplevel()
+    w, h = 320, 180
+    rc.SetTarget(w, h, 2); rc.SetPointLight((0.5, 30.0, -10.0), (4e3, 3.6e3, 3e3)); rc.SetSky((0.3, 0.4, 0.6)); rc.Setting("maxPathLength", 3)
+    views = [scenes.view_pyramid(width=w, height=h, **scenes.C2_CAMERA), scenes.view_pyramid(width=w, height=h, **dict(scenes.C2_CAMERA, fov_deg=35.0))]
+    want = []
+    for v in views:
+        rc.Render(v, converge=1)
+        want.append(rc.ReadFrame())
+    bufs = [torch.empty((h, w, 4), dtype=torch.float32).pin_memory() for _ in views]
+    for v, b in zip(views, bufs):
+        rc.Render(v, converge=1)
+        rc.ReadFrameAsync(b.data_ptr())
+    rc.WaitFrame()
+    rc.WaitFrame()  # (nothing pending: returns at once)
+    for b, wnt in zip(bufs, want):
+        assert np.array_equal(b.numpy().view(np.uint32), wnt.view(np.uint32))
+    assert not np.array_equal(want[0], want[1]) and want[0][..., :3].mean() > 0.01
+    rc.Shutdown()
