@@ -60,6 +60,7 @@ struct RefitArgs {
 	float4* shade;             // pool: (geometric normal, material bits) per ORIGINAL primitive of every mesh; normals are refreshed
 	uint32_t nodeBase;         // absolute index of the mesh root in the pool
 	uint32_t triBase, triCount;
+	const uint2* leafInfo;     // per leaf-order triangle of this mesh: (original primitive, the shading record's .w), LaunchRefitLeafInfo; null: read from the records
 };
 cudaError_t LaunchRefitTop( const RefitArgs& a, const uint32_t* levelStart, int nTop, cudaStream_t s ); // levels [0,nTop) in one launch
 cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t levelEnd, cudaStream_t s );
@@ -67,6 +68,7 @@ cudaError_t LaunchRefitLevel( const RefitArgs& a, uint32_t levelBegin, uint32_t 
 // topology by LaunchRefitParents (nodes = pool pointer, nodeBase = the mesh's root), which also leaves in *stashCount (device) the number of
 // nodes with inner children; stash = 16 float4 (the eight slot boxes) for each of those
 cudaError_t LaunchRefitParents( const uint4* nodes, uint32_t nodeBase, uint32_t nodeCount, uint32_t* parentInfo, uint32_t* arrived, uint32_t* stashOf, uint32_t* stashCount, cudaStream_t s );
+cudaError_t LaunchRefitLeafInfo( const float4* tris, const float4* shade, uint32_t triBase, uint32_t triCount, uint2* out, cudaStream_t s );
 cudaError_t LaunchRefitWalk( const RefitArgs& a, uint32_t nodeCount, const uint32_t* parentInfo, uint32_t* arrived, const uint32_t* stashOf, float4* stash, cudaStream_t s );
 
 // ---- GPU build of the wide-BVH topology (build.cu); the caller runs the refit afterwards -----------------------

@@ -59,10 +59,18 @@ __device__ __forceinline__ void leafSlotBox( const RefitArgs& a, const uint4 n1,
 {
 	const uint32_t cnt = __popc( meta >> 5 ), first = n1.y + (meta & 31u);
 	float4* const tp0 = a.tris + (size_t)first * 3;
-	uint32_t prims[3];
+	uint32_t prims[3], words[3] = { 0, 0, 0 };
 	float4 v[3][3];
+	// which triangle sits in a record and what its shading record carries beside the normal come from a leaf-order copy made when the
+	// tree was placed (8 bytes per triangle, neighbouring lanes read neighbouring entries) -- not from the 48-byte records and the
+	// shading records themselves, which would cost a 32-byte sector each for 4 bytes
+	const uint2* li = a.leafInfo ? a.leafInfo + (first - a.triBase) : nullptr;
 #pragma unroll
-	for (uint32_t k = 0; k < 3; k++) prims[k] = k < cnt ? __float_as_uint( tp0[k * 3].w ) : 0u;
+	for (uint32_t k = 0; k < 3; k++)
+	{
+		prims[k] = 0;
+		if (k < cnt) { if (li) { const uint2 e = __ldg( li + k ); prims[k] = e.x, words[k] = e.y; } else prims[k] = __float_as_uint( tp0[k * 3].w ); }
+	}
 #pragma unroll
 	for (uint32_t k = 0; k < 3; k++) if (k < cnt)
 	{
@@ -84,7 +92,7 @@ __device__ __forceinline__ void leafSlotBox( const RefitArgs& a, const uint4 n1,
 			float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
 			const float l2 = nx * nx + ny * ny + nz * nz, il = l2 > 0 ? 1.0f / sqrtf( l2 ) : 0.f;
 			float4* sp = a.shade + a.triBase + prim;
-			*sp = make_float4( nx * il, ny * il, nz * il, sp->w );
+			*sp = make_float4( nx * il, ny * il, nz * il, li ? __uint_as_float( words[k] ) : sp->w );
 		}
 		lo[0] = fminf( lo[0], fminf( p0.x, fminf( p1.x, p2.x ) ) ), lo[1] = fminf( lo[1], fminf( p0.y, fminf( p1.y, p2.y ) ) );
 		lo[2] = fminf( lo[2], fminf( p0.z, fminf( p1.z, p2.z ) ) );
@@ -170,6 +178,15 @@ __global__ void __launch_bounds__( 1024 ) refitTopKernel( const RefitArgs a, con
 	}
 }
 
+// leaf-order copy of (primitive index, the word the shading record carries beside the normal) for leafSlotBox
+__global__ void refitLeafInfoKernel( const float4* __restrict__ tris, const float4* __restrict__ shade, const uint32_t triBase, const uint32_t triCount, uint2* __restrict__ out )
+{
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= triCount) return;
+	const uint32_t prim = __float_as_uint( tris[(size_t)(triBase + j) * 3].w );
+	out[j] = make_uint2( prim, shade ? __float_as_uint( shade[triBase + prim].w ) : 0u );
+}
+
 // parentInfo[n] = parent of node n (relative to the mesh's root; NO_PARENT for the root) | number of inner children of that parent << 28;
 // stashOf[n] = a dense number for every node WITH inner children (its place in the walk's slot-box stash); *stashCount = how many
 constexpr uint32_t NO_PARENT = 0x0fffffffu;
@@ -191,7 +208,10 @@ __global__ void refitParentsKernel( const uint4* __restrict__ nodes, const uint3
 // A node without inner children is finished with that.  A node WITH inner children parks its leaf-slot boxes in the stash and counts as
 // one more arrival at itself; whoever arrives last at a node -- its own group or the group that brings the last child -- finishes it
 // (child boxes from the scratch boxes, leaf-slot boxes from the stash) and goes on to the parent.
-__global__ void __launch_bounds__( 256, 4 ) refitWalkKernel( const RefitArgs a, const uint32_t nodeCount, const uint32_t* __restrict__ parentInfo, uint32_t* arrived,
+#ifndef REFIT_MIN_BLOCKS
+#define REFIT_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__( 256, REFIT_MIN_BLOCKS ) refitWalkKernel( const RefitArgs a, const uint32_t nodeCount, const uint32_t* __restrict__ parentInfo, uint32_t* arrived,
 	const uint32_t* __restrict__ stashOf, float4* stash )
 {
 	const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, s = lane & 7;
@@ -274,6 +294,13 @@ cudaError_t LaunchRefitParents( const uint4* nodes, uint32_t nodeBase, uint32_t 
 	cudaError_t e = cudaMemsetAsync( stashCount, 0, 4, s );
 	if (e != cudaSuccess) return e;
 	refitParentsKernel<<<(nodeCount + 255) / 256, 256, 0, s>>>( nodes, nodeBase, nodeCount, parentInfo, arrived, stashOf, stashCount );
+	return cudaGetLastError();
+}
+
+cudaError_t LaunchRefitLeafInfo( const float4* tris, const float4* shade, uint32_t triBase, uint32_t triCount, uint2* out, cudaStream_t s )
+{
+	if (!triCount) return cudaSuccess;
+	refitLeafInfoKernel<<<(triCount + 255) / 256, 256, 0, s>>>( tris, shade, triBase, triCount, out );
 	return cudaGetLastError();
 }
 

@@ -141,7 +141,7 @@ RenderCore::~RenderCore()
 	DeviceBuffer* all[] = { &fetchCounter, &nodePool, &triPool, &instPool, &shadePool, &vnormPool, &instShadePool, &vertStage, &nodeLo, &nodeHi,
 		&stepNodes, &stepTris, &tlasIn, &tlasScratch, &tlasInfo };
 	for (DeviceBuffer* b : all) b->release();
-	for (MeshRec& m : meshes) m.refitParents.release(), m.refitArrived.release(), m.refitStash.release();
+	for (MeshRec& m : meshes) m.refitParents.release(), m.refitArrived.release(), m.refitStash.release(), m.refitLeafInfo.release();
 	tlasStage.release();
 	if (buildScratch) cudaFree( buildScratch );
 	for (int i = 0; i < WAVE_SLOTS; i++) rayO[i].release(), rayD[i].release(), hitBuf[i].release(), bitBuf[i].release();
@@ -337,7 +337,7 @@ int RenderCore::SetGeometry( int meshIdx, const float* vertexData, int vertexCou
 		// rebuild of the last mesh: drop it and fall through to a fresh build (a scene that does this once will do it again: the builder's scratch stays)
 		keepBuildScratch = true;
 		blasNodeEnd = meshes[meshIdx].nodeBase, triEnd = meshes[meshIdx].triBase;
-		meshes.back().refitParents.release(), meshes.back().refitArrived.release(), meshes.back().refitStash.release();
+		meshes.back().refitParents.release(), meshes.back().refitArrived.release(), meshes.back().refitStash.release(), meshes.back().refitLeafInfo.release();
 		meshes.pop_back();
 	}
 	const double t0 = nowMs();
@@ -437,6 +437,10 @@ int RenderCore::prepareRefit( MeshRec& m )
 	if ((e = cudaMemcpyAsync( &innerNodes, links + 2 * n1, 4, cudaMemcpyDeviceToHost, stream )) != cudaSuccess || (e = cudaStreamSynchronize( stream )) != cudaSuccess)
 		return fail( "refit links", e );
 	if ((e = m.refitStash.reserve( ((size_t)innerNodes + 1) * 256, false, stream )) != cudaSuccess) return fail( "refit stash", e );
+	// leaf-order copy of what the refit needs of the records it rewrites (the triangle records carry the primitive indices, the shading records the material words, by now)
+	if ((e = m.refitLeafInfo.reserve( ((size_t)m.triCount + 1) * 8, false, stream )) != cudaSuccess) return fail( "refit leaf info", e );
+	if ((e = LaunchRefitLeafInfo( (const float4*)triPool.ptr, (const float4*)shadePool.ptr, m.triBase, m.triCount, (uint2*)m.refitLeafInfo.ptr, stream )) != cudaSuccess) return fail( "refit leaf info", e );
+	stats.kernelLaunches++;
 	return 0;
 }
 
@@ -452,6 +456,7 @@ int RenderCore::RefitDevice( int meshIdx, const void* dVerts, int vertexCount, b
 	a.nodes = (uint4*)nodePool.ptr, a.tris = (float4*)triPool.ptr, a.verts = (const float4*)dVerts;
 	a.nodeLo = (float4*)nodeLo.ptr, a.nodeHi = (float4*)nodeHi.ptr, a.shade = (float4*)shadePool.ptr;
 	a.nodeBase = m.nodeBase, a.triBase = m.triBase, a.triCount = m.triCount;
+	a.leafInfo = (const uint2*)m.refitLeafInfo.ptr;
 	cudaEventRecord( evA, stream );
 	if (refitWalk && m.refitParents.ptr)
 	{

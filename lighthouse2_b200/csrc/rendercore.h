@@ -39,6 +39,7 @@ struct MeshRec {
 	std::vector<uint32_t> levelStart; // relative to nodeBase
 	Aabb bounds;                      // object-space bounds of the current vertex positions
 	bool built = false;
+	DeviceBuffer refitLeafInfo; // (primitive, shading word) per leaf-order triangle, see refit.cu::leafSlotBox
 	DeviceBuffer refitStash; // slot boxes of the nodes with inner children (16 float4 each), see refit.cu::refitWalkKernel
 	DeviceBuffer refitParents, refitArrived; // per node: parent | inner children of the parent << 28; arrival counter (refit.cu::refitWalkKernel)
 };
