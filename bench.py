@@ -552,7 +552,7 @@ def run_b200(args):
                                     % (world, "fused peer-memory pull + finalize kernel" if p2p else "NCCL all-reduce")) if world > 1 else "1 GPU, no sharding",
                        "l2": "no flush: the path buffers of one pass (%.1f GB of rays, hits, path state and contribution slots per rank) exceed the 126 MB L2 many times over; "
                              "the scene (%.0f MB nodes + %.0f MB triangles) is meant to stay L2-resident"
-                             % (min(32 << 20, W * H * spp / world) * 272 / 1e9, st["wideNodeCount"] * 80 / 1e6, st["triangleCount"] * 48 / 1e6),
+                             % (W * H * spp / world / max(1, st["framePasses"]) * 272 / 1e9, st["wideNodeCount"] * 80 / 1e6, st["triangleCount"] * 48 / 1e6),
                        "rays_per_frame": rays_per_frame, "passes_per_frame": st["framePasses"], "wave_chains": st["frameChains"],
                        "frame_graph_replays": st["frameGraphLaunches"], "wide_nodes": st["wideNodeCount"], "bvh_build_s": round(build_s, 2),
                        "timed_region_wall_s": vec[5] * 1e-3},

@@ -1213,7 +1213,7 @@ struct WavefrontState {
 	int useGraph = 1;      // Setting frameGraph: a frame whose plan repeats is replayed as a CUDA graph
 	int waveTimers = 1;    // Setting waveTimers: per-wave CUDA events for the CoreStats trace / shade times
 	int gatherInRender = 1; // Setting gatherInRender: with open peers, a tile-sharded Render() ends with the peer-memory gather
-	uint32_t pathsPerPass = 32u << 20;
+	uint32_t pathsPerPass = 128u << 20; // (272 B of path buffers each, allocated for what a frame needs: the 4K x 16 spp frame is one pass of 133 M paths and 36 GB; with 32 Mi it ran 1.2 % slower in four)
 	Chain chain[MAX_CHAINS];
 	DeviceBuffer counters, passParams, accumOwn, frame, materials, lights, skyImage, texels, blueNoise;
 	PinnedBuffer hostPass, hostCounters;
